@@ -1,0 +1,213 @@
+/*
+ * flowstep.h — C-ABI of libflowstep.so, the B200 batched traffic-microsimulation
+ * step engine that stands in for Flow's per-vehicle Python/SUMO loop.
+ *
+ * Every entry point replaces a piece of the reference interface (paths are
+ * relative to the reference checkout, parthjaggi/flow):
+ *
+ *   fs_create / fs_destroy   Kernel(simulator, sim_params) + start_simulation
+ *                            flow/core/kernel/kernel.py:48-78,
+ *                            flow/core/kernel/simulation/traci.py:70-174
+ *   fs_set_types             VehicleParams.add(...) controller/param tables
+ *                            flow/core/params.py:236-351,
+ *                            flow/core/kernel/vehicle/traci.py:261-372
+ *   fs_reset                 Env.reset + WaveAttenuationEnv.reset + warm-up
+ *                            flow/envs/base.py:414-560,
+ *                            flow/envs/ring/wave_attenuation.py:157-210,
+ *                            flow/core/kernel/network/base.py:263-391
+ *   fs_step / fs_step_host   Env.step (controllers, fail-safes, apply_acceleration,
+ *                            simulation_step, k.update, get_state, compute_reward)
+ *                            flow/envs/base.py:294-412
+ *   fs_buffers               KernelVehicle getters (get_speed, get_position,
+ *                            get_lane, get_headway, get_leader, get_follower)
+ *                            flow/core/kernel/vehicle/traci.py:541-602
+ *   fs_set_state             TraCIVehicle.test_set_speed / set_headway hooks
+ *                            flow/core/kernel/vehicle/traci.py:411-425,639-689
+ *   fs_stats                 Experiment.run return/velocity bookkeeping
+ *                            flow/core/experiment.py:123-176
+ *
+ * Conventions: every call returns 0 on success or a negative FS_E* code;
+ * fs_last_error() gives the message. The engine owns all device memory;
+ * pointers handed out by fs_buffers stay valid until fs_destroy. All work is
+ * enqueued on the engine's stream; only fs_stats, fs_step_host and the *_sync
+ * helpers block. One engine per device; a handle is not thread-safe.
+ * No torch types cross this boundary.
+ */
+#ifndef FLOWSTEP_H_
+#define FLOWSTEP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FS_ABI_VERSION 1
+
+/* error codes */
+#define FS_OK 0
+#define FS_EINVAL (-1)  /* bad argument / unsupported configuration */
+#define FS_ECUDA (-2)   /* CUDA runtime error (message has the detail) */
+#define FS_ENOMEM (-3)
+#define FS_ESTATE (-4)  /* call order violated (e.g. step before set_types) */
+
+/* arithmetic type of the state and of every buffer except done/lane/index */
+#define FS_F32 0
+#define FS_F64 1
+
+/* topology */
+#define FS_TOPO_RING 0
+#define FS_TOPO_HIGHWAY 1
+
+/* environment front: selects observation + reward */
+#define FS_ENV_ACCEL 0             /* AccelEnv: obs 2V, desired_velocity            */
+#define FS_ENV_WAVE_ATTENUATION 1  /* WaveAttenuationEnv: obs 2V, WA reward         */
+#define FS_ENV_WAVE_ATTENUATION_PO 2 /* WaveAttenuationPOEnv: obs 3, WA reward      */
+#define FS_ENV_LANE_CHANGE_ACCEL 3 /* LaneChangeAccelEnv: obs 3V, dv - lc penalty   */
+#define FS_ENV_LANE_CHANGE_ACCEL_PO 4 /* LaneChangeAccelPOEnv                       */
+#define FS_ENV_HIGHWAY 5           /* open highway + inflow: obs 2*slots, dv reward */
+
+/* acceleration controllers (flow/controllers/*.py) */
+#define FS_CTRL_SIM 0          /* SimCarFollowingController: simulator default model */
+#define FS_CTRL_IDM 1          /* p: v0,T,a,b,delta,s0                               */
+#define FS_CTRL_OVM 2          /* p: alpha,beta,h_st,h_go,v_max                      */
+#define FS_CTRL_LINEAR_OVM 3   /* p: v_max,adaptation,h_st                           */
+#define FS_CTRL_BCM 4          /* p: k_d,k_v,k_c,d_des,v_des                         */
+#define FS_CTRL_CFM 5          /* p: k_d,k_v,k_c,d_des,v_des                         */
+#define FS_CTRL_LAC 6          /* p: k_1,k_2,h,tau,a0          (stateful: a)         */
+#define FS_CTRL_GIPPS 7        /* p: v0,acc,b,b_l,s0,tau                             */
+#define FS_CTRL_FOLLOWER_STOPPER 8        /* p: v_des                                */
+#define FS_CTRL_NONLOCAL_FOLLOWER_STOPPER 9
+#define FS_CTRL_PI_SATURATION 10          /* stateful: v_history, v_cmd              */
+#define FS_CTRL_RL 11          /* RLController: accel = clipped action, else SIM     */
+
+#define FS_FAILSAFE_NONE 0
+#define FS_FAILSAFE_INSTANTANEOUS 1
+#define FS_FAILSAFE_SAFE_VELOCITY 2
+
+/* lane-change controllers */
+#define FS_LC_SIM 0     /* SimLaneChangeController: never changes (mode 512)   */
+#define FS_LC_STATIC 1  /* StaticLaneChanger: direction 0                      */
+#define FS_LC_RL 2      /* direction comes from the action vector              */
+
+#define FS_MAX_TYPES 16
+#define FS_NPARAM 8
+
+typedef struct fs_engine fs_engine; /* opaque */
+
+typedef struct fs_vtype {
+  int32_t controller;    /* FS_CTRL_*                                           */
+  int32_t fail_safe;     /* FS_FAILSAFE_*                                       */
+  int32_t lc_controller; /* FS_LC_*                                             */
+  int32_t reserved;
+  double p[FS_NPARAM];   /* controller parameters, order as listed above        */
+  double noise;          /* std of the Gaussian added to accel (0 = none)       */
+  double delay;          /* used by the safe_velocity fail-safe                 */
+  double max_accel;      /* car_following_params.controller_params['accel']     */
+  double max_decel;      /* abs(controller_params['decel'])                     */
+  double length;         /* vehicle length (SUMO default 5 m)                   */
+  /* SumoCarFollowingParams used when the simulator drives the vehicle          */
+  double sim_tau, sim_min_gap, sim_max_speed;
+} fs_vtype;
+
+typedef struct fs_config {
+  int32_t abi_version;   /* FS_ABI_VERSION                                      */
+  int32_t device;        /* CUDA device ordinal                                 */
+  int32_t dtype;         /* FS_F32 / FS_F64                                     */
+  int32_t topology;      /* FS_TOPO_*                                           */
+  int32_t env_kind;      /* FS_ENV_*                                            */
+  int32_t n_envs;        /* E on this device                                    */
+  int32_t n_veh;         /* V: vehicles per env (ring) or slot capacity (hwy)   */
+  int32_t n_lanes;
+  int64_t env_id_base;   /* global index of env 0 (keeps RNG invariant to #GPUs)*/
+  uint64_t seed;
+  double sim_step;       /* dt                                                  */
+  /* network */
+  double length_lo, length_hi; /* ring: integer draw U{lo..hi} per reset (lo==hi fixed);
+                                  highway: length = length_lo                    */
+  double junction_len;   /* ring: 4 junctions of this length are part of the loop */
+  double speed_limit;
+  /* initial placement (InitialConfig) */
+  double x0, bunching, init_min_gap;
+  int32_t lanes_distribution; /* clipped to n_lanes                            */
+  /* env params */
+  int32_t warmup_steps, horizon, sims_per_step;
+  int32_t clip_actions;  /* reward sees clipped actions iff 1                  */
+  int32_t lane_change_duration;
+  double target_velocity;
+  double act_lo, act_hi; /* accel bounds of the action space (-|max_decel|, max_accel) */
+  double obs_max_length; /* WaveAttenuationPO: ring_length[1] normaliser        */
+  /* highway inflow */
+  double inflow_vehs_per_hour, inflow_depart_speed;
+  int32_t inflow_type;   /* vehicle type index of inflow vehicles               */
+  int32_t collision_min_gap; /* 0: crash iff gap<0 ; 1: crash iff gap<minGap    */
+} fs_config;
+
+/* device views; T = float or double per cfg.dtype; [a][b] = a slow, b fast */
+typedef struct fs_views {
+  void* pos;         /* T  [V][E]  continuous route position                    */
+  void* vel;         /* T  [V][E]                                               */
+  uint8_t* lane;     /* u8 [V][E]                                               */
+  uint8_t* active;   /* u8 [V][E]  highway slots; ring: all 1                   */
+  void* headway;     /* T  [V][E]  bumper-to-bumper gap to leader (1000 if none)*/
+  int32_t* leader;   /* i32[V][E]  vehicle index of leader, -1 if none          */
+  int32_t* follower; /* i32[V][E]                                               */
+  void* accel;       /* T  [V][E]  acceleration applied in the last step        */
+  void* length;      /* T  [E]     loop circumference incl. junctions           */
+  void* obs;         /* T  [E][obs_dim]                                         */
+  void* reward;      /* T  [E]                                                  */
+  uint8_t* done;     /* u8 [E]                                                  */
+  uint8_t* crash;    /* u8 [E]                                                  */
+  int32_t* time_counter; /* i32 [E]                                             */
+  int32_t n_envs, n_veh, n_lanes, obs_dim, act_dim, dtype;
+} fs_views;
+
+int fs_abi_version(void);
+int fs_create(const fs_config* cfg, fs_engine** out);
+void fs_destroy(fs_engine* e);
+const char* fs_last_error(const fs_engine* e); /* e may be NULL: last create error */
+
+/* types: n_types entries; type_of_vehicle: host u8 [V] */
+int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
+                 const uint8_t* type_of_vehicle);
+
+/* Reset the envs whose mask byte is non-zero (host u8 [E]; NULL = all):
+ * draw ring length (or take lengths[E] host doubles if non-NULL), place
+ * vehicles, refresh leader/headway, then run cfg.warmup_steps steps with no
+ * RL action. Observation of the reset envs is left in views.obs. */
+int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* lengths);
+
+/* k fused steps. actions: DEVICE pointer, T [k][act_dim][E], or NULL (no RL
+ * action: RL vehicles are driven by the simulator model). If obs_seq /
+ * reward_seq / done_seq are non-NULL (device, T [k][E][obs_dim], T [k][E],
+ * u8 [k][E]) the per-step results are stored there; the last step's results
+ * are always left in views.obs / reward / done. */
+int fs_step(fs_engine* e, const void* actions, int k, void* obs_seq,
+            void* reward_seq, uint8_t* done_seq);
+
+/* Same with HOST buffers (pageable or pinned): copies actions up, runs the k
+ * steps, copies obs/reward/done of every step back, and synchronises. */
+int fs_step_host(fs_engine* e, const void* actions, int k, void* obs_seq,
+                 void* reward_seq, uint8_t* done_seq);
+
+int fs_buffers(fs_engine* e, fs_views* out);
+
+/* Overwrite state from host arrays (T [V][E], any may be NULL), then refresh
+ * leader/headway exactly as k.update does. lane: u8 [V][E]. */
+int fs_set_state(fs_engine* e, const void* pos, const void* vel,
+                 const uint8_t* lane, const double* lengths);
+
+/* host_out[0..7] = sum reward, sum speed, sum speed^2, vehicle-steps,
+ * env-steps, crashes, 0, 0 accumulated since the last fs_stats(reset=1). */
+int fs_stats(fs_engine* e, double* host_out, int n, int reset);
+
+int fs_sync(fs_engine* e);
+/* cudaStream_t of the engine, for callers that want to order their own work */
+void* fs_stream(fs_engine* e);
+/* number of kernel launches issued by this engine since creation */
+int64_t fs_launch_count(const fs_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLOWSTEP_H_ */

@@ -1,0 +1,287 @@
+"""CPU oracle — TEST INFRASTRUCTURE ONLY (never imported by flow_b200/).
+
+One-environment fp64 restatement of the reference's `Env.reset/step` path on a
+ring road: initial placement, k.update (leader / headway / follower),
+controllers + fail-safes (oracle/controllers.py), apply_acceleration, the
+SUMO Euler move, collision flag, observation and reward.
+
+What is restated from the reference (pinned, see tests/golden/):
+  gen_even_start_pos      flow/core/kernel/network/base.py:263-391, :515-608
+  ring edge-start table   flow/networks/ring.py:194-216
+  apply_acceleration      flow/core/kernel/vehicle/traci.py:952-963
+  headway/leader/follower flow/core/kernel/vehicle/traci.py:218-250
+  Env.step order + done   flow/envs/base.py:294-412
+  desired_velocity        flow/core/rewards.py:6-59
+  WaveAttenuation reward  flow/envs/ring/wave_attenuation.py:113-139
+  WaveAttenuationPO obs   flow/envs/ring/wave_attenuation.py:248-269
+  Accel/WaveAtt full obs  flow/envs/ring/accel.py:116-123
+
+What stands in for SUMO (third-party C++, not in /root/reference; pinned only
+by tests/fast_tests/test_files/ring_230_emission.csv for the first steps,
+otherwise "parity unpinned"):
+  * the ring is one continuous loop of circumference C = length + 4*junction
+    (junction = 0.1 m, flow/networks/ring.py:197); controllers never see a
+    ':' edge;
+  * Euler move x' = (x + v'*dt) mod C with v' = the commanded speed;
+  * leader = next vehicle ahead in the same lane, headway = front-to-front
+    distance mod C minus the leader's length; alone in lane -> none / 1000;
+  * collision <=> some headway < 0 after the move;
+  * vehicles without a command (RL vehicle when rl_actions is None,
+    SimCarFollowingController) follow IDM with their SumoCarFollowingParams.
+"""
+import math
+
+import numpy as np
+
+from . import controllers as C
+
+VEHICLE_LENGTH = 5.0  # flow/core/kernel/network/base.py:10
+
+ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
+    ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY = range(6)
+
+F32_EPS = float(np.finfo(np.float32).eps)
+
+
+def ring_edge_tables(length, junction=0.1):
+    """(edgestarts, internal_edgestarts) of RingNetwork, ring.py:194-216."""
+    edgestarts = [("bottom", 0.0),
+                  ("right", 0.25 * length + junction),
+                  ("top", 0.5 * length + 2 * junction),
+                  ("left", 0.75 * length + 3 * junction)]
+    internal = [(":right_0", 0.25 * length),
+                (":top_0", 0.5 * length + junction),
+                (":left_0", 0.75 * length + 2 * junction),
+                (":bottom_0", length + 3 * junction)]
+    return edgestarts, internal
+
+
+def gen_even_start_pos(length, num_vehicles, n_lanes=1, x0=0.0, bunching=0.0,
+                       min_gap=0.0, lanes_distribution=float('inf'),
+                       junction=0.1):
+    """Even placement on a ring; returns (x[V] in loop coordinates, lane[V]).
+
+    Follows gen_even_start_pos / _get_start_pos_util
+    (flow/core/kernel/network/base.py:263-391, :515-608) specialised to the
+    four equal ring edges; a position that falls into a junction slot is
+    moved to the start of the next edge (:339-354)."""
+    min_gap = max(0.0, min_gap)
+    bunching = max(0.0, bunching)
+    lanes_distr = int(min(max(lanes_distribution, 1), n_lanes))
+    edge_len = length / 4.0
+    if edge_len > min_gap + VEHICLE_LENGTH:
+        distribution_length = 4 * (edge_len * min(n_lanes, lanes_distr))
+    else:
+        distribution_length = 0.0
+    available = distribution_length - lanes_distr * bunching - \
+        num_vehicles * (min_gap + VEHICLE_LENGTH)
+    if available < 0:
+        raise ValueError('There is not enough space to place all vehicles '
+                         'in the network.')
+    if num_vehicles == 0:
+        return [], []
+    increment = available / num_vehicles
+    edgestarts, internal = ring_edge_tables(length, junction)
+    total = sorted(edgestarts + internal, key=lambda t: t[1])
+    xs, lanes = [], []
+    x = x0
+    count = 0
+    while count < num_vehicles:
+        # get_edge(x): flow/core/kernel/network/traci.py:267-271
+        idx = max(i for i, (_, s) in enumerate(total) if x >= s)
+        if total[idx][0].startswith(':'):
+            idx = 0 if idx == len(total) - 1 else idx + 1
+            x = total[idx][1]
+        for lane in range(min(n_lanes, lanes_distr)):
+            count += 1
+            xs.append(x)
+            lanes.append(lane)
+            if count == num_vehicles:
+                break
+        x = (x + increment + VEHICLE_LENGTH + min_gap) % length
+    return xs, lanes
+
+
+class RingSim:
+    """One ring environment. Vehicle index == position in `initial_ids`."""
+
+    def __init__(self, types, type_of_vehicle, length=230.0, n_lanes=1,
+                 dt=0.1, junction=0.1, speed_limit=30.0, env_kind=ENV_ACCEL,
+                 x0=0.0, bunching=0.0, init_min_gap=0.0,
+                 lanes_distribution=float('inf'), warmup_steps=0,
+                 horizon=3000, target_velocity=10.0, act_lo=-4.5, act_hi=2.6,
+                 clip_actions=False, obs_max_length=None,
+                 lane_change_duration=5, noise_fn=None):
+        self.types = types
+        self.type_of = list(type_of_vehicle)
+        self.num_vehicles = len(self.type_of)
+        self.n_lanes = n_lanes
+        self.dt = dt
+        self.junction = junction
+        self.speed_limit = speed_limit
+        self.env_kind = env_kind
+        self.init = dict(x0=x0, bunching=bunching, min_gap=init_min_gap,
+                         lanes_distribution=lanes_distribution)
+        self.warmup_steps = warmup_steps
+        self.horizon = horizon
+        self.target_velocity = target_velocity
+        self.act_lo, self.act_hi = act_lo, act_hi
+        self.clip_actions = clip_actions
+        self.obs_max_length = obs_max_length
+        self.lane_change_duration = lane_change_duration
+        self.noise_fn = noise_fn  # (step, vehicle) -> N(0,1) sample
+        self.rl_idx = [i for i, t in enumerate(self.type_of)
+                       if types[t].controller == C.RL]
+        self.reset(length)
+
+    # -- reset ------------------------------------------------------------
+    def reset(self, length, run_warmup=True):
+        """Env.reset (flow/envs/base.py:414-560): place, update, warm up."""
+        V = self.num_vehicles
+        self.net_length = float(length)
+        self.circ = float(length) + 4 * self.junction
+        xs, lanes = gen_even_start_pos(
+            length, V, self.n_lanes, junction=self.junction, **self.init)
+        self.pos = [float(x) for x in xs]
+        self.vel = [0.0] * V
+        self.lane = list(lanes)
+        self.accel = [0.0] * V
+        self.ctrl_state = [dict() for _ in range(V)]
+        self.time_counter = 0
+        self.step_index = 0
+        self.crash = False
+        self.done = False
+        self.update()
+        obs = self.get_state()
+        if run_warmup:
+            for _ in range(self.warmup_steps):
+                obs, _, _ = self.step(None)
+        return obs
+
+    def set_state(self, pos=None, vel=None, lane=None):
+        if pos is not None:
+            self.pos = [float(x) for x in pos]
+        if vel is not None:
+            self.vel = [float(x) for x in vel]
+        if lane is not None:
+            self.lane = [int(x) for x in lane]
+        self.update()
+
+    # -- k.update ---------------------------------------------------------
+    def update(self):
+        """Leader / headway / follower of every vehicle
+        (flow/core/kernel/vehicle/traci.py:218-250 around SUMO's getLeader)."""
+        V = self.num_vehicles
+        self.leader = [-1] * V
+        self.follower = [-1] * V
+        self.headway = [1e3] * V
+        fol_h = [None] * V
+        for i in range(V):
+            best, best_d = -1, None
+            for j in range(V):
+                if j == i or self.lane[j] != self.lane[i]:
+                    continue
+                d = (self.pos[j] - self.pos[i]) % self.circ
+                if best_d is None or d < best_d:
+                    best, best_d = j, d
+            if best >= 0:
+                h = best_d - self.types[self.type_of[best]].length
+                self.leader[i] = best
+                self.headway[i] = h
+        for i in range(V):
+            j = self.leader[i]
+            if j >= 0 and (fol_h[j] is None or self.headway[i] < fol_h[j]):
+                self.follower[j] = i
+                fol_h[j] = self.headway[i]
+
+    def mean_speed(self):
+        return float(np.mean(self.vel))
+
+    # -- Env.step ---------------------------------------------------------
+    def step(self, rl_actions):
+        """One Env.step with sims_per_step = 1 (flow/envs/base.py:294-412).
+        Returns (obs, reward, done). A finished env is frozen."""
+        if self.done:
+            return self.get_state(), 0.0, True
+        V, dt = self.num_vehicles, self.dt
+        self.time_counter += 1
+        next_vel = [0.0] * V
+        clipped = None
+        if rl_actions is not None:
+            clipped = [min(max(float(a), self.act_lo), self.act_hi)
+                       for a in rl_actions]
+        for i in range(V):
+            vt = self.types[self.type_of[i]]
+            if vt.controller == C.RL and clipped is not None:
+                a = clipped[self.rl_idx.index(i)]
+            else:
+                z = self.noise_fn(self.step_index, i) \
+                    if (self.noise_fn and vt.noise > 0) else 0.0
+                a = C.get_action(self, i, vt, self.ctrl_state[i], dt,
+                                 self.speed_limit, z)
+            self.accel[i] = a
+            # apply_acceleration, vehicle/traci.py:961-962
+            next_vel[i] = max(self.vel[i] + a * dt, 0.0)
+        # simulator move (restated SUMO Euler step)
+        for i in range(V):
+            self.vel[i] = next_vel[i]
+            x = self.pos[i] + next_vel[i] * dt
+            self.pos[i] = x % self.circ
+        self.step_index += 1
+        self.update()
+        self.crash = any(h < 0 for h in self.headway)
+        obs = self.get_state()
+        self.done = (self.time_counter >= self.warmup_steps + self.horizon) \
+            or self.crash
+        acts = rl_actions
+        if rl_actions is not None and self.clip_actions:
+            acts = clipped
+        reward = self.compute_reward(acts, self.crash)
+        return obs, reward, self.done
+
+    # -- observations / rewards -------------------------------------------
+    def get_state(self):
+        k = self.env_kind
+        if k in (ENV_ACCEL, ENV_WAVE_ATTENUATION):
+            # accel.py:116-123 / wave_attenuation.py:141-148
+            return np.array([v / self.speed_limit for v in self.vel] +
+                            [x / self.circ for x in self.pos])
+        if k == ENV_WAVE_ATTENUATION_PO:
+            # wave_attenuation.py:248-269
+            rl = self.rl_idx[0]
+            lead = self.leader[rl] if self.leader[rl] >= 0 else rl
+            max_length = self.obs_max_length or self.circ
+            return np.array([
+                self.vel[rl] / 15.,
+                (self.vel[lead] - self.vel[rl]) / 15.,
+                (self.pos[lead] - self.pos[rl]) % self.circ / max_length])
+        raise NotImplementedError(k)
+
+    def desired_velocity(self, fail=False):
+        """flow/core/rewards.py:6-59."""
+        vel = np.array(self.vel)
+        n = len(vel)
+        if any(vel < -100) or fail or n == 0:
+            return 0.
+        target = self.target_velocity
+        max_cost = np.linalg.norm(np.array([target] * n))
+        cost = np.linalg.norm(vel - target)
+        return max(max_cost - cost, 0) / (max_cost + F32_EPS)
+
+    def compute_reward(self, rl_actions, fail):
+        k = self.env_kind
+        if k == ENV_ACCEL:
+            return self.desired_velocity(fail)
+        if k in (ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO):
+            # wave_attenuation.py:113-139
+            if rl_actions is None:
+                return 0
+            vel = np.array(self.vel)
+            if any(vel < -100) or fail:
+                return 0.
+            reward = 4. * np.mean(vel) / 20
+            mean_actions = np.mean(np.abs(np.array(rl_actions)))
+            if mean_actions > 0:
+                reward += 4 * (0 - mean_actions)
+            return float(reward)
+        raise NotImplementedError(k)

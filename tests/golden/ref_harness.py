@@ -1,0 +1,275 @@
+"""Drive the REAL reference controllers / fail-safes / rewards / observation
+functions (imported from /root/reference via ref_shim) on a ring whose
+simulator part (Euler move + leader search, i.e. what SUMO does) is the
+oracle's restatement. Used by make_golden.py to produce tests/golden/*.npz and
+by tests/test_oracle_vs_reference.py (skipped where the reference is absent).
+"""
+import numpy as np
+
+from . import ref_shim
+
+ref_shim.install()
+
+from flow.core.params import SumoCarFollowingParams, EnvParams  # noqa: E402
+from flow.core.kernel.vehicle.traci import TraCIVehicle  # noqa: E402
+from flow.core.kernel.network.base import BaseKernelNetwork  # noqa: E402
+from flow.core.params import InitialConfig  # noqa: E402
+from flow.core import rewards as ref_rewards  # noqa: E402
+from flow.envs.ring.wave_attenuation import WaveAttenuationEnv, \
+    WaveAttenuationPOEnv  # noqa: E402
+from flow.envs.ring.accel import AccelEnv  # noqa: E402
+import flow.controllers as ref_ctrl  # noqa: E402
+
+
+class _Net:
+    """Closed-form stand-in for TraCIKernelNetwork on a ring: supplies the
+    tables the reference's own gen_even_start_pos reads."""
+
+    def __init__(self, length, lanes, speed_limit, junction=0.1):
+        self._length = float(length)
+        self.lanes = lanes
+        self.speed = speed_limit
+        j = junction
+        L = self._length
+        self.edgestarts = [("bottom", 0), ("right", 0.25 * L + j),
+                           ("top", 0.5 * L + 2 * j), ("left", 0.75 * L + 3 * j)]
+        self.internal_edgestarts = [(":right_0", 0.25 * L), (":top_0", 0.5 * L + j),
+                                    (":left_0", 0.75 * L + 2 * j),
+                                    (":bottom_0", L + 3 * j)]
+        self.total_edgestarts = sorted(self.edgestarts + self.internal_edgestarts,
+                                       key=lambda t: t[1])
+        self.total_edgestarts_dict = dict(self.total_edgestarts)
+        self.circ = L + 4 * j
+
+    def get_edge_list(self):
+        return ["bottom", "right", "top", "left"]
+
+    def num_lanes(self, edge):
+        return self.lanes
+
+    def edge_length(self, edge):
+        return self._length / 4 if edge[0] != ':' else 0.1
+
+    def non_internal_length(self):
+        return self._length
+
+    def length(self):
+        return self.circ
+
+    def max_speed(self):
+        return self.speed
+
+    def get_edge(self, x):  # flow/core/kernel/network/traci.py:267-271
+        for (edge, start_pos) in reversed(self.total_edgestarts):
+            if x >= start_pos:
+                return edge, x - start_pos
+
+    def get_x(self, edge, position):
+        return self.total_edgestarts_dict[edge] + position
+
+    gen_even_start_pos = BaseKernelNetwork.gen_even_start_pos
+    _get_start_pos_util = BaseKernelNetwork._get_start_pos_util
+
+
+def ref_start_positions(length, num_vehicles, lanes=1, **init_kw):
+    """Loop coordinates + lanes from the reference's own gen_even_start_pos."""
+    net = _Net(length, lanes, 30)
+    ic = InitialConfig(**init_kw)
+    pos, lane = net.gen_even_start_pos(ic, num_vehicles)
+    return [net.get_x(e, p) for e, p in pos], list(lane)
+
+
+class _Veh:
+    """The getter surface of TraCIVehicle the controllers/rewards call,
+    string ids in, backed by arrays."""
+
+    def __init__(self, h):
+        self.h = h
+
+    def _i(self, vid):
+        return self.h.index[vid]
+
+    def get_ids(self):
+        return list(self.h.ids)
+
+    def get_rl_ids(self):
+        return [self.h.ids[i] for i in self.h.rl_idx]
+
+    def get_human_ids(self):
+        return [v for i, v in enumerate(self.h.ids) if i not in self.h.rl_idx]
+
+    @property
+    def num_vehicles(self):
+        return len(self.h.ids)
+
+    @property
+    def num_rl_vehicles(self):
+        return len(self.h.rl_idx)
+
+    def get_speed(self, vid, error=-1001):
+        if isinstance(vid, (list, np.ndarray)):
+            return [self.get_speed(v, error) for v in vid]
+        if vid is None or vid not in self.h.index:
+            return error
+        return self.h.vel[self._i(vid)]
+
+    def get_headway(self, vid, error=-1001):
+        if vid is None or vid not in self.h.index:
+            return error
+        return self.h.headway[self._i(vid)]
+
+    def get_leader(self, vid, error=""):
+        j = self.h.leader[self._i(vid)]
+        return None if j < 0 else self.h.ids[j]
+
+    def get_follower(self, vid, error=""):
+        j = self.h.follower[self._i(vid)]
+        return None if j < 0 else self.h.ids[j]
+
+    def get_edge(self, vid, error=""):
+        # restated continuous loop: one logical edge, never '' or ':...'
+        return "ring"
+
+    def get_position(self, vid, error=-1001):
+        return self.h.pos[self._i(vid)]
+
+    def get_x_by_id(self, vid):
+        return self.h.pos[self._i(vid)]
+
+    def get_length(self, vid, error=-1001):
+        return 5.0
+
+    def get_lane(self, vid, error=-1001):
+        return self.h.lane[self._i(vid)]
+
+    def set_observed(self, vid):
+        pass
+
+
+class _SlowDownSink:
+    """kernel_api.vehicle stand-in: records what apply_acceleration commands."""
+
+    def __init__(self):
+        self.cmd = {}
+
+    def slowDown(self, vid, speed, duration):
+        self.cmd[vid] = speed
+
+
+class RefRing:
+    """Ring env whose controllers, fail-safes, apply_acceleration, rewards and
+    observations are the reference's code; only the simulator move and the
+    leader search (SUMO's job) are the oracle restatement (oracle/sim.py)."""
+
+    def __init__(self, groups, length, env_kind='accel', dt=0.1, lanes=1,
+                 speed_limit=30, init_kw=None, env_additional=None,
+                 warmup_steps=0, horizon=3000, clip_actions=False):
+        """groups: list of (name, controller_class_or_'rl', ctrl_kwargs,
+        SumoCarFollowingParams kwargs, count)."""
+        self.dt = self.sim_step = dt
+        self.ids, self.ctrl, self.rl_idx = [], [], []
+        self.sim_ctrl = {}
+        for name, cls, kw, cf_kw, n in groups:
+            for q in range(n):
+                vid = '%s_%d' % (name, q)
+                cf = SumoCarFollowingParams(**cf_kw)
+                if cls == 'rl':
+                    self.rl_idx.append(len(self.ids))
+                    self.ctrl.append(None)
+                    # restated simulator default model:
+                    # the reference's IDM law fed with the type's SUMO params
+                    cp = cf.controller_params
+                    self.sim_ctrl[len(self.ids)] = ref_ctrl.IDMController(
+                        vid, v0=min(float(cp['maxSpeed']), speed_limit),
+                        T=float(cp['tau']), a=float(cp['accel']),
+                        b=float(cp['decel']), delta=4, s0=float(cp['minGap']),
+                        car_following_params=cf)
+                else:
+                    self.ctrl.append(cls(vid, car_following_params=cf, **kw))
+                self.ids.append(vid)
+        self.index = {v: i for i, v in enumerate(self.ids)}
+        self.lanes = lanes
+        self.speed_limit = speed_limit
+        self.init_kw = init_kw or {}
+        self.env_kind = env_kind
+        self.env_params = EnvParams(
+            horizon=horizon, warmup_steps=warmup_steps,
+            clip_actions=clip_actions, additional_params=env_additional or {})
+        self.k = type('K', (), {})()
+        self.k.vehicle = _Veh(self)
+        self.sink = _SlowDownSink()
+        self.reset(length)
+
+    # what SUMO would do -------------------------------------------------
+    def _update(self):
+        from oracle.sim import RingSim
+        # borrow the restated leader search
+        shim = type('S', (), {})()
+        shim.num_vehicles = len(self.ids)
+        shim.lane, shim.pos, shim.circ = self.lane, self.pos, self.net.circ
+        from oracle.controllers import VType
+        shim.types, shim.type_of = [VType()], [0] * len(self.ids)
+        RingSim.update(shim)
+        self.leader, self.follower, self.headway = \
+            shim.leader, shim.follower, shim.headway
+
+    def reset(self, length):
+        self.net = _Net(length, self.lanes, self.speed_limit)
+        self.k.network = self.net
+        ic = InitialConfig(**self.init_kw)
+        pos, lane = self.net.gen_even_start_pos(ic, len(self.ids))
+        self.pos = [float(self.net.get_x(e, p)) for e, p in pos]
+        self.lane = list(lane)
+        self.vel = [0.0] * len(self.ids)
+        self.accel = [0.0] * len(self.ids)
+        self.time_counter = 0
+        self._update()
+
+    def step(self, rl_actions):
+        n = len(self.ids)
+        self.time_counter += 1
+        acc = [None] * n
+        for i in range(n):
+            if self.ctrl[i] is not None:
+                acc[i] = self.ctrl[i].get_action(self)
+        if rl_actions is not None:
+            space_lo = -abs(self.env_params.additional_params.get('max_decel', 1e9))
+            space_hi = self.env_params.additional_params.get('max_accel', 1e9)
+            clipped = np.clip(rl_actions, a_min=space_lo, a_max=space_hi)
+            for q, i in enumerate(self.rl_idx):
+                acc[i] = float(clipped[q])
+        else:
+            for i in self.rl_idx:
+                acc[i] = self.sim_ctrl[i].get_accel(self)
+        # reference apply_acceleration (vehicle/traci.py:952-963), unbound
+        stub = type('V', (), {})()
+        stub.sim_step = self.dt
+        stub.get_ids = lambda: self.ids
+        stub.get_speed = lambda vid: self.vel[self.index[vid]]
+        stub.kernel_api = type('A', (), {})()
+        stub.kernel_api.vehicle = self.sink
+        self.sink.cmd = {}
+        TraCIVehicle.apply_acceleration(stub, self.ids, acc)
+        for i, vid in enumerate(self.ids):
+            self.accel[i] = acc[i]
+            self.vel[i] = self.sink.cmd[vid]
+            self.pos[i] = (self.pos[i] + self.vel[i] * self.dt) % self.net.circ
+        self._update()
+        crash = any(h < 0 for h in self.headway)
+        obs = self.get_state()
+        acts = rl_actions
+        reward = self.compute_reward(acts, crash)
+        return obs, reward, crash
+
+    def get_state(self):
+        if self.env_kind == 'wave_po':
+            return WaveAttenuationPOEnv.get_state(self)
+        if self.env_kind == 'wave':
+            return WaveAttenuationEnv.get_state(self)
+        self.sorted_ids = self.ids
+        return AccelEnv.get_state(self)
+
+    def compute_reward(self, rl_actions, fail):
+        if self.env_kind in ('wave', 'wave_po'):
+            return WaveAttenuationEnv.compute_reward(self, rl_actions, fail=fail)
+        return AccelEnv.compute_reward(self, rl_actions, fail=fail)
