@@ -1,0 +1,140 @@
+"""Build and load libflowstep.so (the C-ABI in include/flowstep.h) with ctypes.
+
+The library is built IN-TREE (flow_b200/libflowstep.so) with nvcc for sm_100a
+only. There is no fallback: if the library is missing or does not load, every
+product entry point raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(_HERE)
+SO_PATH = os.path.join(_HERE, 'libflowstep.so')
+CSRC = os.path.join(_HERE, 'csrc')
+SOURCES = ['flowstep.cu']
+HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_reset.cuh']
+
+FS_NPARAM = 8
+FS_MAX_TYPES = 16
+
+
+class FsVType(C.Structure):
+    _fields_ = [('controller', C.c_int32), ('fail_safe', C.c_int32),
+                ('lc_controller', C.c_int32), ('reserved', C.c_int32),
+                ('p', C.c_double * FS_NPARAM),
+                ('noise', C.c_double), ('delay', C.c_double),
+                ('max_accel', C.c_double), ('max_decel', C.c_double),
+                ('length', C.c_double),
+                ('sim_tau', C.c_double), ('sim_min_gap', C.c_double),
+                ('sim_max_speed', C.c_double)]
+
+
+class FsConfig(C.Structure):
+    _fields_ = [('abi_version', C.c_int32), ('device', C.c_int32),
+                ('dtype', C.c_int32), ('topology', C.c_int32),
+                ('env_kind', C.c_int32), ('n_envs', C.c_int32),
+                ('n_veh', C.c_int32), ('n_lanes', C.c_int32),
+                ('env_id_base', C.c_int64), ('seed', C.c_uint64),
+                ('sim_step', C.c_double),
+                ('length_lo', C.c_double), ('length_hi', C.c_double),
+                ('junction_len', C.c_double), ('speed_limit', C.c_double),
+                ('x0', C.c_double), ('bunching', C.c_double),
+                ('init_min_gap', C.c_double),
+                ('lanes_distribution', C.c_int32),
+                ('warmup_steps', C.c_int32), ('horizon', C.c_int32),
+                ('sims_per_step', C.c_int32), ('clip_actions', C.c_int32),
+                ('lane_change_duration', C.c_int32),
+                ('target_velocity', C.c_double),
+                ('act_lo', C.c_double), ('act_hi', C.c_double),
+                ('obs_max_length', C.c_double),
+                ('inflow_vehs_per_hour', C.c_double),
+                ('inflow_depart_speed', C.c_double),
+                ('inflow_type', C.c_int32), ('collision_min_gap', C.c_int32),
+                ('record_views', C.c_int32), ('reserved0', C.c_int32)]
+
+
+class FsViews(C.Structure):
+    _fields_ = [('pos', C.c_void_p), ('vel', C.c_void_p), ('lane', C.c_void_p),
+                ('active', C.c_void_p), ('headway', C.c_void_p),
+                ('leader', C.c_void_p), ('follower', C.c_void_p),
+                ('accel', C.c_void_p), ('length', C.c_void_p),
+                ('obs', C.c_void_p), ('reward', C.c_void_p),
+                ('done', C.c_void_p), ('crash', C.c_void_p),
+                ('time_counter', C.c_void_p),
+                ('n_envs', C.c_int32), ('n_veh', C.c_int32),
+                ('n_lanes', C.c_int32), ('obs_dim', C.c_int32),
+                ('act_dim', C.c_int32), ('dtype', C.c_int32)]
+
+
+# every symbol include/flowstep.h declares: (name, restype, argtypes)
+SYMBOLS = [
+    ('fs_abi_version', C.c_int, []),
+    ('fs_create', C.c_int, [C.POINTER(FsConfig), C.POINTER(C.c_void_p)]),
+    ('fs_destroy', None, [C.c_void_p]),
+    ('fs_last_error', C.c_char_p, [C.c_void_p]),
+    ('fs_set_types', C.c_int, [C.c_void_p, C.POINTER(FsVType), C.c_int, C.c_void_p]),
+    ('fs_reset', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_step', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_buffers', C.c_int, [C.c_void_p, C.POINTER(FsViews)]),
+    ('fs_set_state', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_stats', C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int]),
+    ('fs_sync', C.c_int, [C.c_void_p]),
+    ('fs_stream', C.c_void_p, [C.c_void_p]),
+    ('fs_launch_count', C.c_int64, [C.c_void_p]),
+    ('fs_set_stream', C.c_int, [C.c_void_p, C.c_void_p]),
+]
+
+NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
+              '-std=c++17', '-shared', '-Xcompiler', '-fPIC']
+
+
+def _stale():
+    if not os.path.exists(SO_PATH):
+        return True
+    t = os.path.getmtime(SO_PATH)
+    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
+    deps.append(os.path.join(ROOT, 'include', 'flowstep.h'))
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False):
+    """Compile libflowstep.so for sm_100a with nvcc (cross-compiles without a GPU)."""
+    if not force and not _stale():
+        return SO_PATH
+    nvcc = os.environ.get('NVCC', 'nvcc')
+    cmd = [nvcc] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
+        ['-o', SO_PATH] + [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError('nvcc failed:\n%s\n%s' % (' '.join(cmd), res.stderr[-4000:]))
+    if verbose:
+        print(res.stderr)
+    return SO_PATH
+
+
+_lib = None
+
+
+def load():
+    """Load the library; raises (never falls back) when it is unavailable."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        try:
+            build()
+        except Exception as exc:  # no nvcc on this machine
+            raise RuntimeError(
+                'libflowstep.so is not built (run python -c "import '
+                '__graft_entry__ as g; g.build()"): %s' % exc)
+    lib = C.CDLL(SO_PATH)
+    for name, restype, argtypes in SYMBOLS:
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = restype
+        fn.argtypes = argtypes
+    if lib.fs_abi_version() != 1:
+        raise RuntimeError('libflowstep ABI version mismatch')
+    _lib = lib
+    return lib

@@ -1,0 +1,508 @@
+// flowstep.cu — engine object + C-ABI (include/flowstep.h) of libflowstep.so.
+// Host side only orchestrates: all arithmetic of the step path runs in the
+// CUDA kernels of fs_ring.cuh / fs_reset.cuh. There is NO CPU fallback: every
+// entry point fails with FS_ECUDA when no sm_100 device is usable.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include "../../include/flowstep.h"
+#include "fs_common.cuh"
+#include "fs_ring.cuh"
+#include "fs_reset.cuh"
+
+static thread_local std::string g_create_error;
+
+struct fs_engine {
+  fs_config cfg;
+  bool f64 = false;
+  bool types_set = false;
+  int obs_dim = 0, act_dim = 0, n_rl = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = true;
+  std::string err;
+  int64_t launches = 0;
+  // device state
+  void *pos = nullptr, *vel = nullptr, *circ = nullptr, *st0 = nullptr, *hist = nullptr;
+  double* hist_sum = nullptr;
+  int* hist_cnt = nullptr;
+  int hist_len = 0, n_pi = 0;
+  uint8_t *lane = nullptr, *active = nullptr, *done = nullptr, *crash = nullptr, *mask = nullptr;
+  int *time_counter = nullptr, *episode = nullptr, *leader = nullptr, *follower = nullptr;
+  void *headway = nullptr, *accel = nullptr, *obs = nullptr, *reward = nullptr;
+  double *stats = nullptr, *lengths_dev = nullptr;
+  // staging for fs_step_host
+  void *h_act = nullptr, *h_obs = nullptr, *h_rew = nullptr;
+  uint8_t* h_done = nullptr;
+  size_t h_act_cap = 0, h_obs_cap = 0, h_rew_cap = 0, h_done_cap = 0;
+  // parameter tables (one of the two is used)
+  fs::Cfg<float> cf;
+  fs::Cfg<double> cd;
+  std::vector<void*> allocs;
+  bool env_needs_rl() const { return cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO; }
+};
+
+#define FS_CUDA(e, call)                                                        \
+  do {                                                                          \
+    cudaError_t _st = (call);                                                   \
+    if (_st != cudaSuccess) {                                                   \
+      (e)->err = std::string(#call) + ": " + cudaGetErrorString(_st);           \
+      return FS_ECUDA;                                                          \
+    }                                                                           \
+  } while (0)
+
+static int fail(fs_engine* e, int code, const std::string& msg) {
+  if (e) e->err = msg; else g_create_error = msg;
+  return code;
+}
+
+template <typename P>
+static int dev_alloc(fs_engine* e, P** out, size_t bytes, bool zero = true) {
+  void* p = nullptr;
+  if (bytes == 0) bytes = 16;
+  cudaError_t st = cudaMalloc(&p, bytes);
+  if (st != cudaSuccess) {
+    e->err = std::string("cudaMalloc: ") + cudaGetErrorString(st);
+    return st == cudaErrorMemoryAllocation ? FS_ENOMEM : FS_ECUDA;
+  }
+  if (zero) cudaMemsetAsync(p, 0, bytes, e->stream);
+  e->allocs.push_back(p);
+  *out = reinterpret_cast<P*>(p);
+  return FS_OK;
+}
+
+static size_t tsize(const fs_engine* e) { return e->f64 ? 8 : 4; }
+
+extern "C" int fs_abi_version(void) { return FS_ABI_VERSION; }
+
+extern "C" const char* fs_last_error(const fs_engine* e) {
+  return e ? e->err.c_str() : g_create_error.c_str();
+}
+
+static int obs_dim_for(const fs_config& c) {
+  switch (c.env_kind) {
+    case FS_ENV_ACCEL:
+    case FS_ENV_WAVE_ATTENUATION: return 2 * c.n_veh;
+    case FS_ENV_WAVE_ATTENUATION_PO: return 3;
+    case FS_ENV_LANE_CHANGE_ACCEL: return 3 * c.n_veh;
+    case FS_ENV_HIGHWAY: return 2 * c.n_veh;
+    default: return -1;
+  }
+}
+
+extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
+  if (!cfg || !out) return fail(nullptr, FS_EINVAL, "fs_create: null argument");
+  if (cfg->abi_version != FS_ABI_VERSION)
+    return fail(nullptr, FS_EINVAL, "fs_create: abi_version mismatch");
+  if (cfg->n_envs <= 0 || cfg->n_veh <= 0 || cfg->n_veh > FS_MAX_VEH)
+    return fail(nullptr, FS_EINVAL, "fs_create: n_envs/n_veh out of range (n_veh <= 256)");
+  if (cfg->dtype != FS_F32 && cfg->dtype != FS_F64)
+    return fail(nullptr, FS_EINVAL, "fs_create: dtype must be FS_F32 or FS_F64");
+  if (!(cfg->sim_step > 0)) return fail(nullptr, FS_EINVAL, "fs_create: sim_step must be > 0");
+  if (cfg->n_lanes < 1 || cfg->n_lanes > 8)
+    return fail(nullptr, FS_EINVAL, "fs_create: n_lanes must be in 1..8");
+  if (obs_dim_for(*cfg) < 0)
+    return fail(nullptr, FS_EINVAL, "fs_create: unsupported env_kind");
+  int ndev = 0;
+  cudaError_t st = cudaGetDeviceCount(&ndev);
+  if (st != cudaSuccess || ndev == 0)
+    return fail(nullptr, FS_ECUDA,
+                std::string("fs_create: no CUDA device (") + cudaGetErrorString(st) +
+                    "); libflowstep has no CPU path");
+  if (cfg->device < 0 || cfg->device >= ndev)
+    return fail(nullptr, FS_EINVAL, "fs_create: bad device ordinal");
+  st = cudaSetDevice(cfg->device);
+  if (st != cudaSuccess) return fail(nullptr, FS_ECUDA, cudaGetErrorString(st));
+
+  fs_engine* e = new fs_engine();
+  e->cfg = *cfg;
+  e->f64 = cfg->dtype == FS_F64;
+  e->obs_dim = obs_dim_for(*cfg);
+  st = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+  if (st != cudaSuccess) {
+    g_create_error = cudaGetErrorString(st);
+    delete e;
+    return FS_ECUDA;
+  }
+  const size_t E = cfg->n_envs, V = cfg->n_veh, ts = tsize(e);
+  int rc = FS_OK;
+  auto A = [&](auto** p, size_t bytes) { if (rc == FS_OK) rc = dev_alloc(e, p, bytes); };
+  A(&e->pos, V * E * ts); A(&e->vel, V * E * ts); A(&e->circ, E * ts);
+  A(&e->lane, V * E); A(&e->active, V * E);
+  A(&e->done, E); A(&e->crash, E); A(&e->mask, E);
+  A(&e->time_counter, E * 4); A(&e->episode, E * 4);
+  A(&e->obs, E * e->obs_dim * ts); A(&e->reward, E * ts);
+  A(&e->stats, 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
+  if (cfg->record_views) {
+    A(&e->headway, V * E * ts); A(&e->accel, V * E * ts);
+    A(&e->leader, V * E * 4); A(&e->follower, V * E * 4);
+  }
+  if (rc != FS_OK) {
+    g_create_error = e->err;
+    fs_destroy(e);
+    return rc;
+  }
+  cudaMemsetAsync(e->active, 1, V * E, e->stream);
+  *out = e;
+  return FS_OK;
+}
+
+extern "C" void fs_destroy(fs_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->cfg.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (void* p : e->allocs) if (p) cudaFree(p);
+  if (e->stream && e->own_stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+template <typename T>
+static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_types,
+                     const uint8_t* type_of) {
+  const fs_config& g = e->cfg;
+  memset(&c, 0, sizeof(c));
+  c.n_envs = g.n_envs; c.n_veh = g.n_veh; c.n_lanes = g.n_lanes; c.env_kind = g.env_kind;
+  c.n_types = n_types; c.warmup_steps = g.warmup_steps; c.horizon = g.horizon;
+  c.sims_per_step = g.sims_per_step > 0 ? g.sims_per_step : 1;
+  c.clip_actions = g.clip_actions; c.lane_change_duration = g.lane_change_duration;
+  c.obs_dim = e->obs_dim; c.collision_min_gap = g.collision_min_gap;
+  c.env_id_base = g.env_id_base; c.seed = g.seed;
+  c.dt = (T)g.sim_step; c.inv_dt = (T)(1.0 / g.sim_step);
+  c.junction_len = (T)g.junction_len; c.speed_limit = (T)g.speed_limit;
+  c.inv_speed_limit = (T)(1.0 / g.speed_limit);
+  c.x0 = (T)g.x0; c.bunching = (T)g.bunching; c.init_min_gap = (T)g.init_min_gap;
+  c.target_velocity = (T)g.target_velocity; c.act_lo = (T)g.act_lo; c.act_hi = (T)g.act_hi;
+  c.obs_max_length = (T)g.obs_max_length;
+  c.length_lo = (T)g.length_lo; c.length_hi = (T)g.length_hi;
+  c.lanes_distribution = g.lanes_distribution;
+  for (int t = 0; t < n_types; ++t) {
+    const fs_vtype& s = types[t];
+    fs::TypeP<T>& d = c.types[t];
+    d.ctrl = s.controller; d.fail_safe = s.fail_safe; d.lc = s.lc_controller;
+    for (int q = 0; q < FS_NPARAM; ++q) d.p[q] = (T)s.p[q];
+    d.noise = (T)s.noise; d.delay = (T)s.delay; d.max_accel = (T)s.max_accel;
+    d.max_decel = (T)fabs(s.max_decel); d.length = (T)s.length;
+    d.sim_tau = (T)s.sim_tau; d.sim_min_gap = (T)s.sim_min_gap;
+    const double sim_v0 = fmin(s.sim_max_speed, g.speed_limit);
+    d.sim_v0 = (T)sim_v0;
+    const double tsab = 2.0 * sqrt(s.p[2] * s.p[3]);
+    const double stsab = 2.0 * sqrt(s.max_accel * fabs(s.max_decel));
+    d.two_sqrt_ab = (T)tsab; d.sim_two_sqrt_ab = (T)stsab;
+    d.inv_v0 = (T)(s.p[0] != 0 ? 1.0 / s.p[0] : 0.0); d.sim_inv_v0 = (T)(1.0 / sim_v0);
+    d.inv_two_sqrt_ab = (T)(tsab > 0 ? 1.0 / tsab : 0.0);
+    d.sim_inv_two_sqrt_ab = (T)(stsab > 0 ? 1.0 / stsab : 0.0);
+    if (s.noise > 0) c.any_noise = 1;
+    if (s.controller == FS_CTRL_BCM) c.any_follower |= 1;
+    if (s.controller == FS_CTRL_NONLOCAL_FOLLOWER_STOPPER) c.any_follower |= 2;
+  }
+  int n_rl = 0;
+  for (int i = 0; i < g.n_veh; ++i) {
+    c.type_of[i] = type_of[i];
+    c.rl_index[i] = -1;
+    if (types[type_of[i]].controller == FS_CTRL_RL) c.rl_index[i] = (int16_t)n_rl++;
+  }
+  c.n_rl = n_rl;
+  const bool lc_env = g.env_kind == FS_ENV_LANE_CHANGE_ACCEL ||
+                      g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
+  c.act_dim = lc_env ? 2 * n_rl : n_rl;
+  e->n_rl = n_rl;
+  e->act_dim = c.act_dim;
+}
+
+extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
+                            const uint8_t* type_of_vehicle) {
+  if (!e) return FS_EINVAL;
+  if (!types || !type_of_vehicle || n_types < 1 || n_types > FS_MAX_TYPES)
+    return fail(e, FS_EINVAL, "fs_set_types: need 1..16 types and a type_of_vehicle table");
+  cudaSetDevice(e->cfg.device);
+  int n_pi = 0, n_state = 0;
+  for (int i = 0; i < e->cfg.n_veh; ++i) {
+    if (type_of_vehicle[i] >= n_types)
+      return fail(e, FS_EINVAL, "fs_set_types: type_of_vehicle entry out of range");
+    const int c = types[type_of_vehicle[i]].controller;
+    if (c < 0 || c > FS_CTRL_RL) return fail(e, FS_EINVAL, "fs_set_types: unknown controller");
+    if (c == FS_CTRL_PI_SATURATION) ++n_pi;
+    if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC) ++n_state;
+  }
+  if (e->f64) fill_cfg<double>(e, e->cd, types, n_types, type_of_vehicle);
+  else fill_cfg<float>(e, e->cf, types, n_types, type_of_vehicle);
+  if (e->env_needs_rl() && e->n_rl < 1)
+    return fail(e, FS_EINVAL, "fs_set_types: this env_kind needs at least one RL vehicle");
+  const size_t E = e->cfg.n_envs, V = e->cfg.n_veh, ts = tsize(e);
+  int rc = FS_OK;
+  if (n_state > 0 && !e->st0) rc = dev_alloc(e, &e->st0, V * E * ts);
+  if (rc == FS_OK && n_pi > 0 && !e->hist) {
+    e->n_pi = n_pi;
+    e->hist_len = (int)(38.0 / e->cfg.sim_step);  // int(38 / sim_step), velocity_controllers.py:221
+    rc = dev_alloc(e, &e->hist, (size_t)e->hist_len * n_pi * E * ts);
+    if (rc == FS_OK) rc = dev_alloc(e, &e->hist_sum, (size_t)n_pi * E * sizeof(double));
+    if (rc == FS_OK) rc = dev_alloc(e, &e->hist_cnt, (size_t)n_pi * E * sizeof(int));
+  }
+  if (rc != FS_OK) return rc;
+  e->types_set = true;
+  return FS_OK;
+}
+
+// ---------------------------------------------------------------- launches
+template <typename T>
+static fs::RingBufs<T> ring_bufs(fs_engine* e) {
+  fs::RingBufs<T> b;
+  b.pos = (T*)e->pos; b.vel = (T*)e->vel; b.circ = (T*)e->circ; b.st0 = (T*)e->st0;
+  b.hist = (T*)e->hist; b.hist_sum = e->hist_sum; b.hist_cnt = e->hist_cnt;
+  b.hist_len = e->hist_len; b.n_pi = e->n_pi;
+  b.time_counter = e->time_counter; b.episode = e->episode;
+  b.done = e->done; b.crash = e->crash;
+  b.obs = (T*)e->obs; b.reward = (T*)e->reward;
+  b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
+  b.v_leader = e->leader; b.v_follower = e->follower;
+  b.stats = e->stats;
+  return b;
+}
+
+template <typename T>
+static const fs::Cfg<T>& cfg_of(fs_engine* e);
+template <> const fs::Cfg<float>& cfg_of<float>(fs_engine* e) { return e->cf; }
+template <> const fs::Cfg<double>& cfg_of<double>(fs_engine* e) { return e->cd; }
+
+static int pick_block(int E) {
+  // one env per thread: spread small batches over all 148 SMs (32-thread
+  // blocks), use fatter blocks once every SM has several warps anyway
+  if (E <= 148 * 32 * 8) return 32;
+  if (E <= 148 * 64 * 16) return 64;
+  return 128;
+}
+
+template <typename T, int VS, bool kViews>
+static int launch_ring1(fs_engine* e, const fs::StepArgs<T>& a) {
+  const int E = e->cfg.n_envs;
+  int block = pick_block(E);
+  size_t smem = 0;
+  auto kern = fs::ring1_step_kernel<T, VS, kViews>;
+  if (VS == 0) {
+    smem = (size_t)3 * e->cfg.n_veh * block * sizeof(T);
+    while (smem > 200 * 1024 && block > 32) { block /= 2; smem /= 2; }
+    if (smem > 48 * 1024)
+      FS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+  }
+  const int grid = (E + block - 1) / block;
+  kern<<<grid, block, smem, e->stream>>>(cfg_of<T>(e), ring_bufs<T>(e), a);
+  e->launches++;
+  FS_CUDA(e, cudaGetLastError());
+  return FS_OK;
+}
+
+template <typename T>
+static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
+  if (e->cfg.topology != FS_TOPO_RING || e->cfg.n_lanes != 1)
+    return fail(e, FS_EINVAL, "step: only the single-lane ring path is built in this version");
+  const bool views = e->cfg.record_views != 0;
+  const bool stateful = e->st0 != nullptr;  // LAC / PISaturation use the generic kernel
+  if (e->cfg.n_veh == 22 && !stateful)
+    return views ? launch_ring1<T, 22, true>(e, a) : launch_ring1<T, 22, false>(e, a);
+  return views ? launch_ring1<T, 0, true>(e, a) : launch_ring1<T, 0, false>(e, a);
+}
+
+template <typename T>
+static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
+                   uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done) {
+  fs::StepArgs<T> a;
+  a.actions = (const T*)actions; a.obs_seq = (T*)obs_seq; a.reward_seq = (T*)reward_seq;
+  a.done_seq = done_seq; a.mask = mask; a.k_steps = k; a.accumulate_stats = stats;
+  a.ignore_done = ignore_done;
+  return run_steps<T>(e, a);
+}
+
+extern "C" int fs_step(fs_engine* e, const void* actions, int k, void* obs_seq,
+                       void* reward_seq, uint8_t* done_seq) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_step: call fs_set_types first");
+  if (k < 1) return fail(e, FS_EINVAL, "fs_step: k must be >= 1");
+  cudaSetDevice(e->cfg.device);
+  return e->f64 ? do_step<double>(e, actions, k, obs_seq, reward_seq, done_seq, nullptr, 1, 0)
+                : do_step<float>(e, actions, k, obs_seq, reward_seq, done_seq, nullptr, 1, 0);
+}
+
+template <typename T>
+static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths_dev) {
+  fs::ResetBufs<T> b;
+  b.pos = (T*)e->pos; b.vel = (T*)e->vel; b.circ = (T*)e->circ; b.st0 = (T*)e->st0;
+  b.hist_sum = e->hist_sum; b.hist_cnt = e->hist_cnt; b.n_pi = e->n_pi;
+  b.lane = e->lane; b.done = e->done; b.crash = e->crash;
+  b.time_counter = e->time_counter; b.episode = e->episode;
+  b.mask = mask_dev; b.lengths = lengths_dev;
+  const int E = e->cfg.n_envs, block = 128;
+  fs::ring_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(cfg_of<T>(e), b);
+  e->launches++;
+  FS_CUDA(e, cudaGetLastError());
+  // warm-up: Env.reset steps with rl_actions=None (flow/envs/base.py:554-555)
+  return do_step<T>(e, nullptr, e->cfg.warmup_steps, nullptr, nullptr, nullptr, mask_dev, 0, 1);
+}
+
+static int check_room(fs_engine* e, double L) {
+  // _get_start_pos_util raises FatalFlowError when vehicles do not fit
+  const fs_config& g = e->cfg;
+  const double min_gap = fmax(0.0, g.init_min_gap), bunching = fmax(0.0, g.bunching);
+  int ld = g.lanes_distribution;
+  if (ld > g.n_lanes) ld = g.n_lanes;
+  if (ld < 1) ld = 1;
+  const double edge_len = L / 4.0;
+  const double dist = edge_len > min_gap + 5.0 ? 4 * edge_len * ld : 0.0;
+  if (dist - ld * bunching - g.n_veh * (min_gap + 5.0) < 0)
+    return fail(e, FS_EINVAL, "There is not enough space to place all vehicles in the network.");
+  return FS_OK;
+}
+
+extern "C" int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* lengths) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_reset: call fs_set_types first");
+  if (e->cfg.topology != FS_TOPO_RING)
+    return fail(e, FS_EINVAL, "fs_reset: only ring topology is built in this version");
+  cudaSetDevice(e->cfg.device);
+  const size_t E = e->cfg.n_envs;
+  int rc = check_room(e, e->cfg.length_lo);
+  if (rc != FS_OK) return rc;
+  const uint8_t* mask_dev = nullptr;
+  const double* len_dev = nullptr;
+  if (env_mask) {
+    FS_CUDA(e, cudaMemcpyAsync(e->mask, env_mask, E, cudaMemcpyHostToDevice, e->stream));
+    mask_dev = e->mask;
+  }
+  if (lengths) {
+    for (size_t i = 0; i < E; ++i)
+      if ((!env_mask || env_mask[i]) && lengths[i] > 0 && (rc = check_room(e, lengths[i])) != FS_OK)
+        return rc;
+    FS_CUDA(e, cudaMemcpyAsync(e->lengths_dev, lengths, E * sizeof(double),
+                               cudaMemcpyHostToDevice, e->stream));
+    len_dev = e->lengths_dev;
+  }
+  rc = e->f64 ? do_reset<double>(e, mask_dev, len_dev) : do_reset<float>(e, mask_dev, len_dev);
+  if (rc != FS_OK) return rc;
+  // host buffers may be reused by the caller right away
+  if (env_mask || lengths) FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  return FS_OK;
+}
+
+static int grow(fs_engine* e, void** p, size_t* cap, size_t need) {
+  if (need <= *cap) return FS_OK;
+  if (*p) {
+    cudaStreamSynchronize(e->stream);
+    cudaFree(*p);
+    for (auto& q : e->allocs) if (q == *p) q = nullptr;
+  }
+  void* n = nullptr;
+  cudaError_t st = cudaMalloc(&n, need);
+  if (st != cudaSuccess) { *p = nullptr; *cap = 0; return fail(e, FS_ENOMEM, cudaGetErrorString(st)); }
+  e->allocs.push_back(n);
+  *p = n; *cap = need;
+  return FS_OK;
+}
+
+extern "C" int fs_step_host(fs_engine* e, const void* actions, int k, void* obs_seq,
+                            void* reward_seq, uint8_t* done_seq) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_step_host: call fs_set_types first");
+  if (k < 1) return fail(e, FS_EINVAL, "fs_step_host: k must be >= 1");
+  cudaSetDevice(e->cfg.device);
+  const size_t E = e->cfg.n_envs, ts = tsize(e);
+  const size_t nb_act = (size_t)k * e->act_dim * E * ts, nb_obs = (size_t)k * E * e->obs_dim * ts,
+               nb_rew = (size_t)k * E * ts, nb_done = (size_t)k * E;
+  int rc;
+  void* d_act = nullptr;
+  if (actions && e->act_dim > 0) {
+    if ((rc = grow(e, &e->h_act, &e->h_act_cap, nb_act)) != FS_OK) return rc;
+    FS_CUDA(e, cudaMemcpyAsync(e->h_act, actions, nb_act, cudaMemcpyHostToDevice, e->stream));
+    d_act = e->h_act;
+  }
+  if (obs_seq && (rc = grow(e, &e->h_obs, &e->h_obs_cap, nb_obs)) != FS_OK) return rc;
+  if (reward_seq && (rc = grow(e, &e->h_rew, &e->h_rew_cap, nb_rew)) != FS_OK) return rc;
+  if (done_seq && (rc = grow(e, (void**)&e->h_done, &e->h_done_cap, nb_done)) != FS_OK) return rc;
+  rc = fs_step(e, d_act, k, obs_seq ? e->h_obs : nullptr, reward_seq ? e->h_rew : nullptr,
+               done_seq ? e->h_done : nullptr);
+  if (rc != FS_OK) return rc;
+  if (obs_seq)
+    FS_CUDA(e, cudaMemcpyAsync(obs_seq, e->h_obs, nb_obs, cudaMemcpyDeviceToHost, e->stream));
+  if (reward_seq)
+    FS_CUDA(e, cudaMemcpyAsync(reward_seq, e->h_rew, nb_rew, cudaMemcpyDeviceToHost, e->stream));
+  if (done_seq)
+    FS_CUDA(e, cudaMemcpyAsync(done_seq, e->h_done, nb_done, cudaMemcpyDeviceToHost, e->stream));
+  FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  return FS_OK;
+}
+
+extern "C" int fs_buffers(fs_engine* e, fs_views* out) {
+  if (!e || !out) return FS_EINVAL;
+  memset(out, 0, sizeof(*out));
+  out->pos = e->pos; out->vel = e->vel; out->lane = e->lane; out->active = e->active;
+  out->headway = e->headway; out->leader = e->leader; out->follower = e->follower;
+  out->accel = e->accel; out->length = e->circ; out->obs = e->obs; out->reward = e->reward;
+  out->done = e->done; out->crash = e->crash; out->time_counter = e->time_counter;
+  out->n_envs = e->cfg.n_envs; out->n_veh = e->cfg.n_veh; out->n_lanes = e->cfg.n_lanes;
+  out->obs_dim = e->obs_dim; out->act_dim = e->act_dim; out->dtype = e->cfg.dtype;
+  return FS_OK;
+}
+
+extern "C" int fs_set_state(fs_engine* e, const void* pos, const void* vel, const uint8_t* lane,
+                            const double* lengths) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_set_state: call fs_set_types first");
+  cudaSetDevice(e->cfg.device);
+  const size_t E = e->cfg.n_envs, V = e->cfg.n_veh, ts = tsize(e);
+  if (pos) FS_CUDA(e, cudaMemcpyAsync(e->pos, pos, V * E * ts, cudaMemcpyHostToDevice, e->stream));
+  if (vel) FS_CUDA(e, cudaMemcpyAsync(e->vel, vel, V * E * ts, cudaMemcpyHostToDevice, e->stream));
+  if (lane) FS_CUDA(e, cudaMemcpyAsync(e->lane, lane, V * E, cudaMemcpyHostToDevice, e->stream));
+  if (lengths) {
+    std::vector<double> c64(E);
+    std::vector<float> c32(E);
+    for (size_t i = 0; i < E; ++i) {
+      c64[i] = lengths[i] + 4 * e->cfg.junction_len;
+      c32[i] = (float)c64[i];
+    }
+    FS_CUDA(e, cudaMemcpyAsync(e->circ, e->f64 ? (void*)c64.data() : (void*)c32.data(), E * ts,
+                               cudaMemcpyHostToDevice, e->stream));
+    FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  }
+  // k.update on the injected state (refreshes views + obs); k = 0 moves nothing
+  int rc = e->f64 ? do_step<double>(e, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, 1)
+                  : do_step<float>(e, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, 1);
+  if (rc != FS_OK) return rc;
+  FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  return FS_OK;
+}
+
+extern "C" int fs_stats(fs_engine* e, double* host_out, int n, int reset) {
+  if (!e || !host_out || n < 1) return FS_EINVAL;
+  cudaSetDevice(e->cfg.device);
+  double tmp[8];
+  FS_CUDA(e, cudaMemcpyAsync(tmp, e->stats, sizeof(tmp), cudaMemcpyDeviceToHost, e->stream));
+  if (reset) FS_CUDA(e, cudaMemsetAsync(e->stats, 0, sizeof(tmp), e->stream));
+  FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  for (int i = 0; i < n && i < 8; ++i) host_out[i] = tmp[i];
+  return FS_OK;
+}
+
+extern "C" int fs_sync(fs_engine* e) {
+  if (!e) return FS_EINVAL;
+  cudaSetDevice(e->cfg.device);
+  FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  return FS_OK;
+}
+
+extern "C" void* fs_stream(fs_engine* e) { return e ? (void*)e->stream : nullptr; }
+extern "C" int64_t fs_launch_count(const fs_engine* e) { return e ? e->launches : 0; }
+
+extern "C" int fs_set_stream(fs_engine* e, void* cuda_stream) {
+  if (!e) return FS_EINVAL;
+  cudaSetDevice(e->cfg.device);
+  FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  if (e->stream && e->own_stream) cudaStreamDestroy(e->stream);
+  e->stream = (cudaStream_t)cuda_stream;
+  e->own_stream = false;
+  return FS_OK;
+}

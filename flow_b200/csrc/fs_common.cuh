@@ -1,0 +1,266 @@
+// fs_common.cuh — device-side parameter tables, math helpers and the
+// car-following / fail-safe laws shared by every step kernel.
+//
+// Reference (parthjaggi/flow) lines each law restates are cited at the
+// function. T is float (FS_F32) or double (FS_F64). In double every formula
+// keeps the reference's operation order so results agree to ~1 ulp; in float
+// divisions become reciprocal multiplies / fast intrinsics (tolerance 1e-4).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/flowstep.h"
+
+#define FS_MAX_VEH 256  // vehicles (ring) or slots (highway) per env
+
+namespace fs {
+
+template <typename T>
+struct TypeP {
+  int ctrl, fail_safe, lc, pad;
+  T p[FS_NPARAM];
+  T noise, delay, max_accel, max_decel, length;
+  T sim_tau, sim_min_gap, sim_v0;  // sim_v0 = min(maxSpeed, speed_limit)
+  T two_sqrt_ab;      // IDM: 2*sqrt(a*b)
+  T sim_two_sqrt_ab;  // simulator-default IDM: 2*sqrt(accel*decel)
+  T inv_v0, sim_inv_v0, inv_two_sqrt_ab, sim_inv_two_sqrt_ab;  // f32 fast path
+};
+
+template <typename T>
+struct Cfg {
+  int n_envs, n_veh, n_lanes, env_kind;
+  int n_types, warmup_steps, horizon, sims_per_step;
+  int clip_actions, lane_change_duration, act_dim, obs_dim;
+  int n_rl, collision_min_gap, any_noise, any_follower;
+  long long env_id_base;
+  unsigned long long seed;
+  T dt, inv_dt, junction_len, speed_limit, inv_speed_limit;
+  T x0, bunching, init_min_gap;
+  T target_velocity, act_lo, act_hi, obs_max_length;
+  T length_lo, length_hi;
+  int lanes_distribution, pad0;
+  TypeP<T> types[FS_MAX_TYPES];
+  uint8_t type_of[FS_MAX_VEH];
+  int16_t rl_index[FS_MAX_VEH];  // vehicle -> action slot, -1 if not RL
+};
+
+// ---------------------------------------------------------------- helpers
+template <typename T> struct Num;
+template <> struct Num<float> {
+  static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+  static __device__ __forceinline__ float sqrt(float a) { return sqrtf(a); }
+  static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
+  static __device__ __forceinline__ float cospi(float a) { return ::cospif(a); }
+  static __device__ __forceinline__ float abs(float a) { return fabsf(a); }
+  static __device__ __forceinline__ float max(float a, float b) { return fmaxf(a, b); }
+  static __device__ __forceinline__ float min(float a, float b) { return fminf(a, b); }
+};
+template <> struct Num<double> {
+  static __device__ __forceinline__ double div(double a, double b) { return a / b; }
+  static __device__ __forceinline__ double sqrt(double a) { return ::sqrt(a); }
+  static __device__ __forceinline__ double pow(double a, double b) { return ::pow(a, b); }
+  static __device__ __forceinline__ double cospi(double a) { return ::cos(3.141592653589793 * a); }
+  static __device__ __forceinline__ double abs(double a) { return fabs(a); }
+  static __device__ __forceinline__ double max(double a, double b) { return fmax(a, b); }
+  static __device__ __forceinline__ double min(double a, double b) { return fmin(a, b); }
+};
+
+// No fused multiply-add in double: Python evaluates a*b+c with two roundings,
+// and the 1e-9 parity bar is easier to hold when we do the same.
+__device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float mul(float a, float b) { return a * b; }
+__device__ __forceinline__ float add(float a, float b) { return a + b; }
+
+// wrap x into [0, C) given x in [0, 2C): equals Python's x % C bit for bit
+template <typename T>
+__device__ __forceinline__ T wrap_fwd(T x, T C) { return x >= C ? x - C : x; }
+// (a - b) mod C for a, b in [0, C): equals Python's (a - b) % C bit for bit
+template <typename T>
+__device__ __forceinline__ T fwd_dist(T a, T b, T C) {
+  T d = a - b;
+  return d < T(0) ? d + C : d;
+}
+
+// ------------------------------------------------------------ Philox4x32-10
+struct Philox {
+  static __device__ __forceinline__ void round(uint32_t (&c)[4], uint32_t (&k)[2]) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+    uint32_t hi0 = __umulhi(M0, c[0]), lo0 = M0 * c[0];
+    uint32_t hi1 = __umulhi(M1, c[2]), lo1 = M1 * c[2];
+    uint32_t n0 = hi1 ^ c[1] ^ k[0], n2 = hi0 ^ c[3] ^ k[1];
+    c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+    k[0] += 0x9E3779B9u; k[1] += 0xBB67AE85u;
+  }
+  // counter = (c0,c1,c2,c3), key = (k0,k1) -> 4 x u32
+  static __device__ __forceinline__ void gen(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                             uint32_t k0, uint32_t k1, uint32_t (&out)[4]) {
+    uint32_t c[4] = {c0, c1, c2, c3}, k[2] = {k0, k1};
+#pragma unroll
+    for (int i = 0; i < 10; ++i) round(c, k);
+    out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+  }
+};
+
+// Standard normal for (env, vehicle, step): Box-Muller on two Philox words.
+// Keyed by the GLOBAL env id so results do not depend on the GPU count.
+template <typename T>
+__device__ __forceinline__ T normal_sample(unsigned long long seed, long long env_gid,
+                                           int veh, int step) {
+  uint32_t r[4];
+  Philox::gen((uint32_t)step, (uint32_t)veh, (uint32_t)env_gid, (uint32_t)(env_gid >> 32),
+              (uint32_t)seed, (uint32_t)(seed >> 32), r);
+  // u1 in (0,1], u2 in [0,1)
+  double u1 = ((double)r[0] + 1.0) * (1.0 / 4294967296.0);
+  double u2 = (double)r[1] * (1.0 / 4294967296.0);
+  if (sizeof(T) == 4) {
+    float rad = sqrtf(-2.0f * __logf((float)u1));
+    return (T)(rad * cospif(2.0f * (float)u2));
+  }
+  return (T)(::sqrt(-2.0 * ::log(u1)) * ::cos(6.283185307179586 * u2));
+}
+
+// ------------------------------------------------------------ controller laws
+// IDM, flow/controllers/car_following_models.py:464-482
+template <typename T>
+__device__ __forceinline__ T idm_accel(T v, T v_lead, T h, bool has_leader, T v0, T inv_v0,
+                                       T Tt, T a, T two_sqrt_ab, T inv_two_sqrt_ab, T delta,
+                                       T s0) {
+  typedef Num<T> N;
+  if (N::abs(h) < T(1e-3)) h = T(1e-3);
+  T s_star = T(0);
+  if (has_leader) {
+    T q;
+    if (sizeof(T) == 8) q = N::div(mul(v, v - v_lead), two_sqrt_ab);
+    else q = v * (v - v_lead) * inv_two_sqrt_ab;
+    s_star = add(s0, N::max(T(0), add(mul(v, Tt), q)));
+  }
+  T r = (sizeof(T) == 8) ? N::div(v, v0) : v * inv_v0;
+  T pw;
+  if (delta == T(4)) { T r2 = mul(r, r); pw = mul(r2, r2); }
+  else pw = N::pow(r, delta);
+  T sh = N::div(s_star, h);
+  return mul(a, (T(1) - pw) - mul(sh, sh));
+}
+
+// get_accel for vehicle with type tp. v: own speed, lead/foll: indices validity,
+// v_l: leader speed (-1001 if none), h: headway, v_f / h_f: follower speed and
+// follower's headway (-1001 if none), mean_v: mean speed over the env.
+// st0/st1: controller state words (LAC: a ; PISaturation: v_cmd, running sum).
+template <typename T>
+__device__ __forceinline__ T ctrl_accel(const TypeP<T>& tp, int ctrl, T v, bool has_lead, T v_l,
+                                        T h, bool has_foll, T v_f, T h_f, T mean_v, T dt,
+                                        T inv_dt, T& st0) {
+  typedef Num<T> N;
+  const T* p = tp.p;
+  switch (ctrl) {
+    case FS_CTRL_IDM:
+      return idm_accel<T>(v, v_l, h, has_lead, p[0], tp.inv_v0, p[1], p[2], tp.two_sqrt_ab,
+                          tp.inv_two_sqrt_ab, p[4], p[5]);
+    case FS_CTRL_SIM:
+    case FS_CTRL_RL:
+      // restated simulator default model: IDM fed with the
+      // type's SumoCarFollowingParams, flow/core/params.py:842-846
+      return idm_accel<T>(v, v_l, h, has_lead, tp.sim_v0, tp.sim_inv_v0, tp.sim_tau,
+                          tp.max_accel, tp.sim_two_sqrt_ab, tp.sim_inv_two_sqrt_ab, T(4),
+                          tp.sim_min_gap);
+    case FS_CTRL_OVM: {  // car_following_models.py:308-328
+      if (!has_lead) return tp.max_accel;
+      T h_dot = v_l - v, v_h;
+      if (h <= p[2]) v_h = T(0);
+      else if (h < p[3]) {
+        T c;
+        if (sizeof(T) == 8)  // reference order: cos(pi * (h - h_st) / (h_go - h_st))
+          c = (T)::cos((double)N::div(mul(T(3.141592653589793), h - p[2]), p[3] - p[2]));
+        else
+          c = N::cospi(N::div(h - p[2], p[3] - p[2]));
+        v_h = mul(p[4] / T(2), T(1) - c);
+      } else v_h = p[4];
+      return add(mul(p[0], v_h - v), mul(p[1], h_dot));
+    }
+    case FS_CTRL_LINEAR_OVM: {  // car_following_models.py:383-397
+      const T alpha = T(1.689);
+      T v_h;
+      if (h < p[2]) v_h = T(0);
+      else if (h <= add(p[2], N::div(p[0], alpha))) v_h = mul(alpha, h - p[2]);
+      else v_h = p[0];
+      return N::div(v_h - v, p[1]);
+    }
+    case FS_CTRL_CFM:  // car_following_models.py:76-88
+      if (!has_lead) return tp.max_accel;
+      return add(add(mul(p[0], h - p[3]), mul(p[1], v_l - v)), mul(p[2], p[4] - v));
+    case FS_CTRL_BCM: {  // car_following_models.py:152-176
+      if (!has_lead) return tp.max_accel;
+      return add(add(mul(p[0], h - h_f), mul(p[1], (v_l - v) - (v - v_f))),
+                 mul(p[2], p[4] - v));
+    }
+    case FS_CTRL_LAC: {  // car_following_models.py:232-245 ; st0 = a
+      T ex = (h - tp.length) - mul(p[2], v);
+      T ev = v_l - v;
+      T u = add(mul(p[0], ex), mul(p[1], ev));
+      T a_dot = add(-N::div(st0, p[3]), N::div(u, p[3]));
+      st0 = add(mul(a_dot, dt), st0);
+      return st0;
+    }
+    case FS_CTRL_GIPPS: {  // car_following_models.py:567-582
+      T v0 = p[0], acc = p[1], b = p[2], b_l = p[3], s0 = p[4], tau = p[5];
+      T r = N::div(v, v0);
+      T v_acc = add(v, mul(mul(mul(mul(T(2.5), acc), tau), T(1) - r),
+                           N::sqrt(add(T(0.025), r))));
+      T inner = (mul(T(2), h - s0) - mul(tau, v)) - N::div(mul(v_l, v_l), b_l);
+      T v_safe = add(mul(tau, b),
+                     N::sqrt(mul(mul(tau, tau), mul(b, b)) - mul(b, inner)));
+      T v_next = N::min(N::min(v_acc, v_safe), v0);
+      return N::div(v_next - v, dt);
+    }
+    case FS_CTRL_FOLLOWER_STOPPER:
+    case FS_CTRL_NONLOCAL_FOLLOWER_STOPPER: {  // velocity_controllers.py:75-116, :122-164
+      T v_des = (ctrl == FS_CTRL_NONLOCAL_FOLLOWER_STOPPER) ? mean_v : p[0];
+      T v_cmd;
+      if (!has_lead) v_cmd = v_des;
+      else {
+        T dvm = N::min(v_l - v, T(0));
+        T dv2 = mul(dvm, dvm);
+        T dx1 = add(T(4.5), mul(T(1) / (T(2) * T(1.5)), dv2));
+        T dx2 = add(T(5.25), mul(T(1) / (T(2) * T(1.0)), dv2));
+        T dx3 = add(T(6.0), mul(T(1) / (T(2) * T(0.5)), dv2));
+        T vv = N::min(N::max(v_l, T(0)), v_des);
+        if (h <= dx1) v_cmd = T(0);
+        else if (h <= dx2) v_cmd = N::div(mul(vv, h - dx1), dx2 - dx1);
+        else if (h <= dx3) v_cmd = add(vv, N::div(mul(v_des - v, h - dx2), dx3 - dx2));
+        else v_cmd = v_des;
+      }
+      return N::div(v_cmd - v, dt);
+    }
+    default:
+      return T(0);
+  }
+}
+
+// base_controller.py:120-169
+template <typename T>
+__device__ __forceinline__ T failsafe_instantaneous(T a, T v, T h, bool has_lead, int n_veh,
+                                                    T dt) {
+  if (n_veh == 1 || !has_lead) return a;
+  T next_vel = add(v, mul(a, dt));
+  if (next_vel > T(0)) {
+    T lim = add(add(mul(dt, next_vel), mul(v, T(1e-3))), mul(mul(T(0.5), v), dt));
+    if (h < lim) return Num<T>::div(-v, dt);
+  }
+  return a;
+}
+
+// base_controller.py:171-236
+template <typename T>
+__device__ __forceinline__ T failsafe_safe_velocity(T a, T v, T v_l, T h, int n_veh, T dt,
+                                                    T delay) {
+  if (n_veh == 1) return a;
+  T dv = v_l - v;
+  T v_safe = add(Num<T>::div(mul(T(2), h), dt), dv) - mul(v, mul(T(2), delay));
+  if (add(v, mul(a, dt)) > v_safe) {
+    if (v_safe > T(0)) return Num<T>::div(v_safe - v, dt);
+    return Num<T>::div(-v, dt);
+  }
+  return a;
+}
+
+}  // namespace fs

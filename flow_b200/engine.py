@@ -1,0 +1,249 @@
+"""Python handle on one libflowstep engine (one per GPU).
+
+Device buffers stay owned by the C library; they are exposed to Python as
+torch tensors through DLPack capsules built here from the raw pointers
+fs_buffers() returns (zero copy, never freed by torch).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+# ---- constants mirrored from include/flowstep.h ----------------------------
+F32, F64 = 0, 1
+TOPO_RING, TOPO_HIGHWAY = 0, 1
+ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
+    ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY = range(6)
+CTRL_SIM, CTRL_IDM, CTRL_OVM, CTRL_LINEAR_OVM, CTRL_BCM, CTRL_CFM, CTRL_LAC, \
+    CTRL_GIPPS, CTRL_FOLLOWER_STOPPER, CTRL_NONLOCAL_FOLLOWER_STOPPER, \
+    CTRL_PI_SATURATION, CTRL_RL = range(12)
+FAILSAFE = {None: 0, 'instantaneous': 1, 'safe_velocity': 2}
+LC_SIM, LC_STATIC, LC_RL = 0, 1, 2
+
+
+class FlowStepError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__('libflowstep error %d: %s' % (code, msg))
+        self.code = code
+
+
+# ---- DLPack capsule from a raw device pointer ---------------------------------
+class _DLDevice(C.Structure):
+    _fields_ = [('device_type', C.c_int32), ('device_id', C.c_int32)]
+
+
+class _DLDataType(C.Structure):
+    _fields_ = [('code', C.c_uint8), ('bits', C.c_uint8), ('lanes', C.c_uint16)]
+
+
+class _DLTensor(C.Structure):
+    _fields_ = [('data', C.c_void_p), ('device', _DLDevice), ('ndim', C.c_int32),
+                ('dtype', _DLDataType), ('shape', C.POINTER(C.c_int64)),
+                ('strides', C.POINTER(C.c_int64)), ('byte_offset', C.c_uint64)]
+
+
+class _DLManagedTensor(C.Structure):
+    pass
+
+
+_DELETER = C.CFUNCTYPE(None, C.POINTER(_DLManagedTensor))
+_DLManagedTensor._fields_ = [('dl_tensor', _DLTensor), ('manager_ctx', C.c_void_p),
+                             ('deleter', _DELETER)]
+
+_live = {}
+
+
+@_DELETER
+def _dl_deleter(ptr):
+    _live.pop(C.addressof(ptr.contents), None)
+
+
+_DL_CODES = {'f32': (2, 32), 'f64': (2, 64), 'u8': (1, 8), 'i32': (0, 32)}
+_PyCapsule_New = C.pythonapi.PyCapsule_New
+_PyCapsule_New.restype = C.py_object
+_PyCapsule_New.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+
+
+def dlpack_capsule(ptr, shape, dtype, device_id):
+    """DLPack ('dltensor') capsule for device memory the engine owns."""
+    m = _DLManagedTensor()
+    shp = (C.c_int64 * len(shape))(*shape)
+    code, bits = _DL_CODES[dtype]
+    m.dl_tensor.data = ptr
+    m.dl_tensor.device = _DLDevice(2, device_id)  # kDLCUDA
+    m.dl_tensor.ndim = len(shape)
+    m.dl_tensor.dtype = _DLDataType(code, bits, 1)
+    m.dl_tensor.shape = shp
+    m.dl_tensor.strides = None
+    m.dl_tensor.byte_offset = 0
+    m.manager_ctx = None
+    m.deleter = _dl_deleter
+    _live[C.addressof(m)] = (m, shp)
+    return _PyCapsule_New(C.addressof(m), b'dltensor', None)
+
+
+def _as_tensor(ptr, shape, dtype, device_id):
+    import torch
+    if not ptr:
+        return None
+    return torch.from_dlpack(dlpack_capsule(ptr, shape, dtype, device_id))
+
+
+class VType(dict):
+    """Keyword bag for one fs_vtype row (see include/flowstep.h)."""
+
+
+def make_vtype(controller, p=(), fail_safe=None, noise=0.0, delay=0.0,
+               max_accel=2.6, max_decel=4.5, length=5.0, sim_tau=1.0,
+               sim_min_gap=2.5, sim_max_speed=30.0, lc_controller=LC_SIM):
+    t = _lib.FsVType()
+    t.controller = controller
+    t.fail_safe = FAILSAFE[fail_safe] if not isinstance(fail_safe, int) else fail_safe
+    t.lc_controller = lc_controller
+    for i, v in enumerate(p):
+        t.p[i] = float(v)
+    t.noise, t.delay = float(noise), float(delay)
+    t.max_accel, t.max_decel, t.length = float(max_accel), abs(float(max_decel)), float(length)
+    t.sim_tau, t.sim_min_gap, t.sim_max_speed = float(sim_tau), float(sim_min_gap), float(sim_max_speed)
+    return t
+
+
+class Engine:
+    """One batched step engine on one GPU. Not thread-safe."""
+
+    def __init__(self, types, type_of_vehicle, n_envs, dtype='f32', device=0,
+                 use_torch_stream=True, **cfg):
+        self.lib = _lib.load()
+        c = _lib.FsConfig()
+        c.abi_version = 1
+        c.device = device
+        c.dtype = F64 if dtype in ('f64', F64, 'float64') else F32
+        c.n_envs = n_envs
+        c.n_veh = len(type_of_vehicle)
+        defaults = dict(topology=TOPO_RING, env_kind=ENV_ACCEL, n_lanes=1, env_id_base=0,
+                        seed=0, sim_step=0.1, length_lo=230.0, length_hi=230.0,
+                        junction_len=0.1, speed_limit=30.0, x0=0.0, bunching=0.0,
+                        init_min_gap=0.0, lanes_distribution=1 << 30, warmup_steps=0,
+                        horizon=3000, sims_per_step=1, clip_actions=0,
+                        lane_change_duration=5, target_velocity=10.0, act_lo=-4.5,
+                        act_hi=2.6, obs_max_length=0.0, inflow_vehs_per_hour=0.0,
+                        inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
+                        record_views=0)
+        unknown = set(cfg) - set(defaults)
+        if unknown:
+            raise TypeError('unknown engine config keys: %s' % sorted(unknown))
+        defaults.update(cfg)
+        for k, v in defaults.items():
+            setattr(c, k, v)
+        self.config = c
+        self.dtype = 'f64' if c.dtype == F64 else 'f32'
+        self.np_dtype = np.float64 if c.dtype == F64 else np.float32
+        self.device = device
+        self.n_envs, self.n_veh = n_envs, c.n_veh
+        h = C.c_void_p()
+        rc = self.lib.fs_create(C.byref(c), C.byref(h))
+        if rc != 0:
+            raise FlowStepError(rc, self.lib.fs_last_error(None).decode())
+        self.h = h
+        if use_torch_stream:
+            import torch
+            with torch.cuda.device(device):
+                s = torch.cuda.current_stream().cuda_stream
+            self._check(self.lib.fs_set_stream(self.h, C.c_void_p(s)))
+        arr = (_lib.FsVType * len(types))(*types)
+        tov = np.ascontiguousarray(type_of_vehicle, dtype=np.uint8)
+        self._check(self.lib.fs_set_types(self.h, arr, len(types), tov.ctypes.data))
+        v = _lib.FsViews()
+        self._check(self.lib.fs_buffers(self.h, C.byref(v)))
+        self.views = v
+        self.obs_dim, self.act_dim = v.obs_dim, v.act_dim
+        E, V, dt = n_envs, c.n_veh, self.dtype
+        T = lambda p, shape, d=dt: _as_tensor(p, shape, d, device)  # noqa: E731
+        self.pos, self.vel = T(v.pos, (V, E)), T(v.vel, (V, E))
+        self.lane, self.active = T(v.lane, (V, E), 'u8'), T(v.active, (V, E), 'u8')
+        self.headway, self.accel = T(v.headway, (V, E)), T(v.accel, (V, E))
+        self.leader, self.follower = T(v.leader, (V, E), 'i32'), T(v.follower, (V, E), 'i32')
+        self.length = T(v.length, (E,))
+        self.obs, self.reward = T(v.obs, (E, self.obs_dim)), T(v.reward, (E,))
+        self.done, self.crash = T(v.done, (E,), 'u8'), T(v.crash, (E,), 'u8')
+        self.time_counter = T(v.time_counter, (E,), 'i32')
+
+    def _check(self, rc):
+        if rc != 0:
+            raise FlowStepError(rc, self.lib.fs_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, 'h', None):
+            self.lib.fs_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- reset / step -------------------------------------------------------
+    def reset(self, mask=None, lengths=None):
+        m = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+        ln = None if lengths is None else np.ascontiguousarray(lengths, dtype=np.float64)
+        self._check(self.lib.fs_reset(self.h, None if m is None else m.ctypes.data,
+                                      None if ln is None else ln.ctypes.data))
+        return self.obs
+
+    def step(self, actions=None, k=1, obs_seq=None, reward_seq=None, done_seq=None):
+        """k fused steps with DEVICE tensors (any DLPack producer).
+        actions: [k, act_dim, E] (or [act_dim, E] / [E] when k == 1)."""
+        import torch
+        a_ptr = None
+        if actions is not None:
+            if not isinstance(actions, torch.Tensor):
+                actions = torch.from_dlpack(actions)
+            want = torch.float64 if self.dtype == 'f64' else torch.float32
+            if actions.dtype != want or not actions.is_contiguous():
+                actions = actions.to(want).contiguous()
+            if actions.numel() != k * self.act_dim * self.n_envs:
+                raise ValueError('actions must have k*act_dim*n_envs = %d elements, got %d'
+                                 % (k * self.act_dim * self.n_envs, actions.numel()))
+            a_ptr = actions.data_ptr()
+        p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+        self._check(self.lib.fs_step(self.h, a_ptr, k, p(obs_seq), p(reward_seq), p(done_seq)))
+        return self.obs, self.reward, self.done
+
+    def step_host(self, actions, k=1, want_obs=True):
+        """k fused steps with HOST numpy buffers; returns (obs, reward, done) arrays
+        of every step ([k,E,obs_dim], [k,E], [k,E])."""
+        E = self.n_envs
+        a = None
+        if actions is not None:
+            a = np.ascontiguousarray(actions, dtype=self.np_dtype)
+            if a.size != k * self.act_dim * E:
+                raise ValueError('actions must have k*act_dim*n_envs elements')
+        obs = np.empty((k, E, self.obs_dim), self.np_dtype) if want_obs else None
+        rew = np.empty((k, E), self.np_dtype)
+        done = np.empty((k, E), np.uint8)
+        self._check(self.lib.fs_step_host(
+            self.h, None if a is None else a.ctypes.data, k,
+            None if obs is None else obs.ctypes.data, rew.ctypes.data, done.ctypes.data))
+        return obs, rew, done
+
+    def set_state(self, pos=None, vel=None, lane=None, lengths=None):
+        f = lambda x, d: None if x is None else np.ascontiguousarray(x, dtype=d)  # noqa: E731
+        pos, vel = f(pos, self.np_dtype), f(vel, self.np_dtype)
+        lane, lengths = f(lane, np.uint8), f(lengths, np.float64)
+        q = lambda x: None if x is None else x.ctypes.data  # noqa: E731
+        self._check(self.lib.fs_set_state(self.h, q(pos), q(vel), q(lane), q(lengths)))
+
+    def stats(self, reset=False):
+        out = (C.c_double * 8)()
+        self._check(self.lib.fs_stats(self.h, out, 8, int(reset)))
+        keys = ['sum_reward', 'sum_speed', 'sum_speed_sq', 'vehicle_steps', 'env_steps', 'crashes']
+        return dict(zip(keys, list(out)[:6]))
+
+    def sync(self):
+        self._check(self.lib.fs_sync(self.h))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.fs_launch_count(self.h))

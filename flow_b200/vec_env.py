@@ -1,0 +1,83 @@
+"""B200VecEnv — the batched front of the engine: N independent Flow
+environments stepped together on one GPU.
+
+Mirrors the gym contract of flow/envs/base.py (reset() -> obs,
+step(rl_actions) -> (obs, reward, done, info)) with a leading env axis:
+obs [E, obs_dim], reward [E], done [E] as torch CUDA tensors that alias the
+engine's buffers (zero copy, DLPack). `rollout` runs K fused steps from an
+action sequence; `*_host` variants take/return pinned host arrays.
+"""
+import numpy as np
+
+from . import engine as EN
+
+
+class B200VecEnv:
+    def __init__(self, types, type_of_vehicle, n_envs, dtype='f32', device=0, **cfg):
+        self.engine = EN.Engine(types, type_of_vehicle, n_envs, dtype=dtype,
+                                device=device, **cfg)
+        self.n_envs = n_envs
+        self.obs_dim, self.act_dim = self.engine.obs_dim, self.engine.act_dim
+        self.dtype = self.engine.dtype
+        self._pinned = {}
+
+    # -- gym-like, device tensors -------------------------------------------
+    def reset(self, mask=None, lengths=None):
+        return self.engine.reset(mask, lengths)
+
+    def step(self, rl_actions=None):
+        """One Env.step for every env. rl_actions: [E] / [act_dim, E] device
+        tensor (any DLPack producer) or None (RL vehicles follow the simulator
+        model, as in the reference's warm-up)."""
+        obs, rew, done = self.engine.step(rl_actions, k=1)
+        return obs, rew, done, {}
+
+    def rollout(self, actions, obs_seq=None, reward_seq=None, done_seq=None):
+        """K = actions.shape[0] fused steps in one launch. actions [K, act_dim, E]."""
+        k = int(actions.shape[0])
+        self.engine.step(actions, k=k, obs_seq=obs_seq, reward_seq=reward_seq,
+                         done_seq=done_seq)
+        return obs_seq, reward_seq, done_seq
+
+    # -- host buffers (the e2e path: H2D actions, D2H obs/reward/done) ---------
+    def _pinned_buf(self, name, shape, dtype):
+        import torch
+        key = (name, tuple(shape))
+        if key not in self._pinned:
+            self._pinned[key] = torch.empty(shape, dtype=dtype).pin_memory()
+        return self._pinned[key]
+
+    def pinned_actions(self, k):
+        import torch
+        td = torch.float64 if self.dtype == 'f64' else torch.float32
+        return self._pinned_buf('act', (k, self.act_dim, self.n_envs), td)
+
+    def rollout_host(self, actions_host, k=None):
+        """actions_host: numpy / pinned torch CPU tensor [K, act_dim, E].
+        Returns numpy views (pinned) of obs [K,E,obs_dim], reward [K,E], done [K,E]."""
+        import torch
+        td = torch.float64 if self.dtype == 'f64' else torch.float32
+        if isinstance(actions_host, torch.Tensor):
+            a = actions_host.numpy()
+        else:
+            a = np.ascontiguousarray(actions_host, dtype=self.engine.np_dtype)
+        k = int(a.shape[0]) if k is None else k
+        E = self.n_envs
+        obs = self._pinned_buf('obs', (k, E, self.obs_dim), td).numpy()
+        rew = self._pinned_buf('rew', (k, E), td).numpy()
+        done = self._pinned_buf('done', (k, E), torch.uint8).numpy()
+        e = self.engine
+        e._check(e.lib.fs_step_host(e.h, a.ctypes.data, k, obs.ctypes.data,
+                                    rew.ctypes.data, done.ctypes.data))
+        return obs, rew, done
+
+    def step_host(self, actions_host):
+        a = np.asarray(actions_host).reshape(1, self.act_dim, self.n_envs)
+        obs, rew, done = self.rollout_host(a, 1)
+        return obs[0], rew[0], done[0], {}
+
+    def stats(self, reset=False):
+        return self.engine.stats(reset)
+
+    def close(self):
+        self.engine.close()

@@ -141,6 +141,8 @@ typedef struct fs_config {
   double inflow_vehs_per_hour, inflow_depart_speed;
   int32_t inflow_type;   /* vehicle type index of inflow vehicles               */
   int32_t collision_min_gap; /* 0: crash iff gap<0 ; 1: crash iff gap<minGap    */
+  int32_t record_views;  /* 1: keep views.accel/headway/leader/follower current  */
+  int32_t reserved0;
 } fs_config;
 
 /* device views; T = float or double per cfg.dtype; [a][b] = a slow, b fast */
@@ -204,6 +206,9 @@ int fs_stats(fs_engine* e, double* host_out, int n, int reset);
 int fs_sync(fs_engine* e);
 /* cudaStream_t of the engine, for callers that want to order their own work */
 void* fs_stream(fs_engine* e);
+/* Adopt a caller-owned cudaStream_t (e.g. torch's current stream; NULL = the
+ * legacy default stream) so engine work is ordered with the caller's. */
+int fs_set_stream(fs_engine* e, void* cuda_stream);
 /* number of kernel launches issued by this engine since creation */
 int64_t fs_launch_count(const fs_engine* e);
 

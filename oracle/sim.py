@@ -172,6 +172,19 @@ class RingSim:
         """Leader / headway / follower of every vehicle
         (flow/core/kernel/vehicle/traci.py:218-250 around SUMO's getLeader)."""
         V = self.num_vehicles
+        if self.n_lanes == 1 and V > 1:
+            # single lane, no overtaking: if the vehicles are still in index
+            # order round the loop (forward distances sum to one lap) the
+            # leader of i is i+1 and the follower i-1 — the same answer the
+            # general search below gives, without the O(V^2) scan.
+            C_, pos, types, type_of = self.circ, self.pos, self.types, self.type_of
+            d = [(pos[i + 1 - V] - pos[i]) % C_ for i in range(V)]
+            if abs(sum(d) - C_) < 1e-6 * C_ and min(d) > 0:
+                self.leader = [(i + 1) % V for i in range(V)]
+                self.follower = [(i - 1) % V for i in range(V)]
+                self.headway = [d[i] - types[type_of[i + 1 - V]].length
+                                for i in range(V)]
+                return
         self.leader = [-1] * V
         self.follower = [-1] * V
         self.headway = [1e3] * V
