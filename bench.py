@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py — env-steps/s and vehicle-steps/s of the batched ring step path.
+
+  python bench.py --gpus N --steps K --warmup W [--workload c2|c5] [--fuse F]
+  python bench.py --impl reference ...      # CPU arm: the oracle port on host cores
+
+A "step" is one Env.step of EVERY environment of the batch (E per GPU).
+Workload c2 (default, BASELINE.json configs[1]): WaveAttenuationPOEnv ring,
+21 IDM + 1 RL vehicle, ring length ~ U{220..270}, 750 warm-up steps at reset,
+random RL actions, E = 4096 envs per GPU. c5: same with E = 65536 per GPU.
+
+Timed numbers
+  value    vehicle-steps/s, whole job, inputs (actions) resident in HBM, the
+           K steps issued as fused launches of F steps (per-step obs/reward/
+           done of every env are written for every step);
+  e2e      same metric through B200VecEnv.rollout_host: HOST pinned action
+           buffers in, obs/reward/done of every step back on the host, the
+           copies inside the timed region;
+  single_step  K launches of one step each (the closed-loop gym cadence).
+All device timings use CUDA events on the stream the kernels run on; N > 1 is
+one process per GPU with a barrier and the max over ranks.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# algorithmic bytes: pos+vel read+write 16 B per
+# vehicle-step, plus per env-step: ring length 4 + action 4 read, obs 12 +
+# reward 4 + done 1 written = 25 B  ->  22*16 + 25 = 377 B per env-step.
+BYTES_PER_ENV_STEP = 22 * 16 + 25
+N_VEH = 22
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=3000)
+    ap.add_argument('--warmup', type=int, default=300)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5'])
+    ap.add_argument('--fuse', type=int, default=100, help='steps per fused launch')
+    ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--cpu-envs-per-core', type=int, default=2)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------- CPU arm (oracle)
+def _cpu_worker(args):
+    """One env, `steps` Env.steps of workload c2 on the oracle port (scalar
+    Python, like the reference's per-vehicle loop). Returns seconds."""
+    seed, steps = args
+    import numpy as np
+    from oracle import sim as OS
+    from oracle import controllers as OC
+    rng = np.random.default_rng(seed)
+    types = [OC.VType(OC.IDM, OC.idm_params(), sim_min_gap=0.0), OC.VType(OC.RL)]
+    length = int(rng.integers(220, 271))
+    env = OS.RingSim(types, [0] * 21 + [1], length, bunching=50.0,
+                     env_kind=OS.ENV_WAVE_ATTENUATION_PO, warmup_steps=0, horizon=10 ** 9,
+                     act_lo=-1, act_hi=1, obs_max_length=270.0)
+    acts = rng.uniform(-1, 1, size=steps)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        _, _, done = env.step([acts[k]])
+        if done:
+            env.reset(length, run_warmup=False)
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(steps_per_env, envs_per_core, cores=None):
+    """Oracle port on all host cores, one env per worker process at a time
+    (how RLlib runs the reference). Returns dict for the JSON line."""
+    import multiprocessing as mp
+    cores = cores or os.cpu_count() or 1
+    jobs = [(1000 + i, steps_per_env) for i in range(cores * envs_per_core)]
+    ctx = mp.get_context('spawn')
+    with ctx.Pool(cores) as pool:
+        secs = pool.map(_cpu_worker, jobs, chunksize=1)
+    # process start-up / imports are excluded: every worker times only its
+    # stepping loop; `cores` workers run concurrently, so the aggregate rate
+    # is cores x the mean per-worker rate.
+    rate = cores * statistics.mean(steps_per_env / t for t in secs)
+    return dict(value=rate * N_VEH, unit='vehicle-steps/s', cores=cores, kind='port',
+                env_steps_per_s=rate,
+                sample='%d envs x %d steps of workload c2 on oracle/sim.py (scalar Python port '
+                       'of the reference loop), %d worker processes' % (len(jobs), steps_per_env, cores))
+
+
+def run_reference(a):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    t_all = []
+    base = None
+    for i in range(a.warmup + a.steps):
+        # each "step" of the reference arm = a bounded sample: every core
+        # advances one env by 3000 Env.steps
+        t0 = time.perf_counter()
+        base = cpu_baseline(3000, 1)
+        if i >= a.warmup:
+            t_all.append((time.perf_counter() - t0, base))
+    val = statistics.mean(b['value'] for _, b in t_all)
+    ms = 1e3 * statistics.mean(t for t, _ in t_all)
+    base = dict(base, value=val)
+    print(json.dumps({
+        'impl': 'reference', 'metric': 'vehicle-steps/s', 'value': val, 'unit': 'vehicle-steps/s',
+        'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': ms,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+        'data': 'synthetic', 'env_steps_per_s': val / N_VEH,
+        'config': {'workload': 'c2: WaveAttenuationPOEnv ring 21 IDM + 1 RL, random RL actions; '
+                               'CPU arm: one env per host core, 3000 Env.steps per sample'},
+        'cpu_baseline': base,
+        'e2e': {'value': val, 'unit': 'vehicle-steps/s', 'h2d_bytes_per_step': 0,
+                'd2h_bytes_per_step': 0},
+        'gpu_launches': 0}))
+
+
+# ------------------------------------------------------------------ B200 arm
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed regions."""
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+         'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(
+                ['nvidia-smi', '-i', str(gpu_index), '--query-gpu=' + self.Q,
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for line in self.f:
+            c = [x.strip() for x in line.split(',')]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            # "under load" = upper half of the samples (idle gaps between phases excluded)
+            hi = sorted(sm)[len(sm) // 2:]
+            out.update(sm_mhz=statistics.median(hi), sm_max_mhz=max(mx), samples=len(sm))
+        out['reasons'] = sorted(reasons)
+        return out
+
+
+def measured_peak():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+        except Exception:
+            pass
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from flow_b200.vec_env import B200VecEnv
+    from flow_b200.workloads import WORKLOADS
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if world != a.gpus and world > 1:
+        raise SystemExit('--gpus %d but WORLD_SIZE=%d' % (a.gpus, world))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    wl = WORKLOADS[a.workload]
+    E, K, W, F = wl['n_envs'], a.steps, a.warmup, max(1, min(a.fuse, a.steps))
+    types, tov, kw = wl['builder']()
+    kw['horizon'] = max(kw['horizon'], K)
+    env = B200VecEnv(types, tov, E, dtype=a.dtype, device=local, env_id_base=rank * E,
+                     seed=1234, **kw)
+    eng = env.engine
+    td = torch.float32 if a.dtype == 'f32' else torch.float64
+    ts = 4 if a.dtype == 'f32' else 8
+    gen = torch.Generator(device='cuda'); gen.manual_seed(4321 + rank)
+    act = torch.rand(K, 1, E, device='cuda', dtype=td, generator=gen) * 2 - 1
+    obs_seq = torch.empty(K, E, env.obs_dim, device='cuda', dtype=td)
+    rew_seq = torch.empty(K, E, device='cuda', dtype=td)
+    done_seq = torch.empty(K, E, device='cuda', dtype=torch.uint8)
+    act_host = act.cpu().pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def fused_pass(n_steps):
+        for s in range(0, n_steps, F):
+            k = min(F, n_steps - s)
+            eng.step(act[s:s + k], k=k, obs_seq=obs_seq[s:s + k], reward_seq=rew_seq[s:s + k],
+                     done_seq=done_seq[s:s + k])
+
+    def single_pass(n_steps):
+        for s in range(n_steps):
+            eng.step(act[s], k=1, obs_seq=obs_seq[s:s + 1], reward_seq=rew_seq[s:s + 1],
+                     done_seq=done_seq[s:s + 1])
+
+    def host_pass(n_steps):
+        for s in range(0, n_steps, F):
+            k = min(F, n_steps - s)
+            env.rollout_host(act_host[s:s + k])
+
+    def host_single_pass(n_steps):
+        for s in range(n_steps):
+            env.rollout_host(act_host[s:s + 1])
+
+    def timed(fn, n_steps):
+        """reset -> W warm-up steps -> reset -> barrier -> time n_steps -> barrier.
+        Returns (ms max over ranks, vehicle-steps summed over ranks, launches on this rank)."""
+        env.reset()
+        fn(min(W, n_steps))
+        env.reset()
+        eng.stats(reset=True)
+        barrier()
+        l0 = eng.launch_count
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(n_steps)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        st = eng.stats()
+        v = torch.tensor([ms, st['vehicle_steps'], st['env_steps'], st['crashes'], st['sum_reward'],
+                          st['sum_speed']], device='cuda', dtype=torch.float64)
+        if world > 1:
+            mx = v[:1].clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            dist.all_reduce(v, op=dist.ReduceOp.SUM)   # rollout statistics over NCCL
+            v[0] = mx[0]
+        ms, vs, es, cr, sr, ss = [float(x) for x in v.tolist()]
+        return dict(ms=ms, vehicle_steps=vs, env_steps=es, crashes=cr, mean_reward=sr / max(es, 1),
+                    mean_speed=ss / max(vs, 1), launches=eng.launch_count - l0)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    fused = timed(fused_pass, K)
+    single = timed(single_pass, K)
+    host = timed(host_pass, K)
+    host1 = timed(host_single_pass, min(K, 1000))
+    clocks = sampler.stop() if sampler else None
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    def vps(r):
+        return r['vehicle_steps'] / (r['ms'] * 1e-3)
+
+    peak, peak_src = measured_peak()
+    n_launch = fused['launches']
+    launch_ms = fused['ms'] / max(n_launch, 1)
+    # per-GPU algorithmic bytes of one fused launch / its duration
+    alg_bytes = BYTES_PER_ENV_STEP * (ts / 4) * (fused['env_steps'] / world) / max(n_launch, 1)
+    achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get('%s_%s_fuse%d' % (a.workload, a.dtype, F))
+        except Exception:
+            traffic = None
+    h2d = F * E * ts
+    d2h = F * E * (env.obs_dim * ts + ts + 1)
+    line = {
+        'metric': 'vehicle-steps/s', 'value': vps(fused), 'unit': 'vehicle-steps/s',
+        'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': fused['ms'] / K,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': a.dtype,
+        'data': 'synthetic',
+        'env_steps_per_s': fused['env_steps'] / (fused['ms'] * 1e-3),
+        'config': {'workload': '%s: %s' % (a.workload, wl['name']), 'envs_per_gpu': E,
+                   'vehicles_per_env': N_VEH, 'fuse': F, 'parallelism': 'envs sharded, %d GPU(s), '
+                   'no data-path collective' % world,
+                   'l2': 'streamed actions/obs/reward/done %.0f MB per pass > 126 MB L2 is %s; '
+                         'vehicle state is register-resident inside a fused launch'
+                         % ((act.numel() + obs_seq.numel() + rew_seq.numel()) * ts / 1e6 + done_seq.numel() / 1e6,
+                            str((act.numel() + obs_seq.numel() + rew_seq.numel()) * ts + done_seq.numel() > 126e6)),
+                   'counted': 'vehicle-steps actually advanced (engine counter); frozen (crashed) '
+                              'envs are not counted'},
+        'crashed_env_frac': fused['crashes'] / (E * world),
+        'mean_reward': fused['mean_reward'], 'mean_speed': fused['mean_speed'],
+        'gpu_launches': n_launch,
+        'single_step': {'value': vps(single), 'unit': 'vehicle-steps/s',
+                        'ms_per_step': single['ms'] / K, 'launches': single['launches']},
+        'e2e': {'value': vps(host), 'unit': 'vehicle-steps/s', 'h2d_bytes_per_step': h2d / F,
+                'd2h_bytes_per_step': d2h / F, 'api': 'B200VecEnv.rollout_host, %d steps per call, '
+                'pinned host buffers' % F, 'ms_per_step': host['ms'] / K},
+        'e2e_single_step': {'value': vps(host1), 'unit': 'vehicle-steps/s',
+                            'ms_per_step': host1['ms'] / min(K, 1000),
+                            'api': 'B200VecEnv.rollout_host, 1 step per call'},
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
+                     'kernel': 'ring1_step_kernel<%s,22> fused %d steps/launch' % (a.dtype, F),
+                     'launch_ms': launch_ms,
+                     'note': 'algorithmic bytes = %d B per env-step (SURVEY 8d) x env-steps per '
+                             'launch; fused launches keep state in registers, so this is the '
+                             'single-step HBM roofline the fused kernel is measured against'
+                             % int(BYTES_PER_ENV_STEP * ts / 4)},
+        'roofline_single_step': {
+            'bound': 'hbm', 'unit': 'GB/s', 'peak': peak,
+            'achieved': BYTES_PER_ENV_STEP * (ts / 4) * E / (single['ms'] / K * 1e-3) / 1e9,
+            'frac': BYTES_PER_ENV_STEP * (ts / 4) * E / (single['ms'] / K * 1e-3) / 1e9 / peak},
+        'clocks': clocks,
+    }
+    if world == 1 and not a.no_cpu_baseline:
+        line['cpu_baseline'] = cpu_baseline(10000, a.cpu_envs_per_core)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == '__main__':
+    main()

@@ -206,6 +206,7 @@ class RefRing:
         # borrow the restated leader search
         shim = type('S', (), {})()
         shim.num_vehicles = len(self.ids)
+        shim.n_lanes = 0  # always the general per-lane search, never the shortcut
         shim.lane, shim.pos, shim.circ = self.lane, self.pos, self.net.circ
         from oracle.controllers import VType
         shim.types, shim.type_of = [VType()], [0] * len(self.ids)
