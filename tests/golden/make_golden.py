@@ -1,0 +1,237 @@
+"""Generate tests/golden/*.npz|json by running the REAL reference code
+(imported from /root/reference through ref_shim) — run in the build container:
+
+    python -m tests.golden.make_golden
+
+Outputs (committed):
+  kat.json          known-answer vectors of the reference's own unit tests
+                    (tests/fast_tests/test_controllers.py, test_rewards.py,
+                    test_environments.py) re-evaluated with the reference's
+                    controller / reward code on the stated inputs;
+  ring_c1.npz       22 IDM, 230 m, bunching 20 (examples/exp_configs/non_rl/ring.py)
+  ring_c2.npz       21 IDM + 1 RL WaveAttenuationPO, two lengths, warm-up + actions
+  ring_zoo.npz      one trajectory per controller / fail-safe combination
+  start_pos.json    gen_even_start_pos outputs for several configurations
+  sumo_ring_230.json  the SUMO-produced trajectory fixture of the reference
+                    (tests/fast_tests/test_files/ring_230_emission.csv), reduced
+"""
+import csv
+import json
+import os
+
+import numpy as np
+
+from .ref_harness import RefRing, ref_ctrl, ref_start_positions, ref_rewards
+from . import ref_shim
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+IDM, OVM, LOVM, BCM, CFM, LAC, GIPPS, FS, NLFS, PI = (
+    ref_ctrl.IDMController, ref_ctrl.OVMController, ref_ctrl.LinearOVM,
+    ref_ctrl.BCMController, ref_ctrl.CFMController, ref_ctrl.LACController,
+    ref_ctrl.GippsController, ref_ctrl.FollowerStopper,
+    ref_ctrl.NonLocalFollowerStopper, ref_ctrl.PISaturation)
+
+
+def _inject(ring, headways, speeds=None):
+    """test hook of the reference tests: set_headway / test_set_speed."""
+    ring.headway = list(map(float, headways))
+    if speeds is not None:
+        ring.vel = list(map(float, speeds))
+
+
+def kat():
+    """Known-answer tests: (controller, kwargs, cf kwargs, headways, speeds,
+    expected of the reference test file, line)."""
+    H = [5, 10, 15, 20, 25]
+    SP = [5, 7.5, 7.5, 8, 7]
+    cf = dict(accel=20, decel=5)
+    cases = [
+        ('CFM', CFM, dict(time_delay=0, k_d=1, k_v=1, k_c=1, d_des=1, v_des=8, noise=0), cf, H, None,
+         [12., 17., 22., 27., 32.], 'test_controllers.py:70'),
+        ('BCM', BCM, dict(time_delay=0, k_d=1, k_v=1, k_c=1, d_des=1, v_des=8, noise=0), cf, H, None,
+         [-12., 13., 13., 13., 13.], 'test_controllers.py:119'),
+        ('OVM', OVM, dict(time_delay=0, alpha=1, beta=1, h_st=2, h_go=15, v_max=30, noise=0), cf,
+         [0, 10, 5, 5, 5], None, [0., 20.319073, 3.772339, 3.772339, 3.772339],
+         'test_controllers.py:174'),
+        ('LINEAR_OVM', LOVM, dict(time_delay=0, v_max=30, adaptation=0.65, h_st=5, noise=0), cf,
+         [5, 10, 10, 15, 0], None, [0., 12.992308, 12.992308, 25.984615, 0.],
+         'test_controllers.py:224'),
+        ('IDM', IDM, dict(v0=30, T=1, a=1, b=1.5, delta=4, s0=2, noise=0), cf,
+         [10, 20, 30, 40, 50], None, [0.96, 0.99, 0.995556, 0.9975, 0.9984],
+         'test_controllers.py:271'),
+        ('IDM_zero_headway', IDM, dict(v0=30, T=1, a=1, b=1.5, delta=4, s0=2, noise=0), cf,
+         [0, 0, 0, 0, 0], None, None, 'test_controllers.py:275-285'),
+        ('FOLLOWER_STOPPER', FS, dict(v_des=7.5), cf, H, SP, [0, 0, 0, -5, 5],
+         'test_controllers.py:507'),
+        ('NONLOCAL_FOLLOWER_STOPPER', NLFS, dict(v_des=7.5), cf, H, SP,
+         [-3.33333333333333, -5.0, -5.0, -10.0, 0.0], 'test_controllers.py:579'),
+        ('PI_SATURATION', PI, dict(), cf, H, SP,
+         [20., -36.847826, -35.76087, -37.173913, -31.086957], 'test_controllers.py:654'),
+        ('LAC', LAC, dict(time_delay=0, k_1=0.3, k_2=0.4, h=1, tau=0.1, noise=0), cf,
+         H, None, [0., 1.5, 3., 4.5, 6.], 'test_controllers.py:707'),
+        ('GIPPS', GIPPS, dict(v0=30, acc=1.5, b=-1, b_l=-1, s0=2, tau=1, noise=0), cf,
+         [2, 4, 6, 8, 10], None, [0., 5.929271, 5.929271, 5.929271, 5.929271],
+         'test_controllers.py:763'),
+    ]
+    out = []
+    for name, cls, kw, cfk, hw, sp, expected, cite in cases:
+        ring = RefRing([('test', cls, kw, cfk, 5)], 230, 'accel',
+                       env_additional={'target_velocity': 8, 'max_accel': 3, 'max_decel': 3,
+                                       'sort_vehicles': False})
+        _inject(ring, hw, sp)
+        got = [float(ring.ctrl[i].get_action(ring)) for i in range(5)]
+        if expected is not None:
+            np.testing.assert_array_almost_equal(got, expected)
+        out.append(dict(name=name, controller=name.split('_zero')[0], params=kw, cf=cfk,
+                        headways=hw, speeds=sp, expected=expected, reference_value=got,
+                        cite='tests/fast_tests/' + cite))
+    return out
+
+
+def reward_kat():
+    out = []
+    # test_rewards.py:18-58 (whole-network part)
+    ring = RefRing([('test', IDM, {}, {}, 10)], 230, 'accel',
+                   env_additional={'target_velocity': float(np.sqrt(10)), 'max_accel': 1,
+                                   'max_decel': 1, 'sort_vehicles': False})
+    assert ref_rewards.desired_velocity(ring, fail=True) == 0
+    assert ref_rewards.desired_velocity(ring, fail=False) == 0
+    ring.vel[0] = float(np.sqrt(10))
+    got = float(ref_rewards.desired_velocity(ring, fail=False))
+    np.testing.assert_almost_equal(got, 1 - np.sqrt(90) / 10)
+    out.append(dict(name='desired_velocity', n=10, target=float(np.sqrt(10)),
+                    speeds=list(ring.vel), expected=float(1 - np.sqrt(90) / 10),
+                    reference_value=got, cite='tests/fast_tests/test_rewards.py:18-41'))
+    # test_environments.py:552-613
+    wa = []
+    for vh, vr, act, fail, exp in [(0, 0, [0], False, 0), (0, 1, [0], False, 0.1),
+                                   (1, 1, [0], False, 0.2), (1, 1, [0], True, 0),
+                                   (1, 1, None, False, 0), (1, 1, [1], False, -3.8)]:
+        ring = RefRing([('human', IDM, {}, {}, 1), ('rl', 'rl', {}, {}, 1)], 230, 'wave_po',
+                       env_additional={'max_accel': 1, 'max_decel': 1, 'ring_length': [220, 270]})
+        ring.vel = [float(vh), float(vr)]
+        got = float(ring.compute_reward(act, fail))
+        np.testing.assert_almost_equal(got, exp)
+        wa.append(dict(speeds=[vh, vr], actions=act, fail=fail, expected=exp, reference_value=got))
+    out.append(dict(name='wave_attenuation_reward', cases=wa,
+                    cite='tests/fast_tests/test_environments.py:552-613'))
+    return out
+
+
+def trajectory(ring, n_steps, actions=None, sample_every=1):
+    """Run the reference-driven ring; returns dict of arrays."""
+    P, Vv, A, O, R, Cr = [], [], [], [], [], []
+    P.append(list(ring.pos)); Vv.append(list(ring.vel))
+    for s in range(n_steps):
+        a = None if actions is None or np.isnan(actions[s]).any() else actions[s]
+        obs, rew, crash = ring.step(a)
+        if s % sample_every == 0 or s == n_steps - 1:
+            P.append(list(ring.pos)); Vv.append(list(ring.vel)); A.append(list(ring.accel))
+            O.append(np.asarray(obs, dtype=np.float64))
+        R.append(float(rew)); Cr.append(bool(crash))
+        if crash:
+            break
+    return dict(pos=np.array(P), vel=np.array(Vv), accel=np.array(A), obs=np.array(O),
+                reward=np.array(R), crash=np.array(Cr))
+
+
+def ring_c1():
+    ring = RefRing([('idm', IDM, {}, {}, 22)], 230, 'accel', init_kw=dict(bunching=20),
+                   env_additional={'target_velocity': 10, 'max_accel': 3, 'max_decel': 3,
+                                   'sort_vehicles': False})
+    t = trajectory(ring, 3000)
+    v = t['vel'][1:]
+    np.savez_compressed(
+        os.path.join(HERE, 'ring_c1.npz'),
+        pos=t['pos'][:301], vel=t['vel'][:301], accel=t['accel'][:300], obs=t['obs'][:300],
+        reward=t['reward'], pos_final=t['pos'][-1], vel_final=t['vel'][-1],
+        mean_speed=v[-1000:].mean(), wave_amp=(v[-1000:].max(1) - v[-1000:].min(1)).mean(),
+        sum_reward=t['reward'].sum())
+
+
+def ring_c2():
+    out = {}
+    for tag, length, seed in (('a', 260, 1), ('b', 223, 2)):
+        ring = RefRing([('human', IDM, {}, {'min_gap': 0}, 21), ('rl', 'rl', {}, {}, 1)], length,
+                       'wave_po', init_kw=dict(bunching=50, min_gap=0),
+                       env_additional={'max_accel': 1, 'max_decel': 1, 'ring_length': [220, 270]})
+        rng = np.random.default_rng(seed)
+        n_w, n_a = 750, 600
+        acts = np.full((n_w + n_a, 1), np.nan)
+        acts[n_w:, 0] = rng.uniform(-1.5, 1.5, n_a)   # beyond the [-1,1] box: exercises the clip
+        t = trajectory(ring, n_w + n_a, acts)
+        out.update({'length_' + tag: length, 'actions_' + tag: acts[n_w:, 0],
+                    'pos_' + tag: t['pos'][n_w:], 'vel_' + tag: t['vel'][n_w:],
+                    'obs_' + tag: t['obs'][n_w - 1:], 'reward_' + tag: t['reward'][n_w:],
+                    'pos0_' + tag: t['pos'][0]})
+    np.savez_compressed(os.path.join(HERE, 'ring_c2.npz'), **out)
+
+
+ZOO = [
+    ('ovm', OVM, {}, 'OVM', None),
+    ('ovm_inst', OVM, {'fail_safe': 'instantaneous'}, 'OVM', 'instantaneous'),
+    ('ovm_safe', OVM, {'fail_safe': 'safe_velocity'}, 'OVM', 'safe_velocity'),
+    ('lovm_inst', LOVM, {'fail_safe': 'instantaneous'}, 'LINEAR_OVM', 'instantaneous'),
+    ('bcm', BCM, {}, 'BCM', None),
+    ('cfm_safe', CFM, {'fail_safe': 'safe_velocity'}, 'CFM', 'safe_velocity'),
+    ('lac', LAC, {}, 'LAC', None),
+    ('idm_inst', IDM, {'fail_safe': 'instantaneous'}, 'IDM', 'instantaneous'),
+    ('idm_safe', IDM, {'fail_safe': 'safe_velocity'}, 'IDM', 'safe_velocity'),
+    ('fs', FS, {'v_des': 5.0}, 'FOLLOWER_STOPPER', 'safe_velocity'),
+    ('nlfs', NLFS, {}, 'NONLOCAL_FOLLOWER_STOPPER', 'safe_velocity'),
+    ('pi', PI, {}, 'PI_SATURATION', None),
+]
+
+
+def ring_zoo():
+    """20 IDM + 2 vehicles of the controller under test, 240 m, 300 steps
+    (pos every 10th step, vel/accel/reward every step)."""
+    out = {}
+    for tag, cls, kw, _, _ in ZOO:
+        ring = RefRing([('idm', IDM, {}, {}, 10), ('x', cls, kw, {}, 1), ('idm2', IDM, {}, {}, 10),
+                        ('y', cls, kw, {}, 1)], 240, 'accel', init_kw=dict(bunching=30),
+                       env_additional={'target_velocity': 10, 'max_accel': 3, 'max_decel': 3,
+                                       'sort_vehicles': False})
+        t = trajectory(ring, 300)
+        out['pos_' + tag] = t['pos'][::10]; out['vel_' + tag] = t['vel']
+        out['accel_' + tag] = t['accel']; out['reward_' + tag] = t['reward']
+    np.savez_compressed(os.path.join(HERE, 'ring_zoo.npz'), **out)
+
+
+def start_pos():
+    cases = [dict(length=230, n=22, lanes=1, kw=dict(bunching=20)),
+             dict(length=230, n=22, lanes=1, kw=dict()),
+             dict(length=260, n=22, lanes=1, kw=dict(bunching=50, min_gap=0)),
+             dict(length=221, n=22, lanes=1, kw=dict(bunching=50, min_gap=0)),
+             dict(length=270, n=22, lanes=1, kw=dict(bunching=50, min_gap=0)),
+             dict(length=230, n=5, lanes=1, kw=dict(x0=7.5, min_gap=1.0)),
+             dict(length=230, n=66, lanes=3, kw=dict(lanes_distribution=float('inf'))),
+             dict(length=230, n=21, lanes=3, kw=dict(lanes_distribution=float('inf'))),
+             dict(length=230, n=20, lanes=3, kw=dict(lanes_distribution=2, bunching=10))]
+    out = []
+    for c in cases:
+        x, lane = ref_start_positions(c['length'], c['n'], c['lanes'], **c['kw'])
+        kw = {k: (v if v != float('inf') else 'inf') for k, v in c['kw'].items()}
+        out.append(dict(length=c['length'], n=c['n'], lanes=c['lanes'], kw=kw,
+                        x=[float(v) for v in x], lane=[int(v) for v in lane]))
+    json.dump(out, open(os.path.join(HERE, 'start_pos.json'), 'w'), indent=1)
+
+
+def sumo_fixture():
+    src = os.path.join(ref_shim.REF, 'tests/fast_tests/test_files/ring_230_emission.csv')
+    rows = list(csv.DictReader(open(src)))
+    out = [dict(time=float(r['time']), id=r['id'], edge=r['edge_id'],
+                rel_pos=float(r['relative_position']), speed=float(r['speed'])) for r in rows]
+    json.dump(dict(source='tests/fast_tests/test_files/ring_230_emission.csv (SUMO output)',
+                   rows=out), open(os.path.join(HERE, 'sumo_ring_230.json'), 'w'))
+
+
+def main():
+    json.dump(dict(controllers=kat(), rewards=reward_kat()),
+              open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
+    ring_c1(); ring_c2(); ring_zoo(); start_pos(); sumo_fixture()
+    print('golden vectors written to', HERE)
+
+
+if __name__ == '__main__':
+    main()

@@ -138,7 +138,7 @@ def test_fp32_resync_per_step_and_aggregates():
         chk.step(None)
         eng.step()
         eng.sync()
-        assert close(eng.accel.cpu().numpy()[:, 0], chk.accel, TOL32, floor=1e-2) <= TOL32, step
+        assert close(eng.accel.cpu().numpy()[:, 0], chk.accel, TOL32, floor=0.1) <= TOL32, step
         assert close(eng.vel.cpu().numpy()[:, 0], chk.vel, TOL32, floor=1e-2) <= TOL32, step
         assert close(eng.pos.cpu().numpy()[:, 0], chk.pos, TOL32) <= TOL32, step
     # free-running 3000-step aggregates within 1 %
