@@ -1,0 +1,180 @@
+"""CPU: the oracle restatement against the committed golden vectors
+(tests/golden/*, produced by the reference's own code — make_golden.py) and
+the reference's known-answer tests. Bit-exact / 1e-12 where stated."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import controllers as OC
+from oracle import sim as OS
+from tests import scenarios as S
+
+G = os.path.join(os.path.dirname(__file__), 'golden')
+KAT = json.load(open(os.path.join(G, 'kat.json')))
+
+PARAM_ORDER = dict(
+    CFM=['k_d', 'k_v', 'k_c', 'd_des', 'v_des'], BCM=['k_d', 'k_v', 'k_c', 'd_des', 'v_des'],
+    OVM=['alpha', 'beta', 'h_st', 'h_go', 'v_max'], LINEAR_OVM=['v_max', 'adaptation', 'h_st'],
+    IDM=['v0', 'T', 'a', 'b', 'delta', 's0'], LAC=['k_1', 'k_2', 'h', 'tau'],
+    GIPPS=['v0', 'acc', 'b', 'b_l', 's0', 'tau'], FOLLOWER_STOPPER=['v_des'],
+    NONLOCAL_FOLLOWER_STOPPER=[], PI_SATURATION=[])
+
+
+def kat_groups(case):
+    ctrl = case['controller']
+    p = [case['params'][k] for k in PARAM_ORDER[ctrl]]
+    if ctrl == 'LAC':
+        p.append(0.0)
+    return [S.vt(ctrl, 5, p=p, max_accel=case['cf']['accel'], max_decel=case['cf']['decel'])]
+
+
+def ring_for_headways(headways):
+    """Loop positions whose derived headways equal the injected ones of the
+    reference tests (set_headway): x_{i+1} = x_i + h_i + 5, C = sum(h_i + 5)."""
+    x = [0.0]
+    for h in headways[:-1]:
+        x.append(x[-1] + h + 5.0)
+    return x, float(sum(headways) + 5.0 * len(headways))
+
+
+@pytest.mark.parametrize('case', KAT['controllers'], ids=lambda c: c['name'])
+def test_controller_known_answers(case):
+    """tests/fast_tests/test_controllers.py golden accelerations."""
+    g = kat_groups(case)
+    x, circ = ring_for_headways(case['headways'])
+    o = S.make_oracle(g, 230)
+    if min(case['headways']) <= 0:
+        # headway injection with no consistent geometry (zero headway case)
+        o.headway = [float(h) for h in case['headways']]
+        if case['speeds']:
+            o.vel = [float(v) for v in case['speeds']]
+    else:
+        o.circ = circ
+        o.set_state(x, case['speeds'] or [0.0] * 5)
+        assert np.allclose(o.headway, case['headways'], atol=1e-12)
+    got = [OC.get_action(o, i, o.types[0], o.ctrl_state[i], 0.1, 30.0) for i in range(5)]
+    assert np.allclose(got, case['reference_value'], rtol=1e-12, atol=1e-12)
+    if case['expected'] is not None:
+        np.testing.assert_array_almost_equal(got, case['expected'])
+
+
+def test_reward_known_answers():
+    r = {c['name']: c for c in KAT['rewards']}
+    c = r['desired_velocity']
+    o = S.make_oracle([S.vt('IDM', c['n'])], 230, target_velocity=c['target'])
+    assert o.desired_velocity(fail=True) == 0
+    assert o.desired_velocity() == 0
+    o.vel = list(c['speeds'])
+    assert abs(o.desired_velocity() - c['reference_value']) < 1e-15
+    np.testing.assert_almost_equal(o.desired_velocity(), c['expected'])
+    for case in r['wave_attenuation_reward']['cases']:
+        o = S.make_oracle([S.vt('IDM', 1), S.vt('RL', 1)], 230,
+                          env_kind=OS.ENV_WAVE_ATTENUATION_PO, act_lo=-1, act_hi=1)
+        o.vel = [float(v) for v in case['speeds']]
+        got = o.compute_reward(case['actions'], case['fail'])
+        np.testing.assert_almost_equal(got, case['expected'])
+        assert abs(got - case['reference_value']) < 1e-15
+
+
+def test_start_positions_match_reference():
+    for c in json.load(open(os.path.join(G, 'start_pos.json'))):
+        kw = {k: (float('inf') if v == 'inf' else v) for k, v in c['kw'].items()}
+        x, lane = OS.gen_even_start_pos(c['length'], c['n'], c['lanes'], **kw)
+        assert lane == c['lane']
+        assert np.array_equal(np.array(x), np.array(c['x'])), c
+
+
+def test_not_enough_space_raises():
+    with pytest.raises(ValueError):
+        OS.gen_even_start_pos(100, 22, 1, bunching=20)
+
+
+def test_c1_trajectory_bit_exact():
+    z = np.load(os.path.join(G, 'ring_c1.npz'))
+    o = S.make_oracle(S.c1_groups(), 230, bunching=20.0)
+    assert np.array_equal(np.array(o.pos), z['pos'][0])
+    rew = []
+    for s in range(3000):
+        obs, r, done = o.step(None)
+        rew.append(r)
+        if s < 300:
+            assert np.array_equal(np.array(o.pos), z['pos'][s + 1]), s
+            assert np.array_equal(np.array(o.vel), z['vel'][s + 1]), s
+            assert np.array_equal(np.array(o.accel), z['accel'][s]), s
+            assert np.array_equal(obs, z['obs'][s]), s
+    assert done
+    assert np.array_equal(np.array(rew), z['reward'])
+    assert np.array_equal(np.array(o.pos), z['pos_final'])
+    assert np.array_equal(np.array(o.vel), z['vel_final'])
+
+
+def test_c2_trajectory_bit_exact():
+    z = np.load(os.path.join(G, 'ring_c2.npz'))
+    for tag in 'ab':
+        o = S.make_oracle(S.c2_groups(), float(z['length_' + tag]),
+                          env_kind=OS.ENV_WAVE_ATTENUATION_PO, bunching=50.0, warmup_steps=750,
+                          horizon=3000, act_lo=-1, act_hi=1, obs_max_length=270.0)
+        assert o.time_counter == 750
+        assert np.array_equal(np.array(o.pos), z['pos_' + tag][0])
+        assert np.array_equal(np.array(o.vel), z['vel_' + tag][0])
+        assert np.array_equal(o.get_state(), z['obs_' + tag][0])
+        for s, a in enumerate(z['actions_' + tag]):
+            obs, r, done = o.step([a])
+            assert np.array_equal(np.array(o.pos), z['pos_' + tag][s + 1]), (tag, s)
+            assert np.array_equal(np.array(o.vel), z['vel_' + tag][s + 1]), (tag, s)
+            assert np.array_equal(obs, z['obs_' + tag][s + 1]), (tag, s)
+            assert r == z['reward_' + tag][s], (tag, s)
+
+
+ZOO = [('ovm', 'OVM', None), ('ovm_inst', 'OVM', 'instantaneous'),
+       ('ovm_safe', 'OVM', 'safe_velocity'), ('lovm_inst', 'LINEAR_OVM', 'instantaneous'),
+       ('bcm', 'BCM', None), ('cfm_safe', 'CFM', 'safe_velocity'), ('lac', 'LAC', None),
+       ('idm_inst', 'IDM', 'instantaneous'), ('idm_safe', 'IDM', 'safe_velocity'),
+       ('fs', 'FOLLOWER_STOPPER', None), ('nlfs', 'NONLOCAL_FOLLOWER_STOPPER', None),
+       ('pi', 'PI_SATURATION', None)]
+
+
+def zoo_groups(ctrl, fail_safe):
+    p = [5.0] if ctrl == 'FOLLOWER_STOPPER' else None
+    x = S.vt(ctrl, 1, p=p, fail_safe=fail_safe)
+    return [S.vt('IDM', 10), x, S.vt('IDM', 10), dict(x)]
+
+
+@pytest.mark.parametrize('tag,ctrl,fs', ZOO, ids=[z[0] for z in ZOO])
+def test_zoo_trajectories(tag, ctrl, fs):
+    z = np.load(os.path.join(G, 'ring_zoo.npz'))
+    o = S.make_oracle(zoo_groups(ctrl, fs), 240, bunching=30.0)
+    n = len(z['reward_' + tag])
+    for s in range(n):
+        _, r, _ = o.step(None)
+        # PISaturation: np.mean (pairwise) vs running sum -> last-bit differences
+        tol = 1e-12 if ctrl == 'PI_SATURATION' else 0.0
+        assert np.allclose(o.vel, z['vel_' + tag][s + 1], rtol=tol, atol=tol), (tag, s)
+        assert np.allclose(o.accel, z['accel_' + tag][s], rtol=tol, atol=tol * 10), (tag, s)
+        assert abs(r - z['reward_' + tag][s]) <= tol, (tag, s)
+        if (s + 1) % 10 == 0:
+            assert np.allclose(o.pos, z['pos_' + tag][(s + 1) // 10], rtol=tol, atol=tol)
+
+
+def test_sumo_trajectory_fixture():
+    """The only SUMO-produced numbers the reference holds for this path
+    (tests/fast_tests/test_files/ring_230_emission.csv): speeds to 0.01 and
+    displacement since t=0.1 to 0.01 (+ print rounding) for t <= 0.5."""
+    rows = json.load(open(os.path.join(G, 'sumo_ring_230.json')))['rows']
+    o = S.make_oracle(S.c1_groups(), 230, bunching=20.0)
+    ids = ['idm_%d' % i for i in range(22)]
+    by = {(round(r['time'], 1), r['id']): r for r in rows}
+    x0 = list(o.pos)
+    travelled = [0.0] * 22
+    for step, t in enumerate([0.2, 0.3, 0.4, 0.5]):
+        prev = list(o.pos)
+        o.step(None)
+        for i, vid in enumerate(ids):
+            travelled[i] += (o.pos[i] - prev[i]) % o.circ
+            r, r0 = by[(t, vid)], by[(0.1, vid)]
+            assert abs(o.vel[i] - r['speed']) <= 0.0101, (t, vid)
+            if r['edge'] == r0['edge']:
+                assert abs(travelled[i] - (r['rel_pos'] - r0['rel_pos'])) <= 0.0201, (t, vid)
+    assert x0[0] == 0.0
