@@ -23,6 +23,8 @@ struct fs_engine {
   fs_config cfg;
   bool f64 = false;
   bool types_set = false;
+  bool generic = false;   // some controller is not IDM/SIM/RL
+  int ring_shape = 0;     // FS_RING_SHAPE override: threads per env (1,2,4,8), 0 = auto
   int obs_dim = 0, act_dim = 0, n_rl = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = true;
@@ -124,6 +126,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   e->cfg = *cfg;
   e->f64 = cfg->dtype == FS_F64;
   e->obs_dim = obs_dim_for(*cfg);
+  if (const char* rs = getenv("FS_RING_SHAPE")) e->ring_shape = atoi(rs);
   st = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
   if (st != cudaSuccess) {
     g_create_error = cudaGetErrorString(st);
@@ -197,14 +200,22 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
     d.inv_v0 = (T)(s.p[0] != 0 ? 1.0 / s.p[0] : 0.0); d.sim_inv_v0 = (T)(1.0 / sim_v0);
     d.inv_two_sqrt_ab = (T)(tsab > 0 ? 1.0 / tsab : 0.0);
     d.sim_inv_two_sqrt_ab = (T)(stsab > 0 ? 1.0 / stsab : 0.0);
+    const bool own = s.controller == FS_CTRL_IDM;
+    d.e_v0 = own ? d.p[0] : d.sim_v0; d.e_inv_v0 = own ? d.inv_v0 : d.sim_inv_v0;
+    d.e_T = own ? d.p[1] : d.sim_tau; d.e_a = own ? d.p[2] : d.max_accel;
+    d.e_tsab = own ? d.two_sqrt_ab : d.sim_two_sqrt_ab;
+    d.e_inv_tsab = own ? d.inv_two_sqrt_ab : d.sim_inv_two_sqrt_ab;
+    d.e_delta = own ? d.p[4] : (T)4; d.e_s0 = own ? d.p[5] : d.sim_min_gap;
     if (s.noise > 0) c.any_noise = 1;
     if (s.controller == FS_CTRL_BCM) c.any_follower |= 1;
     if (s.controller == FS_CTRL_NONLOCAL_FOLLOWER_STOPPER) c.any_follower |= 2;
   }
-  int n_rl = 0;
+  int n_rl = 0, n_pi = 0;
   for (int i = 0; i < g.n_veh; ++i) {
     c.type_of[i] = type_of[i];
     c.rl_index[i] = -1;
+    c.pi_index[i] = -1;
+    if (types[type_of[i]].controller == FS_CTRL_PI_SATURATION) c.pi_index[i] = (int16_t)n_pi++;
     if (types[type_of[i]].controller == FS_CTRL_RL) c.rl_index[i] = (int16_t)n_rl++;
   }
   c.n_rl = n_rl;
@@ -227,6 +238,7 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
       return fail(e, FS_EINVAL, "fs_set_types: type_of_vehicle entry out of range");
     const int c = types[type_of_vehicle[i]].controller;
     if (c < 0 || c > FS_CTRL_RL) return fail(e, FS_EINVAL, "fs_set_types: unknown controller");
+    if (c != FS_CTRL_IDM && c != FS_CTRL_SIM && c != FS_CTRL_RL) e->generic = true;
     if (c == FS_CTRL_PI_SATURATION) ++n_pi;
     if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC) ++n_state;
   }
@@ -270,29 +282,17 @@ static const fs::Cfg<T>& cfg_of(fs_engine* e);
 template <> const fs::Cfg<float>& cfg_of<float>(fs_engine* e) { return e->cf; }
 template <> const fs::Cfg<double>& cfg_of<double>(fs_engine* e) { return e->cd; }
 
-static int pick_block(int E) {
-  // one env per thread: spread small batches over all 148 SMs (32-thread
-  // blocks), use fatter blocks once every SM has several warps anyway
-  if (E <= 148 * 32 * 8) return 32;
-  if (E <= 148 * 64 * 16) return 64;
-  return 128;
-}
-
-template <typename T, int VS, bool kViews>
+template <typename T, int VPT, int G, bool kGeneric, bool kNoise>
 static int launch_ring1(fs_engine* e, const fs::StepArgs<T>& a) {
   const int E = e->cfg.n_envs;
-  int block = pick_block(E);
-  size_t smem = 0;
-  auto kern = fs::ring1_step_kernel<T, VS, kViews>;
-  if (VS == 0) {
-    smem = (size_t)3 * e->cfg.n_veh * block * sizeof(T);
-    while (smem > 200 * 1024 && block > 32) { block /= 2; smem /= 2; }
-    if (smem > 48 * 1024)
-      FS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
-  }
-  const int grid = (E + block - 1) / block;
-  kern<<<grid, block, smem, e->stream>>>(cfg_of<T>(e), ring_bufs<T>(e), a);
+  const int epw = 32 / G;
+  const int warps = (E + epw - 1) / epw;
+  // spread small batches over all 148 SMs with one-warp blocks; fatter blocks
+  // once every SM has several warps anyway
+  const int wpb = warps <= 148 * 8 ? 1 : (warps <= 148 * 32 ? 2 : 4);
+  const int grid = (warps + wpb - 1) / wpb;
+  fs::ring1_kernel<T, VPT, G, kGeneric, kNoise>
+      <<<grid, wpb * 32, 0, e->stream>>>(cfg_of<T>(e), ring_bufs<T>(e), a);
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   return FS_OK;
@@ -302,11 +302,27 @@ template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->cfg.topology != FS_TOPO_RING || e->cfg.n_lanes != 1)
     return fail(e, FS_EINVAL, "step: only the single-lane ring path is built in this version");
-  const bool views = e->cfg.record_views != 0;
-  const bool stateful = e->st0 != nullptr;  // LAC / PISaturation use the generic kernel
-  if (e->cfg.n_veh == 22 && !stateful)
-    return views ? launch_ring1<T, 22, true>(e, a) : launch_ring1<T, 22, false>(e, a);
-  return views ? launch_ring1<T, 0, true>(e, a) : launch_ring1<T, 0, false>(e, a);
+  const int V = e->cfg.n_veh, E = e->cfg.n_envs;
+  const fs::Cfg<T>& c = cfg_of<T>(e);
+  if (V == 22 && !e->generic) {
+    // IDM-law fast path; threads per env chosen from the batch size
+    int shape = e->ring_shape;
+    if (shape == 0) shape = E >= 32768 ? 1 : (E >= 8192 ? 2 : 4);
+    const bool nz = c.any_noise != 0;
+    switch (shape) {
+      case 1: return nz ? launch_ring1<T, 22, 1, false, true>(e, a)
+                        : launch_ring1<T, 22, 1, false, false>(e, a);
+      case 2: return nz ? launch_ring1<T, 11, 2, false, true>(e, a)
+                        : launch_ring1<T, 11, 2, false, false>(e, a);
+      case 8: return nz ? launch_ring1<T, 3, 8, false, true>(e, a)
+                        : launch_ring1<T, 3, 8, false, false>(e, a);
+      default: return nz ? launch_ring1<T, 6, 4, false, true>(e, a)
+                         : launch_ring1<T, 6, 4, false, false>(e, a);
+    }
+  }
+  if (V <= 8) return launch_ring1<T, 8, 1, true, true>(e, a);
+  if (V <= 32) return launch_ring1<T, 8, 4, true, true>(e, a);
+  return launch_ring1<T, 8, 32, true, true>(e, a);
 }
 
 template <typename T>
@@ -316,6 +332,7 @@ static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void
   a.actions = (const T*)actions; a.obs_seq = (T*)obs_seq; a.reward_seq = (T*)reward_seq;
   a.done_seq = done_seq; a.mask = mask; a.k_steps = k; a.accumulate_stats = stats;
   a.ignore_done = ignore_done;
+  a.write_views = e->cfg.record_views != 0;
   return run_steps<T>(e, a);
 }
 

@@ -23,6 +23,9 @@ struct TypeP {
   T two_sqrt_ab;      // IDM: 2*sqrt(a*b)
   T sim_two_sqrt_ab;  // simulator-default IDM: 2*sqrt(accel*decel)
   T inv_v0, sim_inv_v0, inv_two_sqrt_ab, sim_inv_two_sqrt_ab;  // f32 fast path
+  // effective IDM block: the law's own parameters for FS_CTRL_IDM, the
+  // simulator-default ones for FS_CTRL_SIM / FS_CTRL_RL (used by the fast kernel)
+  T e_v0, e_inv_v0, e_T, e_a, e_tsab, e_inv_tsab, e_delta, e_s0;
 };
 
 template <typename T>
@@ -41,6 +44,7 @@ struct Cfg {
   TypeP<T> types[FS_MAX_TYPES];
   uint8_t type_of[FS_MAX_VEH];
   int16_t rl_index[FS_MAX_VEH];  // vehicle -> action slot, -1 if not RL
+  int16_t pi_index[FS_MAX_VEH];  // vehicle -> PISaturation history slot, -1 if none
 };
 
 // ---------------------------------------------------------------- helpers
