@@ -49,6 +49,8 @@ def parse():
     ap.add_argument('--workload', default='c2', choices=['c2', 'c5'])
     ap.add_argument('--fuse', type=int, default=100, help='steps per fused launch')
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
+    ap.add_argument('--noise', type=float, default=0.2,
+                    help='IDM accel noise std (0.2 in singleagent_ring.py; 0 = parity setting)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--cpu-envs-per-core', type=int, default=2)
     return ap.parse_args()
@@ -204,7 +206,7 @@ def run_b200(a):
 
     wl = WORKLOADS[a.workload]
     E, K, W, F = wl['n_envs'], a.steps, a.warmup, max(1, min(a.fuse, a.steps))
-    types, tov, kw = wl['builder']()
+    types, tov, kw = wl['builder'](noise=a.noise)
     kw['horizon'] = max(kw['horizon'], K)
     env = B200VecEnv(types, tov, E, dtype=a.dtype, device=local, env_id_base=rank * E,
                      seed=1234, **kw)
@@ -224,16 +226,17 @@ def run_b200(a):
             dist.barrier()
             torch.cuda.synchronize()
 
+    # raw device addresses of step s inside the big buffers (no per-launch torch slicing)
+    pa, po_, pr, pd = act.data_ptr(), obs_seq.data_ptr(), rew_seq.data_ptr(), done_seq.data_ptr()
+    sa, so, sr, sd = E * ts, E * env.obs_dim * ts, E * ts, E
+
     def fused_pass(n_steps):
         for s in range(0, n_steps, F):
-            k = min(F, n_steps - s)
-            eng.step(act[s:s + k], k=k, obs_seq=obs_seq[s:s + k], reward_seq=rew_seq[s:s + k],
-                     done_seq=done_seq[s:s + k])
+            eng.step_ptr(pa + s * sa, min(F, n_steps - s), po_ + s * so, pr + s * sr, pd + s * sd)
 
     def single_pass(n_steps):
         for s in range(n_steps):
-            eng.step(act[s], k=1, obs_seq=obs_seq[s:s + 1], reward_seq=rew_seq[s:s + 1],
-                     done_seq=done_seq[s:s + 1])
+            eng.step_ptr(pa + s * sa, 1, po_ + s * so, pr + s * sr, pd + s * sd)
 
     def host_pass(n_steps):
         for s in range(0, n_steps, F):
@@ -306,7 +309,7 @@ def run_b200(a):
         'data': 'synthetic',
         'env_steps_per_s': fused['env_steps'] / (fused['ms'] * 1e-3),
         'config': {'workload': '%s: %s' % (a.workload, wl['name']), 'envs_per_gpu': E,
-                   'vehicles_per_env': N_VEH, 'fuse': F, 'parallelism': 'envs sharded, %d GPU(s), '
+                   'vehicles_per_env': N_VEH, 'fuse': F, 'idm_noise': a.noise, 'parallelism': 'envs sharded, %d GPU(s), '
                    'no data-path collective' % world,
                    'l2': 'streamed actions/obs/reward/done %.0f MB per pass > 126 MB L2 is %s; '
                          'vehicle state is register-resident inside a fused launch'

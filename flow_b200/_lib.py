@@ -12,8 +12,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
 SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
-SOURCES = ['flowstep.cu']
-HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_reset.cuh']
+SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu']
+HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_reset.cuh', 'fs_launch.h']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -87,7 +87,7 @@ SYMBOLS = [
 ]
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
-              '-std=c++17', '-shared', '-Xcompiler', '-fPIC']
+              '-std=c++17', '-Xcompiler', '-fPIC']
 
 
 def _stale():
@@ -104,13 +104,27 @@ def build(force=False, verbose=False):
     if not force and not _stale():
         return SO_PATH
     nvcc = os.environ.get('NVCC', 'nvcc')
-    cmd = [nvcc] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
-        ['-o', SO_PATH] + [os.path.join(CSRC, s) for s in SOURCES]
+    bdir = os.path.join(_HERE, 'build')
+    os.makedirs(bdir, exist_ok=True)
+    extra = ['-Xptxas', '-v'] if verbose else []
+    procs = []
+    for src in SOURCES:   # one nvcc per translation unit, in parallel
+        obj = os.path.join(bdir, src.replace('.cu', '.o'))
+        cmd = [nvcc] + NVCC_FLAGS + extra + ['-c', '-o', obj, os.path.join(CSRC, src)]
+        procs.append((cmd, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE,
+                                                  stderr=subprocess.PIPE, text=True)))
+    objs = []
+    for cmd, obj, p in procs:
+        out, err = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError('nvcc failed:\n%s\n%s' % (' '.join(cmd), err[-4000:]))
+        if verbose:
+            print(err)
+        objs.append(obj)
+    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', SO_PATH] + objs
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
-        raise RuntimeError('nvcc failed:\n%s\n%s' % (' '.join(cmd), res.stderr[-4000:]))
-    if verbose:
-        print(res.stderr)
+        raise RuntimeError('link failed:\n%s\n%s' % (' '.join(cmd), res.stderr[-4000:]))
     return SO_PATH
 
 

@@ -16,6 +16,7 @@
 #include "fs_common.cuh"
 #include "fs_ring.cuh"
 #include "fs_reset.cuh"
+#include "fs_launch.h"
 
 static thread_local std::string g_create_error;
 
@@ -24,6 +25,8 @@ struct fs_engine {
   bool f64 = false;
   bool types_set = false;
   bool generic = false;   // some controller is not IDM/SIM/RL
+  bool fast_ok = false;   // fs_ring_fast.cuh applies (see fs_set_types)
+  int fast_variant = 0;   // 0 plain, 1 noise, 2 noise+fail-safe, 3 = 2 + views
   int ring_shape = 0;     // FS_RING_SHAPE override: threads per env (1,2,4,8), 0 = auto
   int obs_dim = 0, act_dim = 0, n_rl = 0;
   cudaStream_t stream = nullptr;
@@ -189,7 +192,9 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
     fs::TypeP<T>& d = c.types[t];
     d.ctrl = s.controller; d.fail_safe = s.fail_safe; d.lc = s.lc_controller;
     for (int q = 0; q < FS_NPARAM; ++q) d.p[q] = (T)s.p[q];
-    d.noise = (T)s.noise; d.delay = (T)s.delay; d.max_accel = (T)s.max_accel;
+    const bool sim_driven = s.controller == FS_CTRL_SIM || s.controller == FS_CTRL_RL;
+    d.noise = sim_driven ? (T)0 : (T)s.noise; d.delay = (T)s.delay; d.max_accel = (T)s.max_accel;
+    if (sim_driven) d.fail_safe = FS_FAILSAFE_NONE;  // get_accel -> None: no Flow noise / fail-safe
     d.max_decel = (T)fabs(s.max_decel); d.length = (T)s.length;
     d.sim_tau = (T)s.sim_tau; d.sim_min_gap = (T)s.sim_min_gap;
     const double sim_v0 = fmin(s.sim_max_speed, g.speed_limit);
@@ -206,7 +211,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
     d.e_tsab = own ? d.two_sqrt_ab : d.sim_two_sqrt_ab;
     d.e_inv_tsab = own ? d.inv_two_sqrt_ab : d.sim_inv_two_sqrt_ab;
     d.e_delta = own ? d.p[4] : (T)4; d.e_s0 = own ? d.p[5] : d.sim_min_gap;
-    if (s.noise > 0) c.any_noise = 1;
+    if (s.noise > 0 && !sim_driven) c.any_noise = 1;
     if (s.controller == FS_CTRL_BCM) c.any_follower |= 1;
     if (s.controller == FS_CTRL_NONLOCAL_FOLLOWER_STOPPER) c.any_follower |= 2;
   }
@@ -241,6 +246,30 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     if (c != FS_CTRL_IDM && c != FS_CTRL_SIM && c != FS_CTRL_RL) e->generic = true;
     if (c == FS_CTRL_PI_SATURATION) ++n_pi;
     if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC) ++n_state;
+  }
+  {
+    // hot-kernel preconditions: V = 22, IDM-law vehicles only, ONE human type
+    // and at most one RL type, equal lengths, delta = 4
+    int ta = -1, tb = -1;
+    bool ok = e->cfg.n_veh == 22 && !e->generic && e->cfg.topology == FS_TOPO_RING &&
+              e->cfg.n_lanes == 1;
+    for (int i = 0; ok && i < e->cfg.n_veh; ++i) {
+      const int t = type_of_vehicle[i];
+      const fs_vtype& s = types[t];
+      if (s.controller == FS_CTRL_RL) { if (tb >= 0 && tb != t) ok = false; tb = t; }
+      else { if (ta >= 0 && ta != t) ok = false; ta = t; }
+      if (s.length != types[type_of_vehicle[0]].length) ok = false;
+      if (s.controller == FS_CTRL_IDM && s.p[4] != 4.0) ok = false;
+    }
+    if (ta < 0) ok = false;
+    e->fast_ok = ok;
+    if (ok) {
+      const fs_vtype& s = types[ta];
+      const bool sim = s.controller == FS_CTRL_SIM;
+      e->fast_variant = e->cfg.record_views ? 3
+                        : (!sim && s.fail_safe != FS_FAILSAFE_NONE) ? 2
+                        : (!sim && s.noise > 0) ? 1 : 0;
+    }
   }
   if (e->f64) fill_cfg<double>(e, e->cd, types, n_types, type_of_vehicle);
   else fill_cfg<float>(e, e->cf, types, n_types, type_of_vehicle);
@@ -282,20 +311,29 @@ static const fs::Cfg<T>& cfg_of(fs_engine* e);
 template <> const fs::Cfg<float>& cfg_of<float>(fs_engine* e) { return e->cf; }
 template <> const fs::Cfg<double>& cfg_of<double>(fs_engine* e) { return e->cd; }
 
-template <typename T, int VPT, int G, bool kGeneric, bool kNoise>
+template <typename T, int VPT, int G>
 static int launch_ring1(fs_engine* e, const fs::StepArgs<T>& a) {
   const int E = e->cfg.n_envs;
   const int epw = 32 / G;
   const int warps = (E + epw - 1) / epw;
-  // spread small batches over all 148 SMs with one-warp blocks; fatter blocks
-  // once every SM has several warps anyway
   const int wpb = warps <= 148 * 8 ? 1 : (warps <= 148 * 32 ? 2 : 4);
   const int grid = (warps + wpb - 1) / wpb;
-  fs::ring1_kernel<T, VPT, G, kGeneric, kNoise>
+  fs::ring1_kernel<T, VPT, G, true, true>
       <<<grid, wpb * 32, 0, e->stream>>>(cfg_of<T>(e), ring_bufs<T>(e), a);
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   return FS_OK;
+}
+
+static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
+                               const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
+                               const fs::StepArgs<float>& a) {
+  return fs_launch_fast22_f32(shape, variant, E, st, c, b, a);
+}
+static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
+                               const fs::Cfg<double>& c, const fs::RingBufs<double>& b,
+                               const fs::StepArgs<double>& a) {
+  return fs_launch_fast22_f64(shape, variant, E, st, c, b, a);
 }
 
 template <typename T>
@@ -303,26 +341,19 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->cfg.topology != FS_TOPO_RING || e->cfg.n_lanes != 1)
     return fail(e, FS_EINVAL, "step: only the single-lane ring path is built in this version");
   const int V = e->cfg.n_veh, E = e->cfg.n_envs;
-  const fs::Cfg<T>& c = cfg_of<T>(e);
-  if (V == 22 && !e->generic) {
-    // IDM-law fast path; threads per env chosen from the batch size
+  if (e->fast_ok) {
+    // IDM-law hot kernel; threads per env chosen from the batch size
     int shape = e->ring_shape;
-    if (shape == 0) shape = E >= 32768 ? 1 : (E >= 8192 ? 2 : 4);
-    const bool nz = c.any_noise != 0;
-    switch (shape) {
-      case 1: return nz ? launch_ring1<T, 22, 1, false, true>(e, a)
-                        : launch_ring1<T, 22, 1, false, false>(e, a);
-      case 2: return nz ? launch_ring1<T, 11, 2, false, true>(e, a)
-                        : launch_ring1<T, 11, 2, false, false>(e, a);
-      case 8: return nz ? launch_ring1<T, 3, 8, false, true>(e, a)
-                        : launch_ring1<T, 3, 8, false, false>(e, a);
-      default: return nz ? launch_ring1<T, 6, 4, false, true>(e, a)
-                         : launch_ring1<T, 6, 4, false, false>(e, a);
-    }
+    if (shape != 1 && shape != 2 && shape != 4 && shape != 8)
+      shape = E >= 32768 ? 1 : (E >= 16384 ? 2 : 8);
+    if (sizeof(T) == 8 && shape == 1 && e->ring_shape == 0) shape = 2;  // f64 x 22 slots spills
+    FS_CUDA(e, launch_fast(shape, e->fast_variant, E, e->stream, cfg_of<T>(e), ring_bufs<T>(e), a));
+    e->launches++;
+    return FS_OK;
   }
-  if (V <= 8) return launch_ring1<T, 8, 1, true, true>(e, a);
-  if (V <= 32) return launch_ring1<T, 8, 4, true, true>(e, a);
-  return launch_ring1<T, 8, 32, true, true>(e, a);
+  if (V <= 8) return launch_ring1<T, 8, 1>(e, a);
+  if (V <= 32) return launch_ring1<T, 8, 4>(e, a);
+  return launch_ring1<T, 8, 32>(e, a);
 }
 
 template <typename T>

@@ -1,0 +1,10 @@
+// fs_fast_f32.cu — fp32 instantiations of the IDM-ring hot kernel (own
+// translation unit so the variants compile in parallel with the rest).
+#include "fs_ring_fast.cuh"
+#include "fs_launch.h"
+
+cudaError_t fs_launch_fast22_f32(int shape, int variant, int n_envs, cudaStream_t st,
+                                 const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
+                                 const fs::StepArgs<float>& a) {
+  return fs::launch_fast22<float>(shape, variant, n_envs, st, c, b, a);
+}

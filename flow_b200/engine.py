@@ -168,6 +168,7 @@ class Engine:
         self.obs, self.reward = T(v.obs, (E, self.obs_dim)), T(v.reward, (E,))
         self.done, self.crash = T(v.done, (E,), 'u8'), T(v.crash, (E,), 'u8')
         self.time_counter = T(v.time_counter, (E,), 'i32')
+        self._fs_step = self.lib.fs_step
 
     def _check(self, rc):
         if rc != 0:
@@ -210,6 +211,14 @@ class Engine:
         p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
         self._check(self.lib.fs_step(self.h, a_ptr, k, p(obs_seq), p(reward_seq), p(done_seq)))
         return self.obs, self.reward, self.done
+
+    def step_ptr(self, actions_ptr, k, obs_ptr=0, reward_ptr=0, done_ptr=0):
+        """Same as step() with raw DEVICE addresses (ints; 0 = NULL): the
+        low-overhead path for callers that slice big pre-allocated buffers."""
+        rc = self._fs_step(self.h, actions_ptr or None, k, obs_ptr or None,
+                           reward_ptr or None, done_ptr or None)
+        if rc != 0:
+            self._check(rc)
 
     def step_host(self, actions, k=1, want_obs=True):
         """k fused steps with HOST numpy buffers; returns (obs, reward, done) arrays
