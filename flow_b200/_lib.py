@@ -13,7 +13,8 @@ ROOT = os.path.dirname(_HERE)
 SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
 SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu']
-HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_reset.cuh', 'fs_launch.h']
+HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_reset.cuh', 'fs_launch.h',
+           'fs_multilane.cuh']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -51,7 +52,7 @@ class FsConfig(C.Structure):
                 ('inflow_vehs_per_hour', C.c_double),
                 ('inflow_depart_speed', C.c_double),
                 ('inflow_type', C.c_int32), ('collision_min_gap', C.c_int32),
-                ('record_views', C.c_int32), ('reserved0', C.c_int32)]
+                ('record_views', C.c_int32), ('lc_corrected', C.c_int32)]
 
 
 class FsViews(C.Structure):
@@ -64,7 +65,8 @@ class FsViews(C.Structure):
                 ('time_counter', C.c_void_p),
                 ('n_envs', C.c_int32), ('n_veh', C.c_int32),
                 ('n_lanes', C.c_int32), ('obs_dim', C.c_int32),
-                ('act_dim', C.c_int32), ('dtype', C.c_int32)]
+                ('act_dim', C.c_int32), ('dtype', C.c_int32),
+                ('veh_stride', C.c_int32), ('env_stride', C.c_int32)]
 
 
 # every symbol include/flowstep.h declares: (name, restype, argtypes)

@@ -17,6 +17,7 @@
 #include "fs_ring.cuh"
 #include "fs_reset.cuh"
 #include "fs_launch.h"
+#include "fs_multilane.cuh"
 
 static thread_local std::string g_create_error;
 
@@ -40,6 +41,8 @@ struct fs_engine {
   int hist_len = 0, n_pi = 0;
   uint8_t *lane = nullptr, *active = nullptr, *done = nullptr, *crash = nullptr, *mask = nullptr;
   int *time_counter = nullptr, *episode = nullptr, *leader = nullptr, *follower = nullptr;
+  int* last_lc = nullptr;
+  bool env_major = false;  // pos/vel/lane stored [E][V] (multi-lane, highway)
   void *headway = nullptr, *accel = nullptr, *obs = nullptr, *reward = nullptr;
   double *stats = nullptr, *lengths_dev = nullptr;
   // staging for fs_step_host
@@ -145,6 +148,8 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->time_counter, E * 4); A(&e->episode, E * 4);
   A(&e->obs, E * e->obs_dim * ts); A(&e->reward, E * ts);
   A(&e->stats, 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
+  e->env_major = cfg->n_lanes > 1 || cfg->topology == FS_TOPO_HIGHWAY;
+  if (e->env_major) A(&e->last_lc, V * E * 4);
   if (cfg->record_views) {
     A(&e->headway, V * E * ts); A(&e->accel, V * E * ts);
     A(&e->leader, V * E * 4); A(&e->follower, V * E * 4);
@@ -325,6 +330,29 @@ static int launch_ring1(fs_engine* e, const fs::StepArgs<T>& a) {
   return FS_OK;
 }
 
+template <typename T>
+static int launch_ml(fs_engine* e, const fs::StepArgs<T>& a) {
+  fs::MlBufs<T> b;
+  b.pos = (T*)e->pos; b.vel = (T*)e->vel; b.lane = e->lane; b.circ = (T*)e->circ;
+  b.st0 = (T*)e->st0; b.hist = (T*)e->hist; b.hist_sum = e->hist_sum; b.hist_cnt = e->hist_cnt;
+  b.hist_len = e->hist_len; b.n_pi = e->n_pi; b.last_lc = e->last_lc;
+  b.time_counter = e->time_counter; b.episode = e->episode; b.done = e->done; b.crash = e->crash;
+  b.obs = (T*)e->obs; b.reward = (T*)e->reward;
+  b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
+  b.v_leader = e->leader; b.v_follower = e->follower; b.stats = e->stats;
+  b.lc_bug_compat = e->cfg.lc_corrected ? 0 : 1;
+  const int E = e->cfg.n_envs, V = e->cfg.n_veh;
+  const int wpb = E <= 148 * 8 ? 1 : 4;
+  const int grid = (E + wpb - 1) / wpb;
+  const size_t smem = (size_t)wpb * V * (3 * sizeof(T) + 2 * sizeof(int));
+  if (V <= 32) fs::ring_ml_kernel<T, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  else if (V <= 96) fs::ring_ml_kernel<T, 3><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  else fs::ring_ml_kernel<T, 8><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  e->launches++;
+  FS_CUDA(e, cudaGetLastError());
+  return FS_OK;
+}
+
 static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
                                const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
                                const fs::StepArgs<float>& a) {
@@ -338,9 +366,10 @@ static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
 
 template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
-  if (e->cfg.topology != FS_TOPO_RING || e->cfg.n_lanes != 1)
-    return fail(e, FS_EINVAL, "step: only the single-lane ring path is built in this version");
+  if (e->cfg.topology != FS_TOPO_RING)
+    return fail(e, FS_EINVAL, "step: highway topology is not built in this version");
   const int V = e->cfg.n_veh, E = e->cfg.n_envs;
+  if (e->cfg.n_lanes > 1) return launch_ml<T>(e, a);
   if (e->fast_ok) {
     // IDM-law hot kernel; threads per env chosen from the batch size
     int shape = e->ring_shape;
@@ -385,6 +414,8 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
   b.lane = e->lane; b.done = e->done; b.crash = e->crash;
   b.time_counter = e->time_counter; b.episode = e->episode;
   b.mask = mask_dev; b.lengths = lengths_dev;
+  b.last_lc = e->last_lc;
+  b.vs = e->env_major ? 1 : e->cfg.n_envs; b.es = e->env_major ? e->cfg.n_veh : 1;
   const int E = e->cfg.n_envs, block = 128;
   fs::ring_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(cfg_of<T>(e), b);
   e->launches++;
@@ -493,6 +524,8 @@ extern "C" int fs_buffers(fs_engine* e, fs_views* out) {
   out->done = e->done; out->crash = e->crash; out->time_counter = e->time_counter;
   out->n_envs = e->cfg.n_envs; out->n_veh = e->cfg.n_veh; out->n_lanes = e->cfg.n_lanes;
   out->obs_dim = e->obs_dim; out->act_dim = e->act_dim; out->dtype = e->cfg.dtype;
+  out->veh_stride = e->env_major ? 1 : e->cfg.n_envs;
+  out->env_stride = e->env_major ? e->cfg.n_veh : 1;
   return FS_OK;
 }
 
@@ -502,9 +535,20 @@ extern "C" int fs_set_state(fs_engine* e, const void* pos, const void* vel, cons
   if (!e->types_set) return fail(e, FS_ESTATE, "fs_set_state: call fs_set_types first");
   cudaSetDevice(e->cfg.device);
   const size_t E = e->cfg.n_envs, V = e->cfg.n_veh, ts = tsize(e);
-  if (pos) FS_CUDA(e, cudaMemcpyAsync(e->pos, pos, V * E * ts, cudaMemcpyHostToDevice, e->stream));
-  if (vel) FS_CUDA(e, cudaMemcpyAsync(e->vel, vel, V * E * ts, cudaMemcpyHostToDevice, e->stream));
-  if (lane) FS_CUDA(e, cudaMemcpyAsync(e->lane, lane, V * E, cudaMemcpyHostToDevice, e->stream));
+  // host arrays are [V][E]; env-major engines store [E][V]
+  std::vector<unsigned char> tp, tv, tl;
+  auto transposed = [&](const void* src, size_t es, std::vector<unsigned char>& buf) -> const void* {
+    if (!e->env_major) return src;
+    buf.resize(V * E * es);
+    const unsigned char* s8 = (const unsigned char*)src;
+    for (size_t i = 0; i < V; ++i)
+      for (size_t q = 0; q < E; ++q) memcpy(&buf[(q * V + i) * es], &s8[(i * E + q) * es], es);
+    return buf.data();
+  };
+  if (pos) FS_CUDA(e, cudaMemcpyAsync(e->pos, transposed(pos, ts, tp), V * E * ts, cudaMemcpyHostToDevice, e->stream));
+  if (vel) FS_CUDA(e, cudaMemcpyAsync(e->vel, transposed(vel, ts, tv), V * E * ts, cudaMemcpyHostToDevice, e->stream));
+  if (lane) FS_CUDA(e, cudaMemcpyAsync(e->lane, transposed(lane, 1, tl), V * E, cudaMemcpyHostToDevice, e->stream));
+  if (e->env_major) FS_CUDA(e, cudaStreamSynchronize(e->stream));
   if (lengths) {
     std::vector<double> c64(E);
     std::vector<float> c32(E);

@@ -1,0 +1,343 @@
+// fs_multilane.cuh — multi-lane ring step kernel (config c3: LaneChangeAccelEnv,
+// 3 lanes x 22 columns = 66 vehicles, IDM humans + RL vehicles that change lane).
+//
+// Mapping: ONE WARP OWNS ONE ENVIRONMENT; vehicle i lives in lane (i & 31),
+// register slot (i >> 5). State is env-major here (pos[E][V], vehicle index
+// fastest) so a warp's loads/stores are contiguous. Every step the warp
+// publishes (x, v, lane) of its vehicles to its slice of shared memory and each
+// thread finds, for each of its vehicles, the nearest vehicle ahead IN THE SAME
+// LANE (what SUMO's getLeader returns through
+// flow/core/kernel/vehicle/traci.py:218-250) by scanning that slice with
+// broadcast reads; lane sets are re-derived every step, so lane changes need
+// no list maintenance. Reductions (collision flag, reward norm) are warp
+// shuffles / ballots.
+//
+// Restated from the reference:
+//   LaneChangeAccelEnv._apply_rl_actions   flow/envs/ring/lane_change_accel.py:132-154
+//   apply_lane_change (clip to lanes)      flow/core/kernel/vehicle/traci.py:965-997
+//   get_last_lc returns the headway (bug)  flow/core/kernel/vehicle/traci.py:604-614
+//   LaneChangeAccelEnv.get_state / reward  flow/envs/ring/lane_change_accel.py:100-130
+// Restated SUMO part ("parity unpinned"): a requested change
+// happens in the same simulation step unless the vehicle would overlap its new
+// leader or follower in the target lane; humans (SimLaneChangeController /
+// lane-change mode 512) never change lane.
+#pragma once
+#include "fs_common.cuh"
+#include "fs_ring.cuh"
+
+namespace fs {
+
+template <typename T>
+struct MlBufs {
+  T* pos; T* vel; uint8_t* lane; T* circ;     // [E][V] (vehicle fastest), [E]
+  T* st0;                                     // [V][E] controller state or null
+  T* hist; double* hist_sum; int* hist_cnt; int hist_len, n_pi;
+  int* last_lc;                               // [E][V] step of the last lane change
+  int* time_counter; int* episode;
+  uint8_t* done; uint8_t* crash;
+  T* obs; T* reward;
+  T* v_accel; T* v_headway; int* v_leader; int* v_follower;  // views [E][V] or null
+  double* stats;
+  int lc_bug_compat;
+};
+
+template <typename T, int SLOTS>
+__global__ void __launch_bounds__(128)
+ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const StepArgs<T> A) {
+  typedef Num<T> N;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane_id = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int E = cfg.n_envs, V = cfg.n_veh, L = cfg.n_lanes;
+  const int e = blockIdx.x * (blockDim.x >> 5) + wib;
+  if (e >= E) return;
+  if (A.mask != nullptr && A.mask[e] == 0) return;
+  // per-warp shared slice: xs[V] vs[V] hs[V] (T) | ls[V] ld[V] (int)
+  const size_t per_warp = (size_t)V * (3 * sizeof(T) + 2 * sizeof(int));
+  unsigned char* mine = smem_raw + per_warp * wib;
+  T* xs = reinterpret_cast<T*>(mine);
+  T* vs = xs + V;
+  T* hs = vs + V;
+  int* ls = reinterpret_cast<int*>(hs + V);
+  int* ld = ls + V;
+
+  T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS];
+  int ln[SLOTS], lead[SLOTS], foll[SLOTS];
+  const T C = B.circ[e];
+  const T dt = cfg.dt;
+  const size_t eo = (size_t)e * V;
+#pragma unroll
+  for (int s = 0; s < SLOTS; ++s) {
+    const int i = lane_id + 32 * s;
+    const bool ok = i < V;
+    x[s] = ok ? B.pos[eo + i] : T(0);
+    v[s] = ok ? B.vel[eo + i] : T(0);
+    ln[s] = ok ? (int)B.lane[eo + i] : -1;
+    acc[s] = T(0); foll[s] = -1;
+  }
+
+  auto publish = [&]() {
+    __syncwarp();
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+      const int i = lane_id + 32 * s;
+      if (i < V) { xs[i] = x[s]; vs[i] = v[s]; ls[i] = ln[s]; }
+    }
+    __syncwarp();
+  };
+  // k.update: nearest same-lane vehicle ahead; ties -> lowest index (oracle order)
+  auto update = [&](bool need_followers) {
+    publish();
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+      const int i = lane_id + 32 * s;
+      T best = T(0); int bj = -1;
+      if (i < V) {
+        for (int j = 0; j < V; ++j) {
+          if (j == i || ls[j] != ln[s]) continue;
+          const T d = fwd_dist(xs[j], x[s], C);
+          if (bj < 0 || d < best) { best = d; bj = j; }
+        }
+      }
+      lead[s] = bj;
+      h[s] = (bj >= 0) ? best - cfg.types[cfg.type_of[bj]].length : T(1000);
+    }
+    if (need_followers) {  // vehicle/traci.py:243-250: closest vehicle that calls me leader
+      __syncwarp();
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) {
+        const int i = lane_id + 32 * s;
+        if (i < V) { ld[i] = lead[s]; hs[i] = h[s]; }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) {
+        const int i = lane_id + 32 * s;
+        int f = -1; T fh = T(0);
+        if (i < V)
+          for (int j = 0; j < V; ++j)
+            if (ld[j] == i && (f < 0 || hs[j] < fh)) { f = j; fh = hs[j]; }
+        foll[s] = f;
+      }
+    }
+  };
+  const bool want_foll = (cfg.any_follower & 1) || A.write_views;
+  update(want_foll);
+
+  int tc = B.time_counter[e];
+  const int episode = B.episode[e];
+  bool done = A.ignore_done ? false : (B.done[e] != 0);
+  bool crash = B.crash[e] != 0;
+  const int t_end = cfg.sims_per_step * (cfg.warmup_steps + cfg.horizon);
+  const long long gid = cfg.env_id_base + e;
+  T reward = B.reward[e];
+  const bool have_act = A.actions != nullptr;
+  const bool lc_env = cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL ||
+                      cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
+  int last_lc[SLOTS];
+#pragma unroll
+  for (int s = 0; s < SLOTS; ++s) {
+    const int i = lane_id + 32 * s;
+    last_lc[s] = (i < V) ? B.last_lc[eo + i] : 0;
+  }
+  T max_cost;
+  {
+    T mc2 = T(0);
+    const T t2 = mul(cfg.target_velocity, cfg.target_velocity);
+    for (int i = 0; i < V; ++i) mc2 = add(mc2, t2);
+    max_cost = N::sqrt(mc2);
+  }
+  double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
+
+  auto write_obs = [&](T* o, T* ol) {
+    // LaneChangeAccelEnv.get_state (lane_change_accel.py:114-130) / AccelEnv.get_state
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+      const int i = lane_id + 32 * s;
+      if (i >= V) continue;
+      const T a0 = N::div(v[s], cfg.speed_limit), a1 = N::div(x[s], C);
+      const T a2 = N::div(T(ln[s]), T(L));
+      if (o) { o[i] = a0; o[V + i] = a1; if (lc_env) o[2 * V + i] = a2; }
+      if (ol) { ol[i] = a0; ol[V + i] = a1; if (lc_env) ol[2 * V + i] = a2; }
+    }
+  };
+  if (A.k_steps == 0) write_obs(nullptr, B.obs + (size_t)e * cfg.obs_dim);
+
+  for (int k = 0; k < A.k_steps; ++k) {
+    if (!done) {
+      T mean_v = T(0);
+      if (cfg.any_follower & 2) {
+        T sm = T(0);
+#pragma unroll
+        for (int s = 0; s < SLOTS; ++s) if (lane_id + 32 * s < V) sm = add(sm, v[s]);
+        for (int o = 16; o > 0; o >>= 1) sm += __shfl_xor_sync(0xffffffffu, sm, o);
+        mean_v = N::div(sm, T(V));
+      }
+      int new_ln[SLOTS];
+      T act_abs_sum = T(0);
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) {
+        const int i = lane_id + 32 * s;
+        new_ln[s] = ln[s];
+        if (i >= V) continue;
+        const TypeP<T>& tp = cfg.types[cfg.type_of[i]];
+        const int ctrl = tp.ctrl;
+        const bool has_lead = lead[s] >= 0;
+        const T vi = v[s], hi = h[s];
+        const T vl = has_lead ? vs[lead[s]] : T(-1001);
+        T a;
+        if (ctrl == FS_CTRL_RL && have_act) {
+          const int slot = cfg.rl_index[i];
+          const size_t arow = (size_t)k * cfg.act_dim + (lc_env ? 2 * slot : slot);
+          const T raw = A.actions[arow * E + e];
+          a = N::min(N::max(raw, cfg.act_lo), cfg.act_hi);
+          act_abs_sum = add(act_abs_sum, N::abs(cfg.clip_actions ? a : raw));
+          if (lc_env) {
+            // _apply_rl_actions: direction zeroed while time_counter <=
+            // lane_change_duration + get_last_lc (== headway under the reference bug)
+            T dirf = N::min(N::max(A.actions[(arow + 1) * E + e], T(-1)), T(1));
+            const T last = B.lc_bug_compat ? hi : T(last_lc[s]);
+            if (T(tc + 1) <= add(T(cfg.lane_change_duration), last)) dirf = T(0);
+            const int dir = dirf > T(0.5) ? 1 : (dirf < T(-0.5) ? -1 : 0);
+            int target = ln[s] + dir;
+            target = target < 0 ? 0 : (target > L - 1 ? L - 1 : target);
+            if (target != ln[s]) {
+              bool ok = true;  // restated execution: no overlap in the target lane
+              for (int j = 0; j < V; ++j) {
+                if (j == i || ls[j] != target) continue;
+                const T fwd = fwd_dist(xs[j], x[s], C), back = fwd_dist(x[s], xs[j], C);
+                if (fwd - cfg.types[cfg.type_of[j]].length < T(0) || back - tp.length < T(0))
+                  ok = false;
+              }
+              if (ok) { new_ln[s] = target; last_lc[s] = tc + 1; }
+            }
+          }
+        } else if (ctrl == FS_CTRL_PI_SATURATION) {
+          T v_cmd = B.st0[(size_t)i * E + e];
+          RingBufs<T> rb;
+          rb.hist = B.hist; rb.hist_sum = B.hist_sum; rb.hist_cnt = B.hist_cnt;
+          rb.hist_len = B.hist_len; rb.n_pi = B.n_pi;
+          a = pi_saturation<T>(rb, cfg.pi_index[i], E, e, tc, vi, vl, hi, dt, tp.max_accel, v_cmd);
+          B.st0[(size_t)i * E + e] = v_cmd;
+        } else {
+          T st0 = T(0);
+          const bool stateful = (ctrl == FS_CTRL_LAC);
+          if (stateful) st0 = B.st0[(size_t)i * E + e];
+          const bool has_f = foll[s] >= 0;
+          a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, has_f, has_f ? vs[foll[s]] : T(-1001),
+                            has_f ? hs[foll[s]] : T(-1001), mean_v, dt, cfg.inv_dt, st0);
+          if (stateful) B.st0[(size_t)i * E + e] = st0;
+        }
+        if (ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL) {
+          if (tp.noise > T(0))
+            a = add(a, mul(tp.noise, normal_sample<T>(cfg.seed, gid, i, tc + episode * 1000003)));
+          if (tp.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
+            a = failsafe_instantaneous<T>(a, vi, hi, has_lead, V, dt);
+          else if (tp.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
+            a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, tp.delay);
+        }
+        acc[s] = a;
+      }
+      // all reads of the published pre-move state are done; move
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) {
+        if (lane_id + 32 * s >= V) continue;
+        const T vn = N::max(add(v[s], mul(acc[s], dt)), T(0));
+        x[s] = wrap_fwd(add(x[s], mul(vn, dt)), C);
+        v[s] = vn;
+        ln[s] = new_ln[s];
+      }
+      update(want_foll);
+      bool cr = false;
+      T sv = T(0), sq = T(0), s2 = T(0);
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) {
+        const int i = lane_id + 32 * s;
+        if (i >= V) continue;
+        if (cfg.collision_min_gap)
+          cr |= lead[s] >= 0 && h[s] < cfg.types[cfg.type_of[lead[s]]].sim_min_gap;
+        else
+          cr |= h[s] < T(0);
+        sv = add(sv, v[s]);
+        const T d = v[s] - cfg.target_velocity;
+        sq = add(sq, mul(d, d));
+        s2 += v[s] * v[s];
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        sv += __shfl_xor_sync(0xffffffffu, sv, o);
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        act_abs_sum += __shfl_xor_sync(0xffffffffu, act_abs_sum, o);
+      }
+      crash = __any_sync(0xffffffffu, cr);
+      tc += 1;
+      done = crash || tc >= t_end;
+      if (cfg.env_kind == FS_ENV_WAVE_ATTENUATION || cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO) {
+        if (!have_act || crash) reward = T(0);
+        else {
+          reward = N::div(mul(T(4), N::div(sv, T(V))), T(20));
+          const T mean_act = N::div(act_abs_sum, T(cfg.n_rl > 0 ? cfg.n_rl : 1));
+          if (mean_act > T(0)) reward = add(reward, mul(T(4), T(0) - mean_act));
+        }
+      } else {
+        // rewards.desired_velocity (+ LaneChangeAccelEnv lane-change penalty)
+        if (crash) reward = T(0);
+        else {
+          const T cost = N::sqrt(sq);
+          const T eps = T(1.1920928955078125e-07);
+          reward = N::div(N::max(max_cost - cost, T(0)), add(max_cost, eps));
+        }
+        if (lc_env) {
+          int pen = 0;
+#pragma unroll
+          for (int s = 0; s < SLOTS; ++s) {
+            const int i = lane_id + 32 * s;
+            if (i < V && cfg.rl_index[i] >= 0) {
+              const T last = B.lc_bug_compat ? h[s] : T(last_lc[s]);
+              pen += (last == T(tc)) ? 1 : 0;
+            }
+          }
+          for (int o = 16; o > 0; o >>= 1) pen += __shfl_xor_sync(0xffffffffu, pen, o);
+          for (int q = 0; q < pen; ++q) reward = reward - T(0.1);
+        }
+      }
+      if (A.accumulate_stats && lane_id == 0) {
+        st_rew += (double)reward; st_v += (double)sv; st_v2 += (double)s2;
+        st_vs += V; st_es += 1; st_cr += crash ? 1 : 0;
+      }
+    } else {
+      reward = T(0);
+    }
+    const bool last = (k == A.k_steps - 1);
+    if (A.obs_seq != nullptr || last)
+      write_obs(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
+                last ? B.obs + (size_t)e * cfg.obs_dim : nullptr);
+    if (lane_id == 0) {
+      if (A.reward_seq) A.reward_seq[(size_t)k * E + e] = reward;
+      if (A.done_seq) A.done_seq[(size_t)k * E + e] = done ? 1 : 0;
+    }
+  }
+
+#pragma unroll
+  for (int s = 0; s < SLOTS; ++s) {
+    const int i = lane_id + 32 * s;
+    if (i >= V) continue;
+    B.pos[eo + i] = x[s]; B.vel[eo + i] = v[s]; B.lane[eo + i] = (uint8_t)ln[s];
+    B.last_lc[eo + i] = last_lc[s];
+    if (A.write_views) {
+      B.v_headway[eo + i] = h[s]; B.v_leader[eo + i] = lead[s]; B.v_follower[eo + i] = foll[s];
+      if (A.k_steps > 0) B.v_accel[eo + i] = acc[s];
+    }
+  }
+  if (lane_id == 0) {
+    B.time_counter[e] = tc;
+    B.done[e] = done ? 1 : 0;
+    B.crash[e] = crash ? 1 : 0;
+    B.reward[e] = reward;
+    if (A.accumulate_stats) {
+      const double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
+      for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&B.stats[q], vals[q]);
+    }
+  }
+}
+
+}  // namespace fs

@@ -20,6 +20,8 @@ struct ResetBufs {
   double* hist_sum; int* hist_cnt; int n_pi;
   uint8_t* lane; uint8_t* done; uint8_t* crash;
   int* time_counter; int* episode;
+  int* last_lc;             // [E][V] or null (multi-lane)
+  int vs, es;               // element strides of pos/vel/lane: vehicle, env
   const uint8_t* mask;      // [E] or null
   const double* lengths;    // [E] or null ; <= 0 means "draw"
 };
@@ -82,9 +84,11 @@ __global__ void ring_reset_kernel(const __grid_constant__ Cfg<T> cfg, const Rese
       x = starts[idx];
     }
     for (int lane = 0; lane < per_col && count < V; ++lane) {
-      B.pos[(size_t)count * E + e] = (T)x;
-      B.vel[(size_t)count * E + e] = T(0);
-      B.lane[(size_t)count * E + e] = (uint8_t)lane;
+      const size_t so = (size_t)count * B.vs + (size_t)e * B.es;
+      B.pos[so] = (T)x;
+      B.vel[so] = T(0);
+      B.lane[so] = (uint8_t)lane;
+      if (B.last_lc) B.last_lc[so] = -(1 << 30);  // -inf: vehicle/traci.py:178-180
       if (B.st0) {
         const TypeP<T>& tp = cfg.types[cfg.type_of[count]];
         B.st0[(size_t)count * E + e] = (tp.ctrl == FS_CTRL_LAC) ? tp.p[4] : T(0);

@@ -129,7 +129,7 @@ class Engine:
                         lane_change_duration=5, target_velocity=10.0, act_lo=-4.5,
                         act_hi=2.6, obs_max_length=0.0, inflow_vehs_per_hour=0.0,
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
-                        record_views=0)
+                        record_views=0, lc_corrected=0)
         unknown = set(cfg) - set(defaults)
         if unknown:
             raise TypeError('unknown engine config keys: %s' % sorted(unknown))
@@ -160,10 +160,19 @@ class Engine:
         self.obs_dim, self.act_dim = v.obs_dim, v.act_dim
         E, V, dt = n_envs, c.n_veh, self.dtype
         T = lambda p, shape, d=dt: _as_tensor(p, shape, d, device)  # noqa: E731
-        self.pos, self.vel = T(v.pos, (V, E)), T(v.vel, (V, E))
-        self.lane, self.active = T(v.lane, (V, E), 'u8'), T(v.active, (V, E), 'u8')
-        self.headway, self.accel = T(v.headway, (V, E)), T(v.accel, (V, E))
-        self.leader, self.follower = T(v.leader, (V, E), 'i32'), T(v.follower, (V, E), 'i32')
+
+        def VE(p, d=dt):
+            """logical [V, E] view whatever the engine's memory order is"""
+            if not p:
+                return None
+            if v.env_stride == 1:
+                return T(p, (V, E), d)
+            return T(p, (E, V), d).t()
+        self.env_major = v.env_stride != 1
+        self.pos, self.vel = VE(v.pos), VE(v.vel)
+        self.lane, self.active = VE(v.lane, 'u8'), VE(v.active, 'u8')
+        self.headway, self.accel = VE(v.headway), VE(v.accel)
+        self.leader, self.follower = VE(v.leader, 'i32'), VE(v.follower, 'i32')
         self.length = T(v.length, (E,))
         self.obs, self.reward = T(v.obs, (E, self.obs_dim)), T(v.reward, (E,))
         self.done, self.crash = T(v.done, (E,), 'u8'), T(v.crash, (E,), 'u8')

@@ -142,7 +142,8 @@ typedef struct fs_config {
   int32_t inflow_type;   /* vehicle type index of inflow vehicles               */
   int32_t collision_min_gap; /* 0: crash iff gap<0 ; 1: crash iff gap<minGap    */
   int32_t record_views;  /* 1: keep views.accel/headway/leader/follower current  */
-  int32_t reserved0;
+  int32_t lc_corrected;  /* 0: get_last_lc returns the headway like the reference
+                            (vehicle/traci.py:614); 1: the step of the last change */
 } fs_config;
 
 /* device views; T = float or double per cfg.dtype; [a][b] = a slow, b fast */
@@ -162,6 +163,10 @@ typedef struct fs_views {
   uint8_t* crash;    /* u8 [E]                                                  */
   int32_t* time_counter; /* i32 [E]                                             */
   int32_t n_envs, n_veh, n_lanes, obs_dim, act_dim, dtype;
+  /* element (vehicle i, env e) of pos/vel/lane/headway/leader/follower/accel is at
+   * i*veh_stride + e*env_stride: single-lane rings are [V][E] (E, 1), multi-lane
+   * rings and highways are [E][V] (1, V) */
+  int32_t veh_stride, env_stride;
 } fs_views;
 
 int fs_abi_version(void);

@@ -130,6 +130,7 @@ class RingSim:
         self.obs_max_length = obs_max_length
         self.lane_change_duration = lane_change_duration
         self.noise_fn = noise_fn  # (step, vehicle) -> N(0,1) sample
+        self.lc_bug_compat = True  # get_last_lc returns the headway (vehicle/traci.py:614)
         self.rl_idx = [i for i, t in enumerate(self.type_of)
                        if types[t].controller == C.RL]
         self.reset(length)
@@ -147,6 +148,7 @@ class RingSim:
         self.lane = list(lanes)
         self.accel = [0.0] * V
         self.ctrl_state = [dict() for _ in range(V)]
+        self.last_lc = [-float('inf')] * V   # vehicle/traci.py:178-180
         self.time_counter = 0
         self.step_index = 0
         self.crash = False
@@ -220,9 +222,27 @@ class RingSim:
         self.time_counter += 1
         next_vel = [0.0] * V
         clipped = None
+        lc_env = self.env_kind in (ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO)
+        directions = None
         if rl_actions is not None:
-            clipped = [min(max(float(a), self.act_lo), self.act_hi)
-                       for a in rl_actions]
+            if lc_env:
+                # LaneChangeAccelEnv._apply_rl_actions (lane_change_accel.py:132-154):
+                # interleaved [acc, dir] per RL vehicle; Box clip first (base.py:614)
+                acc_part = [min(max(float(a), self.act_lo), self.act_hi)
+                            for a in rl_actions[0::2]]
+                directions = [min(max(float(d), -1.0), 1.0) for d in rl_actions[1::2]]
+                clipped = acc_part
+                for q, i in enumerate(self.rl_idx):
+                    last = self.headway[i] if self.lc_bug_compat else self.last_lc[i]
+                    if self.time_counter <= self.lane_change_duration + last:
+                        directions[q] = 0.0
+                if any(d not in (-1.0, 0.0, 1.0) for d in directions):
+                    # vehicle/traci.py:973-975
+                    raise ValueError("Direction values for lane changes may only "
+                                     "be: -1, 0, or 1.")
+            else:
+                clipped = [min(max(float(a), self.act_lo), self.act_hi)
+                           for a in rl_actions]
         for i in range(V):
             vt = self.types[self.type_of[i]]
             if vt.controller == C.RL and clipped is not None:
@@ -235,6 +255,31 @@ class RingSim:
             self.accel[i] = a
             # apply_acceleration, vehicle/traci.py:961-962
             next_vel[i] = max(self.vel[i] + a * dt, 0.0)
+        # apply_lane_change (vehicle/traci.py:965-997) + restated execution: the
+        # change happens in this simulation step unless the vehicle would overlap
+        # its new leader or new follower in the target lane (pre-move positions)
+        if directions is not None:
+            new_lane = list(self.lane)
+            for q, i in enumerate(self.rl_idx):
+                d = int(directions[q])
+                if d == 0:
+                    continue
+                target = min(max(self.lane[i] + d, 0), self.n_lanes - 1)
+                if target == self.lane[i]:
+                    continue
+                ok = True
+                for j in range(V):
+                    if j == i or self.lane[j] != target:
+                        continue
+                    fwd = (self.pos[j] - self.pos[i]) % self.circ
+                    back = (self.pos[i] - self.pos[j]) % self.circ
+                    if fwd - self.types[self.type_of[j]].length < 0 or \
+                            back - self.types[self.type_of[i]].length < 0:
+                        ok = False
+                if ok:
+                    new_lane[i] = target
+                    self.last_lc[i] = self.time_counter
+            self.lane = new_lane
         # simulator move (restated SUMO Euler step)
         for i in range(V):
             self.vel[i] = next_vel[i]
@@ -268,6 +313,11 @@ class RingSim:
                 self.vel[rl] / 15.,
                 (self.vel[lead] - self.vel[rl]) / 15.,
                 (self.pos[lead] - self.pos[rl]) % self.circ / max_length])
+        if k == ENV_LANE_CHANGE_ACCEL:
+            # lane_change_accel.py:114-130
+            return np.array([v / self.speed_limit for v in self.vel] +
+                            [x / self.circ for x in self.pos] +
+                            [ln / self.n_lanes for ln in self.lane])
         raise NotImplementedError(k)
 
     def desired_velocity(self, fail=False):
@@ -285,6 +335,15 @@ class RingSim:
         k = self.env_kind
         if k == ENV_ACCEL:
             return self.desired_velocity(fail)
+        if k == ENV_LANE_CHANGE_ACCEL:
+            # lane_change_accel.py:100-112 (penalty compares get_last_lc, i.e.
+            # the headway under the reference's bug, with the time counter)
+            reward = self.desired_velocity(fail)
+            for i in self.rl_idx:
+                last = self.headway[i] if self.lc_bug_compat else self.last_lc[i]
+                if last == self.time_counter:
+                    reward -= 0.1
+            return reward
         if k in (ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO):
             # wave_attenuation.py:113-139
             if rl_actions is None:

@@ -21,7 +21,7 @@ import os
 
 import numpy as np
 
-from .ref_harness import RefRing, ref_ctrl, ref_start_positions, ref_rewards
+from .ref_harness import RefRing, RefRingLC, ref_ctrl, ref_start_positions, ref_rewards
 from . import ref_shim
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -198,6 +198,30 @@ def ring_zoo():
     np.savez_compressed(os.path.join(HERE, 'ring_zoo.npz'), **out)
 
 
+def ring_c3():
+    """3-lane 230 m ring, 63 IDM + 3 RL (one per lane), LaneChangeAccelEnv:
+    reference get_state / compute_reward / _apply_rl_actions / apply_lane_change."""
+    ring = RefRingLC([('human', IDM, {}, {}, 63), ('rl', 'rl', {}, {}, 3)], 230, lanes=3,
+                     init_kw=dict(lanes_distribution=float('inf')),
+                     env_additional={'max_accel': 3, 'max_decel': 3, 'target_velocity': 10})
+    rng = np.random.default_rng(11)
+    P, Vv, Ln, O, R, A = [list(ring.pos)], [list(ring.vel)], [list(ring.lane)], [], [], []
+    for s in range(260):
+        a = []
+        for q in range(3):
+            a += [float(rng.uniform(-0.8, 0.8)), float(rng.integers(-1, 2))]
+        act = None if s < 20 else a
+        obs, rew, crash = ring.step(act)
+        A.append([np.nan] * 6 if act is None else a)
+        P.append(list(ring.pos)); Vv.append(list(ring.vel)); Ln.append(list(ring.lane))
+        O.append(np.asarray(obs)); R.append(float(rew))
+        if crash:
+            break
+    np.savez_compressed(os.path.join(HERE, 'ring_c3.npz'), pos=np.array(P), vel=np.array(Vv),
+                        lane=np.array(Ln, dtype=np.int8), obs=np.array(O), reward=np.array(R),
+                        actions=np.array(A), crashed=bool(crash))
+
+
 def start_pos():
     cases = [dict(length=230, n=22, lanes=1, kw=dict(bunching=20)),
              dict(length=230, n=22, lanes=1, kw=dict()),
@@ -229,7 +253,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_zoo(); start_pos(); sumo_fixture()
+    ring_c1(); ring_c2(); ring_c3(); ring_zoo(); start_pos(); sumo_fixture()
     print('golden vectors written to', HERE)
 
 

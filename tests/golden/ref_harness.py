@@ -274,3 +274,111 @@ class RefRing:
         if self.env_kind in ('wave', 'wave_po'):
             return WaveAttenuationEnv.compute_reward(self, rl_actions, fail=fail)
         return AccelEnv.compute_reward(self, rl_actions, fail=fail)
+
+
+class RefRingLC(RefRing):
+    """Multi-lane ring driven by the reference's LaneChangeAccelEnv code:
+    get_state, compute_reward, _apply_rl_actions, TraCIVehicle.apply_lane_change
+    and TraCIVehicle.get_last_lc (with its headway bug) run unmodified; only the
+    execution of a requested change and the move are the oracle restatement."""
+
+    def __init__(self, *a, lane_change_duration=5, **kw):
+        from flow.envs.ring.lane_change_accel import LaneChangeAccelEnv
+        self.LC = LaneChangeAccelEnv
+        kw.setdefault('env_kind', 'lc')
+        self.requests = {}
+        super().__init__(*a, **kw)
+        self.env_params.additional_params.setdefault('lane_change_duration',
+                                                     lane_change_duration)
+        self.env_params.additional_params.setdefault('sort_vehicles', False)
+        veh = self.k.vehicle
+        h = self
+
+        class _TV:  # what TraCIVehicle methods touch
+            sim_step = self.dt
+            kernel_api = type('A', (), {})()
+            master_kernel = type('M', (), {})()
+            prev_last_lc = {}
+
+            def get_ids(s):
+                return h.ids
+
+            def get_rl_ids(s):
+                return veh.get_rl_ids()
+
+            def get_speed(s, vid):
+                return veh.get_speed(vid)
+
+            def get_lane(s, vid):
+                return veh.get_lane(vid)
+
+            def get_edge(s, vid):
+                return 'ring'
+
+            def get_headway(s, vid, error=-1001):
+                return veh.get_headway(vid, error)
+
+        tv = _TV()
+        tv.kernel_api.vehicle = type('KV', (), {})()
+        tv.kernel_api.vehicle.slowDown = self.sink.slowDown
+        tv.kernel_api.vehicle.changeLane = \
+            lambda vid, lane, dur: self.requests.__setitem__(vid, lane)
+        tv.master_kernel.network = self.net
+        self.tv = tv
+        veh.apply_acceleration = lambda ids, acc: TraCIVehicle.apply_acceleration(tv, ids, acc)
+        veh.apply_lane_change = lambda ids, direction: TraCIVehicle.apply_lane_change(
+            tv, ids, direction)
+        veh.get_last_lc = lambda vid, error=-1001: TraCIVehicle.get_last_lc(tv, vid, error)
+        self.sorted_ids = self.ids
+
+    def _sync_tv(self):
+        self.tv._TraCIVehicle__rl_ids = self.k.vehicle.get_rl_ids()
+        self.tv._TraCIVehicle__vehicles = {
+            vid: {'headway': self.headway[i], 'last_lc': -float('inf')}
+            for i, vid in enumerate(self.ids)}
+
+    def step(self, rl_actions):
+        n = len(self.ids)
+        self.time_counter += 1
+        self._sync_tv()
+        acc = [None] * n
+        for i in range(n):
+            if self.ctrl[i] is not None:
+                acc[i] = self.ctrl[i].get_action(self)
+        self.sink.cmd = {}
+        self.requests = {}
+        TraCIVehicle.apply_acceleration(self.tv, self.ids, acc)   # humans (base.py:335)
+        if rl_actions is not None:
+            lo = [-abs(self.env_params.additional_params['max_decel']), -1] * len(self.rl_idx)
+            hi = [self.env_params.additional_params['max_accel'], 1] * len(self.rl_idx)
+            clipped = np.clip(np.array(rl_actions, dtype=float), lo, hi)
+            self.LC._apply_rl_actions(self, clipped)
+        else:
+            for i in self.rl_idx:
+                a = self.sim_ctrl[i].get_accel(self)
+                self.sink.cmd[self.ids[i]] = max(self.vel[i] + a * self.dt, 0)
+                acc[i] = a
+        # restated SUMO: execute requested changes (no overlap rule), then move
+        new_lane = list(self.lane)
+        for vid, target in self.requests.items():
+            i = self.index[vid]
+            ok = True
+            for j in range(n):
+                if j == i or self.lane[j] != target:
+                    continue
+                fwd = (self.pos[j] - self.pos[i]) % self.net.circ
+                back = (self.pos[i] - self.pos[j]) % self.net.circ
+                if fwd - 5.0 < 0 or back - 5.0 < 0:
+                    ok = False
+            if ok:
+                new_lane[i] = target
+        self.lane = new_lane
+        for i, vid in enumerate(self.ids):
+            self.vel[i] = self.sink.cmd[vid]
+            self.pos[i] = (self.pos[i] + self.vel[i] * self.dt) % self.net.circ
+        self._update()
+        self._sync_tv()
+        crash = any(h < 0 for h in self.headway)
+        obs = self.LC.get_state(self)
+        reward = self.LC.compute_reward(self, rl_actions, fail=crash)
+        return obs, reward, crash

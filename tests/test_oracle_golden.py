@@ -178,3 +178,32 @@ def test_sumo_trajectory_fixture():
             if r['edge'] == r0['edge']:
                 assert abs(travelled[i] - (r['rel_pos'] - r0['rel_pos'])) <= 0.0201, (t, vid)
     assert x0[0] == 0.0
+
+
+def c3_groups():
+    return [S.vt('IDM', 63), S.vt('RL', 3)]
+
+
+def test_c3_lane_change_trajectory_bit_exact():
+    """LaneChangeAccelEnv on the 3-lane ring: reference env code (get_state,
+    compute_reward, _apply_rl_actions, apply_lane_change, get_last_lc bug)."""
+    z = np.load(os.path.join(G, 'ring_c3.npz'))
+    o = S.make_oracle(c3_groups(), 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL, n_lanes=3,
+                      act_lo=-3, act_hi=3)
+    assert np.array_equal(np.array(o.pos), z['pos'][0]) and o.lane == list(z['lane'][0])
+    for s, a in enumerate(z['actions']):
+        obs, r, done = o.step(None if np.isnan(a).any() else list(a))
+        assert np.array_equal(np.array(o.pos), z['pos'][s + 1]), s
+        assert np.array_equal(np.array(o.vel), z['vel'][s + 1]), s
+        assert o.lane == list(z['lane'][s + 1]), s
+        assert np.array_equal(obs, z['obs'][s]) and r == z['reward'][s], s
+    assert done == bool(z['crashed'])
+
+
+def test_lane_change_direction_validation():
+    o = S.make_oracle(c3_groups(), 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL, n_lanes=3,
+                      act_lo=-3, act_hi=3)
+    for _ in range(40):
+        o.step(None)
+    with pytest.raises(ValueError):   # vehicle/traci.py:973-975
+        o.step([0, 0.5, 0, 0, 0, 0])
