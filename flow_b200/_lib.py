@@ -14,7 +14,7 @@ SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
 SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu']
 HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_reset.cuh', 'fs_launch.h',
-           'fs_multilane.cuh']
+           'fs_multilane.cuh', 'fs_highway.cuh']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -52,7 +52,9 @@ class FsConfig(C.Structure):
                 ('inflow_vehs_per_hour', C.c_double),
                 ('inflow_depart_speed', C.c_double),
                 ('inflow_type', C.c_int32), ('collision_min_gap', C.c_int32),
-                ('record_views', C.c_int32), ('lc_corrected', C.c_int32)]
+                ('record_views', C.c_int32), ('lc_corrected', C.c_int32),
+                ('n_initial', C.c_int32), ('reserved1', C.c_int32),
+                ('inflow_begin', C.c_double)]
 
 
 class FsViews(C.Structure):
@@ -62,7 +64,7 @@ class FsViews(C.Structure):
                 ('accel', C.c_void_p), ('length', C.c_void_p),
                 ('obs', C.c_void_p), ('reward', C.c_void_p),
                 ('done', C.c_void_p), ('crash', C.c_void_p),
-                ('time_counter', C.c_void_p),
+                ('time_counter', C.c_void_p), ('counters', C.c_void_p),
                 ('n_envs', C.c_int32), ('n_veh', C.c_int32),
                 ('n_lanes', C.c_int32), ('obs_dim', C.c_int32),
                 ('act_dim', C.c_int32), ('dtype', C.c_int32),

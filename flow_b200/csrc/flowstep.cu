@@ -18,6 +18,7 @@
 #include "fs_reset.cuh"
 #include "fs_launch.h"
 #include "fs_multilane.cuh"
+#include "fs_highway.cuh"
 
 static thread_local std::string g_create_error;
 
@@ -42,6 +43,8 @@ struct fs_engine {
   uint8_t *lane = nullptr, *active = nullptr, *done = nullptr, *crash = nullptr, *mask = nullptr;
   int *time_counter = nullptr, *episode = nullptr, *leader = nullptr, *follower = nullptr;
   int* last_lc = nullptr;
+  int* counters = nullptr;   // highway: [4][E] in network, departed, arrived, spawned
+  uint8_t* vtype = nullptr;  // highway: [E][CAP] type of the vehicle in each slot
   bool env_major = false;  // pos/vel/lane stored [E][V] (multi-lane, highway)
   void *headway = nullptr, *accel = nullptr, *obs = nullptr, *reward = nullptr;
   double *stats = nullptr, *lengths_dev = nullptr;
@@ -150,6 +153,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->stats, 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
   e->env_major = cfg->n_lanes > 1 || cfg->topology == FS_TOPO_HIGHWAY;
   if (e->env_major) A(&e->last_lc, V * E * 4);
+  if (cfg->topology == FS_TOPO_HIGHWAY) { A(&e->counters, 4 * E * 4); A(&e->vtype, V * E); }
   if (cfg->record_views) {
     A(&e->headway, V * E * ts); A(&e->accel, V * E * ts);
     A(&e->leader, V * E * 4); A(&e->follower, V * E * 4);
@@ -276,6 +280,18 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
                         : (!sim && s.noise > 0) ? 1 : 0;
     }
   }
+  if (e->cfg.topology == FS_TOPO_HIGHWAY) {
+    if (e->cfg.n_initial < 0 || e->cfg.n_initial > e->cfg.n_veh)
+      return fail(e, FS_EINVAL, "fs_set_types: n_initial must be within the slot capacity");
+    if (e->cfg.inflow_type < 0 || e->cfg.inflow_type >= n_types)
+      return fail(e, FS_EINVAL, "fs_set_types: inflow_type out of range");
+    for (int t = 0; t < n_types; ++t) {
+      const int c = types[t].controller;
+      if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC || c == FS_CTRL_RL)
+        return fail(e, FS_EINVAL, "fs_set_types: PISaturation / LAC / RL vehicles are not "
+                                  "supported on the highway topology (slots are re-packed)");
+    }
+  }
   if (e->f64) fill_cfg<double>(e, e->cd, types, n_types, type_of_vehicle);
   else fill_cfg<float>(e, e->cf, types, n_types, type_of_vehicle);
   if (e->env_needs_rl() && e->n_rl < 1)
@@ -353,6 +369,40 @@ static int launch_ml(fs_engine* e, const fs::StepArgs<T>& a) {
   return FS_OK;
 }
 
+template <typename T>
+static fs::HwBufs<T> hw_bufs(fs_engine* e) {
+  fs::HwBufs<T> b;
+  const size_t E = e->cfg.n_envs;
+  b.pos = (T*)e->pos; b.vel = (T*)e->vel; b.vtype = e->vtype; b.active = e->active;
+  b.length = (T*)e->circ;
+  b.n_active = e->counters; b.departed = e->counters + E; b.arrived = e->counters + 2 * E;
+  b.spawned = e->counters + 3 * E;
+  b.time_counter = e->time_counter; b.episode = e->episode; b.done = e->done; b.crash = e->crash;
+  b.obs = (T*)e->obs; b.reward = (T*)e->reward;
+  b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
+  b.v_leader = e->leader; b.v_follower = e->follower; b.stats = e->stats;
+  b.period = e->cfg.inflow_vehs_per_hour > 0 ? 3600.0 / e->cfg.inflow_vehs_per_hour : 0.0;
+  b.begin = e->cfg.inflow_begin;
+  b.depart_speed = (T)e->cfg.inflow_depart_speed;
+  b.inflow_type = e->cfg.inflow_type;
+  return b;
+}
+
+template <typename T>
+static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
+  const int E = e->cfg.n_envs, CAP = e->cfg.n_veh;
+  const int wpb = E <= 148 * 8 ? 1 : 4;
+  const int grid = (E + wpb - 1) / wpb;
+  const size_t smem = (size_t)wpb * CAP * (3 * sizeof(T) + sizeof(int));
+  const fs::HwBufs<T> b = hw_bufs<T>(e);
+  if (CAP <= 64) fs::highway_kernel<T, 2><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  else if (CAP <= 160) fs::highway_kernel<T, 5><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  else fs::highway_kernel<T, 8><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  e->launches++;
+  FS_CUDA(e, cudaGetLastError());
+  return FS_OK;
+}
+
 static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
                                const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
                                const fs::StepArgs<float>& a) {
@@ -366,8 +416,7 @@ static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
 
 template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
-  if (e->cfg.topology != FS_TOPO_RING)
-    return fail(e, FS_EINVAL, "step: highway topology is not built in this version");
+  if (e->cfg.topology == FS_TOPO_HIGHWAY) return launch_hw<T>(e, a);
   const int V = e->cfg.n_veh, E = e->cfg.n_envs;
   if (e->cfg.n_lanes > 1) return launch_ml<T>(e, a);
   if (e->fast_ok) {
@@ -417,7 +466,11 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
   b.last_lc = e->last_lc;
   b.vs = e->env_major ? 1 : e->cfg.n_envs; b.es = e->env_major ? e->cfg.n_veh : 1;
   const int E = e->cfg.n_envs, block = 128;
-  fs::ring_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(cfg_of<T>(e), b);
+  if (e->cfg.topology == FS_TOPO_HIGHWAY)
+    fs::highway_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(
+        cfg_of<T>(e), hw_bufs<T>(e), mask_dev, e->cfg.n_initial);
+  else
+    fs::ring_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(cfg_of<T>(e), b);
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   // warm-up: Env.reset steps with rl_actions=None (flow/envs/base.py:554-555)
@@ -431,9 +484,10 @@ static int check_room(fs_engine* e, double L) {
   int ld = g.lanes_distribution;
   if (ld > g.n_lanes) ld = g.n_lanes;
   if (ld < 1) ld = 1;
-  const double edge_len = L / 4.0;
-  const double dist = edge_len > min_gap + 5.0 ? 4 * edge_len * ld : 0.0;
-  if (dist - ld * bunching - g.n_veh * (min_gap + 5.0) < 0)
+  const bool hw = g.topology == FS_TOPO_HIGHWAY;
+  const double edge_len = hw ? L : L / 4.0;
+  const double dist = edge_len > min_gap + 5.0 ? (hw ? 1 : 4) * edge_len * ld : 0.0;
+  if (dist - ld * bunching - (hw ? g.n_initial : g.n_veh) * (min_gap + 5.0) < 0)
     return fail(e, FS_EINVAL, "There is not enough space to place all vehicles in the network.");
   return FS_OK;
 }
@@ -441,8 +495,6 @@ static int check_room(fs_engine* e, double L) {
 extern "C" int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* lengths) {
   if (!e) return FS_EINVAL;
   if (!e->types_set) return fail(e, FS_ESTATE, "fs_reset: call fs_set_types first");
-  if (e->cfg.topology != FS_TOPO_RING)
-    return fail(e, FS_EINVAL, "fs_reset: only ring topology is built in this version");
   cudaSetDevice(e->cfg.device);
   const size_t E = e->cfg.n_envs;
   int rc = check_room(e, e->cfg.length_lo);
@@ -522,6 +574,7 @@ extern "C" int fs_buffers(fs_engine* e, fs_views* out) {
   out->headway = e->headway; out->leader = e->leader; out->follower = e->follower;
   out->accel = e->accel; out->length = e->circ; out->obs = e->obs; out->reward = e->reward;
   out->done = e->done; out->crash = e->crash; out->time_counter = e->time_counter;
+  out->counters = e->counters;
   out->n_envs = e->cfg.n_envs; out->n_veh = e->cfg.n_veh; out->n_lanes = e->cfg.n_lanes;
   out->obs_dim = e->obs_dim; out->act_dim = e->act_dim; out->dtype = e->cfg.dtype;
   out->veh_stride = e->env_major ? 1 : e->cfg.n_envs;

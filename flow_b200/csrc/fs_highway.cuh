@@ -1,0 +1,316 @@
+// fs_highway.cuh — single-lane open highway with an inflow (config c4).
+//
+// Mapping: ONE WARP OWNS ONE ENVIRONMENT; vehicles live head-first in a
+// fixed-capacity slot array (slot 0 = furthest downstream), slot s in lane
+// (s & 31), register (s >> 5); state is env-major ([E][CAP]) so the warp's
+// loads/stores are contiguous. The leader of slot s is slot s-1 (no overtaking
+// on one lane), read through a per-warp shared-memory copy. Vehicles that
+// reach the end of the edge are removed by WARP-BALLOT STREAM COMPACTION
+// (__ballot_sync + popc prefix -> new slot), and the inflow appends at most
+// one vehicle per step at the tail.
+//
+// Restated from the reference / SUMO (see oracle/highway.py for the rules):
+//   arrivals + departures bookkeeping   flow/core/kernel/vehicle/traci.py:145-174,212-216
+//   <flow vehsPerHour begin departSpeed> flow/core/kernel/network/traci.py:801-833,
+//                                        flow/core/params.py:1080-1213
+//   no-leader headway 1000               flow/core/kernel/vehicle/traci.py:234-238
+//   desired_velocity over present vehicles  flow/core/rewards.py:6-59
+// SUMO's insertion / arrival rules have no reference fixture: parity unpinned.
+#pragma once
+#include "fs_common.cuh"
+#include "fs_ring.cuh"
+
+namespace fs {
+
+template <typename T>
+struct HwBufs {
+  T* pos; T* vel; uint8_t* vtype; uint8_t* active;   // [E][CAP]
+  T* length;                                         // [E] edge length
+  int* n_active; int* departed; int* arrived; int* spawned;  // [E]
+  int* time_counter; int* episode;
+  uint8_t* done; uint8_t* crash;
+  T* obs; T* reward;
+  T* v_accel; T* v_headway; int* v_leader; int* v_follower;  // views [E][CAP] or null
+  double* stats;
+  double period, begin;   // s
+  T depart_speed;
+  int inflow_type;
+};
+
+template <typename T, int SLOTS>
+__global__ void __launch_bounds__(128)
+highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const StepArgs<T> A) {
+  typedef Num<T> N;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane_id = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int E = cfg.n_envs, CAP = cfg.n_veh;
+  const int e = blockIdx.x * (blockDim.x >> 5) + wib;
+  if (e >= E) return;
+  if (A.mask != nullptr && A.mask[e] == 0) return;
+  const size_t per_warp = (size_t)CAP * (3 * sizeof(T) + sizeof(int));
+  unsigned char* mine = smem_raw + per_warp * wib;
+  T* xs = reinterpret_cast<T*>(mine);
+  T* vs = xs + CAP;
+  T* hs = vs + CAP;
+  int* ts = reinterpret_cast<int*>(hs + CAP);
+
+  T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS];
+  int ty[SLOTS];
+  const size_t eo = (size_t)e * CAP;
+  int n = B.n_active[e];
+#pragma unroll
+  for (int r = 0; r < SLOTS; ++r) {
+    const int s = lane_id + 32 * r;
+    const bool ok = s < n;
+    x[r] = ok ? B.pos[eo + s] : T(0);
+    v[r] = ok ? B.vel[eo + s] : T(0);
+    ty[r] = ok ? (int)B.vtype[eo + s] : 0;
+    acc[r] = T(0);
+  }
+  const T Lr = B.length[e];
+  const T dt = cfg.dt;
+  int tc = B.time_counter[e];
+  const int episode = B.episode[e];
+  bool done = A.ignore_done ? false : (B.done[e] != 0);
+  bool crash = B.crash[e] != 0;
+  const int t_end = cfg.sims_per_step * (cfg.warmup_steps + cfg.horizon);
+  const long long gid = cfg.env_id_base + e;
+  T reward = B.reward[e];
+  int spawned = B.spawned[e], departed = B.departed[e], arrived = B.arrived[e];
+  double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
+
+  auto publish = [&]() {
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < SLOTS; ++r) {
+      const int s = lane_id + 32 * r;
+      if (s < CAP) { xs[s] = x[r]; vs[s] = v[r]; ts[s] = ty[r]; }
+    }
+    __syncwarp();
+  };
+  auto update = [&]() {  // headway to slot s-1; the head sees 1000 (no leader)
+    publish();
+#pragma unroll
+    for (int r = 0; r < SLOTS; ++r) {
+      const int s = lane_id + 32 * r;
+      h[r] = (s > 0 && s < n) ? (xs[s - 1] - x[r]) - cfg.types[ts[s - 1]].length : T(1000);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < SLOTS; ++r) {
+      const int s = lane_id + 32 * r;
+      if (s < CAP) hs[s] = h[r];
+    }
+    __syncwarp();
+  };
+  update();
+
+  auto write_obs = [&](T* o, T* ol) {
+#pragma unroll
+    for (int r = 0; r < SLOTS; ++r) {
+      const int s = lane_id + 32 * r;
+      if (s >= CAP) continue;
+      const T a0 = s < n ? N::div(v[r], cfg.speed_limit) : T(0);
+      const T a1 = s < n ? N::div(x[r], Lr) : T(0);
+      if (o) { o[s] = a0; o[CAP + s] = a1; }
+      if (ol) { ol[s] = a0; ol[CAP + s] = a1; }
+    }
+  };
+  if (A.k_steps == 0) write_obs(nullptr, B.obs + (size_t)e * cfg.obs_dim);
+
+  for (int k = 0; k < A.k_steps; ++k) {
+    if (!done) {
+      T mean_v = T(0);
+      if (cfg.any_follower & 2) {
+        T sm = T(0);
+#pragma unroll
+        for (int r = 0; r < SLOTS; ++r) if (lane_id + 32 * r < n) sm = add(sm, v[r]);
+        for (int o = 16; o > 0; o >>= 1) sm += __shfl_xor_sync(0xffffffffu, sm, o);
+        mean_v = N::div(sm, T(n > 0 ? n : 1));
+      }
+      // controllers -> apply_acceleration -> Euler move (all read the published state)
+#pragma unroll
+      for (int r = 0; r < SLOTS; ++r) {
+        const int s = lane_id + 32 * r;
+        if (s >= n) continue;
+        const TypeP<T>& tp = cfg.types[ty[r]];
+        const int ctrl = tp.ctrl;
+        const bool has_lead = s > 0, has_f = s + 1 < n;
+        const T vi = v[r], hi = h[r];
+        const T vl = has_lead ? vs[s - 1] : T(-1001);
+        T st0 = T(0);
+        T a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, has_f, has_f ? vs[s + 1] : T(-1001),
+                            has_f ? hs[s + 1] : T(-1001), mean_v, dt, cfg.inv_dt, st0);
+        if (ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL) {
+          if (tp.noise > T(0))
+            a = add(a, mul(tp.noise, normal_sample<T>(cfg.seed, gid, s, tc + episode * 1000003)));
+          if (tp.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
+            a = failsafe_instantaneous<T>(a, vi, hi, has_lead, n, dt);
+          else if (tp.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
+            a = failsafe_safe_velocity<T>(a, vi, vl, hi, n, dt, tp.delay);
+        }
+        acc[r] = a;
+      }
+      __syncwarp();
+      tc += 1;
+      // move, flag arrivals, compact survivors with ballots (order preserved)
+      int base = 0;
+      int dst[SLOTS];
+#pragma unroll
+      for (int r = 0; r < SLOTS; ++r) {
+        const int s = lane_id + 32 * r;
+        bool keep = false;
+        if (s < n) {
+          const T vn = N::max(add(v[r], mul(acc[r], dt)), T(0));
+          x[r] = add(x[r], mul(vn, dt));
+          v[r] = vn;
+          keep = x[r] < Lr;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        dst[r] = keep ? base + __popc(m & ((1u << lane_id) - 1u)) : -1;
+        base += __popc(m);
+      }
+      const int n_keep = base;
+      arrived += n - n_keep;
+      if (n_keep != n) {  // scatter survivors to their new slots through shared memory
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < SLOTS; ++r)
+          if (dst[r] >= 0) { xs[dst[r]] = x[r]; vs[dst[r]] = v[r]; ts[dst[r]] = ty[r]; hs[dst[r]] = acc[r]; }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < SLOTS; ++r) {
+          const int s = lane_id + 32 * r;
+          if (s < n_keep) { x[r] = xs[s]; v[r] = vs[s]; ty[r] = ts[s]; acc[r] = hs[s]; }
+          else { x[r] = T(0); v[r] = T(0); ty[r] = 0; acc[r] = T(0); }
+        }
+        n = n_keep;
+      }
+      // inflow: at most one due vehicle per step, appended at the tail
+      if (B.period > 0.0) {
+        const double t = (double)tc * (double)cfg.dt;
+        const double due = B.begin + (double)spawned * B.period;
+        bool spawn = t >= due && n < CAP;
+        if (spawn && n > 0) {
+          const int sl = n - 1;  // last vehicle
+          T xl = T(0); int tl = 0;
+#pragma unroll
+          for (int r = 0; r < SLOTS; ++r) if (lane_id + 32 * r == sl) { xl = x[r]; tl = ty[r]; }
+          xl = __shfl_sync(0xffffffffu, xl, sl & 31);
+          tl = __shfl_sync(0xffffffffu, tl, sl & 31);
+          spawn = (xl - cfg.types[tl].length) >= cfg.types[B.inflow_type].sim_min_gap;
+        }
+        if (spawn) {
+#pragma unroll
+          for (int r = 0; r < SLOTS; ++r)
+            if (lane_id + 32 * r == n) { x[r] = T(0); v[r] = B.depart_speed; ty[r] = B.inflow_type; acc[r] = T(0); }
+          n += 1; spawned += 1; departed += 1;
+        }
+      }
+      update();
+      bool cr = false;
+      T sv = T(0), sq = T(0), s2 = T(0);
+#pragma unroll
+      for (int r = 0; r < SLOTS; ++r) {
+        const int s = lane_id + 32 * r;
+        if (s >= n) continue;
+        cr |= h[r] < T(0);
+        sv = add(sv, v[r]);
+        const T d = v[r] - cfg.target_velocity;
+        sq = add(sq, mul(d, d));
+        s2 += v[r] * v[r];
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        sv += __shfl_xor_sync(0xffffffffu, sv, o);
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+      }
+      crash = __any_sync(0xffffffffu, cr);
+      done = crash || tc >= t_end;
+      if (crash || n == 0) reward = T(0);
+      else {  // rewards.desired_velocity over the vehicles present
+        T mc2 = T(0);
+        const T t2 = mul(cfg.target_velocity, cfg.target_velocity);
+        for (int i = 0; i < n; ++i) mc2 = add(mc2, t2);
+        const T max_cost = N::sqrt(mc2), cost = N::sqrt(sq);
+        reward = N::div(N::max(max_cost - cost, T(0)), add(max_cost, T(1.1920928955078125e-07)));
+      }
+      if (A.accumulate_stats && lane_id == 0) {
+        st_rew += (double)reward; st_v += (double)sv; st_v2 += (double)s2;
+        st_vs += n; st_es += 1; st_cr += crash ? 1 : 0;
+      }
+    } else {
+      reward = T(0);
+    }
+    const bool last = (k == A.k_steps - 1);
+    if (A.obs_seq != nullptr || last)
+      write_obs(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
+                last ? B.obs + (size_t)e * cfg.obs_dim : nullptr);
+    if (lane_id == 0) {
+      if (A.reward_seq) A.reward_seq[(size_t)k * E + e] = reward;
+      if (A.done_seq) A.done_seq[(size_t)k * E + e] = done ? 1 : 0;
+    }
+  }
+
+#pragma unroll
+  for (int r = 0; r < SLOTS; ++r) {
+    const int s = lane_id + 32 * r;
+    if (s >= CAP) continue;
+    B.pos[eo + s] = x[r]; B.vel[eo + s] = v[r]; B.vtype[eo + s] = (uint8_t)ty[r];
+    B.active[eo + s] = s < n ? 1 : 0;
+    if (A.write_views) {
+      B.v_headway[eo + s] = s < n ? h[r] : T(0);
+      B.v_leader[eo + s] = (s > 0 && s < n) ? s - 1 : -1;
+      B.v_follower[eo + s] = (s + 1 < n) ? s + 1 : -1;
+      if (A.k_steps > 0) B.v_accel[eo + s] = s < n ? acc[r] : T(0);
+    }
+  }
+  if (lane_id == 0) {
+    B.n_active[e] = n; B.spawned[e] = spawned; B.departed[e] = departed; B.arrived[e] = arrived;
+    B.time_counter[e] = tc;
+    B.done[e] = done ? 1 : 0;
+    B.crash[e] = crash ? 1 : 0;
+    B.reward[e] = reward;
+    if (A.accumulate_stats) {
+      const double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
+      for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&B.stats[q], vals[q]);
+    }
+  }
+}
+
+// Env.reset on the highway: initial vehicles by gen_even_start_pos on the single
+// edge (flow/core/kernel/network/base.py:263-391), stored head first.
+template <typename T>
+__global__ void highway_reset_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B,
+                                     const uint8_t* mask, int n_initial) {
+  const int E = cfg.n_envs, CAP = cfg.n_veh;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  if (mask != nullptr && mask[e] == 0) return;
+  const double L = (double)cfg.length_lo;
+  const double min_gap = fmax(0.0, (double)cfg.init_min_gap);
+  const double bunching = fmax(0.0, (double)cfg.bunching);
+  const size_t eo = (size_t)e * CAP;
+  if (n_initial > 0) {
+    const double available = (L - bunching) - n_initial * (min_gap + 5.0);
+    const double increment = available / n_initial;
+    double x = (double)cfg.x0;
+    // index i has the i-th smallest position as long as no wrap happens; head first:
+    for (int i = 0; i < n_initial; ++i) {
+      const int s = n_initial - 1 - i;
+      B.pos[eo + s] = (T)x; B.vel[eo + s] = T(0);
+      B.vtype[eo + s] = cfg.type_of[i]; B.active[eo + s] = 1;
+      x = fmod(__dadd_rn(__dadd_rn(__dadd_rn(x, increment), 5.0), min_gap), L);
+    }
+  }
+  for (int s = n_initial; s < CAP; ++s) {
+    B.pos[eo + s] = T(0); B.vel[eo + s] = T(0); B.vtype[eo + s] = 0; B.active[eo + s] = 0;
+  }
+  B.length[e] = (T)L;
+  B.n_active[e] = n_initial; B.departed[e] = n_initial; B.arrived[e] = 0; B.spawned[e] = 0;
+  B.time_counter[e] = 0;
+  B.episode[e] = B.episode[e] + 1;
+  B.done[e] = 0; B.crash[e] = 0;
+}
+
+}  // namespace fs

@@ -113,13 +113,16 @@ class Engine:
     """One batched step engine on one GPU. Not thread-safe."""
 
     def __init__(self, types, type_of_vehicle, n_envs, dtype='f32', device=0,
-                 use_torch_stream=True, **cfg):
+                 use_torch_stream=True, capacity=None, **cfg):
         self.lib = _lib.load()
         c = _lib.FsConfig()
         c.abi_version = 1
         c.device = device
         c.dtype = F64 if dtype in ('f64', F64, 'float64') else F32
         c.n_envs = n_envs
+        if capacity is not None:   # highway: slots; the table lists the initial vehicles
+            cfg.setdefault('n_initial', len(type_of_vehicle))
+            type_of_vehicle = list(type_of_vehicle) + [0] * (capacity - len(type_of_vehicle))
         c.n_veh = len(type_of_vehicle)
         defaults = dict(topology=TOPO_RING, env_kind=ENV_ACCEL, n_lanes=1, env_id_base=0,
                         seed=0, sim_step=0.1, length_lo=230.0, length_hi=230.0,
@@ -129,7 +132,7 @@ class Engine:
                         lane_change_duration=5, target_velocity=10.0, act_lo=-4.5,
                         act_hi=2.6, obs_max_length=0.0, inflow_vehs_per_hour=0.0,
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
-                        record_views=0, lc_corrected=0)
+                        record_views=0, lc_corrected=0, n_initial=0, inflow_begin=1.0)
         unknown = set(cfg) - set(defaults)
         if unknown:
             raise TypeError('unknown engine config keys: %s' % sorted(unknown))
@@ -177,6 +180,7 @@ class Engine:
         self.obs, self.reward = T(v.obs, (E, self.obs_dim)), T(v.reward, (E,))
         self.done, self.crash = T(v.done, (E,), 'u8'), T(v.crash, (E,), 'u8')
         self.time_counter = T(v.time_counter, (E,), 'i32')
+        self.counters = T(v.counters, (3, E), 'i32')   # highway: in network, departed, arrived
         self._fs_step = self.lib.fs_step
 
     def _check(self, rc):

@@ -144,6 +144,10 @@ typedef struct fs_config {
   int32_t record_views;  /* 1: keep views.accel/headway/leader/follower current  */
   int32_t lc_corrected;  /* 0: get_last_lc returns the headway like the reference
                             (vehicle/traci.py:614); 1: the step of the last change */
+  /* highway: vehicles present at reset (types = type_of_vehicle[0..n_initial)) */
+  int32_t n_initial;
+  int32_t reserved1;
+  double inflow_begin;   /* s; InFlows.add(begin=1) */
 } fs_config;
 
 /* device views; T = float or double per cfg.dtype; [a][b] = a slow, b fast */
@@ -162,6 +166,7 @@ typedef struct fs_views {
   uint8_t* done;     /* u8 [E]                                                  */
   uint8_t* crash;    /* u8 [E]                                                  */
   int32_t* time_counter; /* i32 [E]                                             */
+  int32_t* counters;     /* i32 [3][E] highway: vehicles in network, departed, arrived */
   int32_t n_envs, n_veh, n_lanes, obs_dim, act_dim, dtype;
   /* element (vehicle i, env e) of pos/vel/lane/headway/leader/follower/accel is at
    * i*veh_stride + e*env_stride: single-lane rings are [V][E] (E, 1), multi-lane

@@ -1,0 +1,161 @@
+"""CPU oracle — TEST INFRASTRUCTURE ONLY (never imported by flow_b200/).
+
+Single-lane open highway with an inflow (config c4): one-environment fp64
+restatement. Controllers, fail-safes, apply_acceleration and the
+desired_velocity reward are the reference's (oracle/controllers.py,
+flow/core/rewards.py:6-59). Everything SUMO does on this network is restated
+and is "parity unpinned" (SURVEY.md §8c items 5, 6): no reference test or
+fixture holds numbers for inflow insertion or arrival.
+
+  * network: HighwayNetwork(length, lanes=1, num_edges=1) — one edge
+    'highway_0' of `length` metres, no junctions (flow/networks/highway.py:88-104);
+  * vehicles are kept HEAD FIRST: slot 0 is the vehicle furthest downstream;
+    the leader of slot s is slot s-1, the head has no leader (headway 1000,
+    flow/core/kernel/vehicle/traci.py:234-238); follower of s is s+1;
+  * arrival: a vehicle whose position after the move is >= length leaves the
+    network in that step (SUMO VAR_ARRIVED -> TraCIVehicle.remove,
+    vehicle/traci.py:145-160) and the slots behind it close up;
+  * inflow `<flow vehsPerHour=q begin=b departSpeed=v0 departPos=0>`
+    (flow/core/kernel/network/traci.py:801-833): vehicle k is due at time
+    b + k*3600/q; at the end of a step at most ONE due vehicle is inserted at
+    x = 0 with speed v0 if a slot is free and the bumper gap to the last
+    vehicle (x_last - length_last) is at least the new type's minGap;
+    otherwise it waits (SUMO's insertion backlog);
+  * initial vehicles: gen_even_start_pos on the single edge
+    (flow/core/kernel/network/base.py:263-391), speed 0;
+  * collision <=> some headway < 0 after the move; observation = speeds /
+    speed_limit and positions / length per slot (0 for empty slots).
+"""
+import numpy as np
+
+from . import controllers as C
+
+F32_EPS = float(np.finfo(np.float32).eps)
+
+
+class HighwaySim:
+    def __init__(self, types, initial_types, capacity=160, length=1000.0, dt=0.1,
+                 speed_limit=30.0, inflow_vehs_per_hour=2000.0, inflow_type=0,
+                 inflow_depart_speed=20.0, inflow_begin=1.0, x0=0.0, bunching=0.0,
+                 init_min_gap=0.0, horizon=3000, warmup_steps=0, target_velocity=10.0,
+                 noise_fn=None):
+        self.types = types
+        self.initial_types = list(initial_types)
+        self.capacity = capacity
+        self.length = float(length)
+        self.dt = dt
+        self.speed_limit = speed_limit
+        self.q = inflow_vehs_per_hour
+        self.inflow_type = inflow_type
+        self.depart_speed = inflow_depart_speed
+        self.begin = inflow_begin
+        self.init = dict(x0=x0, bunching=bunching, min_gap=init_min_gap)
+        self.horizon, self.warmup_steps = horizon, warmup_steps
+        self.target_velocity = target_velocity
+        self.noise_fn = noise_fn
+        self.reset()
+
+    # getters the controller functions use ---------------------------------
+    @property
+    def num_vehicles(self):
+        return len(self.pos)
+
+    def mean_speed(self):
+        return float(np.mean(self.vel))
+
+    def reset(self):
+        n = len(self.initial_types)
+        min_gap = max(0.0, self.init['min_gap'])
+        available = self.length - max(0.0, self.init['bunching']) - n * (min_gap + 5.0)
+        if available < 0:
+            raise ValueError('There is not enough space to place all vehicles in the network.')
+        xs = []
+        if n:
+            increment = available / n
+            x = self.init['x0']
+            for _ in range(n):
+                xs.append(x)
+                x = (x + increment + 5.0 + min_gap) % self.length
+        order = sorted(range(n), key=lambda i: -xs[i])        # head first
+        self.pos = [float(xs[i]) for i in order]
+        self.vel = [0.0] * n
+        self.type_of = [self.initial_types[i] for i in order]
+        self.accel = [0.0] * n
+        self.time_counter = 0
+        self.spawned = 0
+        self.departed = n
+        self.arrived = 0
+        self.crash = False
+        self.done = False
+        self.update()
+        for _ in range(self.warmup_steps):
+            self.step()
+        return self.get_state()
+
+    def update(self):
+        n = len(self.pos)
+        self.leader = [s - 1 for s in range(n)]
+        self.follower = [s + 1 if s + 1 < n else -1 for s in range(n)]
+        self.headway = [1e3 if s == 0 else
+                        self.pos[s - 1] - self.pos[s] - self.types[self.type_of[s - 1]].length
+                        for s in range(n)]
+
+    def step(self):
+        if self.done:
+            return self.get_state(), 0.0, True
+        dt = self.dt
+        self.time_counter += 1
+        n = len(self.pos)
+        nv = [0.0] * n
+        for s in range(n):
+            vt = self.types[self.type_of[s]]
+            z = self.noise_fn(self.time_counter - 1, s) if (self.noise_fn and vt.noise > 0) else 0.0
+            a = C.get_action(self, s, vt, {}, dt, self.speed_limit, z)
+            self.accel[s] = a
+            nv[s] = max(self.vel[s] + a * dt, 0.0)
+        for s in range(n):
+            self.vel[s] = nv[s]
+            self.pos[s] = self.pos[s] + nv[s] * dt
+        # arrivals
+        keep = [s for s in range(n) if self.pos[s] < self.length]
+        self.arrived += n - len(keep)
+        self.pos = [self.pos[s] for s in keep]
+        self.vel = [self.vel[s] for s in keep]
+        self.type_of = [self.type_of[s] for s in keep]
+        self.accel = [self.accel[s] for s in keep]
+        # inflow
+        if self.q > 0:
+            t = self.time_counter * dt
+            due = self.begin + self.spawned * (3600.0 / self.q)
+            if t >= due and len(self.pos) < self.capacity:
+                nt = self.types[self.inflow_type]
+                free = (not self.pos) or \
+                    (self.pos[-1] - self.types[self.type_of[-1]].length >= nt.sim_min_gap)
+                if free:
+                    self.pos.append(0.0)
+                    self.vel.append(float(self.depart_speed))
+                    self.type_of.append(self.inflow_type)
+                    self.accel.append(0.0)
+                    self.spawned += 1
+                    self.departed += 1
+        self.update()
+        self.crash = any(h < 0 for h in self.headway)
+        self.done = self.crash or self.time_counter >= self.warmup_steps + self.horizon
+        return self.get_state(), self.desired_velocity(self.crash), self.done
+
+    def get_state(self):
+        cap = self.capacity
+        v = [x / self.speed_limit for x in self.vel] + [0.0] * (cap - len(self.vel))
+        p = [x / self.length for x in self.pos] + [0.0] * (cap - len(self.pos))
+        return np.array(v + p)
+
+    def desired_velocity(self, fail=False):
+        """flow/core/rewards.py:6-59 over the vehicles currently in the network."""
+        vel = np.array(self.vel)
+        n = len(vel)
+        if n == 0 or fail or any(vel < -100):
+            return 0.
+        target = self.target_velocity
+        max_cost = np.linalg.norm(np.array([target] * n))
+        cost = np.linalg.norm(vel - target)
+        return max(max_cost - cost, 0) / (max_cost + F32_EPS)
