@@ -404,12 +404,12 @@ static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
 }
 
 static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
-                               const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
+                               const fs::FastP<float>& c, const fs::RingBufs<float>& b,
                                const fs::StepArgs<float>& a) {
   return fs_launch_fast22_f32(shape, variant, E, st, c, b, a);
 }
 static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
-                               const fs::Cfg<double>& c, const fs::RingBufs<double>& b,
+                               const fs::FastP<double>& c, const fs::RingBufs<double>& b,
                                const fs::StepArgs<double>& a) {
   return fs_launch_fast22_f64(shape, variant, E, st, c, b, a);
 }
@@ -422,10 +422,11 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->fast_ok) {
     // IDM-law hot kernel; threads per env chosen from the batch size
     int shape = e->ring_shape;
-    if (shape != 1 && shape != 2 && shape != 4 && shape != 8)
+    if (shape != 1 && shape != 2 && shape != 4 && shape != 8 && shape != 16 && shape != 32)
       shape = E >= 32768 ? 1 : (E >= 16384 ? 2 : 8);
     if (sizeof(T) == 8 && shape == 1 && e->ring_shape == 0) shape = 2;  // f64 x 22 slots spills
-    FS_CUDA(e, launch_fast(shape, e->fast_variant, E, e->stream, cfg_of<T>(e), ring_bufs<T>(e), a));
+    FS_CUDA(e, launch_fast(shape, e->fast_variant, E, e->stream, fs::make_fastp(cfg_of<T>(e)),
+                           ring_bufs<T>(e), a));
     e->launches++;
     return FS_OK;
   }

@@ -4,7 +4,7 @@
 #include "fs_launch.h"
 
 cudaError_t fs_launch_fast22_f32(int shape, int variant, int n_envs, cudaStream_t st,
-                                 const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
+                                 const fs::FastP<float>& c, const fs::RingBufs<float>& b,
                                  const fs::StepArgs<float>& a) {
   return fs::launch_fast22<float>(shape, variant, n_envs, st, c, b, a);
 }

@@ -3,7 +3,7 @@
 #include "fs_launch.h"
 
 cudaError_t fs_launch_fast22_f64(int shape, int variant, int n_envs, cudaStream_t st,
-                                 const fs::Cfg<double>& c, const fs::RingBufs<double>& b,
+                                 const fs::FastP<double>& c, const fs::RingBufs<double>& b,
                                  const fs::StepArgs<double>& a) {
   return fs::launch_fast22<double>(shape, variant, n_envs, st, c, b, a);
 }

@@ -3,10 +3,11 @@
 #include <cuda_runtime.h>
 #include "fs_common.cuh"
 #include "fs_ring.cuh"
+#include "fs_ring_fast.cuh"
 
 cudaError_t fs_launch_fast22_f32(int shape, int variant, int n_envs, cudaStream_t st,
-                                 const fs::Cfg<float>& c, const fs::RingBufs<float>& b,
+                                 const fs::FastP<float>& c, const fs::RingBufs<float>& b,
                                  const fs::StepArgs<float>& a);
 cudaError_t fs_launch_fast22_f64(int shape, int variant, int n_envs, cudaStream_t st,
-                                 const fs::Cfg<double>& c, const fs::RingBufs<double>& b,
+                                 const fs::FastP<double>& c, const fs::RingBufs<double>& b,
                                  const fs::StepArgs<double>& a);

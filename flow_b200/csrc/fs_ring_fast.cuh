@@ -1,15 +1,29 @@
 // fs_ring_fast.cuh — the hot kernel: single-lane ring where every vehicle
 // follows the IDM law (IDMController humans of ONE type + RL vehicles of one
 // type, which is what examples/exp_configs/non_rl/ring.py and
-// rl/singleagent/singleagent_ring.py build). Same thread mapping as
-// fs_ring.cuh (G threads per env, VPT register-resident vehicles per thread),
-// but with everything that is uniform hoisted out of the K-step loop:
-//   * the human type's IDM parameters live in registers (no per-vehicle
-//     constant-bank gathers), RL vehicles are a bit mask;
-//   * delta == 4 is a template flag (two multiplies instead of pow);
-//   * noise (Philox4x32-10, one call per 4 vehicles, Box-Muller on both
-//     outputs) and the fail-safes are template flags;
-//   * kExact (V == VPT*G) removes all padding predicates.
+// rl/singleagent/singleagent_ring.py build), V <= 32.
+//
+// Thread mapping as in fs_ring.cuh (G threads own one env, VPT vehicles per
+// thread, all state in registers for the K fused steps of a launch), tuned
+// for issue rate:
+//   * everything uniform is precomputed on the host into FastP (a ~200 B
+//     kernel argument): IDM block of the human / RL type, RL bit mask, obs and
+//     reward constants. No per-vehicle table gathers, no prologue loops;
+//   * ONE exchange per step: after the move the group's first (x, v) is
+//     shuffled to the previous thread; it feeds the headway of this step, the
+//     partial observation of this step and the leader speed of the next step;
+//   * the RL vehicle's thread writes obs / reward / done itself (it already
+//     holds its leader's state), so the PO observation costs no shuffles;
+//   * reward sums: fp32 uses ONE integer warp reduction (REDUX) of the speeds
+//     in 2^-20 m/s fixed point (abs error < 3e-6 on the sum) instead of a
+//     shuffle tree; the collision flag is one warp vote; fp64 keeps the tree;
+//   * noise: Philox4x32-10 + Box-Muller gives 4 normals per call; a vehicle
+//     consumes them over 4 CONSECUTIVE steps (counter = step/4, component =
+//     step%4), so the cost is 1/4 call per vehicle-step for every shape;
+//   * RL actions are prefetched 4 steps ahead (the only global load in the
+//     loop would otherwise sit on the step's critical path);
+//   * delta == 4, noise, fail-safes, views and kExact (V == VPT*G) are
+//     template flags.
 // Reference lines restated: see fs_ring.cuh header (same step semantics).
 #pragma once
 #include "fs_common.cuh"
@@ -17,41 +31,88 @@
 
 namespace fs {
 
-// four standard normals for (env, vehicle group q = vehicle/4, step)
-template <typename T>
-__device__ __forceinline__ void normal4(unsigned long long seed, long long env_gid, int q,
-                                        int step, T (&z)[4]) {
-  uint32_t r[4];
-  Philox::gen((uint32_t)step, (uint32_t)q, (uint32_t)env_gid, (uint32_t)(env_gid >> 32),
-              (uint32_t)seed, (uint32_t)(seed >> 32), r);
-  if (sizeof(T) == 4) {
-    const float k = 2.3283064365386963e-10f;  // 2^-32
-    const float u0 = ((float)r[0] + 1.0f) * k, u2 = ((float)r[2] + 1.0f) * k;
-    const float ra = sqrtf(-2.0f * __logf(fminf(u0, 1.0f)));
-    const float rb = sqrtf(-2.0f * __logf(fminf(u2, 1.0f)));
-    float s0, c0, s1, c1;
-    __sincosf(6.2831853071795865f * ((float)r[1] * k), &s0, &c0);
-    __sincosf(6.2831853071795865f * ((float)r[3] * k), &s1, &c1);
-    z[0] = (T)(ra * c0); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1); z[3] = (T)(rb * s1);
-  } else {
-    const double k = 1.0 / 4294967296.0;
-    const double ra = ::sqrt(-2.0 * ::log(((double)r[0] + 1.0) * k));
-    const double rb = ::sqrt(-2.0 * ::log(((double)r[2] + 1.0) * k));
-    double s0, c0, s1, c1;
-    sincos(6.283185307179586 * ((double)r[1] * k), &s0, &c0);
-    sincos(6.283185307179586 * ((double)r[3] * k), &s1, &c1);
-    z[0] = (T)(ra * c0); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1); z[3] = (T)(rb * s1);
-  }
-}
-
 template <typename T>
 struct IdmRegs {  // one type's effective IDM block, register resident
   T v0, inv_v0, Tt, a, tsab, inv_tsab, delta, s0;
-  __device__ __forceinline__ void load(const TypeP<T>& t) {
+  __host__ __device__ void load(const TypeP<T>& t) {
     v0 = t.e_v0; inv_v0 = t.e_inv_v0; Tt = t.e_T; a = t.e_a; tsab = t.e_tsab;
     inv_tsab = t.e_inv_tsab; delta = t.e_delta; s0 = t.e_s0;
   }
 };
+
+// Host-precomputed constants of the hot kernel (built by make_fastp()).
+template <typename T>
+struct FastP {
+  int n_envs, n_veh, env_kind, obs_dim, act_dim, n_rl;
+  int t_end, clip_actions, collision_min_gap, fail_safe;
+  unsigned rl_mask;   // bit i: vehicle i takes its acceleration from the action vector
+  int rl_veh;         // vehicle of action slot 0 (WaveAttenuationPO observes it)
+  long long env_id_base;
+  unsigned long long seed;
+  T dt, len, noise, delay, min_gap, target, act_lo, act_hi;
+  T obs_max_length, speed_limit, max_cost, inv_nrl, n_veh_t;
+  IdmRegs<T> pa, pb;  // human type / un-commanded RL type (simulator default model)
+};
+
+template <typename T>
+static inline FastP<T> make_fastp(const Cfg<T>& c) {
+  FastP<T> p;
+  memset(&p, 0, sizeof(p));
+  p.n_envs = c.n_envs; p.n_veh = c.n_veh; p.env_kind = c.env_kind; p.obs_dim = c.obs_dim;
+  p.act_dim = c.act_dim; p.n_rl = c.n_rl;
+  p.t_end = c.sims_per_step * (c.warmup_steps + c.horizon);
+  p.clip_actions = c.clip_actions; p.collision_min_gap = c.collision_min_gap;
+  int ta = 0, tb = 0;
+  for (int i = 0; i < c.n_veh; ++i) {
+    if (c.rl_index[i] >= 0) { p.rl_mask |= 1u << i; tb = c.type_of[i]; if (c.rl_index[i] == 0) p.rl_veh = i; }
+    else ta = c.type_of[i];
+  }
+  p.env_id_base = c.env_id_base; p.seed = c.seed;
+  p.dt = c.dt; p.len = c.types[ta].length; p.noise = c.types[ta].noise;
+  p.delay = c.types[ta].delay; p.min_gap = c.types[ta].sim_min_gap;
+  p.fail_safe = c.types[ta].fail_safe;
+  p.target = c.target_velocity; p.act_lo = c.act_lo; p.act_hi = c.act_hi;
+  p.obs_max_length = c.obs_max_length; p.speed_limit = c.speed_limit;
+  {  // ||[target]*V||, rewards.py:52-53 (same summation order as numpy's for V < 8 pairwise block)
+    T mc2 = T(0);
+    const T t2 = c.target_velocity * c.target_velocity;
+    for (int i = 0; i < c.n_veh; ++i) mc2 = mc2 + t2;
+    p.max_cost = (T)sqrt((double)mc2);
+  }
+  p.inv_nrl = T(1) / T(c.n_rl > 0 ? c.n_rl : 1);
+  p.n_veh_t = T(c.n_veh);
+  p.pa.load(c.types[ta]); p.pb.load(c.types[tb]);
+  return p;
+}
+
+// four standard normals from one Philox4x32-10 call (Box-Muller on both pairs)
+template <typename T>
+__device__ __forceinline__ void normal4(unsigned long long seed, long long env_gid, uint32_t c0,
+                                        uint32_t c1, T (&z)[4]) {
+  uint32_t r[4];
+  Philox::gen(c0, c1, (uint32_t)env_gid, (uint32_t)(env_gid >> 32), (uint32_t)seed,
+              (uint32_t)(seed >> 32), r);
+  if (sizeof(T) == 4) {
+    const float k = 2.3283064365386963e-10f;  // 2^-32
+    // u in (0,1]: (r + 1) * 2^-32 evaluated as fma so r = 2^32-1 maps to 1
+    const float u0 = fminf(fmaf((float)r[0], k, k), 1.0f), u2 = fminf(fmaf((float)r[2], k, k), 1.0f);
+    // sqrt(-2 ln u) = sqrt(-2 ln2 * log2 u)
+    const float ra = sqrtf(-1.3862943611198906f * __log2f(u0));
+    const float rb = sqrtf(-1.3862943611198906f * __log2f(u2));
+    float s0, c0f, s1, c1f;
+    __sincosf(6.2831853071795865f * ((float)r[1] * k), &s0, &c0f);
+    __sincosf(6.2831853071795865f * ((float)r[3] * k), &s1, &c1f);
+    z[0] = (T)(ra * c0f); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1f); z[3] = (T)(rb * s1);
+  } else {
+    const double k = 1.0 / 4294967296.0;
+    const double ra = ::sqrt(-2.0 * ::log(((double)r[0] + 1.0) * k));
+    const double rb = ::sqrt(-2.0 * ::log(((double)r[2] + 1.0) * k));
+    double s0, c0d, s1, c1d;
+    sincos(6.283185307179586 * ((double)r[1] * k), &s0, &c0d);
+    sincos(6.283185307179586 * ((double)r[3] * k), &s1, &c1d);
+    z[0] = (T)(ra * c0d); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1d); z[3] = (T)(rb * s1);
+  }
+}
 
 // IDM with the exponent handled at compile time (car_following_models.py:464-482)
 template <typename T, bool kDelta4>
@@ -70,16 +131,29 @@ __device__ __forceinline__ T idm_fast(T v, T v_lead, T h, const IdmRegs<T>& p) {
   return mul(p.a, (T(1) - pw) - mul(sh, sh));
 }
 
+// sum over the threads of one env group. fp32: integer REDUX in 2^-20 fixed
+// point (|v| < 90 m/s per vehicle, V <= 22); fp64: xor-shuffle tree.
+template <typename T, int G>
+__device__ __forceinline__ T env_sum(T part, unsigned gmask) {
+  if (G == 1) return part;
+  if (sizeof(T) == 4) {
+    const int q = __float2int_rn((float)part * 1048576.0f);
+    return (T)((float)__reduce_add_sync(gmask, q) * 9.5367431640625e-07f);
+  }
+  return group_sum(part, gmask, 32 / G);
+}
+
 template <typename T, int VPT, int G, bool kExact, bool kNoise, bool kFS, bool kViews>
 __global__ void __launch_bounds__(128)
-ring1_fast_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const StepArgs<T> A) {
+ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
   constexpr int EPW = 32 / G;
-  constexpr int NQ = (VPT + 3) / 4 + (G > 1 ? 1 : 0);  // Philox calls covering my vehicles
+  constexpr bool kTimeNoise = VPT <= 4;     // 4 normals of a call spread over 4 steps
+  constexpr int NQ = kTimeNoise ? VPT : (VPT + 3) / 4;
   const int lane = threadIdx.x & 31;
   const int g = (G == 1) ? 0 : lane / EPW;
   const int es = (G == 1) ? lane : lane % EPW;
-  const int E = cfg.n_envs, V = cfg.n_veh;
+  const int E = P.n_envs, V = P.n_veh;
   const int e_raw = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * EPW + es;
   const bool valid = e_raw < E && (A.mask == nullptr || A.mask[e_raw < E ? e_raw : 0] != 0);
   if (!__any_sync(0xffffffffu, valid)) return;
@@ -92,32 +166,29 @@ ring1_fast_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const
   const int n_mine = kExact ? VPT : max(0, min(VPT, V - base));
   const int g_next = (base + n_mine >= V) ? 0 : g + 1;
   const int lane_next = g_next * EPW + es;
+  const unsigned my_rl = (P.rl_mask >> base) & ((VPT >= 32) ? 0xffffffffu : ((1u << VPT) - 1u));
 
-  // uniform tables -> registers
-  unsigned rl_mask = 0;
-  int type_a = 0, type_b = 0;
-  for (int i = 0; i < V; ++i) {
-    if (cfg.rl_index[i] >= 0) { rl_mask |= 1u << i; type_b = cfg.type_of[i]; }
-    else type_a = cfg.type_of[i];
-  }
-  const unsigned my_rl = rl_mask >> base;
-  IdmRegs<T> pa;
-  pa.load(cfg.types[type_a]);
-  const T len = cfg.types[type_a].length;
-  const T noise_a = cfg.types[type_a].noise, delay_a = cfg.types[type_a].delay;
-  const int fs_a = cfg.types[type_a].fail_safe;
+  // the thread that owns the observed RL vehicle writes obs / reward / done
+  const int rs = P.n_rl > 0 ? P.rl_veh - (P.rl_veh / VPT) * VPT : 0;
+  const bool is_writer = g == (P.n_rl > 0 ? P.rl_veh / VPT : 0);
+  const bool rl_tail = rs == (kExact ? VPT : max(0, min(VPT, V - (P.rl_veh / VPT) * VPT))) - 1;
+
+  const IdmRegs<T> pa = P.pa;
+  const T len = P.len, dt = P.dt;
+  const T C = B.circ[e];
+  const T crash_thr = P.collision_min_gap ? P.min_gap : T(0);
 
   T x[VPT], v[VPT], h[VPT], acc[kViews ? VPT : 1];
-  const T C = B.circ[e];
-  const T dt = cfg.dt;
   FS_SLOTS(j) {
     const bool ok = kExact || j < n_mine;
     x[j] = ok ? B.pos[(size_t)(base + j) * E + e] : T(0);
     v[j] = ok ? B.vel[(size_t)(base + j) * E + e] : T(0);
     if (kViews) acc[kViews ? j : 0] = T(0);
   }
+  // exchange: first vehicle of the next thread = leader of my last vehicle
+  T x_nf = (G == 1) ? x[0] : shfl(x[0], lane_next, gmask);
+  T v_nf = (G == 1) ? v[0] : shfl(v[0], lane_next, gmask);
   auto update_headways = [&]() {  // k.update: vehicle/traci.py:218-250
-    const T x_nf = (G == 1) ? x[0] : shfl(x[0], lane_next, gmask);
     FS_SLOTS(j) {
       T xl;
       if (j + 1 < VPT) xl = (kExact || j + 1 < n_mine) ? x[j + 1 < VPT ? j + 1 : 0] : x_nf;
@@ -131,170 +202,191 @@ ring1_fast_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const
   const int episode = B.episode[e];
   bool done = A.ignore_done ? false : (B.done[e] != 0);
   bool crash = B.crash[e] != 0;
-  const int t_end = cfg.sims_per_step * (cfg.warmup_steps + cfg.horizon);
-  const long long gid = cfg.env_id_base + e;
+  const long long gid = P.env_id_base + e;
   T reward = B.reward[e];
   const bool have_act = A.actions != nullptr;
-  const bool po = cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
-  const bool accel_env = cfg.env_kind == FS_ENV_ACCEL;
-  const T target = cfg.target_velocity;
-  const T inv_nrl = N::div(T(1), T(cfg.n_rl > 0 ? cfg.n_rl : 1));
+  const bool po = P.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
+  const bool accel_env = P.env_kind == FS_ENV_ACCEL;
+  const int K = A.k_steps;
 
-  int rl_veh = 0;
-  for (int i = 0; i < V; ++i) if (cfg.rl_index[i] == 0) rl_veh = i;
-  const int ld_veh = (rl_veh + 1 < V) ? rl_veh + 1 : 0;
-  const int rl_lane = (rl_veh / VPT) * EPW + es, ld_lane = (ld_veh / VPT) * EPW + es;
-  const int rl_slot = rl_veh % VPT, ld_slot = ld_veh % VPT;
-  const bool rl_is_last = kExact && rl_slot == VPT - 1 && ld_slot == 0;
-  const T obs_len = cfg.obs_max_length > T(0) ? cfg.obs_max_length : C;
-
-  T max_cost = T(0);  // ||[target]*V||, rewards.py:52-53
-  {
-    T mc2 = T(0);
-    const T t2 = mul(target, target);
-    for (int i = 0; i < V; ++i) mc2 = add(mc2, t2);
-    max_cost = N::sqrt(mc2);
+  // action prefetch ring for my first RL vehicle (4 steps ahead)
+  const int rl_first = my_rl ? __ffs(my_rl) - 1 : -1;
+  const bool pf = have_act && rl_first >= 0;
+  const T* act_p = A.actions;
+  size_t act_stride = 0;
+  if (pf) {
+    act_p = A.actions + (size_t)__popc(P.rl_mask & ((1u << (base + rl_first)) - 1u)) * E + e;
+    act_stride = (size_t)P.act_dim * E;
   }
-  double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
+  T ap0 = T(0), ap1 = T(0), ap2 = T(0), ap3 = T(0);
+  if (pf) {
+    if (0 < K) ap0 = __ldg(act_p);
+    if (1 < K) ap1 = __ldg(act_p + act_stride);
+    if (2 < K) ap2 = __ldg(act_p + 2 * act_stride);
+    if (3 < K) ap3 = __ldg(act_p + 3 * act_stride);
+  }
 
-  auto write_obs = [&](T* o, T* ol) {
-    if (po) {  // WaveAttenuationPOEnv.get_state, wave_attenuation.py:248-269
-      T xr, vr, xl, vl;
-      if (rl_is_last) { xr = x[VPT - 1]; vr = v[VPT - 1]; xl = x[0]; vl = v[0]; }
-      else { xr = pick(x, rl_slot); vr = pick(v, rl_slot); xl = pick(x, ld_slot); vl = pick(v, ld_slot); }
-      if (G > 1) {
-        xr = shfl(xr, rl_lane, gmask); vr = shfl(vr, rl_lane, gmask);
-        xl = shfl(xl, ld_lane, gmask); vl = shfl(vl, ld_lane, gmask);
-      }
-      if (g == 0 && valid) {
-        const T o0 = N::div(vr, T(15)), o1 = N::div(vl - vr, T(15));
-        const T o2 = N::div(fwd_dist(xl, xr, C), obs_len);
-        if (o) { o[0] = o0; o[1] = o1; o[2] = o2; }
-        if (ol) { ol[0] = o0; ol[1] = o1; ol[2] = o2; }
-      }
-    } else if (valid) {  // AccelEnv / WaveAttenuationEnv.get_state, accel.py:116-123
-      FS_SLOTS(j) if (kExact || j < n_mine) {
-        const T a0 = N::div(v[j], cfg.speed_limit), a1 = N::div(x[j], C);
-        if (o) { o[base + j] = a0; o[V + base + j] = a1; }
-        if (ol) { ol[base + j] = a0; ol[V + base + j] = a1; }
-      }
+  float st_rew = 0.f, st_v = 0.f, st_v2 = 0.f;
+  int st_adv = 0, st_cr = 0;
+  T zn[kNoise ? NQ : 1][4];
+  bool regen = true;
+
+  auto po_obs = [&](T& o0, T& o1, T& o2) {  // WaveAttenuationPOEnv.get_state, wave_attenuation.py:248-269
+    T xr, vr, xl, vl;
+    if (rl_tail) {
+      xr = kExact ? x[VPT - 1] : pick(x, rs); vr = kExact ? v[VPT - 1] : pick(v, rs);
+      xl = x_nf; vl = v_nf;
+    } else {
+      xr = pick(x, rs); vr = pick(v, rs);
+      xl = pick(x, rs + 1 < VPT ? rs + 1 : 0); vl = pick(v, rs + 1 < VPT ? rs + 1 : 0);
+    }
+    o0 = N::div(vr, T(15)); o1 = N::div(vl - vr, T(15));
+    o2 = N::div(fwd_dist(xl, xr, C), P.obs_max_length > T(0) ? P.obs_max_length : C);
+  };
+  auto full_obs = [&](T* o) {  // AccelEnv / WaveAttenuationEnv.get_state, accel.py:116-123
+    FS_SLOTS(j) if (kExact || j < n_mine) {
+      o[base + j] = N::div(v[j], P.speed_limit);
+      o[V + base + j] = N::div(x[j], C);
     }
   };
-  if (A.k_steps == 0) write_obs(nullptr, B.obs + (size_t)e * cfg.obs_dim);
 
-  for (int k = 0; k < A.k_steps; ++k) {
+  T* obs_k = A.obs_seq ? A.obs_seq + (size_t)e * P.obs_dim : nullptr;
+  T* rew_k = A.reward_seq ? A.reward_seq + e : nullptr;
+  uint8_t* done_k = A.done_seq ? A.done_seq + e : nullptr;
+  const size_t obs_stride = (size_t)E * P.obs_dim;
+
+  for (int k = 0; k < K; ++k) {
+    // rotate the action ring; fetch step k+4
+    const T a_cur = ap0;
+    ap0 = ap1; ap1 = ap2; ap2 = ap3;
+    if (pf && k + 4 < K) ap3 = __ldg(act_p + (size_t)(k + 4) * act_stride);
     if (!done) {
-      const T v_nf = (G == 1) ? v[0] : shfl(v[0], lane_next, gmask);
-      T zn[NQ][4];
       if (kNoise) {
+        if (kTimeNoise) {
+          if (regen || (tc & 3) == 0) {
 #pragma unroll
-        for (int q = 0; q < NQ; ++q)
-          normal4<T>(cfg.seed, gid, (base >> 2) + q, tc + episode * 1000003, zn[q]);
+            for (int q = 0; q < NQ; ++q)
+              normal4<T>(P.seed, gid, (uint32_t)(tc >> 2), (uint32_t)(episode * 256 + base + q), zn[q]);
+            regen = false;
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < NQ; ++q)
+            normal4<T>(P.seed, gid, (uint32_t)tc,
+                       0x80000000u | (uint32_t)(episode * 256 + base + 4 * q), zn[q]);
+        }
       }
+      const int zc = tc & 3;
       T act_abs_sum = T(0);
+      const T v_lead_last = v_nf;  // leader speed (old state) of my last vehicle
       FS_SLOTS(j) {
         const bool ok = kExact || j < n_mine;
         const T vi = v[j], hi = h[j];
         T vl;
-        if (j + 1 < VPT) vl = (kExact || j + 1 < n_mine) ? v[j + 1 < VPT ? j + 1 : 0] : v_nf;
-        else vl = v_nf;
+        if (j + 1 < VPT) vl = (kExact || j + 1 < n_mine) ? v[j + 1 < VPT ? j + 1 : 0] : v_lead_last;
+        else vl = v_lead_last;
         T a;
         if ((my_rl >> j) & 1u) {
-          const int i = base + j;
           if (have_act) {
             // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
-            const T raw = A.actions[((size_t)k * cfg.act_dim + cfg.rl_index[i]) * E + e];
-            a = N::min(N::max(raw, cfg.act_lo), cfg.act_hi);
-            act_abs_sum = add(act_abs_sum, N::abs(cfg.clip_actions ? a : raw));
+            T raw;
+            if (j == rl_first) raw = a_cur;
+            else raw = A.actions[((size_t)k * P.act_dim +
+                                  __popc(P.rl_mask & ((1u << (base + j)) - 1u))) * E + e];
+            a = N::min(N::max(raw, P.act_lo), P.act_hi);
+            act_abs_sum = add(act_abs_sum, N::abs(P.clip_actions ? a : raw));
           } else {
-            IdmRegs<T> pb;  // restated simulator default model for the un-commanded RL vehicle
-            pb.load(cfg.types[type_b]);
-            a = idm_fast<T, true>(vi, vl, hi, pb);
+            // restated simulator default model for the un-commanded RL vehicle
+            a = idm_fast<T, true>(vi, vl, hi, P.pb);
           }
         } else {
           a = idm_fast<T, true>(vi, vl, hi, pa);
           if (kNoise) {  // base_controller.py:109-110
-            const int off = (G == 1) ? j : (base & 3) + j;
             T z;
-            if (G == 1) z = zn[j >> 2][j & 3];
-            else {
-              const int qq = off >> 2, cc = off & 3;
-              z = T(0);
-#pragma unroll
-              for (int q = 0; q < NQ; ++q)
-#pragma unroll
-                for (int c = 0; c < 4; ++c) z = (q == qq && c == cc) ? zn[q][c] : z;
+            if (kTimeNoise) {
+              const T* q = zn[kNoise ? j : 0];
+              z = zc == 0 ? q[0] : (zc == 1 ? q[1] : (zc == 2 ? q[2] : q[3]));
+            } else {
+              z = zn[kNoise ? (j >> 2) : 0][j & 3];
             }
-            a = add(a, mul(noise_a, z));
+            a = add(a, mul(P.noise, z));
           }
           if (kFS) {  // base_controller.py:113-116
-            if (fs_a == FS_FAILSAFE_INSTANTANEOUS)
+            if (P.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
               a = failsafe_instantaneous<T>(a, vi, hi, true, V, dt);
-            else if (fs_a == FS_FAILSAFE_SAFE_VELOCITY)
-              a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, delay_a);
+            else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
+              a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, P.delay);
           }
         }
         const T vn = N::max(add(vi, mul(a, dt)), T(0));   // vehicle/traci.py:961-962
         const T xn = wrap_fwd(add(x[j], mul(vn, dt)), C);  // simulator Euler move
         if (ok) { v[j] = vn; x[j] = xn; if (kViews) acc[kViews ? j : 0] = a; }
       }
+      if (G > 1) { x_nf = shfl(x[0], lane_next, gmask); v_nf = shfl(v[0], lane_next, gmask); }
+      else { x_nf = x[0]; v_nf = v[0]; }
       update_headways();
       bool cr = false;
-      T sv = T(0), sq = T(0), s2 = T(0);
+      T sv = T(0), sq = T(0);
+      float s2 = 0.f;
       FS_SLOTS(j) if (kExact || j < n_mine) {
-        cr |= cfg.collision_min_gap ? (h[j] < cfg.types[type_a].sim_min_gap) : (h[j] < T(0));
+        cr |= h[j] < crash_thr;
         sv = add(sv, v[j]);
-        if (accel_env) { const T d = v[j] - target; sq = add(sq, mul(d, d)); }
-        if (A.accumulate_stats) s2 += v[j] * v[j];
+        if (accel_env) { const T d = v[j] - P.target; sq = add(sq, mul(d, d)); }
+        if (A.accumulate_stats) s2 = fmaf((float)v[j], (float)v[j], s2);
       }
-      if (G > 1) {
-        sv = group_sum(sv, gmask, EPW);
-        if (accel_env) sq = group_sum(sq, gmask, EPW);
-        act_abs_sum = group_sum(act_abs_sum, gmask, EPW);
-        cr = group_sum((int)cr, gmask, EPW) != 0;
-        if (A.accumulate_stats) s2 = group_sum(s2, gmask, EPW);
-      }
+      if (A.accumulate_stats && valid) { st_v += (float)sv; st_v2 += s2; st_adv += 1; }
+      if (G > 1) cr = __any_sync(gmask, cr);
       crash = cr;
       tc += 1;
-      done = crash || tc >= t_end;
+      done = crash || tc >= P.t_end;
       if (accel_env) {  // rewards.desired_velocity, flow/core/rewards.py:6-59
+        if (G > 1) sq = group_sum(sq, gmask, EPW);
         if (crash) reward = T(0);
         else {
           const T cost = N::sqrt(sq);
           const T eps = T(1.1920928955078125e-07);
-          reward = N::div(N::max(max_cost - cost, T(0)), add(max_cost, eps));
+          reward = N::div(N::max(P.max_cost - cost, T(0)), add(P.max_cost, eps));
         }
       } else {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
+        if (have_act) {
+          sv = env_sum<T, G>(sv, gmask);
+          if (G > 1 && P.n_rl > 1) act_abs_sum = group_sum(act_abs_sum, gmask, EPW);
+        }
         if (!have_act || crash) reward = T(0);
         else {
-          reward = N::div(mul(T(4), N::div(sv, T(V))), T(20));
-          const T mean_act = mul(act_abs_sum, inv_nrl);
+          reward = N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
+          const T mean_act = mul(act_abs_sum, P.inv_nrl);
           if (mean_act > T(0)) reward = add(reward, mul(T(4), T(0) - mean_act));
         }
       }
-      if (A.accumulate_stats && valid && g == 0) {
-        st_rew += (double)reward; st_v += (double)sv; st_v2 += (double)s2;
-        st_vs += V; st_es += 1; st_cr += crash ? 1 : 0;
-      }
+      if (A.accumulate_stats && valid && is_writer) { st_rew += (float)reward; st_cr += crash ? 1 : 0; }
     } else {
       reward = T(0);
     }
-    const bool last = (k == A.k_steps - 1);
-    if (A.obs_seq != nullptr || last)
-      write_obs(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
-                last ? B.obs + (size_t)e * cfg.obs_dim : nullptr);
-    if (g == 0 && valid) {
-      if (A.reward_seq) A.reward_seq[(size_t)k * E + e] = reward;
-      if (A.done_seq) A.done_seq[(size_t)k * E + e] = done ? 1 : 0;
+    if (valid) {
+      if (obs_k) {
+        if (po) {
+          if (is_writer) { T o0, o1, o2; po_obs(o0, o1, o2); obs_k[0] = o0; obs_k[1] = o1; obs_k[2] = o2; }
+        } else full_obs(obs_k);
+        obs_k += obs_stride;
+      }
+      if (is_writer) {
+        if (rew_k) { *rew_k = reward; rew_k += E; }
+        if (done_k) { *done_k = done ? 1 : 0; done_k += E; }
+      }
     }
   }
 
   if (valid) {
+    T* ol = B.obs + (size_t)e * P.obs_dim;
+    if (po) {
+      if (is_writer) { T o0, o1, o2; po_obs(o0, o1, o2); ol[0] = o0; ol[1] = o1; ol[2] = o2; }
+    } else full_obs(ol);
     FS_SLOTS(j) if (kExact || j < n_mine) {
       B.pos[(size_t)(base + j) * E + e] = x[j];
       B.vel[(size_t)(base + j) * E + e] = v[j];
     }
-    if (g == 0) {
+    if (is_writer) {
       B.time_counter[e] = tc;
       B.done[e] = done ? 1 : 0;
       B.crash[e] = crash ? 1 : 0;
@@ -307,12 +399,14 @@ ring1_fast_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const
         B.v_headway[o] = h[j];
         B.v_leader[o] = (i + 1 < V) ? i + 1 : 0;
         B.v_follower[o] = (i > 0) ? i - 1 : V - 1;
-        if (A.k_steps > 0) B.v_accel[o] = acc[kViews ? j : 0];
+        if (K > 0) B.v_accel[o] = acc[kViews ? j : 0];
       }
     }
   }
   if (A.accumulate_stats) {
-    double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
+    // stats[]: sum reward, sum v, sum v^2, vehicle-steps, env-steps, crashes
+    double vals[6] = {(double)st_rew, (double)st_v, (double)st_v2, (double)(st_adv * n_mine),
+                      is_writer ? (double)st_adv : 0.0, (double)st_cr};
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       double s = vals[q];
@@ -322,11 +416,10 @@ ring1_fast_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const
   }
 }
 
-
 // ---- host-side dispatch (one translation unit per dtype instantiates these)
 template <typename T, int VPT, int G, bool kExact>
 static cudaError_t launch_fast_shape(int variant, int grid, int block, cudaStream_t st,
-                                     const Cfg<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
+                                     const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
   switch (variant) {
     case 0: ring1_fast_kernel<T, VPT, G, kExact, false, false, false><<<grid, block, 0, st>>>(c, b, a); break;
     case 1: ring1_fast_kernel<T, VPT, G, kExact, true, false, false><<<grid, block, 0, st>>>(c, b, a); break;
@@ -336,11 +429,11 @@ static cudaError_t launch_fast_shape(int variant, int grid, int block, cudaStrea
   return cudaGetLastError();
 }
 
-// shape = threads per env (1, 2, 4, 8) for V = 22; variant: 0 plain, 1 noise,
-// 2 noise + fail-safe, 3 = 2 + views (accel / headway / leader / follower)
+// shape = threads per env (1, 2, 4, 8, 16, 32) for V = 22; variant: 0 plain,
+// 1 noise, 2 noise + fail-safe, 3 = 2 + views (accel / headway / leader / follower)
 template <typename T>
 static cudaError_t launch_fast22(int shape, int variant, int n_envs, cudaStream_t st,
-                                 const Cfg<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
+                                 const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
   const int epw = 32 / shape;
   const int warps = (n_envs + epw - 1) / epw;
   // spread small batches over all 148 SMs with one-warp blocks; fatter blocks
@@ -351,7 +444,9 @@ static cudaError_t launch_fast22(int shape, int variant, int n_envs, cudaStream_
     case 1: return launch_fast_shape<T, 22, 1, true>(variant, grid, block, st, c, b, a);
     case 2: return launch_fast_shape<T, 11, 2, true>(variant, grid, block, st, c, b, a);
     case 4: return launch_fast_shape<T, 6, 4, false>(variant, grid, block, st, c, b, a);
-    default: return launch_fast_shape<T, 3, 8, false>(variant, grid, block, st, c, b, a);
+    case 8: return launch_fast_shape<T, 3, 8, false>(variant, grid, block, st, c, b, a);
+    case 16: return launch_fast_shape<T, 2, 16, false>(variant, grid, block, st, c, b, a);
+    default: return launch_fast_shape<T, 1, 32, false>(variant, grid, block, st, c, b, a);
   }
 }
 

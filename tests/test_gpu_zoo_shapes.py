@@ -22,7 +22,7 @@ def close(a, b, floor=1.0):
     return float((np.abs(a - b) / np.maximum(np.abs(b), floor)).max())
 
 
-@pytest.mark.parametrize('shape', [1, 2, 4, 8])
+@pytest.mark.parametrize('shape', [1, 2, 4, 8, 16, 32])
 def test_c2_golden_every_shape_fp64(shape, monkeypatch):
     """ring_c2.npz (reference-generated) through each (VPT, G) instantiation."""
     import torch
