@@ -91,6 +91,7 @@ SYMBOLS = [
 ]
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
+              '-ftz=true', '-prec-sqrt=false',  # fp32 mode only (tolerance 1e-4); fp64 is untouched
               '-std=c++17', '-Xcompiler', '-fPIC']
 
 

@@ -20,8 +20,8 @@
 //   * noise: Philox4x32-10 + Box-Muller gives 4 normals per call; a vehicle
 //     consumes them over 4 CONSECUTIVE steps (counter = step/4, component =
 //     step%4), so the cost is 1/4 call per vehicle-step for every shape;
-//   * RL actions are prefetched 4 steps ahead (the only global load in the
-//     loop would otherwise sit on the step's critical path);
+//   * RL actions are prefetched in blocks of 4 steps, one block ahead (the only
+//     global load in the loop would otherwise sit on the step's critical path);
 //   * delta == 4, noise, fail-safes, views and kExact (V == VPT*G) are
 //     template flags.
 // Reference lines restated: see fs_ring.cuh header (same step semantics).
@@ -51,6 +51,9 @@ struct FastP {
   unsigned long long seed;
   T dt, len, noise, delay, min_gap, target, act_lo, act_hi;
   T obs_max_length, speed_limit, max_cost, inv_nrl, n_veh_t;
+  T rew_scale;        // 4 / (20 V): WaveAttenuation reward per unit of summed speed (fp32 path)
+  T inv_obs_len;      // 1 / obs_max_length, 0 when the ring's own length normalises
+  T inv_speed_limit;
   IdmRegs<T> pa, pb;  // human type / un-commanded RL type (simulator default model)
 };
 
@@ -81,6 +84,9 @@ static inline FastP<T> make_fastp(const Cfg<T>& c) {
   }
   p.inv_nrl = T(1) / T(c.n_rl > 0 ? c.n_rl : 1);
   p.n_veh_t = T(c.n_veh);
+  p.rew_scale = T(4) / (T(20) * T(c.n_veh));
+  p.inv_obs_len = c.obs_max_length > T(0) ? T(1) / c.obs_max_length : T(0);
+  p.inv_speed_limit = T(1) / c.speed_limit;
   p.pa.load(c.types[ta]); p.pb.load(c.types[tb]);
   return p;
 }
@@ -143,11 +149,13 @@ __device__ __forceinline__ T env_sum(T part, unsigned gmask) {
   return group_sum(part, gmask, 32 / G);
 }
 
+
 template <typename T, int VPT, int G, bool kExact, bool kNoise, bool kFS, bool kViews>
 __global__ void __launch_bounds__(128)
 ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
   constexpr int EPW = 32 / G;
+  constexpr bool kF32 = sizeof(T) == 4;
   constexpr bool kTimeNoise = VPT <= 4;     // 4 normals of a call spread over 4 steps
   constexpr int NQ = kTimeNoise ? VPT : (VPT + 3) / 4;
   const int lane = threadIdx.x & 31;
@@ -169,14 +177,27 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
   const unsigned my_rl = (P.rl_mask >> base) & ((VPT >= 32) ? 0xffffffffu : ((1u << VPT) - 1u));
 
   // the thread that owns the observed RL vehicle writes obs / reward / done
-  const int rs = P.n_rl > 0 ? P.rl_veh - (P.rl_veh / VPT) * VPT : 0;
-  const bool is_writer = g == (P.n_rl > 0 ? P.rl_veh / VPT : 0);
-  const bool rl_tail = rs == (kExact ? VPT : max(0, min(VPT, V - (P.rl_veh / VPT) * VPT))) - 1;
+  const int wbase = P.n_rl > 0 ? (P.rl_veh / VPT) * VPT : 0;
+  const int rs = P.n_rl > 0 ? P.rl_veh - wbase : 0;
+  const bool is_writer = base == wbase;
+  const bool rl_tail = rs == (kExact ? VPT : max(0, min(VPT, V - wbase))) - 1;
 
-  const IdmRegs<T> pa = P.pa;
+  const bool have_act = A.actions != nullptr;
+  const bool po = P.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
+  const bool accel_env = P.env_kind == FS_ENV_ACCEL;
+  const int K = A.k_steps;
+
+  // IDM block of my vehicles. One vehicle per thread: picked once (an
+  // un-commanded RL vehicle follows the restated simulator default model).
+  IdmRegs<T> pm = P.pa;
+  T noise_m = P.noise;
+  if (VPT == 1 && (my_rl & 1u)) { pm = P.pb; noise_m = T(0); }
   const T len = P.len, dt = P.dt;
   const T C = B.circ[e];
   const T crash_thr = P.collision_min_gap ? P.min_gap : T(0);
+  const T inv_obs_len = P.inv_obs_len > T(0) ? P.inv_obs_len : T(1) / C;
+  const T obs_len = P.obs_max_length > T(0) ? P.obs_max_length : C;
+  const T inv_C = T(1) / C;
 
   T x[VPT], v[VPT], h[VPT], acc[kViews ? VPT : 1];
   FS_SLOTS(j) {
@@ -204,12 +225,8 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
   bool crash = B.crash[e] != 0;
   const long long gid = P.env_id_base + e;
   T reward = B.reward[e];
-  const bool have_act = A.actions != nullptr;
-  const bool po = P.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
-  const bool accel_env = P.env_kind == FS_ENV_ACCEL;
-  const int K = A.k_steps;
 
-  // action prefetch ring for my first RL vehicle (4 steps ahead)
+  // RL actions of my first RL vehicle: blocks of 4 steps, fetched one block ahead
   const int rl_first = my_rl ? __ffs(my_rl) - 1 : -1;
   const bool pf = have_act && rl_first >= 0;
   const T* act_p = A.actions;
@@ -218,18 +235,19 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
     act_p = A.actions + (size_t)__popc(P.rl_mask & ((1u << (base + rl_first)) - 1u)) * E + e;
     act_stride = (size_t)P.act_dim * E;
   }
-  T ap0 = T(0), ap1 = T(0), ap2 = T(0), ap3 = T(0);
+  T ac0 = T(0), ac1 = T(0), ac2 = T(0), ac3 = T(0);
+  T an0 = T(0), an1 = T(0), an2 = T(0), an3 = T(0);
   if (pf) {
-    if (0 < K) ap0 = __ldg(act_p);
-    if (1 < K) ap1 = __ldg(act_p + act_stride);
-    if (2 < K) ap2 = __ldg(act_p + 2 * act_stride);
-    if (3 < K) ap3 = __ldg(act_p + 3 * act_stride);
+    if (0 < K) an0 = __ldg(act_p);
+    if (1 < K) an1 = __ldg(act_p + act_stride);
+    if (2 < K) an2 = __ldg(act_p + 2 * act_stride);
+    if (3 < K) an3 = __ldg(act_p + 3 * act_stride);
   }
 
   float st_rew = 0.f, st_v = 0.f, st_v2 = 0.f;
   int st_adv = 0, st_cr = 0;
   T zn[kNoise ? NQ : 1][4];
-  bool regen = true;
+  int zleft = 0;
 
   auto po_obs = [&](T& o0, T& o1, T& o2) {  // WaveAttenuationPOEnv.get_state, wave_attenuation.py:248-269
     T xr, vr, xl, vl;
@@ -241,83 +259,102 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
       xl = pick(x, rs + 1 < VPT ? rs + 1 : 0); vl = pick(v, rs + 1 < VPT ? rs + 1 : 0);
     }
     o0 = N::div(vr, T(15)); o1 = N::div(vl - vr, T(15));
-    o2 = N::div(fwd_dist(xl, xr, C), P.obs_max_length > T(0) ? P.obs_max_length : C);
+    o2 = kF32 ? fwd_dist(xl, xr, C) * inv_obs_len : N::div(fwd_dist(xl, xr, C), obs_len);
   };
   auto full_obs = [&](T* o) {  // AccelEnv / WaveAttenuationEnv.get_state, accel.py:116-123
     FS_SLOTS(j) if (kExact || j < n_mine) {
-      o[base + j] = N::div(v[j], P.speed_limit);
-      o[V + base + j] = N::div(x[j], C);
+      o[base + j] = kF32 ? v[j] * P.inv_speed_limit : N::div(v[j], P.speed_limit);
+      o[V + base + j] = kF32 ? x[j] * inv_C : N::div(x[j], C);
     }
   };
 
-  T* obs_k = A.obs_seq ? A.obs_seq + (size_t)e * P.obs_dim : nullptr;
-  T* rew_k = A.reward_seq ? A.reward_seq + e : nullptr;
-  uint8_t* done_k = A.done_seq ? A.done_seq + e : nullptr;
+  // per-step output cursors (null = not requested / not mine)
+  const bool w_obs = valid && A.obs_seq != nullptr && (!po || is_writer);
+  const bool w_rew = valid && is_writer && A.reward_seq != nullptr;
+  const bool w_done = valid && is_writer && A.done_seq != nullptr;
+  T* obs_k = A.obs_seq + (w_obs ? (size_t)e * P.obs_dim : 0);
+  T* rew_k = A.reward_seq + (w_rew ? e : 0);
+  uint8_t* done_k = A.done_seq + (w_done ? e : 0);
   const size_t obs_stride = (size_t)E * P.obs_dim;
+  const bool st_on = A.accumulate_stats && valid;
 
   for (int k = 0; k < K; ++k) {
-    // rotate the action ring; fetch step k+4
-    const T a_cur = ap0;
-    ap0 = ap1; ap1 = ap2; ap2 = ap3;
-    if (pf && k + 4 < K) ap3 = __ldg(act_p + (size_t)(k + 4) * act_stride);
+    // ---- RL action of this step (block of 4 promoted every 4th step; next block requested)
+    T a_cur = T(0);
+    if (have_act) {
+      if ((k & 3) == 0) {
+        ac0 = an0; ac1 = an1; ac2 = an2; ac3 = an3;
+        if (pf) {
+          const T* q = act_p + (size_t)(k + 4) * act_stride;
+          if (k + 4 < K) an0 = __ldg(q);
+          if (k + 5 < K) an1 = __ldg(q + act_stride);
+          if (k + 6 < K) an2 = __ldg(q + 2 * act_stride);
+          if (k + 7 < K) an3 = __ldg(q + 3 * act_stride);
+        }
+      }
+      a_cur = ac0; ac0 = ac1; ac1 = ac2; ac2 = ac3;
+    }
     if (!done) {
+      // ---- noise of this step (base_controller.py:109-110)
+      T zs[kNoise ? VPT : 1];
       if (kNoise) {
         if (kTimeNoise) {
-          if (regen || (tc & 3) == 0) {
+          if (zleft == 0) {
 #pragma unroll
             for (int q = 0; q < NQ; ++q)
               normal4<T>(P.seed, gid, (uint32_t)(tc >> 2), (uint32_t)(episode * 256 + base + q), zn[q]);
-            regen = false;
+            int sk = tc & 3;   // launch started inside a 4-step block: drop the used components
+            zleft = 4 - sk;
+            while (sk-- > 0) {
+#pragma unroll
+              for (int q = 0; q < NQ; ++q) { zn[q][0] = zn[q][1]; zn[q][1] = zn[q][2]; zn[q][2] = zn[q][3]; }
+            }
+          }
+          --zleft;
+#pragma unroll
+          for (int q = 0; q < NQ; ++q) {
+            zs[kNoise ? q : 0] = zn[q][0];
+            zn[q][0] = zn[q][1]; zn[q][1] = zn[q][2]; zn[q][2] = zn[q][3];
           }
         } else {
 #pragma unroll
           for (int q = 0; q < NQ; ++q)
             normal4<T>(P.seed, gid, (uint32_t)tc,
                        0x80000000u | (uint32_t)(episode * 256 + base + 4 * q), zn[q]);
+          FS_SLOTS(j) zs[kNoise ? j : 0] = zn[kNoise ? (j >> 2) : 0][j & 3];
         }
       }
-      const int zc = tc & 3;
+      // ---- controllers -> apply_acceleration -> Euler move (all read the old state)
       T act_abs_sum = T(0);
       const T v_lead_last = v_nf;  // leader speed (old state) of my last vehicle
       FS_SLOTS(j) {
         const bool ok = kExact || j < n_mine;
+        const bool rlj = (my_rl >> j) & 1u;
         const T vi = v[j], hi = h[j];
         T vl;
         if (j + 1 < VPT) vl = (kExact || j + 1 < n_mine) ? v[j + 1 < VPT ? j + 1 : 0] : v_lead_last;
         else vl = v_lead_last;
-        T a;
-        if ((my_rl >> j) & 1u) {
-          if (have_act) {
-            // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
-            T raw;
-            if (j == rl_first) raw = a_cur;
-            else raw = A.actions[((size_t)k * P.act_dim +
-                                  __popc(P.rl_mask & ((1u << (base + j)) - 1u))) * E + e];
-            a = N::min(N::max(raw, P.act_lo), P.act_hi);
-            act_abs_sum = add(act_abs_sum, N::abs(P.clip_actions ? a : raw));
-          } else {
-            // restated simulator default model for the un-commanded RL vehicle
-            a = idm_fast<T, true>(vi, vl, hi, P.pb);
-          }
-        } else {
-          a = idm_fast<T, true>(vi, vl, hi, pa);
-          if (kNoise) {  // base_controller.py:109-110
-            T z;
-            if (kTimeNoise) {
-              const T* q = zn[kNoise ? j : 0];
-              z = zc == 0 ? q[0] : (zc == 1 ? q[1] : (zc == 2 ? q[2] : q[3]));
-            } else {
-              z = zn[kNoise ? (j >> 2) : 0][j & 3];
-            }
-            a = add(a, mul(P.noise, z));
-          }
-          if (kFS) {  // base_controller.py:113-116
-            if (P.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
-              a = failsafe_instantaneous<T>(a, vi, hi, true, V, dt);
-            else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
-              a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, P.delay);
-          }
+        T a = idm_fast<T, true>(vi, vl, hi, pm);
+        T a_rl = a;
+        if (VPT > 1 && rlj && !have_act) a_rl = idm_fast<T, true>(vi, vl, hi, P.pb);
+        if (kNoise) a = add(a, mul(VPT == 1 ? noise_m : P.noise, zs[kNoise ? j : 0]));
+        if (kFS) {  // base_controller.py:113-116
+          if (P.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
+            a = failsafe_instantaneous<T>(a, vi, hi, true, V, dt);
+          else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
+            a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, P.delay);
         }
+        if (have_act) {
+          // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
+          T raw = a_cur;
+          if (VPT > 1 && rlj && j != rl_first)
+            raw = A.actions[((size_t)k * P.act_dim +
+                             __popc(P.rl_mask & ((1u << (base + j)) - 1u))) * E + e];
+          a_rl = N::min(N::max(raw, P.act_lo), P.act_hi);
+          const T aa = N::abs(P.clip_actions ? a_rl : raw);
+          act_abs_sum = rlj ? add(act_abs_sum, aa) : act_abs_sum;
+        }
+        a = rlj ? a_rl : a;
         const T vn = N::max(add(vi, mul(a, dt)), T(0));   // vehicle/traci.py:961-962
         const T xn = wrap_fwd(add(x[j], mul(vn, dt)), C);  // simulator Euler move
         if (ok) { v[j] = vn; x[j] = xn; if (kViews) acc[kViews ? j : 0] = a; }
@@ -332,49 +369,40 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
         cr |= h[j] < crash_thr;
         sv = add(sv, v[j]);
         if (accel_env) { const T d = v[j] - P.target; sq = add(sq, mul(d, d)); }
-        if (A.accumulate_stats) s2 = fmaf((float)v[j], (float)v[j], s2);
+        if (st_on) s2 = fmaf((float)v[j], (float)v[j], s2);
       }
-      if (A.accumulate_stats && valid) { st_v += (float)sv; st_v2 += s2; st_adv += 1; }
+      if (st_on) { st_v += (float)sv; st_v2 += s2; st_adv += 1; }
       if (G > 1) cr = __any_sync(gmask, cr);
       crash = cr;
       tc += 1;
       done = crash || tc >= P.t_end;
       if (accel_env) {  // rewards.desired_velocity, flow/core/rewards.py:6-59
         if (G > 1) sq = group_sum(sq, gmask, EPW);
-        if (crash) reward = T(0);
-        else {
-          const T cost = N::sqrt(sq);
-          const T eps = T(1.1920928955078125e-07);
-          reward = N::div(N::max(P.max_cost - cost, T(0)), add(P.max_cost, eps));
-        }
-      } else {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
-        if (have_act) {
-          sv = env_sum<T, G>(sv, gmask);
-          if (G > 1 && P.n_rl > 1) act_abs_sum = group_sum(act_abs_sum, gmask, EPW);
-        }
-        if (!have_act || crash) reward = T(0);
-        else {
-          reward = N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
-          const T mean_act = mul(act_abs_sum, P.inv_nrl);
-          if (mean_act > T(0)) reward = add(reward, mul(T(4), T(0) - mean_act));
-        }
+        const T cost = N::sqrt(sq);
+        const T eps = T(1.1920928955078125e-07);
+        reward = crash ? T(0) : N::div(N::max(P.max_cost - cost, T(0)), add(P.max_cost, eps));
+      } else if (have_act) {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
+        sv = env_sum<T, G>(sv, gmask);
+        if (G > 1 && P.n_rl > 1) act_abs_sum = group_sum(act_abs_sum, gmask, EPW);
+        T r = kF32 ? sv * P.rew_scale : N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
+        const T mean_act = mul(act_abs_sum, P.inv_nrl);
+        if (mean_act > T(0)) r = add(r, mul(T(4), T(0) - mean_act));
+        reward = crash ? T(0) : r;
+      } else {
+        reward = T(0);
       }
-      if (A.accumulate_stats && valid && is_writer) { st_rew += (float)reward; st_cr += crash ? 1 : 0; }
+      if (st_on && is_writer) { st_rew += (float)reward; st_cr += crash ? 1 : 0; }
     } else {
       reward = T(0);
     }
-    if (valid) {
-      if (obs_k) {
-        if (po) {
-          if (is_writer) { T o0, o1, o2; po_obs(o0, o1, o2); obs_k[0] = o0; obs_k[1] = o1; obs_k[2] = o2; }
-        } else full_obs(obs_k);
-        obs_k += obs_stride;
-      }
-      if (is_writer) {
-        if (rew_k) { *rew_k = reward; rew_k += E; }
-        if (done_k) { *done_k = done ? 1 : 0; done_k += E; }
-      }
+    // ---- per-step outputs
+    if (w_obs) {
+      if (po) { T o0, o1, o2; po_obs(o0, o1, o2); obs_k[0] = o0; obs_k[1] = o1; obs_k[2] = o2; }
+      else full_obs(obs_k);
+      obs_k += obs_stride;
     }
+    if (w_rew) { *rew_k = reward; rew_k += E; }
+    if (w_done) { *done_k = done ? 1 : 0; done_k += E; }
   }
 
   if (valid) {

@@ -9,3 +9,9 @@ for sh in ${C2_SHAPES:-8 16 32 4}; do FS_RING_SHAPE=$sh python bench.py --steps 
 for sh in ${C5_SHAPES:-1 2 4 8 16 32}; do FS_RING_SHAPE=$sh python bench.py --workload c5 --steps 300 --warmup 100 --no-cpu-baseline > gpurun_out/c5_shape$sh.json 2>gpurun_out/c5_shape$sh.err && show gpurun_out/c5_shape$sh.json "c5 shape $sh"; done
 FS_RING_SHAPE=32 python bench.py --steps 1000 --warmup 100 --no-cpu-baseline --noise 0 > gpurun_out/c2_shape32_nonoise.json 2>/dev/null && show gpurun_out/c2_shape32_nonoise.json "c2 shape 32 noise0"
 FS_RING_SHAPE=8 python bench.py --workload c5 --steps 300 --warmup 100 --no-cpu-baseline --noise 0 > gpurun_out/c5_shape8_nonoise.json 2>/dev/null && show gpurun_out/c5_shape8_nonoise.json "c5 shape 8 noise0"
+if [ -n "$NCU" ]; then
+FS_RING_SHAPE=32 python bench.py --steps 200 --warmup 100 --no-cpu-baseline > gpurun_out/plain_c2.log 2>&1 &&
+FS_RING_SHAPE=32 ncu --set full --clock-control none --import-source on -k regex:ring1_fast -s 4 -c 2 -o gpurun_out/prof_c2_g32 python bench.py --steps 200 --warmup 100 --no-cpu-baseline > gpurun_out/ncu_c2.log 2>&1
+FS_RING_SHAPE=8 python bench.py --workload c5 --steps 200 --warmup 100 --no-cpu-baseline > gpurun_out/plain_c5.log 2>&1 &&
+FS_RING_SHAPE=8 ncu --set full --clock-control none --import-source on -k regex:ring1_fast -s 4 -c 2 -o gpurun_out/prof_c5_g8 python bench.py --workload c5 --steps 200 --warmup 100 --no-cpu-baseline > gpurun_out/ncu_c5.log 2>&1
+fi
