@@ -98,30 +98,72 @@ def cpu_baseline(steps_per_env, envs_per_core, cores=None):
                        'of the reference loop), %d worker processes' % (len(jobs), steps_per_env, cores))
 
 
+_REF_ENV = {}
+
+
+def _ref_init(seed_base):
+    """Pool initializer of the reference arm: one persistent env per worker."""
+    import numpy as np
+    from oracle import sim as OS
+    from oracle import controllers as OC
+    rng = np.random.default_rng(seed_base + os.getpid())
+    types = [OC.VType(OC.IDM, OC.idm_params(), sim_min_gap=0.0), OC.VType(OC.RL)]
+    length = int(rng.integers(220, 271))
+    _REF_ENV['env'] = OS.RingSim(types, [0] * 21 + [1], length, bunching=50.0,
+                                 env_kind=OS.ENV_WAVE_ATTENUATION_PO, warmup_steps=0,
+                                 horizon=10 ** 9, act_lo=-1, act_hi=1, obs_max_length=270.0)
+    _REF_ENV['rng'], _REF_ENV['length'] = rng, length
+
+
+def _ref_advance(n):
+    """Advance this worker's env by n Env.steps; returns seconds spent stepping."""
+    env, rng, length = _REF_ENV['env'], _REF_ENV['rng'], _REF_ENV['length']
+    acts = rng.uniform(-1, 1, size=n)
+    t0 = time.perf_counter()
+    for k in range(n):
+        _, _, done = env.step([acts[k]])
+        if done:
+            env.reset(length, run_warmup=False)
+    return time.perf_counter() - t0
+
+
 def run_reference(a):
+    """CPU arm: the oracle port of the reference loop on ALL host cores, one env
+    per worker process (how RLlib runs the reference). One "step" of this arm is
+    a bounded sample: every core advances its env by `chunk` Env.steps, with
+    `chunk` calibrated so that the whole --steps/--warmup run takes about a
+    minute of wall clock whatever K and W are."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    t_all = []
-    base = None
-    for i in range(a.warmup + a.steps):
-        # each "step" of the reference arm = a bounded sample: every core
-        # advances one env by 3000 Env.steps
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    ctx = mp.get_context('spawn')
+    with ctx.Pool(cores, initializer=_ref_init, initargs=(977,)) as pool:
+        cal = pool.map(_ref_advance, [300] * cores, chunksize=1)       # calibration, untimed
+        per_core = 300.0 / statistics.mean(cal)
+        chunk = int(max(1, min(3000, per_core * 60.0 / max(a.warmup + a.steps, 1))))
+        for _ in range(a.warmup):
+            pool.map(_ref_advance, [chunk] * cores, chunksize=1)
         t0 = time.perf_counter()
-        base = cpu_baseline(3000, 1)
-        if i >= a.warmup:
-            t_all.append((time.perf_counter() - t0, base))
-    val = statistics.mean(b['value'] for _, b in t_all)
-    ms = 1e3 * statistics.mean(t for t, _ in t_all)
-    base = dict(base, value=val)
+        for _ in range(a.steps):
+            pool.map(_ref_advance, [chunk] * cores, chunksize=1)
+        wall = time.perf_counter() - t0
+    env_steps = float(a.steps) * chunk * cores
+    val = env_steps * N_VEH / wall
+    sample = ('%d worker processes (all host cores) x 1 env each, %d Env.steps per worker per '
+              'bench step, %d bench steps, workload c2 on oracle/sim.py (scalar Python port of the '
+              'reference per-vehicle loop; SUMO/TraCI unavailable on this box)'
+              % (cores, chunk, a.steps))
     print(json.dumps({
         'impl': 'reference', 'metric': 'vehicle-steps/s', 'value': val, 'unit': 'vehicle-steps/s',
-        'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': ms,
+        'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': 1e3 * wall / a.steps,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
-        'data': 'synthetic', 'env_steps_per_s': val / N_VEH,
+        'data': 'synthetic', 'env_steps_per_s': env_steps / wall,
         'config': {'workload': 'c2: WaveAttenuationPOEnv ring 21 IDM + 1 RL, random RL actions; '
-                               'CPU arm: one env per host core, 3000 Env.steps per sample'},
-        'cpu_baseline': base,
+                               'CPU arm: one env per host core', 'env_steps_per_bench_step': chunk * cores},
+        'cpu_baseline': dict(value=val, unit='vehicle-steps/s', cores=cores, kind='port',
+                             sample=sample),
         'e2e': {'value': val, 'unit': 'vehicle-steps/s', 'h2d_bytes_per_step': 0,
                 'd2h_bytes_per_step': 0},
         'gpu_launches': 0}))
@@ -195,9 +237,8 @@ def run_b200(a):
     from flow_b200.vec_env import B200VecEnv
     from flow_b200.workloads import WORKLOADS
 
-    rank = int(os.environ.get('RANK', '0'))
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    local = int(os.environ.get('LOCAL_RANK', '0'))
+    from flow_b200 import sharding as SH
+    rank, world, local = SH.env_rank_world()
     if world != a.gpus and world > 1:
         raise SystemExit('--gpus %d but WORLD_SIZE=%d' % (a.gpus, world))
     torch.cuda.set_device(local)
@@ -208,7 +249,8 @@ def run_b200(a):
     E, K, W, F = wl['n_envs'], a.steps, a.warmup, max(1, min(a.fuse, a.steps))
     types, tov, kw = wl['builder'](noise=a.noise)
     kw['horizon'] = max(kw['horizon'], K)
-    env = B200VecEnv(types, tov, E, dtype=a.dtype, device=local, env_id_base=rank * E,
+    env_id_base, E = SH.weak_shard(E, rank)   # weak scaling: E envs on every GPU
+    env = B200VecEnv(types, tov, E, dtype=a.dtype, device=local, env_id_base=env_id_base,
                      seed=1234, **kw)
     eng = env.engine
     td = torch.float32 if a.dtype == 'f32' else torch.float64
@@ -263,15 +305,12 @@ def run_b200(a):
         barrier()
         ms = e0.elapsed_time(e1)
         st = eng.stats()
-        v = torch.tensor([ms, st['vehicle_steps'], st['env_steps'], st['crashes'], st['sum_reward'],
-                          st['sum_speed']], device='cuda', dtype=torch.float64)
-        if world > 1:
-            mx = v[:1].clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-            dist.all_reduce(v, op=dist.ReduceOp.SUM)   # rollout statistics over NCCL
-            v[0] = mx[0]
-        ms, vs, es, cr, sr, ss = [float(x) for x in v.tolist()]
-        return dict(ms=ms, vehicle_steps=vs, env_steps=es, crashes=cr, mean_reward=sr / max(es, 1),
-                    mean_speed=ss / max(vs, 1), launches=eng.launch_count - l0)
+        # rollout statistics summed, time max'ed over ranks (NCCL all-reduce of 7 doubles)
+        st, ms = SH.reduce_stats(st, device='cuda', time_ms=ms)
+        agg = SH.summarize(st)
+        return dict(ms=ms, vehicle_steps=st['vehicle_steps'], env_steps=st['env_steps'],
+                    crashes=st['crashes'], mean_reward=agg['mean_reward'],
+                    mean_speed=agg['mean_speed'], launches=eng.launch_count - l0)
 
     sampler = ClockSampler(local) if rank == 0 else None
     fused = timed(fused_pass, K)
@@ -330,7 +369,8 @@ def run_b200(a):
                             'api': 'B200VecEnv.rollout_host, 1 step per call'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
-                     'kernel': 'ring1_step_kernel<%s,22> fused %d steps/launch' % (a.dtype, F),
+                     'kernel': 'ring1_hot_kernel<%s> (fs_ring_hot.cuh), %d fused steps per launch, '
+                               'threads/env = %s' % (a.dtype, F, os.environ.get('FS_RING_SHAPE', 'auto')),
                      'launch_ms': launch_ms,
                      'note': 'algorithmic bytes = %d B per env-step (SURVEY 8d) x env-steps per '
                              'launch; fused launches keep state in registers, so this is the '

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(_HERE)
 SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
 SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu']
-HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_reset.cuh', 'fs_launch.h',
+HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_ring_hot.cuh', 'fs_reset.cuh', 'fs_launch.h',
            'fs_multilane.cuh', 'fs_highway.cuh']
 
 FS_NPARAM = 8

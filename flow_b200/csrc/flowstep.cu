@@ -29,6 +29,8 @@ struct fs_engine {
   bool generic = false;   // some controller is not IDM/SIM/RL
   bool fast_ok = false;   // fs_ring_fast.cuh applies (see fs_set_types)
   int fast_variant = 0;   // 0 plain, 1 noise, 2 noise+fail-safe, 3 = 2 + views
+  bool hot_ok = false;    // c2/c5 pattern: 21 IDM + RL vehicle last, WaveAttenuation(PO), no fail-safe / views
+  bool no_hot = false;    // FS_NO_HOT=1: keep ring1_fast_kernel (A/B tests)
   int ring_shape = 0;     // FS_RING_SHAPE override: threads per env (1,2,4,8), 0 = auto
   int obs_dim = 0, act_dim = 0, n_rl = 0;
   cudaStream_t stream = nullptr;
@@ -136,6 +138,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   e->f64 = cfg->dtype == FS_F64;
   e->obs_dim = obs_dim_for(*cfg);
   if (const char* rs = getenv("FS_RING_SHAPE")) e->ring_shape = atoi(rs);
+  if (const char* nh = getenv("FS_NO_HOT")) e->no_hot = atoi(nh) != 0;
   st = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
   if (st != cudaSuccess) {
     g_create_error = cudaGetErrorString(st);
@@ -150,7 +153,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->done, E); A(&e->crash, E); A(&e->mask, E);
   A(&e->time_counter, E * 4); A(&e->episode, E * 4);
   A(&e->obs, E * e->obs_dim * ts); A(&e->reward, E * ts);
-  A(&e->stats, 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
+  A(&e->stats, FS_STAT_STRIPES * 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
   e->env_major = cfg->n_lanes > 1 || cfg->topology == FS_TOPO_HIGHWAY;
   if (e->env_major) A(&e->last_lc, V * E * 4);
   if (cfg->topology == FS_TOPO_HIGHWAY) { A(&e->counters, 4 * E * 4); A(&e->vtype, V * E); }
@@ -272,12 +275,22 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     }
     if (ta < 0) ok = false;
     e->fast_ok = ok;
+    {
+      // hot-kernel pattern: exactly one RL vehicle and it is the last one
+      int n_rl = 0;
+      for (int i = 0; i < e->cfg.n_veh; ++i) n_rl += types[type_of_vehicle[i]].controller == FS_CTRL_RL;
+      e->hot_ok = ok && n_rl == 1 &&
+                  types[type_of_vehicle[e->cfg.n_veh - 1]].controller == FS_CTRL_RL &&
+                  (e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION ||
+                   e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO) && !e->cfg.record_views;
+    }
     if (ok) {
       const fs_vtype& s = types[ta];
       const bool sim = s.controller == FS_CTRL_SIM;
       e->fast_variant = e->cfg.record_views ? 3
                         : (!sim && s.fail_safe != FS_FAILSAFE_NONE) ? 2
                         : (!sim && s.noise > 0) ? 1 : 0;
+      if (e->fast_variant > 1) e->hot_ok = false;
     }
   }
   if (e->cfg.topology == FS_TOPO_HIGHWAY) {
@@ -414,6 +427,17 @@ static cudaError_t launch_fast(int shape, int variant, int E, cudaStream_t st,
   return fs_launch_fast22_f64(shape, variant, E, st, c, b, a);
 }
 
+static cudaError_t launch_hot(int shape, bool noise, int E, cudaStream_t st,
+                              const fs::FastP<float>& c, const fs::RingBufs<float>& b,
+                              const fs::StepArgs<float>& a) {
+  return fs_launch_hot22_f32(shape, noise, E, st, c, b, a);
+}
+static cudaError_t launch_hot(int shape, bool noise, int E, cudaStream_t st,
+                              const fs::FastP<double>& c, const fs::RingBufs<double>& b,
+                              const fs::StepArgs<double>& a) {
+  return fs_launch_hot22_f64(shape, noise, E, st, c, b, a);
+}
+
 template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->cfg.topology == FS_TOPO_HIGHWAY) return launch_hw<T>(e, a);
@@ -425,6 +449,12 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
     if (shape != 1 && shape != 2 && shape != 4 && shape != 8 && shape != 16 && shape != 32)
       shape = E >= 32768 ? 1 : (E >= 16384 ? 2 : 8);
     if (sizeof(T) == 8 && shape == 1 && e->ring_shape == 0) shape = 2;  // f64 x 22 slots spills
+    if (e->hot_ok && !e->no_hot) {   // c2 / c5 configuration: fully specialised kernel
+      FS_CUDA(e, launch_hot(shape, e->fast_variant == 1, E, e->stream,
+                            fs::make_fastp(cfg_of<T>(e)), ring_bufs<T>(e), a));
+      e->launches++;
+      return FS_OK;
+    }
     FS_CUDA(e, launch_fast(shape, e->fast_variant, E, e->stream, fs::make_fastp(cfg_of<T>(e)),
                            ring_bufs<T>(e), a));
     e->launches++;
@@ -625,11 +655,15 @@ extern "C" int fs_set_state(fs_engine* e, const void* pos, const void* vel, cons
 extern "C" int fs_stats(fs_engine* e, double* host_out, int n, int reset) {
   if (!e || !host_out || n < 1) return FS_EINVAL;
   cudaSetDevice(e->cfg.device);
-  double tmp[8];
+  double tmp[FS_STAT_STRIPES * 8];   // striped accumulators, see fs_common.cuh
   FS_CUDA(e, cudaMemcpyAsync(tmp, e->stats, sizeof(tmp), cudaMemcpyDeviceToHost, e->stream));
   if (reset) FS_CUDA(e, cudaMemsetAsync(e->stats, 0, sizeof(tmp), e->stream));
   FS_CUDA(e, cudaStreamSynchronize(e->stream));
-  for (int i = 0; i < n && i < 8; ++i) host_out[i] = tmp[i];
+  for (int i = 0; i < n && i < 8; ++i) {
+    double s = 0.0;
+    for (int q = 0; q < FS_STAT_STRIPES; ++q) s += tmp[q * 8 + i];
+    host_out[i] = s;
+  }
   return FS_OK;
 }
 

@@ -11,6 +11,11 @@
 #include "../../include/flowstep.h"
 
 #define FS_MAX_VEH 256  // vehicles (ring) or slots (highway) per env
+// Rollout statistics are accumulated with fire-and-forget double atomics. All
+// warps of a launch hitting the SAME 6 addresses serialise in one L2 slice
+// (~25 us for 4096 warps), so every warp adds into one of FS_STAT_STRIPES
+// copies of the 8-double vector; fs_stats() sums the copies on the host.
+#define FS_STAT_STRIPES 64
 
 namespace fs {
 
@@ -48,6 +53,11 @@ struct Cfg {
 };
 
 // ---------------------------------------------------------------- helpers
+__device__ __forceinline__ double* stat_stripe(double* stats) {
+  const unsigned w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  return stats + (w & (FS_STAT_STRIPES - 1)) * 8;
+}
+
 template <typename T> struct Num;
 template <> struct Num<float> {
   static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }

@@ -7,3 +7,9 @@ cudaError_t fs_launch_fast22_f64(int shape, int variant, int n_envs, cudaStream_
                                  const fs::StepArgs<double>& a) {
   return fs::launch_fast22<double>(shape, variant, n_envs, st, c, b, a);
 }
+
+cudaError_t fs_launch_hot22_f64(int shape, bool noise, int n_envs, cudaStream_t st,
+                                const fs::FastP<double>& c, const fs::RingBufs<double>& b,
+                                const fs::StepArgs<double>& a) {
+  return fs::launch_hot22<double>(shape, noise, n_envs, st, c, b, a);
+}

@@ -335,7 +335,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
     B.reward[e] = reward;
     if (A.accumulate_stats) {
       const double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
-      for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&B.stats[q], vals[q]);
+      for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&stat_stripe(B.stats)[q], vals[q]);
     }
   }
 }

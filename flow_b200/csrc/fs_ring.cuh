@@ -370,7 +370,7 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
     for (int q = 0; q < 6; ++q) {
       double s = vals[q];
       for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (lane == 0 && s != 0.0) atomicAdd(&B.stats[q], s);
+      if (lane == 0 && s != 0.0) atomicAdd(&stat_stripe(B.stats)[q], s);
     }
   }
 }

@@ -439,7 +439,7 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
     for (int q = 0; q < 6; ++q) {
       double s = vals[q];
       for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (lane == 0 && s != 0.0) atomicAdd(&B.stats[q], s);
+      if (lane == 0 && s != 0.0) atomicAdd(&stat_stripe(B.stats)[q], s);
     }
   }
 }

@@ -1,0 +1,343 @@
+// fs_ring_hot.cuh — the c2 / c5 kernel: single-lane ring of V = 22 vehicles,
+// 21 IDM humans of one type followed by ONE RL vehicle at index V-1, observed
+// by WaveAttenuationEnv / WaveAttenuationPOEnv, no fail-safe, no views. This is
+// exactly what examples/exp_configs/rl/singleagent/singleagent_ring.py builds;
+// anything else runs on ring1_fast_kernel (fs_ring_fast.cuh) or ring1_kernel.
+//
+// Same thread mapping and step semantics as ring1_fast_kernel (G threads per
+// env, VPT vehicles per thread in registers for the K fused steps), with
+// everything that kernel decides at run time per vehicle or per step fixed at
+// compile time:
+//   * V, the RL vehicle's thread (RL_G) and slot (RL_SLOT) are constants, so
+//     the per-vehicle "is this one RL?" tests, mask shifts and the alternate
+//     action loads disappear; the RL thread is also the writer of obs/reward/
+//     done, and the leader of vehicle V-1 is vehicle 0 = the exchanged value;
+//   * kAct (RL actions present) is a template flag: warm-up launches carry no
+//     action loads, reward arithmetic or clipping;
+//   * one-vehicle-per-thread shapes (VPT <= 4) run the step loop in blocks of 4
+//     steps aligned to the env's time counter, unrolled: the four normals of a
+//     Philox call and the four prefetched actions of a block are addressed with
+//     compile-time indices (no register rotation, no per-step phase tests);
+//   * Philox4x32-10 runs with a compile-time key schedule (seed and global env
+//     id travel in the counter words), so the 20 key additions per call fold
+//     into immediates;
+//   * the steps-advanced statistic is the time-counter difference.
+// Reference lines restated: see fs_ring.cuh header (same step semantics).
+#pragma once
+#include "fs_ring_fast.cuh"
+
+namespace fs {
+
+struct PhiloxCK {
+  // counter = (c0,c1,c2,c3) -> 4 x u32, fixed key (0xA4093822, 0x299F31D0)
+  static __device__ __forceinline__ void gen(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                             uint32_t (&out)[4]) {
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      const uint32_t k0 = 0xA4093822u + (uint32_t)i * 0x9E3779B9u;
+      const uint32_t k1 = 0x299F31D0u + (uint32_t)i * 0xBB67AE85u;
+      const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
+      const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
+      const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+      const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+      c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+  }
+};
+
+// four standard normals (Box-Muller on both pairs of one Philox call)
+template <typename T>
+__device__ __forceinline__ void normal4_ck(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                           T (&z)[4]) {
+  uint32_t r[4];
+  PhiloxCK::gen(c0, c1, c2, c3, r);
+  if (sizeof(T) == 4) {
+    const float k = 2.3283064365386963e-10f;  // 2^-32
+    const float u0 = fminf(fmaf((float)r[0], k, k), 1.0f), u2 = fminf(fmaf((float)r[2], k, k), 1.0f);
+    const float ra = sqrtf(-1.3862943611198906f * __log2f(u0));   // sqrt(-2 ln u)
+    const float rb = sqrtf(-1.3862943611198906f * __log2f(u2));
+    float s0, c0f, s1, c1f;
+    __sincosf(6.2831853071795865f * ((float)r[1] * k), &s0, &c0f);
+    __sincosf(6.2831853071795865f * ((float)r[3] * k), &s1, &c1f);
+    z[0] = (T)(ra * c0f); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1f); z[3] = (T)(rb * s1);
+  } else {
+    const double k = 1.0 / 4294967296.0;
+    const double ra = ::sqrt(-2.0 * ::log(((double)r[0] + 1.0) * k));
+    const double rb = ::sqrt(-2.0 * ::log(((double)r[2] + 1.0) * k));
+    double s0, c0d, s1, c1d;
+    sincos(6.283185307179586 * ((double)r[1] * k), &s0, &c0d);
+    sincos(6.283185307179586 * ((double)r[3] * k), &s1, &c1d);
+    z[0] = (T)(ra * c0d); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1d); z[3] = (T)(rb * s1);
+  }
+}
+
+constexpr int kHotV = 22;
+
+template <typename T, int VPT, int G, bool kNoise, bool kAct>
+__global__ void __launch_bounds__(128)
+ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const StepArgs<T> A) {
+  typedef Num<T> N;
+  constexpr int V = kHotV;
+  constexpr int EPW = 32 / G;
+  constexpr bool kF32 = sizeof(T) == 4;
+  constexpr bool kExact = VPT * G == V;
+  constexpr int RL_G = (V - 1) / VPT, RL_SLOT = (V - 1) % VPT;  // thread / slot of vehicle V-1
+  constexpr bool kTimeNoise = VPT <= 4;   // 4 normals of a call spread over 4 consecutive steps
+  constexpr int NQ = kTimeNoise ? VPT : (VPT + 3) / 4;
+  constexpr int UNR = kTimeNoise ? 4 : 1;  // steps per unrolled block
+  static_assert(VPT * G >= V, "shape does not hold 22 vehicles");
+
+  const int lane = threadIdx.x & 31;
+  const int g = (G == 1) ? 0 : lane / EPW;
+  const int es = (G == 1) ? lane : lane % EPW;
+  const int E = P.n_envs;
+  const int e_raw = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * EPW + es;
+  const bool valid = e_raw < E && (A.mask == nullptr || A.mask[e_raw < E ? e_raw : 0] != 0);
+  if (!__any_sync(0xffffffffu, valid)) return;
+  const int e = e_raw < E ? e_raw : E - 1;
+  unsigned gmask = 0;
+#pragma unroll
+  for (int q = 0; q < G; ++q) gmask |= 1u << (es + q * EPW);
+
+  const int base = g * VPT;
+  const int n_mine = kExact ? VPT : max(0, min(VPT, V - base));
+  const bool is_rl = g == RL_G;   // owns vehicle V-1: RL vehicle, writer of obs / reward / done
+  const int lane_next = ((g >= RL_G) ? 0 : g + 1) * EPW + es;
+  const int K = A.k_steps;
+  const bool po = P.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
+
+  IdmRegs<T> pm = P.pa;
+  T nz = P.noise;
+  if (VPT == 1 && is_rl) { pm = P.pb; nz = T(0); }
+  const T len = P.len, dt = P.dt;
+  const T C = B.circ[e];
+  const T crash_thr = P.collision_min_gap ? P.min_gap : T(0);
+  const T inv_obs_len = P.inv_obs_len > T(0) ? P.inv_obs_len : T(1) / C;
+  const T obs_len = P.obs_max_length > T(0) ? P.obs_max_length : C;
+  const T inv_C = T(1) / C;
+
+  T x[VPT], v[VPT], h[VPT];
+  FS_SLOTS(i) {
+    const bool ok = kExact || i < n_mine;
+    x[i] = ok ? B.pos[(size_t)(base + i) * E + e] : T(0);
+    v[i] = ok ? B.vel[(size_t)(base + i) * E + e] : T(0);
+  }
+  // first vehicle of the next thread = leader of my last vehicle (vehicle 0 for the RL thread)
+  T x_nf = (G == 1) ? x[0] : shfl(x[0], lane_next, gmask);
+  T v_nf = (G == 1) ? v[0] : shfl(v[0], lane_next, gmask);
+  auto update_headways = [&]() {  // k.update: vehicle/traci.py:218-250
+    FS_SLOTS(i) {
+      T xl;
+      if (i + 1 < VPT) xl = (kExact || i + 1 < n_mine) ? x[i + 1 < VPT ? i + 1 : 0] : x_nf;
+      else xl = x_nf;
+      h[i] = fwd_dist(xl, x[i], C) - len;
+    }
+  };
+  update_headways();
+
+  int tc = B.time_counter[e];
+  const int tc0 = tc;
+  const int episode = B.episode[e];
+  bool done = A.ignore_done ? false : (B.done[e] != 0);
+  bool crash = B.crash[e] != 0;
+  const long long gid = P.env_id_base + e;
+  T reward = B.reward[e];
+  // Philox counter words 2, 3: global env id and seed; word 1: episode / vehicle block
+  const uint32_t pc2 = (uint32_t)gid;
+  const uint32_t pc3 = (uint32_t)(gid >> 32) ^ (uint32_t)P.seed ^ ((uint32_t)(P.seed >> 32) * 0x9E3779B9u);
+  const uint32_t pc1 = (uint32_t)(episode * 256 + base) | (kTimeNoise ? 0u : 0x80000000u);
+
+  const T* act_p = A.actions + e;  // action of step s: act_p[s * E] (act_dim == 1)
+  auto ld_act = [&](int s) -> T {  // clamped: slots outside [0, K) are fetched but never used
+    s = s < 0 ? 0 : (s >= K ? K - 1 : s);
+    return __ldg(act_p + (size_t)s * E);
+  };
+
+  float st_rew = 0.f, st_v = 0.f, st_v2 = 0.f;
+  int st_cr = 0;
+  const bool w_obs = valid && A.obs_seq != nullptr && (!po || is_rl);
+  const bool w_rew = valid && is_rl && A.reward_seq != nullptr;
+  const bool w_done = valid && is_rl && A.done_seq != nullptr;
+  T* obs_k = A.obs_seq + (w_obs ? (size_t)e * P.obs_dim : 0);
+  T* rew_k = A.reward_seq + (w_rew ? e : 0);
+  uint8_t* done_k = A.done_seq + (w_done ? e : 0);
+  const size_t obs_stride = (size_t)E * P.obs_dim;
+  const bool st_on = A.accumulate_stats && valid;
+
+  auto po_obs = [&](T& o0, T& o1, T& o2) {  // WaveAttenuationPOEnv.get_state, wave_attenuation.py:248-269
+    const T xr = x[RL_SLOT], vr = v[RL_SLOT];
+    o0 = N::div(vr, T(15)); o1 = N::div(v_nf - vr, T(15));
+    o2 = kF32 ? fwd_dist(x_nf, xr, C) * inv_obs_len : N::div(fwd_dist(x_nf, xr, C), obs_len);
+  };
+  auto full_obs = [&](T* o) {  // WaveAttenuationEnv.get_state, wave_attenuation.py:141-148
+    FS_SLOTS(i) if (kExact || i < n_mine) {
+      o[base + i] = kF32 ? v[i] * P.inv_speed_limit : N::div(v[i], P.speed_limit);
+      o[V + base + i] = kF32 ? x[i] * inv_C : N::div(x[i], C);
+    }
+  };
+
+  T ac[UNR], an[UNR];
+  int j0 = kTimeNoise ? (tc & 3) : 0;   // phase of the first (possibly partial) block
+  int kb = -j0;                         // launch-relative step of the block's slot 0
+#pragma unroll
+  for (int j = 0; j < UNR; ++j) { ac[j] = T(0); an[j] = (kAct && is_rl) ? ld_act(kb + j) : T(0); }
+
+  while (kb < K) {
+    if (kAct) {
+#pragma unroll
+      for (int j = 0; j < UNR; ++j) ac[j] = an[j];
+      if (is_rl) {
+#pragma unroll
+        for (int j = 0; j < UNR; ++j) an[j] = ld_act(kb + UNR + j);
+      }
+    }
+    T zn[kNoise ? NQ : 1][4];
+    if (kNoise && kTimeNoise && !done) {
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) normal4_ck<T>((uint32_t)(tc >> 2), pc1 + q, pc2, pc3, zn[q]);
+    }
+#pragma unroll
+    for (int j = 0; j < UNR; ++j) {
+      if (j >= j0 && kb + j < K) {
+        if (!done) {
+          if (kNoise && !kTimeNoise) {  // base_controller.py:109-110
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) normal4_ck<T>((uint32_t)tc, pc1 + 4 * q, pc2, pc3, zn[q]);
+          }
+          // ---- controllers -> apply_acceleration -> Euler move (all read the old state)
+          const T v_lead_last = v_nf;
+          T act_abs = T(0);
+          FS_SLOTS(i) {
+            const bool ok = kExact || i < n_mine;
+            const T vi = v[i], hi = h[i];
+            T vl;
+            if (i + 1 < VPT) vl = (kExact || i + 1 < n_mine) ? v[i + 1 < VPT ? i + 1 : 0] : v_lead_last;
+            else vl = v_lead_last;
+            T a = idm_fast<T, true>(vi, vl, hi, pm);
+            if (kNoise) {
+              const T z = kTimeNoise ? zn[kNoise ? i : 0][j] : zn[kNoise ? (i >> 2) : 0][i & 3];
+              a = add(a, mul(VPT == 1 ? nz : P.noise, z));
+            }
+            if (i == RL_SLOT) {
+              if (kAct) {  // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
+                const T raw = ac[j];
+                const T a_c = N::min(N::max(raw, P.act_lo), P.act_hi);
+                act_abs = N::abs(P.clip_actions ? a_c : raw);
+                a = is_rl ? a_c : a;
+              } else if (VPT > 1) {  // un-commanded RL vehicle: restated simulator default model
+                if (is_rl) a = idm_fast<T, true>(vi, vl, hi, P.pb);
+              }
+            }
+            const T vn = N::max(add(vi, mul(a, dt)), T(0));   // vehicle/traci.py:961-962
+            const T xn = wrap_fwd(add(x[i], mul(vn, dt)), C);  // simulator Euler move
+            if (ok) { v[i] = vn; x[i] = xn; }
+          }
+          if (G > 1) { x_nf = shfl(x[0], lane_next, gmask); v_nf = shfl(v[0], lane_next, gmask); }
+          else { x_nf = x[0]; v_nf = v[0]; }
+          update_headways();
+          bool cr = false;
+          T sv = T(0);
+          float s2 = 0.f;
+          FS_SLOTS(i) if (kExact || i < n_mine) {
+            cr |= h[i] < crash_thr;
+            sv = add(sv, v[i]);
+            s2 = fmaf((float)v[i], (float)v[i], s2);
+          }
+          st_v += (float)sv; st_v2 += s2;
+          if (G > 1) cr = __any_sync(gmask, cr);
+          crash = cr;
+          tc += 1;
+          done = crash || tc >= P.t_end;
+          if (kAct) {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
+            sv = env_sum<T, G>(sv, gmask);
+            T r = kF32 ? sv * P.rew_scale : N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
+            if (act_abs > T(0)) r = add(r, mul(T(4), T(0) - act_abs));
+            reward = crash ? T(0) : r;
+          } else {
+            reward = T(0);
+          }
+          st_rew += (float)reward; st_cr += crash ? 1 : 0;
+        } else {
+          reward = T(0);
+        }
+        // ---- per-step outputs
+        if (w_obs) {
+          if (po) { T o0, o1, o2; po_obs(o0, o1, o2); obs_k[0] = o0; obs_k[1] = o1; obs_k[2] = o2; }
+          else full_obs(obs_k);
+          obs_k += obs_stride;
+        }
+        if (w_rew) { *rew_k = reward; rew_k += E; }
+        if (w_done) { *done_k = done ? 1 : 0; done_k += E; }
+      }
+    }
+    kb += UNR;
+    j0 = 0;
+  }
+
+  if (valid) {
+    T* ol = B.obs + (size_t)e * P.obs_dim;
+    if (po) {
+      if (is_rl) { T o0, o1, o2; po_obs(o0, o1, o2); ol[0] = o0; ol[1] = o1; ol[2] = o2; }
+    } else full_obs(ol);
+    FS_SLOTS(i) if (kExact || i < n_mine) {
+      B.pos[(size_t)(base + i) * E + e] = x[i];
+      B.vel[(size_t)(base + i) * E + e] = v[i];
+    }
+    if (is_rl) {
+      B.time_counter[e] = tc;
+      B.done[e] = done ? 1 : 0;
+      B.crash[e] = crash ? 1 : 0;
+      B.reward[e] = reward;
+    }
+  }
+  if (A.accumulate_stats) {
+    // stats[]: sum reward, sum v, sum v^2, vehicle-steps, env-steps, crashes
+    const int adv = st_on ? tc - tc0 : 0;
+    double vals[6] = {(st_on && is_rl) ? (double)st_rew : 0.0, st_on ? (double)st_v : 0.0,
+                      st_on ? (double)st_v2 : 0.0, (double)(adv * n_mine),
+                      is_rl ? (double)adv : 0.0, (st_on && is_rl) ? (double)st_cr : 0.0};
+    double* sp = stat_stripe(B.stats);
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+      double s = vals[q];
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0 && s != 0.0) atomicAdd(&sp[q], s);
+    }
+  }
+}
+
+// ---- host-side dispatch (one translation unit per dtype instantiates these)
+template <typename T, int VPT, int G>
+static cudaError_t launch_hot_shape(bool noise, bool act, int grid, int block, cudaStream_t st,
+                                    const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
+  if (noise) {
+    if (act) ring1_hot_kernel<T, VPT, G, true, true><<<grid, block, 0, st>>>(c, b, a);
+    else ring1_hot_kernel<T, VPT, G, true, false><<<grid, block, 0, st>>>(c, b, a);
+  } else {
+    if (act) ring1_hot_kernel<T, VPT, G, false, true><<<grid, block, 0, st>>>(c, b, a);
+    else ring1_hot_kernel<T, VPT, G, false, false><<<grid, block, 0, st>>>(c, b, a);
+  }
+  return cudaGetLastError();
+}
+
+// shape = threads per env (1, 2, 4, 8, 16, 32)
+template <typename T>
+static cudaError_t launch_hot22(int shape, bool noise, int n_envs, cudaStream_t st,
+                                const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
+  const int epw = 32 / shape;
+  const int warps = (n_envs + epw - 1) / epw;
+  const int wpb = warps <= 148 * 8 ? 1 : (warps <= 148 * 32 ? 2 : 4);
+  const int grid = (warps + wpb - 1) / wpb, block = wpb * 32;
+  const bool act = a.actions != nullptr;
+  switch (shape) {
+    case 1: return launch_hot_shape<T, 22, 1>(noise, act, grid, block, st, c, b, a);
+    case 2: return launch_hot_shape<T, 11, 2>(noise, act, grid, block, st, c, b, a);
+    case 4: return launch_hot_shape<T, 6, 4>(noise, act, grid, block, st, c, b, a);
+    case 8: return launch_hot_shape<T, 3, 8>(noise, act, grid, block, st, c, b, a);
+    case 16: return launch_hot_shape<T, 2, 16>(noise, act, grid, block, st, c, b, a);
+    default: return launch_hot_shape<T, 1, 32>(noise, act, grid, block, st, c, b, a);
+  }
+}
+
+}  // namespace fs

@@ -1,0 +1,154 @@
+"""GPU parity of ring1_hot_kernel (the c2 / c5 specialisation): against the
+reference-generated golden trajectory, against ring1_fast_kernel on the same
+inputs (bit for bit in fp64), across every thread-mapping shape, with launches
+that start inside a 4-step noise block, and the statistics of its Philox noise."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import scenarios as S
+from oracle import sim as OS
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), 'golden')
+SHAPES = [1, 2, 4, 8, 16, 32]
+KW = dict(env_kind=OS.ENV_WAVE_ATTENUATION_PO, length_lo=220., length_hi=270., **S.C2)
+
+
+def close(a, b, floor=1.0):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float((np.abs(a - b) / np.maximum(np.abs(b), floor)).max())
+
+
+@pytest.mark.parametrize('shape', SHAPES)
+def test_hot_golden_c2_fp64(shape, monkeypatch):
+    import torch
+    monkeypatch.setenv('FS_RING_SHAPE', str(shape))
+    z = np.load(os.path.join(G, 'ring_c2.npz'))
+    lengths = [float(z['length_a']), float(z['length_b'])] * 20
+    E = len(lengths)
+    eng = S.make_engine(S.c2_groups(), E, 'f64', **KW)
+    eng.reset(lengths=lengths)
+    n = 240
+    act = np.zeros((n, 1, E))
+    act[:, 0, 0::2] = z['actions_a'][:n, None]
+    act[:, 0, 1::2] = z['actions_b'][:n, None]
+    s = 0
+    for K in (1, 2, 7, 30, 50, 3, 100, 47):     # launches start at every phase of a 4-step block
+        obs_seq = torch.empty(K, E, 3, device='cuda', dtype=torch.float64)
+        rew_seq = torch.empty(K, E, device='cuda', dtype=torch.float64)
+        eng.step(torch.tensor(act[s:s + K], device='cuda'), k=K, obs_seq=obs_seq, reward_seq=rew_seq)
+        o, r = obs_seq.cpu().numpy(), rew_seq.cpu().numpy()
+        for e, tag in ((0, 'a'), (1, 'b'), (38, 'a'), (39, 'b')):
+            assert close(o[:, e], z['obs_' + tag][s + 1:s + K + 1]) <= 1e-9, (shape, s, tag)
+            assert close(r[:, e], z['reward_' + tag][s:s + K]) <= 1e-9, (shape, s, tag)
+            assert close(eng.pos.cpu().numpy()[:, e], z['pos_' + tag][s + K]) <= 1e-9
+            assert close(eng.vel.cpu().numpy()[:, e], z['vel_' + tag][s + K]) <= 1e-9
+        s += K
+    assert s == n
+
+
+@pytest.mark.parametrize('dtype', ['f64', 'f32'])
+@pytest.mark.parametrize('shape', SHAPES)
+def test_hot_equals_fast_kernel(shape, dtype, monkeypatch):
+    """Same inputs through ring1_hot_kernel and ring1_fast_kernel (FS_NO_HOT=1):
+    identical in fp64, 1e-5 in fp32; warm-up (no actions) included."""
+    import torch
+    monkeypatch.setenv('FS_RING_SHAPE', str(shape))
+    E, K = 100, 83
+    td = torch.float64 if dtype == 'f64' else torch.float32
+    hot = S.make_engine(S.c2_groups(), E, dtype, seed=9, **KW)
+    monkeypatch.setenv('FS_NO_HOT', '1')
+    ref = S.make_engine(S.c2_groups(), E, dtype, seed=9, **KW)
+    monkeypatch.delenv('FS_NO_HOT')
+    o_h, o_r = hot.reset(), ref.reset()       # 750 warm-up steps without actions
+    tol = 0.0 if dtype == 'f64' else 1e-5
+    assert close(o_h.cpu().numpy(), o_r.cpu().numpy()) <= tol
+    gen = torch.Generator(device='cuda'); gen.manual_seed(2)
+    act = torch.rand(K, 1, E, device='cuda', dtype=td, generator=gen) * 3 - 1.5   # clipping exercised
+    out = []
+    for eng in (hot, ref):
+        obs_seq = torch.empty(K, E, 3, device='cuda', dtype=td)
+        rew_seq = torch.empty(K, E, device='cuda', dtype=td)
+        done_seq = torch.empty(K, E, device='cuda', dtype=torch.uint8)
+        eng.stats(reset=True)
+        eng.step(act[:5], k=5, obs_seq=obs_seq[:5], reward_seq=rew_seq[:5], done_seq=done_seq[:5])
+        eng.step(act[5:], k=K - 5, obs_seq=obs_seq[5:], reward_seq=rew_seq[5:], done_seq=done_seq[5:])
+        out.append((obs_seq.cpu().numpy(), rew_seq.cpu().numpy(), done_seq.cpu().numpy(),
+                    eng.pos.cpu().numpy(), eng.vel.cpu().numpy(), eng.stats(),
+                    eng.time_counter.cpu().numpy()))
+    a, b = out
+    for i in range(5):
+        if i == 2:
+            assert np.array_equal(a[i], b[i])
+        else:
+            assert close(a[i], b[i]) <= tol, i
+    assert np.array_equal(a[6], b[6])
+    for k in ('vehicle_steps', 'env_steps', 'crashes'):
+        assert a[5][k] == b[5][k], k
+    for k in ('sum_reward', 'sum_speed', 'sum_speed_sq'):
+        assert abs(a[5][k] - b[5][k]) <= 1e-5 * max(1.0, abs(b[5][k])), k
+
+
+@pytest.mark.parametrize('shape', [1, 8, 32])
+def test_hot_wave_attenuation_full_obs(shape, monkeypatch):
+    """WaveAttenuationEnv (2V observation) also takes the hot kernel."""
+    import torch
+    monkeypatch.setenv('FS_RING_SHAPE', str(shape))
+    kw = dict(KW, env_kind=OS.ENV_WAVE_ATTENUATION)
+    E, K = 37, 21
+    hot = S.make_engine(S.c2_groups(), E, 'f64', seed=4, **kw)
+    monkeypatch.setenv('FS_NO_HOT', '1')
+    ref = S.make_engine(S.c2_groups(), E, 'f64', seed=4, **kw)
+    hot.reset(); ref.reset()
+    act = torch.rand(K, 1, E, device='cuda', dtype=torch.float64) * 2 - 1
+    res = []
+    for eng in (hot, ref):
+        obs_seq = torch.empty(K, E, 44, device='cuda', dtype=torch.float64)
+        rew_seq = torch.empty(K, E, device='cuda', dtype=torch.float64)
+        eng.step(act, k=K, obs_seq=obs_seq, reward_seq=rew_seq)
+        res.append((obs_seq.cpu().numpy(), rew_seq.cpu().numpy(), eng.obs.cpu().numpy()))
+    for x, y in zip(*res):
+        assert np.array_equal(x, y)
+
+
+@pytest.mark.parametrize('shape', [1, 2, 8, 32])
+def test_hot_noise_is_invariant_to_fusing_and_well_distributed(shape, monkeypatch):
+    import torch
+    monkeypatch.setenv('FS_RING_SHAPE', str(shape))
+    E, K = 512, 24
+    kw = dict(KW, warmup_steps=0)
+    a = S.make_engine(S.c2_groups(noise=0.2), E, 'f32', seed=21, **kw)
+    b = S.make_engine(S.c2_groups(noise=0.2), E, 'f32', seed=21, **kw)
+    q = S.make_engine(S.c2_groups(noise=0.0), E, 'f32', seed=21, **kw)
+    for eng in (a, b, q):
+        eng.reset()
+    act = torch.rand(K, 1, E, device='cuda') * 2 - 1
+    a.step(act, k=K)
+    for chunk in ((0, 1), (1, 3), (3, 10), (10, 11), (11, 24)):     # every block phase
+        b.step(act[chunk[0]:chunk[1]], k=chunk[1] - chunk[0])
+    assert torch.equal(a.pos, b.pos) and torch.equal(a.vel, b.vel)
+    # one noisy step from a common state: dv = noise * z * dt for the 21 humans, 0 for the RL car
+    n1 = S.make_engine(S.c2_groups(noise=0.2), E, 'f32', seed=5, **kw)
+    n1.reset(); q.reset()
+    zs = []
+    for k in range(8):
+        q.set_state(n1.pos.cpu().numpy(), n1.vel.cpu().numpy())
+        q.time_counter.copy_(n1.time_counter)
+        n1.step(act[k]); q.step(act[k])
+        dv = (n1.vel - q.vel).cpu().numpy().astype(np.float64)
+        moving = (q.vel.cpu().numpy() > 0.05)
+        assert np.abs(dv[21]).max() == 0.0
+        z = dv[:21] / (0.2 * 0.1)
+        zs.append(np.where(moving[:21], z, np.nan))
+    z = np.stack(zs)                       # [step, vehicle, env]
+    flat = z[np.isfinite(z)]
+    assert flat.size > 50000
+    assert abs(flat.mean()) < 0.02 and abs(flat.std() - 1.0) < 0.02
+    assert abs(np.mean(flat ** 3)) < 0.06 and abs(np.mean(flat ** 4) - 3.0) < 0.15
+    zz = np.nan_to_num(z)
+    c_veh = np.mean(zz[:, :-1] * zz[:, 1:])       # neighbours in the ring
+    c_time = np.mean(zz[:-1] * zz[1:])            # successive steps (same Philox call for VPT <= 4)
+    c_env = np.mean(zz[:, :, :-1] * zz[:, :, 1:])
+    assert max(abs(c_veh), abs(c_time), abs(c_env)) < 0.02
