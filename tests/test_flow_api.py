@@ -229,10 +229,9 @@ def test_gpu_wave_attenuation_po_env_matches_golden():
     z = np.load(os.path.join(G, 'ring_c2.npz'))
     for tag in ('a', 'b'):
         fp = ring_flow_params(warmup=0)
-        L = float(z['length_' + tag])
-        fp['env'].additional_params['ring_length'] = [L, L]
         env = F.make_create_env(fp)[0]()
         env.reset()
+        env.engine.reset(lengths=[float(z['length_' + tag])])   # the golden run's ring length
         env.engine.set_state(pos=z['pos_' + tag][0][:, None], vel=z['vel_' + tag][0][:, None])
         for s in range(600):
             a = z['actions_' + tag][s]
@@ -269,9 +268,10 @@ def test_gpu_batched_env_and_action_layout():
 
 
 @pytest.mark.gpu
-def test_gpu_highway_env_rates():
+@pytest.mark.parametrize('n_init', [0, 10])
+def test_gpu_highway_env_rates(n_init):
     v = F.VehicleParams()
-    v.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=10)
+    v.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=n_init)
     inflow = F.InFlows()
     inflow.add(veh_type='human', edge='highway_0', vehs_per_hour=2000, depart_speed=20)
     fp = dict(exp_tag='hw', env_name=F.AccelEnv, network=F.HighwayNetwork, simulator='traci',
@@ -282,13 +282,20 @@ def test_gpu_highway_env_rates():
               veh=v, initial=F.InitialConfig())
     env = F.make_create_env(fp)[0]()
     env.reset()
-    assert env.k.vehicle.num_vehicles == 10
+    assert env.k.vehicle.num_vehicles == n_init
     for _ in range(1500):
         obs, r, done, _ = env.step(None)
     assert not done
     n = env.k.vehicle.num_vehicles
-    assert n > 10 and len(env.k.vehicle.get_speed(env.k.vehicle.get_ids())) == n
-    # 2000 veh/h: one departure per 1.8 s (vehicle/traci.py:493-505 rate formulas)
-    assert env.k.vehicle.get_inflow_rate(500) == pytest.approx(2000, rel=0.05)
-    assert env.k.vehicle.get_outflow_rate(500) > 0
+    assert n > n_init and len(env.k.vehicle.get_speed(env.k.vehicle.get_ids())) == n
+    c = env.engine.counters[:, 0].cpu().numpy()
+    assert n == c[0] == c[1] - c[2]
+    rate_in, rate_out = env.k.vehicle.get_inflow_rate(500), env.k.vehicle.get_outflow_rate(500)
+    if n_init == 0:
+        # free entry: 2000 veh/h = one departure per 1.8 s (vehicle/traci.py:493-505 formulas)
+        assert rate_in == pytest.approx(2000, rel=0.03)
+        assert rate_out > 0
+    else:
+        # ten stationary vehicles queue at the entry: departures are held back (blocked insertion)
+        assert 0 < rate_in < 2000
     env.terminate()
