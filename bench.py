@@ -52,6 +52,8 @@ def parse():
     ap.add_argument('--noise', type=float, default=0.2,
                     help='IDM accel noise std (0.2 in singleagent_ring.py; 0 = parity setting)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--only-fused', action='store_true',
+                    help='development: time only the fused device-resident pass')
     ap.add_argument('--cpu-envs-per-core', type=int, default=2)
     return ap.parse_args()
 
@@ -314,9 +316,12 @@ def run_b200(a):
 
     sampler = ClockSampler(local) if rank == 0 else None
     fused = timed(fused_pass, K)
-    single = timed(single_pass, K)
-    host = timed(host_pass, K)
-    host1 = timed(host_single_pass, min(K, 1000))
+    if a.only_fused:
+        single = host = host1 = fused
+    else:
+        single = timed(single_pass, K)
+        host = timed(host_pass, K)
+        host1 = timed(host_single_pass, min(K, 1000))
     clocks = sampler.stop() if sampler else None
     if rank != 0:
         if world > 1:

@@ -112,6 +112,8 @@ def build(force=False, verbose=False):
     bdir = os.path.join(_HERE, 'build')
     os.makedirs(bdir, exist_ok=True)
     extra = ['-Xptxas', '-v'] if verbose else []
+    if os.environ.get('FS_HOT_EXPERIMENTS'):   # timing variants of the hot kernel (FS_HOT_VAR)
+        extra.append('-DFS_HOT_EXPERIMENTS')
     procs = []
     for src in SOURCES:   # one nvcc per translation unit, in parallel
         obj = os.path.join(bdir, src.replace('.cu', '.o'))

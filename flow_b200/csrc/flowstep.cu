@@ -447,7 +447,13 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
     // IDM-law hot kernel; threads per env chosen from the batch size
     int shape = e->ring_shape;
     if (shape != 1 && shape != 2 && shape != 4 && shape != 8 && shape != 16 && shape != 32)
-      shape = E >= 32768 ? 1 : (E >= 16384 ? 2 : 8);
+    {
+      // about 1024 warps (1.7 per SM sub-partition) whatever the batch: the fewest
+      // threads per env (most vehicles per thread, least per-env overhead) that
+      // still spread the batch over every scheduler. Measured on c2 / c5.
+      shape = 1;
+      while (shape < 32 && (long long)E * shape < 32768) shape <<= 1;
+    }
     if (sizeof(T) == 8 && shape == 1 && e->ring_shape == 0) shape = 2;  // f64 x 22 slots spills
     if (e->hot_ok && !e->no_hot) {   // c2 / c5 configuration: fully specialised kernel
       FS_CUDA(e, launch_hot(shape, e->fast_variant == 1, E, e->stream,

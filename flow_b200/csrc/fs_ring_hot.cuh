@@ -74,18 +74,47 @@ __device__ __forceinline__ void normal4_ck(uint32_t c0, uint32_t c1, uint32_t c2
 
 constexpr int kHotV = 22;
 
-template <typename T, int VPT, int G, bool kNoise, bool kAct>
+// sum of `part` over the G threads of each env of the warp; every lane of the
+// warp must call it (full-mask collectives). fp32, <= 4 envs per warp: one
+// integer REDUX per env slot in 2^-20 m/s fixed point (|sum| < 2000 m/s);
+// otherwise an xor-shuffle tree over the group's lanes.
+template <typename T, int G>
+__device__ __forceinline__ T env_sum_full(T part, int es) {
+  constexpr int EPW = 32 / G;
+  if (G == 1) return part;
+  if (sizeof(T) == 4 && EPW <= 4) {
+    const int q = __float2int_rn((float)part * 1048576.0f);
+    int mine = 0;
+#pragma unroll
+    for (int s = 0; s < EPW; ++s) {
+      const int r = __reduce_add_sync(0xffffffffu, (EPW == 1 || es == s) ? q : 0);
+      mine = (EPW == 1 || es == s) ? r : mine;
+    }
+    return (T)((float)mine * 9.5367431640625e-07f);
+  }
+#pragma unroll
+  for (int o = EPW; o < 32; o <<= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  return part;
+}
+
+template <typename T, int VPT, int G, bool kNoise, bool kAct, int kVar = 0>
 __global__ void __launch_bounds__(128)
 ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
   constexpr int V = kHotV;
   constexpr int EPW = 32 / G;
+  constexpr unsigned FULL = 0xffffffffu;
   constexpr bool kF32 = sizeof(T) == 4;
   constexpr bool kExact = VPT * G == V;
   constexpr int RL_G = (V - 1) / VPT, RL_SLOT = (V - 1) % VPT;  // thread / slot of vehicle V-1
   constexpr bool kTimeNoise = VPT <= 4;   // 4 normals of a call spread over 4 consecutive steps
   constexpr int NQ = kTimeNoise ? VPT : (VPT + 3) / 4;
   constexpr int UNR = kTimeNoise ? 4 : 1;  // steps per unrolled block
+  // Several envs share a warp (1 < G < 32): the step body runs for every lane
+  // and frozen / not-selected envs are handled by predication, so that every
+  // collective is a full-warp one (a partial-mask REDUX / VOTE compiles to a
+  // loop over mask groups). One env per warp or per thread: plain branches.
+  constexpr bool kPred = G > 1 && G < 32;
   static_assert(VPT * G >= V, "shape does not hold 22 vehicles");
 
   const int lane = threadIdx.x & 31;
@@ -94,7 +123,7 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   const int E = P.n_envs;
   const int e_raw = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * EPW + es;
   const bool valid = e_raw < E && (A.mask == nullptr || A.mask[e_raw < E ? e_raw : 0] != 0);
-  if (!__any_sync(0xffffffffu, valid)) return;
+  if (!__any_sync(FULL, valid)) return;   // warp-uniform: all 32 lanes stay together below
   const int e = e_raw < E ? e_raw : E - 1;
   unsigned gmask = 0;
 #pragma unroll
@@ -124,8 +153,8 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
     v[i] = ok ? B.vel[(size_t)(base + i) * E + e] : T(0);
   }
   // first vehicle of the next thread = leader of my last vehicle (vehicle 0 for the RL thread)
-  T x_nf = (G == 1) ? x[0] : shfl(x[0], lane_next, gmask);
-  T v_nf = (G == 1) ? v[0] : shfl(v[0], lane_next, gmask);
+  T x_nf = (G == 1) ? x[0] : __shfl_sync(FULL, x[0], lane_next);
+  T v_nf = (G == 1) ? v[0] : __shfl_sync(FULL, v[0], lane_next);
   auto update_headways = [&]() {  // k.update: vehicle/traci.py:218-250
     FS_SLOTS(i) {
       T xl;
@@ -156,18 +185,22 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
 
   float st_rew = 0.f, st_v = 0.f, st_v2 = 0.f;
   int st_cr = 0;
-  const bool w_obs = valid && A.obs_seq != nullptr && (!po || is_rl);
-  const bool w_rew = valid && is_rl && A.reward_seq != nullptr;
-  const bool w_done = valid && is_rl && A.done_seq != nullptr;
-  T* obs_k = A.obs_seq + (w_obs ? (size_t)e * P.obs_dim : 0);
-  T* rew_k = A.reward_seq + (w_rew ? e : 0);
-  uint8_t* done_k = A.done_seq + (w_done ? e : 0);
-  const size_t obs_stride = (size_t)E * P.obs_dim;
-  const bool st_on = A.accumulate_stats && valid;
+  // per-step outputs: a missing sequence is redirected to the env's last-step
+  // slot with stride 0 (it ends up holding the last step's value, which is what
+  // the epilogue stores there anyway), so one predicate guards all stores
+  const bool seq_on = !(kVar & 4) &&
+                      (A.obs_seq != nullptr || A.reward_seq != nullptr || A.done_seq != nullptr);
+  const bool wr = valid && is_rl;
+  T* const obs_b = A.obs_seq ? A.obs_seq + (size_t)e * P.obs_dim : B.obs + (size_t)e * P.obs_dim;
+  T* const rew_b = A.reward_seq ? A.reward_seq + e : B.reward + e;
+  uint8_t* const done_b = A.done_seq ? A.done_seq + e : B.done + e;
+  const unsigned obs_st = A.obs_seq ? (unsigned)E * (unsigned)P.obs_dim : 0u;   // elements per step
+  const unsigned rew_st = A.reward_seq ? (unsigned)E : 0u, done_st = A.done_seq ? (unsigned)E : 0u;
 
   auto po_obs = [&](T& o0, T& o1, T& o2) {  // WaveAttenuationPOEnv.get_state, wave_attenuation.py:248-269
     const T xr = x[RL_SLOT], vr = v[RL_SLOT];
-    o0 = N::div(vr, T(15)); o1 = N::div(v_nf - vr, T(15));
+    if (kF32) { o0 = vr * T(1.0 / 15.0); o1 = (v_nf - vr) * T(1.0 / 15.0); }
+    else { o0 = N::div(vr, T(15)); o1 = N::div(v_nf - vr, T(15)); }
     o2 = kF32 ? fwd_dist(x_nf, xr, C) * inv_obs_len : N::div(fwd_dist(x_nf, xr, C), obs_len);
   };
   auto full_obs = [&](T* o) {  // WaveAttenuationEnv.get_state, wave_attenuation.py:141-148
@@ -177,102 +210,139 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
     }
   };
 
-  T ac[UNR], an[UNR];
-  int j0 = kTimeNoise ? (tc & 3) : 0;   // phase of the first (possibly partial) block
-  int kb = -j0;                         // launch-relative step of the block's slot 0
+  // One pass per phase of the 4-step noise block (tc & 3) that occurs in this
+  // warp: a pass advances the envs of that phase through all K steps with the
+  // block loop aligned to their time counters; the other envs are predicated
+  // off. All envs of a warp share the phase unless they were reset at different
+  // times, so normally exactly one pass runs.
+  int my_phase = kTimeNoise ? (tc & 3) : 0;
+  if (kTimeNoise && G < 32) {
+    // frozen envs (done: their time counter stopped at some other phase) ride
+    // along with the first live phase of the warp instead of costing a pass
+    unsigned live_ph = 0;
 #pragma unroll
-  for (int j = 0; j < UNR; ++j) { ac[j] = T(0); an[j] = (kAct && is_rl) ? ld_act(kb + j) : T(0); }
+    for (int ph = 0; ph < 4; ++ph)
+      if (__any_sync(FULL, !done && my_phase == ph)) live_ph |= 1u << ph;
+    if (done) my_phase = live_ph ? __ffs(live_ph) - 1 : 0;
+  }
+#pragma unroll 1
+  for (int ph = 0; ph < (kTimeNoise ? 4 : 1); ++ph) {
+    const bool sel = my_phase == ph;
+    if (kTimeNoise && !__any_sync(FULL, sel)) continue;
+    T ac[UNR], an[UNR];
+    int j0 = ph;        // first (possibly partial) block starts at slot j0
+    int kb = -j0;       // launch-relative step of the block's slot 0
+#pragma unroll
+    for (int j = 0; j < UNR; ++j) { ac[j] = T(0); an[j] = (kAct && is_rl) ? ld_act(kb + j) : T(0); }
 
-  while (kb < K) {
-    if (kAct) {
+#pragma unroll 1
+    while (kb < K) {
+      if (kAct) {
 #pragma unroll
-      for (int j = 0; j < UNR; ++j) ac[j] = an[j];
-      if (is_rl) {
+        for (int j = 0; j < UNR; ++j) ac[j] = an[j];
+        if (is_rl) {
 #pragma unroll
-        for (int j = 0; j < UNR; ++j) an[j] = ld_act(kb + UNR + j);
+          for (int j = 0; j < UNR; ++j) an[j] = ld_act(kb + UNR + j);
+        }
       }
-    }
-    T zn[kNoise ? NQ : 1][4];
-    if (kNoise && kTimeNoise && !done) {
+      T zn[kNoise ? NQ : 1][4];
+      if (kNoise && kTimeNoise && (kPred || !done)) {
 #pragma unroll
-      for (int q = 0; q < NQ; ++q) normal4_ck<T>((uint32_t)(tc >> 2), pc1 + q, pc2, pc3, zn[q]);
-    }
+        for (int q = 0; q < NQ; ++q) normal4_ck<T>((uint32_t)(tc >> 2), pc1 + q, pc2, pc3, zn[q]);
+      }
 #pragma unroll
-    for (int j = 0; j < UNR; ++j) {
-      if (j >= j0 && kb + j < K) {
-        if (!done) {
-          if (kNoise && !kTimeNoise) {  // base_controller.py:109-110
+      for (int j = 0; j < UNR; ++j) {
+        if (j >= j0 && kb + j < K) {    // warp-uniform
+          const bool live = sel && !done;
+          if (kPred || live) {
+            if (kNoise && !kTimeNoise) {  // base_controller.py:109-110
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) normal4_ck<T>((uint32_t)tc, pc1 + 4 * q, pc2, pc3, zn[q]);
-          }
-          // ---- controllers -> apply_acceleration -> Euler move (all read the old state)
-          const T v_lead_last = v_nf;
-          T act_abs = T(0);
-          FS_SLOTS(i) {
-            const bool ok = kExact || i < n_mine;
-            const T vi = v[i], hi = h[i];
-            T vl;
-            if (i + 1 < VPT) vl = (kExact || i + 1 < n_mine) ? v[i + 1 < VPT ? i + 1 : 0] : v_lead_last;
-            else vl = v_lead_last;
-            T a = idm_fast<T, true>(vi, vl, hi, pm);
-            if (kNoise) {
-              const T z = kTimeNoise ? zn[kNoise ? i : 0][j] : zn[kNoise ? (i >> 2) : 0][i & 3];
-              a = add(a, mul(VPT == 1 ? nz : P.noise, z));
+              for (int q = 0; q < NQ; ++q) normal4_ck<T>((uint32_t)tc, pc1 + 4 * q, pc2, pc3, zn[q]);
             }
-            if (i == RL_SLOT) {
-              if (kAct) {  // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
-                const T raw = ac[j];
-                const T a_c = N::min(N::max(raw, P.act_lo), P.act_hi);
-                act_abs = N::abs(P.clip_actions ? a_c : raw);
-                a = is_rl ? a_c : a;
-              } else if (VPT > 1) {  // un-commanded RL vehicle: restated simulator default model
-                if (is_rl) a = idm_fast<T, true>(vi, vl, hi, P.pb);
+            // ---- controllers -> apply_acceleration -> Euler move (all read the old state)
+            const T v_lead_last = v_nf;
+            T act_abs = T(0);
+            FS_SLOTS(i) {
+              const bool ok = (kExact || i < n_mine) && (!kPred || live);
+              const T vi = v[i], hi = h[i];
+              T vl;
+              if (i + 1 < VPT) vl = (kExact || i + 1 < n_mine) ? v[i + 1 < VPT ? i + 1 : 0] : v_lead_last;
+              else vl = v_lead_last;
+              T a = idm_fast<T, true>(vi, vl, hi, pm);
+              if (kNoise) {
+                const T z = kTimeNoise ? zn[kNoise ? i : 0][j] : zn[kNoise ? (i >> 2) : 0][i & 3];
+                a = add(a, mul(VPT == 1 ? nz : P.noise, z));
               }
+              if (i == RL_SLOT) {
+                if (kAct) {  // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
+                  const T raw = ac[j];
+                  const T a_c = N::min(N::max(raw, P.act_lo), P.act_hi);
+                  act_abs = N::abs(P.clip_actions ? a_c : raw);
+                  a = is_rl ? a_c : a;
+                } else if (VPT > 1) {  // un-commanded RL vehicle: restated simulator default model
+                  if (is_rl) a = idm_fast<T, true>(vi, vl, hi, P.pb);
+                }
+              }
+              const T vn = N::max(add(vi, mul(a, dt)), T(0));   // vehicle/traci.py:961-962
+              const T xn = wrap_fwd(add(x[i], mul(vn, dt)), C);  // simulator Euler move
+              if (ok) { v[i] = vn; x[i] = xn; }
             }
-            const T vn = N::max(add(vi, mul(a, dt)), T(0));   // vehicle/traci.py:961-962
-            const T xn = wrap_fwd(add(x[i], mul(vn, dt)), C);  // simulator Euler move
-            if (ok) { v[i] = vn; x[i] = xn; }
-          }
-          if (G > 1) { x_nf = shfl(x[0], lane_next, gmask); v_nf = shfl(v[0], lane_next, gmask); }
-          else { x_nf = x[0]; v_nf = v[0]; }
-          update_headways();
-          bool cr = false;
-          T sv = T(0);
-          float s2 = 0.f;
-          FS_SLOTS(i) if (kExact || i < n_mine) {
-            cr |= h[i] < crash_thr;
-            sv = add(sv, v[i]);
-            s2 = fmaf((float)v[i], (float)v[i], s2);
-          }
-          st_v += (float)sv; st_v2 += s2;
-          if (G > 1) cr = __any_sync(gmask, cr);
-          crash = cr;
-          tc += 1;
-          done = crash || tc >= P.t_end;
-          if (kAct) {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
-            sv = env_sum<T, G>(sv, gmask);
-            T r = kF32 ? sv * P.rew_scale : N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
-            if (act_abs > T(0)) r = add(r, mul(T(4), T(0) - act_abs));
-            reward = crash ? T(0) : r;
-          } else {
+            if (G > 1) { x_nf = __shfl_sync(FULL, x[0], lane_next); v_nf = __shfl_sync(FULL, v[0], lane_next); }
+            else { x_nf = x[0]; v_nf = v[0]; }
+            update_headways();
+            bool cr = false;
+            T sv = T(0);
+            float s2 = 0.f;
+            FS_SLOTS(i) if (kExact || i < n_mine) {
+              cr |= h[i] < crash_thr;
+              sv = add(sv, v[i]);
+              s2 = fmaf((float)v[i], (float)v[i], s2);
+            }
+            if (!kPred || live) { st_v += (float)sv; st_v2 += s2; }
+            if (G > 1) cr = (__ballot_sync(FULL, cr) & gmask) != 0u;
+            T r = T(0);
+            if (kAct) {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
+              if (kVar & 2) sv = sv * T(22);   // timing experiment: no reduction (wrong reward)
+              else if (kVar & 1) { for (int o = EPW; o < 32; o <<= 1) sv += __shfl_xor_sync(FULL, sv, o); }
+              else sv = env_sum_full<T, G>(sv, es);
+              r = kF32 ? sv * P.rew_scale : N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
+              if (act_abs > T(0)) r = add(r, mul(T(4), T(0) - act_abs));
+              r = cr ? T(0) : r;
+            }
+            if (!kPred || live) {
+              crash = cr;
+              tc += 1;
+              done = crash || tc >= P.t_end;
+              reward = r;
+              st_rew += (float)r; st_cr += cr ? 1 : 0;
+            } else if (sel) {
+              reward = T(0);
+            }
+          } else if (sel) {
             reward = T(0);
           }
-          st_rew += (float)reward; st_cr += crash ? 1 : 0;
-        } else {
-          reward = T(0);
+          // ---- per-step outputs
+          if (seq_on) {
+            const unsigned s = (unsigned)(kb + j);
+            if (po) {
+              if (wr && sel) {
+                T o0, o1, o2; po_obs(o0, o1, o2);
+                T* o = obs_b + (size_t)s * obs_st;
+                o[0] = o0; o[1] = o1; o[2] = o2;
+              }
+            } else if (valid && sel) {
+              full_obs(obs_b + (size_t)s * obs_st);
+            }
+            if (wr && sel) {
+              rew_b[(size_t)s * rew_st] = reward;
+              done_b[(size_t)s * done_st] = done ? 1 : 0;
+            }
+          }
         }
-        // ---- per-step outputs
-        if (w_obs) {
-          if (po) { T o0, o1, o2; po_obs(o0, o1, o2); obs_k[0] = o0; obs_k[1] = o1; obs_k[2] = o2; }
-          else full_obs(obs_k);
-          obs_k += obs_stride;
-        }
-        if (w_rew) { *rew_k = reward; rew_k += E; }
-        if (w_done) { *done_k = done ? 1 : 0; done_k += E; }
       }
+      kb += UNR;
+      j0 = 0;
     }
-    kb += UNR;
-    j0 = 0;
   }
 
   if (valid) {
@@ -293,6 +363,7 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   }
   if (A.accumulate_stats) {
     // stats[]: sum reward, sum v, sum v^2, vehicle-steps, env-steps, crashes
+    const bool st_on = valid;
     const int adv = st_on ? tc - tc0 : 0;
     double vals[6] = {(st_on && is_rl) ? (double)st_rew : 0.0, st_on ? (double)st_v : 0.0,
                       st_on ? (double)st_v2 : 0.0, (double)(adv * n_mine),
@@ -301,16 +372,36 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       double s = vals[q];
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
       if (lane == 0 && s != 0.0) atomicAdd(&sp[q], s);
     }
   }
 }
 
 // ---- host-side dispatch (one translation unit per dtype instantiates these)
+#ifdef FS_HOT_EXPERIMENTS
+template <typename T, int VPT, int G>
+static bool launch_hot_var(int var, int grid, int block, cudaStream_t st,
+                           const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
+  switch (var) {
+    case 1: ring1_hot_kernel<T, VPT, G, true, true, 1><<<grid, block, 0, st>>>(c, b, a); return true;
+    case 2: ring1_hot_kernel<T, VPT, G, true, true, 2><<<grid, block, 0, st>>>(c, b, a); return true;
+    case 4: ring1_hot_kernel<T, VPT, G, true, true, 4><<<grid, block, 0, st>>>(c, b, a); return true;
+    case 6: ring1_hot_kernel<T, VPT, G, true, true, 6><<<grid, block, 0, st>>>(c, b, a); return true;
+    default: return false;
+  }
+}
+#endif
+
 template <typename T, int VPT, int G>
 static cudaError_t launch_hot_shape(bool noise, bool act, int grid, int block, cudaStream_t st,
                                     const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
+#ifdef FS_HOT_EXPERIMENTS
+  if (sizeof(T) == 4 && noise && act && G >= 4) {
+    static const int var = getenv("FS_HOT_VAR") ? atoi(getenv("FS_HOT_VAR")) : 0;
+    if (var && launch_hot_var<T, VPT, G>(var, grid, block, st, c, b, a)) return cudaGetLastError();
+  }
+#endif
   if (noise) {
     if (act) ring1_hot_kernel<T, VPT, G, true, true><<<grid, block, 0, st>>>(c, b, a);
     else ring1_hot_kernel<T, VPT, G, true, false><<<grid, block, 0, st>>>(c, b, a);
