@@ -281,8 +281,7 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
       for (int i = 0; i < e->cfg.n_veh; ++i) n_rl += types[type_of_vehicle[i]].controller == FS_CTRL_RL;
       e->hot_ok = ok && n_rl == 1 &&
                   types[type_of_vehicle[e->cfg.n_veh - 1]].controller == FS_CTRL_RL &&
-                  (e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION ||
-                   e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO) && !e->cfg.record_views;
+                  e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO && !e->cfg.record_views;
     }
     if (ok) {
       const fs_vtype& s = types[ta];

@@ -1,6 +1,6 @@
 // fs_ring_hot.cuh — the c2 / c5 kernel: single-lane ring of V = 22 vehicles,
 // 21 IDM humans of one type followed by ONE RL vehicle at index V-1, observed
-// by WaveAttenuationEnv / WaveAttenuationPOEnv, no fail-safe, no views. This is
+// by WaveAttenuationPOEnv, no fail-safe, no views. This is
 // exactly what examples/exp_configs/rl/singleagent/singleagent_ring.py builds;
 // anything else runs on ring1_fast_kernel (fs_ring_fast.cuh) or ring1_kernel.
 //
@@ -36,8 +36,9 @@ struct PhiloxCK {
     for (int i = 0; i < 10; ++i) {
       const uint32_t k0 = 0xA4093822u + (uint32_t)i * 0x9E3779B9u;
       const uint32_t k1 = 0x299F31D0u + (uint32_t)i * 0xBB67AE85u;
-      const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
-      const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
+      unsigned long long p0, p1;   // one IMAD.WIDE.U32 each (a C++ 64-bit product adds a dead carry)
+      asm("mul.wide.u32 %0, %1, %2;" : "=l"(p0) : "r"(c0), "r"(0xD2511F53u));
+      asm("mul.wide.u32 %0, %1, %2;" : "=l"(p1) : "r"(c2), "r"(0xCD9E8D57u));
       const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
       const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
       c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
@@ -58,8 +59,9 @@ __device__ __forceinline__ void normal4_ck(uint32_t c0, uint32_t c1, uint32_t c2
     const float ra = sqrtf(-1.3862943611198906f * __log2f(u0));   // sqrt(-2 ln u)
     const float rb = sqrtf(-1.3862943611198906f * __log2f(u2));
     float s0, c0f, s1, c1f;
-    __sincosf(6.2831853071795865f * ((float)r[1] * k), &s0, &c0f);
-    __sincosf(6.2831853071795865f * ((float)r[3] * k), &s1, &c1f);
+    const float k2pi = 1.4629180792671596e-09f;   // 2 pi 2^-32
+    __sincosf((float)r[1] * k2pi, &s0, &c0f);
+    __sincosf((float)r[3] * k2pi, &s1, &c1f);
     z[0] = (T)(ra * c0f); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1f); z[3] = (T)(rb * s1);
   } else {
     const double k = 1.0 / 4294967296.0;
@@ -75,22 +77,16 @@ __device__ __forceinline__ void normal4_ck(uint32_t c0, uint32_t c1, uint32_t c2
 constexpr int kHotV = 22;
 
 // sum of `part` over the G threads of each env of the warp; every lane of the
-// warp must call it (full-mask collectives). fp32, <= 4 envs per warp: one
-// integer REDUX per env slot in 2^-20 m/s fixed point (|sum| < 2000 m/s);
-// otherwise an xor-shuffle tree over the group's lanes.
+// warp must call it (full-mask collectives). One env per warp in fp32: a single
+// integer REDUX in 2^-20 m/s fixed point (|sum| < 2000 m/s); otherwise an
+// xor-shuffle tree over the group's lanes (log2 G steps).
 template <typename T, int G>
 __device__ __forceinline__ T env_sum_full(T part, int es) {
   constexpr int EPW = 32 / G;
   if (G == 1) return part;
-  if (sizeof(T) == 4 && EPW <= 4) {
+  if (sizeof(T) == 4 && EPW == 1) {
     const int q = __float2int_rn((float)part * 1048576.0f);
-    int mine = 0;
-#pragma unroll
-    for (int s = 0; s < EPW; ++s) {
-      const int r = __reduce_add_sync(0xffffffffu, (EPW == 1 || es == s) ? q : 0);
-      mine = (EPW == 1 || es == s) ? r : mine;
-    }
-    return (T)((float)mine * 9.5367431640625e-07f);
+    return (T)((float)__reduce_add_sync(0xffffffffu, q) * 9.5367431640625e-07f);
   }
 #pragma unroll
   for (int o = EPW; o < 32; o <<= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
@@ -134,7 +130,6 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   const bool is_rl = g == RL_G;   // owns vehicle V-1: RL vehicle, writer of obs / reward / done
   const int lane_next = ((g >= RL_G) ? 0 : g + 1) * EPW + es;
   const int K = A.k_steps;
-  const bool po = P.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
 
   IdmRegs<T> pm = P.pa;
   T nz = P.noise;
@@ -191,10 +186,10 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   const bool seq_on = !(kVar & 4) &&
                       (A.obs_seq != nullptr || A.reward_seq != nullptr || A.done_seq != nullptr);
   const bool wr = valid && is_rl;
-  T* const obs_b = A.obs_seq ? A.obs_seq + (size_t)e * P.obs_dim : B.obs + (size_t)e * P.obs_dim;
+  T* const obs_b = A.obs_seq ? A.obs_seq + (size_t)e * 3 : B.obs + (size_t)e * 3;
   T* const rew_b = A.reward_seq ? A.reward_seq + e : B.reward + e;
   uint8_t* const done_b = A.done_seq ? A.done_seq + e : B.done + e;
-  const unsigned obs_st = A.obs_seq ? (unsigned)E * (unsigned)P.obs_dim : 0u;   // elements per step
+  const unsigned obs_st = A.obs_seq ? (unsigned)E * 3u : 0u;   // elements per step
   const unsigned rew_st = A.reward_seq ? (unsigned)E : 0u, done_st = A.done_seq ? (unsigned)E : 0u;
 
   auto po_obs = [&](T& o0, T& o1, T& o2) {  // WaveAttenuationPOEnv.get_state, wave_attenuation.py:248-269
@@ -203,13 +198,6 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
     else { o0 = N::div(vr, T(15)); o1 = N::div(v_nf - vr, T(15)); }
     o2 = kF32 ? fwd_dist(x_nf, xr, C) * inv_obs_len : N::div(fwd_dist(x_nf, xr, C), obs_len);
   };
-  auto full_obs = [&](T* o) {  // WaveAttenuationEnv.get_state, wave_attenuation.py:141-148
-    FS_SLOTS(i) if (kExact || i < n_mine) {
-      o[base + i] = kF32 ? v[i] * P.inv_speed_limit : N::div(v[i], P.speed_limit);
-      o[V + base + i] = kF32 ? x[i] * inv_C : N::div(x[i], C);
-    }
-  };
-
   // One pass per phase of the 4-step noise block (tc & 3) that occurs in this
   // warp: a pass advances the envs of that phase through all K steps with the
   // block loop aligned to their time counters; the other envs are predicated
@@ -240,9 +228,15 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
       if (kAct) {
 #pragma unroll
         for (int j = 0; j < UNR; ++j) ac[j] = an[j];
-        if (is_rl) {
+        if (is_rl) {   // actions of the next block, requested one block ahead
+          if (kb >= 0 && kb + 2 * UNR <= K) {   // whole next block inside the launch: no clamping
+            const T* q = act_p + (size_t)(unsigned)(kb + UNR) * (unsigned)E;
 #pragma unroll
-          for (int j = 0; j < UNR; ++j) an[j] = ld_act(kb + UNR + j);
+            for (int j = 0; j < UNR; ++j) an[j] = __ldg(q + (size_t)((unsigned)j * (unsigned)E));
+          } else {
+#pragma unroll
+            for (int j = 0; j < UNR; ++j) an[j] = ld_act(kb + UNR + j);
+          }
         }
       }
       T zn[kNoise ? NQ : 1][4];
@@ -324,16 +318,10 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
           // ---- per-step outputs
           if (seq_on) {
             const unsigned s = (unsigned)(kb + j);
-            if (po) {
-              if (wr && sel) {
-                T o0, o1, o2; po_obs(o0, o1, o2);
-                T* o = obs_b + (size_t)s * obs_st;
-                o[0] = o0; o[1] = o1; o[2] = o2;
-              }
-            } else if (valid && sel) {
-              full_obs(obs_b + (size_t)s * obs_st);
-            }
             if (wr && sel) {
+              T o0, o1, o2; po_obs(o0, o1, o2);
+              T* o = obs_b + (size_t)s * obs_st;
+              o[0] = o0; o[1] = o1; o[2] = o2;
               rew_b[(size_t)s * rew_st] = reward;
               done_b[(size_t)s * done_st] = done ? 1 : 0;
             }
@@ -346,10 +334,8 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   }
 
   if (valid) {
-    T* ol = B.obs + (size_t)e * P.obs_dim;
-    if (po) {
-      if (is_rl) { T o0, o1, o2; po_obs(o0, o1, o2); ol[0] = o0; ol[1] = o1; ol[2] = o2; }
-    } else full_obs(ol);
+    T* ol = B.obs + (size_t)e * 3;
+    if (is_rl) { T o0, o1, o2; po_obs(o0, o1, o2); ol[0] = o0; ol[1] = o1; ol[2] = o2; }
     FS_SLOTS(i) if (kExact || i < n_mine) {
       B.pos[(size_t)(base + i) * E + e] = x[i];
       B.vel[(size_t)(base + i) * E + e] = v[i];
