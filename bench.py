@@ -52,6 +52,7 @@ def parse():
     ap.add_argument('--noise', type=float, default=0.2,
                     help='IDM accel noise std (0.2 in singleagent_ring.py; 0 = parity setting)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--envs', type=int, default=0, help='development: override envs per GPU')
     ap.add_argument('--only-fused', action='store_true',
                     help='development: time only the fused device-resident pass')
     ap.add_argument('--cpu-envs-per-core', type=int, default=2)
@@ -248,7 +249,7 @@ def run_b200(a):
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 
     wl = WORKLOADS[a.workload]
-    E, K, W, F = wl['n_envs'], a.steps, a.warmup, max(1, min(a.fuse, a.steps))
+    E, K, W, F = (a.envs or wl['n_envs']), a.steps, a.warmup, max(1, min(a.fuse, a.steps))
     types, tov, kw = wl['builder'](noise=a.noise)
     kw['horizon'] = max(kw['horizon'], K)
     env_id_base, E = SH.weak_shard(E, rank)   # weak scaling: E envs on every GPU
@@ -282,7 +283,31 @@ def run_b200(a):
         for s in range(n_steps):
             eng.step_ptr(pa + s * sa, 1, po_ + s * so, pr + s * sr, pd + s * sd)
 
+    host_out = {}
+
+    def host_bufs(n_steps):
+        """pinned result buffers, allocated once (outside every timed region)"""
+        if not host_out:
+            n = max(K, W)
+            host_out.update(obs=torch.empty(n, E, env.obs_dim, dtype=td).pin_memory(),
+                            rew=torch.empty(n, E, dtype=td).pin_memory(),
+                            done=torch.empty(n, E, dtype=torch.uint8).pin_memory())
+        return host_out['obs'], host_out['rew'], host_out['done']
+
+    if not a.only_fused:
+        host_bufs(K)
+
     def host_pass(n_steps):
+        """e2e, open loop: pinned host actions in, every step's obs/reward/done back in
+        pinned host memory; calls are pipelined (fs_step_host_async), one wait at the end."""
+        o, r, d = host_bufs(n_steps)
+        for s in range(0, n_steps, F):
+            k = min(F, n_steps - s)
+            env.rollout_host_async(act_host[s:s + k], o[s:s + k], r[s:s + k], d[s:s + k])
+        env.wait()
+
+    def host_sync_pass(n_steps):
+        """e2e, closed-loop cadence: every call blocks until its results are on the host."""
         for s in range(0, n_steps, F):
             k = min(F, n_steps - s)
             env.rollout_host(act_host[s:s + k])
@@ -291,11 +316,11 @@ def run_b200(a):
         for s in range(n_steps):
             env.rollout_host(act_host[s:s + 1])
 
-    def timed(fn, n_steps):
+    def timed(fn, n_steps, warm=None):
         """reset -> W warm-up steps -> reset -> barrier -> time n_steps -> barrier.
         Returns (ms max over ranks, vehicle-steps summed over ranks, launches on this rank)."""
         env.reset()
-        fn(min(W, n_steps))
+        fn(warm or min(W, n_steps))
         env.reset()
         eng.stats(reset=True)
         barrier()
@@ -317,10 +342,12 @@ def run_b200(a):
     sampler = ClockSampler(local) if rank == 0 else None
     fused = timed(fused_pass, K)
     if a.only_fused:
-        single = host = host1 = fused
+        single = host = host_sync = host1 = fused
     else:
         single = timed(single_pass, K)
-        host = timed(host_pass, K)
+        # host passes warm up over the whole pinned buffers (first DMA into a pinned page is slow)
+        host = timed(host_pass, K, warm=K)
+        host_sync = timed(host_sync_pass, K, warm=K)
         host1 = timed(host_single_pass, min(K, 1000))
     clocks = sampler.stop() if sampler else None
     if rank != 0:
@@ -367,8 +394,14 @@ def run_b200(a):
         'single_step': {'value': vps(single), 'unit': 'vehicle-steps/s',
                         'ms_per_step': single['ms'] / K, 'launches': single['launches']},
         'e2e': {'value': vps(host), 'unit': 'vehicle-steps/s', 'h2d_bytes_per_step': h2d / F,
-                'd2h_bytes_per_step': d2h / F, 'api': 'B200VecEnv.rollout_host, %d steps per call, '
-                'pinned host buffers' % F, 'ms_per_step': host['ms'] / K},
+                'd2h_bytes_per_step': d2h / F, 'api': 'B200VecEnv.rollout_host_async -> '
+                'fs_step_host_async, %d steps per call, pinned host buffers, upload / kernel / '
+                'download of consecutive calls overlapped, one wait at the end' % F,
+                'ms_per_step': host['ms'] / K},
+        'e2e_blocking': {'value': vps(host_sync), 'unit': 'vehicle-steps/s',
+                         'ms_per_step': host_sync['ms'] / K,
+                         'api': 'B200VecEnv.rollout_host -> fs_step_host, %d steps per call, every '
+                                'call waits for its results (closed-loop cadence)' % F},
         'e2e_single_step': {'value': vps(host1), 'unit': 'vehicle-steps/s',
                             'ms_per_step': host1['ms'] / min(K, 1000),
                             'api': 'B200VecEnv.rollout_host, 1 step per call'},

@@ -81,6 +81,7 @@ SYMBOLS = [
     ('fs_reset', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_step_host_async', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_buffers', C.c_int, [C.c_void_p, C.POINTER(FsViews)]),
     ('fs_set_state', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_stats', C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int]),

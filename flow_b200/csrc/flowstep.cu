@@ -54,6 +54,16 @@ struct fs_engine {
   void *h_act = nullptr, *h_obs = nullptr, *h_rew = nullptr;
   uint8_t* h_done = nullptr;
   size_t h_act_cap = 0, h_obs_cap = 0, h_rew_cap = 0, h_done_cap = 0;
+  // fs_step_host_async: three staging slots, copy streams and events, so that the
+  // H2D of call n+1, the kernel of call n and the D2H of call n-1 overlap
+  struct Slot {
+    void *act = nullptr, *obs = nullptr, *rew = nullptr, *done = nullptr;
+    size_t act_cap = 0, obs_cap = 0, rew_cap = 0, done_cap = 0;
+    cudaEvent_t up = nullptr, run = nullptr, down = nullptr;
+    bool used = false;
+  } slots[3];
+  cudaStream_t up_stream = nullptr, down_stream = nullptr;
+  int64_t async_calls = 0;
   // parameter tables (one of the two is used)
   fs::Cfg<float> cf;
   fs::Cfg<double> cd;
@@ -175,6 +185,13 @@ extern "C" void fs_destroy(fs_engine* e) {
   if (!e) return;
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  if (e->down_stream) { cudaStreamSynchronize(e->down_stream); cudaStreamDestroy(e->down_stream); }
+  if (e->up_stream) { cudaStreamSynchronize(e->up_stream); cudaStreamDestroy(e->up_stream); }
+  for (auto& sl : e->slots) {
+    if (sl.up) cudaEventDestroy(sl.up);
+    if (sl.run) cudaEventDestroy(sl.run);
+    if (sl.down) cudaEventDestroy(sl.down);
+  }
   for (void* p : e->allocs) if (p) cudaFree(p);
   if (e->stream && e->own_stream) cudaStreamDestroy(e->stream);
   delete e;
@@ -603,6 +620,66 @@ extern "C" int fs_step_host(fs_engine* e, const void* actions, int k, void* obs_
   return FS_OK;
 }
 
+extern "C" int fs_step_host_async(fs_engine* e, const void* actions, int k, void* obs_seq,
+                                  void* reward_seq, uint8_t* done_seq) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_step_host_async: call fs_set_types first");
+  if (k < 1) return fail(e, FS_EINVAL, "fs_step_host_async: k must be >= 1");
+  cudaSetDevice(e->cfg.device);
+  if (!e->up_stream) {
+    FS_CUDA(e, cudaStreamCreateWithFlags(&e->up_stream, cudaStreamNonBlocking));
+    FS_CUDA(e, cudaStreamCreateWithFlags(&e->down_stream, cudaStreamNonBlocking));
+    for (auto& sl : e->slots) {
+      FS_CUDA(e, cudaEventCreateWithFlags(&sl.up, cudaEventDisableTiming));
+      FS_CUDA(e, cudaEventCreateWithFlags(&sl.run, cudaEventDisableTiming));
+      FS_CUDA(e, cudaEventCreateWithFlags(&sl.down, cudaEventDisableTiming));
+    }
+  }
+  fs_engine::Slot& sl = e->slots[e->async_calls % 3];
+  const size_t E = e->cfg.n_envs, ts = tsize(e);
+  const size_t nb_act = (size_t)k * e->act_dim * E * ts, nb_obs = (size_t)k * E * e->obs_dim * ts,
+               nb_rew = (size_t)k * E * ts, nb_done = (size_t)k * E;
+  int rc;
+  const bool want_act = actions && e->act_dim > 0;
+  if ((want_act && nb_act > sl.act_cap) || (obs_seq && nb_obs > sl.obs_cap) ||
+      (reward_seq && nb_rew > sl.rew_cap) || (done_seq && nb_done > sl.done_cap)) {
+    // (re)size ALL slots at once (cudaMalloc synchronises the device: do it on the
+    // first call of a size, not once per slot in the middle of a pipelined run)
+    FS_CUDA(e, cudaDeviceSynchronize());
+    for (auto& q : e->slots) {
+      if (want_act && (rc = grow(e, &q.act, &q.act_cap, nb_act)) != FS_OK) return rc;
+      if (obs_seq && (rc = grow(e, &q.obs, &q.obs_cap, nb_obs)) != FS_OK) return rc;
+      if (reward_seq && (rc = grow(e, &q.rew, &q.rew_cap, nb_rew)) != FS_OK) return rc;
+      if (done_seq && (rc = grow(e, &q.done, &q.done_cap, nb_done)) != FS_OK) return rc;
+    }
+  }
+  // the slot's previous results must have left the device before it is reused
+  if (sl.used) FS_CUDA(e, cudaStreamWaitEvent(e->up_stream, sl.down, 0));
+  void* d_act = nullptr;
+  if (want_act) {
+    FS_CUDA(e, cudaMemcpyAsync(sl.act, actions, nb_act, cudaMemcpyHostToDevice, e->up_stream));
+    d_act = sl.act;
+  }
+  FS_CUDA(e, cudaEventRecord(sl.up, e->up_stream));
+  FS_CUDA(e, cudaStreamWaitEvent(e->stream, sl.up, 0));
+  if (sl.used) FS_CUDA(e, cudaStreamWaitEvent(e->stream, sl.down, 0));  // outputs of the slot's last use
+  rc = fs_step(e, d_act, k, obs_seq ? sl.obs : nullptr, reward_seq ? sl.rew : nullptr,
+               done_seq ? (uint8_t*)sl.done : nullptr);
+  if (rc != FS_OK) return rc;
+  FS_CUDA(e, cudaEventRecord(sl.run, e->stream));
+  FS_CUDA(e, cudaStreamWaitEvent(e->down_stream, sl.run, 0));
+  if (obs_seq)
+    FS_CUDA(e, cudaMemcpyAsync(obs_seq, sl.obs, nb_obs, cudaMemcpyDeviceToHost, e->down_stream));
+  if (reward_seq)
+    FS_CUDA(e, cudaMemcpyAsync(reward_seq, sl.rew, nb_rew, cudaMemcpyDeviceToHost, e->down_stream));
+  if (done_seq)
+    FS_CUDA(e, cudaMemcpyAsync(done_seq, sl.done, nb_done, cudaMemcpyDeviceToHost, e->down_stream));
+  FS_CUDA(e, cudaEventRecord(sl.down, e->down_stream));
+  sl.used = true;
+  e->async_calls++;
+  return FS_OK;
+}
+
 extern "C" int fs_buffers(fs_engine* e, fs_views* out) {
   if (!e || !out) return FS_EINVAL;
   memset(out, 0, sizeof(*out));
@@ -675,7 +752,9 @@ extern "C" int fs_stats(fs_engine* e, double* host_out, int n, int reset) {
 extern "C" int fs_sync(fs_engine* e) {
   if (!e) return FS_EINVAL;
   cudaSetDevice(e->cfg.device);
+  if (e->up_stream) FS_CUDA(e, cudaStreamSynchronize(e->up_stream));
   FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  if (e->down_stream) FS_CUDA(e, cudaStreamSynchronize(e->down_stream));
   return FS_OK;
 }
 

@@ -228,7 +228,8 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
       if (kAct) {
 #pragma unroll
         for (int j = 0; j < UNR; ++j) ac[j] = an[j];
-        if (is_rl) {   // actions of the next block, requested one block ahead
+        if (kVar & 8) { for (int j = 0; j < UNR; ++j) an[j] = T(0.1); }   // timing experiment: no action loads
+        else if (is_rl) {   // actions of the next block, requested one block ahead
           if (kb >= 0 && kb + 2 * UNR <= K) {   // whole next block inside the launch: no clamping
             const T* q = act_p + (size_t)(unsigned)(kb + UNR) * (unsigned)E;
 #pragma unroll
@@ -374,6 +375,8 @@ static bool launch_hot_var(int var, int grid, int block, cudaStream_t st,
     case 2: ring1_hot_kernel<T, VPT, G, true, true, 2><<<grid, block, 0, st>>>(c, b, a); return true;
     case 4: ring1_hot_kernel<T, VPT, G, true, true, 4><<<grid, block, 0, st>>>(c, b, a); return true;
     case 6: ring1_hot_kernel<T, VPT, G, true, true, 6><<<grid, block, 0, st>>>(c, b, a); return true;
+    case 8: ring1_hot_kernel<T, VPT, G, true, true, 8><<<grid, block, 0, st>>>(c, b, a); return true;
+    case 12: ring1_hot_kernel<T, VPT, G, true, true, 12><<<grid, block, 0, st>>>(c, b, a); return true;
     default: return false;
   }
 }

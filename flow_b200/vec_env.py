@@ -71,6 +71,20 @@ class B200VecEnv:
                                     rew.ctypes.data, done.ctypes.data))
         return obs, rew, done
 
+    def rollout_host_async(self, actions_host, obs_out, rew_out, done_out):
+        """Pipelined open-loop rollout: enqueue K = actions_host.shape[0] fused steps
+        with PINNED host tensors (actions [K, act_dim, E] in; obs [K, E, obs_dim],
+        reward [K, E], done [K, E] out) and return at once; the upload of the next
+        call overlaps this call's kernel and the previous call's download
+        (fs_step_host_async). Call `wait()` before reading the outputs."""
+        e = self.engine
+        k = int(actions_host.shape[0])
+        e._check(e.lib.fs_step_host_async(e.h, actions_host.data_ptr(), k, obs_out.data_ptr(),
+                                          rew_out.data_ptr(), done_out.data_ptr()))
+
+    def wait(self):
+        self.engine.sync()
+
     def step_host(self, actions_host):
         a = np.asarray(actions_host).reshape(1, self.act_dim, self.n_envs)
         obs, rew, done = self.rollout_host(a, 1)

@@ -15,7 +15,8 @@
  *                            flow/envs/base.py:414-560,
  *                            flow/envs/ring/wave_attenuation.py:157-210,
  *                            flow/core/kernel/network/base.py:263-391
- *   fs_step / fs_step_host   Env.step (controllers, fail-safes, apply_acceleration,
+ *   fs_step / fs_step_host / fs_step_host_async
+ *                            Env.step (controllers, fail-safes, apply_acceleration,
  *                            simulation_step, k.update, get_state, compute_reward)
  *                            flow/envs/base.py:294-412
  *   fs_buffers               KernelVehicle getters (get_speed, get_position,
@@ -201,6 +202,15 @@ int fs_step(fs_engine* e, const void* actions, int k, void* obs_seq,
  * steps, copies obs/reward/done of every step back, and synchronises. */
 int fs_step_host(fs_engine* e, const void* actions, int k, void* obs_seq,
                  void* reward_seq, uint8_t* done_seq);
+
+/* Pipelined form of fs_step_host for open-loop rollouts (the action sequence
+ * is known up front): enqueues H2D actions -> k fused steps -> D2H results on
+ * three internal streams and returns without waiting, so the upload of call
+ * n+1, the kernel of call n and the download of call n-1 overlap (three
+ * staging slots). The HOST buffers must be pinned for the copies to overlap and
+ * must stay valid and untouched until fs_sync(), which waits for everything. */
+int fs_step_host_async(fs_engine* e, const void* actions, int k, void* obs_seq,
+                       void* reward_seq, uint8_t* done_seq);
 
 int fs_buffers(fs_engine* e, fs_views* out);
 

@@ -152,3 +152,36 @@ def test_hot_noise_is_invariant_to_fusing_and_well_distributed(shape, monkeypatc
     c_time = np.mean(zz[:-1] * zz[1:])            # successive steps (same Philox call for VPT <= 4)
     c_env = np.mean(zz[:, :, :-1] * zz[:, :, 1:])
     assert max(abs(c_veh), abs(c_time), abs(c_env)) < 0.02
+
+
+def test_pipelined_host_rollout_equals_blocking():
+    """fs_step_host_async (three staging slots, overlapped copies) delivers the
+    same bytes as the blocking fs_step_host, for several calls in flight and a
+    call larger than the previous staging size."""
+    import torch
+    from flow_b200.vec_env import B200VecEnv
+    from flow_b200 import workloads as W
+    types, tov, kw = W.ring_c2(noise=0.2)
+    E = 300
+    a = B200VecEnv(types, tov, E, dtype='f32', seed=3, **kw)
+    b = B200VecEnv(types, tov, E, dtype='f32', seed=3, **kw)
+    a.reset(); b.reset()
+    chunks = [10, 10, 10, 25, 3, 40, 10]
+    K = sum(chunks)
+    act = (torch.rand(K, 1, E) * 2 - 1).pin_memory()
+    obs = torch.empty(K, E, 3).pin_memory()
+    rew = torch.empty(K, E).pin_memory()
+    done = torch.empty(K, E, dtype=torch.uint8).pin_memory()
+    s = 0
+    for k in chunks:
+        a.rollout_host_async(act[s:s + k], obs[s:s + k], rew[s:s + k], done[s:s + k])
+        s += k
+    a.wait()
+    s = 0
+    for k in chunks:
+        o, r, d = b.rollout_host(act[s:s + k])
+        assert np.array_equal(o, obs[s:s + k].numpy()), s
+        assert np.array_equal(r, rew[s:s + k].numpy()), s
+        assert np.array_equal(d, done[s:s + k].numpy()), s
+        s += k
+    assert torch.equal(a.engine.pos, b.engine.pos)
