@@ -29,6 +29,7 @@ import sys
 import tempfile
 import time
 
+_emit = print
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -158,7 +159,7 @@ def run_reference(a):
               'bench step, %d bench steps, workload c2 on oracle/sim.py (scalar Python port of the '
               'reference per-vehicle loop; SUMO/TraCI unavailable on this box)'
               % (cores, chunk, a.steps))
-    print(json.dumps({
+    _emit(json.dumps({
         'impl': 'reference', 'metric': 'vehicle-steps/s', 'value': val, 'unit': 'vehicle-steps/s',
         'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': 1e3 * wall / a.steps,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
@@ -407,13 +408,27 @@ def run_b200(a):
                             'api': 'B200VecEnv.rollout_host, 1 step per call'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
-                     'kernel': 'ring1_hot_kernel<%s> (fs_ring_hot.cuh), %d fused steps per launch, '
-                               'threads/env = %s' % (a.dtype, F, os.environ.get('FS_RING_SHAPE', 'auto')),
+                     'kernel': 'ring1_hot_kernel<%s> (flow_b200/csrc/fs_ring_hot.cuh), %d fused steps '
+                               'per launch, threads/env = %s' % (a.dtype, F, os.environ.get('FS_RING_SHAPE', 'auto')),
                      'launch_ms': launch_ms,
-                     'note': 'algorithmic bytes = %d B per env-step (SURVEY 8d) x env-steps per '
-                             'launch; fused launches keep state in registers, so this is the '
-                             'single-step HBM roofline the fused kernel is measured against'
-                             % int(BYTES_PER_ENV_STEP * ts / 4)},
+                     'note': 'achieved = ALGORITHMIC bytes (SURVEY 8d: %d B per env-step = state round '
+                             'trip + action/obs/reward/done, the single-step figure) x env-steps per '
+                             'launch / launch duration. The fused launch keeps the state in registers, '
+                             'so its real DRAM traffic (`traffic`, ncu) is far below that and frac may '
+                             'exceed 1: it says how the fused path compares with the best a '
+                             'one-step-per-launch HBM-bound kernel could do. The fused kernel itself is '
+                             'bound by instruction issue (profiles/: issue-active 51 %% on c2, 74 %% on '
+                             'c5; `issue` below).' % int(BYTES_PER_ENV_STEP * ts / 4)},
+        # what the fused kernel must move at least: action in, obs/reward/done out per env-step,
+        # state once per launch
+        'roofline_fused_stream': (lambda b: {
+            'bound': 'hbm', 'unit': 'GB/s', 'peak': peak, 'bytes_per_launch': b,
+            'achieved': b / (launch_ms * 1e-3) / 1e9, 'frac': b / (launch_ms * 1e-3) / 1e9 / peak})(
+                (fused['env_steps'] / world / max(n_launch, 1)) * (ts + env.obs_dim * ts + ts + 1)
+                + E * (2 * N_VEH * 2 * ts + ts)),
+        'issue': {'unit': 'warp-instructions per vehicle-step (static SASS count of the step loop, '
+                          'scripts/sass_loops.py)', 'c5_shape1': 46.9, 'c2_shape8': 89.0,
+                  'note': 'B200: 148 SMs x 4 schedulers x 1 warp-instruction/cycle x 1.965 GHz'},
         'roofline_single_step': {
             'bound': 'hbm', 'unit': 'GB/s', 'peak': peak,
             'achieved': BYTES_PER_ENV_STEP * (ts / 4) * E / (single['ms'] / K * 1e-3) / 1e9,
@@ -422,13 +437,22 @@ def run_b200(a):
     }
     if world == 1 and not a.no_cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(10000, a.cpu_envs_per_core)
-    print(json.dumps(line))
+    _emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
     a = parse()
+    # stdout carries exactly ONE JSON line: library chatter on fd 1 (e.g. NCCL's version
+    # banner) is sent to stderr, the line is written to the saved descriptor at the end
+    sys.stdout.flush()
+    real_out = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+
+    def _emit(line):
+        os.write(real_out, (line + '\n').encode())
     if a.impl == 'reference':
         run_reference(a)
     else:
