@@ -68,7 +68,9 @@ struct fs_engine {
   fs::Cfg<float> cf;
   fs::Cfg<double> cd;
   std::vector<void*> allocs;
-  bool env_needs_rl() const { return cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO; }
+  bool env_needs_rl() const {
+    return cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO || cfg.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO;
+  }
 };
 
 #define FS_CUDA(e, call)                                                        \
@@ -115,6 +117,7 @@ static int obs_dim_for(const fs_config& c) {
     case FS_ENV_WAVE_ATTENUATION_PO: return 3;
     case FS_ENV_LANE_CHANGE_ACCEL: return 3 * c.n_veh;
     case FS_ENV_HIGHWAY: return 2 * c.n_veh;
+    case FS_ENV_MA_WAVE_ATTENUATION_PO: return 3 * c.n_veh;  // capacity; 3 * n_rl after fs_set_types
     default: return -1;
   }
 }
@@ -256,6 +259,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
   const bool lc_env = g.env_kind == FS_ENV_LANE_CHANGE_ACCEL ||
                       g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
   c.act_dim = lc_env ? 2 * n_rl : n_rl;
+  if (g.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO) { e->obs_dim = 3 * n_rl; c.obs_dim = e->obs_dim; }
   e->n_rl = n_rl;
   e->act_dim = c.act_dim;
 }
@@ -285,8 +289,15 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     for (int i = 0; ok && i < e->cfg.n_veh; ++i) {
       const int t = type_of_vehicle[i];
       const fs_vtype& s = types[t];
-      if (s.controller == FS_CTRL_RL) { if (tb >= 0 && tb != t) ok = false; tb = t; }
-      else { if (ta >= 0 && ta != t) ok = false; ta = t; }
+      // several type rows are fine as long as they are byte-identical (e.g. the
+      // "human_0" / "human_1" groups of examples/exp_configs/rl/multiagent/multiagent_ring.py)
+      if (s.controller == FS_CTRL_RL) {
+        if (tb >= 0 && tb != t && memcmp(&types[tb], &s, sizeof(s)) != 0) ok = false;
+        tb = t;
+      } else {
+        if (ta >= 0 && ta != t && memcmp(&types[ta], &s, sizeof(s)) != 0) ok = false;
+        ta = t;
+      }
       if (s.length != types[type_of_vehicle[0]].length) ok = false;
       if (s.controller == FS_CTRL_IDM && s.p[4] != 4.0) ok = false;
     }

@@ -167,6 +167,7 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
   T reward = B.reward[e];
   const bool have_act = A.actions != nullptr;
   const bool po = cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
+  const bool ma = cfg.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO;
 
   // WaveAttenuationPO: who holds the RL vehicle and its leader
   int rl_veh = 0;
@@ -197,6 +198,17 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
                             cfg.obs_max_length > T(0) ? cfg.obs_max_length : C);
         if (o) { o[0] = o0; o[1] = o1; o[2] = o2; }
         if (ol) { ol[0] = o0; ol[1] = o1; ol[2] = o2; }
+      }
+    } else if (ma) {
+      // MultiAgentWaveAttenuationPOEnv.get_state, multiagent/ring/wave_attenuation.py:195-213
+      const T v_nf = (G == 1) ? v[0] : shfl(v[0], lane_next, gmask);
+      const T ml = cfg.obs_max_length > T(0) ? cfg.obs_max_length : C;
+      FS_SLOTS(j) if (valid && j < n_mine && cfg.rl_index[base + j] >= 0) {
+        const int r = cfg.rl_index[base + j];
+        const T vl = (j + 1 < VPT && j + 1 < n_mine) ? v[j + 1 < VPT ? j + 1 : 0] : v_nf;
+        const T o0 = N::div(v[j], T(15)), o1 = N::div(vl - v[j], T(15)), o2 = N::div(h[j], ml);
+        if (o) { o[3 * r] = o0; o[3 * r + 1] = o1; o[3 * r + 2] = o2; }
+        if (ol) { ol[3 * r] = o0; ol[3 * r + 1] = o1; ol[3 * r + 2] = o2; }
       }
     } else if (valid) {
       // AccelEnv / WaveAttenuationEnv.get_state, accel.py:116-123

@@ -185,6 +185,7 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
   const bool have_act = A.actions != nullptr;
   const bool po = P.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
   const bool accel_env = P.env_kind == FS_ENV_ACCEL;
+  const bool ma = P.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO;
   const int K = A.k_steps;
 
   // IDM block of my vehicles. One vehicle per thread: picked once (an
@@ -260,6 +261,19 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
     }
     o0 = N::div(vr, T(15)); o1 = N::div(vl - vr, T(15));
     o2 = kF32 ? fwd_dist(xl, xr, C) * inv_obs_len : N::div(fwd_dist(xl, xr, C), obs_len);
+  };
+  // MultiAgentWaveAttenuationPOEnv.get_state (multiagent/ring/wave_attenuation.py:195-213):
+  // every RL vehicle: own speed, speed difference to its leader, bumper-to-bumper headway
+  auto ma_obs = [&](T* o) {
+    FS_SLOTS(j) if ((kExact || j < n_mine) && ((my_rl >> j) & 1u)) {
+      const int r = __popc(P.rl_mask & ((1u << (base + j)) - 1u));
+      T vl;
+      if (j + 1 < VPT) vl = (kExact || j + 1 < n_mine) ? v[j + 1 < VPT ? j + 1 : 0] : v_nf;
+      else vl = v_nf;
+      o[3 * r] = N::div(v[j], T(15));
+      o[3 * r + 1] = N::div(vl - v[j], T(15));
+      o[3 * r + 2] = kF32 ? h[j] * inv_obs_len : N::div(h[j], obs_len);
+    }
   };
   auto full_obs = [&](T* o) {  // AccelEnv / WaveAttenuationEnv.get_state, accel.py:116-123
     FS_SLOTS(j) if (kExact || j < n_mine) {
@@ -398,6 +412,7 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
     // ---- per-step outputs
     if (w_obs) {
       if (po) { T o0, o1, o2; po_obs(o0, o1, o2); obs_k[0] = o0; obs_k[1] = o1; obs_k[2] = o2; }
+      else if (ma) ma_obs(obs_k);
       else full_obs(obs_k);
       obs_k += obs_stride;
     }
@@ -409,7 +424,8 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
     T* ol = B.obs + (size_t)e * P.obs_dim;
     if (po) {
       if (is_writer) { T o0, o1, o2; po_obs(o0, o1, o2); ol[0] = o0; ol[1] = o1; ol[2] = o2; }
-    } else full_obs(ol);
+    } else if (ma) ma_obs(ol);
+    else full_obs(ol);
     FS_SLOTS(j) if (kExact || j < n_mine) {
       B.pos[(size_t)(base + j) * E + e] = x[j];
       B.vel[(size_t)(base + j) * E + e] = v[j];

@@ -11,6 +11,7 @@ What each piece stands for in the reference (parthjaggi/flow):
   RingNetwork / HighwayNetwork                          flow/networks/ring.py, highway.py
   AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv    flow/envs/ring/accel.py, wave_attenuation.py
   LaneChangeAccelEnv                                    flow/envs/ring/lane_change_accel.py
+  MultiAgentWaveAttenuationPOEnv                        flow/envs/multiagent/ring/wave_attenuation.py:143-312
   Env.reset / Env.step / clip_actions                   flow/envs/base.py:294-615
   env.k.vehicle.* / env.k.network.*                     flow/core/kernel/vehicle/traci.py, network/traci.py
   make_create_env                                       flow/utils/registry.py:13-134
@@ -570,7 +571,7 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         L = float(net['length'])
         lo, hi = (float(ring[0]), float(ring[1])) if ring else (L, L)
         kw.update(length_lo=lo, length_hi=hi, junction_len=RING_JUNCTION_LENGTH)
-        if env_cls.KIND == EN.ENV_WAVE_ATTENUATION_PO and ring:
+        if env_cls.KIND in (EN.ENV_WAVE_ATTENUATION_PO, EN.ENV_MA_WAVE_ATTENUATION_PO) and ring:
             kw['obs_max_length'] = hi        # wave_attenuation.py:253-256
         # network/base.py:599-605: no room -> the reference aborts the run
         lanes_d = int(min(max(ini.lanes_distribution, 1), int(net['lanes'])))
@@ -1014,8 +1015,70 @@ class LaneChangeAccelEnv(AccelEnv):
             raise ValueError('Direction values for lane changes may only be: {-1, 0, 1}.')
 
 
+class MultiAgentWaveAttenuationPOEnv(Env):
+    """flow/envs/multiagent/ring/wave_attenuation.py:143-312 +
+    flow/envs/multiagent/base.py:31-225 (MultiEnv): every RL vehicle is an agent.
+    `step` takes {rl_id: action} (or None) and returns dicts keyed by rl id:
+    obs (3,), the SHARED reward, done (+ '__all__'), info. Batched envs get
+    tensors [E, 3] / [E] per key.
+
+    Deviation, documented: the reference's MultiEnv discards the collision flag
+    (`crash = 0`, base.py:174) and lets SUMO's teleporting continue the run; the
+    engine keeps its collision rule (env frozen, reward 0, done['__all__'])."""
+    KIND = EN.ENV_MA_WAVE_ATTENUATION_PO
+    ADDITIONAL = {'max_accel': 1, 'max_decel': 1, 'ring_length': [220, 270]}
+
+    def __init__(self, env_params, sim_params, network, simulator='b200', **kw):
+        super().__init__(env_params, sim_params, network, simulator, **kw)
+        # action slot r belongs to the r-th RL vehicle in vehicle-index order
+        self.rl_ids = [v for i, v in enumerate(self.spec.veh_ids) if self._is_rl[i]]
+
+    @property
+    def action_space(self):
+        ap = self.env_params.additional_params
+        return _box(low=-abs(ap['max_decel']), high=ap['max_accel'], shape=(1,), dtype=np.float32)
+
+    @property
+    def observation_space(self):
+        return _box(low=-5, high=5, shape=(3,), dtype=np.float32)
+
+    def _split(self, obs):
+        if self.n_envs == 1:
+            o = obs[0].double().cpu().numpy().reshape(len(self.rl_ids), 3)
+            return {v: o[r] for r, v in enumerate(self.rl_ids)}
+        o = obs.view(self.n_envs, len(self.rl_ids), 3)
+        return {v: o[:, r] for r, v in enumerate(self.rl_ids)}
+
+    def reset(self):
+        obs = super().reset()
+        return self._split(self.state)
+
+    def step(self, rl_actions):
+        a = None
+        if rl_actions:   # MultiEnv._apply_rl_actions: `if rl_actions:` (empty dict = no command)
+            missing = [v for v in self.rl_ids if v not in rl_actions]
+            if missing:
+                raise KeyError('no action for agent(s) %s' % missing)
+            if self.n_envs == 1:
+                a = np.array([float(np.asarray(rl_actions[v]).reshape(-1)[0]) for v in self.rl_ids])
+            else:
+                import torch
+                a = torch.stack([torch.as_tensor(rl_actions[v]).reshape(self.n_envs)
+                                 for v in self.rl_ids], dim=1)
+        obs, rew, done, _ = super().step(a)
+        o = self._split(self.state)
+        if self.n_envs == 1:
+            # compute_reward returns 0 (not a dict) when rl_actions is None (:223-224)
+            r = {v: rew for v in self.rl_ids} if rl_actions else 0
+        else:
+            r = {v: rew for v in self.rl_ids}
+        d = {v: False if self.n_envs == 1 else done.new_zeros(done.shape) for v in self.rl_ids}
+        d['__all__'] = done
+        return o, r, d, {v: {} for v in self.rl_ids}
+
+
 _ENV_BY_NAME = {c.__name__: c for c in (AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv,
-                                        LaneChangeAccelEnv)}
+                                        LaneChangeAccelEnv, MultiAgentWaveAttenuationPOEnv)}
 
 
 # =============================================================================

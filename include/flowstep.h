@@ -67,6 +67,10 @@ extern "C" {
 #define FS_ENV_LANE_CHANGE_ACCEL 3 /* LaneChangeAccelEnv: obs 3V, dv - lc penalty   */
 #define FS_ENV_LANE_CHANGE_ACCEL_PO 4 /* LaneChangeAccelPOEnv                       */
 #define FS_ENV_HIGHWAY 5           /* open highway + inflow: obs 2*slots, dv reward */
+#define FS_ENV_MA_WAVE_ATTENUATION_PO 6 /* MultiAgentWaveAttenuationPOEnv
+                                      (flow/envs/multiagent/ring/wave_attenuation.py:143-312):
+                                      obs [n_rl][3] per env = (v/15, (v_lead-v)/15, headway/ring_length[1])
+                                      of every RL vehicle in action-slot order, shared WA reward */
 
 /* acceleration controllers (flow/controllers/*.py) */
 #define FS_CTRL_SIM 0          /* SimCarFollowingController: simulator default model */

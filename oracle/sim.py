@@ -38,7 +38,8 @@ from . import controllers as C
 VEHICLE_LENGTH = 5.0  # flow/core/kernel/network/base.py:10
 
 ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
-    ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY = range(6)
+    ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY, \
+    ENV_MA_WAVE_ATTENUATION_PO = range(7)
 
 F32_EPS = float(np.finfo(np.float32).eps)
 
@@ -313,6 +314,15 @@ class RingSim:
                 self.vel[rl] / 15.,
                 (self.vel[lead] - self.vel[rl]) / 15.,
                 (self.pos[lead] - self.pos[rl]) % self.circ / max_length])
+        if k == ENV_MA_WAVE_ATTENUATION_PO:
+            # multiagent/ring/wave_attenuation.py:195-213, one row per RL vehicle
+            max_length = self.obs_max_length or self.circ
+            out = []
+            for rl in self.rl_idx:
+                lead = self.leader[rl] if self.leader[rl] >= 0 else rl
+                out += [self.vel[rl] / 15., (self.vel[lead] - self.vel[rl]) / 15.,
+                        self.headway[rl] / max_length]
+            return np.array(out)
         if k == ENV_LANE_CHANGE_ACCEL:
             # lane_change_accel.py:114-130
             return np.array([v / self.speed_limit for v in self.vel] +
@@ -344,8 +354,8 @@ class RingSim:
                 if last == self.time_counter:
                     reward -= 0.1
             return reward
-        if k in (ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO):
-            # wave_attenuation.py:113-139
+        if k in (ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, ENV_MA_WAVE_ATTENUATION_PO):
+            # wave_attenuation.py:113-139; multiagent/ring/wave_attenuation.py:221-247 (shared)
             if rl_actions is None:
                 return 0
             vel = np.array(self.vel)

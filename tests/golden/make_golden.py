@@ -167,6 +167,36 @@ def ring_c2():
     np.savez_compressed(os.path.join(HERE, 'ring_c2.npz'), **out)
 
 
+def ring_ma():
+    """examples/exp_configs/rl/multiagent/multiagent_ring.py: two RL vehicles, each
+    followed by ten IDM humans, MultiAgentWaveAttenuationPOEnv observation/reward.
+    Actions come from a noisy gap-keeping rule fed with the previous observation
+    (purely random accelerations run the RL car into its leader within ~120 steps);
+    a good part of them lies outside the [-1, 1] box, which exercises the clip."""
+    groups = [('rl_0', 'rl', {}, {}, 1), ('human_0', IDM, {}, {'min_gap': 0}, 10),
+              ('rl_1', 'rl', {}, {}, 1), ('human_1', IDM, {}, {'min_gap': 0}, 10)]
+    ring = RefRing(groups, 247, 'ma_wave_po', init_kw=dict(bunching=50, min_gap=0),
+                   env_additional={'max_accel': 1, 'max_decel': 1, 'ring_length': [220, 270]})
+    rng = np.random.default_rng(5)
+    n_w, n_a = 200, 600
+    acts = np.full((n_w + n_a, 2), np.nan)
+    P, Vv, O, Rw = [list(ring.pos)], [list(ring.vel)], [], []
+    obs = ring.get_state()
+    for s in range(n_w + n_a):
+        a = None
+        if s >= n_w:
+            o = np.asarray(obs).reshape(2, 3)
+            a = 2.0 * o[:, 1] * 15 + 0.08 * (o[:, 2] * 270 - 8.0) + rng.normal(0, 0.6, 2)
+            acts[s] = a
+        obs, rew, crash = ring.step(a)
+        assert not crash, s
+        P.append(list(ring.pos)); Vv.append(list(ring.vel)); O.append(np.asarray(obs, float))
+        Rw.append(float(rew))
+    assert (np.abs(acts[n_w:]) > 1).mean() > 0.1
+    np.savez_compressed(os.path.join(HERE, 'ring_ma.npz'), length=247, actions=acts,
+                        pos=np.array(P), vel=np.array(Vv), obs=np.array(O), reward=np.array(Rw))
+
+
 ZOO = [
     ('ovm', OVM, {}, 'OVM', None),
     ('ovm_inst', OVM, {'fail_safe': 'instantaneous'}, 'OVM', 'instantaneous'),
@@ -253,7 +283,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c3(); ring_zoo(); start_pos(); sumo_fixture()
+    ring_c1(); ring_c2(); ring_c3(); ring_zoo(); ring_ma(); start_pos(); sumo_fixture()
     print('golden vectors written to', HERE)
 
 

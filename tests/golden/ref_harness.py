@@ -18,6 +18,8 @@ from flow.core import rewards as ref_rewards  # noqa: E402
 from flow.envs.ring.wave_attenuation import WaveAttenuationEnv, \
     WaveAttenuationPOEnv  # noqa: E402
 from flow.envs.ring.accel import AccelEnv  # noqa: E402
+from flow.envs.multiagent.ring.wave_attenuation import \
+    MultiAgentWaveAttenuationPOEnv  # noqa: E402
 import flow.controllers as ref_ctrl  # noqa: E402
 
 
@@ -263,6 +265,10 @@ class RefRing:
         return obs, reward, crash
 
     def get_state(self):
+        if self.env_kind == 'ma_wave_po':
+            # dict keyed by rl id -> rows in get_rl_ids() order (= action-slot order)
+            d = MultiAgentWaveAttenuationPOEnv.get_state(self)
+            return np.concatenate([d[v] for v in self.k.vehicle.get_rl_ids()])
         if self.env_kind == 'wave_po':
             return WaveAttenuationPOEnv.get_state(self)
         if self.env_kind == 'wave':
@@ -271,6 +277,15 @@ class RefRing:
         return AccelEnv.get_state(self)
 
     def compute_reward(self, rl_actions, fail):
+        if self.env_kind == 'ma_wave_po':
+            acts = None if rl_actions is None else \
+                dict(zip(self.k.vehicle.get_rl_ids(), [float(a) for a in rl_actions]))
+            r = MultiAgentWaveAttenuationPOEnv.compute_reward(self, acts, fail=fail)
+            if isinstance(r, dict):   # shared reward: every agent gets the same number
+                vals = list(r.values())
+                assert all(x == vals[0] for x in vals)
+                return vals[0]
+            return r
         if self.env_kind in ('wave', 'wave_po'):
             return WaveAttenuationEnv.compute_reward(self, rl_actions, fail=fail)
         return AccelEnv.compute_reward(self, rl_actions, fail=fail)

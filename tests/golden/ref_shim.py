@@ -59,6 +59,11 @@ class _GymEnv:
     pass
 
 
+class _MultiAgentEnv:
+    """ray.rllib.env.MultiAgentEnv stand-in (distinct from gym.Env so that
+    `class MultiEnv(MultiAgentEnv, Env)` has a consistent MRO)."""
+
+
 def install():
     if not available():
         raise RuntimeError('reference checkout not found at %s' % REF)
@@ -78,8 +83,8 @@ def install():
         'FatalTraCIError', (Exception,), {})
     sys.modules['traci.exceptions'].TraCIException = type(
         'TraCIException', (Exception,), {})
-    sys.modules['ray.rllib.env'].MultiAgentEnv = _GymEnv
-    sys.modules['ray.rllib.env.multi_agent_env'].MultiAgentEnv = _GymEnv
+    sys.modules['ray.rllib.env'].MultiAgentEnv = _MultiAgentEnv
+    sys.modules['ray.rllib.env.multi_agent_env'].MultiAgentEnv = _MultiAgentEnv
     sys.modules['cached_property'].cached_property = property
     if 'gym' not in sys.modules:
         gym = _Anything('gym')

@@ -207,3 +207,30 @@ def test_lane_change_direction_validation():
         o.step(None)
     with pytest.raises(ValueError):   # vehicle/traci.py:973-975
         o.step([0, 0.5, 0, 0, 0, 0])
+
+
+def ma_groups():
+    """examples/exp_configs/rl/multiagent/multiagent_ring.py vehicle order."""
+    return [S.vt('RL', 1), S.vt('IDM', 10, sim_min_gap=0.0), S.vt('RL', 1),
+            S.vt('IDM', 10, sim_min_gap=0.0)]
+
+
+MA = dict(bunching=50.0, init_min_gap=0.0, warmup_steps=0, horizon=3000, act_lo=-1.0, act_hi=1.0,
+          obs_max_length=270.0)
+
+
+def test_multiagent_ring_trajectory_bit_exact():
+    """MultiAgentWaveAttenuationPOEnv.get_state / compute_reward of the reference
+    (tests/golden/ring_ma.npz) vs the oracle restatement."""
+    z = np.load(os.path.join(G, 'ring_ma.npz'))
+    kw = dict(MA); kw.pop('init_min_gap')
+    o = S.make_oracle(ma_groups(), float(z['length']), env_kind=OS.ENV_MA_WAVE_ATTENUATION_PO,
+                      **kw)
+    assert np.array_equal(np.array(o.pos), z['pos'][0])
+    for s, a in enumerate(z['actions']):
+        obs, rew, done = o.step(None if np.isnan(a).any() else list(a))
+        assert np.array_equal(np.array(o.pos), z['pos'][s + 1]), s
+        assert np.array_equal(np.array(o.vel), z['vel'][s + 1]), s
+        assert np.array_equal(np.asarray(obs), z['obs'][s]), s
+        assert rew == z['reward'][s], s
+        assert not done
