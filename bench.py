@@ -47,7 +47,7 @@ def parse():
     ap.add_argument('--steps', type=int, default=3000)
     ap.add_argument('--warmup', type=int, default=300)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=['c2', 'c5'])
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma'])
     ap.add_argument('--fuse', type=int, default=100, help='steps per fused launch')
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     ap.add_argument('--noise', type=float, default=0.2,
@@ -260,7 +260,7 @@ def run_b200(a):
     td = torch.float32 if a.dtype == 'f32' else torch.float64
     ts = 4 if a.dtype == 'f32' else 8
     gen = torch.Generator(device='cuda'); gen.manual_seed(4321 + rank)
-    act = torch.rand(K, 1, E, device='cuda', dtype=td, generator=gen) * 2 - 1
+    act = torch.rand(K, env.act_dim, E, device='cuda', dtype=td, generator=gen) * 2 - 1
     obs_seq = torch.empty(K, E, env.obs_dim, device='cuda', dtype=td)
     rew_seq = torch.empty(K, E, device='cuda', dtype=td)
     done_seq = torch.empty(K, E, device='cuda', dtype=torch.uint8)
@@ -274,7 +274,7 @@ def run_b200(a):
 
     # raw device addresses of step s inside the big buffers (no per-launch torch slicing)
     pa, po_, pr, pd = act.data_ptr(), obs_seq.data_ptr(), rew_seq.data_ptr(), done_seq.data_ptr()
-    sa, so, sr, sd = E * ts, E * env.obs_dim * ts, E * ts, E
+    sa, so, sr, sd = E * env.act_dim * ts, E * env.obs_dim * ts, E * ts, E
 
     def fused_pass(n_steps):
         for s in range(0, n_steps, F):
@@ -363,7 +363,9 @@ def run_b200(a):
     n_launch = fused['launches']
     launch_ms = fused['ms'] / max(n_launch, 1)
     # per-GPU algorithmic bytes of one fused launch / its duration
-    alg_bytes = BYTES_PER_ENV_STEP * (ts / 4) * (fused['env_steps'] / world) / max(n_launch, 1)
+    # SURVEY 8d per env-step: state round trip 16 B x V + ring length 4 + actions + obs + reward 4 + done 1 (f32)
+    bpe = (N_VEH * 16 + 4 + 4 * env.act_dim + 4 * env.obs_dim + 4) * (ts / 4) + 1
+    alg_bytes = bpe * (fused['env_steps'] / world) / max(n_launch, 1)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
     tp = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
@@ -372,7 +374,7 @@ def run_b200(a):
             traffic = json.load(open(tp)).get('%s_%s_fuse%d' % (a.workload, a.dtype, F))
         except Exception:
             traffic = None
-    h2d = F * E * ts
+    h2d = F * E * env.act_dim * ts
     d2h = F * E * (env.obs_dim * ts + ts + 1)
     line = {
         'metric': 'vehicle-steps/s', 'value': vps(fused), 'unit': 'vehicle-steps/s',
@@ -408,8 +410,9 @@ def run_b200(a):
                             'api': 'B200VecEnv.rollout_host, 1 step per call'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
-                     'kernel': 'ring1_hot_kernel<%s> (flow_b200/csrc/fs_ring_hot.cuh), %d fused steps '
-                               'per launch, threads/env = %s' % (a.dtype, F, os.environ.get('FS_RING_SHAPE', 'auto')),
+                     'kernel': '%s<%s> (flow_b200/csrc/), %d fused steps per launch, threads/env = %s'
+                               % ('ring1_fast_kernel' if a.workload == 'ma' else 'ring1_hot_kernel', a.dtype, F,
+                                  os.environ.get('FS_RING_SHAPE', 'auto')),
                      'launch_ms': launch_ms,
                      'note': 'achieved = ALGORITHMIC bytes (SURVEY 8d: %d B per env-step = state round '
                              'trip + action/obs/reward/done, the single-step figure) x env-steps per '
@@ -418,21 +421,21 @@ def run_b200(a):
                              'exceed 1: it says how the fused path compares with the best a '
                              'one-step-per-launch HBM-bound kernel could do. The fused kernel itself is '
                              'bound by instruction issue (profiles/: issue-active 51 %% on c2, 74 %% on '
-                             'c5; `issue` below).' % int(BYTES_PER_ENV_STEP * ts / 4)},
+                             'c5; `issue` below).' % int(bpe)},
         # what the fused kernel must move at least: action in, obs/reward/done out per env-step,
         # state once per launch
         'roofline_fused_stream': (lambda b: {
             'bound': 'hbm', 'unit': 'GB/s', 'peak': peak, 'bytes_per_launch': b,
             'achieved': b / (launch_ms * 1e-3) / 1e9, 'frac': b / (launch_ms * 1e-3) / 1e9 / peak})(
-                (fused['env_steps'] / world / max(n_launch, 1)) * (ts + env.obs_dim * ts + ts + 1)
+                (fused['env_steps'] / world / max(n_launch, 1)) * (env.act_dim * ts + env.obs_dim * ts + ts + 1)
                 + E * (2 * N_VEH * 2 * ts + ts)),
         'issue': {'unit': 'warp-instructions per vehicle-step (static SASS count of the step loop, '
                           'scripts/sass_loops.py)', 'c5_shape1': 46.9, 'c2_shape8': 89.0,
                   'note': 'B200: 148 SMs x 4 schedulers x 1 warp-instruction/cycle x 1.965 GHz'},
         'roofline_single_step': {
             'bound': 'hbm', 'unit': 'GB/s', 'peak': peak,
-            'achieved': BYTES_PER_ENV_STEP * (ts / 4) * E / (single['ms'] / K * 1e-3) / 1e9,
-            'frac': BYTES_PER_ENV_STEP * (ts / 4) * E / (single['ms'] / K * 1e-3) / 1e9 / peak},
+            'achieved': bpe * E / (single['ms'] / K * 1e-3) / 1e9,
+            'frac': bpe * E / (single['ms'] / K * 1e-3) / 1e9 / peak},
         'clocks': clocks,
     }
     if world == 1 and not a.no_cpu_baseline:

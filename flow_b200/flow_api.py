@@ -233,11 +233,26 @@ class SumoCarFollowingParams:
 
 
 class SumoLaneChangeParams:
-    """flow/core/params.py:904-1067 (only the mode matters to the engine)."""
+    """flow/core/params.py:904-1067. The engine only reads `lane_change_mode`; the SUMO
+    model parameters are carried so that flow_params.json stays interchangeable."""
+    _BASE = (('lcStrategic', 'lc_strategic', 1.0), ('lcCooperative', 'lc_cooperative', 1.0),
+             ('lcSpeedGain', 'lc_speed_gain', 1.0), ('lcKeepRight', 'lc_keep_right', 1.0))
+    _SUBLANE = (('lcLookaheadLeft', 'lc_look_ahead_left', 2.0),
+                ('lcSpeedGainRight', 'lc_speed_gain_right', 1.0), ('lcSublane', 'lc_sublane', 1.0),
+                ('lcPushy', 'lc_pushy', 0), ('lcPushyGap', 'lc_pushy_gap', 0.6),
+                ('lcAssertive', 'lc_assertive', 1), ('lcAccelLat', 'lc_accel_lat', 1.0))
 
     def __init__(self, lane_change_mode='no_lat_collide', model='LC2013', **kwargs):
-        self.controller_params = dict(laneChangeModel=model, **{
-            k: str(v) for k, v in kwargs.items()})
+        if model not in ('LC2013', 'SL2015'):
+            model = 'LC2013'
+        rows = self._BASE + (self._SUBLANE if model == 'SL2015' else ())
+        known = {k for r in self._BASE + self._SUBLANE for k in r[:2]}
+        unknown = set(kwargs) - known
+        if unknown:
+            raise TypeError('unexpected arguments %s' % sorted(unknown))
+        self.controller_params = {'laneChangeModel': model}
+        for sumo_key, key, default in rows:   # camelCase spellings are the deprecated aliases
+            self.controller_params[sumo_key] = str(kwargs.get(sumo_key, kwargs.get(key, default)))
         if isinstance(lane_change_mode, str) and lane_change_mode in LC_MODES:
             lane_change_mode = LC_MODES[lane_change_mode]
         elif not isinstance(lane_change_mode, (int, float)):
@@ -341,10 +356,11 @@ class EnvParams:
 
 
 class InFlows:
-    """flow/core/params.py:1070-1221"""
+    """flow/core/params.py:1070-1221 (the list lives in the same name-mangled
+    attribute as the reference's, so a flow_params.json round-trips both ways)"""
 
     def __init__(self):
-        self._flows = []
+        self.__flows = []
 
     def add(self, edge, veh_type, vehs_per_hour=None, probability=None, period=None,
             depart_lane='first', depart_speed=0, name='flow', begin=1, end=86400,
@@ -355,7 +371,7 @@ class InFlows:
         if probability is not None:
             raise NotImplementedError('probabilistic inflows are not compiled (only '
                                       'vehs_per_hour / period)')
-        new = dict(name='%s_%d' % (name, len(self._flows)), vtype=veh_type, edge=edge,
+        new = dict(name='%s_%d' % (name, len(self.__flows)), vtype=veh_type, edge=edge,
                    departLane=depart_lane, departSpeed=depart_speed, begin=begin, end=end)
         new.update(kwargs)
         if vehs_per_hour is not None:
@@ -364,13 +380,13 @@ class InFlows:
             new['period'] = period
         if number is not None:
             new['number'] = number
-        self._flows.append(new)
+        self.__flows.append(new)
 
     def sort(self, key):
-        self._flows.sort(key=key)
+        self.__flows.sort(key=key)
 
     def get(self):
-        return self._flows
+        return self.__flows
 
 
 class NetParams:
@@ -1130,8 +1146,10 @@ class Experiment:
         if convert_to_csv and env.sim_params.emission_path is None:
             raise ValueError('The experiment was run with convert_to_csv set to True, but no '
                              'emission file will be generated.')
-        if convert_to_csv:
-            raise NotImplementedError('emission files (SUMO output) are out of scope')
+        rec = None
+        if convert_to_csv:   # the reference converts SUMO's emission xml; here rows come from the engine
+            from .emission import EmissionRecorder
+            rec = EmissionRecorder(env)
         info = {'returns': [], 'velocities': [], 'outflows': []}
         info.update({k: [] for k in self.custom_callables})
         if rl_actions is None:
@@ -1142,9 +1160,14 @@ class Experiment:
             ret, vel = 0, []
             custom = {k: [] for k in self.custom_callables}
             state = env.reset()
+            if rec is not None and i == num_runs - 1:
+                rec.rows, rec._waiting = [], {}
+                rec.record()
             for _ in range(int(num_steps)):
                 state, reward, done, _i = env.step(rl_actions(state))
                 steps += 1
+                if rec is not None and i == num_runs - 1:   # like SUMO's file: the last run
+                    rec.record()
                 vel.append(np.mean(env.k.vehicle.get_speed(env.k.vehicle.get_ids())))
                 ret += reward
                 for k, f in self.custom_callables.items():
@@ -1162,5 +1185,9 @@ class Experiment:
         dt = time.time() - t
         print('Total time:', dt)
         print('steps/second:', steps / dt if dt > 0 else float('inf'))
+        if rec is not None:
+            import os
+            rec.write_csv(os.path.join(env.sim_params.emission_path,
+                                       '{0}-emission.csv'.format(env.network.name)))
         env.terminate()
         return info

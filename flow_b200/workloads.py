@@ -25,9 +25,23 @@ def ring_c2(noise=0.0):
     return types, [0] * 21 + [1], kw
 
 
+def ring_ma(noise=0.0):
+    """examples/exp_configs/rl/multiagent/multiagent_ring.py:
+    MultiAgentWaveAttenuationPOEnv, (1 RL + 10 IDM) x 2 on one ring."""
+    human = EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, sim_min_gap=0.0)
+    types = [EN.make_vtype(EN.CTRL_RL), human]
+    kw = dict(env_kind=EN.ENV_MA_WAVE_ATTENUATION_PO, length_lo=220.0, length_hi=270.0,
+              bunching=50.0, init_min_gap=0.0, warmup_steps=750, horizon=3000,
+              act_lo=-1.0, act_hi=1.0, obs_max_length=270.0, clip_actions=0)
+    return types, [0] + [1] * 10 + [0] + [1] * 10, kw
+
+
 WORKLOADS = {
     'c2': dict(builder=ring_c2, n_envs=4096, n_veh=22,
                name='WaveAttenuationPOEnv ring 21 IDM + 1 RL, 4096 envs/GPU, random RL actions'),
+    'ma': dict(builder=ring_ma, n_envs=4096, n_veh=22,
+               name='MultiAgentWaveAttenuationPOEnv ring (1 RL + 10 IDM) x 2, 4096 envs/GPU, '
+                    'random RL actions'),
     'c5': dict(builder=ring_c2, n_envs=65536, n_veh=22,
                name='WaveAttenuationPOEnv ring stress, 65536 envs/GPU, fused 100-step launches'),
 }

@@ -299,3 +299,42 @@ def test_gpu_highway_env_rates(n_init):
         # ten stationary vehicles queue at the entry: departures are held back (blocked insertion)
         assert 0 < rate_in < 2000
     env.terminate()
+
+
+@pytest.mark.gpu
+def test_gpu_emission_csv_matches_the_reference_sumo_fixture(tmp_path):
+    """Experiment.run(convert_to_csv=True) writes `<name>-emission.csv` with the
+    reference's columns; the rows reproduce tests/fast_tests/test_files/
+    ring_230_emission.csv (real SUMO output) where SUMO prints them: speed to
+    0.01, edge ids, displacement to 0.01 for t <= 0.5."""
+    import csv
+    import json
+    from flow_b200 import emission
+    fp = c1_flow_params()
+    fp['sim'].emission_path = str(tmp_path)
+    fp['env'].horizon = 6
+    exp = F.Experiment(fp)
+    exp.run(1, convert_to_csv=True)
+    path = os.path.join(str(tmp_path), 'ring-emission.csv')
+    rows = list(csv.DictReader(open(path)))
+    assert list(rows[0].keys()) == emission.COLUMNS
+    assert len(rows) == 22 * 7 and [r['id'] for r in rows] == sorted(r['id'] for r in rows)
+    ours = {(round(float(r['time']), 1), r['id']): r for r in rows}
+    ref = json.load(open(os.path.join(G, 'sumo_ring_230.json')))['rows']
+    by = {(round(r['time'], 1), r['id']): r for r in ref}
+    n = 0
+    for (t, vid), r in by.items():
+        if t > 0.5 or (t, vid) not in ours:
+            continue
+        o, o0, r0 = ours[(t, vid)], ours[(0.1, vid)], by[(0.1, vid)]
+        assert abs(float(o['speed']) - r['speed']) <= 0.0101, (t, vid)
+        assert o['type'] == 'idm' and o['lane_number'] == '0'
+        if r['edge'] == r0['edge'] and o['edge_id'] == o0['edge_id']:
+            d_ref = r['rel_pos'] - r0['rel_pos']
+            d_our = float(o['relative_position']) - float(o0['relative_position'])
+            assert abs(d_our - d_ref) <= 0.0301, (t, vid)
+        n += 1
+    assert n >= 22 * 5
+    # the reference's time-space reader needs exactly these columns
+    for k in ('time', 'id', 'edge_id', 'relative_position', 'speed', 'lane_number'):
+        assert k in rows[0]
