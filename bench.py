@@ -261,6 +261,11 @@ def run_b200(a):
     ts = 4 if a.dtype == 'f32' else 8
     gen = torch.Generator(device='cuda'); gen.manual_seed(4321 + rank)
     act = torch.rand(K, env.act_dim, E, device='cuda', dtype=td, generator=gen) * 2 - 1
+    if a.workload == 'ma':
+        # agents that ignore their leaders in stop-and-go traffic ram them within ~100 steps
+        # (zero or zero-mean accelerations: > 90 % of the rings); braking-biased random
+        # actions U(-1, 0.2) keep the rings alive for the timed pass
+        act = act * 0.6 - 0.4
     obs_seq = torch.empty(K, E, env.obs_dim, device='cuda', dtype=td)
     rew_seq = torch.empty(K, E, device='cuda', dtype=td)
     done_seq = torch.empty(K, E, device='cuda', dtype=torch.uint8)

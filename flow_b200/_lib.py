@@ -83,6 +83,8 @@ SYMBOLS = [
     ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host_async', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_buffers', C.c_int, [C.c_void_p, C.POINTER(FsViews)]),
+    ('fs_dlpack_wrap', C.c_void_p, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     ('fs_set_state', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_stats', C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int]),
     ('fs_sync', C.c_int, [C.c_void_p]),

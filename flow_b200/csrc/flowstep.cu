@@ -691,6 +691,41 @@ extern "C" int fs_step_host_async(fs_engine* e, const void* actions, int k, void
   return FS_OK;
 }
 
+// ---------------------------------------------------------------- DLPack
+// Minimal DLPack v0 ABI (dlpack.h: DLDevice, DLDataType, DLTensor, DLManagedTensor),
+// declared here so the library has no build dependency. The managed tensor does
+// NOT own the device memory (the engine does); its deleter only frees the
+// descriptor block, in C, so consumers may drop tensors at any time — including
+// interpreter shutdown — without calling back into Python.
+namespace {
+struct DLDev { int32_t device_type; int32_t device_id; };
+struct DLType { uint8_t code; uint8_t bits; uint16_t lanes; };
+struct DLTens { void* data; DLDev device; int32_t ndim; DLType dtype; int64_t* shape;
+                int64_t* strides; uint64_t byte_offset; };
+struct DLManaged { DLTens dl_tensor; void* manager_ctx; void (*deleter)(DLManaged*); };
+void dl_free(DLManaged* m) { free(m); }
+}  // namespace
+
+extern "C" void* fs_dlpack_wrap(void* dev_ptr, int device, int type_code, int bits, int ndim,
+                                const int64_t* shape, const int64_t* strides) {
+  if (!dev_ptr || ndim < 1 || ndim > 8 || !shape) return nullptr;
+  const size_t bytes = sizeof(DLManaged) + 2 * ndim * sizeof(int64_t);
+  DLManaged* m = (DLManaged*)malloc(bytes);
+  if (!m) return nullptr;
+  int64_t* tail = (int64_t*)(m + 1);
+  m->dl_tensor.data = dev_ptr;
+  m->dl_tensor.device = DLDev{2 /* kDLCUDA */, device};
+  m->dl_tensor.ndim = ndim;
+  m->dl_tensor.dtype = DLType{(uint8_t)type_code, (uint8_t)bits, 1};
+  m->dl_tensor.shape = tail;
+  m->dl_tensor.strides = strides ? tail + ndim : nullptr;
+  m->dl_tensor.byte_offset = 0;
+  for (int i = 0; i < ndim; ++i) { tail[i] = shape[i]; if (strides) tail[ndim + i] = strides[i]; }
+  m->manager_ctx = nullptr;
+  m->deleter = dl_free;
+  return m;
+}
+
 extern "C" int fs_buffers(fs_engine* e, fs_views* out) {
   if (!e || !out) return FS_EINVAL;
   memset(out, 0, sizeof(*out));

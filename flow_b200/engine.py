@@ -30,36 +30,9 @@ class FlowStepError(RuntimeError):
 
 
 # ---- DLPack capsule from a raw device pointer ---------------------------------
-class _DLDevice(C.Structure):
-    _fields_ = [('device_type', C.c_int32), ('device_id', C.c_int32)]
-
-
-class _DLDataType(C.Structure):
-    _fields_ = [('code', C.c_uint8), ('bits', C.c_uint8), ('lanes', C.c_uint16)]
-
-
-class _DLTensor(C.Structure):
-    _fields_ = [('data', C.c_void_p), ('device', _DLDevice), ('ndim', C.c_int32),
-                ('dtype', _DLDataType), ('shape', C.POINTER(C.c_int64)),
-                ('strides', C.POINTER(C.c_int64)), ('byte_offset', C.c_uint64)]
-
-
-class _DLManagedTensor(C.Structure):
-    pass
-
-
-_DELETER = C.CFUNCTYPE(None, C.POINTER(_DLManagedTensor))
-_DLManagedTensor._fields_ = [('dl_tensor', _DLTensor), ('manager_ctx', C.c_void_p),
-                             ('deleter', _DELETER)]
-
-_live = {}
-
-
-@_DELETER
-def _dl_deleter(ptr):
-    _live.pop(C.addressof(ptr.contents), None)
-
-
+# The DLManagedTensor is built and freed inside libflowstep (fs_dlpack_wrap): no
+# Python callback sits in a tensor's destructor, so tensors may outlive the
+# interpreter's teardown order safely.
 _DL_CODES = {'f32': (2, 32), 'f64': (2, 64), 'u8': (1, 8), 'i32': (0, 32)}
 _PyCapsule_New = C.pythonapi.PyCapsule_New
 _PyCapsule_New.restype = C.py_object
@@ -68,20 +41,12 @@ _PyCapsule_New.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
 
 def dlpack_capsule(ptr, shape, dtype, device_id):
     """DLPack ('dltensor') capsule for device memory the engine owns."""
-    m = _DLManagedTensor()
-    shp = (C.c_int64 * len(shape))(*shape)
     code, bits = _DL_CODES[dtype]
-    m.dl_tensor.data = ptr
-    m.dl_tensor.device = _DLDevice(2, device_id)  # kDLCUDA
-    m.dl_tensor.ndim = len(shape)
-    m.dl_tensor.dtype = _DLDataType(code, bits, 1)
-    m.dl_tensor.shape = shp
-    m.dl_tensor.strides = None
-    m.dl_tensor.byte_offset = 0
-    m.manager_ctx = None
-    m.deleter = _dl_deleter
-    _live[C.addressof(m)] = (m, shp)
-    return _PyCapsule_New(C.addressof(m), b'dltensor', None)
+    shp = (C.c_int64 * len(shape))(*shape)
+    m = _lib.load().fs_dlpack_wrap(C.c_void_p(ptr), device_id, code, bits, len(shape), shp, None)
+    if not m:
+        raise ValueError('fs_dlpack_wrap rejected ptr=%r shape=%r' % (ptr, shape))
+    return _PyCapsule_New(m, b'dltensor', None)
 
 
 def _as_tensor(ptr, shape, dtype, device_id):

@@ -218,6 +218,16 @@ int fs_step_host_async(fs_engine* e, const void* actions, int k, void* obs_seq,
 
 int fs_buffers(fs_engine* e, fs_views* out);
 
+/* DLPack export of engine-owned device memory (obs / reward / state views, or
+ * any sub-range of them): returns a malloc'ed DLManagedTensor* (DLPack v0 ABI,
+ * device type kDLCUDA) describing `dev_ptr` with the given element type
+ * (type_code 0 int, 1 uint, 2 float; bits 8/32/64), shape and optional strides
+ * (in elements; NULL = C-contiguous). The tensor does not own the memory; its
+ * deleter frees only the descriptor. Wrap it in a PyCapsule named "dltensor"
+ * and hand it to torch.from_dlpack / cupy / jax. NULL on bad arguments. */
+void* fs_dlpack_wrap(void* dev_ptr, int device, int type_code, int bits, int ndim,
+                     const int64_t* shape, const int64_t* strides);
+
 /* Overwrite state from host arrays (T [V][E], any may be NULL), then refresh
  * leader/headway exactly as k.update does. lane: u8 [V][E]. */
 int fs_set_state(fs_engine* e, const void* pos, const void* vel,
