@@ -69,8 +69,11 @@ struct fs_engine {
   fs::Cfg<double> cd;
   std::vector<void*> allocs;
   bool env_needs_rl() const {
-    return cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO || cfg.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO;
+    return cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO || cfg.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO ||
+           cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
   }
+  // warp-per-env multi-lane kernel (also the only one with the per-lane neighbour observation)
+  bool multilane() const { return cfg.n_lanes > 1 || cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO; }
 };
 
 #define FS_CUDA(e, call)                                                        \
@@ -116,6 +119,8 @@ static int obs_dim_for(const fs_config& c) {
     case FS_ENV_WAVE_ATTENUATION: return 2 * c.n_veh;
     case FS_ENV_WAVE_ATTENUATION_PO: return 3;
     case FS_ENV_LANE_CHANGE_ACCEL: return 3 * c.n_veh;
+    case FS_ENV_LANE_CHANGE_ACCEL_PO:   // capacity; 4 * n_rl * n_lanes + (1 | n_rl) after fs_set_types
+      return c.topology == FS_TOPO_RING ? 4 * c.n_veh * c.n_lanes + c.n_veh : -1;
     case FS_ENV_HIGHWAY: return 2 * c.n_veh;
     case FS_ENV_MA_WAVE_ATTENUATION_PO: return 3 * c.n_veh;  // capacity; 3 * n_rl after fs_set_types
     default: return -1;
@@ -167,7 +172,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->time_counter, E * 4); A(&e->episode, E * 4);
   A(&e->obs, E * e->obs_dim * ts); A(&e->reward, E * ts);
   A(&e->stats, FS_STAT_STRIPES * 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
-  e->env_major = cfg->n_lanes > 1 || cfg->topology == FS_TOPO_HIGHWAY;
+  e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY;
   if (e->env_major) A(&e->last_lc, V * E * 4);
   if (cfg->topology == FS_TOPO_HIGHWAY) { A(&e->counters, 4 * E * 4); A(&e->vtype, V * E); }
   if (cfg->record_views) {
@@ -260,6 +265,12 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
                       g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
   c.act_dim = lc_env ? 2 * n_rl : n_rl;
   if (g.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO) { e->obs_dim = 3 * n_rl; c.obs_dim = e->obs_dim; }
+  // LaneChangeAccelPOEnv.get_state returns inside its loop over RL vehicles
+  // (lane_change_accel.py:215-263): 4 * n_rl * lanes zeros-or-first-block + ONE ego speed
+  // (with lc_corrected: every block and n_rl ego speeds, the declared observation_space)
+  if (g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO) {
+    e->obs_dim = 4 * n_rl * g.n_lanes + (g.lc_corrected ? n_rl : 1); c.obs_dim = e->obs_dim;
+  }
   e->n_rl = n_rl;
   e->act_dim = c.act_dim;
 }
@@ -469,7 +480,7 @@ template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->cfg.topology == FS_TOPO_HIGHWAY) return launch_hw<T>(e, a);
   const int V = e->cfg.n_veh, E = e->cfg.n_envs;
-  if (e->cfg.n_lanes > 1) return launch_ml<T>(e, a);
+  if (e->multilane()) return launch_ml<T>(e, a);
   if (e->fast_ok) {
     // IDM-law hot kernel; threads per env chosen from the batch size
     int shape = e->ring_shape;

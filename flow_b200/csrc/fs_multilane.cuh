@@ -148,7 +148,67 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   }
   double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
 
+  const bool po_env = cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
+  auto rl_vehicle = [&](int r) {  // r-th RL vehicle in get_rl_ids order
+    for (int i = 0; i < V; ++i) if (cfg.rl_index[i] == r) return i;
+    return 0;
+  };
+
   auto write_obs = [&](T* o, T* ol) {
+    if (po_env) {
+      // LaneChangeAccelPOEnv.get_state (lane_change_accel.py:215-263). Per RL vehicle a
+      // block [headway_l | tailway_l | v_leader_l | v_follower_l] (l = lane), then ego speed.
+      // As the reference BEHAVES (default): the `return` sits inside the loop over RL
+      // vehicles, so only the FIRST block is filled, the others stay 0 and ONE raw ego
+      // speed follows (4*n_rl*L + 1 values); headways / tailways are copied before the
+      // in-place normalisation, i.e. they stay in metres (1000 = empty lane).
+      // lc_corrected: every block, distances / network length (1 when the lane is empty),
+      // n_rl ego speeds / max_speed (4*n_rl*L + n_rl values, the declared observation_space).
+      // Lane neighbours = TraCIVehicle._multi_lane_headways on a closed loop
+      // (vehicle/traci.py:699-937), scanned in the slice published by update().
+      const bool fixed = !B.lc_bug_compat;
+      const int nb = 4 * cfg.n_rl * L;
+      const int n_blk = fixed ? cfg.n_rl : 1;
+      for (int q = 4 * L * n_blk + lane_id; q < nb; q += 32) {
+        if (o) o[q] = T(0);
+        if (ol) ol[q] = T(0);
+      }
+      for (int r = lane_id; r < n_blk; r += 32) {
+        const T sp = vs[rl_vehicle(r)];
+        const T ego = fixed ? N::div(sp, cfg.speed_limit) : sp;
+        if (o) o[nb + r] = ego;
+        if (ol) ol[nb + r] = ego;
+      }
+      for (int q = lane_id; q < n_blk * L; q += 32) {
+        const int r = q / L, lq = q - r * L;
+        const int me = rl_vehicle(r);
+        const T p = xs[me];
+        int jl = -1, jf = -1;
+        T bd = T(0), bb = T(0);
+        for (int j = 0; j < V; ++j) {
+          if (ls[j] != lq || j == me) continue;
+          T d = xs[j] - p;             // a vehicle level with us in another lane is ahead (d = 0)
+          if (d < T(0)) d = d + C;
+          if (jl < 0 || d < bd) { jl = j; bd = d; }          // ties: lowest index
+          T b = p - xs[j];
+          if (!(xs[j] < p)) b = b + C;
+          if (jf < 0 || b <= bb) { jf = j; bb = b; }         // ties: highest index
+        }
+        if (jl < 0 && ls[me] == lq) { jl = jf = me; bd = bb = C; }  // alone: itself, one lap away
+        T hw = jl >= 0 ? bd - cfg.types[cfg.type_of[jl]].length : T(1000);
+        T tw = jf >= 0 ? bb - cfg.types[cfg.type_of[me]].length : T(1000);
+        if (fixed) {
+          hw = jl >= 0 ? N::div(hw, C) : T(1);
+          tw = jf >= 0 ? N::div(tw, C) : T(1);
+        }
+        const T vl = jl >= 0 ? N::div(vs[jl], cfg.speed_limit) : T(0);
+        const T vf = jf >= 0 ? N::div(vs[jf], cfg.speed_limit) : T(0);
+        const int at = 4 * L * r + lq;
+        if (o) { o[at] = hw; o[at + L] = tw; o[at + 2 * L] = vl; o[at + 3 * L] = vf; }
+        if (ol) { ol[at] = hw; ol[at + L] = tw; ol[at + 2 * L] = vl; ol[at + 3 * L] = vf; }
+      }
+      return;
+    }
     // LaneChangeAccelEnv.get_state (lane_change_accel.py:114-130) / AccelEnv.get_state
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {

@@ -831,7 +831,8 @@ class Env:
     ADDITIONAL = {}
 
     def __init__(self, env_params, sim_params, network, simulator='b200', n_envs=1,
-                 dtype=None, device=0, env_id_base=0, seed=None, record_views=None):
+                 dtype=None, device=0, env_id_base=0, seed=None, record_views=None,
+                 lc_corrected=False):
         if simulator not in ('b200', 'traci'):
             # 'traci' is accepted so unmodified flow_params run; 'aimsun' is out of scope
             raise FatalFlowError('simulator %r is not supported by the B200 engine' % simulator)
@@ -852,7 +853,7 @@ class Env:
         self.engine = EN.Engine(self.spec.types, self.spec.type_of, self.n_envs,
                                 dtype=self.dtype, device=device, capacity=self.spec.capacity,
                                 env_id_base=env_id_base, record_views=int(bool(record_views)),
-                                **self.spec.kw)
+                                lc_corrected=int(bool(lc_corrected)), **self.spec.kw)
         if self.spec.capacity is not None:   # highway: vehicles come and go -> slot ids
             self.spec.veh_ids = ['slot_%d' % i for i in range(self.engine.n_veh)]
             self.spec.type_of = list(self.spec.type_of) + [self.spec.kw.get('inflow_type', 0)] * \
@@ -1031,6 +1032,26 @@ class LaneChangeAccelEnv(AccelEnv):
             raise ValueError('Direction values for lane changes may only be: {-1, 0, 1}.')
 
 
+class LaneChangeAccelPOEnv(LaneChangeAccelEnv):
+    """flow/envs/ring/lane_change_accel.py:164-269. The observation is what the
+    reference's get_state RETURNS (it returns inside its loop over RL vehicles): the
+    per-lane [headways | tailways | leader speeds | follower speeds] block of the first
+    RL vehicle, zeros for the others and one ego speed - 4*n_rl*lanes + 1 numbers, while
+    `observation_space` declares 4*n_rl*lanes + n_rl exactly like the reference. Pass
+    `lc_corrected=True` to the env for the full, normalised observation."""
+    KIND = EN.ENV_LANE_CHANGE_ACCEL_PO
+
+    def __init__(self, env_params, sim_params, network, simulator='b200', **kw):
+        super().__init__(env_params, sim_params, network, simulator, **kw)
+        self.num_lanes = int(network.net_params.additional_params['lanes'])
+        self.visible = []
+
+    @property
+    def observation_space(self):
+        n = self.initial_vehicles.num_rl_vehicles
+        return _box(low=0, high=1, shape=(4 * n * self.num_lanes + n,), dtype=np.float32)
+
+
 class MultiAgentWaveAttenuationPOEnv(Env):
     """flow/envs/multiagent/ring/wave_attenuation.py:143-312 +
     flow/envs/multiagent/base.py:31-225 (MultiEnv): every RL vehicle is an agent.
@@ -1094,7 +1115,8 @@ class MultiAgentWaveAttenuationPOEnv(Env):
 
 
 _ENV_BY_NAME = {c.__name__: c for c in (AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv,
-                                        LaneChangeAccelEnv, MultiAgentWaveAttenuationPOEnv)}
+                                        LaneChangeAccelEnv, LaneChangeAccelPOEnv,
+                                        MultiAgentWaveAttenuationPOEnv)}
 
 
 # =============================================================================

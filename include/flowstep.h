@@ -65,7 +65,14 @@ extern "C" {
 #define FS_ENV_WAVE_ATTENUATION 1  /* WaveAttenuationEnv: obs 2V, WA reward         */
 #define FS_ENV_WAVE_ATTENUATION_PO 2 /* WaveAttenuationPOEnv: obs 3, WA reward      */
 #define FS_ENV_LANE_CHANGE_ACCEL 3 /* LaneChangeAccelEnv: obs 3V, dv - lc penalty   */
-#define FS_ENV_LANE_CHANGE_ACCEL_PO 4 /* LaneChangeAccelPOEnv                       */
+#define FS_ENV_LANE_CHANGE_ACCEL_PO 4 /* LaneChangeAccelPOEnv (lane_change_accel.py:164-269), ring only:
+                                      per-lane leader / follower of the RL vehicles
+                                      (TraCIVehicle._multi_lane_headways, vehicle/traci.py:699-937).
+                                      obs as the reference BEHAVES: block of the FIRST RL vehicle
+                                      [headway_l | tailway_l (m, 1000 = empty lane) | v_lead_l/vmax |
+                                      v_follow_l/vmax], zeros for the other RL vehicles, ONE raw ego
+                                      speed -> 4*n_rl*lanes + 1. lc_corrected=1: every block,
+                                      distances / ring length, n_rl ego speeds / vmax. */
 #define FS_ENV_HIGHWAY 5           /* open highway + inflow: obs 2*slots, dv reward */
 #define FS_ENV_MA_WAVE_ATTENUATION_PO 6 /* MultiAgentWaveAttenuationPOEnv
                                       (flow/envs/multiagent/ring/wave_attenuation.py:143-312):
@@ -147,8 +154,10 @@ typedef struct fs_config {
   int32_t inflow_type;   /* vehicle type index of inflow vehicles               */
   int32_t collision_min_gap; /* 0: crash iff gap<0 ; 1: crash iff gap<minGap    */
   int32_t record_views;  /* 1: keep views.accel/headway/leader/follower current  */
-  int32_t lc_corrected;  /* 0: get_last_lc returns the headway like the reference
-                            (vehicle/traci.py:614); 1: the step of the last change */
+  int32_t lc_corrected;  /* 0: reference behaviour, bugs included: get_last_lc returns the
+                            headway (vehicle/traci.py:614), LaneChangeAccelPOEnv.get_state
+                            returns inside its loop (lane_change_accel.py:263);
+                            1: the step of the last change / the full observation */
   /* highway: vehicles present at reset (types = type_of_vehicle[0..n_initial)) */
   int32_t n_initial;
   int32_t reserved1;

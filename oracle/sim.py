@@ -210,6 +210,45 @@ class RingSim:
                 self.follower[j] = i
                 fol_h[j] = self.headway[i]
 
+    def lane_neighbours(self, i):
+        """Per lane: (headway, tailway, leader, follower) of vehicle i, the result
+        of TraCIVehicle._multi_lane_headways on a closed loop
+        (flow/core/kernel/vehicle/traci.py:699-937). In each lane the leader is
+        the vehicle with the smallest forward distance d = x_j - x_i (+ circ when
+        negative; a vehicle of ANOTHER lane at the same x counts as ahead, d = 0),
+        the follower the one with the smallest backward distance b = x_i - x_j
+        for x_j < x_i, else x_i - x_j + circ. A vehicle alone in its own lane is
+        its own leader and follower one lap away (the edge walk comes back to the
+        vehicle's own edge); an empty lane gives 1000 / -1. Ties: leader = lowest
+        index, follower = highest index (stable sort by position + bisect_left)."""
+        p, C_ = self.pos[i], self.circ
+        own_len = self.types[self.type_of[i]].length
+        out = []
+        for lane in range(self.n_lanes):
+            members = [j for j in range(self.num_vehicles) if self.lane[j] == lane]
+            others = [j for j in members if j != i]
+            if not members:
+                out.append((1000, 1000, -1, -1))
+                continue
+            cand = others if others else [i]
+            lead, best = -1, None
+            for j in cand:
+                d = self.pos[j] - p
+                if d < 0 or j == i:
+                    d = d + C_
+                if best is None or d < best:
+                    lead, best = j, d
+            head = best - self.types[self.type_of[lead]].length
+            foll, bestb = -1, None
+            for j in cand:
+                b = p - self.pos[j]
+                if not self.pos[j] < p:
+                    b = b + C_
+                if bestb is None or b <= bestb:
+                    foll, bestb = j, b
+            out.append((head, bestb - own_len, lead, foll))
+        return out
+
     def mean_speed(self):
         return float(np.mean(self.vel))
 
@@ -328,6 +367,34 @@ class RingSim:
             return np.array([v / self.speed_limit for v in self.vel] +
                             [x / self.circ for x in self.pos] +
                             [ln / self.n_lanes for ln in self.lane])
+        if k == ENV_LANE_CHANGE_ACCEL_PO:
+            # LaneChangeAccelPOEnv.get_state (lane_change_accel.py:215-263) as it
+            # behaves: the `return` sits inside the loop over RL vehicles, so only
+            # the FIRST RL vehicle's block is filled and one ego speed appended
+            # (length 4*n_rl*lanes + 1); headways / tailways are copied before the
+            # in-place normalisation, i.e. they stay in metres (1000 = empty lane);
+            # neighbour speeds / max_speed; ego speed un-normalised.
+            L = self.n_lanes
+            obs = [0.0] * (4 * len(self.rl_idx) * L)
+            if not self.lc_bug_compat:
+                # corrected form (the declared observation_space, 4*n_rl*L + n_rl): every
+                # RL vehicle's block, distances / network length (1 for an empty lane),
+                # ego speeds / max_speed
+                for q, rl in enumerate(self.rl_idx):
+                    nb = self.lane_neighbours(rl)
+                    obs[4 * L * q:4 * L * (q + 1)] = \
+                        [t[0] / self.circ if t[2] >= 0 else 1.0 for t in nb] + \
+                        [t[1] / self.circ if t[3] >= 0 else 1.0 for t in nb] + \
+                        [self.vel[t[2]] / self.speed_limit if t[2] >= 0 else 0.0 for t in nb] + \
+                        [self.vel[t[3]] / self.speed_limit if t[3] >= 0 else 0.0 for t in nb]
+                return np.array(obs + [self.vel[rl] / self.speed_limit for rl in self.rl_idx])
+            rl = self.rl_idx[0]
+            nb = self.lane_neighbours(rl)
+            obs[0:4 * L] = [float(t[0]) for t in nb] + [float(t[1]) for t in nb] + \
+                [self.vel[t[2]] / self.speed_limit if t[2] >= 0 else 0.0 for t in nb] + \
+                [self.vel[t[3]] / self.speed_limit if t[3] >= 0 else 0.0 for t in nb]
+            obs.append(self.vel[rl])
+            return np.array(obs)
         raise NotImplementedError(k)
 
     def desired_velocity(self, fail=False):
@@ -345,7 +412,7 @@ class RingSim:
         k = self.env_kind
         if k == ENV_ACCEL:
             return self.desired_velocity(fail)
-        if k == ENV_LANE_CHANGE_ACCEL:
+        if k in (ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO):
             # lane_change_accel.py:100-112 (penalty compares get_last_lc, i.e.
             # the headway under the reference's bug, with the time counter)
             reward = self.desired_velocity(fail)

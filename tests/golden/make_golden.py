@@ -252,6 +252,41 @@ def ring_c3():
                         actions=np.array(A), crashed=bool(crash))
 
 
+def ring_c3_po():
+    """LaneChangeAccelPOEnv.get_state driven by the reference's own
+    _multi_lane_headways on the 4-edge + 4-junction ring. Case a: 3 lanes, 21 IDM + 1 RL.
+    Case b: 3 lanes with lane 2 empty at the start, 4 IDM + 2 RL (empty-lane 1000s, an RL
+    vehicle alone in a lane being its own leader, the reference's early return leaving the
+    second RL block zero)."""
+    out = {}
+    for tag, groups, init_kw, seed, steps in (
+            ('a', [('human', IDM, {}, {}, 21), ('rl', 'rl', {}, {}, 1)],
+             dict(lanes_distribution=float('inf')), 5, 300),
+            ('b', [('human', IDM, {}, {}, 4), ('rl', 'rl', {}, {}, 2)],
+             dict(lanes_distribution=2), 6, 300)):
+        ring = RefRingLC(groups, 230, lanes=3, init_kw=init_kw, env_kind='lc_po',
+                         env_additional={'max_accel': 3, 'max_decel': 3, 'target_velocity': 10})
+        n_rl = len(ring.rl_idx)
+        rng = np.random.default_rng(seed)
+        P, Vv, Ln, O, R, A = [list(ring.pos)], [list(ring.vel)], [list(ring.lane)], [], [], []
+        for s in range(steps):
+            a = []
+            for q in range(n_rl):
+                a += [float(rng.uniform(-0.8, 0.8)), float(rng.integers(-1, 2))]
+            act = None if s < 20 else a
+            obs, rew, crash = ring.step(act)
+            A.append([np.nan] * (2 * n_rl) if act is None else a)
+            P.append(list(ring.pos)); Vv.append(list(ring.vel)); Ln.append(list(ring.lane))
+            O.append(np.asarray(obs, dtype=np.float64)); R.append(float(rew))
+            if crash:
+                break
+        out.update({'pos_' + tag: np.array(P), 'vel_' + tag: np.array(Vv),
+                    'lane_' + tag: np.array(Ln, dtype=np.int8), 'obs_' + tag: np.array(O),
+                    'reward_' + tag: np.array(R), 'actions_' + tag: np.array(A),
+                    'crashed_' + tag: bool(crash)})
+    np.savez_compressed(os.path.join(HERE, 'ring_c3_po.npz'), **out)
+
+
 def start_pos():
     cases = [dict(length=230, n=22, lanes=1, kw=dict(bunching=20)),
              dict(length=230, n=22, lanes=1, kw=dict()),
@@ -283,7 +318,8 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c3(); ring_zoo(); ring_ma(); start_pos(); sumo_fixture()
+    ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_zoo(); ring_ma(); start_pos()
+    sumo_fixture()
     print('golden vectors written to', HERE)
 
 

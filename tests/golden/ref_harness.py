@@ -69,6 +69,22 @@ class _Net:
     def get_x(self, edge, position):
         return self.total_edgestarts_dict[edge] + position
 
+    # connection tables of the generated ring net (edge -> junction -> edge, lane kept),
+    # what TraCIKernelNetwork.next_edge / prev_edge return (network/traci.py:347-359)
+    _ORDER = ["bottom", ":right_0", "right", ":top_0", "top", ":left_0", "left", ":bottom_0"]
+
+    def get_junction_list(self):
+        return [":right_0", ":top_0", ":left_0", ":bottom_0"]
+
+    def get_lane_list(self):
+        return ['%s_%d' % (e, l) for e in self._ORDER for l in range(self.lanes)]
+
+    def next_edge(self, edge, lane):
+        return [(self._ORDER[(self._ORDER.index(edge) + 1) % 8], lane)]
+
+    def prev_edge(self, edge, lane):
+        return [(self._ORDER[(self._ORDER.index(edge) - 1) % 8], lane)]
+
     gen_even_start_pos = BaseKernelNetwork.gen_even_start_pos
     _get_start_pos_util = BaseKernelNetwork._get_start_pos_util
 
@@ -299,7 +315,8 @@ class RefRingLC(RefRing):
 
     def __init__(self, *a, lane_change_duration=5, **kw):
         from flow.envs.ring.lane_change_accel import LaneChangeAccelEnv
-        self.LC = LaneChangeAccelEnv
+        from flow.envs.ring.lane_change_accel import LaneChangeAccelPOEnv
+        self.LC = LaneChangeAccelPOEnv if kw.get('env_kind') == 'lc_po' else LaneChangeAccelEnv
         kw.setdefault('env_kind', 'lc')
         self.requests = {}
         super().__init__(*a, **kw)
@@ -333,7 +350,23 @@ class RefRingLC(RefRing):
             def get_headway(s, vid, error=-1001):
                 return veh.get_headway(vid, error)
 
-        tv = _TV()
+            def get_length(s, vid, error=-1001):
+                return 5.0
+
+        class _TVPO(_TV):
+            def get_edge(s, vid):
+                return h.net.get_edge(h.pos[h.index[vid]])[0]
+
+            def get_position(s, vid, error=-1001):
+                return h.net.get_edge(h.pos[h.index[vid]])[1]
+
+        for name in ('_multi_lane_headways', '_multi_lane_headways_util', '_next_edge_leaders',
+                     '_prev_edge_followers', 'set_lane_headways', 'set_lane_tailways',
+                     'set_lane_leaders', 'set_lane_followers', 'get_lane_headways',
+                     'get_lane_tailways', 'get_lane_leaders', 'get_lane_followers'):
+            setattr(_TVPO, name, getattr(TraCIVehicle, name))
+
+        tv = _TVPO() if self.env_kind == 'lc_po' else _TV()
         tv.kernel_api.vehicle = type('KV', (), {})()
         tv.kernel_api.vehicle.slowDown = self.sink.slowDown
         tv.kernel_api.vehicle.changeLane = \
@@ -345,6 +378,12 @@ class RefRingLC(RefRing):
             tv, ids, direction)
         veh.get_last_lc = lambda vid, error=-1001: TraCIVehicle.get_last_lc(tv, vid, error)
         self.sorted_ids = self.ids
+        if self.env_kind == 'lc_po':
+            for name in ('get_lane_headways', 'get_lane_tailways', 'get_lane_leaders',
+                         'get_lane_followers'):
+                setattr(veh, name, getattr(tv, name))
+            self.num_lanes = self.lanes        # LaneChangeAccelPOEnv.__init__
+            self.visible = []
 
     def _sync_tv(self):
         self.tv._TraCIVehicle__rl_ids = self.k.vehicle.get_rl_ids()
@@ -393,6 +432,8 @@ class RefRingLC(RefRing):
             self.pos[i] = (self.pos[i] + self.vel[i] * self.dt) % self.net.circ
         self._update()
         self._sync_tv()
+        if self.env_kind == 'lc_po':
+            self.tv._multi_lane_headways()        # k.update, vehicle/traci.py:255-256
         crash = any(h < 0 for h in self.headway)
         obs = self.LC.get_state(self)
         reward = self.LC.compute_reward(self, rl_actions, fail=crash)

@@ -61,6 +61,8 @@ def make_engine(groups, n_envs, dtype='f64', length=None, **kw):
     if length is not None:
         kw.setdefault('length_lo', float(length))
         kw.setdefault('length_hi', float(length))
+    if 'lanes_distribution' in kw:
+        kw['lanes_distribution'] = int(min(kw['lanes_distribution'], 1 << 30))
     return EN.Engine(engine_types(groups), type_table(groups), n_envs, dtype=dtype, **kw)
 
 

@@ -160,6 +160,30 @@ def test_lane_change_direction_check_is_the_references():
     env._check_host_actions(np.array([0.5, -1, 0.1, 1]))
 
 
+def lane_change_po_flow_params(api=F):
+    """3-lane 230 m ring, 21 IDM + 1 RL, LaneChangeAccelPOEnv (tests/golden/ring_c3_po.npz, case a)."""
+    v = api.VehicleParams()
+    v.add(veh_id='human', acceleration_controller=(api.IDMController, {}),
+          routing_controller=(api.ContinuousRouter, {}), num_vehicles=21)
+    v.add(veh_id='rl', acceleration_controller=(api.RLController, {}),
+          routing_controller=(api.ContinuousRouter, {}), num_vehicles=1)
+    return dict(
+        exp_tag='lc_po', env_name=api.LaneChangeAccelPOEnv, network=api.RingNetwork,
+        simulator='traci', sim=api.SumoParams(sim_step=0.1, render=False),
+        env=api.EnvParams(horizon=3000, additional_params={
+            'max_accel': 3, 'max_decel': 3, 'lane_change_duration': 5, 'target_velocity': 10,
+            'sort_vehicles': False}),
+        net=api.NetParams(additional_params={'length': 230, 'lanes': 3, 'speed_limit': 30,
+                                             'resolution': 40}),
+        veh=v, initial=api.InitialConfig(lanes_distribution=float('inf')), detector_params=None)
+
+
+def test_lane_change_po_env_compiles():
+    spec = spec_of(lane_change_po_flow_params())
+    assert spec.kw['env_kind'] == EN.ENV_LANE_CHANGE_ACCEL_PO and spec.kw['n_lanes'] == 3
+    assert spec.types[1].lc_controller == EN.LC_RL
+
+
 def test_highway_inflow_compiles():
     v = F.VehicleParams()
     v.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=10)
@@ -241,6 +265,30 @@ def test_gpu_wave_attenuation_po_env_matches_golden():
         assert env.k.vehicle.get_rl_ids() == ['rl_0']
         assert env.k.vehicle.num_rl_vehicles == 1
         env.terminate()
+
+
+@pytest.mark.gpu
+def test_gpu_lane_change_po_env_matches_golden():
+    """LaneChangeAccelPOEnv through the mirrored API == the reference's get_state on its own
+    multi-lane bookkeeping; spaces as the reference declares them."""
+    z = np.load(os.path.join(G, 'ring_c3_po.npz'))
+    env = F.make_create_env(lane_change_po_flow_params())[0]()
+    obs = env.reset()
+    assert env.observation_space.shape == (13,) and env.action_space.shape == (2,)
+    assert obs.shape == (13,) and env.num_lanes == 3
+    for s, a in enumerate(z['actions_a'][:150]):
+        obs, r, done, _ = env.step(None if np.isnan(a).any() else a)
+        np.testing.assert_allclose(obs, z['obs_a'][s], rtol=1e-9, atol=1e-9)
+        assert abs(r - z['reward_a'][s]) <= 1e-9
+        assert not done
+    assert env.k.vehicle.get_lane('rl_0') == int(z['lane_a'][150][21])
+    with pytest.raises(ValueError):          # vehicle/traci.py:973-975
+        env.step(np.array([0.1, 0.5]))
+    env.terminate()
+    full = F.make_create_env(lane_change_po_flow_params(), lc_corrected=True)[0]()
+    o = full.reset()
+    assert o.shape == (13,) and 0 <= o.min() and o.max() <= 1     # one RL: same length, normalised
+    full.terminate()
 
 
 @pytest.mark.gpu

@@ -94,3 +94,116 @@ def test_c3_fp32_aggregates_vs_oracle():
     assert (eng.lane.cpu().numpy()[:, 0] == np.array(o.lane)).all()
     assert abs(eng.vel.cpu().numpy()[:, 0].mean() - np.mean(o.vel)) <= 0.01 * np.mean(o.vel)
     assert abs(float(rew_seq[:, 0].sum()) - r_o) <= 0.01 * abs(r_o)
+
+
+# ---- LaneChangeAccelPOEnv (per-lane leaders / followers of the RL vehicles) ----------
+from tests.test_oracle_golden import PO_CASES
+
+
+def mk_po(tag, E, dtype, **kw):
+    groups, dist = PO_CASES[tag]
+    kw.setdefault('n_lanes', 3)
+    return S.make_engine([S.vt(c, n) for c, n in groups], E, dtype, length=230,
+                         env_kind=OS.ENV_LANE_CHANGE_ACCEL_PO, act_lo=-3.0, act_hi=3.0,
+                         lanes_distribution=dist, **kw)
+
+
+@pytest.mark.parametrize('tag', ['a', 'b'])
+def test_lane_change_po_golden_fp64(tag):
+    """Observation of the reference's LaneChangeAccelPOEnv.get_state fed by its own
+    _multi_lane_headways (tests/golden/ring_c3_po.npz): fused launches with obs_seq and
+    single steps, 1e-9; the 1000-m empty-lane defaults and the zero block exactly."""
+    import torch
+    z = np.load(os.path.join(G, 'ring_c3_po.npz'))
+    acts, ref = z['actions_' + tag], z['obs_' + tag]
+    n_rl = acts.shape[1] // 2
+    E = 3
+    eng = mk_po(tag, E, 'f64')
+    eng.reset()
+    assert eng.obs_dim == ref.shape[1] == 4 * n_rl * 3 + 1
+    warm = int(np.isnan(acts).any(1).sum())
+    for s in range(warm):
+        obs, rew, done = eng.step(None)
+        assert close(obs.cpu().numpy()[1], ref[s]) <= 1e-9, s
+    s, n = warm, len(acts)
+    for K in (1, 5, 60, 2, 100, 112):
+        K = min(K, n - s)
+        act = torch.tensor(np.repeat(acts[s:s + K, :, None], E, 2), device='cuda')
+        obs_seq = torch.empty(K, E, eng.obs_dim, device='cuda', dtype=torch.float64)
+        rew_seq = torch.empty(K, E, device='cuda', dtype=torch.float64)
+        eng.step(act, k=K, obs_seq=obs_seq, reward_seq=rew_seq)
+        o = obs_seq.cpu().numpy()
+        for e in (0, 2):
+            assert close(o[:, e], ref[s:s + K]) <= 1e-9, (s, K)
+            assert np.array_equal(o[:, e] == 1000, ref[s:s + K] == 1000)
+            assert np.array_equal(o[:, e, 12:-1], ref[s:s + K, 12:-1])       # zero blocks
+            assert close(rew_seq.cpu().numpy()[:, e], z['reward_' + tag][s:s + K]) <= 1e-9
+        assert close(eng.obs.cpu().numpy()[0], ref[s + K - 1]) <= 1e-9
+        assert (eng.lane.cpu().numpy()[:, 0] == z['lane_' + tag][s + K]).all()
+        s += K
+    assert s == n
+
+
+@pytest.mark.parametrize('corrected', [0, 1])
+@pytest.mark.parametrize('lanes,groups', [(1, [('IDM', 5), ('RL', 1)]),
+                                          (4, [('IDM', 9), ('RL', 3)]),
+                                          (3, [('RL', 2)])])
+def test_lane_change_po_vs_oracle(lanes, groups, corrected):
+    """Other shapes against the oracle: one lane, 4 lanes with 3 RL vehicles, RL vehicles
+    alone on the ring (own leader one lap away, empty lanes); reference behaviour and the
+    corrected observation (lc_corrected=1: every block, normalised)."""
+    import torch
+    E, K = 4, 80
+    g = [S.vt(c, n) for c, n in groups]
+    n_rl = sum(n for c, n in groups if c == 'RL')
+    kw = dict(env_kind=OS.ENV_LANE_CHANGE_ACCEL_PO, n_lanes=lanes, act_lo=-3, act_hi=3,
+              lanes_distribution=float('inf'))
+    eng = S.make_engine(g, E, 'f64', length=120, lc_corrected=corrected, **kw)
+    o = S.make_oracle(g, 120, **kw)
+    o.lc_bug_compat = not corrected
+    obs0 = eng.reset()
+    assert eng.obs_dim == 4 * n_rl * lanes + (n_rl if corrected else 1)
+    assert close(obs0.cpu().numpy()[0], o.get_state()) <= 1e-9
+    rng = np.random.default_rng(7 + lanes)
+    acts = np.zeros((K, 2 * n_rl))
+    acts[:, 0::2] = rng.uniform(-0.6, 1.0, (K, n_rl))
+    acts[:, 1::2] = rng.integers(-1, 2, (K, n_rl))
+    obs_seq = torch.empty(K, E, eng.obs_dim, device='cuda', dtype=torch.float64)
+    rew_seq = torch.empty(K, E, device='cuda', dtype=torch.float64)
+    done_seq = torch.empty(K, E, device='cuda', dtype=torch.uint8)
+    eng.step(torch.tensor(np.repeat(acts[:, :, None], E, 2), device='cuda'), k=K,
+             obs_seq=obs_seq, reward_seq=rew_seq, done_seq=done_seq)
+    og, rg, dg = obs_seq.cpu().numpy(), rew_seq.cpu().numpy(), done_seq.cpu().numpy()
+    for k in range(K):
+        ob, r, d = o.step(list(acts[k]))
+        assert close(og[k, 3], ob) <= 1e-9, k
+        assert close(rg[k, 3], r) <= 1e-9 and bool(dg[k, 3]) == d, k
+        if d:
+            break
+    assert k > 20
+
+
+def test_lane_change_po_fp32_and_batch():
+    """fp32 against fp64 on the same actions (short horizon, before rounding can flip a
+    lane-change decision), envs of a batch independent of each other."""
+    import torch
+    E, K = 64, 40
+    a32, a64 = mk_po('a', E, 'f32'), mk_po('a', E, 'f64')
+    a32.reset(); a64.reset()
+    gen = torch.Generator(device='cuda'); gen.manual_seed(5)
+    act = torch.empty(K, 2, E, device='cuda', dtype=torch.float64)
+    act[:, 0] = torch.rand(K, E, device='cuda', dtype=torch.float64, generator=gen) - 0.5
+    act[:, 1] = torch.randint(-1, 2, (K, E), device='cuda', generator=gen).to(torch.float64)
+    o32 = torch.empty(K, E, 13, device='cuda')
+    o64 = torch.empty(K, E, 13, device='cuda', dtype=torch.float64)
+    a32.step(act.float(), k=K, obs_seq=o32)
+    a64.step(act, k=K, obs_seq=o64)
+    same = (a32.lane == a64.lane).all(0)
+    assert same.float().mean() > 0.9
+    d = (o32.double() - o64).abs()[:, same]
+    assert float(d.max()) < 5e-3
+    solo = mk_po('a', 1, 'f64')
+    solo.reset()
+    o1 = torch.empty(K, 1, 13, device='cuda', dtype=torch.float64)
+    solo.step(act[:, :, 17:18].contiguous(), k=K, obs_seq=o1)
+    assert torch.equal(o1[:, 0], o64[:, 17])

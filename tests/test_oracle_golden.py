@@ -200,6 +200,41 @@ def test_c3_lane_change_trajectory_bit_exact():
     assert done == bool(z['crashed'])
 
 
+PO_CASES = {'a': ([('IDM', 21), ('RL', 1)], float('inf')), 'b': ([('IDM', 4), ('RL', 2)], 2)}
+
+
+@pytest.mark.parametrize('tag', ['a', 'b'])
+def test_c3_lane_change_po_observation(tag):
+    """LaneChangeAccelPOEnv.get_state fed by the reference's own _multi_lane_headways
+    walking the ring's 4 edges + 4 junctions (tests/golden/ring_c3_po.npz) vs the
+    oracle's closed-loop restatement. Trajectory bit-exact; the observation to 1e-12
+    relative (the reference adds per-edge offsets, the oracle subtracts loop
+    coordinates - same numbers up to the last bits), leaders' speeds exactly."""
+    z = np.load(os.path.join(G, 'ring_c3_po.npz'))
+    groups, dist = PO_CASES[tag]
+    o = S.make_oracle([S.vt(c, n) for c, n in groups], 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL_PO,
+                      n_lanes=3, act_lo=-3, act_hi=3, lanes_distribution=dist)
+    assert np.array_equal(np.array(o.pos), z['pos_' + tag][0])
+    assert o.lane == list(z['lane_' + tag][0])
+    n_rl = sum(n for c, n in groups if c == 'RL')
+    assert z['obs_' + tag].shape[1] == 4 * n_rl * 3 + 1      # the reference's early return
+    for s, a in enumerate(z['actions_' + tag]):
+        obs, r, done = o.step(None if np.isnan(a).any() else list(a))
+        assert np.array_equal(np.array(o.pos), z['pos_' + tag][s + 1]), s
+        assert np.array_equal(np.array(o.vel), z['vel_' + tag][s + 1]), s
+        assert o.lane == list(z['lane_' + tag][s + 1]), s
+        ref = z['obs_' + tag][s]
+        assert obs.shape == ref.shape
+        assert np.abs(obs - ref).max() <= 1e-12 * 230, (s, obs, ref)
+        assert np.array_equal(obs[6:], ref[6:]), s          # speeds, zero block, ego speed
+        assert np.array_equal(obs == 1000, ref == 1000)
+        assert r == z['reward_' + tag][s], s
+    assert done == bool(z['crashed_' + tag])
+    if tag == 'b':
+        assert (z['obs_b'] == 1000).any()                     # empty lanes were seen
+        assert np.abs(z['obs_b'][:, :6] - (230.4 - 5)).min() < 1e-9   # own leader, one lap away
+
+
 def test_lane_change_direction_validation():
     o = S.make_oracle(c3_groups(), 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL, n_lanes=3,
                       act_lo=-3, act_hi=3)
