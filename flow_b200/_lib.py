@@ -14,7 +14,7 @@ SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
 SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu']
 HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_ring_hot.cuh', 'fs_reset.cuh', 'fs_launch.h',
-           'fs_multilane.cuh', 'fs_highway.cuh']
+           'fs_multilane.cuh', 'fs_highway.cuh', 'fs_sort.cuh']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -53,7 +53,7 @@ class FsConfig(C.Structure):
                 ('inflow_depart_speed', C.c_double),
                 ('inflow_type', C.c_int32), ('collision_min_gap', C.c_int32),
                 ('record_views', C.c_int32), ('lc_corrected', C.c_int32),
-                ('n_initial', C.c_int32), ('reserved1', C.c_int32),
+                ('n_initial', C.c_int32), ('env_flags', C.c_int32),
                 ('inflow_begin', C.c_double)]
 
 

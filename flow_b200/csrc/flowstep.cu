@@ -19,6 +19,7 @@
 #include "fs_launch.h"
 #include "fs_multilane.cuh"
 #include "fs_highway.cuh"
+#include "fs_sort.cuh"
 
 static thread_local std::string g_create_error;
 
@@ -48,6 +49,10 @@ struct fs_engine {
   int* counters = nullptr;   // highway: [4][E] in network, departed, arrived, spawned
   uint8_t* vtype = nullptr;  // highway: [E][CAP] type of the vehicle in each slot
   bool env_major = false;  // pos/vel/lane stored [E][V] (multi-lane, highway)
+  // FS_ENVF_SORT_VEHICLES (fs_sort.cuh): keys [E][V], their validity [E], permuted actions [A][E]
+  void *abs_pos = nullptr, *prev_pos = nullptr, *act_sorted = nullptr;
+  uint8_t* keys_valid = nullptr;
+  bool sort_on() const { return (cfg.env_flags & FS_ENVF_SORT_VEHICLES) != 0; }
   void *headway = nullptr, *accel = nullptr, *obs = nullptr, *reward = nullptr;
   double *stats = nullptr, *lengths_dev = nullptr;
   // staging for fs_step_host
@@ -140,6 +145,14 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
     return fail(nullptr, FS_EINVAL, "fs_create: n_lanes must be in 1..8");
   if (obs_dim_for(*cfg) < 0)
     return fail(nullptr, FS_EINVAL, "fs_create: unsupported env_kind");
+  if ((cfg->env_flags & FS_ENVF_SORT_VEHICLES) &&
+      (cfg->topology != FS_TOPO_RING ||
+       (cfg->env_kind != FS_ENV_ACCEL && cfg->env_kind != FS_ENV_LANE_CHANGE_ACCEL &&
+        cfg->env_kind != FS_ENV_LANE_CHANGE_ACCEL_PO)))
+    return fail(nullptr, FS_EINVAL, "fs_create: sort_vehicles exists for AccelEnv / "
+                                    "LaneChangeAccel(PO)Env on the ring only");
+  if (cfg->env_flags & ~(FS_ENVF_EVALUATE | FS_ENVF_SORT_VEHICLES))
+    return fail(nullptr, FS_EINVAL, "fs_create: unknown env_flags bit");
   int ndev = 0;
   cudaError_t st = cudaGetDeviceCount(&ndev);
   if (st != cudaSuccess || ndev == 0)
@@ -174,6 +187,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->stats, FS_STAT_STRIPES * 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
   e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY;
   if (e->env_major) A(&e->last_lc, V * E * 4);
+  if (e->sort_on()) { A(&e->abs_pos, V * E * ts); A(&e->prev_pos, V * E * ts); A(&e->keys_valid, E); }
   if (cfg->topology == FS_TOPO_HIGHWAY) { A(&e->counters, 4 * E * 4); A(&e->vtype, V * E); }
   if (cfg->record_views) {
     A(&e->headway, V * E * ts); A(&e->accel, V * E * ts);
@@ -224,6 +238,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
   c.obs_max_length = (T)g.obs_max_length;
   c.length_lo = (T)g.length_lo; c.length_hi = (T)g.length_hi;
   c.lanes_distribution = g.lanes_distribution;
+  c.evaluate = (g.env_flags & FS_ENVF_EVALUATE) ? 1 : 0;
   for (int t = 0; t < n_types; ++t) {
     const fs_vtype& s = types[t];
     fs::TypeP<T>& d = c.types[t];
@@ -296,7 +311,7 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     // and at most one RL type, equal lengths, delta = 4
     int ta = -1, tb = -1;
     bool ok = e->cfg.n_veh == 22 && !e->generic && e->cfg.topology == FS_TOPO_RING &&
-              e->cfg.n_lanes == 1;
+              e->cfg.n_lanes == 1 && !(e->cfg.env_flags & FS_ENVF_EVALUATE);
     for (int i = 0; ok && i < e->cfg.n_veh; ++i) {
       const int t = type_of_vehicle[i];
       const fs_vtype& s = types[t];
@@ -357,6 +372,8 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     if (rc == FS_OK) rc = dev_alloc(e, &e->hist_sum, (size_t)n_pi * E * sizeof(double));
     if (rc == FS_OK) rc = dev_alloc(e, &e->hist_cnt, (size_t)n_pi * E * sizeof(int));
   }
+  if (rc == FS_OK && e->sort_on() && e->act_dim > 0 && !e->act_sorted)
+    rc = dev_alloc(e, &e->act_sorted, (size_t)e->act_dim * E * ts);
   if (rc != FS_OK) return rc;
   e->types_set = true;
   return FS_OK;
@@ -510,8 +527,71 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
 }
 
 template <typename T>
+static fs::SortBufs<T> sort_bufs(fs_engine* e, const uint8_t* mask) {
+  fs::SortBufs<T> b;
+  b.pos = (const T*)e->pos;
+  b.vs = e->env_major ? 1 : e->cfg.n_envs; b.es = e->env_major ? e->cfg.n_veh : 1;
+  b.abs_pos = (T*)e->abs_pos; b.prev_pos = (T*)e->prev_pos; b.keys_valid = e->keys_valid;
+  b.circ = (const T*)e->circ; b.done = e->done; b.mask = mask;
+  return b;
+}
+
+// sort_vehicles: every step is  sort_pre -> step kernel (k = 1) -> sort_obs  (fs_sort.cuh)
+template <typename T>
+static int do_step_sorted(fs_engine* e, const void* actions, int k, void* obs_seq,
+                          void* reward_seq, uint8_t* done_seq, const uint8_t* mask, int stats,
+                          int ignore_done) {
+  const int E = e->cfg.n_envs, V = e->cfg.n_veh, wpb = 4, grid = (E + wpb - 1) / wpb;
+  const fs::SortBufs<T> sb = sort_bufs<T>(e, mask);
+  const bool accel_env = e->cfg.env_kind == FS_ENV_ACCEL;
+  const int rows = e->cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL ? 3 : 2;
+  const bool permute_obs = e->cfg.env_kind != FS_ENV_LANE_CHANGE_ACCEL_PO;
+  auto post = [&](T* obs_step) {
+    if (!permute_obs) return;
+    if (V <= 32) fs::sort_obs_kernel<T, 1><<<grid, wpb * 32, 0, e->stream>>>(cfg_of<T>(e), sb, (T*)e->obs, obs_step, rows);
+    else if (V <= 96) fs::sort_obs_kernel<T, 3><<<grid, wpb * 32, 0, e->stream>>>(cfg_of<T>(e), sb, (T*)e->obs, obs_step, rows);
+    else fs::sort_obs_kernel<T, 8><<<grid, wpb * 32, 0, e->stream>>>(cfg_of<T>(e), sb, (T*)e->obs, obs_step, rows);
+    e->launches++;
+  };
+  fs::StepArgs<T> a;
+  a.mask = mask; a.accumulate_stats = stats; a.ignore_done = ignore_done;
+  a.write_views = e->cfg.record_views != 0;
+  if (k == 0) {  // observation of the current state (reset without warm-up)
+    a.actions = nullptr; a.obs_seq = nullptr; a.reward_seq = nullptr; a.done_seq = nullptr;
+    a.k_steps = 0;
+    int rc = run_steps<T>(e, a);
+    if (rc != FS_OK) return rc;
+    post(nullptr);
+    FS_CUDA(e, cudaGetLastError());
+    return FS_OK;
+  }
+  const size_t act_row = (size_t)e->act_dim * E, obs_row = (size_t)E * e->obs_dim;
+  for (int s = 0; s < k; ++s) {
+    const T* act = actions ? (const T*)actions + s * act_row : nullptr;
+    const bool remap = act != nullptr && e->n_rl > 1;
+    if (remap || accel_env) {
+      fs::sort_pre_kernel<T><<<grid, wpb * 32, 0, e->stream>>>(
+          cfg_of<T>(e), sb, remap ? act : nullptr, (T*)e->act_sorted, accel_env ? 1 : 0, ignore_done);
+      e->launches++;
+    }
+    a.actions = remap ? (const T*)e->act_sorted : act;
+    a.obs_seq = obs_seq ? (T*)obs_seq + s * obs_row : nullptr;
+    a.reward_seq = reward_seq ? (T*)reward_seq + (size_t)s * E : nullptr;
+    a.done_seq = done_seq ? done_seq + (size_t)s * E : nullptr;
+    a.k_steps = 1;
+    int rc = run_steps<T>(e, a);
+    if (rc != FS_OK) return rc;
+    post(a.obs_seq);
+  }
+  FS_CUDA(e, cudaGetLastError());
+  return FS_OK;
+}
+
+template <typename T>
 static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
                    uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done) {
+  if (e->sort_on())
+    return do_step_sorted<T>(e, actions, k, obs_seq, reward_seq, done_seq, mask, stats, ignore_done);
   fs::StepArgs<T> a;
   a.actions = (const T*)actions; a.obs_seq = (T*)obs_seq; a.reward_seq = (T*)reward_seq;
   a.done_seq = done_seq; a.mask = mask; a.k_steps = k; a.accumulate_stats = stats;
@@ -549,7 +629,14 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   // warm-up: Env.reset steps with rl_actions=None (flow/envs/base.py:554-555)
-  return do_step<T>(e, nullptr, e->cfg.warmup_steps, nullptr, nullptr, nullptr, mask_dev, 0, 1);
+  int rc = do_step<T>(e, nullptr, e->cfg.warmup_steps, nullptr, nullptr, nullptr, mask_dev, 0, 1);
+  if (rc == FS_OK && e->sort_on()) {  // AccelEnv.reset tail (accel.py:178-181), after the observation
+    fs::sort_setkeys_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(
+        cfg_of<T>(e), sort_bufs<T>(e, mask_dev));
+    e->launches++;
+    FS_CUDA(e, cudaGetLastError());
+  }
+  return rc;
 }
 
 static int check_room(fs_engine* e, double L) {

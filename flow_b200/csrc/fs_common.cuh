@@ -45,7 +45,7 @@ struct Cfg {
   T x0, bunching, init_min_gap;
   T target_velocity, act_lo, act_hi, obs_max_length;
   T length_lo, length_hi;
-  int lanes_distribution, pad0;
+  int lanes_distribution, evaluate;  // evaluate: EnvParams.evaluate (AccelEnv reward = mean speed)
   TypeP<T> types[FS_MAX_TYPES];
   uint8_t type_of[FS_MAX_VEH];
   int16_t rl_index[FS_MAX_VEH];  // vehicle -> action slot, -1 if not RL

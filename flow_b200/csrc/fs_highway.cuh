@@ -227,7 +227,8 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       }
       crash = __any_sync(0xffffffffu, cr);
       done = crash || tc >= t_end;
-      if (crash || n == 0) reward = T(0);
+      if (cfg.evaluate) reward = N::div(sv, T(n));   // accel.py:111-112 (np.mean: NaN when empty)
+      else if (crash || n == 0) reward = T(0);
       else {  // rewards.desired_velocity over the vehicles present
         T mc2 = T(0);
         const T t2 = mul(cfg.target_velocity, cfg.target_velocity);

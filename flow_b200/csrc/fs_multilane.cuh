@@ -339,8 +339,10 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
           if (mean_act > T(0)) reward = add(reward, mul(T(4), T(0) - mean_act));
         }
       } else {
-        // rewards.desired_velocity (+ LaneChangeAccelEnv lane-change penalty)
-        if (crash) reward = T(0);
+        // rewards.desired_velocity (+ LaneChangeAccelEnv lane-change penalty);
+        // AccelEnv with env_params.evaluate: mean speed (accel.py:111-112)
+        if (cfg.evaluate && !lc_env) reward = N::div(sv, T(V));
+        else if (crash) reward = T(0);
         else {
           const T cost = N::sqrt(sq);
           const T eps = T(1.1920928955078125e-07);

@@ -317,8 +317,10 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
       tc += 1;
       done = crash || tc >= t_end;
       if (cfg.env_kind == FS_ENV_ACCEL) {
-        // rewards.desired_velocity, flow/core/rewards.py:6-59
-        if (crash) reward = T(0);
+        // AccelEnv.compute_reward (accel.py:109-114): mean speed when env_params.evaluate,
+        // else rewards.desired_velocity, flow/core/rewards.py:6-59
+        if (cfg.evaluate) reward = N::div(sv, T(V));
+        else if (crash) reward = T(0);
         else {
           const T cost = N::sqrt(sq);
           const T eps = T(1.1920928955078125e-07);  // np.finfo(np.float32).eps

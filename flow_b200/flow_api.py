@@ -554,10 +554,10 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         raise NotImplementedError('edges_distribution other than "all"')
     if getattr(sim_params, 'use_ballistic', False):
         raise NotImplementedError('ballistic integration (the engine restates the Euler move)')
-    if env_params.evaluate:
-        raise NotImplementedError('evaluate=True reward variants')
-    if ap.get('sort_vehicles'):
-        raise NotImplementedError('sort_vehicles=True (vehicle order is the id order)')
+    sort_on = bool(ap.get('sort_vehicles')) and env_cls.KIND in (
+        EN.ENV_ACCEL, EN.ENV_LANE_CHANGE_ACCEL, EN.ENV_LANE_CHANGE_ACCEL_PO)
+    if sort_on and network.TOPOLOGY != EN.TOPO_RING:
+        raise NotImplementedError('sort_vehicles=True on the open highway (slots are re-packed)')
     lc_env = env_cls.KIND in (EN.ENV_LANE_CHANGE_ACCEL, EN.ENV_LANE_CHANGE_ACCEL_PO)
     types, names, type_of, ids = [], [], [], []
     for t, row in enumerate(veh.initial):
@@ -580,6 +580,10 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         target_velocity=float(ap.get('target_velocity', 10.0)),
         act_lo=-abs(float(ap.get('max_decel', 4.5))), act_hi=float(ap.get('max_accel', 2.6)),
         lane_change_duration=int(ap.get('lane_change_duration', 5)),
+        # AccelEnv.compute_reward is the only reader of env_params.evaluate on this path
+        # (accel.py:111-112); sorted_ids: accel.py:150-169
+        evaluate=int(bool(env_params.evaluate) and env_cls.KIND == EN.ENV_ACCEL),
+        sort_vehicles=int(sort_on),
         seed=int(seed if seed is not None else (getattr(sim_params, 'seed', None) or 0)))
     capacity = None
     if network.TOPOLOGY == EN.TOPO_RING:

@@ -102,6 +102,13 @@ extern "C" {
 #define FS_LC_STATIC 1  /* StaticLaneChanger: direction 0                      */
 #define FS_LC_RL 2      /* direction comes from the action vector              */
 
+/* fs_config.env_flags */
+#define FS_ENVF_EVALUATE 1      /* EnvParams.evaluate: AccelEnv reward = mean speed
+                                   (flow/envs/ring/accel.py:109-114)                    */
+#define FS_ENVF_SORT_VEHICLES 2 /* additional_params['sort_vehicles']: observation rows and RL
+                                   action slots in order of AccelEnv.absolute_position
+                                   (flow/envs/ring/accel.py:100-169); ring topology only  */
+
 #define FS_MAX_TYPES 16
 #define FS_NPARAM 8
 
@@ -160,7 +167,7 @@ typedef struct fs_config {
                             1: the step of the last change / the full observation */
   /* highway: vehicles present at reset (types = type_of_vehicle[0..n_initial)) */
   int32_t n_initial;
-  int32_t reserved1;
+  int32_t env_flags;     /* FS_ENVF_* bits (0 = reference defaults)              */
   double inflow_begin;   /* s; InFlows.add(begin=1) */
 } fs_config;
 

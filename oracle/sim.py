@@ -112,7 +112,8 @@ class RingSim:
                  lanes_distribution=float('inf'), warmup_steps=0,
                  horizon=3000, target_velocity=10.0, act_lo=-4.5, act_hi=2.6,
                  clip_actions=False, obs_max_length=None,
-                 lane_change_duration=5, noise_fn=None):
+                 lane_change_duration=5, noise_fn=None, evaluate=False,
+                 sort_vehicles=False):
         self.types = types
         self.type_of = list(type_of_vehicle)
         self.num_vehicles = len(self.type_of)
@@ -132,6 +133,12 @@ class RingSim:
         self.lane_change_duration = lane_change_duration
         self.noise_fn = noise_fn  # (step, vehicle) -> N(0,1) sample
         self.lc_bug_compat = True  # get_last_lc returns the headway (vehicle/traci.py:614)
+        self.evaluate = evaluate            # EnvParams.evaluate (accel.py:111-112)
+        self.sort_vehicles = sort_vehicles  # additional_params['sort_vehicles'] (accel.py:150-169)
+        # AccelEnv.absolute_position / prev_pos: dicts made once in __init__ (accel.py:77-78),
+        # so they persist across resets; None = no entry yet (key -1001)
+        self.abs_position = None
+        self.prev_pos = None
         self.rl_idx = [i for i, t in enumerate(self.type_of)
                        if types[t].controller == C.RL]
         self.reset(length)
@@ -159,7 +166,34 @@ class RingSim:
         if run_warmup:
             for _ in range(self.warmup_steps):
                 obs, _, _ = self.step(None)
+        if self.env_kind in (ENV_ACCEL, ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO):
+            # AccelEnv.reset tail (accel.py:178-181), after the observation was taken
+            self.abs_position = list(self.pos)
+            self.prev_pos = list(self.pos)
         return obs
+
+    def sorted_idx(self):
+        """AccelEnv.sorted_ids (accel.py:150-169): stable sort by absolute position."""
+        V = self.num_vehicles
+        if not self.sort_vehicles or self.abs_position is None:
+            return list(range(V))
+        return sorted(range(V), key=lambda i: self.abs_position[i])
+
+    def additional_command(self):
+        """AccelEnv.additional_command (accel.py:125-148), called before the simulator
+        moves (base.py:365). WaveAttenuationEnv is not an AccelEnv and LaneChangeAccelEnv
+        overrides it without the bookkeeping (lane_change_accel.py:156-161)."""
+        if self.env_kind != ENV_ACCEL:
+            return
+        V = self.num_vehicles
+        first = self.abs_position is None
+        if first:
+            self.abs_position, self.prev_pos = [0.0] * V, [0.0] * V
+        for i in range(V):
+            this = self.pos[i]
+            change = 0.0 if first else this - self.prev_pos[i]
+            self.abs_position[i] = ((this if first else self.abs_position[i]) + change) % self.circ
+            self.prev_pos[i] = this
 
     def set_state(self, pos=None, vel=None, lane=None):
         if pos is not None:
@@ -264,6 +298,9 @@ class RingSim:
         clipped = None
         lc_env = self.env_kind in (ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO)
         directions = None
+        # _apply_rl_actions hands action r to the r-th RL vehicle of sorted_ids
+        # (accel.py:100-106, lane_change_accel.py:138-154)
+        rl_order = [i for i in self.sorted_idx() if i in self.rl_idx]
         if rl_actions is not None:
             if lc_env:
                 # LaneChangeAccelEnv._apply_rl_actions (lane_change_accel.py:132-154):
@@ -272,7 +309,7 @@ class RingSim:
                             for a in rl_actions[0::2]]
                 directions = [min(max(float(d), -1.0), 1.0) for d in rl_actions[1::2]]
                 clipped = acc_part
-                for q, i in enumerate(self.rl_idx):
+                for q, i in enumerate(rl_order):
                     last = self.headway[i] if self.lc_bug_compat else self.last_lc[i]
                     if self.time_counter <= self.lane_change_duration + last:
                         directions[q] = 0.0
@@ -286,7 +323,7 @@ class RingSim:
         for i in range(V):
             vt = self.types[self.type_of[i]]
             if vt.controller == C.RL and clipped is not None:
-                a = clipped[self.rl_idx.index(i)]
+                a = clipped[rl_order.index(i)]
             else:
                 z = self.noise_fn(self.step_index, i) \
                     if (self.noise_fn and vt.noise > 0) else 0.0
@@ -300,7 +337,7 @@ class RingSim:
         # its new leader or new follower in the target lane (pre-move positions)
         if directions is not None:
             new_lane = list(self.lane)
-            for q, i in enumerate(self.rl_idx):
+            for q, i in enumerate(rl_order):
                 d = int(directions[q])
                 if d == 0:
                     continue
@@ -320,6 +357,7 @@ class RingSim:
                     new_lane[i] = target
                     self.last_lc[i] = self.time_counter
             self.lane = new_lane
+        self.additional_command()      # base.py:365, before simulation_step
         # simulator move (restated SUMO Euler step)
         for i in range(V):
             self.vel[i] = next_vel[i]
@@ -340,8 +378,13 @@ class RingSim:
     # -- observations / rewards -------------------------------------------
     def get_state(self):
         k = self.env_kind
-        if k in (ENV_ACCEL, ENV_WAVE_ATTENUATION):
-            # accel.py:116-123 / wave_attenuation.py:141-148
+        if k == ENV_ACCEL:
+            # accel.py:116-123, rows in sorted_ids order
+            order = self.sorted_idx()
+            return np.array([self.vel[i] / self.speed_limit for i in order] +
+                            [self.pos[i] / self.circ for i in order])
+        if k == ENV_WAVE_ATTENUATION:
+            # wave_attenuation.py:141-148 (get_ids order)
             return np.array([v / self.speed_limit for v in self.vel] +
                             [x / self.circ for x in self.pos])
         if k == ENV_WAVE_ATTENUATION_PO:
@@ -364,9 +407,10 @@ class RingSim:
             return np.array(out)
         if k == ENV_LANE_CHANGE_ACCEL:
             # lane_change_accel.py:114-130
-            return np.array([v / self.speed_limit for v in self.vel] +
-                            [x / self.circ for x in self.pos] +
-                            [ln / self.n_lanes for ln in self.lane])
+            order = self.sorted_idx()
+            return np.array([self.vel[i] / self.speed_limit for i in order] +
+                            [self.pos[i] / self.circ for i in order] +
+                            [self.lane[i] / self.n_lanes for i in order])
         if k == ENV_LANE_CHANGE_ACCEL_PO:
             # LaneChangeAccelPOEnv.get_state (lane_change_accel.py:215-263) as it
             # behaves: the `return` sits inside the loop over RL vehicles, so only
@@ -411,6 +455,8 @@ class RingSim:
     def compute_reward(self, rl_actions, fail):
         k = self.env_kind
         if k == ENV_ACCEL:
+            if self.evaluate:     # accel.py:111-112
+                return float(np.mean(self.vel))
             return self.desired_velocity(fail)
         if k in (ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO):
             # lane_change_accel.py:100-112 (penalty compares get_last_lc, i.e.

@@ -21,7 +21,8 @@ import os
 
 import numpy as np
 
-from .ref_harness import RefRing, RefRingLC, ref_ctrl, ref_start_positions, ref_rewards
+from .ref_harness import RefRing, RefRingLC, RefRingSorted, RefRingLCSorted, ref_ctrl, \
+    ref_start_positions, ref_rewards
 from . import ref_shim
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -287,6 +288,65 @@ def ring_c3_po():
     np.savez_compressed(os.path.join(HERE, 'ring_c3_po.npz'), **out)
 
 
+def ring_sorted():
+    """additional_params['sort_vehicles'] = True and env_params.evaluate = True.
+    Part 1 (AccelEnv, 120 m, 10 IDM + 2 RL apart from each other): the reference's
+    sorted_ids / additional_command / _apply_rl_actions over two episodes - the first
+    reset observes in id order (no keys yet), the second with the keys the first episode
+    left behind. Part 2 (LaneChangeAccelEnv, 3 lanes, 9 IDM + 3 RL): keys frozen at the
+    reset positions, ties between side-by-side vehicles. Part 3: c1 with evaluate."""
+    out = {}
+    groups = [('ha', IDM, {}, {}, 5), ('rla', 'rl', {}, {}, 1), ('hb', IDM, {}, {}, 4),
+              ('rlb', 'rl', {}, {}, 1), ('hc', IDM, {}, {}, 1)]
+    ring = RefRingSorted(groups, 120, env_additional={'max_accel': 3, 'max_decel': 3,
+                                                       'target_velocity': 10})
+    rng = np.random.default_rng(4)
+    for ep, (warm, steps) in enumerate(((30, 400), (10, 80))):
+        if ep:
+            ring.reset(120)
+        P, Vv, O, R, A = [list(ring.pos)], [list(ring.vel)], [np.asarray(ring.get_state())], [], []
+        for s in range(warm + steps):
+            if s == warm:
+                ring.finish_reset()
+            if s < warm:
+                act = None
+            else:   # noisy gap-keeping rule so that nobody rams its leader; slot order = sorted order
+                act = []
+                for vid in [v for v in ring.sorted_ids if v in ring.k.vehicle.get_rl_ids()]:
+                    i = ring.index[vid]
+                    act.append(float(np.clip(0.3 * (ring.headway[i] - 4 - 1.2 * ring.vel[i])
+                                             + rng.normal(0, 0.4), -3.5, 3.5)))
+            obs, rew, crash = ring.step(act)
+            assert not crash
+            A.append([np.nan, np.nan] if act is None else act)
+            P.append(list(ring.pos)); Vv.append(list(ring.vel))
+            O.append(np.asarray(obs)); R.append(float(rew))
+        out.update({'pos_%d' % ep: np.array(P), 'vel_%d' % ep: np.array(Vv), 'obs_%d' % ep: np.array(O),
+                    'reward_%d' % ep: np.array(R), 'actions_%d' % ep: np.array(A), 'warm_%d' % ep: warm})
+    lc = RefRingLCSorted([('human', IDM, {}, {}, 9), ('rl', 'rl', {}, {}, 3)], 230, lanes=3,
+                         init_kw=dict(lanes_distribution=float('inf'), x0=200.0),
+                         env_additional={'max_accel': 3, 'max_decel': 3, 'target_velocity': 10})
+    P, Ln, O, R, A = [list(lc.pos)], [list(lc.lane)], [], [], []
+    for s in range(170):
+        if s == 20:
+            lc.finish_reset()
+        a = []
+        for q in range(3):
+            a += [float(rng.uniform(-0.8, 0.8)), float(rng.integers(-1, 2))]
+        act = None if s < 20 else a
+        obs, rew, crash = lc.step(act)
+        assert not crash
+        A.append([np.nan] * 6 if act is None else a)
+        P.append(list(lc.pos)); Ln.append(list(lc.lane)); O.append(np.asarray(obs)); R.append(float(rew))
+    out.update(lc_pos=np.array(P), lc_lane=np.array(Ln, dtype=np.int8), lc_obs=np.array(O),
+               lc_reward=np.array(R), lc_actions=np.array(A))
+    ev = RefRing([('idm', IDM, {}, {}, 22)], 230, init_kw=dict(bunching=20),
+                 env_additional={'max_accel': 3, 'max_decel': 3, 'target_velocity': 10})
+    ev.env_params.evaluate = True
+    out['eval_reward'] = np.array([ev.step(None)[1] for _ in range(120)])
+    np.savez_compressed(os.path.join(HERE, 'ring_sorted.npz'), **out)
+
+
 def start_pos():
     cases = [dict(length=230, n=22, lanes=1, kw=dict(bunching=20)),
              dict(length=230, n=22, lanes=1, kw=dict()),
@@ -318,7 +378,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_zoo(); ring_ma(); start_pos()
+    ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); start_pos()
     sumo_fixture()
     print('golden vectors written to', HERE)
 

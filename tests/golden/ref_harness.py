@@ -255,11 +255,11 @@ class RefRing:
             space_lo = -abs(self.env_params.additional_params.get('max_decel', 1e9))
             space_hi = self.env_params.additional_params.get('max_accel', 1e9)
             clipped = np.clip(rl_actions, a_min=space_lo, a_max=space_hi)
-            for q, i in enumerate(self.rl_idx):
-                acc[i] = float(clipped[q])
+            self._assign_rl(acc, clipped)
         else:
             for i in self.rl_idx:
                 acc[i] = self.sim_ctrl[i].get_accel(self)
+        self._before_move()
         # reference apply_acceleration (vehicle/traci.py:952-963), unbound
         stub = type('V', (), {})()
         stub.sim_step = self.dt
@@ -279,6 +279,13 @@ class RefRing:
         acts = rl_actions
         reward = self.compute_reward(acts, crash)
         return obs, reward, crash
+
+    def _assign_rl(self, acc, clipped):
+        for q, i in enumerate(self.rl_idx):
+            acc[i] = float(clipped[q])
+
+    def _before_move(self):      # Env.additional_command, base.py:365
+        pass
 
     def get_state(self):
         if self.env_kind == 'ma_wave_po':
@@ -305,6 +312,45 @@ class RefRing:
         if self.env_kind in ('wave', 'wave_po'):
             return WaveAttenuationEnv.compute_reward(self, rl_actions, fail=fail)
         return AccelEnv.compute_reward(self, rl_actions, fail=fail)
+
+
+class _SortedMixin:
+    """additional_params['sort_vehicles'] = True with the reference's own
+    AccelEnv.sorted_ids / _get_abs_position / additional_command / _apply_rl_actions;
+    `finish_reset` is AccelEnv.reset's tail (accel.py:178-181), to be called where the
+    reference's reset would return (after the warm-up steps)."""
+    sorted_ids = AccelEnv.sorted_ids
+    _get_abs_position = AccelEnv._get_abs_position
+
+    def _init_keys(self):
+        self.absolute_position = dict()      # accel.py:77-78: made once, survive resets
+        self.prev_pos = dict()
+
+    def finish_reset(self):
+        for vid in self.k.vehicle.get_ids():
+            self.absolute_position[vid] = self.k.vehicle.get_x_by_id(vid)
+            self.prev_pos[vid] = self.k.vehicle.get_x_by_id(vid)
+
+
+class RefRingSorted(_SortedMixin, RefRing):
+    def __init__(self, *a, **kw):
+        self._init_keys()
+        add = dict(kw.pop('env_additional', None) or {})
+        add['sort_vehicles'] = True
+        super().__init__(*a, env_additional=add, **kw)
+
+    def _assign_rl(self, acc, clipped):
+        got = {}
+        self.k.vehicle.apply_acceleration = lambda ids, a: got.update(zip(ids, a))
+        AccelEnv._apply_rl_actions(self, clipped)
+        for vid, a in got.items():
+            acc[self.index[vid]] = float(a)
+
+    def _before_move(self):
+        AccelEnv.additional_command(self)
+
+    def get_state(self):
+        return AccelEnv.get_state(self)
 
 
 class RefRingLC(RefRing):
@@ -377,7 +423,8 @@ class RefRingLC(RefRing):
         veh.apply_lane_change = lambda ids, direction: TraCIVehicle.apply_lane_change(
             tv, ids, direction)
         veh.get_last_lc = lambda vid, error=-1001: TraCIVehicle.get_last_lc(tv, vid, error)
-        self.sorted_ids = self.ids
+        if not isinstance(getattr(type(self), 'sorted_ids', None), property):
+            self.sorted_ids = self.ids
         if self.env_kind == 'lc_po':
             for name in ('get_lane_headways', 'get_lane_tailways', 'get_lane_leaders',
                          'get_lane_followers'):
@@ -438,3 +485,15 @@ class RefRingLC(RefRing):
         obs = self.LC.get_state(self)
         reward = self.LC.compute_reward(self, rl_actions, fail=crash)
         return obs, reward, crash
+
+
+class RefRingLCSorted(_SortedMixin, RefRingLC):
+    """LaneChangeAccelEnv with sort_vehicles: its get_state / _apply_rl_actions read
+    sorted_ids, its additional_command (lane_change_accel.py:156-161) keeps no
+    bookkeeping, so the keys are the positions AccelEnv.reset stored."""
+
+    def __init__(self, *a, **kw):
+        self._init_keys()
+        add = dict(kw.pop('env_additional', None) or {})
+        add['sort_vehicles'] = True
+        super().__init__(*a, env_additional=add, **kw)

@@ -184,6 +184,19 @@ def test_lane_change_po_env_compiles():
     assert spec.types[1].lc_controller == EN.LC_RL
 
 
+def test_evaluate_and_sort_vehicles_compile_to_env_flags():
+    fp = c1_flow_params()
+    fp['env'].evaluate = True
+    fp['env'].additional_params['sort_vehicles'] = True
+    kw = spec_of(fp).kw
+    assert kw['evaluate'] == 1 and kw['sort_vehicles'] == 1
+    fp = ring_flow_params()                      # WaveAttenuationPOEnv reads neither
+    fp['env'].evaluate = True
+    fp['env'].additional_params['sort_vehicles'] = True
+    kw = spec_of(fp).kw
+    assert kw['evaluate'] == 0 and kw['sort_vehicles'] == 0
+
+
 def test_highway_inflow_compiles():
     v = F.VehicleParams()
     v.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=10)

@@ -235,6 +235,75 @@ def test_c3_lane_change_po_observation(tag):
         assert np.abs(z['obs_b'][:, :6] - (230.4 - 5)).min() < 1e-9   # own leader, one lap away
 
 
+SORT_GROUPS = [('IDM', 5), ('RL', 1), ('IDM', 4), ('RL', 1), ('IDM', 1)]
+
+
+def test_sort_vehicles_two_episodes_bit_exact():
+    """additional_params['sort_vehicles'] with the reference's own sorted_ids /
+    additional_command / _apply_rl_actions (tests/golden/ring_sorted.npz): observation rows
+    and the RL action slots follow the absolute-position keys; the keys survive a reset."""
+    z = np.load(os.path.join(G, 'ring_sorted.npz'))
+    o = None
+    swaps = 0
+    for ep in (0, 1):
+        warm = int(z['warm_%d' % ep])
+        kw = dict(env_kind=OS.ENV_ACCEL, act_lo=-3, act_hi=3, sort_vehicles=True, warmup_steps=warm)
+        if o is None:
+            o = S.make_oracle([S.vt(c, n) for c, n in SORT_GROUPS], 120, **kw)
+            # the constructor ran reset + warm-up; redo it stepwise to see every observation
+            o.abs_position = o.prev_pos = None
+        obs = o.reset(120, run_warmup=False)
+        # reset(run_warmup=False) already stored the keys; the reference does that after warm-up
+        assert np.array_equal(np.array(o.pos), z['pos_%d' % ep][0])
+        acts = z['actions_%d' % ep]
+        if ep == 0:
+            o.abs_position = o.prev_pos = None
+            assert np.array_equal(o.get_state(), z['obs_0'][0])          # id order: no keys yet
+        else:
+            o.abs_position, o.prev_pos = stale
+            assert np.array_equal(o.get_state(), z['obs_1'][0])          # keys of episode 0
+        for s, a in enumerate(acts):
+            if s == warm:
+                o.abs_position, o.prev_pos = list(o.pos), list(o.pos)      # accel.py:178-181
+            obs, r, done = o.step(None if np.isnan(a).any() else list(a))
+            assert np.array_equal(np.array(o.pos), z['pos_%d' % ep][s + 1]), (ep, s)
+            assert np.array_equal(obs, z['obs_%d' % ep][s + 1]), (ep, s)
+            assert r == z['reward_%d' % ep][s], (ep, s)
+            order = o.sorted_idx()
+            swaps += order.index(10) < order.index(5)
+        stale = (list(o.abs_position), list(o.prev_pos))
+    assert swaps > 20           # the two RL vehicles did trade action slots
+    # the packaged reset (warm-up inside) ends where the stepwise one did
+    o2 = S.make_oracle([S.vt(c, n) for c, n in SORT_GROUPS], 120, env_kind=OS.ENV_ACCEL, act_lo=-3,
+                       act_hi=3, sort_vehicles=True, warmup_steps=30)
+    w = 30
+    assert np.array_equal(o2.reset(120), z['obs_0'][w])
+    assert o2.abs_position == list(z['pos_0'][w])
+
+
+def test_sort_vehicles_lane_change_env_bit_exact():
+    z = np.load(os.path.join(G, 'ring_sorted.npz'))
+    o = S.make_oracle([S.vt('IDM', 9), S.vt('RL', 3)], 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL,
+                      n_lanes=3, act_lo=-3, act_hi=3, x0=200.0, sort_vehicles=True)
+    o.abs_position = o.prev_pos = None
+    assert np.array_equal(np.array(o.pos), z['lc_pos'][0])
+    for s, a in enumerate(z['lc_actions']):
+        if s == 20:
+            o.abs_position, o.prev_pos = list(o.pos), list(o.pos)
+        obs, r, done = o.step(None if np.isnan(a).any() else list(a))
+        assert np.array_equal(np.array(o.pos), z['lc_pos'][s + 1]), s
+        assert o.lane == list(z['lc_lane'][s + 1]), s
+        assert np.array_equal(obs, z['lc_obs'][s]) and r == z['lc_reward'][s], s
+    assert o.sorted_idx() != list(range(12))
+
+
+def test_evaluate_reward_is_mean_speed():
+    z = np.load(os.path.join(G, 'ring_sorted.npz'))
+    o = S.make_oracle(S.c1_groups(), 230, bunching=20.0, evaluate=True)
+    r = [o.step(None)[1] for _ in range(120)]
+    assert np.abs(np.array(r) - z['eval_reward']).max() <= 1e-15 * 30
+
+
 def test_lane_change_direction_validation():
     o = S.make_oracle(c3_groups(), 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL, n_lanes=3,
                       act_lo=-3, act_hi=3)
