@@ -47,7 +47,7 @@ def parse():
     ap.add_argument('--steps', type=int, default=3000)
     ap.add_argument('--warmup', type=int, default=300)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma'])
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4'])
     ap.add_argument('--fuse', type=int, default=100, help='steps per fused launch')
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     ap.add_argument('--noise', type=float, default=0.2,
@@ -260,7 +260,11 @@ def run_b200(a):
     td = torch.float32 if a.dtype == 'f32' else torch.float64
     ts = 4 if a.dtype == 'f32' else 8
     gen = torch.Generator(device='cuda'); gen.manual_seed(4321 + rank)
-    act = torch.rand(K, env.act_dim, E, device='cuda', dtype=td, generator=gen) * 2 - 1
+    act = torch.rand(K, max(env.act_dim, 1), E, device='cuda', dtype=td, generator=gen) * 2 - 1
+    if a.workload == 'c3':
+        # rows [accel, direction] per RL vehicle: gentle accelerations, directions in {-1, 0, 1}
+        act[:, 0::2] *= 0.5
+        act[:, 1::2] = torch.round(act[:, 1::2] * 1.49)
     if a.workload == 'ma':
         # agents that ignore their leaders in stop-and-go traffic ram them within ~100 steps
         # (zero or zero-mean accelerations: > 90 % of the rings); braking-biased random
@@ -369,7 +373,9 @@ def run_b200(a):
     launch_ms = fused['ms'] / max(n_launch, 1)
     # per-GPU algorithmic bytes of one fused launch / its duration
     # SURVEY 8d per env-step: state round trip 16 B x V + ring length 4 + actions + obs + reward 4 + done 1 (f32)
-    bpe = (N_VEH * 16 + 4 + 4 * env.act_dim + 4 * env.obs_dim + 4) * (ts / 4) + 1
+    nv = eng.n_veh            # vehicles (ring) or slots (highway) whose state makes the round trip
+    extra = {'c3': 2, 'c4': 2}.get(a.workload, 0)    # + lane / slot-type byte read and written
+    bpe = (nv * 16 + 4 + 4 * env.act_dim + 4 * env.obs_dim + 4) * (ts / 4) + 1 + nv * extra
     alg_bytes = bpe * (fused['env_steps'] / world) / max(n_launch, 1)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
@@ -388,7 +394,7 @@ def run_b200(a):
         'data': 'synthetic',
         'env_steps_per_s': fused['env_steps'] / (fused['ms'] * 1e-3),
         'config': {'workload': '%s: %s' % (a.workload, wl['name']), 'envs_per_gpu': E,
-                   'vehicles_per_env': N_VEH, 'fuse': F, 'idm_noise': a.noise, 'parallelism': 'envs sharded, %d GPU(s), '
+                   'vehicles_per_env': nv, 'fuse': F, 'idm_noise': a.noise, 'parallelism': 'envs sharded, %d GPU(s), '
                    'no data-path collective' % world,
                    'l2': 'streamed actions/obs/reward/done %.0f MB per pass > 126 MB L2 is %s; '
                          'vehicle state is register-resident inside a fused launch'
@@ -416,7 +422,8 @@ def run_b200(a):
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
                      'kernel': '%s<%s> (flow_b200/csrc/), %d fused steps per launch, threads/env = %s'
-                               % ('ring1_fast_kernel' if a.workload == 'ma' else 'ring1_hot_kernel', a.dtype, F,
+                               % ({'ma': 'ring1_fast_kernel', 'c3': 'ring_ml_kernel', 'c4': 'highway_kernel'}.get(
+                                   a.workload, 'ring1_hot_kernel'), a.dtype, F,
                                   os.environ.get('FS_RING_SHAPE', 'auto')),
                      'launch_ms': launch_ms,
                      'note': 'achieved = ALGORITHMIC bytes (SURVEY 8d: %d B per env-step = state round '
@@ -433,7 +440,7 @@ def run_b200(a):
             'bound': 'hbm', 'unit': 'GB/s', 'peak': peak, 'bytes_per_launch': b,
             'achieved': b / (launch_ms * 1e-3) / 1e9, 'frac': b / (launch_ms * 1e-3) / 1e9 / peak})(
                 (fused['env_steps'] / world / max(n_launch, 1)) * (env.act_dim * ts + env.obs_dim * ts + ts + 1)
-                + E * (2 * N_VEH * 2 * ts + ts)),
+                + E * (2 * nv * 2 * ts + ts)),
         'issue': {'unit': 'warp-instructions per vehicle-step (static SASS count of the step loop, '
                           'scripts/sass_loops.py)', 'c5_shape1': 46.9, 'c2_shape8': 89.0,
                   'note': 'B200: 148 SMs x 4 schedulers x 1 warp-instruction/cycle x 1.965 GHz'},

@@ -36,7 +36,35 @@ def ring_ma(noise=0.0):
     return types, [0] + [1] * 10 + [0] + [1] * 10, kw
 
 
+def ring_c3(noise=0.0):
+    """LaneChangeAccelEnv on a 3-lane 230 m ring, 66 vehicles 3-abreast
+    (63 IDM that keep their lane + 3 RL that change lane), actions [accel, direction] per RL."""
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise),
+             EN.make_vtype(EN.CTRL_RL, lc_controller=EN.LC_RL)]
+    kw = dict(env_kind=EN.ENV_LANE_CHANGE_ACCEL, n_lanes=3, length_lo=230.0, length_hi=230.0,
+              target_velocity=10.0, horizon=3000, warmup_steps=0, act_lo=-3.0, act_hi=3.0,
+              lane_change_duration=5)
+    return types, [0] * 63 + [1] * 3, kw
+
+
+def highway_c4(noise=0.0):
+    """single-lane 1 km HighwayNetwork, IDM vehicles, inflow 2000 veh/h at
+    20 m/s, 160 vehicle slots per env, departures / arrivals compacted every step."""
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise)]
+    kw = dict(topology=EN.TOPO_HIGHWAY, env_kind=EN.ENV_HIGHWAY, length_lo=1000.0, length_hi=1000.0,
+              junction_len=0.0, target_velocity=10.0, horizon=3000, warmup_steps=0,
+              inflow_vehs_per_hour=2000.0, inflow_depart_speed=20.0, inflow_type=0,
+              capacity=160)
+    return types, [0] * 20, kw
+
+
 WORKLOADS = {
+    'c3': dict(builder=ring_c3, n_envs=2048, n_veh=66,
+               name='LaneChangeAccelEnv 3-lane ring, 63 IDM + 3 RL lane changers, 2048 envs/GPU, '
+                    'random accelerations and directions'),
+    'c4': dict(builder=highway_c4, n_envs=1024, n_veh=160,
+               name='open 1 km highway, inflow 2000 veh/h, 20 initial IDM vehicles, 160 slots, '
+                    '1024 envs/GPU'),
     'c2': dict(builder=ring_c2, n_envs=4096, n_veh=22,
                name='WaveAttenuationPOEnv ring 21 IDM + 1 RL, 4096 envs/GPU, random RL actions'),
     'ma': dict(builder=ring_ma, n_envs=4096, n_veh=22,

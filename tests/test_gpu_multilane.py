@@ -207,3 +207,15 @@ def test_lane_change_po_fp32_and_batch():
     o1 = torch.empty(K, 1, 13, device='cuda', dtype=torch.float64)
     solo.step(act[:, :, 17:18].contiguous(), k=K, obs_seq=o1)
     assert torch.equal(o1[:, 0], o64[:, 17])
+
+
+def test_multilane_known_answers_of_the_reference_test():
+    """TestMultiLaneData.test_no_junctions_ring (tests/fast_tests/test_vehicles.py:205-253)
+    through the CUDA observation: headways [27.857142857142858, -5, -5], tailways 28.577143."""
+    eng = S.make_engine([S.vt('RL', 21)], 2, 'f64', length=230, env_kind=OS.ENV_LANE_CHANGE_ACCEL_PO,
+                        n_lanes=3, junction_len=0.18, lanes_distribution=float('inf'))
+    obs = eng.reset().cpu().numpy()[1]
+    assert obs.shape == (4 * 21 * 3 + 1,)
+    np.testing.assert_allclose(obs[0:3], [27.85714285714286, -5, -5], rtol=1e-13)
+    np.testing.assert_array_almost_equal(obs[3:6], [28.577143] * 3)
+    assert (obs[6:] == 0).all()                     # everyone at rest, other blocks untouched

@@ -304,6 +304,21 @@ def test_evaluate_reward_is_mean_speed():
     assert np.abs(np.array(r) - z['eval_reward']).max() <= 1e-15 * 30
 
 
+def test_multilane_known_answers_of_the_reference_test():
+    """tests/fast_tests/test_vehicles.py:205-253 (TestMultiLaneData.test_no_junctions_ring):
+    3-lane 230 m ring, 21 vehicles 3-abreast; for test_0: lane leaders [test_3, test_1, test_2],
+    headways [27.857142857142858, -5, -5], followers [test_18, test_19, test_20], tailways
+    28.577143. The tailway = 27.857143 + 0.72 mixes the three 0.1 m junction offsets of
+    RingNetwork.specify_edge_starts in front of edge "left" with the 0.42 m netconvert gave
+    the junction the walk crosses; a closed loop of 230.72 m (junction 0.18) is the same sum."""
+    o = S.make_oracle([S.vt('RL', 21)], 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL_PO, n_lanes=3,
+                      junction=0.18, lanes_distribution=float('inf'))
+    nb = o.lane_neighbours(0)
+    assert [t[2] for t in nb] == [3, 1, 2] and [t[3] for t in nb] == [18, 19, 20]
+    assert [t[0] for t in nb] == [27.85714285714286, -5, -5]
+    np.testing.assert_array_almost_equal([t[1] for t in nb], [28.577143] * 3)
+
+
 def test_lane_change_direction_validation():
     o = S.make_oracle(c3_groups(), 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL, n_lanes=3,
                       act_lo=-3, act_hi=3)
