@@ -263,7 +263,8 @@ def run_b200(a):
     act = torch.rand(K, max(env.act_dim, 1), E, device='cuda', dtype=td, generator=gen) * 2 - 1
     if a.workload == 'c3':
         # rows [accel, direction] per RL vehicle: gentle accelerations, directions in {-1, 0, 1}
-        act[:, 0::2] *= 0.5
+        # braking-biased like 'ma': an RL car with zero-mean accelerations rams its leader
+        act[:, 0::2] = act[:, 0::2] * 0.6 - 0.4
         act[:, 1::2] = torch.round(act[:, 1::2] * 1.49)
     if a.workload == 'ma':
         # agents that ignore their leaders in stop-and-go traffic ram them within ~100 steps

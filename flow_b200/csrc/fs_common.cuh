@@ -133,6 +133,35 @@ __device__ __forceinline__ T normal_sample(unsigned long long seed, long long en
   return (T)(::sqrt(-2.0 * ::log(u1)) * ::cos(6.283185307179586 * u2));
 }
 
+// Four standard normals from ONE Philox call (Box-Muller on both word pairs), all in T's
+// own precision: what the warp-per-env kernels use, one call per thread and step.
+template <typename T>
+__device__ __forceinline__ void normal4(unsigned long long seed, long long env_gid, int idx,
+                                        int step, T* z) {
+  uint32_t r[4];
+  Philox::gen((uint32_t)step, (uint32_t)idx, (uint32_t)env_gid, (uint32_t)(env_gid >> 32),
+              (uint32_t)seed, (uint32_t)(seed >> 32), r);
+  if (sizeof(T) == 4) {
+    const float k = 2.3283064365386963e-10f;  // 2^-32; u in (0, 1]
+    const float u0 = fminf(fmaf((float)r[0], k, k), 1.0f), u2 = fminf(fmaf((float)r[2], k, k), 1.0f);
+    const float ra = sqrtf(-1.3862943611198906f * __log2f(u0));   // sqrt(-2 ln u)
+    const float rb = sqrtf(-1.3862943611198906f * __log2f(u2));
+    float s0, c0, s1, c1;
+    const float k2pi = 1.4629180792671596e-09f;   // 2 pi 2^-32
+    __sincosf((float)r[1] * k2pi, &s0, &c0);
+    __sincosf((float)r[3] * k2pi, &s1, &c1);
+    z[0] = (T)(ra * c0); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1); z[3] = (T)(rb * s1);
+  } else {
+    const double k = 1.0 / 4294967296.0;
+    const double ra = ::sqrt(-2.0 * ::log(((double)r[0] + 1.0) * k));
+    const double rb = ::sqrt(-2.0 * ::log(((double)r[2] + 1.0) * k));
+    double s0, c0, s1, c1;
+    sincos(6.283185307179586 * ((double)r[1] * k), &s0, &c0);
+    sincos(6.283185307179586 * ((double)r[3] * k), &s1, &c1);
+    z[0] = (T)(ra * c0); z[1] = (T)(ra * s0); z[2] = (T)(rb * c1); z[3] = (T)(rb * s1);
+  }
+}
+
 // ------------------------------------------------------------ controller laws
 // IDM, flow/controllers/car_following_models.py:464-482
 template <typename T>

@@ -41,6 +41,11 @@ struct MlBufs {
   int lc_bug_compat;
 };
 
+template <typename T>
+__host__ __device__ inline size_t ml_smem_per_warp(int V) {
+  return (size_t)V * (5 * sizeof(T) + 3 * sizeof(int)) + 16 * sizeof(int);
+}
+
 template <typename T, int SLOTS>
 __global__ void __launch_bounds__(128)
 ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const StepArgs<T> A) {
@@ -51,14 +56,18 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   const int e = blockIdx.x * (blockDim.x >> 5) + wib;
   if (e >= E) return;
   if (A.mask != nullptr && A.mask[e] == 0) return;
-  // per-warp shared slice: xs[V] vs[V] hs[V] (T) | ls[V] ld[V] (int)
-  const size_t per_warp = (size_t)V * (3 * sizeof(T) + 2 * sizeof(int));
+  // per-warp shared slice: xs[V] vs[V] hs[V] cx[V] lens[V] (T) | ls[V] ld[V] cidx[V] loff[16] (int)
+  const size_t per_warp = ml_smem_per_warp<T>(V);
   unsigned char* mine = smem_raw + per_warp * wib;
   T* xs = reinterpret_cast<T*>(mine);
   T* vs = xs + V;
   T* hs = vs + V;
-  int* ls = reinterpret_cast<int*>(hs + V);
+  T* cx = hs + V;                  // positions grouped by lane (index order inside a lane)
+  T* lens = cx + V;                // vehicle lengths (static; one LDS instead of two indexed LDCs)
+  int* ls = reinterpret_cast<int*>(lens + V);
   int* ld = ls + V;
+  int* cidx = ld + V;              // vehicle index of every entry of cx
+  int* loff = cidx + V;            // lane l occupies entries [loff[l], loff[l+1])
 
   T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS];
   int ln[SLOTS], lead[SLOTS], foll[SLOTS];
@@ -69,6 +78,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   for (int s = 0; s < SLOTS; ++s) {
     const int i = lane_id + 32 * s;
     const bool ok = i < V;
+    if (ok) lens[i] = cfg.types[cfg.type_of[i]].length;
     x[s] = ok ? B.pos[eo + i] : T(0);
     v[s] = ok ? B.vel[eo + i] : T(0);
     ln[s] = ok ? (int)B.lane[eo + i] : -1;
@@ -84,22 +94,44 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
     }
     __syncwarp();
   };
-  // k.update: nearest same-lane vehicle ahead; ties -> lowest index (oracle order)
+  // k.update: nearest same-lane vehicle ahead; ties -> lowest index (oracle order).
+  // The warp first groups the vehicles by lane (ballot compaction, index order kept), so a
+  // vehicle scans the members of its own lane only: V/L entries instead of V, no lane test.
+  const unsigned lt_mask = (1u << lane_id) - 1u;
   auto update = [&](bool need_followers) {
     publish();
+    {
+      int base = 0;
+      for (int l = 0; l < L; ++l) {
+        if (lane_id == 0) loff[l] = base;
+#pragma unroll
+        for (int s = 0; s < SLOTS; ++s) {
+          const int i = lane_id + 32 * s;
+          const bool m = i < V && ln[s] == l;
+          const unsigned b = __ballot_sync(0xffffffffu, m);
+          if (m) { const int p = base + __popc(b & lt_mask); cidx[p] = i; cx[p] = x[s]; }
+          base += __popc(b);
+        }
+      }
+      if (lane_id == 0) loff[L] = base;
+      __syncwarp();
+    }
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {
       const int i = lane_id + 32 * s;
       T best = T(0); int bj = -1;
       if (i < V) {
-        for (int j = 0; j < V; ++j) {
-          if (j == i || ls[j] != ln[s]) continue;
-          const T d = fwd_dist(xs[j], x[s], C);
-          if (bj < 0 || d < best) { best = d; bj = j; }
+        const int p1 = loff[ln[s] + 1];
+        const T xi = x[s];
+#pragma unroll 4
+        for (int p = loff[ln[s]]; p < p1; ++p) {
+          const int j = cidx[p];
+          const T d = fwd_dist(cx[p], xi, C);
+          if (j != i && (bj < 0 || d < best)) { best = d; bj = j; }
         }
       }
       lead[s] = bj;
-      h[s] = (bj >= 0) ? best - cfg.types[cfg.type_of[bj]].length : T(1000);
+      h[s] = (bj >= 0) ? best - lens[bj] : T(1000);
     }
     if (need_followers) {  // vehicle/traci.py:243-250: closest vehicle that calls me leader
       __syncwarp();
@@ -113,9 +145,13 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       for (int s = 0; s < SLOTS; ++s) {
         const int i = lane_id + 32 * s;
         int f = -1; T fh = T(0);
-        if (i < V)
-          for (int j = 0; j < V; ++j)
+        if (i < V) {   // only a vehicle of my lane can call me leader
+          const int p1 = loff[ln[s] + 1];
+          for (int p = loff[ln[s]]; p < p1; ++p) {
+            const int j = cidx[p];
             if (ld[j] == i && (f < 0 || hs[j] < fh)) { f = j; fh = hs[j]; }
+          }
+        }
         foll[s] = f;
       }
     }
@@ -195,8 +231,8 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
           if (jf < 0 || b <= bb) { jf = j; bb = b; }         // ties: highest index
         }
         if (jl < 0 && ls[me] == lq) { jl = jf = me; bd = bb = C; }  // alone: itself, one lap away
-        T hw = jl >= 0 ? bd - cfg.types[cfg.type_of[jl]].length : T(1000);
-        T tw = jf >= 0 ? bb - cfg.types[cfg.type_of[me]].length : T(1000);
+        T hw = jl >= 0 ? bd - lens[jl] : T(1000);
+        T tw = jf >= 0 ? bb - lens[me] : T(1000);
         if (fixed) {
           hw = jl >= 0 ? N::div(hw, C) : T(1);
           tw = jf >= 0 ? N::div(tw, C) : T(1);
@@ -222,7 +258,28 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   };
   if (A.k_steps == 0) write_obs(nullptr, B.obs + (size_t)e * cfg.obs_dim);
 
+  // action rows of this thread's RL vehicles, fetched one step ahead of their use
+  T nxt_a[SLOTS], nxt_d[SLOTS];
+  auto fetch_actions = [&](int k) {
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+      const int i = lane_id + 32 * s;
+      nxt_a[s] = T(0); nxt_d[s] = T(0);
+      if (have_act && i < V && cfg.rl_index[i] >= 0) {
+        const int slot = cfg.rl_index[i];
+        const size_t arow = (size_t)k * cfg.act_dim + (lc_env ? 2 * slot : slot);
+        nxt_a[s] = A.actions[arow * E + e];
+        if (lc_env) nxt_d[s] = A.actions[(arow + 1) * E + e];
+      }
+    }
+  };
+  if (A.k_steps > 0) fetch_actions(0);
+
   for (int k = 0; k < A.k_steps; ++k) {
+    T act_a[SLOTS], act_d[SLOTS];
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) { act_a[s] = nxt_a[s]; act_d[s] = nxt_d[s]; }
+    if (k + 1 < A.k_steps) fetch_actions(k + 1);
     if (!done) {
       T mean_v = T(0);
       if (cfg.any_follower & 2) {
@@ -235,9 +292,54 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       int new_ln[SLOTS];
       T act_abs_sum = T(0);
 #pragma unroll
+      for (int s = 0; s < SLOTS; ++s) new_ln[s] = ln[s];
+      if (lc_env && have_act) {
+        // LaneChangeAccelEnv._apply_rl_actions + apply_lane_change + the restated execution.
+        // Requests are checked by the WHOLE warp, one requesting vehicle at a time: every
+        // thread tests its share of the target lane's members (pre-move lane lists).
+#pragma unroll
+        for (int s = 0; s < SLOTS; ++s) {
+          const int i = lane_id + 32 * s;
+          int target = -1;
+          T len_i = T(0);
+          if (i < V && cfg.rl_index[i] >= 0) {
+            // direction zeroed while time_counter <= lane_change_duration + get_last_lc
+            // (== headway under the reference bug)
+            T dirf = N::min(N::max(act_d[s], T(-1)), T(1));
+            const T last = B.lc_bug_compat ? h[s] : T(last_lc[s]);
+            if (T(tc + 1) <= add(T(cfg.lane_change_duration), last)) dirf = T(0);
+            const int dir = dirf > T(0.5) ? 1 : (dirf < T(-0.5) ? -1 : 0);
+            int t = ln[s] + dir;
+            t = t < 0 ? 0 : (t > L - 1 ? L - 1 : t);
+            if (t != ln[s]) target = t;
+            len_i = lens[i];
+          }
+          unsigned req = __ballot_sync(0xffffffffu, target >= 0);
+          while (req) {
+            const int src = __ffs(req) - 1;
+            req &= req - 1;
+            const int t = __shfl_sync(0xffffffffu, target, src);
+            const T xi = __shfl_sync(0xffffffffu, x[s], src);
+            const T li = __shfl_sync(0xffffffffu, len_i, src);
+            const int p1 = loff[t + 1];
+            bool bad = false;   // no overlap with any vehicle of the target lane
+            for (int p = loff[t] + lane_id; p < p1; p += 32) {
+              const T fwd = fwd_dist(cx[p], xi, C), back = fwd_dist(xi, cx[p], C);
+              bad |= fwd - lens[cidx[p]] < T(0) || back - li < T(0);
+            }
+            const bool ok = !__any_sync(0xffffffffu, bad);
+            if (lane_id == src && ok) { new_ln[s] = t; last_lc[s] = tc + 1; }
+          }
+        }
+      }
+      T zn[SLOTS > 4 ? 8 : 4];
+      if (cfg.any_noise) {   // one Philox call = four normals = the thread's first four slots
+        normal4<T>(cfg.seed, gid, lane_id, tc + episode * 1000003, zn);
+        if (SLOTS > 4) normal4<T>(cfg.seed, gid, lane_id + 32, tc + episode * 1000003, zn + 4);
+      }
+#pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
         const int i = lane_id + 32 * s;
-        new_ln[s] = ln[s];
         if (i >= V) continue;
         const TypeP<T>& tp = cfg.types[cfg.type_of[i]];
         const int ctrl = tp.ctrl;
@@ -246,31 +348,9 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
         const T vl = has_lead ? vs[lead[s]] : T(-1001);
         T a;
         if (ctrl == FS_CTRL_RL && have_act) {
-          const int slot = cfg.rl_index[i];
-          const size_t arow = (size_t)k * cfg.act_dim + (lc_env ? 2 * slot : slot);
-          const T raw = A.actions[arow * E + e];
+          const T raw = act_a[s];
           a = N::min(N::max(raw, cfg.act_lo), cfg.act_hi);
           act_abs_sum = add(act_abs_sum, N::abs(cfg.clip_actions ? a : raw));
-          if (lc_env) {
-            // _apply_rl_actions: direction zeroed while time_counter <=
-            // lane_change_duration + get_last_lc (== headway under the reference bug)
-            T dirf = N::min(N::max(A.actions[(arow + 1) * E + e], T(-1)), T(1));
-            const T last = B.lc_bug_compat ? hi : T(last_lc[s]);
-            if (T(tc + 1) <= add(T(cfg.lane_change_duration), last)) dirf = T(0);
-            const int dir = dirf > T(0.5) ? 1 : (dirf < T(-0.5) ? -1 : 0);
-            int target = ln[s] + dir;
-            target = target < 0 ? 0 : (target > L - 1 ? L - 1 : target);
-            if (target != ln[s]) {
-              bool ok = true;  // restated execution: no overlap in the target lane
-              for (int j = 0; j < V; ++j) {
-                if (j == i || ls[j] != target) continue;
-                const T fwd = fwd_dist(xs[j], x[s], C), back = fwd_dist(x[s], xs[j], C);
-                if (fwd - cfg.types[cfg.type_of[j]].length < T(0) || back - tp.length < T(0))
-                  ok = false;
-              }
-              if (ok) { new_ln[s] = target; last_lc[s] = tc + 1; }
-            }
-          }
         } else if (ctrl == FS_CTRL_PI_SATURATION) {
           T v_cmd = B.st0[(size_t)i * E + e];
           RingBufs<T> rb;
@@ -289,7 +369,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
         }
         if (ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL) {
           if (tp.noise > T(0))
-            a = add(a, mul(tp.noise, normal_sample<T>(cfg.seed, gid, i, tc + episode * 1000003)));
+            a = add(a, mul(tp.noise, zn[s]));
           if (tp.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
             a = failsafe_instantaneous<T>(a, vi, hi, has_lead, V, dt);
           else if (tp.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
