@@ -246,6 +246,7 @@ def run_b200(a):
     if world != a.gpus and world > 1:
         raise SystemExit('--gpus %d but WORLD_SIZE=%d' % (a.gpus, world))
     torch.cuda.set_device(local)
+    numa_cores = SH.bind_to_gpu_cpus(local) if world > 1 else 0
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 
@@ -401,6 +402,7 @@ def run_b200(a):
                          'vehicle state is register-resident inside a fused launch'
                          % ((act.numel() + obs_seq.numel() + rew_seq.numel()) * ts / 1e6 + done_seq.numel() / 1e6,
                             str((act.numel() + obs_seq.numel() + rew_seq.numel()) * ts + done_seq.numel() > 126e6)),
+                   'host_cores_bound_to_gpu_numa_node': numa_cores,
                    'counted': 'vehicle-steps actually advanced (engine counter); frozen (crashed) '
                               'envs are not counted'},
         'crashed_env_frac': fused['crashes'] / (E * world),

@@ -75,6 +75,7 @@ struct fs_engine {
   std::vector<void*> allocs;
   bool env_needs_rl() const {
     return cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO || cfg.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO ||
+           cfg.env_kind == FS_ENV_MA_ACCEL_PO ||
            cfg.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
   }
   // warp-per-env multi-lane kernel (also the only one with the per-lane neighbour observation)
@@ -128,6 +129,8 @@ static int obs_dim_for(const fs_config& c) {
       return c.topology == FS_TOPO_RING ? 4 * c.n_veh * c.n_lanes + c.n_veh : -1;
     case FS_ENV_HIGHWAY: return 2 * c.n_veh;
     case FS_ENV_MA_WAVE_ATTENUATION_PO: return 3 * c.n_veh;  // capacity; 3 * n_rl after fs_set_types
+    case FS_ENV_MA_ACCEL_PO:                                  // capacity; 6 * n_rl after fs_set_types
+      return c.topology == FS_TOPO_RING && c.n_lanes == 1 ? 6 * c.n_veh : -1;
     default: return -1;
   }
 }
@@ -280,6 +283,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
                       g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO;
   c.act_dim = lc_env ? 2 * n_rl : n_rl;
   if (g.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO) { e->obs_dim = 3 * n_rl; c.obs_dim = e->obs_dim; }
+  if (g.env_kind == FS_ENV_MA_ACCEL_PO) { e->obs_dim = 6 * n_rl; c.obs_dim = e->obs_dim; }
   // LaneChangeAccelPOEnv.get_state returns inside its loop over RL vehicles
   // (lane_change_accel.py:215-263): 4 * n_rl * lanes zeros-or-first-block + ONE ego speed
   // (with lc_corrected: every block and n_rl ego speeds, the declared observation_space)
@@ -311,7 +315,8 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     // and at most one RL type, equal lengths, delta = 4
     int ta = -1, tb = -1;
     bool ok = e->cfg.n_veh == 22 && !e->generic && e->cfg.topology == FS_TOPO_RING &&
-              e->cfg.n_lanes == 1 && !(e->cfg.env_flags & FS_ENVF_EVALUATE);
+              e->cfg.n_lanes == 1 && !(e->cfg.env_flags & FS_ENVF_EVALUATE) &&
+              e->cfg.env_kind != FS_ENV_MA_ACCEL_PO;   // follower view: generic kernel only
     for (int i = 0; ok && i < e->cfg.n_veh; ++i) {
       const int t = type_of_vehicle[i];
       const fs_vtype& s = types[t];

@@ -168,6 +168,7 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
   const bool have_act = A.actions != nullptr;
   const bool po = cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO;
   const bool ma = cfg.env_kind == FS_ENV_MA_WAVE_ATTENUATION_PO;
+  const bool mac = cfg.env_kind == FS_ENV_MA_ACCEL_PO;
 
   // WaveAttenuationPO: who holds the RL vehicle and its leader
   int rl_veh = 0;
@@ -209,6 +210,38 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
         const T o0 = N::div(v[j], T(15)), o1 = N::div(vl - v[j], T(15)), o2 = N::div(h[j], ml);
         if (o) { o[3 * r] = o0; o[3 * r + 1] = o1; o[3 * r + 2] = o2; }
         if (ol) { ol[3 * r] = o0; ol[3 * r + 1] = o1; ol[3 * r + 2] = o2; }
+      }
+    } else if (mac) {
+      // MultiAgentAccelPOEnv.get_state, multiagent/ring/accel.py:163-206: per RL vehicle
+      // (x/L, v/vmax, (v_lead - v)/vmax, (x_lead - x - own length)/L  [not wrapped, own
+      // length: as the reference computes it], (v - v_follow)/vmax, headway(follower)/L);
+      // nobody ahead / behind: speeds vmax / 0, distances L
+      const T v_nf = (G == 1) ? v[0] : shfl(v[0], lane_next, gmask);
+      const T x_nf = (G == 1) ? x[0] : shfl(x[0], lane_next, gmask);
+      const int lastj = n_mine > 0 ? n_mine - 1 : 0;
+      const T vlast = pick(v, lastj), hlast = pick(h, lastj);
+      const T v_pf = (G == 1) ? vlast : shfl(vlast, lane_prev, gmask);
+      const T h_pf = (G == 1) ? hlast : shfl(hlast, lane_prev, gmask);
+      FS_SLOTS(j) if (valid && j < n_mine && cfg.rl_index[base + j] >= 0) {
+        const int r = cfg.rl_index[base + j];
+        const bool in_next = !(j + 1 < VPT && j + 1 < n_mine);
+        const T vl = in_next ? v_nf : v[j + 1 < VPT ? j + 1 : 0];
+        const T xl = in_next ? x_nf : x[j + 1 < VPT ? j + 1 : 0];
+        const T vfo = j > 0 ? v[j > 0 ? j - 1 : 0] : v_pf;
+        const T hfo = j > 0 ? h[j > 0 ? j - 1 : 0] : h_pf;
+        const T len = cfg.types[cfg.type_of[base + j]].length;
+        T q[6];
+        q[0] = N::div(x[j], C);
+        q[1] = N::div(v[j], cfg.speed_limit);
+        q[2] = N::div((has_lead ? vl : cfg.speed_limit) - v[j], cfg.speed_limit);
+        q[3] = N::div(has_lead ? (xl - x[j]) - len : C, C);
+        q[4] = N::div(v[j] - (has_lead ? vfo : T(0)), cfg.speed_limit);
+        q[5] = N::div(has_lead ? hfo : C, C);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          if (o) o[6 * r + c] = q[c];
+          if (ol) ol[6 * r + c] = q[c];
+        }
       }
     } else if (valid) {
       // AccelEnv / WaveAttenuationEnv.get_state, accel.py:116-123
@@ -316,10 +349,11 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
       crash = cr;
       tc += 1;
       done = crash || tc >= t_end;
-      if (cfg.env_kind == FS_ENV_ACCEL) {
-        // AccelEnv.compute_reward (accel.py:109-114): mean speed when env_params.evaluate,
+      if (cfg.env_kind == FS_ENV_ACCEL || mac) {
+        // MultiAgentAccelPOEnv.compute_reward (multiagent/ring/accel.py:154-161): the same
+        // desired_velocity, shared by the agents. AccelEnv.compute_reward (accel.py:109-114): mean speed when env_params.evaluate,
         // else rewards.desired_velocity, flow/core/rewards.py:6-59
-        if (cfg.evaluate) reward = N::div(sv, T(V));
+        if (cfg.evaluate && !mac) reward = N::div(sv, T(V));
         else if (crash) reward = T(0);
         else {
           const T cost = N::sqrt(sq);

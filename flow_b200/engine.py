@@ -15,7 +15,7 @@ F32, F64 = 0, 1
 TOPO_RING, TOPO_HIGHWAY = 0, 1
 ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
     ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY, \
-    ENV_MA_WAVE_ATTENUATION_PO = range(7)
+    ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO = range(8)
 CTRL_SIM, CTRL_IDM, CTRL_OVM, CTRL_LINEAR_OVM, CTRL_BCM, CTRL_CFM, CTRL_LAC, \
     CTRL_GIPPS, CTRL_FOLLOWER_STOPPER, CTRL_NONLOCAL_FOLLOWER_STOPPER, \
     CTRL_PI_SATURATION, CTRL_RL = range(12)

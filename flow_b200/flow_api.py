@@ -1083,11 +1083,15 @@ class MultiAgentWaveAttenuationPOEnv(Env):
     def observation_space(self):
         return _box(low=-5, high=5, shape=(3,), dtype=np.float32)
 
+    OBS_PER_AGENT = 3
+    REWARD_WITHOUT_ACTIONS = 0     # compute_reward returns 0 (not a dict) when rl_actions is None
+
     def _split(self, obs):
+        w = self.OBS_PER_AGENT
         if self.n_envs == 1:
-            o = obs[0].double().cpu().numpy().reshape(len(self.rl_ids), 3)
+            o = obs[0].double().cpu().numpy().reshape(len(self.rl_ids), w)
             return {v: o[r] for r, v in enumerate(self.rl_ids)}
-        o = obs.view(self.n_envs, len(self.rl_ids), 3)
+        o = obs.view(self.n_envs, len(self.rl_ids), w)
         return {v: o[:, r] for r, v in enumerate(self.rl_ids)}
 
     def reset(self):
@@ -1109,8 +1113,10 @@ class MultiAgentWaveAttenuationPOEnv(Env):
         obs, rew, done, _ = super().step(a)
         o = self._split(self.state)
         if self.n_envs == 1:
-            # compute_reward returns 0 (not a dict) when rl_actions is None (:223-224)
-            r = {v: rew for v in self.rl_ids} if rl_actions else 0
+            # wave attenuation: compute_reward returns 0 (not a dict) when rl_actions is None
+            # (:223-224); accel: always the dict
+            r = {v: rew for v in self.rl_ids} \
+                if (rl_actions or self.REWARD_WITHOUT_ACTIONS is None) else 0
         else:
             r = {v: rew for v in self.rl_ids}
         d = {v: False if self.n_envs == 1 else done.new_zeros(done.shape) for v in self.rl_ids}
@@ -1118,9 +1124,28 @@ class MultiAgentWaveAttenuationPOEnv(Env):
         return o, r, d, {v: {} for v in self.rl_ids}
 
 
+class MultiAgentAccelPOEnv(MultiAgentWaveAttenuationPOEnv):
+    """flow/envs/multiagent/ring/accel.py:87-226 on a single-lane ring: every RL vehicle
+    observes (x/L, v/vmax, (v_lead - v)/vmax, (x_lead - x - own length)/L, (v - v_follow)/vmax,
+    headway(follower)/L) - the leader distance is NOT wrapped, as in the reference - and all
+    agents share rewards.desired_velocity. Same collision deviation as the class above."""
+    KIND = EN.ENV_MA_ACCEL_PO
+    ADDITIONAL = {'max_accel': 1, 'max_decel': 1, 'target_velocity': 20}
+    OBS_PER_AGENT = 6
+    REWARD_WITHOUT_ACTIONS = None
+
+    def __init__(self, env_params, sim_params, network, simulator='b200', **kw):
+        super().__init__(env_params, sim_params, network, simulator, **kw)
+        self.leader, self.follower = [], []
+
+    @property
+    def observation_space(self):
+        return _box(low=-5, high=5, shape=(6,), dtype=np.float32)
+
+
 _ENV_BY_NAME = {c.__name__: c for c in (AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv,
                                         LaneChangeAccelEnv, LaneChangeAccelPOEnv,
-                                        MultiAgentWaveAttenuationPOEnv)}
+                                        MultiAgentWaveAttenuationPOEnv, MultiAgentAccelPOEnv)}
 
 
 # =============================================================================

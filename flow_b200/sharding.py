@@ -19,6 +19,27 @@ def env_rank_world():
             int(os.environ.get('LOCAL_RANK', '0')))
 
 
+def bind_to_gpu_cpus(local_rank):
+    """Pin this process to the host cores NVML reports as closest to its GPU, BEFORE any
+    pinned staging buffer is allocated: first-touch then places the buffers on the GPU's own
+    NUMA node and eight ranks do not push their 45 GB/s of results across the socket link.
+    Returns the number of cores kept (0: NVML unavailable or nothing changed)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(local_rank))
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return 0
+
+
 def shard_envs(total_envs, rank, world):
     """Contiguous block of the global env range owned by `rank`:
     returns (env_id_base, n_local). Blocks differ by at most one env."""

@@ -102,6 +102,11 @@ extern "C" {
 #define FS_LC_STATIC 1  /* StaticLaneChanger: direction 0                      */
 #define FS_LC_RL 2      /* direction comes from the action vector              */
 
+#define FS_ENV_MA_ACCEL_PO 7 /* MultiAgentAccelPOEnv (flow/envs/multiagent/ring/accel.py:87-226), single-lane
+                                ring: obs [n_rl][6] per env = (x/L, v/vmax, (v_lead-v)/vmax,
+                                (x_lead - x - len)/L  -- NOT wrapped, like the reference --,
+                                (v-v_follow)/vmax, headway(follower)/L); shared desired_velocity reward */
+
 /* fs_config.env_flags */
 #define FS_ENVF_EVALUATE 1      /* EnvParams.evaluate: AccelEnv reward = mean speed
                                    (flow/envs/ring/accel.py:109-114)                    */

@@ -39,7 +39,7 @@ VEHICLE_LENGTH = 5.0  # flow/core/kernel/network/base.py:10
 
 ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
     ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY, \
-    ENV_MA_WAVE_ATTENUATION_PO = range(7)
+    ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO = range(8)
 
 F32_EPS = float(np.finfo(np.float32).eps)
 
@@ -405,6 +405,25 @@ class RingSim:
                 out += [self.vel[rl] / 15., (self.vel[lead] - self.vel[rl]) / 15.,
                         self.headway[rl] / max_length]
             return np.array(out)
+        if k == ENV_MA_ACCEL_PO:
+            # MultiAgentAccelPOEnv.get_state, multiagent/ring/accel.py:163-206: rows in
+            # get_rl_ids order; lead_head is x_lead - x_rl - length(rl), NOT wrapped
+            out = []
+            for rl in self.rl_idx:
+                lead, fol = self.leader[rl], self.follower[rl]
+                if lead < 0:
+                    lead_speed, lead_head = self.speed_limit, self.circ
+                else:
+                    lead_speed = self.vel[lead]
+                    lead_head = self.pos[lead] - self.pos[rl] - self.types[self.type_of[rl]].length
+                if fol < 0:
+                    follow_speed, follow_head = 0, self.circ
+                else:
+                    follow_speed, follow_head = self.vel[fol], self.headway[fol]
+                out += [self.pos[rl] / self.circ, self.vel[rl] / self.speed_limit,
+                        (lead_speed - self.vel[rl]) / self.speed_limit, lead_head / self.circ,
+                        (self.vel[rl] - follow_speed) / self.speed_limit, follow_head / self.circ]
+            return np.array(out)
         if k == ENV_LANE_CHANGE_ACCEL:
             # lane_change_accel.py:114-130
             order = self.sorted_idx()
@@ -454,6 +473,8 @@ class RingSim:
 
     def compute_reward(self, rl_actions, fail):
         k = self.env_kind
+        if k == ENV_MA_ACCEL_PO:    # multiagent/ring/accel.py:154-161, shared by the agents
+            return self.desired_velocity(fail)
         if k == ENV_ACCEL:
             if self.evaluate:     # accel.py:111-112
                 return float(np.mean(self.vel))

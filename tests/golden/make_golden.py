@@ -198,6 +198,36 @@ def ring_ma():
                         pos=np.array(P), vel=np.array(Vv), obs=np.array(O), reward=np.array(Rw))
 
 
+def ring_ma_accel():
+    """MultiAgentAccelPOEnv.get_state / compute_reward of the reference on a 180 m ring:
+    3 RL vehicles (first, middle and LAST index, so one leader sits across x = 0) among 13
+    IDM humans; actions from a noisy gap-keeping rule, some outside the [-1, 1] box."""
+    groups = [('rl_a', 'rl', {}, {}, 1), ('ha', IDM, {}, {}, 6), ('rl_b', 'rl', {}, {}, 1),
+              ('hb', IDM, {}, {}, 7), ('rl_c', 'rl', {}, {}, 1)]
+    ring = RefRing(groups, 180, 'ma_accel_po',
+                   env_additional={'max_accel': 1, 'max_decel': 1, 'target_velocity': 20})
+    rng = np.random.default_rng(8)
+    n_w, n_a = 50, 500
+    acts = np.full((n_w + n_a, 3), np.nan)
+    P, Vv, O, Rw = [list(ring.pos)], [list(ring.vel)], [np.asarray(ring.get_state(), float)], []
+    for s in range(n_w + n_a):
+        a = None
+        if s >= n_w:
+            a = np.array([0.3 * (ring.headway[i] - 5 - 2.5 * ring.vel[i])
+                          + 0.8 * (ring.vel[ring.leader[i]] - ring.vel[i]) for i in ring.rl_idx]) \
+                + rng.normal(0, 0.4, 3)
+            acts[s] = a
+        obs, rew, crash = ring.step(a)
+        assert not crash, s
+        P.append(list(ring.pos)); Vv.append(list(ring.vel)); O.append(np.asarray(obs, float))
+        Rw.append(float(rew))
+    assert (np.abs(acts[n_w:]) > 1).any()      # the Box clip is exercised
+    O = np.array(O)
+    assert (O[:, 3::6] < 0).any()          # the unwrapped lead_head went negative across x = 0
+    np.savez_compressed(os.path.join(HERE, 'ring_ma_accel.npz'), actions=acts, pos=np.array(P),
+                        vel=np.array(Vv), obs=O, reward=np.array(Rw))
+
+
 ZOO = [
     ('ovm', OVM, {}, 'OVM', None),
     ('ovm_inst', OVM, {'fail_safe': 'instantaneous'}, 'OVM', 'instantaneous'),
@@ -378,7 +408,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); start_pos()
+    ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos()
     sumo_fixture()
     print('golden vectors written to', HERE)
 

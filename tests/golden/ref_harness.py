@@ -18,6 +18,7 @@ from flow.core import rewards as ref_rewards  # noqa: E402
 from flow.envs.ring.wave_attenuation import WaveAttenuationEnv, \
     WaveAttenuationPOEnv  # noqa: E402
 from flow.envs.ring.accel import AccelEnv  # noqa: E402
+from flow.envs.multiagent.ring.accel import MultiAgentAccelPOEnv  # noqa: E402
 from flow.envs.multiagent.ring.wave_attenuation import \
     MultiAgentWaveAttenuationPOEnv  # noqa: E402
 import flow.controllers as ref_ctrl  # noqa: E402
@@ -292,6 +293,13 @@ class RefRing:
             # dict keyed by rl id -> rows in get_rl_ids() order (= action-slot order)
             d = MultiAgentWaveAttenuationPOEnv.get_state(self)
             return np.concatenate([d[v] for v in self.k.vehicle.get_rl_ids()])
+        if self.env_kind == 'ma_accel_po':
+            # the reference's get_state keeps its own `leader` / `follower` lists on the env:
+            # hand it a view that shares the kernel but not this harness's arrays
+            view = type('EnvView', (), {})()
+            view.k, view.env_params = self.k, self.env_params
+            d = MultiAgentAccelPOEnv.get_state(view)
+            return np.concatenate([d[v] for v in self.k.vehicle.get_rl_ids()])
         if self.env_kind == 'wave_po':
             return WaveAttenuationPOEnv.get_state(self)
         if self.env_kind == 'wave':
@@ -309,6 +317,11 @@ class RefRing:
                 assert all(x == vals[0] for x in vals)
                 return vals[0]
             return r
+        if self.env_kind == 'ma_accel_po':
+            r = MultiAgentAccelPOEnv.compute_reward(self, rl_actions, fail=fail)
+            vals = list(r.values())
+            assert all(x == vals[0] for x in vals)
+            return vals[0]
         if self.env_kind in ('wave', 'wave_po'):
             return WaveAttenuationEnv.compute_reward(self, rl_actions, fail=fail)
         return AccelEnv.compute_reward(self, rl_actions, fail=fail)

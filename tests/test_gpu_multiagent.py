@@ -124,3 +124,93 @@ def test_ma_env_dict_api_matches_golden():
     o, r, d, _ = envb.step({'rl_0_0': torch.zeros(16), 'rl_1_0': torch.full((16,), 0.5)})
     assert r['rl_0_0'].shape == (16,) and d['__all__'].shape == (16,)
     envb.terminate()
+
+
+# ---- MultiAgentAccelPOEnv (flow/envs/multiagent/ring/accel.py:87-226) --------------------
+def test_multiagent_accel_po_golden_fp64():
+    """6 numbers per RL vehicle incl. follower speed / headway and the reference's unwrapped
+    leader distance, every thread shape of the generic ring kernel; reward shared."""
+    import torch
+    from tests.test_oracle_golden import ma_accel_groups, MA_ACCEL
+    z = np.load(os.path.join(G, 'ring_ma_accel.npz'))
+    E = 5
+    eng = S.make_engine(ma_accel_groups(), E, 'f64', length=180, env_kind=OS.ENV_MA_ACCEL_PO,
+                        **MA_ACCEL)
+    obs = eng.reset()
+    assert eng.obs_dim == 18 and eng.act_dim == 3
+    assert close(obs.cpu().numpy()[4], z['obs'][0]) <= 1e-12
+    acts = z['actions']
+    warm = int(np.isnan(acts).any(1).sum())
+    for s in range(warm):
+        obs, rew, done = eng.step(None)
+        assert close(obs.cpu().numpy()[0], z['obs'][s + 1]) <= 1e-9, s
+    s, n = warm, len(acts)
+    for K in (1, 7, 100, n):
+        K = min(K, n - s)
+        obs_seq = torch.empty(K, E, 18, device='cuda', dtype=torch.float64)
+        rew_seq = torch.empty(K, E, device='cuda', dtype=torch.float64)
+        eng.step(torch.tensor(np.repeat(acts[s:s + K, :, None], E, 2), device='cuda'), k=K,
+                 obs_seq=obs_seq, reward_seq=rew_seq)
+        assert close(obs_seq.cpu().numpy()[:, 2], z['obs'][s + 1:s + K + 1]) <= 1e-9, s
+        assert close(rew_seq.cpu().numpy()[:, 2], z['reward'][s:s + K]) <= 1e-9, s
+        s += K
+    assert s == n
+
+
+def test_multiagent_accel_po_small_rings_vs_oracle():
+    """V = 1 (nobody ahead or behind: vmax / 0 / L defaults), V = 2 and V = 40 (other thread
+    mappings of the generic kernel), fp32 within 1e-4."""
+    import torch
+    for groups, L in (([S.vt('RL', 1)], 60), ([S.vt('RL', 2)], 60),
+                      ([S.vt('IDM', 19), S.vt('RL', 1), S.vt('IDM', 19), S.vt('RL', 1)], 420)):
+        kw = dict(env_kind=OS.ENV_MA_ACCEL_PO, act_lo=-1.0, act_hi=1.0, target_velocity=20.0)
+        o = S.make_oracle(groups, L, **kw)
+        A = len(o.rl_idx)
+        rng = np.random.default_rng(A)
+        acts = rng.uniform(-0.2, 0.6, (60, A))
+        ref = [o.step(list(a)) for a in acts]
+        for dt, tol in (('f64', 1e-9), ('f32', 1e-4)):
+            eng = S.make_engine(groups, 3, dt, length=L, **kw)
+            eng.reset()
+            td = torch.float64 if dt == 'f64' else torch.float32
+            obs_seq = torch.empty(60, 3, 6 * A, device='cuda', dtype=td)
+            rew_seq = torch.empty(60, 3, device='cuda', dtype=td)
+            eng.step(torch.tensor(np.repeat(acts[:, :, None], 3, 2), device='cuda', dtype=td), k=60,
+                     obs_seq=obs_seq, reward_seq=rew_seq)
+            assert close(obs_seq.cpu().numpy()[:, 1], np.array([r[0] for r in ref]), floor=0.05) <= tol
+            assert close(rew_seq.cpu().numpy()[:, 1], np.array([r[1] for r in ref]), floor=0.05) <= tol
+
+
+def test_multiagent_accel_po_dict_api_matches_golden():
+    from flow_b200 import flow_api as F
+    z = np.load(os.path.join(G, 'ring_ma_accel.npz'))
+    v = F.VehicleParams()
+    for name, ctrl, n in (('rl_a', F.RLController, 1), ('ha', F.IDMController, 6),
+                          ('rl_b', F.RLController, 1), ('hb', F.IDMController, 7),
+                          ('rl_c', F.RLController, 1)):
+        v.add(veh_id=name, acceleration_controller=(ctrl, {}),
+              routing_controller=(F.ContinuousRouter, {}), num_vehicles=n)
+    fp = dict(exp_tag='ma_accel', env_name=F.MultiAgentAccelPOEnv, network=F.RingNetwork,
+              simulator='traci', sim=F.SumoParams(sim_step=0.1),
+              env=F.EnvParams(horizon=3000, additional_params={
+                  'max_accel': 1, 'max_decel': 1, 'target_velocity': 20}),
+              net=F.NetParams(additional_params={'length': 180, 'lanes': 1, 'speed_limit': 30,
+                                                 'resolution': 40}),
+              veh=v, initial=F.InitialConfig())
+    env = F.make_create_env(fp)[0]()
+    ids = ['rl_a_0', 'rl_b_0', 'rl_c_0']
+    assert env.rl_ids == ids and env.observation_space.shape == (6,)
+    obs = env.reset()
+    np.testing.assert_allclose(np.concatenate([obs[i] for i in ids]), z['obs'][0], atol=1e-12)
+    for s, a in enumerate(z['actions'][:300]):
+        acts = None if np.isnan(a).any() else {i: [a[q]] for q, i in enumerate(ids)}
+        obs, rew, done, info = env.step(acts)
+        np.testing.assert_allclose(np.concatenate([obs[i] for i in ids]), z['obs'][s + 1],
+                                   rtol=1e-9, atol=1e-12)
+        assert set(rew) == set(ids)                       # a dict even during the warm-up
+        assert abs(rew['rl_b_0'] - z['reward'][s]) <= 1e-9
+        assert not done['__all__']
+    env.terminate()
+    with pytest.raises(KeyError):            # multiagent/ring/accel.py:125-128
+        bad = dict(fp, env=F.EnvParams(horizon=10, additional_params={'max_accel': 1, 'max_decel': 1}))
+        F.make_create_env(bad)[0]()

@@ -319,6 +319,28 @@ def test_multilane_known_answers_of_the_reference_test():
     np.testing.assert_array_almost_equal([t[1] for t in nb], [28.577143] * 3)
 
 
+def ma_accel_groups():
+    return [S.vt('RL', 1), S.vt('IDM', 6), S.vt('RL', 1), S.vt('IDM', 7), S.vt('RL', 1)]
+
+
+MA_ACCEL = dict(act_lo=-1.0, act_hi=1.0, target_velocity=20.0)
+
+
+def test_multiagent_accel_po_trajectory_bit_exact():
+    """MultiAgentAccelPOEnv.get_state / compute_reward of the reference
+    (tests/golden/ring_ma_accel.npz) vs the oracle restatement, incl. the unwrapped
+    leader distance across x = 0."""
+    z = np.load(os.path.join(G, 'ring_ma_accel.npz'))
+    o = S.make_oracle(ma_accel_groups(), 180, env_kind=OS.ENV_MA_ACCEL_PO, **MA_ACCEL)
+    assert np.array_equal(np.array(o.pos), z['pos'][0])
+    assert np.array_equal(o.get_state(), z['obs'][0])
+    for s, a in enumerate(z['actions']):
+        obs, rew, done = o.step(None if np.isnan(a).any() else list(a))
+        assert np.array_equal(np.array(o.pos), z['pos'][s + 1]), s
+        assert np.array_equal(np.asarray(obs), z['obs'][s + 1]), s
+        assert rew == z['reward'][s] and not done, s
+
+
 def test_lane_change_direction_validation():
     o = S.make_oracle(c3_groups(), 230, env_kind=OS.ENV_LANE_CHANGE_ACCEL, n_lanes=3,
                       act_lo=-3, act_hi=3)
