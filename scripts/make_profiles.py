@@ -48,15 +48,20 @@ if os.path.exists(ll):
 
 # 2. full captures -> summary csv + traffic json
 traffic = {}
-for wl in ('c2', 'c5'):
+KERNEL = {'c2': 'ring1_hot', 'c5': 'ring1_hot', 'c3': 'ring_ml', 'c4': 'highway_kernel'}
+for wl in ('c2', 'c5', 'c3', 'c4'):
     raw = os.path.join(G, 'prof_%s_final_raw.csv' % wl)
+    rep = os.path.join(G, ('prof_%s_final.ncu-rep' if wl in ('c2', 'c5') else 'prof_%s.ncu-rep') % wl)
+    if os.path.exists(rep) and (not os.path.exists(raw) or os.path.getmtime(raw) < os.path.getmtime(rep)):
+        with open(raw, 'w') as f:
+            subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], stdout=f, stderr=subprocess.DEVNULL)
     if not os.path.exists(raw):
         continue
     out = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'ncu_summary.py'), raw],
                          capture_output=True, text=True).stdout
-    open(os.path.join(P, '%s_ncu_full_%s_ring1_hot_f32.csv' % (tag, wl)), 'w').write(
-        '# ncu --set full --clock-control none --import-source on -k regex:ring1_hot, one timed '
-        'fused launch (100 steps) of python bench.py --workload %s --only-fused\n' % wl + out)
+    open(os.path.join(P, '%s_ncu_full_%s_%s_f32.csv' % (tag, wl, KERNEL[wl] if wl in ('c3', 'c4') else 'ring1_hot')), 'w').write(
+        '# ncu --set full --clock-control none --import-source on -k regex:%s, one timed '
+        'fused launch (100 steps) of python bench.py --workload %s --only-fused\n' % (KERNEL[wl], wl) + out)
     rows = list(csv.reader(open(raw)))
     h, u, r = rows[0], rows[1], rows[2]
     def val(k):
@@ -68,8 +73,9 @@ if traffic:
     json.dump(traffic, open(os.path.join(P, 'ncu_traffic.json'), 'w'), indent=1)
 
 # 3. bench lines
-for wl in ('c2', 'c5'):
-    b = os.path.join(G, 'bench_%s.json' % wl)
+for wl, src in (('c2', 'final_default.json'), ('c5', 'final_c5.json'), ('c3', 'bench_c3.json'),
+                ('c4', 'bench_c4.json'), ('reference_arm', 'final_reference.json')):
+    b = os.path.join(G, src)
     if os.path.exists(b):
         open(os.path.join(P, '%s_bench_%s.json' % (tag, wl)), 'w').write(open(b).read())
 print(sorted(os.listdir(P)))
