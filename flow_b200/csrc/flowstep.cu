@@ -596,8 +596,36 @@ static int do_step_sorted(fs_engine* e, const void* actions, int k, void* obs_se
 }
 
 template <typename T>
+static int do_step1(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
+                    uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done);
+
+// Env.step runs sims_per_step simulation steps on the same actions and observes once
+// (flow/envs/base.py:325-383). Every shipped ring / highway config uses 1; other values take
+// one launch per simulation step, outputs from the last one (a collision freezes the env, so
+// the remaining sub-steps of that env are no-ops, like the reference's `break`).
+template <typename T>
 static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
                    uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done) {
+  const int S = e->cfg.sims_per_step;
+  if (S <= 1 || k == 0)
+    return do_step1<T>(e, actions, k, obs_seq, reward_seq, done_seq, mask, stats, ignore_done);
+  const size_t E = e->cfg.n_envs, act_row = (size_t)e->act_dim * E, obs_row = E * e->obs_dim;
+  for (int s = 0; s < k; ++s) {
+    const T* act = actions ? (const T*)actions + s * act_row : nullptr;
+    for (int q = 0; q < S; ++q) {
+      const bool last = q == S - 1;
+      int rc = do_step1<T>(e, act, 1, last && obs_seq ? (T*)obs_seq + s * obs_row : nullptr,
+                           last && reward_seq ? (T*)reward_seq + s * E : nullptr,
+                           last && done_seq ? done_seq + s * E : nullptr, mask, stats, ignore_done);
+      if (rc != FS_OK) return rc;
+    }
+  }
+  return FS_OK;
+}
+
+template <typename T>
+static int do_step1(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
+                    uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done) {
   if (e->sort_on())
     return do_step_sorted<T>(e, actions, k, obs_seq, reward_seq, done_seq, mask, stats, ignore_done);
   fs::StepArgs<T> a;

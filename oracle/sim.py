@@ -113,7 +113,7 @@ class RingSim:
                  horizon=3000, target_velocity=10.0, act_lo=-4.5, act_hi=2.6,
                  clip_actions=False, obs_max_length=None,
                  lane_change_duration=5, noise_fn=None, evaluate=False,
-                 sort_vehicles=False):
+                 sort_vehicles=False, sims_per_step=1):
         self.types = types
         self.type_of = list(type_of_vehicle)
         self.num_vehicles = len(self.type_of)
@@ -133,6 +133,7 @@ class RingSim:
         self.lane_change_duration = lane_change_duration
         self.noise_fn = noise_fn  # (step, vehicle) -> N(0,1) sample
         self.lc_bug_compat = True  # get_last_lc returns the headway (vehicle/traci.py:614)
+        self.sims_per_step = int(sims_per_step)   # EnvParams.sims_per_step (base.py:325)
         self.evaluate = evaluate            # EnvParams.evaluate (accel.py:111-112)
         self.sort_vehicles = sort_vehicles  # additional_params['sort_vehicles'] (accel.py:150-169)
         # AccelEnv.absolute_position / prev_pos: dicts made once in __init__ (accel.py:77-78),
@@ -288,10 +289,27 @@ class RingSim:
 
     # -- Env.step ---------------------------------------------------------
     def step(self, rl_actions):
-        """One Env.step with sims_per_step = 1 (flow/envs/base.py:294-412).
-        Returns (obs, reward, done). A finished env is frozen."""
+        """One Env.step (flow/envs/base.py:294-412): sims_per_step simulation steps with
+        the same actions (stopping at a collision, :378-383), then observation, done and
+        reward once. Returns (obs, reward, done). A finished env is frozen."""
         if self.done:
             return self.get_state(), 0.0, True
+        clipped = None
+        for _ in range(self.sims_per_step):
+            clipped = self._sim_step(rl_actions)
+            if self.crash:
+                break
+        obs = self.get_state()
+        self.done = (self.time_counter >= self.sims_per_step *
+                     (self.warmup_steps + self.horizon)) or self.crash
+        acts = rl_actions
+        if rl_actions is not None and self.clip_actions:
+            acts = clipped
+        reward = self.compute_reward(acts, self.crash)
+        return obs, reward, self.done
+
+    def _sim_step(self, rl_actions):
+        """Body of the `for _ in range(sims_per_step)` loop; returns the clipped actions."""
         V, dt = self.num_vehicles, self.dt
         self.time_counter += 1
         next_vel = [0.0] * V
@@ -366,14 +384,7 @@ class RingSim:
         self.step_index += 1
         self.update()
         self.crash = any(h < 0 for h in self.headway)
-        obs = self.get_state()
-        self.done = (self.time_counter >= self.warmup_steps + self.horizon) \
-            or self.crash
-        acts = rl_actions
-        if rl_actions is not None and self.clip_actions:
-            acts = clipped
-        reward = self.compute_reward(acts, self.crash)
-        return obs, reward, self.done
+        return clipped
 
     # -- observations / rewards -------------------------------------------
     def get_state(self):

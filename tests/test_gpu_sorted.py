@@ -121,3 +121,41 @@ def test_sort_vehicles_rejected_where_the_reference_has_no_such_option():
     with pytest.raises(FlowStepError):
         S.make_engine(S.c2_groups(), 2, 'f32', env_kind=OS.ENV_WAVE_ATTENUATION_PO,
                       sort_vehicles=1, **S.C2)
+
+
+def test_sims_per_step_counters_and_trajectory():
+    """EnvParams.sims_per_step (flow/envs/base.py:325-383): the reference's own checks
+    (tests/fast_tests/test_environment_base_class.py:256-303: reset advances
+    warmup_steps x sims_per_step, a step advances sims_per_step) and the trajectory /
+    observation / reward against the oracle, fused and stepwise."""
+    import torch
+    S5 = 5
+    kw = dict(env_kind=OS.ENV_WAVE_ATTENUATION_PO, length_lo=230., length_hi=230.,
+              sims_per_step=S5, **dict(S.C2, warmup_steps=7, horizon=40))
+    E = 4
+    eng = S.make_engine(S.c2_groups(), E, 'f64', **kw)
+    okw = dict(kw); okw.pop('length_lo'); okw.pop('length_hi')
+    o = S.make_oracle(S.c2_groups(), 230, **okw)
+    obs = eng.reset()
+    assert int(eng.time_counter[0]) == 7 * S5 == o.time_counter
+    assert close(obs.cpu().numpy()[0], o.get_state()) <= 1e-9
+    rng = np.random.default_rng(2)
+    acts = rng.uniform(-1.2, 0.6, (40, 1))
+    obs, rew, done = eng.step(torch.tensor(np.repeat(acts[0][:, None], E, 1), device='cuda'))
+    ob, r, d = o.step(list(acts[0]))
+    assert int(eng.time_counter[1]) == 8 * S5 == o.time_counter
+    assert close(obs.cpu().numpy()[1], ob) <= 1e-9 and close(rew.cpu().numpy()[1], r) <= 1e-9
+    K = 39
+    obs_seq = torch.empty(K, E, 3, device='cuda', dtype=torch.float64)
+    rew_seq = torch.empty(K, E, device='cuda', dtype=torch.float64)
+    done_seq = torch.empty(K, E, device='cuda', dtype=torch.uint8)
+    eng.step(torch.tensor(np.repeat(acts[1:, :, None], E, 2), device='cuda'), k=K,
+             obs_seq=obs_seq, reward_seq=rew_seq, done_seq=done_seq)
+    for k in range(K):
+        ob, r, d = o.step(list(acts[1 + k]))
+        assert close(obs_seq.cpu().numpy()[k, 2], ob) <= 1e-9, k
+        assert close(rew_seq.cpu().numpy()[k, 2], r) <= 1e-9, k
+        assert bool(done_seq[k, 2]) == d, k
+    assert d and int(eng.time_counter[3]) == o.time_counter      # stopped where the oracle stopped
+    assert o.time_counter % S5 == 0 or o.crash
+    assert close(eng.pos.cpu().numpy()[:, 0], o.pos) <= 1e-9
