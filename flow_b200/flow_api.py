@@ -561,6 +561,15 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
     lc_env = env_cls.KIND in (EN.ENV_LANE_CHANGE_ACCEL, EN.ENV_LANE_CHANGE_ACCEL_PO)
     types, names, type_of, ids = [], [], [], []
     for t, row in enumerate(veh.initial):
+        lcp = row.get('lane_change_params')
+        mode = getattr(lcp, 'lane_change_mode', 512)
+        if int(net['lanes']) > 1 and isinstance(mode, (int, float)) and int(mode) & 0xFF:
+            # bits 0-7 = SUMO's autonomous strategic / cooperative / speed-gain / keep-right
+            # changes (LC2013 / SL2015): not restated, and never silently dropped
+            raise NotImplementedError(
+                'lane_change_mode %r of "%s" lets SUMO change lanes on its own; only modes without '
+                'autonomous changes (512 "no_lat_collide", 0 "aggressive") are compiled'
+                % (mode, row['veh_id']))
         types.append(_vtype_row(row, lc_env))
         names.append(row['veh_id'])
         type_of += [t] * row['num_vehicles']

@@ -132,6 +132,15 @@ def test_reference_error_behaviour():
         F.IDMController('x', bogus=1)
 
 
+def test_sumo_autonomous_lane_changes_are_refused_not_dropped():
+    fp = lane_change_po_flow_params()
+    fp['veh'].initial[0]['lane_change_params'] = F.SumoLaneChangeParams(lane_change_mode='strategic')
+    with pytest.raises(NotImplementedError):
+        spec_of(fp)
+    fp['veh'].initial[0]['lane_change_params'] = F.SumoLaneChangeParams(lane_change_mode='aggressive')
+    spec_of(fp)
+
+
 def test_controller_tables():
     fs = F.FollowerStopper('a', v_des=7)
     assert (fs.delay, fs.fail_safe, fs.engine_params()) == (1.0, 'safe_velocity', [7])
