@@ -154,7 +154,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
         cfg->env_kind != FS_ENV_LANE_CHANGE_ACCEL_PO)))
     return fail(nullptr, FS_EINVAL, "fs_create: sort_vehicles exists for AccelEnv / "
                                     "LaneChangeAccel(PO)Env on the ring only");
-  if (cfg->env_flags & ~(FS_ENVF_EVALUATE | FS_ENVF_SORT_VEHICLES))
+  if (cfg->env_flags & ~(FS_ENVF_EVALUATE | FS_ENVF_SORT_VEHICLES | FS_ENVF_BALLISTIC))
     return fail(nullptr, FS_EINVAL, "fs_create: unknown env_flags bit");
   int ndev = 0;
   cudaError_t st = cudaGetDeviceCount(&ndev);
@@ -242,6 +242,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
   c.length_lo = (T)g.length_lo; c.length_hi = (T)g.length_hi;
   c.lanes_distribution = g.lanes_distribution;
   c.evaluate = (g.env_flags & FS_ENVF_EVALUATE) ? 1 : 0;
+  c.ballistic = (g.env_flags & FS_ENVF_BALLISTIC) ? 1 : 0;
   for (int t = 0; t < n_types; ++t) {
     const fs_vtype& s = types[t];
     fs::TypeP<T>& d = c.types[t];
@@ -315,7 +316,7 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     // and at most one RL type, equal lengths, delta = 4
     int ta = -1, tb = -1;
     bool ok = e->cfg.n_veh == 22 && !e->generic && e->cfg.topology == FS_TOPO_RING &&
-              e->cfg.n_lanes == 1 && !(e->cfg.env_flags & FS_ENVF_EVALUATE) &&
+              e->cfg.n_lanes == 1 && !(e->cfg.env_flags & (FS_ENVF_EVALUATE | FS_ENVF_BALLISTIC)) &&
               e->cfg.env_kind != FS_ENV_MA_ACCEL_PO;   // follower view: generic kernel only
     for (int i = 0; ok && i < e->cfg.n_veh; ++i) {
       const int t = type_of_vehicle[i];

@@ -45,7 +45,9 @@ struct Cfg {
   T x0, bunching, init_min_gap;
   T target_velocity, act_lo, act_hi, obs_max_length;
   T length_lo, length_hi;
-  int lanes_distribution, evaluate;  // evaluate: EnvParams.evaluate (AccelEnv reward = mean speed)
+  int lanes_distribution;
+  int16_t evaluate;   // EnvParams.evaluate (AccelEnv reward = mean speed)
+  int16_t ballistic;  // SumoParams.use_ballistic: x += (v_old + v_new)/2 dt instead of v_new dt
   TypeP<T> types[FS_MAX_TYPES];
   uint8_t type_of[FS_MAX_VEH];
   int16_t rl_index[FS_MAX_VEH];  // vehicle -> action slot, -1 if not RL
@@ -93,6 +95,14 @@ template <typename T>
 __device__ __forceinline__ T fwd_dist(T a, T b, T C) {
   T d = a - b;
   return d < T(0) ? d + C : d;
+}
+
+// The simulator move (restated SUMO): Euler x += v_new dt by default,
+// the ballistic update x += (v_old + v_new)/2 dt with SumoParams(use_ballistic=True)
+// (flow/core/kernel/simulation/traci.py:95-96 only hands SUMO the switch).
+template <typename T>
+__device__ __forceinline__ T move_dist(T v_old, T v_new, T dt, int ballistic) {
+  return ballistic ? mul(mul(T(0.5), add(v_old, v_new)), dt) : mul(v_new, dt);
 }
 
 // ------------------------------------------------------------ Philox4x32-10

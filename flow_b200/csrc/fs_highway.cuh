@@ -162,7 +162,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         bool keep = false;
         if (s < n) {
           const T vn = N::max(add(v[r], mul(acc[r], dt)), T(0));
-          x[r] = add(x[r], mul(vn, dt));
+          x[r] = add(x[r], move_dist<T>(v[r], vn, dt, cfg.ballistic));
           v[r] = vn;
           keep = x[r] < Lr;
         }

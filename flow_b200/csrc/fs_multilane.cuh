@@ -382,7 +382,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       for (int s = 0; s < SLOTS; ++s) {
         if (lane_id + 32 * s >= V) continue;
         const T vn = N::max(add(v[s], mul(acc[s], dt)), T(0));
-        x[s] = wrap_fwd(add(x[s], mul(vn, dt)), C);
+        x[s] = wrap_fwd(add(x[s], move_dist<T>(v[s], vn, dt, cfg.ballistic)), C);
         v[s] = vn;
         ln[s] = new_ln[s];
       }

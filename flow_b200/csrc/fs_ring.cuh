@@ -321,7 +321,7 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
         }
         // apply_acceleration (vehicle/traci.py:961-962) + Euler move
         const T vn = N::max(add(vi, mul(a, dt)), T(0));
-        const T xn = wrap_fwd(add(x[j], mul(vn, dt)), C);
+        const T xn = wrap_fwd(add(x[j], move_dist<T>(vi, vn, dt, cfg.ballistic)), C);
         vf = vi; hf = hi;  // old values: follower data of the next slot
         if (ok) { v[j] = vn; x[j] = xn; acc[j] = a; }
       }

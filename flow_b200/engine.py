@@ -21,7 +21,7 @@ CTRL_SIM, CTRL_IDM, CTRL_OVM, CTRL_LINEAR_OVM, CTRL_BCM, CTRL_CFM, CTRL_LAC, \
     CTRL_PI_SATURATION, CTRL_RL = range(12)
 FAILSAFE = {None: 0, 'instantaneous': 1, 'safe_velocity': 2}
 LC_SIM, LC_STATIC, LC_RL = 0, 1, 2
-ENVF_EVALUATE, ENVF_SORT_VEHICLES = 1, 2
+ENVF_EVALUATE, ENVF_SORT_VEHICLES, ENVF_BALLISTIC = 1, 2, 4
 
 
 class FlowStepError(RuntimeError):
@@ -100,14 +100,15 @@ class Engine:
                         act_hi=2.6, obs_max_length=0.0, inflow_vehs_per_hour=0.0,
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
                         record_views=0, lc_corrected=0, n_initial=0, inflow_begin=1.0,
-                        evaluate=0, sort_vehicles=0)
+                        evaluate=0, sort_vehicles=0, use_ballistic=0)
         unknown = set(cfg) - set(defaults)
         if unknown:
             raise TypeError('unknown engine config keys: %s' % sorted(unknown))
         defaults.update(cfg)
         # EnvParams.evaluate / additional_params['sort_vehicles'] -> fs_config.env_flags
         defaults['env_flags'] = (ENVF_EVALUATE if defaults.pop('evaluate') else 0) | \
-            (ENVF_SORT_VEHICLES if defaults.pop('sort_vehicles') else 0)
+            (ENVF_SORT_VEHICLES if defaults.pop('sort_vehicles') else 0) | \
+            (ENVF_BALLISTIC if defaults.pop('use_ballistic') else 0)
         for k, v in defaults.items():
             setattr(c, k, v)
         self.config = c

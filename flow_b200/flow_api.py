@@ -552,8 +552,6 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
                                   'perturbation=0) placements are compiled')
     if ini.edges_distribution != 'all':
         raise NotImplementedError('edges_distribution other than "all"')
-    if getattr(sim_params, 'use_ballistic', False):
-        raise NotImplementedError('ballistic integration (the engine restates the Euler move)')
     sort_on = bool(ap.get('sort_vehicles')) and env_cls.KIND in (
         EN.ENV_ACCEL, EN.ENV_LANE_CHANGE_ACCEL, EN.ENV_LANE_CHANGE_ACCEL_PO)
     if sort_on and network.TOPOLOGY != EN.TOPO_RING:
@@ -593,6 +591,7 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         # (accel.py:111-112); sorted_ids: accel.py:150-169
         evaluate=int(bool(env_params.evaluate) and env_cls.KIND == EN.ENV_ACCEL),
         sort_vehicles=int(sort_on),
+        use_ballistic=int(bool(getattr(sim_params, 'use_ballistic', False))),
         seed=int(seed if seed is not None else (getattr(sim_params, 'seed', None) or 0)))
     capacity = None
     if network.TOPOLOGY == EN.TOPO_RING:

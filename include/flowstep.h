@@ -114,6 +114,9 @@ extern "C" {
                                    action slots in order of AccelEnv.absolute_position
                                    (flow/envs/ring/accel.py:100-169); ring topology only  */
 
+#define FS_ENVF_BALLISTIC 4     /* SumoParams.use_ballistic (flow/core/kernel/simulation/traci.py:95-96):
+                                   the restated move becomes x += (v_old + v_new)/2 dt           */
+
 #define FS_MAX_TYPES 16
 #define FS_NPARAM 8
 

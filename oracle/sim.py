@@ -113,7 +113,7 @@ class RingSim:
                  horizon=3000, target_velocity=10.0, act_lo=-4.5, act_hi=2.6,
                  clip_actions=False, obs_max_length=None,
                  lane_change_duration=5, noise_fn=None, evaluate=False,
-                 sort_vehicles=False, sims_per_step=1):
+                 sort_vehicles=False, sims_per_step=1, use_ballistic=False):
         self.types = types
         self.type_of = list(type_of_vehicle)
         self.num_vehicles = len(self.type_of)
@@ -134,6 +134,7 @@ class RingSim:
         self.noise_fn = noise_fn  # (step, vehicle) -> N(0,1) sample
         self.lc_bug_compat = True  # get_last_lc returns the headway (vehicle/traci.py:614)
         self.sims_per_step = int(sims_per_step)   # EnvParams.sims_per_step (base.py:325)
+        self.use_ballistic = use_ballistic        # SumoParams.use_ballistic (simulation/traci.py:95-96)
         self.evaluate = evaluate            # EnvParams.evaluate (accel.py:111-112)
         self.sort_vehicles = sort_vehicles  # additional_params['sort_vehicles'] (accel.py:150-169)
         # AccelEnv.absolute_position / prev_pos: dicts made once in __init__ (accel.py:77-78),
@@ -378,8 +379,11 @@ class RingSim:
         self.additional_command()      # base.py:365, before simulation_step
         # simulator move (restated SUMO Euler step)
         for i in range(V):
+            if self.use_ballistic:      # restated SUMO ballistic update
+                x = self.pos[i] + 0.5 * (self.vel[i] + next_vel[i]) * dt
+            else:
+                x = self.pos[i] + next_vel[i] * dt
             self.vel[i] = next_vel[i]
-            x = self.pos[i] + next_vel[i] * dt
             self.pos[i] = x % self.circ
         self.step_index += 1
         self.update()

@@ -159,3 +159,27 @@ def test_sims_per_step_counters_and_trajectory():
     assert d and int(eng.time_counter[3]) == o.time_counter      # stopped where the oracle stopped
     assert o.time_counter % S5 == 0 or o.crash
     assert close(eng.pos.cpu().numpy()[:, 0], o.pos) <= 1e-9
+
+
+@pytest.mark.parametrize('lanes', [1, 3])
+def test_ballistic_update_vs_oracle(lanes):
+    """SumoParams(use_ballistic=True): x += (v_old + v_new)/2 dt in the generic ring kernel
+    (the IDM fast paths are bypassed) and the multi-lane kernel; differs from the Euler run."""
+    import torch
+    g = [S.vt('IDM', 14), S.vt('OVM', 4)] if lanes == 1 else [S.vt('IDM', 18)]
+    kw = dict(env_kind=OS.ENV_ACCEL, n_lanes=lanes, use_ballistic=1)
+    eng = S.make_engine(g, 2, 'f64', length=200, **kw)
+    eul = S.make_engine(g, 2, 'f64', length=200, **dict(kw, use_ballistic=0))
+    o = S.make_oracle(g, 200, **dict(kw, use_ballistic=True))
+    eng.reset(); eul.reset()
+    K = 150
+    obs_seq = torch.empty(K, 2, 36, device='cuda', dtype=torch.float64)
+    rew_seq = torch.empty(K, 2, device='cuda', dtype=torch.float64)
+    eng.step(None, k=K, obs_seq=obs_seq, reward_seq=rew_seq)
+    eul.step(None, k=K)
+    for k in range(K):
+        ob, r, d = o.step(None)
+        assert close(obs_seq.cpu().numpy()[k, 1], ob) <= 1e-9, k
+        assert close(rew_seq.cpu().numpy()[k, 1], r) <= 1e-9, k
+    assert close(eng.pos.cpu().numpy()[:, 0], o.pos) <= 1e-9
+    assert np.abs(eng.pos.cpu().numpy() - eul.pos.cpu().numpy()).max() > 1e-3
