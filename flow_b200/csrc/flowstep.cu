@@ -341,7 +341,10 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
       for (int i = 0; i < e->cfg.n_veh; ++i) n_rl += types[type_of_vehicle[i]].controller == FS_CTRL_RL;
       e->hot_ok = ok && n_rl == 1 &&
                   types[type_of_vehicle[e->cfg.n_veh - 1]].controller == FS_CTRL_RL &&
-                  e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO && !e->cfg.record_views;
+                  e->cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO && !e->cfg.record_views &&
+                  // the hot kernel omits the went-through-its-leader test of the other ring
+                  // kernels: with dt <= 0.1 that needs a closing speed above 50 m/s
+                  e->cfg.sim_step <= 0.1;
     }
     if (ok) {
       const fs_vtype& s = types[ta];

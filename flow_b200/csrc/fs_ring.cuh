@@ -326,10 +326,16 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
         if (ok) { v[j] = vn; x[j] = xn; acc[j] = a; }
       }
       // ---- k.update + collision + reward sums on the post-move state
+      T h_old[VPT];
+      FS_SLOTS(j) h_old[j] = h[j];
       update_headways();
       bool cr = false;
       T sv = T(0), sq = T(0);
+      const T half_lap = mul(T(0.5), C);
       FS_SLOTS(j) if (j < n_mine) {
+        // a vehicle that went THROUGH its leader inside the step (forward distance wraps by
+        // a lap) collided on a single lane even if the two no longer overlap afterwards
+        cr |= has_lead && (h[j] - h_old[j]) > half_lap;
         if (cfg.collision_min_gap) {
           int i1 = base + j + 1; if (i1 >= V) i1 = 0;
           cr |= has_lead && h[j] < cfg.types[cfg.type_of[i1]].sim_min_gap;

@@ -375,12 +375,16 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
       }
       if (G > 1) { x_nf = shfl(x[0], lane_next, gmask); v_nf = shfl(v[0], lane_next, gmask); }
       else { x_nf = x[0]; v_nf = v[0]; }
+      T h_old[VPT];
+      FS_SLOTS(j) h_old[j] = h[j];
       update_headways();
       bool cr = false;
       T sv = T(0), sq = T(0);
       float s2 = 0.f;
+      const T half_lap = T(0.5) * C;
       FS_SLOTS(j) if (kExact || j < n_mine) {
         cr |= h[j] < crash_thr;
+        cr |= (h[j] - h_old[j]) > half_lap;   // went through its leader inside the step
         sv = add(sv, v[j]);
         if (accel_env) { const T d = v[j] - P.target; sq = add(sq, mul(d, d)); }
         if (st_on) s2 = fmaf((float)v[j], (float)v[j], s2);

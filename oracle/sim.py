@@ -386,8 +386,18 @@ class RingSim:
             self.vel[i] = next_vel[i]
             self.pos[i] = x % self.circ
         self.step_index += 1
+        old_leader, old_headway = list(self.leader), list(self.headway)
         self.update()
         self.crash = any(h < 0 for h in self.headway)
+        if self.n_lanes == 1:
+            # restated SUMO: on a single lane a vehicle cannot get past its leader; one that
+            # went THROUGH it inside the step (the forward distance to that leader wraps by a
+            # lap) has collided even if the two no longer overlap afterwards
+            for i, j in enumerate(old_leader):
+                if j >= 0:
+                    d_new = (self.pos[j] - self.pos[i]) % self.circ - self.types[self.type_of[j]].length
+                    if d_new - old_headway[i] > 0.5 * self.circ:
+                        self.crash = True
         return clipped
 
     # -- observations / rewards -------------------------------------------
