@@ -38,7 +38,7 @@ class HighwaySim:
                  speed_limit=30.0, inflow_vehs_per_hour=2000.0, inflow_type=0,
                  inflow_depart_speed=20.0, inflow_begin=1.0, x0=0.0, bunching=0.0,
                  init_min_gap=0.0, horizon=3000, warmup_steps=0, target_velocity=10.0,
-                 noise_fn=None):
+                 noise_fn=None, evaluate=False, use_ballistic=False, sims_per_step=1):
         self.types = types
         self.initial_types = list(initial_types)
         self.capacity = capacity
@@ -53,6 +53,9 @@ class HighwaySim:
         self.horizon, self.warmup_steps = horizon, warmup_steps
         self.target_velocity = target_velocity
         self.noise_fn = noise_fn
+        self.evaluate = evaluate              # AccelEnv.compute_reward, accel.py:111-112
+        self.use_ballistic = use_ballistic    # SumoParams.use_ballistic
+        self.sims_per_step = int(sims_per_step)   # EnvParams.sims_per_step, base.py:325
         self.reset()
 
     # getters the controller functions use ---------------------------------
@@ -101,8 +104,22 @@ class HighwaySim:
                         for s in range(n)]
 
     def step(self):
+        """One Env.step: sims_per_step simulation steps (base.py:325-383), then obs / reward."""
         if self.done:
             return self.get_state(), 0.0, True
+        for _ in range(self.sims_per_step):
+            self._sim_step()
+            if self.crash:
+                break
+        self.done = self.crash or self.time_counter >= self.sims_per_step * (
+            self.warmup_steps + self.horizon)
+        if self.evaluate:
+            rew = float(np.mean(self.vel)) if self.vel else float('nan')
+        else:
+            rew = self.desired_velocity(self.crash)
+        return self.get_state(), rew, self.done
+
+    def _sim_step(self):
         dt = self.dt
         self.time_counter += 1
         n = len(self.pos)
@@ -114,8 +131,11 @@ class HighwaySim:
             self.accel[s] = a
             nv[s] = max(self.vel[s] + a * dt, 0.0)
         for s in range(n):
+            if self.use_ballistic:
+                self.pos[s] = self.pos[s] + 0.5 * (self.vel[s] + nv[s]) * dt
+            else:
+                self.pos[s] = self.pos[s] + nv[s] * dt
             self.vel[s] = nv[s]
-            self.pos[s] = self.pos[s] + nv[s] * dt
         # arrivals
         keep = [s for s in range(n) if self.pos[s] < self.length]
         self.arrived += n - len(keep)
@@ -140,8 +160,6 @@ class HighwaySim:
                     self.departed += 1
         self.update()
         self.crash = any(h < 0 for h in self.headway)
-        self.done = self.crash or self.time_counter >= self.warmup_steps + self.horizon
-        return self.get_state(), self.desired_velocity(self.crash), self.done
 
     def get_state(self):
         cap = self.capacity
