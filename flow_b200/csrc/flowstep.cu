@@ -435,15 +435,29 @@ static int launch_ml(fs_engine* e, const fs::StepArgs<T>& a) {
   b.v_leader = e->leader; b.v_follower = e->follower; b.stats = e->stats;
   b.lc_bug_compat = e->cfg.lc_corrected ? 0 : 1;
   const int E = e->cfg.n_envs, V = e->cfg.n_veh;
-  // one warp per block balances small batches over the 148 SMs (2048 envs: 13.8 blocks per
-  // SM instead of 3.5 four-warp blocks, +4 % on c3); four per block once occupancy matters
-  int wpb = E <= 148 * 32 ? 1 : 4;
-  if (const char* w = getenv("FS_ML_WPB")) { const int q = atoi(w); if (q == 1 || q == 2 || q == 4) wpb = q; }
-  const int grid = (E + wpb - 1) / wpb;
-  const size_t smem = (size_t)wpb * fs::ml_smem_per_warp<T>(V);
-  if (V <= 32) fs::ring_ml_kernel<T, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  else if (V <= 96) fs::ring_ml_kernel<T, 3><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  else fs::ring_ml_kernel<T, 8><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  // FS_ML_SPLIT=1: a block of W warps per env, one vehicle per thread (three times the warps
+  // for c3's 66 vehicles). Measured on c3 (2048 envs): 10.8 us per step against 9.1 us with
+  // one warp per env - the ~10 block barriers per step and the per-warp fixed work cost more
+  // than the extra warps hide - so one warp per env stays the default at every size.
+  bool split = false;
+  if (const char* w = getenv("FS_ML_SPLIT")) split = atoi(w) != 0 && V > 32;
+  if (split) {
+    const int W = V <= 64 ? 2 : (V <= 96 ? 3 : 4);
+    const size_t smem = fs::ml_smem_per_env<T>(V, W);
+    if (W == 2) fs::ring_ml_kernel<T, 1, 2><<<E, 64, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else if (W == 3) fs::ring_ml_kernel<T, 1, 3><<<E, 96, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else if (V <= 128) fs::ring_ml_kernel<T, 1, 4><<<E, 128, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else fs::ring_ml_kernel<T, 2, 4><<<E, 128, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  } else {
+    // one warp per block balances small batches over the 148 SMs (+4 % on c3 at 2048 envs);
+    // four per block once occupancy matters
+    const int wpb = E <= 148 * 32 ? 1 : 4;
+    const int grid = (E + wpb - 1) / wpb;
+    const size_t smem = (size_t)wpb * fs::ml_smem_per_env<T>(V, 1);
+    if (V <= 32) fs::ring_ml_kernel<T, 1, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else if (V <= 96) fs::ring_ml_kernel<T, 3, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else fs::ring_ml_kernel<T, 8, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  }
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   return FS_OK;

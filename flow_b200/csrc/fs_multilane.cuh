@@ -41,33 +41,84 @@ struct MlBufs {
   int lc_bug_compat;
 };
 
+// shared bytes of ONE environment's slice (W = warps that share the env)
 template <typename T>
-__host__ __device__ inline size_t ml_smem_per_warp(int V) {
-  return (size_t)V * (5 * sizeof(T) + 3 * sizeof(int)) + 16 * sizeof(int);
+__host__ __device__ inline size_t ml_smem_per_env(int V, int W) {
+  const size_t b = (size_t)V * (5 * sizeof(T) + 5 * sizeof(int)) + 16 * sizeof(T) +
+                   (16 + 8 + 8 * 8 * (size_t)W) * sizeof(int);
+  return (b + 15) & ~(size_t)15;   // slices of several envs in one block stay aligned for T
 }
 
-template <typename T, int SLOTS>
+// W = 1 (default): one warp owns an env, vehicle i lives in lane (i & 31), slot (i >> 5);
+//        several envs per block.
+// W > 1 (FS_ML_SPLIT=1, experiment kept under test): ONE BLOCK of W warps owns an env,
+//        vehicle i = tid + 32 W s; warp collectives become block collectives (__syncthreads,
+//        shared-memory partials). Same results; slower on c3 (see launch_ml in flowstep.cu).
+template <typename T, int SLOTS, int W>
 __global__ void __launch_bounds__(128)
 ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
+  constexpr int NT = 32 * W;       // threads per env
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane_id = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int lane_id = threadIdx.x & 31;
+  const int wid = W == 1 ? 0 : (int)(threadIdx.x >> 5);     // warp inside the env's group
+  const int tid = W == 1 ? lane_id : (int)threadIdx.x;      // thread inside the env's group
+  const int wib = W == 1 ? (int)(threadIdx.x >> 5) : 0;     // env slice inside the block
   const int E = cfg.n_envs, V = cfg.n_veh, L = cfg.n_lanes;
-  const int e = blockIdx.x * (blockDim.x >> 5) + wib;
-  if (e >= E) return;
+  const int e = W == 1 ? blockIdx.x * (blockDim.x >> 5) + wib : (int)blockIdx.x;
+  if (e >= E) return;                                  // block-uniform when W > 1
   if (A.mask != nullptr && A.mask[e] == 0) return;
-  // per-warp shared slice: xs[V] vs[V] hs[V] cx[V] lens[V] (T) | ls[V] ld[V] cidx[V] loff[16] (int)
-  const size_t per_warp = ml_smem_per_warp<T>(V);
-  unsigned char* mine = smem_raw + per_warp * wib;
+  // per-env shared slice: xs vs hs cx lens [V] redT[16] (T) | ls ld cidx rq_i rq_t [V]
+  //                       loff[16] rq_n[8] wcnt[8][8][W] (int)
+  const size_t per_env = ml_smem_per_env<T>(V, W);
+  unsigned char* mine = smem_raw + per_env * wib;
   T* xs = reinterpret_cast<T*>(mine);
   T* vs = xs + V;
   T* hs = vs + V;
   T* cx = hs + V;                  // positions grouped by lane (index order inside a lane)
   T* lens = cx + V;                // vehicle lengths (static; one LDS instead of two indexed LDCs)
-  int* ls = reinterpret_cast<int*>(lens + V);
+  T* redT = lens + V;              // W > 1: per-warp partial sums
+  int* ls = reinterpret_cast<int*>(redT + 16);
   int* ld = ls + V;
   int* cidx = ld + V;              // vehicle index of every entry of cx
-  int* loff = cidx + V;            // lane l occupies entries [loff[l], loff[l+1])
+  int* rq_i = cidx + V;            // W > 1: lane-change requests of this step (vehicle, target)
+  int* rq_t = rq_i + V;
+  int* loff = rq_t + V;            // lane l occupies entries [loff[l], loff[l+1])
+  int* rq_n = loff + 16;
+  int* wcnt = rq_n + 8;            // W > 1: members of lane l in slot s of warp w
+
+  auto grp_sync = [&]() { if (W == 1) __syncwarp(); else __syncthreads(); };
+  // sums over the env's threads (W > 1: warp tree, then the W partials in warp order)
+  auto grp_sum4 = [&](T& a0, T& a1, T& a2, T& a3) {
+    for (int o = 16; o > 0; o >>= 1) {
+      a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+      a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+      a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+      a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+    }
+    if (W > 1) {
+      if (lane_id == 0) { redT[wid] = a0; redT[4 + wid] = a1; redT[8 + wid] = a2; redT[12 + wid] = a3; }
+      __syncthreads();
+      a0 = redT[0]; a1 = redT[4]; a2 = redT[8]; a3 = redT[12];
+      for (int w = 1; w < W; ++w) { a0 += redT[w]; a1 += redT[4 + w]; a2 += redT[8 + w]; a3 += redT[12 + w]; }
+      __syncthreads();
+    }
+  };
+  auto grp_any = [&](bool p) -> bool {
+    if (W == 1) return __any_sync(0xffffffffu, p);
+    return __syncthreads_or(p ? 1 : 0) != 0;
+  };
+  auto grp_count = [&](int n) -> int {   // sum of small per-thread counts
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if (W > 1) {
+      if (lane_id == 0) rq_n[1 + wid] = n;
+      __syncthreads();
+      n = 0;
+      for (int w = 0; w < W; ++w) n += rq_n[1 + w];
+      __syncthreads();
+    }
+    return n;
+  };
 
   T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS];
   int ln[SLOTS], lead[SLOTS], foll[SLOTS];
@@ -76,7 +127,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   const size_t eo = (size_t)e * V;
 #pragma unroll
   for (int s = 0; s < SLOTS; ++s) {
-    const int i = lane_id + 32 * s;
+    const int i = tid + NT * s;
     const bool ok = i < V;
     if (ok) lens[i] = cfg.types[cfg.type_of[i]].length;
     x[s] = ok ? B.pos[eo + i] : T(0);
@@ -85,14 +136,15 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
     acc[s] = T(0); foll[s] = -1;
   }
 
+  if (W > 1 && tid == 0) rq_n[0] = 0;
   auto publish = [&]() {
-    __syncwarp();
+    grp_sync();
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {
-      const int i = lane_id + 32 * s;
+      const int i = tid + NT * s;
       if (i < V) { xs[i] = x[s]; vs[i] = v[s]; ls[i] = ln[s]; }
     }
-    __syncwarp();
+    grp_sync();
   };
   // k.update: nearest same-lane vehicle ahead; ties -> lowest index (oracle order).
   // The warp first groups the vehicles by lane (ballot compaction, index order kept), so a
@@ -100,13 +152,13 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   const unsigned lt_mask = (1u << lane_id) - 1u;
   auto update = [&](bool need_followers) {
     publish();
-    {
+    if (W == 1) {
       int base = 0;
       for (int l = 0; l < L; ++l) {
         if (lane_id == 0) loff[l] = base;
 #pragma unroll
         for (int s = 0; s < SLOTS; ++s) {
-          const int i = lane_id + 32 * s;
+          const int i = tid + NT * s;
           const bool m = i < V && ln[s] == l;
           const unsigned b = __ballot_sync(0xffffffffu, m);
           if (m) { const int p = base + __popc(b & lt_mask); cidx[p] = i; cx[p] = x[s]; }
@@ -115,10 +167,40 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       }
       if (lane_id == 0) loff[L] = base;
       __syncwarp();
+    } else {
+      // members of lane l in (slot s, warp w), then exclusive offsets in (l, s, w) order,
+      // which is index order inside a lane (i = lane + 32 w + 32 W s)
+      int rk[SLOTS];
+      for (int l = 0; l < L; ++l) {
+#pragma unroll
+        for (int s = 0; s < SLOTS; ++s) {
+          const bool m = tid + NT * s < V && ln[s] == l;
+          const unsigned b = __ballot_sync(0xffffffffu, m);
+          if (m) rk[s] = __popc(b & lt_mask);
+          if (lane_id == 0) wcnt[(l * SLOTS + s) * W + wid] = __popc(b);
+        }
+      }
+      __syncthreads();
+      if (tid <= L) {
+        int base = 0;
+        for (int q = 0; q < tid * SLOTS * W; ++q) base += wcnt[q];
+        loff[tid] = base;
+      }
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) {
+        const int i = tid + NT * s;
+        if (i < V) {
+          const int mine_q = (ln[s] * SLOTS + s) * W + wid;
+          int p = rk[s];
+          for (int q = 0; q < mine_q; ++q) p += wcnt[q];
+          cidx[p] = i; cx[p] = x[s];
+        }
+      }
+      __syncthreads();
     }
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {
-      const int i = lane_id + 32 * s;
+      const int i = tid + NT * s;
       T best = T(0); int bj = -1;
       if (i < V) {
         const int p1 = loff[ln[s] + 1];
@@ -134,16 +216,16 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       h[s] = (bj >= 0) ? best - lens[bj] : T(1000);
     }
     if (need_followers) {  // vehicle/traci.py:243-250: closest vehicle that calls me leader
-      __syncwarp();
+      grp_sync();
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
-        const int i = lane_id + 32 * s;
+        const int i = tid + NT * s;
         if (i < V) { ld[i] = lead[s]; hs[i] = h[s]; }
       }
-      __syncwarp();
+      grp_sync();
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
-        const int i = lane_id + 32 * s;
+        const int i = tid + NT * s;
         int f = -1; T fh = T(0);
         if (i < V) {   // only a vehicle of my lane can call me leader
           const int p1 = loff[ln[s] + 1];
@@ -172,7 +254,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   int last_lc[SLOTS];
 #pragma unroll
   for (int s = 0; s < SLOTS; ++s) {
-    const int i = lane_id + 32 * s;
+    const int i = tid + NT * s;
     last_lc[s] = (i < V) ? B.last_lc[eo + i] : 0;
   }
   T max_cost;
@@ -205,17 +287,17 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       const bool fixed = !B.lc_bug_compat;
       const int nb = 4 * cfg.n_rl * L;
       const int n_blk = fixed ? cfg.n_rl : 1;
-      for (int q = 4 * L * n_blk + lane_id; q < nb; q += 32) {
+      for (int q = 4 * L * n_blk + tid; q < nb; q += NT) {
         if (o) o[q] = T(0);
         if (ol) ol[q] = T(0);
       }
-      for (int r = lane_id; r < n_blk; r += 32) {
+      for (int r = tid; r < n_blk; r += NT) {
         const T sp = vs[rl_vehicle(r)];
         const T ego = fixed ? N::div(sp, cfg.speed_limit) : sp;
         if (o) o[nb + r] = ego;
         if (ol) ol[nb + r] = ego;
       }
-      for (int q = lane_id; q < n_blk * L; q += 32) {
+      for (int q = tid; q < n_blk * L; q += NT) {
         const int r = q / L, lq = q - r * L;
         const int me = rl_vehicle(r);
         const T p = xs[me];
@@ -248,7 +330,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
     // LaneChangeAccelEnv.get_state (lane_change_accel.py:114-130) / AccelEnv.get_state
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {
-      const int i = lane_id + 32 * s;
+      const int i = tid + NT * s;
       if (i >= V) continue;
       const T a0 = N::div(v[s], cfg.speed_limit), a1 = N::div(x[s], C);
       const T a2 = N::div(T(ln[s]), T(L));
@@ -263,7 +345,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
   auto fetch_actions = [&](int k) {
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {
-      const int i = lane_id + 32 * s;
+      const int i = tid + NT * s;
       nxt_a[s] = T(0); nxt_d[s] = T(0);
       if (have_act && i < V && cfg.rl_index[i] >= 0) {
         const int slot = cfg.rl_index[i];
@@ -285,8 +367,9 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       if (cfg.any_follower & 2) {
         T sm = T(0);
 #pragma unroll
-        for (int s = 0; s < SLOTS; ++s) if (lane_id + 32 * s < V) sm = add(sm, v[s]);
-        for (int o = 16; o > 0; o >>= 1) sm += __shfl_xor_sync(0xffffffffu, sm, o);
+        for (int s = 0; s < SLOTS; ++s) if (tid + NT * s < V) sm = add(sm, v[s]);
+        T z1 = T(0), z2 = T(0), z3 = T(0);
+        grp_sum4(sm, z1, z2, z3);
         mean_v = N::div(sm, T(V));
       }
       int new_ln[SLOTS];
@@ -299,7 +382,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
         // thread tests its share of the target lane's members (pre-move lane lists).
 #pragma unroll
         for (int s = 0; s < SLOTS; ++s) {
-          const int i = lane_id + 32 * s;
+          const int i = tid + NT * s;
           int target = -1;
           T len_i = T(0);
           if (i < V && cfg.rl_index[i] >= 0) {
@@ -313,6 +396,10 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
             t = t < 0 ? 0 : (t > L - 1 ? L - 1 : t);
             if (t != ln[s]) target = t;
             len_i = lens[i];
+          }
+          if (W > 1) {   // block-wide: queue the request, checked below by all W warps
+            if (target >= 0) { const int q = atomicAdd(rq_n, 1); rq_i[q] = i; rq_t[q] = target; }
+            continue;
           }
           unsigned req = __ballot_sync(0xffffffffu, target >= 0);
           while (req) {
@@ -331,15 +418,46 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
             if (lane_id == src && ok) { new_ln[s] = t; last_lc[s] = tc + 1; }
           }
         }
+        if (W > 1) {
+          __syncthreads();
+          const int n_req = rq_n[0];
+          for (int r = 0; r < n_req; ++r) {   // requests are independent: all read pre-move lists
+            const int i = rq_i[r], t = rq_t[r];
+            const T xi = xs[i], li = lens[i];
+            const int p1 = loff[t + 1];
+            bool bad = false;
+            for (int p = loff[t] + tid; p < p1; p += NT) {
+              const T fwd = fwd_dist(cx[p], xi, C), back = fwd_dist(xi, cx[p], C);
+              bad |= fwd - lens[cidx[p]] < T(0) || back - li < T(0);
+            }
+            const bool ok = !grp_any(bad);
+#pragma unroll
+            for (int s = 0; s < SLOTS; ++s)
+              if (ok && tid + NT * s == i) { new_ln[s] = t; last_lc[s] = tc + 1; }
+          }
+          __syncthreads();
+          if (tid == 0) rq_n[0] = 0;
+        }
       }
       T zn[SLOTS > 4 ? 8 : 4];
       if (cfg.any_noise) {   // one Philox call = four normals = the thread's first four slots
-        normal4<T>(cfg.seed, gid, lane_id, tc + episode * 1000003, zn);
-        if (SLOTS > 4) normal4<T>(cfg.seed, gid, lane_id + 32, tc + episode * 1000003, zn + 4);
+        if (W == 1) {
+          normal4<T>(cfg.seed, gid, lane_id, tc + episode * 1000003, zn);
+          if (SLOTS > 4) normal4<T>(cfg.seed, gid, lane_id + 32, tc + episode * 1000003, zn + 4);
+        } else {
+          // the same stream whatever W: vehicle i draws output (i >> 5) & 3 of call (i & 31) + 32 (i >> 7)
+#pragma unroll
+          for (int s = 0; s < SLOTS; ++s) {
+            const int i = tid + NT * s;
+            T z4[4];
+            normal4<T>(cfg.seed, gid, (i & 31) + 32 * (i >> 7), tc + episode * 1000003, z4);
+            zn[s] = z4[(i >> 5) & 3];
+          }
+        }
       }
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
-        const int i = lane_id + 32 * s;
+        const int i = tid + NT * s;
         if (i >= V) continue;
         const TypeP<T>& tp = cfg.types[cfg.type_of[i]];
         const int ctrl = tp.ctrl;
@@ -380,7 +498,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       // all reads of the published pre-move state are done; move
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
-        if (lane_id + 32 * s >= V) continue;
+        if (tid + NT * s >= V) continue;
         const T vn = N::max(add(v[s], mul(acc[s], dt)), T(0));
         x[s] = wrap_fwd(add(x[s], move_dist<T>(v[s], vn, dt, cfg.ballistic)), C);
         v[s] = vn;
@@ -391,7 +509,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       T sv = T(0), sq = T(0), s2 = T(0);
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
-        const int i = lane_id + 32 * s;
+        const int i = tid + NT * s;
         if (i >= V) continue;
         if (cfg.collision_min_gap)
           cr |= lead[s] >= 0 && h[s] < cfg.types[cfg.type_of[lead[s]]].sim_min_gap;
@@ -402,13 +520,8 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
         sq = add(sq, mul(d, d));
         s2 += v[s] * v[s];
       }
-      for (int o = 16; o > 0; o >>= 1) {
-        sv += __shfl_xor_sync(0xffffffffu, sv, o);
-        sq += __shfl_xor_sync(0xffffffffu, sq, o);
-        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-        act_abs_sum += __shfl_xor_sync(0xffffffffu, act_abs_sum, o);
-      }
-      crash = __any_sync(0xffffffffu, cr);
+      grp_sum4(sv, sq, s2, act_abs_sum);
+      crash = grp_any(cr);
       tc += 1;
       done = crash || tc >= t_end;
       if (cfg.env_kind == FS_ENV_WAVE_ATTENUATION || cfg.env_kind == FS_ENV_WAVE_ATTENUATION_PO) {
@@ -432,17 +545,17 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
           int pen = 0;
 #pragma unroll
           for (int s = 0; s < SLOTS; ++s) {
-            const int i = lane_id + 32 * s;
+            const int i = tid + NT * s;
             if (i < V && cfg.rl_index[i] >= 0) {
               const T last = B.lc_bug_compat ? h[s] : T(last_lc[s]);
               pen += (last == T(tc)) ? 1 : 0;
             }
           }
-          for (int o = 16; o > 0; o >>= 1) pen += __shfl_xor_sync(0xffffffffu, pen, o);
+          pen = grp_count(pen);
           for (int q = 0; q < pen; ++q) reward = reward - T(0.1);
         }
       }
-      if (A.accumulate_stats && lane_id == 0) {
+      if (A.accumulate_stats && tid == 0) {
         st_rew += (double)reward; st_v += (double)sv; st_v2 += (double)s2;
         st_vs += V; st_es += 1; st_cr += crash ? 1 : 0;
       }
@@ -453,7 +566,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
     if (A.obs_seq != nullptr || last)
       write_obs(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
                 last ? B.obs + (size_t)e * cfg.obs_dim : nullptr);
-    if (lane_id == 0) {
+    if (tid == 0) {
       if (A.reward_seq) A.reward_seq[(size_t)k * E + e] = reward;
       if (A.done_seq) A.done_seq[(size_t)k * E + e] = done ? 1 : 0;
     }
@@ -461,7 +574,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
 
 #pragma unroll
   for (int s = 0; s < SLOTS; ++s) {
-    const int i = lane_id + 32 * s;
+    const int i = tid + NT * s;
     if (i >= V) continue;
     B.pos[eo + i] = x[s]; B.vel[eo + i] = v[s]; B.lane[eo + i] = (uint8_t)ln[s];
     B.last_lc[eo + i] = last_lc[s];
@@ -470,7 +583,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       if (A.k_steps > 0) B.v_accel[eo + i] = acc[s];
     }
   }
-  if (lane_id == 0) {
+  if (tid == 0) {
     B.time_counter[e] = tc;
     B.done[e] = done ? 1 : 0;
     B.crash[e] = crash ? 1 : 0;

@@ -219,3 +219,29 @@ def test_multilane_known_answers_of_the_reference_test():
     np.testing.assert_allclose(obs[0:3], [27.85714285714286, -5, -5], rtol=1e-13)
     np.testing.assert_array_almost_equal(obs[3:6], [28.577143] * 3)
     assert (obs[6:] == 0).all()                     # everyone at rest, other blocks untouched
+
+
+def test_block_per_env_mapping_gives_the_same_results(monkeypatch):
+    """FS_ML_SPLIT=1 (W warps per env, block collectives) against the default one-warp-per-env
+    mapping on c3 with noise: identical lanes, positions and rewards in fp64."""
+    import torch
+    from flow_b200 import workloads as W
+    from flow_b200.vec_env import B200VecEnv
+    types, tov, kw = W.ring_c3(noise=0.2)
+    E, K = 33, 60
+    gen = torch.Generator(device='cuda'); gen.manual_seed(3)
+    act = torch.rand(K, 6, E, device='cuda', dtype=torch.float64, generator=gen) * 0.6 - 0.4
+    act[:, 1::2] = torch.round(act[:, 1::2] * 2.4 + 1.0).clamp(-1, 1)
+    out = []
+    for split in ('0', '1'):
+        monkeypatch.setenv('FS_ML_SPLIT', split)
+        env = B200VecEnv(types, tov, E, dtype='f64', seed=5, **kw)
+        env.reset()
+        rew = torch.empty(K, E, device='cuda', dtype=torch.float64)
+        obs = torch.empty(K, E, env.obs_dim, device='cuda', dtype=torch.float64)
+        env.rollout(act, obs, rew)
+        out.append((obs.cpu().numpy(), rew.cpu().numpy(), env.engine.lane.cpu().numpy(),
+                    env.engine.pos.cpu().numpy()))
+    assert np.array_equal(out[0][2], out[1][2])
+    assert close(out[0][3], out[1][3]) <= 1e-12 and close(out[0][0], out[1][0]) <= 1e-12
+    assert close(out[0][1], out[1][1]) <= 1e-12
