@@ -15,6 +15,12 @@ What is restated from the reference (pinned, see tests/golden/):
   WaveAttenuation reward  flow/envs/ring/wave_attenuation.py:113-139
   WaveAttenuationPO obs   flow/envs/ring/wave_attenuation.py:248-269
   Accel/WaveAtt full obs  flow/envs/ring/accel.py:116-123
+  sorted_ids / abs. pos.  flow/envs/ring/accel.py:100-183
+  LaneChangeAccel(PO)Env  flow/envs/ring/lane_change_accel.py:100-263
+  per-lane neighbours     flow/core/kernel/vehicle/traci.py:699-937
+  multi-agent fronts      flow/envs/multiagent/ring/wave_attenuation.py:195-247,
+                          flow/envs/multiagent/ring/accel.py:154-206
+  sims_per_step, evaluate flow/envs/base.py:325-383, flow/envs/ring/accel.py:109-114
 
 What stands in for SUMO (third-party C++, not in /root/reference; pinned only
 by tests/fast_tests/test_files/ring_230_emission.csv for the first steps,
@@ -25,7 +31,9 @@ otherwise "parity unpinned"):
   * Euler move x' = (x + v'*dt) mod C with v' = the commanded speed;
   * leader = next vehicle ahead in the same lane, headway = front-to-front
     distance mod C minus the leader's length; alone in lane -> none / 1000;
-  * collision <=> some headway < 0 after the move;
+  * collision <=> some headway < 0 after the move, or (single lane) a vehicle went through
+    its leader inside the step;
+  * SumoParams(use_ballistic=True): x' = x + (v + v')/2 * dt;
   * vehicles without a command (RL vehicle when rl_actions is None,
     SimCarFollowingController) follow IDM with their SumoCarFollowingParams.
 """
