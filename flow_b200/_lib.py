@@ -54,7 +54,25 @@ class FsConfig(C.Structure):
                 ('inflow_type', C.c_int32), ('collision_min_gap', C.c_int32),
                 ('record_views', C.c_int32), ('lc_corrected', C.c_int32),
                 ('n_initial', C.c_int32), ('env_flags', C.c_int32),
-                ('inflow_begin', C.c_double)]
+                ('inflow_begin', C.c_double),
+                ('max_agents', C.c_int32), ('reserved0', C.c_int32)]
+
+
+FS_ABI_VERSION = 2
+FS_MAX_INFLOWS = 4
+
+
+class FsInflow(C.Structure):
+    _fields_ = [('vtype', C.c_int32), ('reserved', C.c_int32),
+                ('vehs_per_hour', C.c_double), ('depart_speed', C.c_double),
+                ('begin', C.c_double)]
+
+
+class FsAgentViews(C.Structure):
+    _fields_ = [('agent_obs', C.c_void_p), ('agent_reward', C.c_void_p),
+                ('agent_id', C.c_void_p), ('veh_id', C.c_void_p),
+                ('veh_type', C.c_void_p),
+                ('max_agents', C.c_int32), ('obs_per_agent', C.c_int32)]
 
 
 class FsViews(C.Structure):
@@ -91,6 +109,8 @@ SYMBOLS = [
     ('fs_stream', C.c_void_p, [C.c_void_p]),
     ('fs_launch_count', C.c_int64, [C.c_void_p]),
     ('fs_set_stream', C.c_int, [C.c_void_p, C.c_void_p]),
+    ('fs_set_inflows', C.c_int, [C.c_void_p, C.POINTER(FsInflow), C.c_int]),
+    ('fs_agents', C.c_int, [C.c_void_p, C.POINTER(FsAgentViews)]),
 ]
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
@@ -158,7 +178,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype = restype
         fn.argtypes = argtypes
-    if lib.fs_abi_version() != 1:
+    if lib.fs_abi_version() != FS_ABI_VERSION:
         raise RuntimeError('libflowstep ABI version mismatch')
     _lib = lib
     return lib

@@ -46,8 +46,16 @@ struct fs_engine {
   uint8_t *lane = nullptr, *active = nullptr, *done = nullptr, *crash = nullptr, *mask = nullptr;
   int *time_counter = nullptr, *episode = nullptr, *leader = nullptr, *follower = nullptr;
   int* last_lc = nullptr;
-  int* counters = nullptr;   // highway: [4][E] in network, departed, arrived, spawned
+  int* counters = nullptr;   // highway: [3 + FS_MAX_INFLOWS][E] in network, departed, arrived, emitted per inflow
   uint8_t* vtype = nullptr;  // highway: [E][CAP] type of the vehicle in each slot
+  // highway inflows (fs_set_inflows; flow 0 defaults to the one in fs_config)
+  int n_flows = 0;
+  fs_inflow flows[FS_MAX_INFLOWS] = {};
+  // FS_ENV_MA_HIGHWAY_PO
+  int* veh_id = nullptr;       // [E][CAP]
+  int* agent_id = nullptr;     // [E][A]
+  void* agent_reward = nullptr;  // T [E][A]
+  bool ma_highway() const { return cfg.env_kind == FS_ENV_MA_HIGHWAY_PO; }
   bool env_major = false;  // pos/vel/lane stored [E][V] (multi-lane, highway)
   // FS_ENVF_SORT_VEHICLES (fs_sort.cuh): keys [E][V], their validity [E], permuted actions [A][E]
   void *abs_pos = nullptr, *prev_pos = nullptr, *act_sorted = nullptr;
@@ -128,6 +136,9 @@ static int obs_dim_for(const fs_config& c) {
     case FS_ENV_LANE_CHANGE_ACCEL_PO:   // capacity; 4 * n_rl * n_lanes + (1 | n_rl) after fs_set_types
       return c.topology == FS_TOPO_RING ? 4 * c.n_veh * c.n_lanes + c.n_veh : -1;
     case FS_ENV_HIGHWAY: return 2 * c.n_veh;
+    case FS_ENV_MA_HIGHWAY_PO:
+      return c.topology == FS_TOPO_HIGHWAY && c.max_agents >= 1 && c.max_agents <= c.n_veh
+                 ? 5 * c.max_agents : -1;
     case FS_ENV_MA_WAVE_ATTENUATION_PO: return 3 * c.n_veh;  // capacity; 3 * n_rl after fs_set_types
     case FS_ENV_MA_ACCEL_PO:                                  // capacity; 6 * n_rl after fs_set_types
       return c.topology == FS_TOPO_RING && c.n_lanes == 1 ? 6 * c.n_veh : -1;
@@ -191,7 +202,18 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY;
   if (e->env_major) A(&e->last_lc, V * E * 4);
   if (e->sort_on()) { A(&e->abs_pos, V * E * ts); A(&e->prev_pos, V * E * ts); A(&e->keys_valid, E); }
-  if (cfg->topology == FS_TOPO_HIGHWAY) { A(&e->counters, 4 * E * 4); A(&e->vtype, V * E); }
+  if (cfg->topology == FS_TOPO_HIGHWAY) {
+    A(&e->counters, (3 + FS_MAX_INFLOWS) * E * 4); A(&e->vtype, V * E);
+    if (cfg->inflow_vehs_per_hour > 0) {
+      e->n_flows = 1;
+      e->flows[0].vtype = cfg->inflow_type; e->flows[0].vehs_per_hour = cfg->inflow_vehs_per_hour;
+      e->flows[0].depart_speed = cfg->inflow_depart_speed; e->flows[0].begin = cfg->inflow_begin;
+    }
+  }
+  if (e->ma_highway()) {
+    A(&e->veh_id, V * E * 4); A(&e->agent_id, E * (size_t)cfg->max_agents * 4);
+    A(&e->agent_reward, E * (size_t)cfg->max_agents * ts);
+  }
   if (cfg->record_views) {
     A(&e->headway, V * E * ts); A(&e->accel, V * E * ts);
     A(&e->leader, V * E * 4); A(&e->follower, V * E * 4);
@@ -291,6 +313,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
   if (g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO) {
     e->obs_dim = 4 * n_rl * g.n_lanes + (g.lc_corrected ? n_rl : 1); c.obs_dim = e->obs_dim;
   }
+  if (g.env_kind == FS_ENV_MA_HIGHWAY_PO) c.act_dim = g.max_agents;  // one action row per agent row
   e->n_rl = n_rl;
   e->act_dim = c.act_dim;
 }
@@ -362,9 +385,10 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
       return fail(e, FS_EINVAL, "fs_set_types: inflow_type out of range");
     for (int t = 0; t < n_types; ++t) {
       const int c = types[t].controller;
-      if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC || c == FS_CTRL_RL)
-        return fail(e, FS_EINVAL, "fs_set_types: PISaturation / LAC / RL vehicles are not "
-                                  "supported on the highway topology (slots are re-packed)");
+      if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC || (c == FS_CTRL_RL && !e->ma_highway()))
+        return fail(e, FS_EINVAL, "fs_set_types: PISaturation / LAC vehicles are not supported on the "
+                                  "highway topology (slots are re-packed); RL vehicles need "
+                                  "FS_ENV_MA_HIGHWAY_PO");
     }
   }
   if (e->f64) fill_cfg<double>(e, e->cd, types, n_types, type_of_vehicle);
@@ -475,10 +499,17 @@ static fs::HwBufs<T> hw_bufs(fs_engine* e) {
   b.obs = (T*)e->obs; b.reward = (T*)e->reward;
   b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
   b.v_leader = e->leader; b.v_follower = e->follower; b.stats = e->stats;
-  b.period = e->cfg.inflow_vehs_per_hour > 0 ? 3600.0 / e->cfg.inflow_vehs_per_hour : 0.0;
-  b.begin = e->cfg.inflow_begin;
-  b.depart_speed = (T)e->cfg.inflow_depart_speed;
-  b.inflow_type = e->cfg.inflow_type;
+  b.n_flows = e->n_flows;
+  for (int f = 0; f < FS_MAX_INFLOWS; ++f) {
+    const fs_inflow& q = e->flows[f];
+    const bool on = f < e->n_flows && q.vehs_per_hour > 0;
+    b.period[f] = on ? 3600.0 / q.vehs_per_hour : 0.0;
+    b.begin[f] = on ? q.begin : 0.0;
+    b.depart_speed[f] = on ? (T)q.depart_speed : T(0);
+    b.inflow_type[f] = on ? q.vtype : 0;
+  }
+  b.vid = e->veh_id; b.agent_reward = (T*)e->agent_reward; b.agent_id = e->agent_id;
+  b.max_agents = e->ma_highway() ? e->cfg.max_agents : 0;
   return b;
 }
 
@@ -487,11 +518,15 @@ static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
   const int E = e->cfg.n_envs, CAP = e->cfg.n_veh;
   const int wpb = E <= 148 * 8 ? 1 : 4;
   const int grid = (E + wpb - 1) / wpb;
-  const size_t smem = (size_t)wpb * CAP * (3 * sizeof(T) + sizeof(int));
+  const size_t smem = (size_t)wpb * fs::hw_smem_per_warp<T>(CAP);
   const fs::HwBufs<T> b = hw_bufs<T>(e);
-  if (CAP <= 64) fs::highway_kernel<T, 2><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  else if (CAP <= 160) fs::highway_kernel<T, 5><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  else fs::highway_kernel<T, 8><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  if (e->ma_highway()) {
+    if (CAP <= 64) fs::highway_kernel<T, 2, true><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else if (CAP <= 160) fs::highway_kernel<T, 5, true><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else fs::highway_kernel<T, 8, true><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  } else if (CAP <= 64) fs::highway_kernel<T, 2, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  else if (CAP <= 160) fs::highway_kernel<T, 5, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+  else fs::highway_kernel<T, 8, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   return FS_OK;
@@ -705,6 +740,38 @@ static int check_room(fs_engine* e, double L) {
   const double dist = edge_len > min_gap + 5.0 ? (hw ? 1 : 4) * edge_len * ld : 0.0;
   if (dist - ld * bunching - (hw ? g.n_initial : g.n_veh) * (min_gap + 5.0) < 0)
     return fail(e, FS_EINVAL, "There is not enough space to place all vehicles in the network.");
+  return FS_OK;
+}
+
+extern "C" int fs_set_inflows(fs_engine* e, const fs_inflow* flows, int n_flows) {
+  if (!e) return FS_EINVAL;
+  if (e->cfg.topology != FS_TOPO_HIGHWAY)
+    return fail(e, FS_EINVAL, "fs_set_inflows: inflows exist on the highway topology only");
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_set_inflows: call fs_set_types first");
+  if (n_flows < 0 || n_flows > FS_MAX_INFLOWS || (n_flows > 0 && !flows))
+    return fail(e, FS_EINVAL, "fs_set_inflows: 0..4 flows");
+  const int n_types = e->f64 ? e->cd.n_types : e->cf.n_types;
+  for (int f = 0; f < n_flows; ++f) {
+    if (flows[f].vtype < 0 || flows[f].vtype >= n_types)
+      return fail(e, FS_EINVAL, "fs_set_inflows: vtype out of range");
+    if (!(flows[f].vehs_per_hour > 0) || !(flows[f].depart_speed >= 0) || !(flows[f].begin >= 0))
+      return fail(e, FS_EINVAL, "fs_set_inflows: vehs_per_hour > 0, depart_speed >= 0, begin >= 0");
+    const fs::TypeP<double>* td = e->f64 ? &e->cd.types[flows[f].vtype] : nullptr;
+    const int ctrl = td ? td->ctrl : e->cf.types[flows[f].vtype].ctrl;
+    if (ctrl == FS_CTRL_RL && !e->ma_highway())
+      return fail(e, FS_EINVAL, "fs_set_inflows: an RL inflow needs FS_ENV_MA_HIGHWAY_PO");
+  }
+  e->n_flows = n_flows;
+  for (int f = 0; f < FS_MAX_INFLOWS; ++f) e->flows[f] = f < n_flows ? flows[f] : fs_inflow{};
+  return FS_OK;
+}
+
+extern "C" int fs_agents(fs_engine* e, fs_agent_views* out) {
+  if (!e || !out) return FS_EINVAL;
+  if (!e->ma_highway()) return fail(e, FS_EINVAL, "fs_agents: FS_ENV_MA_HIGHWAY_PO only");
+  out->agent_obs = e->obs; out->agent_reward = e->agent_reward; out->agent_id = e->agent_id;
+  out->veh_id = e->veh_id; out->veh_type = e->vtype;
+  out->max_agents = e->cfg.max_agents; out->obs_per_agent = 5;
   return FS_OK;
 }
 

@@ -15,7 +15,15 @@
 //                                        flow/core/params.py:1080-1213
 //   no-leader headway 1000               flow/core/kernel/vehicle/traci.py:234-238
 //   desired_velocity over present vehicles  flow/core/rewards.py:6-59
+//   MultiAgentHighwayPOEnv (kMA)        flow/envs/multiagent/highway.py:97-196,
+//                                       flow/envs/multiagent/base.py:116-225
 // SUMO's insertion / arrival rules have no reference fixture: parity unpinned.
+//
+// kMA = true (FS_ENV_MA_HIGHWAY_PO): RL vehicles may enter through an inflow, so
+// every vehicle carries a persistent id through the compaction, the RL vehicles
+// present are ranked from the downstream end by ballot + popc each step
+// (rank a <-> action row a <-> observation row a), and each agent gets its own
+// observation row and reward.
 #pragma once
 #include "fs_common.cuh"
 #include "fs_ring.cuh"
@@ -26,18 +34,30 @@ template <typename T>
 struct HwBufs {
   T* pos; T* vel; uint8_t* vtype; uint8_t* active;   // [E][CAP]
   T* length;                                         // [E] edge length
-  int* n_active; int* departed; int* arrived; int* spawned;  // [E]
+  int* n_active; int* departed; int* arrived;  // [E]
+  int* spawned;                                // [FS_MAX_INFLOWS][E] vehicles emitted per inflow
   int* time_counter; int* episode;
   uint8_t* done; uint8_t* crash;
   T* obs; T* reward;
   T* v_accel; T* v_headway; int* v_leader; int* v_follower;  // views [E][CAP] or null
   double* stats;
-  double period, begin;   // s
-  T depart_speed;
-  int inflow_type;
+  int n_flows;
+  double period[FS_MAX_INFLOWS], begin[FS_MAX_INFLOWS];   // s
+  T depart_speed[FS_MAX_INFLOWS];
+  int inflow_type[FS_MAX_INFLOWS];
+  // multi-agent front (kMA)
+  int* vid;            // [E][CAP] persistent vehicle id
+  T* agent_reward;     // [E][A]
+  int* agent_id;       // [E][A]
+  int max_agents;
 };
 
-template <typename T, int SLOTS>
+template <typename T>
+__host__ __device__ inline size_t hw_smem_per_warp(int cap) {
+  return (size_t)cap * (3 * sizeof(T) + 2 * sizeof(int));
+}
+
+template <typename T, int SLOTS, bool kMA>
 __global__ void __launch_bounds__(128)
 highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -47,15 +67,16 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   const int e = blockIdx.x * (blockDim.x >> 5) + wib;
   if (e >= E) return;
   if (A.mask != nullptr && A.mask[e] == 0) return;
-  const size_t per_warp = (size_t)CAP * (3 * sizeof(T) + sizeof(int));
-  unsigned char* mine = smem_raw + per_warp * wib;
+  unsigned char* mine = smem_raw + hw_smem_per_warp<T>(CAP) * wib;
   T* xs = reinterpret_cast<T*>(mine);
   T* vs = xs + CAP;
   T* hs = vs + CAP;
   int* ts = reinterpret_cast<int*>(hs + CAP);
+  int* is = ts + CAP;   // vehicle ids during the compaction (kMA)
 
   T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS];
   int ty[SLOTS];
+  int id[kMA ? SLOTS : 1], rank[kMA ? SLOTS : 1];
   const size_t eo = (size_t)e * CAP;
   int n = B.n_active[e];
 #pragma unroll
@@ -66,7 +87,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     v[r] = ok ? B.vel[eo + s] : T(0);
     ty[r] = ok ? (int)B.vtype[eo + s] : 0;
     acc[r] = T(0);
+    if (kMA) id[r] = ok ? B.vid[eo + s] : -1;
   }
+  const int AG = kMA ? B.max_agents : 0;
+  int n_rl = 0;
   const T Lr = B.length[e];
   const T dt = cfg.dt;
   int tc = B.time_counter[e];
@@ -76,7 +100,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   const int t_end = cfg.sims_per_step * (cfg.warmup_steps + cfg.horizon);
   const long long gid = cfg.env_id_base + e;
   T reward = B.reward[e];
-  int spawned = B.spawned[e], departed = B.departed[e], arrived = B.arrived[e];
+  int departed = B.departed[e], arrived = B.arrived[e];
+  int spawned[FS_MAX_INFLOWS];
+#pragma unroll
+  for (int f = 0; f < FS_MAX_INFLOWS; ++f) spawned[f] = f < B.n_flows ? B.spawned[(size_t)f * E + e] : 0;
   double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
 
   auto publish = [&]() {
@@ -105,7 +132,80 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   };
   update();
 
+  // RL vehicles present, ranked head first: rank a <-> action row a <-> observation row a
+  auto rank_agents = [&]() {
+    if (!kMA) return;
+    n_rl = 0;
+#pragma unroll
+    for (int r = 0; r < SLOTS; ++r) {
+      const int s = lane_id + 32 * r;
+      const bool rl = s < n && cfg.types[ty[r]].ctrl == FS_CTRL_RL;
+      const unsigned m = __ballot_sync(0xffffffffu, rl);
+      rank[kMA ? r : 0] = rl ? n_rl + __popc(m & ((1u << lane_id) - 1u)) : -1;
+      n_rl += __popc(m);
+    }
+  };
+  rank_agents();
+  // MultiAgentHighwayPOEnv.get_state / compute_reward (multiagent/highway.py:97-172) for the
+  // agents present after the step; cost1 = rewards.desired_velocity of the whole network
+  auto write_agents = [&](T* o, T* ol, bool with_reward, T cost1, bool fail) {
+    if (!kMA) return;
+    T rsum = T(0);
+#pragma unroll
+    for (int r = 0; r < SLOTS; ++r) {
+      const int s = lane_id + 32 * r;
+      const int a = rank[kMA ? r : 0];
+      if (a < 0 || a >= AG) continue;
+      const T vi = v[r];
+      const bool has_lead = s > 0, has_f = s + 1 < n;
+      // "lead_head" is the LEADER's own headway (highway.py:118), 1000 for the head vehicle
+      const T lead_speed = has_lead ? vs[s - 1] : cfg.speed_limit;
+      const T lead_head = has_lead ? hs[s - 1] : Lr;
+      const T follow_speed = has_f ? vs[s + 1] : T(0);
+      const T follow_head = has_f ? hs[s + 1] : Lr;
+      const T q[5] = {N::div(vi, cfg.speed_limit), N::div(lead_speed - vi, cfg.speed_limit),
+                      N::div(lead_head, Lr), N::div(vi - follow_speed, cfg.speed_limit),
+                      N::div(follow_head, Lr)};
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        if (o) o[a * 5 + c] = q[c];
+        if (ol) ol[a * 5 + c] = q[c];
+      }
+      if (ol) B.agent_id[(size_t)e * AG + a] = id[kMA ? r : 0];
+      if (with_reward) {
+        T rw;
+        if (cfg.evaluate) rw = vi;
+        else if (fail) rw = T(0);
+        else {
+          T cost2 = T(0);
+          if (has_lead && vi > T(0)) {
+            const T th = N::max(N::div(h[r], vi), T(0));   // time headway, t_min = 1
+            cost2 = N::min(N::div(th - T(1), T(1)), T(0));
+          }
+          rw = N::max(add(mul(T(1), cost1), mul(T(0.1), cost2)), T(0));
+        }
+        rsum = add(rsum, rw);
+        if (ol) B.agent_reward[(size_t)e * AG + a] = rw;
+      }
+    }
+    for (int a = lane_id; a < AG; a += 32) {
+      if (a < n_rl) continue;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        if (o) o[a * 5 + c] = T(0);
+        if (ol) ol[a * 5 + c] = T(0);
+      }
+      if (ol) { B.agent_id[(size_t)e * AG + a] = -1; B.agent_reward[(size_t)e * AG + a] = T(0); }
+    }
+    if (with_reward) {   // env-level reward = mean over the agents present (statistics only)
+      for (int of = 16; of > 0; of >>= 1) rsum += __shfl_xor_sync(0xffffffffu, rsum, of);
+      const int na = n_rl < AG ? n_rl : AG;
+      reward = na > 0 ? N::div(rsum, T(na)) : T(0);
+    }
+  };
+
   auto write_obs = [&](T* o, T* ol) {
+    if (kMA) { write_agents(o, ol, false, T(0), false); return; }
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
       const int s = lane_id + 32 * r;
@@ -119,6 +219,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   if (A.k_steps == 0) write_obs(nullptr, B.obs + (size_t)e * cfg.obs_dim);
 
   for (int k = 0; k < A.k_steps; ++k) {
+    const bool done_before = done;
     if (!done) {
       T mean_v = T(0);
       if (cfg.any_follower & 2) {
@@ -141,6 +242,12 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         T st0 = T(0);
         T a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, has_f, has_f ? vs[s + 1] : T(-1001),
                             has_f ? hs[s + 1] : T(-1001), mean_v, dt, cfg.inv_dt, st0);
+        if (kMA && ctrl == FS_CTRL_RL && A.actions != nullptr && rank[kMA ? r : 0] < AG) {
+          // MultiAgentHighwayPOEnv._apply_rl_actions: apply_acceleration(rl_id, actions[0]),
+          // not clipped; NaN = this agent got no command (stays with the simulator model)
+          const T raw = A.actions[((size_t)k * cfg.act_dim + rank[kMA ? r : 0]) * E + e];
+          if (raw == raw) a = raw;
+        }
         if (ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL) {
           if (tp.noise > T(0))
             a = add(a, mul(tp.noise, normal_sample<T>(cfg.seed, gid, s, tc + episode * 1000003)));
@@ -176,20 +283,27 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         __syncwarp();
 #pragma unroll
         for (int r = 0; r < SLOTS; ++r)
-          if (dst[r] >= 0) { xs[dst[r]] = x[r]; vs[dst[r]] = v[r]; ts[dst[r]] = ty[r]; hs[dst[r]] = acc[r]; }
+          if (dst[r] >= 0) {
+            xs[dst[r]] = x[r]; vs[dst[r]] = v[r]; ts[dst[r]] = ty[r]; hs[dst[r]] = acc[r];
+            if (kMA) is[dst[r]] = id[kMA ? r : 0];
+          }
         __syncwarp();
 #pragma unroll
         for (int r = 0; r < SLOTS; ++r) {
           const int s = lane_id + 32 * r;
           if (s < n_keep) { x[r] = xs[s]; v[r] = vs[s]; ty[r] = ts[s]; acc[r] = hs[s]; }
           else { x[r] = T(0); v[r] = T(0); ty[r] = 0; acc[r] = T(0); }
+          if (kMA) id[kMA ? r : 0] = s < n_keep ? is[s] : -1;
         }
         n = n_keep;
       }
-      // inflow: at most one due vehicle per step, appended at the tail
-      if (B.period > 0.0) {
+      // inflows, in definition order: each emits at most one due vehicle per step at the
+      // tail, if the entry gap to the last vehicle allows it
+#pragma unroll
+      for (int f = 0; f < FS_MAX_INFLOWS; ++f) {
+        if (f >= B.n_flows || !(B.period[f] > 0.0)) continue;
         const double t = (double)tc * (double)cfg.dt;
-        const double due = B.begin + (double)spawned * B.period;
+        const double due = B.begin[f] + (double)spawned[f] * B.period[f];
         bool spawn = t >= due && n < CAP;
         if (spawn && n > 0) {
           const int sl = n - 1;  // last vehicle
@@ -198,13 +312,16 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
           for (int r = 0; r < SLOTS; ++r) if (lane_id + 32 * r == sl) { xl = x[r]; tl = ty[r]; }
           xl = __shfl_sync(0xffffffffu, xl, sl & 31);
           tl = __shfl_sync(0xffffffffu, tl, sl & 31);
-          spawn = (xl - cfg.types[tl].length) >= cfg.types[B.inflow_type].sim_min_gap;
+          spawn = (xl - cfg.types[tl].length) >= cfg.types[B.inflow_type[f]].sim_min_gap;
         }
         if (spawn) {
 #pragma unroll
           for (int r = 0; r < SLOTS; ++r)
-            if (lane_id + 32 * r == n) { x[r] = T(0); v[r] = B.depart_speed; ty[r] = B.inflow_type; acc[r] = T(0); }
-          n += 1; spawned += 1; departed += 1;
+            if (lane_id + 32 * r == n) {
+              x[r] = T(0); v[r] = B.depart_speed[f]; ty[r] = B.inflow_type[f]; acc[r] = T(0);
+              if (kMA) id[kMA ? r : 0] = ((f + 1) << 24) | spawned[f];
+            }
+          n += 1; spawned[f] += 1; departed += 1;
         }
       }
       update();
@@ -236,6 +353,14 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         const T max_cost = N::sqrt(mc2), cost = N::sqrt(sq);
         reward = N::div(N::max(max_cost - cost, T(0)), add(max_cost, T(1.1920928955078125e-07)));
       }
+      if (kMA) {
+        rank_agents();
+        const bool lastk = (k == A.k_steps - 1);
+        // fail = the engine's collision flag (the reference's MultiEnv zeroes it, base.py:174)
+        write_agents(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
+                     lastk ? B.obs + (size_t)e * cfg.obs_dim : nullptr, true,
+                     (crash || n == 0) ? T(0) : reward, crash);
+      }
       if (A.accumulate_stats && lane_id == 0) {
         st_rew += (double)reward; st_v += (double)sv; st_v2 += (double)s2;
         st_vs += n; st_es += 1; st_cr += crash ? 1 : 0;
@@ -244,7 +369,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       reward = T(0);
     }
     const bool last = (k == A.k_steps - 1);
-    if (A.obs_seq != nullptr || last)
+    if (kMA) {
+      if (done_before) write_obs(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
+                                 last ? B.obs + (size_t)e * cfg.obs_dim : nullptr);
+    } else if (A.obs_seq != nullptr || last)
       write_obs(A.obs_seq ? A.obs_seq + ((size_t)k * E + e) * cfg.obs_dim : nullptr,
                 last ? B.obs + (size_t)e * cfg.obs_dim : nullptr);
     if (lane_id == 0) {
@@ -259,6 +387,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     if (s >= CAP) continue;
     B.pos[eo + s] = x[r]; B.vel[eo + s] = v[r]; B.vtype[eo + s] = (uint8_t)ty[r];
     B.active[eo + s] = s < n ? 1 : 0;
+    if (kMA) B.vid[eo + s] = s < n ? id[kMA ? r : 0] : -1;
     if (A.write_views) {
       B.v_headway[eo + s] = s < n ? h[r] : T(0);
       B.v_leader[eo + s] = (s > 0 && s < n) ? s - 1 : -1;
@@ -267,7 +396,9 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     }
   }
   if (lane_id == 0) {
-    B.n_active[e] = n; B.spawned[e] = spawned; B.departed[e] = departed; B.arrived[e] = arrived;
+    B.n_active[e] = n; B.departed[e] = departed; B.arrived[e] = arrived;
+#pragma unroll
+    for (int f = 0; f < FS_MAX_INFLOWS; ++f) if (f < B.n_flows) B.spawned[(size_t)f * E + e] = spawned[f];
     B.time_counter[e] = tc;
     B.done[e] = done ? 1 : 0;
     B.crash[e] = crash ? 1 : 0;
@@ -301,14 +432,17 @@ __global__ void highway_reset_kernel(const __grid_constant__ Cfg<T> cfg, const H
       const int s = n_initial - 1 - i;
       B.pos[eo + s] = (T)x; B.vel[eo + s] = T(0);
       B.vtype[eo + s] = cfg.type_of[i]; B.active[eo + s] = 1;
+      if (B.vid) B.vid[eo + s] = i;
       x = fmod(__dadd_rn(__dadd_rn(__dadd_rn(x, increment), 5.0), min_gap), L);
     }
   }
   for (int s = n_initial; s < CAP; ++s) {
     B.pos[eo + s] = T(0); B.vel[eo + s] = T(0); B.vtype[eo + s] = 0; B.active[eo + s] = 0;
+    if (B.vid) B.vid[eo + s] = -1;
   }
   B.length[e] = (T)L;
-  B.n_active[e] = n_initial; B.departed[e] = n_initial; B.arrived[e] = 0; B.spawned[e] = 0;
+  B.n_active[e] = n_initial; B.departed[e] = n_initial; B.arrived[e] = 0;
+  for (int f = 0; f < FS_MAX_INFLOWS; ++f) B.spawned[(size_t)f * E + e] = 0;
   B.time_counter[e] = 0;
   B.episode[e] = B.episode[e] + 1;
   B.done[e] = 0; B.crash[e] = 0;

@@ -15,7 +15,7 @@ F32, F64 = 0, 1
 TOPO_RING, TOPO_HIGHWAY = 0, 1
 ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
     ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY, \
-    ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO = range(8)
+    ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO, ENV_MA_HIGHWAY_PO = range(9)
 CTRL_SIM, CTRL_IDM, CTRL_OVM, CTRL_LINEAR_OVM, CTRL_BCM, CTRL_CFM, CTRL_LAC, \
     CTRL_GIPPS, CTRL_FOLLOWER_STOPPER, CTRL_NONLOCAL_FOLLOWER_STOPPER, \
     CTRL_PI_SATURATION, CTRL_RL = range(12)
@@ -83,7 +83,7 @@ class Engine:
                  use_torch_stream=True, capacity=None, **cfg):
         self.lib = _lib.load()
         c = _lib.FsConfig()
-        c.abi_version = 1
+        c.abi_version = _lib.FS_ABI_VERSION
         c.device = device
         c.dtype = F64 if dtype in ('f64', F64, 'float64') else F32
         c.n_envs = n_envs
@@ -100,7 +100,8 @@ class Engine:
                         act_hi=2.6, obs_max_length=0.0, inflow_vehs_per_hour=0.0,
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
                         record_views=0, lc_corrected=0, n_initial=0, inflow_begin=1.0,
-                        evaluate=0, sort_vehicles=0, use_ballistic=0)
+                        evaluate=0, sort_vehicles=0, use_ballistic=0, max_agents=0)
+        inflows = cfg.pop('inflows', None)   # [(vtype, vehs_per_hour, depart_speed, begin), ...]
         unknown = set(cfg) - set(defaults)
         if unknown:
             raise TypeError('unknown engine config keys: %s' % sorted(unknown))
@@ -129,6 +130,12 @@ class Engine:
         arr = (_lib.FsVType * len(types))(*types)
         tov = np.ascontiguousarray(type_of_vehicle, dtype=np.uint8)
         self._check(self.lib.fs_set_types(self.h, arr, len(types), tov.ctypes.data))
+        if inflows is not None:
+            rows = (_lib.FsInflow * max(1, len(inflows)))()
+            for r, (vt, rate, speed, begin) in zip(rows, inflows):
+                r.vtype, r.vehs_per_hour, r.depart_speed, r.begin = \
+                    int(vt), float(rate), float(speed), float(begin)
+            self._check(self.lib.fs_set_inflows(self.h, rows, len(inflows)))
         v = _lib.FsViews()
         self._check(self.lib.fs_buffers(self.h, C.byref(v)))
         self.views = v
@@ -153,6 +160,17 @@ class Engine:
         self.done, self.crash = T(v.done, (E,), 'u8'), T(v.crash, (E,), 'u8')
         self.time_counter = T(v.time_counter, (E,), 'i32')
         self.counters = T(v.counters, (3, E), 'i32')   # highway: in network, departed, arrived
+        self.agent_obs = self.agent_reward = self.agent_id = self.veh_id = self.veh_type = None
+        if c.env_kind == ENV_MA_HIGHWAY_PO:
+            av = _lib.FsAgentViews()
+            self._check(self.lib.fs_agents(self.h, C.byref(av)))
+            A = av.max_agents
+            self.max_agents = A
+            self.agent_obs = T(av.agent_obs, (E, A, av.obs_per_agent))
+            self.agent_reward = T(av.agent_reward, (E, A))
+            self.agent_id = T(av.agent_id, (E, A), 'i32')
+            self.veh_id = T(av.veh_id, (E, V), 'i32')       # per highway slot, head first
+            self.veh_type = T(av.veh_type, (E, V), 'u8')
         self._fs_step = self.lib.fs_step
 
     def _check(self, rc):

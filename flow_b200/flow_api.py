@@ -589,7 +589,8 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         lane_change_duration=int(ap.get('lane_change_duration', 5)),
         # AccelEnv.compute_reward is the only reader of env_params.evaluate on this path
         # (accel.py:111-112); sorted_ids: accel.py:150-169
-        evaluate=int(bool(env_params.evaluate) and env_cls.KIND == EN.ENV_ACCEL),
+        evaluate=int(bool(env_params.evaluate) and
+                     env_cls.KIND in (EN.ENV_ACCEL, EN.ENV_MA_HIGHWAY_PO)),
         sort_vehicles=int(sort_on),
         use_ballistic=int(bool(getattr(sim_params, 'use_ballistic', False))),
         seed=int(seed if seed is not None else (getattr(sim_params, 'seed', None) or 0)))
@@ -611,21 +612,36 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
     else:
         if int(net['lanes']) != 1 or int(net.get('num_edges', 1)) != 1:
             raise NotImplementedError('highway: single lane, single edge only')
+        ma = env_cls.KIND == EN.ENV_MA_HIGHWAY_PO
         kw.update(length_lo=float(net['length']), length_hi=float(net['length']),
-                  junction_len=0.0, env_kind=EN.ENV_HIGHWAY)
+                  junction_len=0.0, env_kind=EN.ENV_MA_HIGHWAY_PO if ma else EN.ENV_HIGHWAY)
         flows = network.net_params.inflows.get()
-        if len(flows) > 1:
-            raise NotImplementedError('more than one inflow')
+        if len(flows) > 4:
+            raise NotImplementedError('more than four inflows')
+        rows = []
         for f in flows:
             rate = f.get('vehsPerHour')
             if rate is None:
                 rate = 3600.0 / float(f['period'])
-            kw.update(inflow_vehs_per_hour=float(rate),
-                      inflow_depart_speed=float(f['departSpeed']),
-                      inflow_type=names.index(f['vtype']), inflow_begin=float(f['begin']))
+            if isinstance(f['departSpeed'], str):
+                raise NotImplementedError('depart_speed=%r: SUMO picks the speed; only numeric '
+                                          'departure speeds are compiled' % (f['departSpeed'],))
+            if f['vtype'] not in names:
+                raise KeyError('inflow of unknown vehicle type %r' % (f['vtype'],))
+            t = names.index(f['vtype'])
+            if types[t].controller == EN.CTRL_RL and not ma:
+                raise NotImplementedError('an RL inflow needs MultiAgentHighwayPOEnv')
+            rows.append((t, float(rate), float(f['departSpeed']), float(f['begin'])))
+        if len(rows) == 1:     # the single <flow> of fs_config
+            kw.update(inflow_type=rows[0][0], inflow_vehs_per_hour=rows[0][1],
+                      inflow_depart_speed=rows[0][2], inflow_begin=rows[0][3])
+        elif rows:             # fs_set_inflows
+            kw['inflows'] = rows
         # slots: one vehicle per (length + minGap) of road is the physical maximum
         capacity = max(32, int(math.ceil(float(net['length']) / (VEHICLE_LENGTH + 1.0) / 32) * 32))
         capacity = min(capacity, 256)
+        if ma:
+            kw['max_agents'] = int(min(capacity, ap.get('max_agents', env_cls.MAX_AGENTS)))
     return EngineSpec(types, type_of, kw, ids, names, capacity)
 
 
@@ -867,6 +883,7 @@ class Env:
                                 env_id_base=env_id_base, record_views=int(bool(record_views)),
                                 lc_corrected=int(bool(lc_corrected)), **self.spec.kw)
         if self.spec.capacity is not None:   # highway: vehicles come and go -> slot ids
+            self._initial_ids = list(self.spec.veh_ids)
             self.spec.veh_ids = ['slot_%d' % i for i in range(self.engine.n_veh)]
             self.spec.type_of = list(self.spec.type_of) + [self.spec.kw.get('inflow_type', 0)] * \
                 (self.engine.n_veh - len(self.spec.type_of))
@@ -1151,9 +1168,98 @@ class MultiAgentAccelPOEnv(MultiAgentWaveAttenuationPOEnv):
         return _box(low=-5, high=5, shape=(6,), dtype=np.float32)
 
 
+class MultiAgentHighwayPOEnv(Env):
+    """flow/envs/multiagent/highway.py:14-196 + MultiEnv (flow/envs/multiagent/base.py:116-225) on
+    the single-lane, single-edge HighwayNetwork: every RL vehicle currently IN the network is an
+    agent; agents arrive through RL inflows and leave at the end of the edge.
+
+    One env (n_envs == 1, the gym seam): `step({veh_id: [accel]})` -> dicts keyed by vehicle id
+    ("rl_0" for initial vehicles, "<inflow name>.<k>" for inflow vehicles, as SUMO names them):
+    obs (5,), per-agent reward, done (+ '__all__'), info; an RL vehicle that left the network
+    in this step reports done = True, reward 0 and observation None (base.py:214-217). Actions are
+    not clipped (MultiEnv.clip_actions returns its input); an agent without an entry keeps the
+    simulator's model. Batched envs: `step(tensor [E, max_agents])` (NaN = no command) ->
+    (obs [E, A, 5], reward [E, A], done [E], {'agent_id': [E, A]}), row a = a-th RL vehicle
+    counted from the downstream end.
+
+    Deviations, documented: the collision rule stays on (see MultiAgentWaveAttenuationPOEnv);
+    the reference's config (multiagent_highway.py) runs on HighwayRampsNetwork with three lanes
+    and SUMO lane changing, which is not restated - this is the single-lane straight edge."""
+    KIND = EN.ENV_MA_HIGHWAY_PO
+    ADDITIONAL = {'max_accel': 1, 'max_decel': 1, 'target_velocity': 25}
+    MAX_AGENTS = 16     # observation / action rows per env (additional_params['max_agents'])
+
+    def __init__(self, env_params, sim_params, network, simulator='b200', **kw):
+        super().__init__(env_params, sim_params, network, simulator, **kw)
+        self._flow_names = [f['name'] for f in network.net_params.inflows.get()]
+        self._present = []
+
+    @property
+    def action_space(self):
+        ap = self.env_params.additional_params
+        return _box(low=-abs(ap['max_decel']), high=ap['max_accel'], shape=(1,), dtype=np.float32)
+
+    @property
+    def observation_space(self):
+        return _box(low=-float('inf'), high=float('inf'), shape=(5,), dtype=np.float32)
+
+    def vehicle_name(self, vid):
+        """engine vehicle id -> the id SUMO would give the vehicle"""
+        vid = int(vid)
+        if vid < (1 << 24):
+            return self._initial_ids[vid]
+        return '%s.%d' % (self._flow_names[(vid >> 24) - 1], vid & 0xFFFFFF)
+
+    def _agent_rows(self):
+        ids = self.engine.agent_id[self.view_env].cpu().numpy()
+        return [(a, self.vehicle_name(v)) for a, v in enumerate(ids) if v >= 0]
+
+    def get_rl_ids(self):
+        return [name for _, name in self._agent_rows()]
+
+    def _obs_dict(self, rows):
+        o = self.engine.agent_obs[self.view_env].double().cpu().numpy()
+        return {name: o[a].copy() for a, name in rows}
+
+    def reset(self):
+        super().reset()
+        if self.n_envs > 1:
+            return self.engine.agent_obs
+        self._present = self._agent_rows()
+        return self._obs_dict(self._present)
+
+    def step(self, rl_actions):
+        if self.n_envs > 1:
+            _, _, done, _ = super().step(rl_actions)
+            return self.engine.agent_obs, self.engine.agent_reward, done, \
+                {'agent_id': self.engine.agent_id}
+        a = None
+        if rl_actions:   # `if rl_actions:` highway.py:88 - None and {} both mean "no command"
+            a = np.full(self.engine.max_agents, np.nan)
+            for row, name in self._present:
+                if name in rl_actions:
+                    a[row] = float(np.asarray(rl_actions[name], dtype=np.float64).reshape(-1)[0])
+        before = [name for _, name in self._present]
+        _, _, done, _ = super().step(a)
+        self._present = rows = self._agent_rows()
+        obs = self._obs_dict(rows)
+        d = {name: False for _, name in rows}
+        d['__all__'] = done
+        rew = {}
+        if rl_actions is not None:   # compute_reward: {} during warm-up (highway.py:141-142)
+            r = self.engine.agent_reward[self.view_env].double().cpu().numpy()
+            rew = {name: float(r[a]) for a, name in rows}
+        now = set(obs)
+        for name in before:          # get_arrived_rl_ids, base.py:214-217
+            if name not in now:
+                d[name], rew[name], obs[name] = True, 0, None
+        return obs, rew, d, {name: {} for _, name in rows}
+
+
 _ENV_BY_NAME = {c.__name__: c for c in (AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv,
                                         LaneChangeAccelEnv, LaneChangeAccelPOEnv,
-                                        MultiAgentWaveAttenuationPOEnv, MultiAgentAccelPOEnv)}
+                                        MultiAgentWaveAttenuationPOEnv, MultiAgentAccelPOEnv,
+                                        MultiAgentHighwayPOEnv)}
 
 
 # =============================================================================

@@ -26,6 +26,13 @@
  *                            flow/core/kernel/vehicle/traci.py:411-425,639-689
  *   fs_stats                 Experiment.run return/velocity bookkeeping
  *                            flow/core/experiment.py:123-176
+ *   fs_set_inflows           NetParams(inflows=InFlows()) with several <flow> rows
+ *                            flow/core/params.py:1080-1213,
+ *                            flow/core/kernel/network/traci.py:801-833
+ *   fs_agents                MultiEnv's dict-keyed observations / rewards and the
+ *                            vehicle ids behind them (get_rl_ids, get_arrived_rl_ids)
+ *                            flow/envs/multiagent/base.py:116-225,
+ *                            flow/envs/multiagent/highway.py:97-196
  *
  * Conventions: every call returns 0 on success or a negative FS_E* code;
  * fs_last_error() gives the message. The engine owns all device memory;
@@ -43,7 +50,7 @@
 extern "C" {
 #endif
 
-#define FS_ABI_VERSION 1
+#define FS_ABI_VERSION 2
 
 /* error codes */
 #define FS_OK 0
@@ -106,6 +113,16 @@ extern "C" {
                                 ring: obs [n_rl][6] per env = (x/L, v/vmax, (v_lead-v)/vmax,
                                 (x_lead - x - len)/L  -- NOT wrapped, like the reference --,
                                 (v-v_follow)/vmax, headway(follower)/L); shared desired_velocity reward */
+
+#define FS_ENV_MA_HIGHWAY_PO 8 /* MultiAgentHighwayPOEnv (flow/envs/multiagent/highway.py:97-196) on the
+                                single-lane open highway: every RL vehicle IN the network is an agent.
+                                obs [max_agents][5] per env, row a = a-th RL vehicle counted from the
+                                downstream end: (v/vmax, (v_lead-v)/vmax, headway(LEADER)/L,
+                                (v-v_follow)/vmax, headway(follower)/L), defaults vmax / L / 0 / L
+                                when there is no leader / follower; action row a drives the same
+                                vehicle, UNCLIPPED (MultiEnv.clip_actions is a no-op,
+                                multiagent/base.py:372-395), NaN = no command (simulator model);
+                                per-agent reward max(desired_velocity + 0.1 min(h/v - 1, 0), 0) */
 
 /* fs_config.env_flags */
 #define FS_ENVF_EVALUATE 1      /* EnvParams.evaluate: AccelEnv reward = mean speed
@@ -177,7 +194,30 @@ typedef struct fs_config {
   int32_t n_initial;
   int32_t env_flags;     /* FS_ENVF_* bits (0 = reference defaults)              */
   double inflow_begin;   /* s; InFlows.add(begin=1) */
+  int32_t max_agents;    /* FS_ENV_MA_HIGHWAY_PO: observation / action rows per env (<= n_veh) */
+  int32_t reserved0;
 } fs_config;
+
+/* one <flow> of the open highway (InFlows.add: veh_type, vehs_per_hour | period, depart_speed,
+ * begin); vehicle k of flow f is due at begin + k * 3600 / vehs_per_hour and gets the id
+ * ((f + 1) << 24) | k   ("flow_<f>.<k>" in the reference) */
+#define FS_MAX_INFLOWS 4
+typedef struct fs_inflow {
+  int32_t vtype;         /* vehicle type index                                  */
+  int32_t reserved;
+  double vehs_per_hour, depart_speed, begin;
+} fs_inflow;
+
+/* device views of the multi-agent front (FS_ENV_MA_HIGHWAY_PO); A = max_agents */
+typedef struct fs_agent_views {
+  void* agent_obs;        /* T  [E][A][5] (= views.obs)                          */
+  void* agent_reward;     /* T  [E][A]   reward of the agent in row a (0 if none) */
+  int32_t* agent_id;      /* i32[E][A]   vehicle id of row a, -1 = empty row      */
+  int32_t* veh_id;        /* i32[E][V]   vehicle id in each highway slot: initial vehicle i -> i,
+                                         k-th vehicle of inflow f -> ((f + 1) << 24) | k */
+  uint8_t* veh_type;      /* u8 [E][V]   vehicle type in each highway slot         */
+  int32_t max_agents, obs_per_agent;
+} fs_agent_views;
 
 /* device views; T = float or double per cfg.dtype; [a][b] = a slow, b fast */
 typedef struct fs_views {
@@ -195,7 +235,8 @@ typedef struct fs_views {
   uint8_t* done;     /* u8 [E]                                                  */
   uint8_t* crash;    /* u8 [E]                                                  */
   int32_t* time_counter; /* i32 [E]                                             */
-  int32_t* counters;     /* i32 [3][E] highway: vehicles in network, departed, arrived */
+  int32_t* counters;     /* i32 [3 + FS_MAX_INFLOWS][E] highway: vehicles in network, departed,
+                            arrived, then vehicles emitted by inflow 0..3 */
   int32_t n_envs, n_veh, n_lanes, obs_dim, act_dim, dtype;
   /* element (vehicle i, env e) of pos/vel/lane/headway/leader/follower/accel is at
    * i*veh_stride + e*env_stride: single-lane rings are [V][E] (E, 1), multi-lane
@@ -241,6 +282,14 @@ int fs_step_host_async(fs_engine* e, const void* actions, int k, void* obs_seq,
                        void* reward_seq, uint8_t* done_seq);
 
 int fs_buffers(fs_engine* e, fs_views* out);
+
+/* Highway: replace the single inflow of fs_config by n_flows (0..FS_MAX_INFLOWS) flows, served
+ * in this order when several are due in one step (each needs the entry gap on its own). Call
+ * after fs_set_types and before fs_reset. */
+int fs_set_inflows(fs_engine* e, const fs_inflow* flows, int n_flows);
+
+/* Multi-agent views (FS_ENV_MA_HIGHWAY_PO only; FS_EINVAL otherwise). */
+int fs_agents(fs_engine* e, fs_agent_views* out);
 
 /* DLPack export of engine-owned device memory (obs / reward / state views, or
  * any sub-range of them): returns a malloc'ed DLManagedTensor* (DLPack v0 ABI,

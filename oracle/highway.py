@@ -24,7 +24,19 @@ fixture holds numbers for inflow insertion or arrival.
   * initial vehicles: gen_even_start_pos on the single edge
     (flow/core/kernel/network/base.py:263-391), speed 0;
   * collision <=> some headway < 0 after the move; observation = speeds /
-    speed_limit and positions / length per slot (0 for empty slots).
+    speed_limit and positions / length per slot (0 for empty slots);
+  * several inflows (`inflows=[dict(type, vehs_per_hour, depart_speed, begin)]`)
+    are served in definition order, each needing the entry gap on its own;
+    vehicle k of inflow f carries the id ((f + 1) << 24) | k ('flow_<f>.<k>' in
+    the reference, flow/core/params.py:1163-1213), initial vehicle i the id i.
+
+Multi-agent front (`ma_state` / `ma_reward`): MultiAgentHighwayPOEnv.get_state
+and compute_reward (flow/envs/multiagent/highway.py:97-172) over the RL vehicles
+present, head first; pinned on the reference's own methods by
+tests/golden/make_golden.py::highway_ma (tests/golden/highway_ma.npz). RL
+vehicles take `actions[id]` UNCLIPPED (MultiEnv.clip_actions returns its input,
+multiagent/base.py:372-395) and fall back to the restated simulator model when
+no action is given for them.
 """
 import numpy as np
 
@@ -38,7 +50,8 @@ class HighwaySim:
                  speed_limit=30.0, inflow_vehs_per_hour=2000.0, inflow_type=0,
                  inflow_depart_speed=20.0, inflow_begin=1.0, x0=0.0, bunching=0.0,
                  init_min_gap=0.0, horizon=3000, warmup_steps=0, target_velocity=10.0,
-                 noise_fn=None, evaluate=False, use_ballistic=False, sims_per_step=1):
+                 noise_fn=None, evaluate=False, use_ballistic=False, sims_per_step=1,
+                 inflows=None):
         self.types = types
         self.initial_types = list(initial_types)
         self.capacity = capacity
@@ -49,6 +62,11 @@ class HighwaySim:
         self.inflow_type = inflow_type
         self.depart_speed = inflow_depart_speed
         self.begin = inflow_begin
+        if inflows is None:
+            inflows = [dict(type=inflow_type, vehs_per_hour=inflow_vehs_per_hour,
+                            depart_speed=inflow_depart_speed, begin=inflow_begin)] \
+                if inflow_vehs_per_hour > 0 else []
+        self.inflows = [dict(f) for f in inflows]
         self.init = dict(x0=x0, bunching=bunching, min_gap=init_min_gap)
         self.horizon, self.warmup_steps = horizon, warmup_steps
         self.target_velocity = target_velocity
@@ -83,9 +101,10 @@ class HighwaySim:
         self.pos = [float(xs[i]) for i in order]
         self.vel = [0.0] * n
         self.type_of = [self.initial_types[i] for i in order]
+        self.ids = list(order)
         self.accel = [0.0] * n
         self.time_counter = 0
-        self.spawned = 0
+        self.spawned_by_flow = [0] * len(self.inflows)
         self.departed = n
         self.arrived = 0
         self.crash = False
@@ -103,12 +122,17 @@ class HighwaySim:
                         self.pos[s - 1] - self.pos[s] - self.types[self.type_of[s - 1]].length
                         for s in range(n)]
 
-    def step(self):
-        """One Env.step: sims_per_step simulation steps (base.py:325-383), then obs / reward."""
+    @property
+    def spawned(self):
+        return sum(self.spawned_by_flow)
+
+    def step(self, actions=None):
+        """One Env.step: sims_per_step simulation steps (base.py:325-383), then obs / reward.
+        actions: {vehicle id: acceleration} for RL vehicles (multi-agent front) or None."""
         if self.done:
             return self.get_state(), 0.0, True
         for _ in range(self.sims_per_step):
-            self._sim_step()
+            self._sim_step(actions)
             if self.crash:
                 break
         self.done = self.crash or self.time_counter >= self.sims_per_step * (
@@ -119,7 +143,7 @@ class HighwaySim:
             rew = self.desired_velocity(self.crash)
         return self.get_state(), rew, self.done
 
-    def _sim_step(self):
+    def _sim_step(self, actions=None):
         dt = self.dt
         self.time_counter += 1
         n = len(self.pos)
@@ -128,6 +152,10 @@ class HighwaySim:
             vt = self.types[self.type_of[s]]
             z = self.noise_fn(self.time_counter - 1, s) if (self.noise_fn and vt.noise > 0) else 0.0
             a = C.get_action(self, s, vt, {}, dt, self.speed_limit, z)
+            if vt.controller == C.RL and actions and self.ids[s] in actions:
+                raw = float(actions[self.ids[s]])
+                if raw == raw:          # NaN = no command for this agent
+                    a = raw             # multiagent/highway.py:86-95, not clipped
             self.accel[s] = a
             nv[s] = max(self.vel[s] + a * dt, 0.0)
         for s in range(n):
@@ -143,20 +171,25 @@ class HighwaySim:
         self.vel = [self.vel[s] for s in keep]
         self.type_of = [self.type_of[s] for s in keep]
         self.accel = [self.accel[s] for s in keep]
-        # inflow
-        if self.q > 0:
+        self.arrived_ids = [self.ids[s] for s in range(n) if s not in set(keep)]
+        self.ids = [self.ids[s] for s in keep]
+        # inflows, in definition order
+        for f, fl in enumerate(self.inflows):
+            if not fl['vehs_per_hour'] > 0:
+                continue
             t = self.time_counter * dt
-            due = self.begin + self.spawned * (3600.0 / self.q)
+            due = fl['begin'] + self.spawned_by_flow[f] * (3600.0 / fl['vehs_per_hour'])
             if t >= due and len(self.pos) < self.capacity:
-                nt = self.types[self.inflow_type]
+                nt = self.types[fl['type']]
                 free = (not self.pos) or \
                     (self.pos[-1] - self.types[self.type_of[-1]].length >= nt.sim_min_gap)
                 if free:
                     self.pos.append(0.0)
-                    self.vel.append(float(self.depart_speed))
-                    self.type_of.append(self.inflow_type)
+                    self.vel.append(float(fl['depart_speed']))
+                    self.type_of.append(fl['type'])
+                    self.ids.append(((f + 1) << 24) | self.spawned_by_flow[f])
                     self.accel.append(0.0)
-                    self.spawned += 1
+                    self.spawned_by_flow[f] += 1
                     self.departed += 1
         self.update()
         self.crash = any(h < 0 for h in self.headway)
@@ -177,3 +210,48 @@ class HighwaySim:
         max_cost = np.linalg.norm(np.array([target] * n))
         cost = np.linalg.norm(vel - target)
         return max(max_cost - cost, 0) / (max_cost + F32_EPS)
+
+    # ---- multi-agent front: flow/envs/multiagent/highway.py --------------------
+    def rl_slots(self):
+        """RL vehicles present, head first (= the engine's agent rows)."""
+        return [s for s in range(len(self.pos)) if self.types[self.type_of[s]].controller == C.RL]
+
+    def ma_state(self):
+        """get_state, highway.py:97-136: {id: 5 numbers}; note `lead_head` is the LEADER's
+        headway (highway.py:118) and the follower's headway is the gap behind the agent."""
+        max_speed, max_length = self.speed_limit, self.length
+        obs = {}
+        n = len(self.pos)
+        for s in self.rl_slots():
+            v = self.vel[s]
+            if s == 0:
+                lead_speed, lead_head = max_speed, max_length
+            else:
+                lead_speed, lead_head = self.vel[s - 1], self.headway[s - 1]
+            if s + 1 >= n:
+                follow_speed, follow_head = 0, max_length
+            else:
+                follow_speed, follow_head = self.vel[s + 1], self.headway[s + 1]
+            obs[self.ids[s]] = np.array([v / max_speed, (lead_speed - v) / max_speed,
+                                         lead_head / max_length, (v - follow_speed) / max_speed,
+                                         follow_head / max_length])
+        return obs
+
+    def ma_reward(self, fail=False):
+        """compute_reward, highway.py:138-172 (rl_actions not None)."""
+        rewards = {}
+        for s in self.rl_slots():
+            v = self.vel[s]
+            if self.evaluate:
+                r = v
+            elif fail:
+                r = 0
+            else:
+                cost1 = self.desired_velocity(fail)
+                cost2 = 0
+                if s > 0 and v > 0:
+                    t_headway = max(self.headway[s] / v, 0)
+                    cost2 += min((t_headway - 1) / 1, 0)
+                r = max(1.00 * cost1 + 0.10 * cost2, 0)
+            rewards[self.ids[s]] = r
+        return rewards

@@ -377,6 +377,61 @@ def ring_sorted():
     np.savez_compressed(os.path.join(HERE, 'ring_sorted.npz'), **out)
 
 
+def highway_ma():
+    """MultiAgentHighwayPOEnv.get_state / compute_reward of the reference, step by step, on the
+    restated open highway with a human and an RL inflow: agents enter and leave, the head agent
+    has no leader, the tail agent no follower. 40 steps without actions first."""
+    from .ref_harness import RefHighwayMA
+    from tests.scenarios import highway_ma_sim, highway_ma_action
+    A = 8
+    sim = highway_ma_sim()
+    ref = RefHighwayMA(sim, 25.0)
+    rng = np.random.default_rng(11)
+    n_w, n_a = 40, 700
+    ids = np.full((n_w + n_a + 1, A), -1, np.int64)
+    obs = np.zeros((n_w + n_a + 1, A, 5))
+    rew = np.zeros((n_w + n_a + 1, A))
+    acts = np.full((n_w + n_a, A), np.nan)
+    nveh = np.zeros(n_w + n_a + 1, np.int64)
+
+    def record(t, with_reward):
+        st = ref.get_state()
+        mine = sim.ma_state()
+        assert list(st) == list(mine) and len(st) <= A
+        for a, (vid, o) in enumerate(st.items()):
+            assert np.array_equal(o, mine[vid])          # oracle restatement == reference
+            ids[t, a], obs[t, a] = vid, o
+        if with_reward:
+            r = ref.compute_reward({}, fail=False)
+            mr = sim.ma_reward(False)
+            for a, vid in enumerate(st):
+                assert r[vid] == mr[vid]
+                rew[t, a] = r[vid]
+        nveh[t] = len(sim.pos)
+        return st
+
+    st = record(0, False)
+    seen_head = seen_tail = False
+    for s in range(n_w + n_a):
+        a = None
+        if s >= n_w:
+            a = {}
+            for row, (vid, slot) in enumerate(zip(st, sim.rl_slots())):
+                assert sim.ids[slot] == vid
+                acts[s, row] = highway_ma_action(sim, slot, rng.normal(0, 0.5))
+                a[vid] = acts[s, row]
+        sim.step(a)
+        assert not sim.crash, s
+        st = record(s + 1, True)
+        slots = sim.rl_slots()
+        seen_head |= bool(slots) and slots[0] == 0
+        seen_tail |= bool(slots) and slots[-1] == len(sim.pos) - 1
+    assert seen_head and seen_tail and sim.arrived > 20 and (np.abs(acts[n_w:]) > 1).any()
+    assert (ids >= 0).sum(axis=1).max() >= 3
+    np.savez_compressed(os.path.join(HERE, 'highway_ma.npz'), ids=ids, obs=obs, reward=rew,
+                        actions=acts, n_veh=nveh)
+
+
 def start_pos():
     cases = [dict(length=230, n=22, lanes=1, kw=dict(bunching=20)),
              dict(length=230, n=22, lanes=1, kw=dict()),
@@ -409,6 +464,7 @@ def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
     ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos()
+    highway_ma()
     sumo_fixture()
     print('golden vectors written to', HERE)
 

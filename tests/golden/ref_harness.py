@@ -510,3 +510,65 @@ class RefRingLCSorted(_SortedMixin, RefRingLC):
         add = dict(kw.pop('env_additional', None) or {})
         add['sort_vehicles'] = True
         super().__init__(*a, env_additional=add, **kw)
+
+
+class RefHighwayMA:
+    """MultiAgentHighwayPOEnv.get_state / compute_reward of the REFERENCE
+    (flow/envs/multiagent/highway.py:97-172, with rewards.desired_velocity) evaluated on
+    the state of the restated open highway (oracle/highway.py: SUMO's move, insertion and
+    arrival are the restatement). Vehicle ids are str(engine id)."""
+
+    def __init__(self, sim, target_velocity, evaluate=False):
+        from flow.envs.multiagent.highway import MultiAgentHighwayPOEnv
+        self._cls = MultiAgentHighwayPOEnv
+        self.sim = sim
+        self.env_params = EnvParams(evaluate=evaluate, additional_params={
+            'max_accel': 1, 'max_decel': 1, 'target_velocity': target_velocity})
+        h = self
+
+        class V:
+            def _s(self, vid):
+                return h.sim.ids.index(int(vid))
+
+            def get_ids(self):
+                return [str(i) for i in h.sim.ids]
+
+            def get_rl_ids(self):
+                return [str(h.sim.ids[s]) for s in h.sim.rl_slots()]
+
+            @property
+            def num_vehicles(self):
+                return len(h.sim.ids)
+
+            def get_speed(self, vid, error=-1001):
+                if isinstance(vid, (list, np.ndarray)):
+                    return [self.get_speed(v, error) for v in vid]
+                return h.sim.vel[self._s(vid)]
+
+            def get_headway(self, vid, error=-1001):
+                return h.sim.headway[self._s(vid)]
+
+            def get_leader(self, vid, error=''):
+                s = self._s(vid)
+                return None if s == 0 else str(h.sim.ids[s - 1])   # vehicle/traci.py:234-238
+
+            def get_follower(self, vid, error=''):
+                s = self._s(vid)
+                return None if s + 1 >= len(h.sim.ids) else str(h.sim.ids[s + 1])
+
+        class Nw:
+            def max_speed(self):
+                return h.sim.speed_limit
+
+            def length(self):
+                return h.sim.length
+
+        self.k = type('K', (), {})()
+        self.k.vehicle, self.k.network = V(), Nw()
+
+    def get_state(self):
+        return {int(k): np.asarray(v, float) for k, v in self._cls.get_state(self).items()}
+
+    def compute_reward(self, rl_actions, fail=False):
+        r = self._cls.compute_reward(self, rl_actions, fail=fail)
+        return {int(k): float(v) for k, v in r.items()}

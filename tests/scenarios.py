@@ -87,3 +87,49 @@ C2 = dict(bunching=50.0, init_min_gap=0.0, warmup_steps=750, horizon=3000,
 def rel_err(a, b, floor=1e-12):
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor))) if a.size else 0.0
+
+
+# multi-agent open highway (tests/golden/highway_ma.npz) ------------------------
+HIGHWAY_MA = dict(capacity=64, length=600.0, dt=0.2, speed_limit=30.0, horizon=1500,
+                  target_velocity=25.0, x0=100.0, max_agents=8,
+                  # (type, vehs_per_hour, depart_speed, begin): RL flow first
+                  inflows=[(1, 360.0, 10.0, 5.0), (0, 720.0, 12.0, 5.0)])
+
+
+def highway_ma_groups():
+    return [vt('IDM', 2), vt('RL', 1)]
+
+
+def highway_ma_sim(evaluate=False, **over):
+    """600 m single-lane open highway, 3 initial vehicles (IDM, RL, IDM), an RL inflow of
+    360 veh/h served before an IDM inflow of 720 veh/h, both from t = 5 s (with a saturated
+    entry the first flow in definition order wins every free gap)."""
+    from oracle import highway as OH
+    c = dict(HIGHWAY_MA, **over)
+    return OH.HighwaySim(oracle_types(highway_ma_groups()), [0, 1, 0], capacity=c['capacity'],
+                         length=c['length'], dt=c['dt'], speed_limit=c['speed_limit'],
+                         horizon=c['horizon'], target_velocity=c['target_velocity'], x0=c['x0'],
+                         evaluate=evaluate,
+                         inflows=[dict(type=t, vehs_per_hour=q, depart_speed=v, begin=b)
+                                  for t, q, v, b in c['inflows']])
+
+
+def highway_ma_engine(n_envs, dtype='f64', evaluate=False, **over):
+    from flow_b200 import engine as EN
+    c = dict(HIGHWAY_MA, **over)
+    return EN.Engine(engine_types(highway_ma_groups()), [0, 1, 0], n_envs, dtype=dtype,
+                     capacity=c['capacity'], topology=EN.TOPO_HIGHWAY,
+                     env_kind=EN.ENV_MA_HIGHWAY_PO, length_lo=c['length'], length_hi=c['length'],
+                     sim_step=c['dt'], speed_limit=c['speed_limit'], horizon=c['horizon'],
+                     target_velocity=c['target_velocity'], x0=c['x0'], evaluate=int(evaluate),
+                     max_agents=c['max_agents'], inflows=c['inflows'], record_views=1)
+
+
+def highway_ma_action(sim, slot, z):
+    """Noisy gap-keeping rule on the agent's own gap and closing speed (unclipped on purpose;
+    the observation holds the LEADER's headway, not the agent's, so it cannot drive safely)."""
+    v = sim.vel[slot]
+    if slot == 0:
+        return float(np.clip(0.5 * (20.0 - v), -3.0, 1.2)) + z
+    return float(np.clip(0.1 * (sim.headway[slot] - 5.0 - 1.5 * v) + 0.6 * (sim.vel[slot - 1] - v),
+                         -6.0, 1.2)) + z
