@@ -16,7 +16,9 @@ Timed numbers
   e2e      same metric through B200VecEnv.rollout_host: HOST pinned action
            buffers in, obs/reward/done of every step back on the host, the
            copies inside the timed region;
-  single_step  K launches of one step each (the closed-loop gym cadence).
+  single_step  K launches of one step each, issued by fs_step_unfused and replayed from a
+           CUDA graph (the HBM-bound variant); single_step_per_call = the same from a Python
+           loop of fs_step(k=1) calls (the closed-loop gym cadence).
 All device timings use CUDA events on the stream the kernels run on; N > 1 is
 one process per GPU with a barrier and the max over ranks.
 """
@@ -47,7 +49,7 @@ def parse():
     ap.add_argument('--steps', type=int, default=3000)
     ap.add_argument('--warmup', type=int, default=300)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4'])
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4', 'mah'])
     ap.add_argument('--fuse', type=int, default=100, help='steps per fused launch')
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     ap.add_argument('--noise', type=float, default=0.2,
@@ -267,6 +269,11 @@ def run_b200(a):
         # braking-biased like 'ma': an RL car with zero-mean accelerations rams its leader
         act[:, 0::2] = act[:, 0::2] * 0.6 - 0.4
         act[:, 1::2] = torch.round(act[:, 1::2] * 1.49)
+    if a.workload == 'mah':
+        # random accelerations make every agent ram its leader within a few hundred steps (the
+        # observation does not even hold the agent's own gap): the agents get "no command" rows
+        # (NaN), i.e. the simulator model, which still runs the ranking / observation / reward path
+        act.fill_(float('nan'))
     if a.workload == 'ma':
         # agents that ignore their leaders in stop-and-go traffic ram them within ~100 steps
         # (zero or zero-mean accelerations: > 90 % of the rings); braking-biased random
@@ -292,6 +299,11 @@ def run_b200(a):
             eng.step_ptr(pa + s * sa, min(F, n_steps - s), po_ + s * so, pr + s * sr, pd + s * sd)
 
     def single_pass(n_steps):
+        # K single-step launches issued by libflowstep itself; the second call with the same
+        # buffers (the timed one: warm-up covers the same K steps) replays them from a CUDA graph
+        eng.step_unfused_ptr(pa, n_steps, po_, pr, pd)
+
+    def single_call_pass(n_steps):
         for s in range(n_steps):
             eng.step_ptr(pa + s * sa, 1, po_ + s * so, pr + s * sr, pd + s * sd)
 
@@ -354,9 +366,10 @@ def run_b200(a):
     sampler = ClockSampler(local) if rank == 0 else None
     fused = timed(fused_pass, K)
     if a.only_fused:
-        single = host = host_sync = host1 = fused
+        single = single_call = host = host_sync = host1 = fused
     else:
-        single = timed(single_pass, K)
+        single = timed(single_pass, K, warm=K)
+        single_call = timed(single_call_pass, K)
         # host passes warm up over the whole pinned buffers (first DMA into a pinned page is slow)
         host = timed(host_pass, K, warm=K)
         host_sync = timed(host_sync_pass, K, warm=K)
@@ -376,7 +389,8 @@ def run_b200(a):
     # per-GPU algorithmic bytes of one fused launch / its duration
     # SURVEY 8d per env-step: state round trip 16 B x V + ring length 4 + actions + obs + reward 4 + done 1 (f32)
     nv = eng.n_veh            # vehicles (ring) or slots (highway) whose state makes the round trip
-    extra = {'c3': 2, 'c4': 2}.get(a.workload, 0)    # + lane / slot-type byte read and written
+    # + lane / slot-type byte read and written (+ the 4-byte vehicle id on the multi-agent highway)
+    extra = {'c3': 2, 'c4': 2, 'mah': 10}.get(a.workload, 0)
     bpe = (nv * 16 + 4 + 4 * env.act_dim + 4 * env.obs_dim + 4) * (ts / 4) + 1 + nv * extra
     alg_bytes = bpe * (fused['env_steps'] / world) / max(n_launch, 1)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
@@ -409,7 +423,12 @@ def run_b200(a):
         'mean_reward': fused['mean_reward'], 'mean_speed': fused['mean_speed'],
         'gpu_launches': n_launch,
         'single_step': {'value': vps(single), 'unit': 'vehicle-steps/s',
-                        'ms_per_step': single['ms'] / K, 'launches': single['launches']},
+                        'ms_per_step': single['ms'] / K, 'launches': single['launches'],
+                        'api': 'fs_step_unfused: K one-step launches (state through HBM every '
+                               'step) replayed from one CUDA graph'},
+        'single_step_per_call': {'value': vps(single_call), 'unit': 'vehicle-steps/s',
+                                 'ms_per_step': single_call['ms'] / K,
+                                 'api': 'fs_step(k=1) called K times from Python (ctypes)'},
         'e2e': {'value': vps(host), 'unit': 'vehicle-steps/s', 'h2d_bytes_per_step': h2d / F,
                 'd2h_bytes_per_step': d2h / F, 'api': 'B200VecEnv.rollout_host_async -> '
                 'fs_step_host_async, %d steps per call, pinned host buffers, upload / kernel / '
@@ -425,7 +444,8 @@ def run_b200(a):
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
                      'kernel': '%s<%s> (flow_b200/csrc/), %d fused steps per launch, threads/env = %s'
-                               % ({'ma': 'ring1_fast_kernel', 'c3': 'ring_ml_kernel', 'c4': 'highway_kernel'}.get(
+                               % ({'ma': 'ring1_fast_kernel', 'c3': 'ring_ml_kernel', 'c4': 'highway_kernel',
+                                   'mah': 'highway_kernel'}.get(
                                    a.workload, 'ring1_hot_kernel'), a.dtype, F,
                                   os.environ.get('FS_RING_SHAPE', 'auto')),
                      'launch_ms': launch_ms,

@@ -98,6 +98,7 @@ SYMBOLS = [
     ('fs_set_types', C.c_int, [C.c_void_p, C.POINTER(FsVType), C.c_int, C.c_void_p]),
     ('fs_reset', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_step_unfused', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host_async', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_buffers', C.c_int, [C.c_void_p, C.POINTER(FsViews)]),

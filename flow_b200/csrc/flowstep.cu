@@ -56,6 +56,12 @@ struct fs_engine {
   int* agent_id = nullptr;     // [E][A]
   void* agent_reward = nullptr;  // T [E][A]
   bool ma_highway() const { return cfg.env_kind == FS_ENV_MA_HIGHWAY_PO; }
+  // fs_step_unfused: the k single-step launches of the last call, kept as an instantiated graph
+  cudaGraphExec_t uf_exec = nullptr;
+  const void* uf_key[4] = {nullptr, nullptr, nullptr, nullptr};
+  int uf_k = 0;
+  int64_t uf_launches = 0;
+  bool pdl_hint = false;   // set while fs_step_unfused issues its launches
   bool env_major = false;  // pos/vel/lane stored [E][V] (multi-lane, highway)
   // FS_ENVF_SORT_VEHICLES (fs_sort.cuh): keys [E][V], their validity [E], permuted actions [A][E]
   void *abs_pos = nullptr, *prev_pos = nullptr, *act_sorted = nullptr;
@@ -239,6 +245,7 @@ extern "C" void fs_destroy(fs_engine* e) {
     if (sl.run) cudaEventDestroy(sl.run);
     if (sl.down) cudaEventDestroy(sl.down);
   }
+  if (e->uf_exec) cudaGraphExecDestroy(e->uf_exec);
   for (void* p : e->allocs) if (p) cudaFree(p);
   if (e->stream && e->own_stream) cudaStreamDestroy(e->stream);
   delete e;
@@ -520,13 +527,17 @@ static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
   const int grid = (E + wpb - 1) / wpb;
   const size_t smem = (size_t)wpb * fs::hw_smem_per_warp<T>(CAP);
   const fs::HwBufs<T> b = hw_bufs<T>(e);
+  const auto& cfg = cfg_of<T>(e);
+  constexpr int NF = FS_MAX_INFLOWS;
+#define FS_HW(SL, MA, F) fs::highway_kernel<T, SL, MA, F><<<grid, wpb * 32, smem, e->stream>>>(cfg, b, a)
   if (e->ma_highway()) {
-    if (CAP <= 64) fs::highway_kernel<T, 2, true><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-    else if (CAP <= 160) fs::highway_kernel<T, 5, true><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-    else fs::highway_kernel<T, 8, true><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  } else if (CAP <= 64) fs::highway_kernel<T, 2, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  else if (CAP <= 160) fs::highway_kernel<T, 5, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-  else fs::highway_kernel<T, 8, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    if (CAP <= 64) FS_HW(2, true, NF); else if (CAP <= 160) FS_HW(5, true, NF); else FS_HW(8, true, NF);
+  } else if (e->n_flows <= 1) {
+    if (CAP <= 64) FS_HW(2, false, 1); else if (CAP <= 160) FS_HW(5, false, 1); else FS_HW(8, false, 1);
+  } else {
+    if (CAP <= 64) FS_HW(2, false, NF); else if (CAP <= 160) FS_HW(5, false, NF); else FS_HW(8, false, NF);
+  }
+#undef FS_HW
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   return FS_OK;
@@ -617,6 +628,7 @@ static int do_step_sorted(fs_engine* e, const void* actions, int k, void* obs_se
   fs::StepArgs<T> a;
   a.mask = mask; a.accumulate_stats = stats; a.ignore_done = ignore_done;
   a.write_views = e->cfg.record_views != 0;
+  a.pdl = 0;
   if (k == 0) {  // observation of the current state (reset without warm-up)
     a.actions = nullptr; a.obs_seq = nullptr; a.reward_seq = nullptr; a.done_seq = nullptr;
     a.k_steps = 0;
@@ -686,6 +698,7 @@ static int do_step1(fs_engine* e, const void* actions, int k, void* obs_seq, voi
   a.done_seq = done_seq; a.mask = mask; a.k_steps = k; a.accumulate_stats = stats;
   a.ignore_done = ignore_done;
   a.write_views = e->cfg.record_views != 0;
+  a.pdl = e->pdl_hint ? 1 : 0;
   return run_steps<T>(e, a);
 }
 
@@ -697,6 +710,78 @@ extern "C" int fs_step(fs_engine* e, const void* actions, int k, void* obs_seq,
   cudaSetDevice(e->cfg.device);
   return e->f64 ? do_step<double>(e, actions, k, obs_seq, reward_seq, done_seq, nullptr, 1, 0)
                 : do_step<float>(e, actions, k, obs_seq, reward_seq, done_seq, nullptr, 1, 0);
+}
+
+// k steps as k SINGLE-STEP launches (state round-trips through memory every step: the
+// HBM-bound variant of SURVEY 8d). The launch sequence is issued from C and, when the engine's
+// stream can be captured, recorded into a CUDA graph that later calls with the same buffers
+// replay with one cudaGraphLaunch (the pointers are baked into the nodes).
+template <typename T>
+static int unfused_loop(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
+                        uint8_t* done_seq) {
+  const size_t E = e->cfg.n_envs, act_row = (size_t)e->act_dim * E, obs_row = E * e->obs_dim;
+  static const bool no_pdl = getenv("FS_NO_PDL") && atoi(getenv("FS_NO_PDL")) != 0;
+  // measured (c5, 65 536 envs: 8.9 -> 8.0 us per step; c2, 4096 envs: 6.2 -> 6.9 us): only
+  // launches with a long per-thread run gain from starting the next grid early
+  e->pdl_hint = !no_pdl && E >= 32768;
+  int rc = FS_OK;
+  for (int s = 0; s < k && rc == FS_OK; ++s)
+    rc = do_step<T>(e, actions ? (const T*)actions + s * act_row : nullptr, 1,
+                    obs_seq ? (T*)obs_seq + s * obs_row : nullptr,
+                    reward_seq ? (T*)reward_seq + s * E : nullptr,
+                    done_seq ? done_seq + s * E : nullptr, nullptr, 1, 0);
+  e->pdl_hint = false;
+  return rc;
+}
+
+extern "C" int fs_step_unfused(fs_engine* e, const void* actions, int k, void* obs_seq,
+                               void* reward_seq, uint8_t* done_seq) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_step_unfused: call fs_set_types first");
+  if (k < 1) return fail(e, FS_EINVAL, "fs_step_unfused: k must be >= 1");
+  cudaSetDevice(e->cfg.device);
+  auto loop = [&]() {
+    return e->f64 ? unfused_loop<double>(e, actions, k, obs_seq, reward_seq, done_seq)
+                  : unfused_loop<float>(e, actions, k, obs_seq, reward_seq, done_seq);
+  };
+  const bool same = e->uf_exec && e->uf_k == k && e->uf_key[0] == actions &&
+                    e->uf_key[1] == obs_seq && e->uf_key[2] == reward_seq && e->uf_key[3] == done_seq;
+  if (same) {
+    FS_CUDA(e, cudaGraphLaunch(e->uf_exec, e->stream));
+    e->launches += e->uf_launches;
+    return FS_OK;
+  }
+  if (e->uf_exec) { cudaGraphExecDestroy(e->uf_exec); e->uf_exec = nullptr; }
+  static const bool no_graph = getenv("FS_NO_GRAPH") && atoi(getenv("FS_NO_GRAPH")) != 0;
+  // the legacy default stream cannot be captured; k == 1 gains nothing from a graph
+  if (no_graph || k == 1 || e->stream == nullptr || e->stream == cudaStreamLegacy) return loop();
+  if (cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    return loop();
+  }
+  const int64_t l0 = e->launches;
+  const int rc = loop();
+  cudaGraph_t g = nullptr;
+  cudaError_t st = cudaStreamEndCapture(e->stream, &g);
+  if (rc != FS_OK) { if (g) cudaGraphDestroy(g); return rc; }
+  if (st != cudaSuccess || !g) {
+    cudaGetLastError();
+    e->launches = l0;
+    return loop();   // capture refused (e.g. another capture in flight): plain launches
+  }
+  e->uf_launches = e->launches - l0;
+  st = cudaGraphInstantiate(&e->uf_exec, g, 0);
+  cudaGraphDestroy(g);
+  if (st != cudaSuccess) {
+    e->uf_exec = nullptr;
+    e->launches = l0;
+    cudaGetLastError();
+    return loop();
+  }
+  e->uf_k = k; e->uf_key[0] = actions; e->uf_key[1] = obs_seq; e->uf_key[2] = reward_seq;
+  e->uf_key[3] = done_seq;
+  FS_CUDA(e, cudaGraphLaunch(e->uf_exec, e->stream));
+  return FS_OK;
 }
 
 template <typename T>

@@ -57,7 +57,8 @@ __host__ __device__ inline size_t hw_smem_per_warp(int cap) {
   return (size_t)cap * (3 * sizeof(T) + 2 * sizeof(int));
 }
 
-template <typename T, int SLOTS, bool kMA>
+// NF = inflows compiled in (1: the single <flow> of c4; FS_MAX_INFLOWS otherwise)
+template <typename T, int SLOTS, bool kMA, int NF>
 __global__ void __launch_bounds__(128)
 highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -101,9 +102,9 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   const long long gid = cfg.env_id_base + e;
   T reward = B.reward[e];
   int departed = B.departed[e], arrived = B.arrived[e];
-  int spawned[FS_MAX_INFLOWS];
+  int spawned[NF];
 #pragma unroll
-  for (int f = 0; f < FS_MAX_INFLOWS; ++f) spawned[f] = f < B.n_flows ? B.spawned[(size_t)f * E + e] : 0;
+  for (int f = 0; f < NF; ++f) spawned[f] = f < B.n_flows ? B.spawned[(size_t)f * E + e] : 0;
   double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
 
   auto publish = [&]() {
@@ -300,7 +301,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       // inflows, in definition order: each emits at most one due vehicle per step at the
       // tail, if the entry gap to the last vehicle allows it
 #pragma unroll
-      for (int f = 0; f < FS_MAX_INFLOWS; ++f) {
+      for (int f = 0; f < NF; ++f) {
         if (f >= B.n_flows || !(B.period[f] > 0.0)) continue;
         const double t = (double)tc * (double)cfg.dt;
         const double due = B.begin[f] + (double)spawned[f] * B.period[f];
@@ -398,7 +399,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   if (lane_id == 0) {
     B.n_active[e] = n; B.departed[e] = departed; B.arrived[e] = arrived;
 #pragma unroll
-    for (int f = 0; f < FS_MAX_INFLOWS; ++f) if (f < B.n_flows) B.spawned[(size_t)f * E + e] = spawned[f];
+    for (int f = 0; f < NF; ++f) if (f < B.n_flows) B.spawned[(size_t)f * E + e] = spawned[f];
     B.time_counter[e] = tc;
     B.done[e] = done ? 1 : 0;
     B.crash[e] = crash ? 1 : 0;

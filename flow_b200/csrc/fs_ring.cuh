@@ -54,6 +54,7 @@ struct StepArgs {
   int accumulate_stats;
   int ignore_done;   // warm-up inside reset
   int write_views;
+  int pdl = 0;       // host-side hint: launch with programmatic stream serialization (fs_step_unfused)
 };
 
 template <typename T>

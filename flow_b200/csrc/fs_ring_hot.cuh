@@ -113,6 +113,12 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   constexpr bool kPred = G > 1 && G < 32;
   static_assert(VPT * G >= V, "shape does not hold 22 vehicles");
 
+  // Programmatic dependent launch (fs_step_unfused issues its one-step launches with
+  // programmatic stream serialization): let the next launch of the stream start being
+  // scheduled right away, and do not touch memory before the previous one has completed and
+  // flushed. Both are no-ops for an ordinary launch.
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const int lane = threadIdx.x & 31;
   const int g = (G == 1) ? 0 : lane / EPW;
   const int es = (G == 1) ? lane : lane % EPW;
@@ -391,12 +397,25 @@ static cudaError_t launch_hot_shape(bool noise, bool act, int grid, int block, c
     if (var && launch_hot_var<T, VPT, G>(var, grid, block, st, c, b, a)) return cudaGetLastError();
   }
 #endif
+  auto go = [&](void (*kern)(const FastP<T>, const RingBufs<T>, const StepArgs<T>)) {
+    if (a.pdl) {   // programmatic dependent launch: overlaps this launch's ramp with the previous tail
+      cudaLaunchConfig_t lc = {};
+      lc.gridDim = dim3(grid); lc.blockDim = dim3(block); lc.dynamicSmemBytes = 0; lc.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      lc.attrs = at; lc.numAttrs = 1;
+      cudaLaunchKernelEx(&lc, kern, c, b, a);
+    } else {
+      kern<<<grid, block, 0, st>>>(c, b, a);
+    }
+  };
   if (noise) {
-    if (act) ring1_hot_kernel<T, VPT, G, true, true><<<grid, block, 0, st>>>(c, b, a);
-    else ring1_hot_kernel<T, VPT, G, true, false><<<grid, block, 0, st>>>(c, b, a);
+    if (act) go(ring1_hot_kernel<T, VPT, G, true, true>);
+    else go(ring1_hot_kernel<T, VPT, G, true, false>);
   } else {
-    if (act) ring1_hot_kernel<T, VPT, G, false, true><<<grid, block, 0, st>>>(c, b, a);
-    else ring1_hot_kernel<T, VPT, G, false, false><<<grid, block, 0, st>>>(c, b, a);
+    if (act) go(ring1_hot_kernel<T, VPT, G, false, true>);
+    else go(ring1_hot_kernel<T, VPT, G, false, false>);
   }
   return cudaGetLastError();
 }

@@ -223,6 +223,14 @@ class Engine:
         if rc != 0:
             self._check(rc)
 
+    def step_unfused_ptr(self, actions_ptr, k, obs_ptr=0, reward_ptr=0, done_ptr=0):
+        """k steps as k single-step launches issued from C / replayed from a CUDA graph
+        (fs_step_unfused): the variant whose state round-trips through HBM every step."""
+        rc = self.lib.fs_step_unfused(self.h, actions_ptr or None, k, obs_ptr or None,
+                                      reward_ptr or None, done_ptr or None)
+        if rc != 0:
+            self._check(rc)
+
     def step_host(self, actions, k=1, want_obs=True):
         """k fused steps with HOST numpy buffers; returns (obs, reward, done) arrays
         of every step ([k,E,obs_dim], [k,E], [k,E])."""

@@ -58,7 +58,23 @@ def highway_c4(noise=0.0):
     return types, [0] * 20, kw
 
 
+def highway_ma(noise=0.0):
+    """MultiAgentHighwayPOEnv (flow/envs/multiagent/highway.py) on the single-lane 1 km
+    HighwayNetwork with the inflow split of examples/exp_configs/rl/multiagent/
+    multiagent_highway.py (20 % RL penetration): an RL inflow of 400 veh/h served before an IDM
+    inflow of 1600 veh/h, 160 slots, up to 32 agent rows per env."""
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise), EN.make_vtype(EN.CTRL_RL)]
+    kw = dict(topology=EN.TOPO_HIGHWAY, env_kind=EN.ENV_MA_HIGHWAY_PO, length_lo=1000.0,
+              length_hi=1000.0, junction_len=0.0, target_velocity=25.0, horizon=3000,
+              warmup_steps=0, capacity=160, max_agents=32,
+              inflows=[(1, 400.0, 20.0, 1.0), (0, 1600.0, 20.0, 1.0)])
+    return types, [0] * 20, kw
+
+
 WORKLOADS = {
+    'mah': dict(builder=highway_ma, n_envs=1024, n_veh=160,
+                name='MultiAgentHighwayPOEnv open 1 km highway, IDM inflow 1600 + RL inflow 400 veh/h, '
+                     '160 slots, 32 agent rows, 1024 envs/GPU, agents without command (simulator model)'),
     'c3': dict(builder=ring_c3, n_envs=2048, n_veh=66,
                name='LaneChangeAccelEnv 3-lane ring, 63 IDM + 3 RL lane changers, 2048 envs/GPU, '
                     'random accelerations and directions'),

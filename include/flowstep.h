@@ -15,7 +15,7 @@
  *                            flow/envs/base.py:414-560,
  *                            flow/envs/ring/wave_attenuation.py:157-210,
  *                            flow/core/kernel/network/base.py:263-391
- *   fs_step / fs_step_host / fs_step_host_async
+ *   fs_step / fs_step_unfused / fs_step_host / fs_step_host_async
  *                            Env.step (controllers, fail-safes, apply_acceleration,
  *                            simulation_step, k.update, get_state, compute_reward)
  *                            flow/envs/base.py:294-412
@@ -266,6 +266,15 @@ int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* lengths);
  * are always left in views.obs / reward / done. */
 int fs_step(fs_engine* e, const void* actions, int k, void* obs_seq,
             void* reward_seq, uint8_t* done_seq);
+
+/* The same k steps as k SINGLE-STEP launches - the variant whose vehicle state makes the round
+ * trip through device memory every step (SURVEY 8d "single-step variant"; fs_step fuses the k
+ * steps in one launch and keeps the state in registers). Results are identical to fs_step's.
+ * The launches are issued from C and recorded into a CUDA graph; a later call with the same
+ * k and buffer addresses replays it with one cudaGraphLaunch (new action values are picked up:
+ * only the addresses are baked in). FS_NO_GRAPH=1 keeps plain launches. */
+int fs_step_unfused(fs_engine* e, const void* actions, int k, void* obs_seq,
+                    void* reward_seq, uint8_t* done_seq);
 
 /* Same with HOST buffers (pageable or pinned): copies actions up, runs the k
  * steps, copies obs/reward/done of every step back, and synchronises. */

@@ -185,3 +185,36 @@ def test_pipelined_host_rollout_equals_blocking():
         assert np.array_equal(d, done[s:s + k].numpy()), s
         s += k
     assert torch.equal(a.engine.pos, b.engine.pos)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('dtype', ['f64', 'f32'])
+def test_unfused_graph_replay_equals_fused_launch(dtype):
+    """fs_step_unfused (K single-step launches, second call replayed from the CUDA graph with
+    NEW action values in the same buffers) == fs_step (one fused launch), bit for bit."""
+    import torch
+    K, E = 60, 96
+    td = torch.float64 if dtype == 'f64' else torch.float32
+    mk = lambda: S.make_engine(S.c2_groups(noise=0.2), E, dtype, **KW)  # noqa: E731
+    a, b = mk(), mk()
+    act = torch.empty(K, 1, E, device='cuda', dtype=td)
+    outs = []
+    for eng in (a, b):
+        outs.append((torch.zeros(K, E, 3, device='cuda', dtype=td),
+                     torch.zeros(K, E, device='cuda', dtype=td),
+                     torch.zeros(K, E, device='cuda', dtype=torch.uint8)))
+    gen = torch.Generator(device='cuda')
+    for rnd in range(3):            # round 0 captures, rounds 1-2 replay
+        gen.manual_seed(100 + rnd)
+        act.copy_(torch.rand(K, 1, E, device='cuda', dtype=td, generator=gen) * 2 - 1)
+        a.reset(); b.reset()
+        l0 = a.launch_count
+        a.step_unfused_ptr(act.data_ptr(), K, *(t.data_ptr() for t in outs[0]))
+        assert a.launch_count - l0 == K
+        b.step(act, k=K, obs_seq=outs[1][0], reward_seq=outs[1][1], done_seq=outs[1][2])
+        for x, y in zip(outs[0], outs[1]):
+            assert torch.equal(x, y), rnd
+        assert torch.equal(a.pos, b.pos) and torch.equal(a.vel, b.vel)
+        sa_, sb_ = a.stats(reset=True), b.stats(reset=True)   # float partial sums: order differs
+        assert sa_['vehicle_steps'] == sb_['vehicle_steps'] and sa_['crashes'] == sb_['crashes']
+        assert close(sa_['sum_speed'], sb_['sum_speed']) <= 1e-5
