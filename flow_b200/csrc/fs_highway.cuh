@@ -427,10 +427,21 @@ __global__ void highway_reset_kernel(const __grid_constant__ Cfg<T> cfg, const H
   if (n_initial > 0) {
     const double available = (L - bunching) - n_initial * (min_gap + 5.0);
     const double increment = available / n_initial;
+    // positions grow with the index until the `% length` of gen_even_start_pos wraps them to
+    // the start of the edge (x0 > 0; at most once, the vehicles span less than the edge):
+    // indices [0, w) lie downstream of indices [w, n). Head first: w-1 .. 0, n-1 .. w.
+    int w = n_initial;
+    {
+      double x = (double)cfg.x0;
+      for (int i = 1; i < n_initial; ++i) {
+        const double xn = fmod(__dadd_rn(__dadd_rn(__dadd_rn(x, increment), 5.0), min_gap), L);
+        if (xn < x) { w = i; break; }
+        x = xn;
+      }
+    }
     double x = (double)cfg.x0;
-    // index i has the i-th smallest position as long as no wrap happens; head first:
     for (int i = 0; i < n_initial; ++i) {
-      const int s = n_initial - 1 - i;
+      const int s = i < w ? w - 1 - i : n_initial - 1 - (i - w);
       B.pos[eo + s] = (T)x; B.vel[eo + s] = T(0);
       B.vtype[eo + s] = cfg.type_of[i]; B.active[eo + s] = 1;
       if (B.vid) B.vid[eo + s] = i;

@@ -239,3 +239,98 @@ def test_fuzz_highway_vs_oracle_fp64(seed):
     c = eng.counters.cpu().numpy()
     if not nonlocal_mean:
         assert (c[:3, 1] == list(ref[-1][3:])).all(), (c[:, 1], ref[-1][3:])
+
+
+# ------------------------------------------------- multi-agent open highway
+def draw_highway_ma(seed):
+    rng = np.random.default_rng(9000 + seed)
+    kinds = [str(k) for k in rng.choice(['IDM', 'OVM', 'LINEAR_OVM', 'BCM', 'CFM', 'GIPPS', 'SIM'],
+                                        size=int(rng.integers(1, 3)), replace=False)]
+    groups = []
+    for k in kinds:
+        fs = None
+        if k in ('IDM', 'OVM', 'LINEAR_OVM', 'CFM') and rng.random() < 0.4:
+            fs = str(rng.choice(['instantaneous', 'safe_velocity']))
+        groups.append(S.vt(k, 0, fail_safe=fs))
+    groups.append(S.vt('RL', 0, max_accel=float(rng.choice([1.0, 2.6])),
+                       sim_min_gap=float(rng.choice([0.0, 2.5]))))
+    rl_t = len(groups) - 1
+    cap = int(rng.choice([32, 64, 96, 160]))
+    length = float(rng.choice([300.0, 600.0, 1000.0]))
+    n_init = int(rng.integers(0, min(cap, int(length / 12)) // 2 + 1))
+    init_types = [int(t) for t in rng.integers(0, len(groups), n_init)]
+    flows = []
+    for _ in range(int(rng.integers(1, 5))):
+        flows.append((int(rl_t if rng.random() < 0.4 else rng.integers(0, len(groups))),
+                      float(rng.choice([300.0, 900.0, 2000.0])),
+                      float(rng.choice([0.0, 8.0, 15.0])), float(rng.choice([0.0, 1.0, 2.5]))))
+    kw = dict(length=length, dt=float(rng.choice([0.1, 0.2, 0.5])),
+              x0=float(rng.choice([0.0, 7.5, 50.0])), horizon=int(rng.choice([80, 3000])),
+              warmup_steps=int(rng.choice([0, 5])), target_velocity=float(rng.choice([10.0, 25.0])),
+              evaluate=bool(rng.random() < 0.25), use_ballistic=bool(rng.random() < 0.25))
+    A = int(rng.choice([1, 4, 33])) if cap > 32 else int(rng.choice([1, 4, 32]))
+    return groups, init_types, cap, flows, min(A, cap), kw, rng
+
+
+@pytest.mark.parametrize('seed', range(30))
+def test_fuzz_highway_multiagent_vs_oracle_fp64(seed):
+    """Random open highways with up to four inflows (RL ones included), random agent commands
+    (some missing = NaN), more agents than action rows in some cases, collisions allowed: agent
+    ids, observations, per-agent rewards, slot occupancy and counters vs the oracle each step."""
+    import torch
+    from oracle import highway as OH
+    from flow_b200 import engine as EN
+    groups, init_types, cap, flows, A, kw, rng = draw_highway_ma(seed)
+    try:
+        h = OH.HighwaySim(S.oracle_types(groups), init_types, capacity=cap,
+                          inflows=[dict(type=t, vehs_per_hour=q, depart_speed=v, begin=b)
+                                   for t, q, v, b in flows], **kw)
+    except ValueError:
+        pytest.skip('initial vehicles do not fit')
+    E = 2
+    eng = EN.Engine(S.engine_types(groups), init_types, E, dtype='f64', capacity=cap,
+                    topology=EN.TOPO_HIGHWAY, env_kind=EN.ENV_MA_HIGHWAY_PO, length_lo=kw['length'],
+                    length_hi=kw['length'], junction_len=0.0, record_views=1, sim_step=kw['dt'],
+                    x0=kw['x0'], horizon=kw['horizon'], warmup_steps=kw['warmup_steps'],
+                    target_velocity=kw['target_velocity'], evaluate=int(kw['evaluate']),
+                    use_ballistic=int(kw['use_ballistic']), max_agents=A, inflows=flows)
+    eng.reset()
+    n_agents_seen = 0
+    for k in range(160):
+        slots = h.rl_slots()
+        ids = [h.ids[s] for s in slots]
+        got = eng.agent_id.cpu().numpy()
+        want = (ids + [-1] * A)[:A]
+        assert (got == want).all(), (k, got, want)
+        st = h.ma_state()
+        ob = eng.agent_obs.cpu().numpy()
+        for a, vid in enumerate(ids[:A]):
+            assert close(ob[1, a], st[vid], floor=1e-3) <= 1e-9, (k, a)
+        assert (ob[:, len(ids[:A]):] == 0).all()
+        n_agents_seen = max(n_agents_seen, len(ids))
+        if h.done:
+            assert eng.done.cpu().numpy().all(), k
+            break
+        # commands for the agents that have an action row; ~20 % missing
+        acts, row = {}, np.full((A, E), np.nan)
+        for a, (vid, s) in enumerate(zip(ids[:A], slots[:A])):
+            if rng.random() < 0.8:
+                acts[vid] = float(np.clip(0.2 * (h.headway[s] - 4 - 1.2 * h.vel[s]), -4, 1.5)
+                                  + rng.normal(0, 0.4)) if s > 0 else float(rng.normal(0.3, 0.5))
+                row[a] = acts[vid]
+        use = bool(acts) or rng.random() < 0.5
+        eng.step(torch.as_tensor(row, dtype=torch.float64, device='cuda') if use else None)
+        h.step(acts if use else None)
+        n = len(h.pos)
+        c = eng.counters.cpu().numpy()
+        assert (c[:, 0] == [n, h.departed, h.arrived]).all(), (k, c[:, 0], n, h.departed, h.arrived)
+        assert (eng.veh_id.cpu().numpy()[0, :n] == h.ids).all(), k
+        assert close(eng.pos.cpu().numpy()[:n, 1], h.pos) <= 1e-9, k
+        assert close(eng.vel.cpu().numpy()[:n, 1], h.vel) <= 1e-9, k
+        assert bool(eng.crash.cpu().numpy()[0]) == h.crash, k
+        if not h.crash:
+            rw = h.ma_reward(False)
+            er = eng.agent_reward.cpu().numpy()
+            now = [h.ids[s] for s in h.rl_slots()][:A]
+            for a, vid in enumerate(now):
+                assert close(er[0, a], rw[vid]) <= 1e-9, (k, a, er[0, a], rw[vid])

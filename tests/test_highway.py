@@ -92,3 +92,21 @@ def test_gpu_highway_fused_fp32_aggregates():
     assert abs(float(rew_seq[:, 7].sum()) - r) <= 0.01 * max(abs(r), 1.0)
     st = eng.stats()
     assert st['env_steps'] == K * 40 and st['crashes'] == 0
+
+
+@pytest.mark.gpu
+def test_gpu_highway_start_positions_that_wrap_past_the_end():
+    """InitialConfig(x0 > 0): gen_even_start_pos wraps the last vehicles to the start of the edge
+    (`% length`, network/base.py:380); the slots must still be head first."""
+    eng = engine(2, 'f64', 30, x0=400.0, record_views=1)
+    eng.reset()
+    h = make_oracle(30, x0=400.0)
+    assert max(h.pos) == h.pos[0] and min(h.pos) < 400.0 < max(h.pos)      # it did wrap
+    assert close(eng.pos.cpu().numpy()[:30, 1], h.pos) <= 1e-12
+    for s in range(300):
+        o_obs, o_rew, o_done = h.step()
+        obs, rew, done = eng.step()
+        n = len(h.pos)
+        assert close(eng.pos.cpu().numpy()[:n, 0], h.pos) <= 1e-9, s
+        assert close(rew.cpu().numpy()[1], o_rew) <= 1e-9, s
+    assert not h.crash and h.arrived > 5
