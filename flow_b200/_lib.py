@@ -65,7 +65,7 @@ FS_MAX_INFLOWS = 4
 class FsInflow(C.Structure):
     _fields_ = [('vtype', C.c_int32), ('reserved', C.c_int32),
                 ('vehs_per_hour', C.c_double), ('depart_speed', C.c_double),
-                ('begin', C.c_double)]
+                ('begin', C.c_double), ('end', C.c_double), ('probability', C.c_double)]
 
 
 class FsAgentViews(C.Structure):

@@ -209,7 +209,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   if (e->env_major) A(&e->last_lc, V * E * 4);
   if (e->sort_on()) { A(&e->abs_pos, V * E * ts); A(&e->prev_pos, V * E * ts); A(&e->keys_valid, E); }
   if (cfg->topology == FS_TOPO_HIGHWAY) {
-    A(&e->counters, (3 + FS_MAX_INFLOWS) * E * 4); A(&e->vtype, V * E);
+    A(&e->counters, (3 + 2 * FS_MAX_INFLOWS) * E * 4); A(&e->vtype, V * E);
     if (cfg->inflow_vehs_per_hour > 0) {
       e->n_flows = 1;
       e->flows[0].vtype = cfg->inflow_type; e->flows[0].vehs_per_hour = cfg->inflow_vehs_per_hour;
@@ -502,6 +502,7 @@ static fs::HwBufs<T> hw_bufs(fs_engine* e) {
   b.length = (T*)e->circ;
   b.n_active = e->counters; b.departed = e->counters + E; b.arrived = e->counters + 2 * E;
   b.spawned = e->counters + 3 * E;
+  b.pending = e->counters + (3 + FS_MAX_INFLOWS) * E;
   b.time_counter = e->time_counter; b.episode = e->episode; b.done = e->done; b.crash = e->crash;
   b.obs = (T*)e->obs; b.reward = (T*)e->reward;
   b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
@@ -509,9 +510,11 @@ static fs::HwBufs<T> hw_bufs(fs_engine* e) {
   b.n_flows = e->n_flows;
   for (int f = 0; f < FS_MAX_INFLOWS; ++f) {
     const fs_inflow& q = e->flows[f];
-    const bool on = f < e->n_flows && q.vehs_per_hour > 0;
-    b.period[f] = on ? 3600.0 / q.vehs_per_hour : 0.0;
+    const bool on = f < e->n_flows && (q.vehs_per_hour > 0 || q.probability > 0);
+    b.period[f] = on && q.vehs_per_hour > 0 ? 3600.0 / q.vehs_per_hour : 0.0;
+    b.prob[f] = on && !(q.vehs_per_hour > 0) ? q.probability : 0.0;
     b.begin[f] = on ? q.begin : 0.0;
+    b.end[f] = on ? q.end : 0.0;
     b.depart_speed[f] = on ? (T)q.depart_speed : T(0);
     b.inflow_type[f] = on ? q.vtype : 0;
   }
@@ -529,13 +532,16 @@ static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
   const fs::HwBufs<T> b = hw_bufs<T>(e);
   const auto& cfg = cfg_of<T>(e);
   constexpr int NF = FS_MAX_INFLOWS;
-#define FS_HW(SL, MA, F) fs::highway_kernel<T, SL, MA, F><<<grid, wpb * 32, smem, e->stream>>>(cfg, b, a)
+#define FS_HW(SL, MA, F, PR) \
+  fs::highway_kernel<T, SL, MA, F, PR><<<grid, wpb * 32, smem, e->stream>>>(cfg, b, a)
+  bool any_prob = false;
+  for (int f = 0; f < e->n_flows; ++f) any_prob |= b.prob[f] > 0.0 || b.end[f] > 0.0;
   if (e->ma_highway()) {
-    if (CAP <= 64) FS_HW(2, true, NF); else if (CAP <= 160) FS_HW(5, true, NF); else FS_HW(8, true, NF);
-  } else if (e->n_flows <= 1) {
-    if (CAP <= 64) FS_HW(2, false, 1); else if (CAP <= 160) FS_HW(5, false, 1); else FS_HW(8, false, 1);
+    if (CAP <= 64) FS_HW(2, true, NF, true); else if (CAP <= 160) FS_HW(5, true, NF, true); else FS_HW(8, true, NF, true);
+  } else if (e->n_flows <= 1 && !any_prob) {   // c4: one periodic <flow>
+    if (CAP <= 64) FS_HW(2, false, 1, false); else if (CAP <= 160) FS_HW(5, false, 1, false); else FS_HW(8, false, 1, false);
   } else {
-    if (CAP <= 64) FS_HW(2, false, NF); else if (CAP <= 160) FS_HW(5, false, NF); else FS_HW(8, false, NF);
+    if (CAP <= 64) FS_HW(2, false, NF, true); else if (CAP <= 160) FS_HW(5, false, NF, true); else FS_HW(8, false, NF, true);
   }
 #undef FS_HW
   e->launches++;
@@ -839,8 +845,12 @@ extern "C" int fs_set_inflows(fs_engine* e, const fs_inflow* flows, int n_flows)
   for (int f = 0; f < n_flows; ++f) {
     if (flows[f].vtype < 0 || flows[f].vtype >= n_types)
       return fail(e, FS_EINVAL, "fs_set_inflows: vtype out of range");
-    if (!(flows[f].vehs_per_hour > 0) || !(flows[f].depart_speed >= 0) || !(flows[f].begin >= 0))
-      return fail(e, FS_EINVAL, "fs_set_inflows: vehs_per_hour > 0, depart_speed >= 0, begin >= 0");
+    const bool periodic = flows[f].vehs_per_hour > 0;
+    const bool prob = flows[f].probability > 0 && flows[f].probability <= 1;
+    if (periodic == prob || flows[f].probability < 0 || flows[f].vehs_per_hour < 0 ||
+        !(flows[f].depart_speed >= 0) || !(flows[f].begin >= 0))
+      return fail(e, FS_EINVAL, "fs_set_inflows: exactly one of vehs_per_hour > 0 / probability in "
+                                "(0, 1]; depart_speed >= 0, begin >= 0");
     const fs::TypeP<double>* td = e->f64 ? &e->cd.types[flows[f].vtype] : nullptr;
     const int ctrl = td ? td->ctrl : e->cf.types[flows[f].vtype].ctrl;
     if (ctrl == FS_CTRL_RL && !e->ma_highway())

@@ -36,13 +36,15 @@ struct HwBufs {
   T* length;                                         // [E] edge length
   int* n_active; int* departed; int* arrived;  // [E]
   int* spawned;                                // [FS_MAX_INFLOWS][E] vehicles emitted per inflow
+  int* pending;                                // [FS_MAX_INFLOWS][E] probabilistic flows: due, not yet in
   int* time_counter; int* episode;
   uint8_t* done; uint8_t* crash;
   T* obs; T* reward;
   T* v_accel; T* v_headway; int* v_leader; int* v_follower;  // views [E][CAP] or null
   double* stats;
   int n_flows;
-  double period[FS_MAX_INFLOWS], begin[FS_MAX_INFLOWS];   // s
+  double period[FS_MAX_INFLOWS], begin[FS_MAX_INFLOWS], end[FS_MAX_INFLOWS];   // s (end <= 0: none)
+  double prob[FS_MAX_INFLOWS];                 // per second; > 0: probabilistic flow
   T depart_speed[FS_MAX_INFLOWS];
   int inflow_type[FS_MAX_INFLOWS];
   // multi-agent front (kMA)
@@ -57,8 +59,9 @@ __host__ __device__ inline size_t hw_smem_per_warp(int cap) {
   return (size_t)cap * (3 * sizeof(T) + 2 * sizeof(int));
 }
 
-// NF = inflows compiled in (1: the single <flow> of c4; FS_MAX_INFLOWS otherwise)
-template <typename T, int SLOTS, bool kMA, int NF>
+// NF = inflows compiled in (1: the single <flow> of c4; FS_MAX_INFLOWS otherwise);
+// kProb = probabilistic flows and flow ends compiled in
+template <typename T, int SLOTS, bool kMA, int NF, bool kProb>
 __global__ void __launch_bounds__(128)
 highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -105,6 +108,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   int spawned[NF];
 #pragma unroll
   for (int f = 0; f < NF; ++f) spawned[f] = f < B.n_flows ? B.spawned[(size_t)f * E + e] : 0;
+  int pending[NF];
+#pragma unroll
+  for (int f = 0; f < NF; ++f)
+    pending[f] = (kProb && f < B.n_flows && B.prob[f] > 0.0) ? B.pending[(size_t)f * E + e] : 0;
   double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
 
   auto publish = [&]() {
@@ -302,10 +309,25 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       // tail, if the entry gap to the last vehicle allows it
 #pragma unroll
       for (int f = 0; f < NF; ++f) {
-        if (f >= B.n_flows || !(B.period[f] > 0.0)) continue;
+        if (f >= B.n_flows) continue;
         const double t = (double)tc * (double)cfg.dt;
-        const double due = B.begin[f] + (double)spawned[f] * B.period[f];
-        bool spawn = t >= due && n < CAP;
+        const bool probabilistic = kProb && B.prob[f] > 0.0;
+        bool want;
+        if (probabilistic) {   // one Bernoulli(probability * dt) draw per step inside [begin, end)
+          if (t >= B.begin[f] && (B.end[f] <= 0.0 || t < B.end[f])) {
+            uint32_t rr[4];
+            Philox::gen((uint32_t)tc, 0x40000000u | (uint32_t)f, (uint32_t)gid, (uint32_t)(gid >> 32),
+                        (uint32_t)cfg.seed ^ ((uint32_t)episode * 0x9E3779B9u),
+                        (uint32_t)(cfg.seed >> 32), rr);
+            if ((double)rr[0] * (1.0 / 4294967296.0) < B.prob[f] * (double)cfg.dt) pending[f] += 1;
+          }
+          want = pending[f] > 0;
+        } else {
+          if (!(B.period[f] > 0.0)) continue;
+          const double due = B.begin[f] + (double)spawned[f] * B.period[f];
+          want = t >= due && (!kProb || B.end[f] <= 0.0 || due < B.end[f]);
+        }
+        bool spawn = want && n < CAP;
         if (spawn && n > 0) {
           const int sl = n - 1;  // last vehicle
           T xl = T(0); int tl = 0;
@@ -323,6 +345,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
               if (kMA) id[kMA ? r : 0] = ((f + 1) << 24) | spawned[f];
             }
           n += 1; spawned[f] += 1; departed += 1;
+          if (probabilistic) pending[f] -= 1;
         }
       }
       update();
@@ -399,7 +422,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   if (lane_id == 0) {
     B.n_active[e] = n; B.departed[e] = departed; B.arrived[e] = arrived;
 #pragma unroll
-    for (int f = 0; f < NF; ++f) if (f < B.n_flows) B.spawned[(size_t)f * E + e] = spawned[f];
+    for (int f = 0; f < NF; ++f) if (f < B.n_flows) {
+      B.spawned[(size_t)f * E + e] = spawned[f];
+      if (kProb && B.prob[f] > 0.0) B.pending[(size_t)f * E + e] = pending[f];
+    }
     B.time_counter[e] = tc;
     B.done[e] = done ? 1 : 0;
     B.crash[e] = crash ? 1 : 0;
@@ -454,7 +480,7 @@ __global__ void highway_reset_kernel(const __grid_constant__ Cfg<T> cfg, const H
   }
   B.length[e] = (T)L;
   B.n_active[e] = n_initial; B.departed[e] = n_initial; B.arrived[e] = 0;
-  for (int f = 0; f < FS_MAX_INFLOWS; ++f) B.spawned[(size_t)f * E + e] = 0;
+  for (int f = 0; f < FS_MAX_INFLOWS; ++f) { B.spawned[(size_t)f * E + e] = 0; B.pending[(size_t)f * E + e] = 0; }
   B.time_counter[e] = 0;
   B.episode[e] = B.episode[e] + 1;
   B.done[e] = 0; B.crash[e] = 0;

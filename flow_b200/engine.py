@@ -101,7 +101,8 @@ class Engine:
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
                         record_views=0, lc_corrected=0, n_initial=0, inflow_begin=1.0,
                         evaluate=0, sort_vehicles=0, use_ballistic=0, max_agents=0)
-        inflows = cfg.pop('inflows', None)   # [(vtype, vehs_per_hour, depart_speed, begin), ...]
+        # [(vtype, vehs_per_hour, depart_speed, begin[, end[, probability]]), ...]
+        inflows = cfg.pop('inflows', None)
         unknown = set(cfg) - set(defaults)
         if unknown:
             raise TypeError('unknown engine config keys: %s' % sorted(unknown))
@@ -132,9 +133,12 @@ class Engine:
         self._check(self.lib.fs_set_types(self.h, arr, len(types), tov.ctypes.data))
         if inflows is not None:
             rows = (_lib.FsInflow * max(1, len(inflows)))()
-            for r, (vt, rate, speed, begin) in zip(rows, inflows):
+            for r, row in zip(rows, inflows):
+                vt, rate, speed, begin = row[:4]
                 r.vtype, r.vehs_per_hour, r.depart_speed, r.begin = \
                     int(vt), float(rate), float(speed), float(begin)
+                r.end = float(row[4]) if len(row) > 4 else 0.0
+                r.probability = float(row[5]) if len(row) > 5 else 0.0
             self._check(self.lib.fs_set_inflows(self.h, rows, len(inflows)))
         v = _lib.FsViews()
         self._check(self.lib.fs_buffers(self.h, C.byref(v)))

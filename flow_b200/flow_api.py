@@ -368,9 +368,9 @@ class InFlows:
         given = [x is not None for x in (vehs_per_hour, probability, period)]
         if sum(given) > 1:
             raise ValueError('define exactly one of vehs_per_hour, probability, period')
-        if probability is not None:
-            raise NotImplementedError('probabilistic inflows are not compiled (only '
-                                      'vehs_per_hour / period)')
+        if probability is not None and not 0 <= probability <= 1:
+            raise ValueError('Inflow.add called with parameter \'probability\' set to {}, but '
+                             'probability should be between 0 and 1'.format(probability))
         new = dict(name='%s_%d' % (name, len(self.__flows)), vtype=veh_type, edge=edge,
                    departLane=depart_lane, departSpeed=depart_speed, begin=begin, end=end)
         new.update(kwargs)
@@ -378,6 +378,8 @@ class InFlows:
             new['vehsPerHour'] = vehs_per_hour
         if period is not None:
             new['period'] = period
+        if probability is not None:
+            new['probability'] = probability
         if number is not None:
             new['number'] = number
         self.__flows.append(new)
@@ -620,9 +622,20 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
             raise NotImplementedError('more than four inflows')
         rows = []
         for f in flows:
-            rate = f.get('vehsPerHour')
-            if rate is None:
+            rate, prob = f.get('vehsPerHour'), float(f.get('probability') or 0.0)
+            begin, end = float(f['begin']), float(f.get('end') or 0.0)
+            if rate is None and f.get('period') is not None:
                 rate = 3600.0 / float(f['period'])
+            if f.get('number') is not None and end > begin:
+                # SUMO: `number` vehicles, evenly spaced over [begin, end) when no rate is given,
+                # else the flow ends after `number` vehicles
+                if rate is None and not prob:
+                    rate = 3600.0 * float(f['number']) / (end - begin)
+                elif rate is not None:
+                    end = min(end, begin + float(f['number']) * 3600.0 / float(rate))
+            if rate is None and not prob:
+                raise ValueError('inflow %r: one of vehs_per_hour, probability, period, number is '
+                                 'needed' % (f.get('name'),))
             if isinstance(f['departSpeed'], str):
                 raise NotImplementedError('depart_speed=%r: SUMO picks the speed; only numeric '
                                           'departure speeds are compiled' % (f['departSpeed'],))
@@ -631,8 +644,8 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
             t = names.index(f['vtype'])
             if types[t].controller == EN.CTRL_RL and not ma:
                 raise NotImplementedError('an RL inflow needs MultiAgentHighwayPOEnv')
-            rows.append((t, float(rate), float(f['departSpeed']), float(f['begin'])))
-        if len(rows) == 1:     # the single <flow> of fs_config
+            rows.append((t, float(rate or 0.0), float(f['departSpeed']), begin, end, prob))
+        if len(rows) == 1 and not rows[0][5] and rows[0][4] >= 86400:   # the single <flow> of fs_config
             kw.update(inflow_type=rows[0][0], inflow_vehs_per_hour=rows[0][1],
                       inflow_depart_speed=rows[0][2], inflow_begin=rows[0][3])
         elif rows:             # fs_set_inflows

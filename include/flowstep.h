@@ -198,14 +198,21 @@ typedef struct fs_config {
   int32_t reserved0;
 } fs_config;
 
-/* one <flow> of the open highway (InFlows.add: veh_type, vehs_per_hour | period, depart_speed,
- * begin); vehicle k of flow f is due at begin + k * 3600 / vehs_per_hour and gets the id
- * ((f + 1) << 24) | k   ("flow_<f>.<k>" in the reference) */
+/* one <flow> of the open highway (InFlows.add: veh_type, vehs_per_hour | period | probability,
+ * depart_speed, begin, end). Periodic flow (vehs_per_hour > 0): vehicle k is due at
+ * begin + k * 3600 / vehs_per_hour as long as that is before `end`. Probabilistic flow
+ * (probability > 0, per second): in every simulation step inside [begin, end) one more vehicle
+ * becomes due with probability `probability * sim_step` (counter-based Philox keyed by seed,
+ * global env id, episode, flow and step, so the draw does not depend on the GPU count). Due
+ * vehicles that find the entry blocked wait. Vehicle k of flow f gets the id
+ * ((f + 1) << 24) | k   ("flow_<f>.<k>" in the reference). */
 #define FS_MAX_INFLOWS 4
 typedef struct fs_inflow {
   int32_t vtype;         /* vehicle type index                                  */
   int32_t reserved;
   double vehs_per_hour, depart_speed, begin;
+  double end;            /* s; <= 0: never ends (InFlows.add default 86400)      */
+  double probability;    /* per second, in (0, 1]; 0 = periodic flow             */
 } fs_inflow;
 
 /* device views of the multi-agent front (FS_ENV_MA_HIGHWAY_PO); A = max_agents */
@@ -235,8 +242,9 @@ typedef struct fs_views {
   uint8_t* done;     /* u8 [E]                                                  */
   uint8_t* crash;    /* u8 [E]                                                  */
   int32_t* time_counter; /* i32 [E]                                             */
-  int32_t* counters;     /* i32 [3 + FS_MAX_INFLOWS][E] highway: vehicles in network, departed,
-                            arrived, then vehicles emitted by inflow 0..3 */
+  int32_t* counters;     /* i32 [3 + 2 FS_MAX_INFLOWS][E] highway: vehicles in network, departed,
+                            arrived, vehicles emitted by inflow 0..3, vehicles of the
+                            probabilistic inflows 0..3 still waiting to enter */
   int32_t n_envs, n_veh, n_lanes, obs_dim, act_dim, dtype;
   /* element (vehicle i, env e) of pos/vel/lane/headway/leader/follower/accel is at
    * i*veh_stride + e*env_stride: single-lane rings are [V][E] (E, 1), multi-lane

@@ -26,7 +26,13 @@ fixture holds numbers for inflow insertion or arrival.
   * collision <=> some headway < 0 after the move; observation = speeds /
     speed_limit and positions / length per slot (0 for empty slots);
   * several inflows (`inflows=[dict(type, vehs_per_hour, depart_speed, begin)]`)
-    are served in definition order, each needing the entry gap on its own;
+    are served in definition order, each needing the entry gap on its own; a flow
+    with `end` emits only vehicles due before it; a flow with `probability` p
+    (per second) instead makes one more vehicle due with probability p * dt in
+    every step inside [begin, end) - SUMO scales the per-second probability by
+    the step length - drawn from Philox4x32-10 keyed by (seed, global env id,
+    episode, flow, step) exactly as the engine does, so the arrival pattern is
+    reproducible bit for bit (SUMO's own generator is not: parity unpinned);
     vehicle k of inflow f carries the id ((f + 1) << 24) | k ('flow_<f>.<k>' in
     the reference, flow/core/params.py:1163-1213), initial vehicle i the id i.
 
@@ -42,6 +48,19 @@ import numpy as np
 
 from . import controllers as C
 
+
+def philox4x32_10(counter, key):
+    """Philox4x32-10 (Salmon et al., SC'11), the counter-based generator the engine uses;
+    counter: 4 x u32, key: 2 x u32 -> 4 x u32."""
+    c = [int(x) & 0xFFFFFFFF for x in counter]
+    k = [int(x) & 0xFFFFFFFF for x in key]
+    for _ in range(10):
+        p0, p1 = 0xD2511F53 * c[0], 0xCD9E8D57 * c[2]
+        c = [((p1 >> 32) ^ c[1] ^ k[0]) & 0xFFFFFFFF, p1 & 0xFFFFFFFF,
+             ((p0 >> 32) ^ c[3] ^ k[1]) & 0xFFFFFFFF, p0 & 0xFFFFFFFF]
+        k = [(k[0] + 0x9E3779B9) & 0xFFFFFFFF, (k[1] + 0xBB67AE85) & 0xFFFFFFFF]
+    return c
+
 F32_EPS = float(np.finfo(np.float32).eps)
 
 
@@ -51,7 +70,7 @@ class HighwaySim:
                  inflow_depart_speed=20.0, inflow_begin=1.0, x0=0.0, bunching=0.0,
                  init_min_gap=0.0, horizon=3000, warmup_steps=0, target_velocity=10.0,
                  noise_fn=None, evaluate=False, use_ballistic=False, sims_per_step=1,
-                 inflows=None):
+                 inflows=None, seed=0, env_gid=0):
         self.types = types
         self.initial_types = list(initial_types)
         self.capacity = capacity
@@ -67,6 +86,7 @@ class HighwaySim:
                             depart_speed=inflow_depart_speed, begin=inflow_begin)] \
                 if inflow_vehs_per_hour > 0 else []
         self.inflows = [dict(f) for f in inflows]
+        self.seed, self.env_gid, self.episode = int(seed), int(env_gid), 0
         self.init = dict(x0=x0, bunching=bunching, min_gap=init_min_gap)
         self.horizon, self.warmup_steps = horizon, warmup_steps
         self.target_velocity = target_velocity
@@ -105,6 +125,8 @@ class HighwaySim:
         self.accel = [0.0] * n
         self.time_counter = 0
         self.spawned_by_flow = [0] * len(self.inflows)
+        self.pending = [0] * len(self.inflows)
+        self.episode += 1
         self.departed = n
         self.arrived = 0
         self.crash = False
@@ -175,11 +197,24 @@ class HighwaySim:
         self.ids = [self.ids[s] for s in keep]
         # inflows, in definition order
         for f, fl in enumerate(self.inflows):
-            if not fl['vehs_per_hour'] > 0:
-                continue
             t = self.time_counter * dt
-            due = fl['begin'] + self.spawned_by_flow[f] * (3600.0 / fl['vehs_per_hour'])
-            if t >= due and len(self.pos) < self.capacity:
+            end = fl.get('end', 0.0)
+            prob = 0.0 if fl.get('vehs_per_hour', 0) > 0 else fl.get('probability', 0.0)
+            if prob > 0:
+                if t >= fl['begin'] and (end <= 0 or t < end):
+                    r = philox4x32_10(
+                        [self.time_counter, 0x40000000 | f, self.env_gid, self.env_gid >> 32],
+                        [(self.seed & 0xFFFFFFFF) ^ ((self.episode * 0x9E3779B9) & 0xFFFFFFFF),
+                         self.seed >> 32])
+                    if r[0] * (1.0 / 4294967296.0) < prob * dt:
+                        self.pending[f] += 1
+                want = self.pending[f] > 0
+            elif fl.get('vehs_per_hour', 0) > 0:
+                due = fl['begin'] + self.spawned_by_flow[f] * (3600.0 / fl['vehs_per_hour'])
+                want = t >= due and (end <= 0 or due < end)
+            else:
+                continue
+            if want and len(self.pos) < self.capacity:
                 nt = self.types[fl['type']]
                 free = (not self.pos) or \
                     (self.pos[-1] - self.types[self.type_of[-1]].length >= nt.sim_min_gap)
@@ -191,6 +226,8 @@ class HighwaySim:
                     self.accel.append(0.0)
                     self.spawned_by_flow[f] += 1
                     self.departed += 1
+                    if prob > 0:
+                        self.pending[f] -= 1
         self.update()
         self.crash = any(h < 0 for h in self.headway)
 

@@ -110,3 +110,82 @@ def test_gpu_highway_start_positions_that_wrap_past_the_end():
         assert close(eng.pos.cpu().numpy()[:n, 0], h.pos) <= 1e-9, s
         assert close(rew.cpu().numpy()[1], o_rew) <= 1e-9, s
     assert not h.crash and h.arrived > 5
+
+
+# ---------------------------------------------------------------- probabilistic inflows
+def prob_oracle(gid, seed=77, p=0.2, **kw):
+    return OH.HighwaySim([OC.VType(OC.IDM, OC.idm_params())], [], capacity=96, length=600.0,
+                         inflows=[dict(type=0, probability=p, depart_speed=15.0, begin=1.0, end=120.0),
+                                  dict(type=0, vehs_per_hour=300.0, depart_speed=15.0, begin=2.0,
+                                       end=30.0)],
+                         seed=seed, env_gid=gid, **kw)
+
+
+def test_oracle_philox_known_answer():
+    """Random123's published known-answer vectors for Philox4x32-10."""
+    assert OH.philox4x32_10([0, 0, 0, 0], [0, 0]) == \
+        [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert OH.philox4x32_10([0xffffffff] * 4, [0xffffffff] * 2) == \
+        [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert OH.philox4x32_10([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344],
+                            [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_oracle_probabilistic_inflow_rate_and_end():
+    """p = 0.2 / s over [1 s, 120 s): about 24 vehicles (binomial, sd 4.8), none generated after
+    `end`; the periodic flow (one per 12 s from 2 s) stops before its end = 30 s: 2, 14, 26."""
+    tot = []
+    for gid in range(8):
+        h = prob_oracle(gid)
+        for _ in range(1500):
+            h.step()
+        assert h.spawned_by_flow[1] == 3
+        assert h.pending[0] == 0 and not h.crash
+        tot.append(h.spawned_by_flow[0])
+    assert len(set(tot)) > 1                      # keyed by the env id
+    assert abs(np.mean(tot) - 23.8) < 3 * 4.8 / np.sqrt(8), tot
+    a, b = prob_oracle(3), prob_oracle(3)
+    for _ in range(300):
+        a.step(); b.step()
+    assert a.pos == b.pos                          # counter-based: reproducible
+
+
+@pytest.mark.gpu
+def test_gpu_probabilistic_inflow_matches_oracle_bit_for_bit():
+    """The engine draws from the same Philox stream (seed, GLOBAL env id, episode, flow, step):
+    arrivals, slot occupancy and trajectories equal the oracle's, and a shard that starts at
+    env_id_base = 5 reproduces envs 5.. of the unsharded run."""
+    from flow_b200 import engine as EN
+    types = [EN.make_vtype(EN.CTRL_IDM, [30, 1, 1, 1.5, 4, 2])]
+    flows = [(0, 0.0, 15.0, 1.0, 120.0, 0.2), (0, 300.0, 15.0, 2.0, 30.0, 0.0)]
+
+    def mk(E, base):
+        return EN.Engine(types, [], E, dtype='f64', capacity=96, topology=EN.TOPO_HIGHWAY,
+                         env_kind=EN.ENV_HIGHWAY, length_lo=600.0, length_hi=600.0, seed=77,
+                         env_id_base=base, horizon=3000, inflows=flows, record_views=1)
+    eng, shard = mk(8, 0), mk(3, 5)
+    eng.reset(); shard.reset()
+    sims = [prob_oracle(g) for g in range(8)]
+    for s in range(1500):
+        eng.step(); shard.step()
+        for h in sims:
+            h.step()
+        if s % 50 == 0 or s > 1450:
+            c = eng.counters.cpu().numpy()
+            for g, h in enumerate(sims):
+                assert (c[:, g] == [len(h.pos), h.departed, h.arrived]).all(), (s, g)
+                n = len(h.pos)
+                assert close(eng.pos.cpu().numpy()[:n, g], h.pos) <= 1e-9, (s, g)
+    import torch
+    assert torch.equal(eng.pos[:, 5:], shard.pos) and torch.equal(eng.counters[:, 5:], shard.counters)
+    # second episode: another stream
+    eng.reset()
+    for h in sims:
+        h.reset()
+    for s in range(400):
+        eng.step()
+        for h in sims:
+            h.step()
+    c = eng.counters.cpu().numpy()
+    assert (c[1] == [h.departed for h in sims]).all()
