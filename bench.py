@@ -59,6 +59,9 @@ def parse():
     ap.add_argument('--only-fused', action='store_true',
                     help='development: time only the fused device-resident pass')
     ap.add_argument('--cpu-envs-per-core', type=int, default=2)
+    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
+                    help="weak (default, the driver's contract): the workload's envs on EVERY GPU; "
+                         'strong: the same total split over the GPUs (SURVEY 8d c5)')
     return ap.parse_args()
 
 
@@ -256,7 +259,10 @@ def run_b200(a):
     E, K, W, F = (a.envs or wl['n_envs']), a.steps, a.warmup, max(1, min(a.fuse, a.steps))
     types, tov, kw = wl['builder'](noise=a.noise)
     kw['horizon'] = max(kw['horizon'], K)
-    env_id_base, E = SH.weak_shard(E, rank)   # weak scaling: E envs on every GPU
+    if a.scaling == 'strong':
+        env_id_base, E = SH.shard_envs(E, rank, world)   # the workload's envs split over the GPUs
+    else:
+        env_id_base, E = SH.weak_shard(E, rank)          # weak scaling: E envs on every GPU
     env = B200VecEnv(types, tov, E, dtype=a.dtype, device=local, env_id_base=env_id_base,
                      seed=1234, **kw)
     eng = env.engine
@@ -406,7 +412,7 @@ def run_b200(a):
     line = {
         'metric': 'vehicle-steps/s', 'value': vps(fused), 'unit': 'vehicle-steps/s',
         'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': fused['ms'] / K,
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': a.dtype,
+        'higher_is_better': True, 'scaling': a.scaling, 'vs_baseline': None, 'dtype': a.dtype,
         'data': 'synthetic',
         'env_steps_per_s': fused['env_steps'] / (fused['ms'] * 1e-3),
         'config': {'workload': '%s: %s' % (a.workload, wl['name']), 'envs_per_gpu': E,

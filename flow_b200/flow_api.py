@@ -12,6 +12,8 @@ What each piece stands for in the reference (parthjaggi/flow):
   AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv    flow/envs/ring/accel.py, wave_attenuation.py
   LaneChangeAccelEnv                                    flow/envs/ring/lane_change_accel.py
   MultiAgentWaveAttenuationPOEnv                        flow/envs/multiagent/ring/wave_attenuation.py:143-312
+  MultiAgentAccelPOEnv                                  flow/envs/multiagent/ring/accel.py:87-226
+  MultiAgentHighwayPOEnv                                flow/envs/multiagent/highway.py:14-196
   Env.reset / Env.step / clip_actions                   flow/envs/base.py:294-615
   env.k.vehicle.* / env.k.network.*                     flow/core/kernel/vehicle/traci.py, network/traci.py
   make_create_env                                       flow/utils/registry.py:13-134

@@ -6,3 +6,11 @@ python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tai
 python bench.py --workload c5 --steps 300 --warmup 10 --no-cpu-baseline > gpurun_out/final_c5.json 2> gpurun_out/final_c5.err
 bash scripts/gpu_profile.sh
 bash scripts/gpu_profile_c3.sh
+# gpurun brings back at most 64 MiB: keep the csv exports (raw metrics + per-SASS-line source page), drop the reports
+for f in gpurun_out/*.ncu-rep; do
+  [ -f "$f" ] || continue
+  ncu -i "$f" --page raw --csv > "${f%.ncu-rep}_raw.csv" 2>/dev/null
+  ncu -i "$f" --page source --csv > "${f%.ncu-rep}_source.csv" 2>/dev/null
+  rm -f "$f"
+done
+du -sh gpurun_out

@@ -10,4 +10,7 @@ ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 3 -
 python bench.py --workload c5 --steps 200 --warmup 100 --no-cpu-baseline --only-fused > gpurun_out/prof_plain_c5.json 2> gpurun_out/prof_plain_c5.err || exit 1
 ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 3 -c 1 -o gpurun_out/prof_c5_final \
     python bench.py --workload c5 --steps 200 --warmup 100 --no-cpu-baseline --only-fused > gpurun_out/ncu_full_c5.log 2>&1
+# one SINGLE-STEP launch (k = 1) of c5: the HBM-bound variant
+FS_NO_GRAPH=1 FS_NO_PDL=1 ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 12 -c 1 -o gpurun_out/prof_c5_single \
+    python bench.py --workload c5 --steps 40 --warmup 10 --fuse 40 --no-cpu-baseline > gpurun_out/ncu_full_c5_single.log 2>&1
 for f in gpurun_out/ncu_full_c2.log gpurun_out/ncu_full_c5.log; do tail -n 2 $f; done

@@ -1,7 +1,7 @@
 #!/bin/bash
 # c3 / c4: plain bench (must exit 0) -> one `--set full` capture of the step kernel.
 mkdir -p gpurun_out
-for w in c3 c4; do
+for w in c3 c4 mah; do
   python bench.py --workload $w --steps 1000 --warmup 3 --no-cpu-baseline > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err || { tail -n 5 gpurun_out/bench_$w.err; exit 1; }
 done
 ncu --set full --clock-control none --import-source on -k regex:ring_ml -s 3 -c 1 -o gpurun_out/prof_c3 \

@@ -51,6 +51,8 @@ traffic = {}
 KERNEL = {'c2': 'ring1_hot', 'c5': 'ring1_hot', 'c3': 'ring_ml', 'c4': 'highway_kernel'}
 for wl in ('c2', 'c5', 'c3', 'c4'):
     raw = os.path.join(G, 'prof_%s_final_raw.csv' % wl)
+    if not os.path.exists(raw) and os.path.exists(os.path.join(G, 'prof_%s_raw.csv' % wl)):
+        raw = os.path.join(G, 'prof_%s_raw.csv' % wl)     # exported on the GPU box (gpu_final.sh)
     rep = os.path.join(G, ('prof_%s_final.ncu-rep' if wl in ('c2', 'c5') else 'prof_%s.ncu-rep') % wl)
     if os.path.exists(rep) and (not os.path.exists(raw) or os.path.getmtime(raw) < os.path.getmtime(rep)):
         with open(raw, 'w') as f:
@@ -69,12 +71,25 @@ for wl in ('c2', 'c5', 'c3', 'c4'):
         x = float(r[i])
         return x * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u[i]]
     traffic['%s_f32_fuse100' % wl] = val('dram__bytes_read.sum') + val('dram__bytes_write.sum')
+rep = os.path.join(G, 'prof_c5_single.ncu-rep')
+raw = os.path.join(G, 'prof_c5_single_raw.csv')
+if os.path.exists(rep):
+    with open(raw, 'w') as f:
+        subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], stdout=f, stderr=subprocess.DEVNULL)
+if os.path.exists(raw):
+    out = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'ncu_summary.py'), raw],
+                         capture_output=True, text=True).stdout
+    open(os.path.join(P, '%s_ncu_full_c5_single_step.csv' % tag), 'w').write(
+        '# ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 12 -c 1, ONE '
+        'single-step launch (k = 1, 65 536 envs) of FS_NO_GRAPH=1 FS_NO_PDL=1 python bench.py '
+        '--workload c5 --steps 40 --warmup 10 --fuse 40\n' + out)
 if traffic:
     json.dump(traffic, open(os.path.join(P, 'ncu_traffic.json'), 'w'), indent=1)
 
 # 3. bench lines
 for wl, src in (('c2', 'final_default.json'), ('c5', 'final_c5.json'), ('c3', 'bench_c3.json'),
-                ('c4', 'bench_c4.json'), ('reference_arm', 'final_reference.json')):
+                ('c4', 'bench_c4.json'), ('mah', 'bench_mah.json'),
+                ('reference_arm', 'final_reference.json')):
     b = os.path.join(G, src)
     if os.path.exists(b):
         open(os.path.join(P, '%s_bench_%s.json' % (tag, wl)), 'w').write(open(b).read())
