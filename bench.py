@@ -50,7 +50,11 @@ def parse():
     ap.add_argument('--warmup', type=int, default=300)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4', 'mah'])
-    ap.add_argument('--fuse', type=int, default=100, help='steps per fused launch')
+    ap.add_argument('--fuse', type=int, default=0,
+                    help='steps per fused launch; 0 = per workload: 100 (what BASELINE.json states for '
+                         'c5), 500 for the 4096-env rings c2 / ma, whose 100-step launch is short '
+                         'enough (53 us) for its ramp and drain to cost 10 %% (measured: 1.51e11 at '
+                         '100, 1.61e11 at 250, 1.66e11 at 500, 1.69e11 at 1000 vehicle-steps/s)')
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     ap.add_argument('--noise', type=float, default=0.2,
                     help='IDM accel noise std (0.2 in singleagent_ring.py; 0 = parity setting)')
@@ -256,7 +260,8 @@ def run_b200(a):
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 
     wl = WORKLOADS[a.workload]
-    E, K, W, F = (a.envs or wl['n_envs']), a.steps, a.warmup, max(1, min(a.fuse, a.steps))
+    fuse = a.fuse or (500 if a.workload in ('c2', 'ma') else 100)
+    E, K, W, F = (a.envs or wl['n_envs']), a.steps, a.warmup, max(1, min(fuse, a.steps))
     types, tov, kw = wl['builder'](noise=a.noise)
     kw['horizon'] = max(kw['horizon'], K)
     if a.scaling == 'strong':

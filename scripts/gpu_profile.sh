@@ -6,7 +6,7 @@ python bench.py --steps 300 --warmup 100 --no-cpu-baseline > gpurun_out/prof_pla
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_c2.csv \
     python bench.py --steps 300 --warmup 100 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 3 -c 1 -o gpurun_out/prof_c2_final \
-    python bench.py --steps 300 --warmup 100 --no-cpu-baseline --only-fused > gpurun_out/ncu_full_c2.log 2>&1
+    python bench.py --steps 1000 --warmup 500 --no-cpu-baseline --only-fused > gpurun_out/ncu_full_c2.log 2>&1
 python bench.py --workload c5 --steps 200 --warmup 100 --no-cpu-baseline --only-fused > gpurun_out/prof_plain_c5.json 2> gpurun_out/prof_plain_c5.err || exit 1
 ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 3 -c 1 -o gpurun_out/prof_c5_final \
     python bench.py --workload c5 --steps 200 --warmup 100 --no-cpu-baseline --only-fused > gpurun_out/ncu_full_c5.log 2>&1

@@ -63,14 +63,16 @@ for wl in ('c2', 'c5', 'c3', 'c4'):
                          capture_output=True, text=True).stdout
     open(os.path.join(P, '%s_ncu_full_%s_%s_f32.csv' % (tag, wl, KERNEL[wl] if wl in ('c3', 'c4') else 'ring1_hot')), 'w').write(
         '# ncu --set full --clock-control none --import-source on -k regex:%s, one timed '
-        'fused launch (100 steps) of python bench.py --workload %s --only-fused\n' % (KERNEL[wl], wl) + out)
+        'fused launch (%d steps) of python bench.py --workload %s --only-fused\n'
+        % (KERNEL[wl], 500 if wl == 'c2' else 100, wl) + out)
     rows = list(csv.reader(open(raw)))
     h, u, r = rows[0], rows[1], rows[2]
     def val(k):
         i = h.index(k)
         x = float(r[i])
         return x * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u[i]]
-    traffic['%s_f32_fuse100' % wl] = val('dram__bytes_read.sum') + val('dram__bytes_write.sum')
+    traffic['%s_f32_fuse%d' % (wl, 500 if wl == 'c2' else 100)] = \
+        val('dram__bytes_read.sum') + val('dram__bytes_write.sum')
 rep = os.path.join(G, 'prof_c5_single.ncu-rep')
 raw = os.path.join(G, 'prof_c5_single_raw.csv')
 if os.path.exists(rep):

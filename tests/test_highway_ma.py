@@ -207,3 +207,46 @@ def test_gpu_flow_api_multiagent_highway_dicts():
     assert 'rl_0' in arrived and len(arrived) == len(set(arrived)) >= 3
     assert any(n.startswith('rl_in_0.') for n in names)
     env.terminate()
+
+
+@pytest.mark.gpu
+def test_gpu_flow_api_multiagent_highway_batched_tensors():
+    """n_envs > 1: tensors [E, A, 5] / [E, A] / [E] + agent ids; every env of the batch equals
+    the single-env dict run under the same policy (fp64)."""
+    import torch
+    from flow_b200 import flow_api as F
+
+    def build(n_envs):
+        veh = F.VehicleParams()
+        veh.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=0)
+        veh.add('rl', acceleration_controller=(F.RLController, {}), num_vehicles=1)
+        flows = F.InFlows()
+        flows.add(veh_type='rl', edge='highway_0', vehs_per_hour=360, depart_speed=10, begin=5,
+                  name='rl_in')
+        flows.add(veh_type='human', edge='highway_0', probability=0.15, depart_speed=12, begin=5)
+        net = F.NetParams(inflows=flows, additional_params=dict(
+            length=600, lanes=1, speed_limit=30, num_edges=1))
+        env_params = F.EnvParams(horizon=1500, additional_params=dict(
+            max_accel=1, max_decel=1, target_velocity=25, max_agents=8))
+        network = F.HighwayNetwork('hw', veh, net, F.InitialConfig(x0=100))
+        return F.MultiAgentHighwayPOEnv(env_params, F.SumoParams(sim_step=0.2), network,
+                                        n_envs=n_envs, dtype='f64', seed=9)
+    one, many = build(1), build(3)
+    o1, om = one.reset(), many.reset()
+    assert om.shape == (3, 8, 5)
+    for t in range(250):
+        a = torch.clamp(2.0 * om[:, :, 1] * 30, -3.0, 0.5)
+        a1 = {k: [float(np.clip(2.0 * v[1] * 30, -3.0, 0.5))] for k, v in o1.items() if v is not None}
+        om, rm, dm, info = many.step(a)
+        o1, r1, d1, _ = one.step(a1)
+        ids = info['agent_id'][0].cpu().numpy()        # env 0 of the batch = the single env (gid 0)
+        names = [one.vehicle_name(v) for v in ids if v >= 0]
+        assert names == [k for k, v in o1.items() if v is not None], t
+        for row, k in enumerate(names):
+            assert np.array_equal(om[0, row].cpu().numpy(), o1[k]), (t, k)
+            assert float(rm[0, row]) == r1[k], (t, k)
+        assert bool(dm[0]) == d1['__all__']
+    # the probabilistic human inflow is keyed by the env id: the envs of the batch differ
+    c = many.engine.counters.cpu().numpy()
+    assert len(set(c[1])) > 1
+    one.terminate(); many.terminate()
