@@ -334,3 +334,55 @@ def test_fuzz_highway_multiagent_vs_oracle_fp64(seed):
             now = [h.ids[s] for s in h.rl_slots()][:A]
             for a, vid in enumerate(now):
                 assert close(er[0, a], rw[vid]) <= 1e-9, (k, a, er[0, a], rw[vid])
+
+
+# ------------------------------------------------- inflow kinds (periodic / end / probabilistic)
+@pytest.mark.parametrize('seed', range(16))
+def test_fuzz_highway_inflow_kinds_vs_oracle_fp64(seed):
+    """One to four flows drawn from {periodic, periodic with an end, probabilistic, probabilistic
+    with an end}, random seeds and env_id_base: per env, arrivals / occupancy / trajectories equal
+    the oracle's over two episodes (the Philox stream is keyed by seed, GLOBAL env id, episode,
+    flow and step)."""
+    from oracle import highway as OH
+    from flow_b200 import engine as EN
+    rng = np.random.default_rng(12000 + seed)
+    groups = [S.vt('IDM', 0), S.vt(str(rng.choice(['OVM', 'SIM', 'IDM'])), 0)]
+    flows = []
+    for _ in range(int(rng.integers(1, 5))):
+        kind = int(rng.integers(0, 4))
+        end = float(rng.choice([8.0, 15.0])) if kind & 1 else 0.0
+        if kind & 2:
+            flows.append((int(rng.integers(0, 2)), 0.0, float(rng.choice([5.0, 12.0])),
+                          float(rng.choice([0.0, 1.0])), end, float(rng.choice([0.1, 0.3, 1.0]))))
+        else:
+            flows.append((int(rng.integers(0, 2)), float(rng.choice([400.0, 1200.0])),
+                          float(rng.choice([5.0, 12.0])), float(rng.choice([0.0, 1.0])), end, 0.0))
+    dt = float(rng.choice([0.1, 0.2]))
+    sd, base = int(rng.integers(0, 2 ** 40)), int(rng.choice([0, 7, 2 ** 33]))
+    E = 2
+    eng = EN.Engine(S.engine_types(groups), [], E, dtype='f64', capacity=64, topology=EN.TOPO_HIGHWAY,
+                    env_kind=EN.ENV_HIGHWAY, length_lo=400.0, length_hi=400.0, sim_step=dt, seed=sd,
+                    env_id_base=base, horizon=3000, inflows=flows, record_views=1)
+    sims = [OH.HighwaySim(S.oracle_types(groups), [], capacity=64, length=400.0, dt=dt,
+                          inflows=[dict(type=t, vehs_per_hour=q, depart_speed=v, begin=b, end=en,
+                                        probability=p) for t, q, v, b, en, p in flows],
+                          seed=sd, env_gid=base + g) for g in range(E)]
+    for episode in range(2):
+        eng.reset()
+        if episode:
+            for h in sims:
+                h.reset()
+        for k in range(150):
+            eng.step()
+            for h in sims:
+                h.step()
+            c = eng.counters.cpu().numpy()
+            for g, h in enumerate(sims):
+                assert (c[:, g] == [len(h.pos), h.departed, h.arrived]).all(), (episode, k, g)
+            if k % 10 == 9:
+                for g, h in enumerate(sims):
+                    n = len(h.pos)
+                    assert close(eng.pos.cpu().numpy()[:n, g], h.pos) <= 1e-9, (episode, k, g)
+                    assert bool(eng.crash.cpu().numpy()[g]) == h.crash
+            if any(h.done for h in sims):
+                break
