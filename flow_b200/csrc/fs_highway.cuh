@@ -371,9 +371,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       if (cfg.evaluate) reward = N::div(sv, T(n));   // accel.py:111-112 (np.mean: NaN when empty)
       else if (crash || n == 0) reward = T(0);
       else {  // rewards.desired_velocity over the vehicles present
-        T mc2 = T(0);
+        // || [v_t] * n ||: n equal squares; their sum is exact (and so independent of numpy's
+        // summation order) whenever v_t^2 * n is representable, which one multiply gives as well
         const T t2 = mul(cfg.target_velocity, cfg.target_velocity);
-        for (int i = 0; i < n; ++i) mc2 = add(mc2, t2);
+        const T mc2 = mul(t2, T(n));
         const T max_cost = N::sqrt(mc2), cost = N::sqrt(sq);
         reward = N::div(N::max(max_cost - cost, T(0)), add(max_cost, T(1.1920928955078125e-07)));
       }
