@@ -141,13 +141,16 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   update();
 
   // RL vehicles present, ranked head first: rank a <-> action row a <-> observation row a
+  unsigned rl_types = 0;   // bit t: type t is driven by RL actions (no table lookup per slot and step)
+  if (kMA)
+    for (int t = 0; t < cfg.n_types; ++t) rl_types |= (cfg.types[t].ctrl == FS_CTRL_RL ? 1u : 0u) << t;
   auto rank_agents = [&]() {
     if (!kMA) return;
     n_rl = 0;
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
       const int s = lane_id + 32 * r;
-      const bool rl = s < n && cfg.types[ty[r]].ctrl == FS_CTRL_RL;
+      const bool rl = s < n && ((rl_types >> ty[r]) & 1u);
       const unsigned m = __ballot_sync(0xffffffffu, rl);
       rank[kMA ? r : 0] = rl ? n_rl + __popc(m & ((1u << lane_id) - 1u)) : -1;
       n_rl += __popc(m);
