@@ -386,6 +386,11 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     }
   }
   if (e->cfg.topology == FS_TOPO_HIGHWAY) {
+    // inflow vehicles may be of a type no initial vehicle has: look at every type
+    for (int t = 0; t < n_types; ++t) {
+      const int c = types[t].controller;
+      if (c != FS_CTRL_IDM && c != FS_CTRL_SIM && c != FS_CTRL_RL) e->generic = true;
+    }
     if (e->cfg.n_initial < 0 || e->cfg.n_initial > e->cfg.n_veh)
       return fail(e, FS_EINVAL, "fs_set_types: n_initial must be within the slot capacity");
     if (e->cfg.inflow_type < 0 || e->cfg.inflow_type >= n_types)
@@ -532,8 +537,10 @@ static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
   const fs::HwBufs<T> b = hw_bufs<T>(e);
   const auto& cfg = cfg_of<T>(e);
   constexpr int NF = FS_MAX_INFLOWS;
+#define FS_HW2(SL, MA, F, PR, GEN) \
+  fs::highway_kernel<T, SL, MA, F, PR, GEN><<<grid, wpb * 32, smem, e->stream>>>(cfg, b, a)
 #define FS_HW(SL, MA, F, PR) \
-  fs::highway_kernel<T, SL, MA, F, PR><<<grid, wpb * 32, smem, e->stream>>>(cfg, b, a)
+  do { if (e->generic) FS_HW2(SL, MA, F, PR, true); else FS_HW2(SL, MA, F, PR, false); } while (0)
   bool any_prob = false;
   for (int f = 0; f < e->n_flows; ++f) any_prob |= b.prob[f] > 0.0 || b.end[f] > 0.0;
   if (e->ma_highway()) {
@@ -544,6 +551,7 @@ static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
     if (CAP <= 64) FS_HW(2, false, NF, true); else if (CAP <= 160) FS_HW(5, false, NF, true); else FS_HW(8, false, NF, true);
   }
 #undef FS_HW
+#undef FS_HW2
   e->launches++;
   FS_CUDA(e, cudaGetLastError());
   return FS_OK;

@@ -60,8 +60,10 @@ __host__ __device__ inline size_t hw_smem_per_warp(int cap) {
 }
 
 // NF = inflows compiled in (1: the single <flow> of c4; FS_MAX_INFLOWS otherwise);
-// kProb = probabilistic flows and flow ends compiled in
-template <typename T, int SLOTS, bool kMA, int NF, bool kProb>
+// kProb = probabilistic flows and flow ends compiled in;
+// kGeneric = false: every type follows the IDM law (IDM, or the simulator model of SIM / RL
+// vehicles), so the controller switch, follower and mean-speed inputs are compiled out
+template <typename T, int SLOTS, bool kMA, int NF, bool kProb, bool kGeneric>
 __global__ void __launch_bounds__(128)
 highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -233,7 +235,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     const bool done_before = done;
     if (!done) {
       T mean_v = T(0);
-      if (cfg.any_follower & 2) {
+      if (kGeneric && (cfg.any_follower & 2)) {
         T sm = T(0);
 #pragma unroll
         for (int r = 0; r < SLOTS; ++r) if (lane_id + 32 * r < n) sm = add(sm, v[r]);
@@ -251,8 +253,13 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         const T vi = v[r], hi = h[r];
         const T vl = has_lead ? vs[s - 1] : T(-1001);
         T st0 = T(0);
-        T a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, has_f, has_f ? vs[s + 1] : T(-1001),
+        T a;
+        if (kGeneric)
+          a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, has_f, has_f ? vs[s + 1] : T(-1001),
                             has_f ? hs[s + 1] : T(-1001), mean_v, dt, cfg.inv_dt, st0);
+        else   // the same arithmetic as ctrl_accel's IDM / SIM cases (fs_ring.cuh does the same)
+          a = idm_accel<T>(vi, vl, hi, has_lead, tp.e_v0, tp.e_inv_v0, tp.e_T, tp.e_a, tp.e_tsab,
+                           tp.e_inv_tsab, tp.e_delta, tp.e_s0);
         if (kMA && ctrl == FS_CTRL_RL && A.actions != nullptr && rank[kMA ? r : 0] < AG) {
           // MultiAgentHighwayPOEnv._apply_rl_actions: apply_acceleration(rl_id, actions[0]),
           // not clipped; NaN = this agent got no command (stays with the simulator model)
