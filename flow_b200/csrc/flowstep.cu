@@ -491,7 +491,13 @@ static int launch_ml(fs_engine* e, const fs::StepArgs<T>& a) {
     const int grid = (E + wpb - 1) / wpb;
     const size_t smem = (size_t)wpb * fs::ml_smem_per_env<T>(V, 1);
     if (V <= 32) fs::ring_ml_kernel<T, 1, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
-    else if (V <= 96) fs::ring_ml_kernel<T, 3, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    else if (V <= 96) {
+      // IDM-law instantiation (no controller switch, no follower search): c3 9.10 -> 8.39 us per
+      // step; FS_ML_GENERIC=1 keeps the generic instantiation (A/B)
+      static const bool idm_only = !(getenv("FS_ML_GENERIC") && atoi(getenv("FS_ML_GENERIC")) != 0);
+      if (e->generic || !idm_only) fs::ring_ml_kernel<T, 3, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+      else fs::ring_ml_kernel<T, 3, 1, false><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
+    }
     else fs::ring_ml_kernel<T, 8, 1><<<grid, wpb * 32, smem, e->stream>>>(cfg_of<T>(e), b, a);
   }
   e->launches++;

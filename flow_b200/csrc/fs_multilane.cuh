@@ -54,7 +54,9 @@ __host__ __device__ inline size_t ml_smem_per_env(int V, int W) {
 // W > 1 (FS_ML_SPLIT=1, experiment kept under test): ONE BLOCK of W warps owns an env,
 //        vehicle i = tid + 32 W s; warp collectives become block collectives (__syncthreads,
 //        shared-memory partials). Same results; slower on c3 (see launch_ml in flowstep.cu).
-template <typename T, int SLOTS, int W>
+// kGeneric = false: every type follows the IDM law (IDM, or the simulator model of SIM / RL
+// vehicles): no controller switch, no follower search, no controller state
+template <typename T, int SLOTS, int W, bool kGeneric = true>
 __global__ void __launch_bounds__(128)
 ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -238,7 +240,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
       }
     }
   };
-  const bool want_foll = (cfg.any_follower & 1) || A.write_views;
+  const bool want_foll = (kGeneric && (cfg.any_follower & 1)) || A.write_views;
   update(want_foll);
 
   int tc = B.time_counter[e];
@@ -364,7 +366,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
     if (k + 1 < A.k_steps) fetch_actions(k + 1);
     if (!done) {
       T mean_v = T(0);
-      if (cfg.any_follower & 2) {
+      if (kGeneric && (cfg.any_follower & 2)) {
         T sm = T(0);
 #pragma unroll
         for (int s = 0; s < SLOTS; ++s) if (tid + NT * s < V) sm = add(sm, v[s]);
@@ -469,6 +471,9 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const MlBufs<T> B, const Step
           const T raw = act_a[s];
           a = N::min(N::max(raw, cfg.act_lo), cfg.act_hi);
           act_abs_sum = add(act_abs_sum, N::abs(cfg.clip_actions ? a : raw));
+        } else if (!kGeneric) {   // same arithmetic as ctrl_accel's IDM / SIM cases
+          a = idm_accel<T>(vi, vl, hi, has_lead, tp.e_v0, tp.e_inv_v0, tp.e_T, tp.e_a, tp.e_tsab,
+                           tp.e_inv_tsab, tp.e_delta, tp.e_s0);
         } else if (ctrl == FS_CTRL_PI_SATURATION) {
           T v_cmd = B.st0[(size_t)i * E + e];
           RingBufs<T> rb;
