@@ -182,10 +182,14 @@ class RefRing:
 
     def __init__(self, groups, length, env_kind='accel', dt=0.1, lanes=1,
                  speed_limit=30, init_kw=None, env_additional=None,
-                 warmup_steps=0, horizon=3000, clip_actions=False):
+                 warmup_steps=0, horizon=3000, clip_actions=False, index_shortcut=False):
         """groups: list of (name, controller_class_or_'rl', ctrl_kwargs,
         SumoCarFollowingParams kwargs, count)."""
         self.dt = self.sim_step = dt
+        # bench.py's CPU arm: let the restated SUMO part use the single-lane leader = i+1
+        # shortcut (same answer, oracle/sim.py RingSim.update) so that the time measured is the
+        # reference's own Python, not the O(V^2) restatement of SUMO's C++ leader search
+        self.index_shortcut = index_shortcut
         self.ids, self.ctrl, self.rl_idx = [], [], []
         self.sim_ctrl = {}
         for name, cls, kw, cf_kw, n in groups:
@@ -225,7 +229,8 @@ class RefRing:
         # borrow the restated leader search
         shim = type('S', (), {})()
         shim.num_vehicles = len(self.ids)
-        shim.n_lanes = 0  # always the general per-lane search, never the shortcut
+        # golden generation: always the general per-lane search, never the shortcut
+        shim.n_lanes = self.lanes if self.index_shortcut else 0
         shim.lane, shim.pos, shim.circ = self.lane, self.pos, self.net.circ
         from oracle.controllers import VType
         shim.types, shim.type_of = [VType()], [0] * len(self.ids)

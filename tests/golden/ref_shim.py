@@ -4,14 +4,30 @@ container so golden vectors can be generated from its own code.
 The reference needs third-party packages that are absent here (gym, traci,
 sumolib, lxml, pyglet, matplotlib, imutils, pyprind, ...). None of them does
 arithmetic on the step path, so inert stand-ins are placed in sys.modules.
-Only used by make_golden.py and by tests that skip when /root/reference is
-missing (it does not exist on the GPU box).
+Used by make_golden.py, by tests that skip when no reference package is importable, and by
+bench.py's CPU arm (kind "reference"). On the GPU box /root/reference does not exist; the
+reference's package is then imported from baseline/_ref, the unmodified offline install of
+/root/reference (`pip install --no-index --no-deps --target baseline/_ref`).
 """
 import os
 import sys
 import types
 
-REF = os.environ.get('FLOW_REFERENCE', '/root/reference')
+_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def _find():
+    """The read-only checkout in the build container, else the offline install of the same
+    package under baseline/_ref (pip install --target, see __graft_entry__.build): git-ignored,
+    NOT gpurun-ignored, so it travels to the GPU box."""
+    for p in (os.environ.get('FLOW_REFERENCE'), '/root/reference',
+              os.path.join(_ROOT, 'baseline', '_ref')):
+        if p and os.path.isdir(os.path.join(p, 'flow', 'controllers')):
+            return p
+    return '/root/reference'
+
+
+REF = _find()
 
 
 def available():
