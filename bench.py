@@ -485,9 +485,11 @@ class Leg:
 
     def call_host_closed_loop(self, k):
         h, c = self._host_slot(k)
-        a = h['act']
+        if 'act_np' not in h:
+            h['act_np'] = h['act'].numpy()
+        a, step = h['act_np'], self.env.step_host
         for s in range(c, c + k):
-            self.env.step_host(a[s])
+            step(a[s] if self.A else None)
 
     # ---- timing
     def barrier(self):
@@ -738,8 +740,9 @@ def run_b200(a):
             'blocking': dict(brief(hb), api='B200VecEnv.rollout_host -> fs_step_host, %d steps per call, '
                              'every call waits for its results' % info['fuse']),
             'closed_loop': dict(brief(hc), api='B200VecEnv.step_host -> fs_step_host(k=1): ONE Env.step per '
-                                'call, pinned host action in, obs / reward / done on the host before the '
-                                'next call (the gym cadence of Env.step(policy(obs)))')}
+                                'call, host action copied into the engine\'s pinned staging block, upload -> '
+                                'kernel -> one download replayed as one CUDA graph, obs / reward / done on '
+                                'the host before the next call (the gym cadence of Env.step(policy(obs)))')}
     if legs:
         line['legs'] = legs
     if world == 1 and not a.no_cpu_baseline and not a.only_fused:

@@ -12,9 +12,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
 SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
-SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu']
-HEADERS = ['fs_common.cuh', 'fs_ring.cuh', 'fs_ring_fast.cuh', 'fs_ring_hot.cuh', 'fs_reset.cuh', 'fs_launch.h',
-           'fs_multilane.cuh', 'fs_highway.cuh', 'fs_sort.cuh']
+SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu', 'fs_ring_f32.cu', 'fs_ring_f64.cu',
+           'fs_ml_f32.cu', 'fs_ml_f64.cu', 'fs_hw_f32.cu', 'fs_hw_f64.cu']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -58,7 +57,7 @@ class FsConfig(C.Structure):
                 ('max_agents', C.c_int32), ('reserved0', C.c_int32)]
 
 
-FS_ABI_VERSION = 2
+FS_ABI_VERSION = 3
 FS_MAX_INFLOWS = 4
 
 
@@ -73,6 +72,13 @@ class FsAgentViews(C.Structure):
                 ('agent_id', C.c_void_p), ('veh_id', C.c_void_p),
                 ('veh_type', C.c_void_p),
                 ('max_agents', C.c_int32), ('obs_per_agent', C.c_int32)]
+
+
+class FsHostViews(C.Structure):
+    _fields_ = [('actions', C.c_void_p), ('obs', C.c_void_p), ('reward', C.c_void_p),
+                ('done', C.c_void_p),
+                ('k', C.c_int32), ('n_envs', C.c_int32), ('obs_dim', C.c_int32),
+                ('act_dim', C.c_int32), ('dtype', C.c_int32), ('reserved', C.c_int32)]
 
 
 class FsViews(C.Structure):
@@ -100,6 +106,7 @@ SYMBOLS = [
     ('fs_step', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_unfused', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_host_staging', C.c_int, [C.c_void_p, C.c_int, C.POINTER(FsHostViews)]),
     ('fs_step_host_async', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_buffers', C.c_int, [C.c_void_p, C.POINTER(FsViews)]),
     ('fs_dlpack_wrap', C.c_void_p, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -119,44 +126,98 @@ NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
               '-std=c++17', '-Xcompiler', '-fPIC']
 
 
-def _stale():
-    if not os.path.exists(SO_PATH):
+def _deps(path, seen=None):
+    """`path` plus every header it includes (transitively, quoted includes only)."""
+    import re
+    seen = set() if seen is None else seen
+    if path in seen or not os.path.exists(path):
+        return seen
+    seen.add(path)
+    for inc in re.findall(r'^\s*#include\s+"([^"]+)"', open(path).read(), re.M):
+        _deps(os.path.normpath(os.path.join(os.path.dirname(path), inc)), seen)
+    return seen
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
         return True
-    t = os.path.getmtime(SO_PATH)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
-    deps.append(os.path.join(ROOT, 'include', 'flowstep.h'))
-    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+HASH_PATH = SO_PATH + '.srchash'
+
+
+def _src_hash():
+    """Content hash of every source / header / compiler flag the library is built from
+    (mtimes do not survive the snapshot copy to the GPU box; contents do)."""
+    import hashlib
+    deps = set()
+    for src in SOURCES:
+        _deps(os.path.join(CSRC, src), deps)
+    h = hashlib.sha256(' '.join(NVCC_FLAGS).encode())
+    for d in sorted(deps):
+        h.update(os.path.relpath(d, ROOT).encode())
+        h.update(open(d, 'rb').read())
+    return h.hexdigest()
+
+
+def _stale():
+    """True when libflowstep.so was not built from the sources that are in the tree now."""
+    if not os.path.exists(SO_PATH) or not os.path.exists(HASH_PATH):
+        return True
+    return open(HASH_PATH).read().strip() != _src_hash()
 
 
 def build(force=False, verbose=False):
-    """Compile libflowstep.so for sm_100a with nvcc (cross-compiles without a GPU)."""
+    """Compile libflowstep.so for sm_100a with nvcc (cross-compiles without a GPU): one
+    translation unit per kernel family and dtype, compiled in parallel; only units whose
+    sources or headers changed are recompiled unless `force`. The library is written to a
+    temporary name and renamed, and the whole build holds a file lock, so concurrent ranks
+    never load a half-written file."""
     if not force and not _stale():
         return SO_PATH
+    import fcntl
     nvcc = os.environ.get('NVCC', 'nvcc')
     bdir = os.path.join(_HERE, 'build')
     os.makedirs(bdir, exist_ok=True)
-    extra = ['-Xptxas', '-v'] if verbose else []
-    if os.environ.get('FS_HOT_EXPERIMENTS'):   # timing variants of the hot kernel (FS_HOT_VAR)
-        extra.append('-DFS_HOT_EXPERIMENTS')
-    procs = []
-    for src in SOURCES:   # one nvcc per translation unit, in parallel
-        obj = os.path.join(bdir, src.replace('.cu', '.o'))
-        cmd = [nvcc] + NVCC_FLAGS + extra + ['-c', '-o', obj, os.path.join(CSRC, src)]
-        procs.append((cmd, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE,
-                                                  stderr=subprocess.PIPE, text=True)))
-    objs = []
-    for cmd, obj, p in procs:
-        out, err = p.communicate()
-        if p.returncode != 0:
-            raise RuntimeError('nvcc failed:\n%s\n%s' % (' '.join(cmd), err[-4000:]))
-        if verbose:
-            print(err)
-        objs.append(obj)
-    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', SO_PATH] + objs
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError('link failed:\n%s\n%s' % (' '.join(cmd), res.stderr[-4000:]))
-    return SO_PATH
+    lock = open(os.path.join(bdir, '.lock'), 'w')
+    fcntl.flock(lock, fcntl.LOCK_EX)
+    try:
+        if not force and not _stale():      # another process built it while we waited
+            return SO_PATH
+        extra = ['-Xptxas', '-v'] if verbose else []
+        procs, objs = [], []
+        for src in SOURCES:
+            path = os.path.join(CSRC, src)
+            obj = os.path.join(bdir, src.replace('.cu', '.o'))
+            objs.append(obj)
+            if not force and not _newer(obj, _deps(path)):
+                continue
+            cmd = [nvcc] + NVCC_FLAGS + extra + ['-c', '-o', obj, path]
+            procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE,
+                                                stderr=subprocess.PIPE, text=True)))
+        failed = None
+        for cmd, p in procs:
+            out, err = p.communicate()
+            if p.returncode != 0 and failed is None:
+                failed = 'nvcc failed:\n%s\n%s' % (' '.join(cmd), err[-4000:])
+            if verbose:
+                print(err)
+        if failed:
+            raise RuntimeError(failed)
+        tmp = SO_PATH + '.tmp.%d' % os.getpid()
+        cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError('link failed:\n%s\n%s' % (' '.join(cmd), res.stderr[-4000:]))
+        os.replace(tmp, SO_PATH)
+        with open(HASH_PATH, 'w') as f:
+            f.write(_src_hash())
+        return SO_PATH
+    finally:
+        fcntl.flock(lock, fcntl.LOCK_UN)
+        lock.close()
 
 
 _lib = None
@@ -167,13 +228,21 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(SO_PATH):
+    if not os.path.exists(SO_PATH) or _stale():
+        # edited sources must never run against an old binary; without nvcc (a box that only
+        # received the built library) a missing library is fatal, a stale one is reported
         try:
             build()
-        except Exception as exc:  # no nvcc on this machine
-            raise RuntimeError(
-                'libflowstep.so is not built (run python -c "import '
-                '__graft_entry__ as g; g.build()"): %s' % exc)
+        except Exception as exc:
+            if not os.path.exists(SO_PATH):
+                raise RuntimeError(
+                    'libflowstep.so is not built (run python -c "import '
+                    '__graft_entry__ as g; g.build()"): %s' % exc)
+            import shutil
+            if shutil.which(os.environ.get('NVCC', 'nvcc')):
+                raise
+            import warnings
+            warnings.warn('libflowstep.so is older than its sources and nvcc is absent: %s' % exc)
     lib = C.CDLL(SO_PATH)
     for name, restype, argtypes in SYMBOLS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing

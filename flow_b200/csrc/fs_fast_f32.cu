@@ -1,6 +1,7 @@
 // fs_fast_f32.cu — fp32 instantiations of the IDM-ring hot kernel (own
 // translation unit so the variants compile in parallel with the rest).
 #include "fs_ring_fast.cuh"
+#include "fs_ring_hot.cuh"
 #include "fs_launch.h"
 
 cudaError_t fs_launch_fast22_f32(int shape, int variant, int n_envs, cudaStream_t st,

@@ -1,5 +1,6 @@
 // fs_fast_f64.cu — fp64 (parity mode) instantiations of the IDM-ring hot kernel.
 #include "fs_ring_fast.cuh"
+#include "fs_ring_hot.cuh"
 #include "fs_launch.h"
 
 cudaError_t fs_launch_fast22_f64(int shape, int variant, int n_envs, cudaStream_t st,

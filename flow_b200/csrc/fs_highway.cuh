@@ -497,4 +497,27 @@ __global__ void highway_reset_kernel(const __grid_constant__ Cfg<T> cfg, const H
   B.done[e] = 0; B.crash[e] = 0;
 }
 
+// host-side dispatch (instantiated in fs_hw_f32.cu / fs_hw_f64.cu). multi_agent:
+// FS_ENV_MA_HIGHWAY_PO; single_periodic: one periodic <flow> without end (c4)
+template <typename T>
+static cudaError_t launch_hw_impl(int cap, bool multi_agent, bool single_periodic, bool generic,
+                                  int grid, int block, size_t smem, cudaStream_t st,
+                                  const Cfg<T>& cfg, const HwBufs<T>& b, const StepArgs<T>& a) {
+  constexpr int NF = FS_MAX_INFLOWS;
+#define FS_HW2(SL, MA, F, PR, GEN) \
+  highway_kernel<T, SL, MA, F, PR, GEN><<<grid, block, smem, st>>>(cfg, b, a)
+#define FS_HW(SL, MA, F, PR) \
+  do { if (generic) FS_HW2(SL, MA, F, PR, true); else FS_HW2(SL, MA, F, PR, false); } while (0)
+  if (multi_agent) {
+    if (cap <= 64) FS_HW(2, true, NF, true); else if (cap <= 160) FS_HW(5, true, NF, true); else FS_HW(8, true, NF, true);
+  } else if (single_periodic) {
+    if (cap <= 64) FS_HW(2, false, 1, false); else if (cap <= 160) FS_HW(5, false, 1, false); else FS_HW(8, false, 1, false);
+  } else {
+    if (cap <= 64) FS_HW(2, false, NF, true); else if (cap <= 160) FS_HW(5, false, NF, true); else FS_HW(8, false, NF, true);
+  }
+#undef FS_HW
+#undef FS_HW2
+  return cudaGetLastError();
+}
+
 }  // namespace fs

@@ -430,4 +430,19 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
   }
 }
 
+// host-side dispatch of the generic ring kernel (instantiated in fs_ring_f32.cu / fs_ring_f64.cu)
+template <typename T>
+static cudaError_t launch_ring1_impl(int V, int E, cudaStream_t st, const Cfg<T>& c,
+                                     const RingBufs<T>& b, const StepArgs<T>& a) {
+  const int G = V <= 8 ? 1 : (V <= 32 ? 4 : 32);
+  const int epw = 32 / G;
+  const int warps = (E + epw - 1) / epw;
+  const int wpb = warps <= 148 * 8 ? 1 : (warps <= 148 * 32 ? 2 : 4);
+  const int grid = (warps + wpb - 1) / wpb;
+  if (G == 1) ring1_kernel<T, 8, 1, true, true><<<grid, wpb * 32, 0, st>>>(c, b, a);
+  else if (G == 4) ring1_kernel<T, 8, 4, true, true><<<grid, wpb * 32, 0, st>>>(c, b, a);
+  else ring1_kernel<T, 8, 32, true, true><<<grid, wpb * 32, 0, st>>>(c, b, a);
+  return cudaGetLastError();
+}
+
 }  // namespace fs

@@ -252,6 +252,42 @@ class Engine:
             None if obs is None else obs.ctypes.data, rew.ctypes.data, done.ctypes.data))
         return obs, rew, done
 
+    def host_staging(self, k=1):
+        """The engine's pinned host block for closed-loop calls of k <= 8 steps
+        (fs_host_staging): numpy views (actions [k, act_dim, E], obs [k, E, obs_dim],
+        reward [k, E], done [k, E]) plus their raw addresses. Writing actions into the view
+        and calling step_staged() costs no host-side copy; the outputs are overwritten by the
+        next call."""
+        hv = _lib.FsHostViews()
+        self._check(self.lib.fs_host_staging(self.h, int(k), C.byref(hv)))
+        E, ct = self.n_envs, (C.c_double if self.dtype == 'f64' else C.c_float)
+
+        def arr(ptr, shape, ctype):
+            n = int(np.prod(shape))
+            if n == 0:
+                return np.empty(shape, self.np_dtype)
+            return np.ctypeslib.as_array((ctype * n).from_address(ptr)).reshape(shape)
+        self._staging = dict(
+            k=hv.k, ptr=(hv.actions, hv.obs, hv.reward, hv.done),
+            actions=arr(hv.actions, (hv.k, self.act_dim, E), ct),
+            obs=arr(hv.obs, (hv.k, E, self.obs_dim), ct),
+            reward=arr(hv.reward, (hv.k, E), ct),
+            done=arr(hv.done, (hv.k, E), C.c_uint8))
+        return self._staging
+
+    def step_staged(self, k=1, with_actions=True):
+        """k <= 8 steps on the actions already written into host_staging()['actions'];
+        blocks until obs / reward / done of those steps are in the staging views."""
+        st = getattr(self, '_staging', None)
+        if st is None or st['k'] < k:
+            st = self.host_staging(max(k, 1))
+        pa, po, pr, pd = st['ptr']
+        rc = self.lib.fs_step_host(self.h, pa if (with_actions and self.act_dim) else None, k,
+                                   po, pr, pd)
+        if rc != 0:
+            self._check(rc)
+        return st
+
     def set_state(self, pos=None, vel=None, lane=None, lengths=None):
         f = lambda x, d: None if x is None else np.ascontiguousarray(x, dtype=d)  # noqa: E731
         pos, vel = f(pos, self.np_dtype), f(vel, self.np_dtype)

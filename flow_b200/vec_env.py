@@ -85,10 +85,20 @@ class B200VecEnv:
     def wait(self):
         self.engine.sync()
 
-    def step_host(self, actions_host):
-        a = np.asarray(actions_host).reshape(1, self.act_dim, self.n_envs)
-        obs, rew, done = self.rollout_host(a, 1)
-        return obs[0], rew[0], done[0], {}
+    def step_host(self, actions_host=None):
+        """One Env.step of every env with HOST data, the gym cadence obs = env.step(policy(obs)):
+        `actions_host` ([E] / [act_dim, E], numpy or CPU tensor; None = simulator model) is
+        copied into the engine's pinned staging block, the step runs as one replayed CUDA graph
+        (upload -> kernel -> one download) and the call returns when obs [E, obs_dim],
+        reward [E], done [E] are on the host. The returned arrays are views of the staging
+        block: valid until the next call."""
+        e = self.engine
+        st = getattr(e, '_staging', None) or e.host_staging(1)
+        if actions_host is not None:
+            # [E] broadcasts onto [act_dim = 1, E]; [act_dim, E] copies row for row
+            np.copyto(st['actions'][0], actions_host, casting='same_kind')
+        e.step_staged(1, with_actions=actions_host is not None)
+        return st['obs'][0], st['reward'][0], st['done'][0], {}
 
     def stats(self, reset=False):
         return self.engine.stats(reset)

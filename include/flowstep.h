@@ -15,7 +15,7 @@
  *                            flow/envs/base.py:414-560,
  *                            flow/envs/ring/wave_attenuation.py:157-210,
  *                            flow/core/kernel/network/base.py:263-391
- *   fs_step / fs_step_unfused / fs_step_host / fs_step_host_async
+ *   fs_step / fs_step_unfused / fs_step_host (+ fs_host_staging) / fs_step_host_async
  *                            Env.step (controllers, fail-safes, apply_acceleration,
  *                            simulation_step, k.update, get_state, compute_reward)
  *                            flow/envs/base.py:294-412
@@ -50,7 +50,7 @@
 extern "C" {
 #endif
 
-#define FS_ABI_VERSION 2
+#define FS_ABI_VERSION 3
 
 /* error codes */
 #define FS_OK 0
@@ -288,6 +288,25 @@ int fs_step_unfused(fs_engine* e, const void* actions, int k, void* obs_seq,
  * steps, copies obs/reward/done of every step back, and synchronises. */
 int fs_step_host(fs_engine* e, const void* actions, int k, void* obs_seq,
                  void* reward_seq, uint8_t* done_seq);
+
+/* Closed-loop cadence (Env.step(policy(obs)), flow/envs/base.py:294-412 called once per
+ * policy forward): calls of k <= 8 steps run through ONE pinned host block and ONE device block
+ * laid out [actions | obs | reward | done]; upload -> step kernel(s) -> ONE download are
+ * captured into a CUDA graph on the first call and replayed by one cudaGraphLaunch afterwards.
+ * The host block is mapped; FS_CL_MODE (read at fs_create) lets the kernel read the actions
+ * (bit 0) and / or write the results (bit 1) in place instead of using the copy engine - kept
+ * for A/B runs, not faster on the measured box (flowstep.cu, step_host_closed_loop). fs_host_staging hands out that pinned block: a caller that writes its actions
+ * into views.actions and passes the four pointers of `out` to fs_step_host pays no host-side
+ * copy at all; any other host buffer is copied through the block. The pointers stay valid
+ * until a later fs_host_staging call asks for a larger k, or fs_destroy. */
+typedef struct fs_host_views {
+  void* actions;        /* T  [k][act_dim][E]   pinned host                               */
+  void* obs;            /* T  [k][E][obs_dim]                                             */
+  void* reward;         /* T  [k][E]                                                      */
+  uint8_t* done;        /* u8 [k][E]                                                      */
+  int32_t k, n_envs, obs_dim, act_dim, dtype, reserved;
+} fs_host_views;
+int fs_host_staging(fs_engine* e, int k, fs_host_views* out);
 
 /* Pipelined form of fs_step_host for open-loop rollouts (the action sequence
  * is known up front): enqueues H2D actions -> k fused steps -> D2H results on

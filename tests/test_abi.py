@@ -25,7 +25,7 @@ def test_library_builds_and_exports_header_symbols():
     assert declared == bound, declared ^ bound
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.fs_abi_version() == 2
+    assert lib.fs_abi_version() == _lib.FS_ABI_VERSION == 3
 
 
 def test_struct_layouts_match_header():
@@ -42,7 +42,7 @@ def test_create_rejects_bad_arguments_without_gpu():
     c = _lib.FsConfig()
     assert lib.fs_create(C.byref(c), C.byref(h)) == -1       # abi_version 0
     assert b'abi_version' in lib.fs_last_error(None)
-    c.abi_version = 2
+    c.abi_version = _lib.FS_ABI_VERSION
     c.n_envs, c.n_veh, c.n_lanes, c.sim_step = 4, 1000, 1, 0.1
     assert lib.fs_create(C.byref(c), C.byref(h)) == -1       # n_veh > 256
     c.n_veh = 22
@@ -58,7 +58,7 @@ def test_no_cpu_fallback():
     lib = _lib.load()
     h = C.c_void_p()
     c = _lib.FsConfig()
-    c.abi_version, c.n_envs, c.n_veh, c.n_lanes, c.sim_step = 2, 4, 22, 1, 0.1
+    c.abi_version, c.n_envs, c.n_veh, c.n_lanes, c.sim_step = _lib.FS_ABI_VERSION, 4, 22, 1, 0.1
     assert lib.fs_create(C.byref(c), C.byref(h)) == -2       # FS_ECUDA
     assert b'no CPU path' in lib.fs_last_error(None)
 

@@ -221,27 +221,36 @@ def test_multilane_known_answers_of_the_reference_test():
     assert (obs[6:] == 0).all()                     # everyone at rest, other blocks untouched
 
 
-def test_block_per_env_mapping_gives_the_same_results(monkeypatch):
-    """FS_ML_SPLIT=1 (W warps per env, block collectives) against the default one-warp-per-env
-    mapping on c3 with noise: identical lanes, positions and rewards in fp64."""
+def test_uniform_type_instantiation_equals_the_table_driven_one(monkeypatch):
+    """kGeneric = false (one IDM-law human type + one RL type, parameters as kernel-argument
+    constants; the default for c3) against FS_ML_GENERIC=1 (per-vehicle type table), with noise
+    and lane changes, on c3 and on a sparser ring where the RL vehicles find gaps often:
+    identical lanes, positions, observations and rewards in fp64."""
     import torch
     from flow_b200 import workloads as W
     from flow_b200.vec_env import B200VecEnv
-    types, tov, kw = W.ring_c3(noise=0.2)
-    E, K = 33, 60
-    gen = torch.Generator(device='cuda'); gen.manual_seed(3)
-    act = torch.rand(K, 6, E, device='cuda', dtype=torch.float64, generator=gen) * 0.6 - 0.4
-    act[:, 1::2] = torch.round(act[:, 1::2] * 2.4 + 1.0).clamp(-1, 1)
-    out = []
-    for split in ('0', '1'):
-        monkeypatch.setenv('FS_ML_SPLIT', split)
-        env = B200VecEnv(types, tov, E, dtype='f64', seed=5, **kw)
-        env.reset()
-        rew = torch.empty(K, E, device='cuda', dtype=torch.float64)
-        obs = torch.empty(K, E, env.obs_dim, device='cuda', dtype=torch.float64)
-        env.rollout(act, obs, rew)
-        out.append((obs.cpu().numpy(), rew.cpu().numpy(), env.engine.lane.cpu().numpy(),
-                    env.engine.pos.cpu().numpy()))
-    assert np.array_equal(out[0][2], out[1][2])
-    assert close(out[0][3], out[1][3]) <= 1e-12 and close(out[0][0], out[1][0]) <= 1e-12
-    assert close(out[0][1], out[1][1]) <= 1e-12
+    types, _, kw = W.ring_c3(noise=0.2)
+    E, K = 33, 300
+    n_changed = 0
+    for tov in ([0] * 63 + [1] * 3, [0] * 9 + [1] + [0] * 10 + [1, 1] + [0] * 8):
+        n_rl = sum(tov)
+        gen = torch.Generator(device='cuda'); gen.manual_seed(3)
+        act = torch.rand(K, 2 * n_rl, E, device='cuda', dtype=torch.float64, generator=gen) * 0.6 - 0.4
+        act[:, 1::2] = torch.round(torch.rand(K, n_rl, E, device='cuda', dtype=torch.float64,
+                                              generator=gen) * 3 - 1.5)
+        out = []
+        for generic in ('0', '1'):
+            monkeypatch.setenv('FS_ML_GENERIC', generic)
+            env = B200VecEnv(types, tov, E, dtype='f64', seed=5, **kw)
+            env.reset()
+            lane0 = env.engine.lane.cpu().numpy().copy()
+            rew = torch.empty(K, E, device='cuda', dtype=torch.float64)
+            obs = torch.empty(K, E, env.obs_dim, device='cuda', dtype=torch.float64)
+            env.rollout(act, obs, rew)
+            out.append((obs.cpu().numpy(), rew.cpu().numpy(), env.engine.lane.cpu().numpy(),
+                        env.engine.pos.cpu().numpy()))
+        n_changed += int((out[0][2] != lane0).sum())
+        assert np.array_equal(out[0][2], out[1][2])
+        assert close(out[0][3], out[1][3]) <= 1e-12 and close(out[0][0], out[1][0]) <= 1e-12
+        assert close(out[0][1], out[1][1]) <= 1e-12
+    assert n_changed > 0      # the rebuild-on-lane-change path ran
