@@ -21,7 +21,7 @@ FS_MAX_TYPES = 16
 
 class FsVType(C.Structure):
     _fields_ = [('controller', C.c_int32), ('fail_safe', C.c_int32),
-                ('lc_controller', C.c_int32), ('reserved', C.c_int32),
+                ('lc_controller', C.c_int32), ('speed_mode', C.c_int32),
                 ('p', C.c_double * FS_NPARAM),
                 ('noise', C.c_double), ('delay', C.c_double),
                 ('max_accel', C.c_double), ('max_decel', C.c_double),

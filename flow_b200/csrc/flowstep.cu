@@ -30,6 +30,7 @@ struct fs_engine {
   bool ml_uniform = false;  // multi-lane kernel: one IDM-law human type + at most one RL type
   int cl_mode = 0;                // FS_CL_MODE at fs_create: zero-copy bits of the closed-loop host step
   bool ml_force_generic = false;  // FS_ML_GENERIC=1 at fs_create: table-driven instantiation (A/B tests)
+  bool hot_noise = false;   // the human type of the hot-kernel pattern carries noise
   bool hot_ok = false;    // c2/c5 pattern: 21 IDM + RL vehicle last, WaveAttenuation(PO), no fail-safe / views
   bool no_hot = false;    // FS_NO_HOT=1: keep ring1_fast_kernel (A/B tests)
   int ring_shape = 0;     // FS_RING_SHAPE override: threads per env (1,2,4,8), 0 = auto
@@ -302,6 +303,7 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
     const fs_vtype& s = types[t];
     fs::TypeP<T>& d = c.types[t];
     d.ctrl = s.controller; d.fail_safe = s.fail_safe; d.lc = s.lc_controller;
+    d.speed_mode = s.speed_mode & 7;
     for (int q = 0; q < FS_NPARAM; ++q) d.p[q] = (T)s.p[q];
     const bool sim_driven = s.controller == FS_CTRL_SIM || s.controller == FS_CTRL_RL;
     d.noise = sim_driven ? (T)0 : (T)s.noise; d.delay = (T)s.delay; d.max_accel = (T)s.max_accel;
@@ -412,6 +414,12 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
                         : (!sim && s.fail_safe != FS_FAILSAFE_NONE) ? 2
                         : (!sim && s.noise > 0) ? 1 : 0;
       if (e->fast_variant > 1) e->hot_ok = false;
+      // a SUMO speed mode on some type: the fast kernel applies it in its fail-safe variants,
+      // the hot kernel in its kSafe instantiations
+      const bool any_mode = (!sim && (s.speed_mode & 7) != 0) ||
+                            (tb >= 0 && (types[tb].speed_mode & 7) != 0);
+      if (any_mode && e->fast_variant < 2) e->fast_variant = 2;
+      e->hot_noise = !sim && s.noise > 0;
     }
   }
   {
@@ -610,7 +618,7 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
     }
     if (sizeof(T) == 8 && shape == 1 && e->ring_shape == 0) shape = 2;  // f64 x 22 slots spills
     if (e->hot_ok && !e->no_hot) {   // c2 / c5 configuration: fully specialised kernel
-      FS_CUDA(e, launch_hot(shape, e->fast_variant == 1, E, e->stream,
+      FS_CUDA(e, launch_hot(shape, e->hot_noise, E, e->stream,
                             fs::make_fastp(cfg_of<T>(e)), ring_bufs<T>(e), a));
       e->launches++;
       return FS_OK;

@@ -21,7 +21,7 @@ namespace fs {
 
 template <typename T>
 struct TypeP {
-  int ctrl, fail_safe, lc, pad;
+  int ctrl, fail_safe, lc, speed_mode;   // speed_mode: SUMO bits 0-2, see speed_mode_accel
   T p[FS_NPARAM];
   T noise, delay, max_accel, max_decel, length;
   T sim_tau, sim_min_gap, sim_v0;  // sim_v0 = min(maxSpeed, speed_limit)
@@ -287,6 +287,30 @@ __device__ __forceinline__ T ctrl_accel(const TypeP<T>& tp, int ctrl, T v, bool 
     default:
       return T(0);
   }
+}
+
+// What SUMO makes of a speed commanded through slowDown (apply_acceleration,
+// flow/core/kernel/vehicle/traci.py:952-963) under the vehicle's speed mode (setSpeedMode at
+// departure, vehicle/traci.py:343-347; SPEED_MODES flow/core/params.py:12-18: aggressive 0,
+// obey_safe_speed 1, no_collide 7, right_of_way 25 = the default, all_checks 31).
+// RESTATED SUMO, "parity unpinned": bit 0 (regard safe speed) caps the commanded speed by the
+// car-following model's own next speed, i.e. the restated simulator model = IDM fed with the
+// type's SumoCarFollowingParams (carFollowModel "IDM" is the default, params.py:833); bit 1 caps
+// the acceleration at the type's `accel`, bit 2 floors it at -`decel`; bits 3-4 (right of way,
+// red lights) have nothing to act on on a ring / straight highway. Written on accelerations:
+// max(v + min(a, a_sim) dt, 0) = min(max(v + a dt, 0), max(v + a_sim dt, 0)).
+template <typename T>
+__device__ __forceinline__ T speed_mode_accel(const TypeP<T>& tp, T a, T v, T v_l, T h,
+                                              bool has_lead) {
+  typedef Num<T> N;
+  const int m = tp.speed_mode;
+  if (m & 1)
+    a = N::min(a, idm_accel<T>(v, v_l, h, has_lead, tp.sim_v0, tp.sim_inv_v0, tp.sim_tau,
+                               tp.max_accel, tp.sim_two_sqrt_ab, tp.sim_inv_two_sqrt_ab, T(4),
+                               tp.sim_min_gap));
+  if (m & 2) a = N::min(a, tp.max_accel);
+  if (m & 4) a = N::max(a, T(0) - tp.max_decel);
+  return a;
 }
 
 // base_controller.py:120-169

@@ -80,7 +80,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   int* ts = reinterpret_cast<int*>(hs + CAP);
   int* is = ts + CAP;   // vehicle ids during the compaction (kMA)
 
-  T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS];
+  T x[SLOTS], v[SLOTS], h[SLOTS], acc[SLOTS], aeff[SLOTS];
   int ty[SLOTS];
   int id[kMA ? SLOTS : 1], rank[kMA ? SLOTS : 1];
   const size_t eo = (size_t)e * CAP;
@@ -260,11 +260,12 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         else   // the same arithmetic as ctrl_accel's IDM / SIM cases (fs_ring.cuh does the same)
           a = idm_accel<T>(vi, vl, hi, has_lead, tp.e_v0, tp.e_inv_v0, tp.e_T, tp.e_a, tp.e_tsab,
                            tp.e_inv_tsab, tp.e_delta, tp.e_s0);
+        bool commanded = ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL;
         if (kMA && ctrl == FS_CTRL_RL && A.actions != nullptr && rank[kMA ? r : 0] < AG) {
           // MultiAgentHighwayPOEnv._apply_rl_actions: apply_acceleration(rl_id, actions[0]),
           // not clipped; NaN = this agent got no command (stays with the simulator model)
           const T raw = A.actions[((size_t)k * cfg.act_dim + rank[kMA ? r : 0]) * E + e];
-          if (raw == raw) a = raw;
+          if (raw == raw) { a = raw; commanded = true; }
         }
         if (ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL) {
           if (tp.noise > T(0))
@@ -274,7 +275,9 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
           else if (tp.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
             a = failsafe_safe_velocity<T>(a, vi, vl, hi, n, dt, tp.delay);
         }
-        acc[r] = a;
+        acc[r] = a;      // commanded (the `accel` view)
+        // a speed Flow commands passes SUMO's speed mode (restated, fs_common.cuh)
+        aeff[r] = (commanded && tp.speed_mode != 0) ? speed_mode_accel<T>(tp, a, vi, vl, hi, has_lead) : a;
       }
       __syncwarp();
       tc += 1;
@@ -286,7 +289,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         const int s = lane_id + 32 * r;
         bool keep = false;
         if (s < n) {
-          const T vn = N::max(add(v[r], mul(acc[r], dt)), T(0));
+          const T vn = N::max(add(v[r], mul(aeff[r], dt)), T(0));
           x[r] = add(x[r], move_dist<T>(v[r], vn, dt, cfg.ballistic));
           v[r] = vn;
           keep = x[r] < Lr;

@@ -42,7 +42,10 @@ namespace fs {
 template <typename T>
 struct MlFast {
   IdmRegs<T> pa, pb;     // human type / un-commanded RL type (simulator default model)
+  IdmRegs<T> ps;         // simulator model of the HUMAN type (its speed mode's safe speed)
   T len, noise, delay, min_gap;
+  T cap_a, floor_a, cap_b, floor_b;   // speed-mode bits 1 / 2 of the two types (+-inf when off)
+  int safe_a, safe_b;                 // speed-mode bit 0
   T inv_speed_limit, inv_lanes, rew_inv;   // fp32 observation / reward reciprocals
   int fail_safe, human_is_sim;
 };
@@ -76,6 +79,9 @@ static inline MlFast<T> make_mlfast(const Cfg<T>& c) {
   p.len = c.types[ta].length; p.noise = c.types[ta].noise; p.delay = c.types[ta].delay;
   p.min_gap = c.types[ta].sim_min_gap; p.fail_safe = c.types[ta].fail_safe;
   p.human_is_sim = c.types[ta].ctrl != FS_CTRL_IDM;
+  load_sim_block(p.ps, c.types[ta]);
+  speed_mode_consts(c.types[ta], p.safe_a, p.cap_a, p.floor_a);
+  speed_mode_consts(c.types[tb], p.safe_b, p.cap_b, p.floor_b);
   p.inv_speed_limit = T(1) / c.speed_limit; p.inv_lanes = T(1) / T(c.n_lanes);
   T mc2 = T(0);
   for (int i = 0; i < c.n_veh; ++i) mc2 = mc2 + c.target_velocity * c.target_velocity;
@@ -117,7 +123,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
   int* loff = cidx + V;            // lane l occupies entries [loff[l], loff[l+1])
   const MlFast<T>& P = B.fp;
 
-  T x[SLOTS], v[SLOTS], h[SLOTS], vl[SLOTS], acc[SLOTS];
+  T x[SLOTS], v[SLOTS], h[SLOTS], vl[SLOTS], acc[SLOTS], aeff[SLOTS];
   int ln[SLOTS], lead[SLOTS], foll[SLOTS];
   int tt[SLOTS], rls[SLOTS];       // type index / action slot (-1: not RL) of my vehicles
   const T C = B.circ[e];
@@ -439,7 +445,7 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
         const bool has_lead = lead[s] >= 0;
         const T vi = v[s], hi = h[s];
         const T vlead = vl[s];       // -1001 without a leader
-        T a;
+        T a, ae;             // commanded / what moves the vehicle (after SUMO's speed mode)
         if (!kGeneric) {
           // ONE IDM-law human type (+ RL): parameters are uniform kernel-argument constants
           if (rls[s] >= 0) {
@@ -447,19 +453,23 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
               const T raw = act_a[s];
               a = N::min(N::max(raw, cfg.act_lo), cfg.act_hi);
               act_abs_sum = add(act_abs_sum, N::abs(cfg.clip_actions ? a : raw));
+              ae = speed_mode_fast<T>(a, vi, vlead, hi, has_lead, P.pb, P.safe_b, P.cap_b, P.floor_b);
             } else {   // un-commanded RL vehicle: restated simulator default model
               a = idm_accel<T>(vi, vlead, hi, has_lead, P.pb.v0, P.pb.inv_v0, P.pb.Tt, P.pb.a,
                                P.pb.tsab, P.pb.inv_tsab, P.pb.delta, P.pb.s0);
+              ae = a;
             }
           } else {
             a = idm_accel<T>(vi, vlead, hi, has_lead, P.pa.v0, P.pa.inv_v0, P.pa.Tt, P.pa.a,
                              P.pa.tsab, P.pa.inv_tsab, P.pa.delta, P.pa.s0);
+            ae = a;
             if (!P.human_is_sim) {   // base_controller.py:109-116: noise, then fail-safe
               if (noisy) a = add(a, mul(P.noise, zn[s]));
               if (P.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
                 a = failsafe_instantaneous<T>(a, vi, hi, has_lead, V, dt);
               else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
                 a = failsafe_safe_velocity<T>(a, vi, vlead, hi, V, dt, P.delay);
+              ae = speed_mode_fast<T>(a, vi, vlead, hi, has_lead, P.ps, P.safe_a, P.cap_a, P.floor_a);
             }
           }
         } else {
@@ -493,14 +503,18 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
             else if (tp.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
               a = failsafe_safe_velocity<T>(a, vi, vlead, hi, V, dt, tp.delay);
           }
+          ae = a;
+          if (tp.speed_mode != 0 && ctrl != FS_CTRL_SIM && !(ctrl == FS_CTRL_RL && !have_act))
+            ae = speed_mode_accel<T>(tp, a, vi, vlead, hi, has_lead);
         }
         acc[s] = a;
+        aeff[s] = ae;
       }
       // all reads of the published pre-move state are done (refresh / rebuild sync first); move
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s) {
         if (lane_id + 32 * s >= V) continue;
-        const T vn = N::max(add(v[s], mul(acc[s], dt)), T(0));
+        const T vn = N::max(add(v[s], mul(aeff[s], dt)), T(0));
         x[s] = wrap_fwd(add(x[s], move_dist<T>(v[s], vn, dt, cfg.ballistic)), C);
         v[s] = vn;
         ln[s] = new_ln[s];

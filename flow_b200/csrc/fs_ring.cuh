@@ -320,8 +320,13 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
           else if (tp.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
             a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, tp.delay);
         }
+        // a speed Flow commands passes SUMO's speed mode (restated); vehicles the simulator
+        // drives itself (SimCarFollowing, un-commanded RL) do not
+        T a_eff = a;
+        if (tp.speed_mode != 0 && ctrl != FS_CTRL_SIM && !(ctrl == FS_CTRL_RL && !have_act))
+          a_eff = speed_mode_accel<T>(tp, a, vi, vl, hi, has_lead);
         // apply_acceleration (vehicle/traci.py:961-962) + Euler move
-        const T vn = N::max(add(vi, mul(a, dt)), T(0));
+        const T vn = N::max(add(vi, mul(a_eff, dt)), T(0));
         const T xn = wrap_fwd(add(x[j], move_dist<T>(vi, vn, dt, cfg.ballistic)), C);
         vf = vi; hf = hi;  // old values: follower data of the next slot
         if (ok) { v[j] = vn; x[j] = xn; acc[j] = a; }

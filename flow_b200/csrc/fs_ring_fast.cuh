@@ -40,6 +40,21 @@ struct IdmRegs {  // one type's effective IDM block, register resident
   }
 };
 
+// the simulator-model block of a type whatever its controller (for the speed mode's safe speed)
+template <typename T>
+static inline void load_sim_block(IdmRegs<T>& r, const TypeP<T>& t) {
+  r.v0 = t.sim_v0; r.inv_v0 = t.sim_inv_v0; r.Tt = t.sim_tau; r.a = t.max_accel;
+  r.tsab = t.sim_two_sqrt_ab; r.inv_tsab = t.sim_inv_two_sqrt_ab; r.delta = T(4); r.s0 = t.sim_min_gap;
+}
+// speed-mode bits of a type as kernel constants: bit 0 -> safe, bits 1 / 2 -> cap / floor
+// (+-inf when the bit is off, so they are applied unconditionally)
+template <typename T>
+static inline void speed_mode_consts(const TypeP<T>& t, int& safe, T& cap, T& floor) {
+  safe = t.speed_mode & 1;
+  cap = (t.speed_mode & 2) ? t.max_accel : (T)INFINITY;
+  floor = (t.speed_mode & 4) ? T(0) - t.max_decel : T(0) - (T)INFINITY;
+}
+
 // Host-precomputed constants of the hot kernel (built by make_fastp()).
 template <typename T>
 struct FastP {
@@ -55,6 +70,10 @@ struct FastP {
   T inv_obs_len;      // 1 / obs_max_length, 0 when the ring's own length normalises
   T inv_speed_limit;
   IdmRegs<T> pa, pb;  // human type / un-commanded RL type (simulator default model)
+  IdmRegs<T> ps;      // simulator model of the HUMAN type (safe speed of its speed mode)
+  T cap_a, floor_a, cap_b, floor_b;   // speed-mode bits 1 / 2 of the two types (+-inf when off)
+  int safe_a, safe_b;                 // speed-mode bit 0
+  int any_speed_mode;
 };
 
 template <typename T>
@@ -88,6 +107,14 @@ static inline FastP<T> make_fastp(const Cfg<T>& c) {
   p.inv_obs_len = c.obs_max_length > T(0) ? T(1) / c.obs_max_length : T(0);
   p.inv_speed_limit = T(1) / c.speed_limit;
   p.pa.load(c.types[ta]); p.pb.load(c.types[tb]);
+  load_sim_block(p.ps, c.types[ta]);
+  speed_mode_consts(c.types[ta], p.safe_a, p.cap_a, p.floor_a);
+  speed_mode_consts(c.types[tb], p.safe_b, p.cap_b, p.floor_b);
+  if (c.types[ta].ctrl != FS_CTRL_IDM) {   // SimCarFollowing humans: the simulator drives, no mode
+    p.safe_a = 0; p.cap_a = (T)INFINITY; p.floor_a = T(0) - (T)INFINITY;
+  }
+  p.any_speed_mode = (c.types[ta].ctrl == FS_CTRL_IDM && c.types[ta].speed_mode != 0) ||
+                     (c.n_rl > 0 && c.types[tb].speed_mode != 0);
   return p;
 }
 
@@ -135,6 +162,17 @@ __device__ __forceinline__ T idm_fast(T v, T v_lead, T h, const IdmRegs<T>& p) {
   else pw = N::pow(r, p.delta);
   const T sh = N::div(s_star, h);
   return mul(p.a, (T(1) - pw) - mul(sh, sh));
+}
+
+// speed_mode_accel (fs_common.cuh) with the type's constants in registers / kernel arguments
+template <typename T>
+__device__ __forceinline__ T speed_mode_fast(T a, T v, T v_l, T h, bool has_lead,
+                                             const IdmRegs<T>& sim, int safe, T cap, T floor) {
+  typedef Num<T> N;
+  if (safe)
+    a = N::min(a, idm_accel<T>(v, v_l, h, has_lead, sim.v0, sim.inv_v0, sim.Tt, sim.a, sim.tsab,
+                               sim.inv_tsab, sim.delta, sim.s0));
+  return N::max(N::min(a, cap), floor);
 }
 
 // sum over the threads of one env group. fp32: integer REDUX in 2^-20 fixed
@@ -358,6 +396,10 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
           else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
             a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, P.delay);
         }
+        T a_h = a;          // what moves a human (after SUMO's speed mode, restated)
+        if (kFS && P.any_speed_mode)
+          a_h = speed_mode_fast<T>(a, vi, vl, hi, true, P.ps, P.safe_a, P.cap_a, P.floor_a);
+        T a_rl_eff = a_rl;
         if (have_act) {
           // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
           T raw = a_cur;
@@ -367,9 +409,13 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
           a_rl = N::min(N::max(raw, P.act_lo), P.act_hi);
           const T aa = N::abs(P.clip_actions ? a_rl : raw);
           act_abs_sum = rlj ? add(act_abs_sum, aa) : act_abs_sum;
+          a_rl_eff = a_rl;
+          if (kFS && P.any_speed_mode)
+            a_rl_eff = speed_mode_fast<T>(a_rl, vi, vl, hi, true, P.pb, P.safe_b, P.cap_b, P.floor_b);
         }
-        a = rlj ? a_rl : a;
-        const T vn = N::max(add(vi, mul(a, dt)), T(0));   // vehicle/traci.py:961-962
+        a = rlj ? a_rl : a;                       // commanded (the `accel` view)
+        const T a_mv = rlj ? a_rl_eff : a_h;
+        const T vn = N::max(add(vi, mul(a_mv, dt)), T(0));   // vehicle/traci.py:961-962
         const T xn = wrap_fwd(add(x[j], mul(vn, dt)), C);  // simulator Euler move
         if (ok) { v[j] = vn; x[j] = xn; if (kViews) acc[kViews ? j : 0] = a; }
       }

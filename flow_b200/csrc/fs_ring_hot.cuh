@@ -93,7 +93,10 @@ __device__ __forceinline__ T env_sum_full(T part, int es) {
   return part;
 }
 
-template <typename T, int VPT, int G, bool kNoise, bool kAct, int kVar = 0>
+// kSafe: some type carries a SUMO speed mode (the reference's default, 'right_of_way' = 25, has
+// bit 0 set): the speed Flow commands is capped by the restated simulator model's own next
+// speed (speed_mode_fast, fs_ring_fast.cuh) - a second IDM evaluation per vehicle and step
+template <typename T, int VPT, int G, bool kNoise, bool kAct, bool kSafe>
 __global__ void __launch_bounds__(128)
 ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -189,8 +192,7 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   // per-step outputs: a missing sequence is redirected to the env's last-step
   // slot with stride 0 (it ends up holding the last step's value, which is what
   // the epilogue stores there anyway), so one predicate guards all stores
-  const bool seq_on = !(kVar & 4) &&
-                      (A.obs_seq != nullptr || A.reward_seq != nullptr || A.done_seq != nullptr);
+  const bool seq_on = A.obs_seq != nullptr || A.reward_seq != nullptr || A.done_seq != nullptr;
   const bool wr = valid && is_rl;
   T* const obs_b = A.obs_seq ? A.obs_seq + (size_t)e * 3 : B.obs + (size_t)e * 3;
   T* const rew_b = A.reward_seq ? A.reward_seq + e : B.reward + e;
@@ -234,8 +236,7 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
       if (kAct) {
 #pragma unroll
         for (int j = 0; j < UNR; ++j) ac[j] = an[j];
-        if (kVar & 8) { for (int j = 0; j < UNR; ++j) an[j] = T(0.1); }   // timing experiment: no action loads
-        else if (is_rl) {   // actions of the next block, requested one block ahead
+        if (is_rl) {   // actions of the next block, requested one block ahead
           if (kb >= 0 && kb + 2 * UNR <= K) {   // whole next block inside the launch: no clamping
             const T* q = act_p + (size_t)(unsigned)(kb + UNR) * (unsigned)E;
 #pragma unroll
@@ -274,13 +275,16 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
                 const T z = kTimeNoise ? zn[kNoise ? i : 0][j] : zn[kNoise ? (i >> 2) : 0][i & 3];
                 a = add(a, mul(VPT == 1 ? nz : P.noise, z));
               }
+              if (kSafe)   // SUMO's speed mode on the human's commanded speed (restated)
+                a = speed_mode_fast<T>(a, vi, vl, hi, true, P.ps, P.safe_a, P.cap_a, P.floor_a);
               if (i == RL_SLOT) {
                 if (kAct) {  // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
                   const T raw = ac[j];
-                  const T a_c = N::min(N::max(raw, P.act_lo), P.act_hi);
+                  T a_c = N::min(N::max(raw, P.act_lo), P.act_hi);
                   act_abs = N::abs(P.clip_actions ? a_c : raw);
+                  if (kSafe) a_c = speed_mode_fast<T>(a_c, vi, vl, hi, true, P.pb, P.safe_b, P.cap_b, P.floor_b);
                   a = is_rl ? a_c : a;
-                } else if (VPT > 1) {  // un-commanded RL vehicle: restated simulator default model
+                } else {  // un-commanded RL vehicle: restated simulator default model, no speed mode
                   if (is_rl) a = idm_fast<T, true>(vi, vl, hi, P.pb);
                 }
               }
@@ -303,9 +307,7 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
             if (G > 1) cr = (__ballot_sync(FULL, cr) & gmask) != 0u;
             T r = T(0);
             if (kAct) {  // WaveAttenuationEnv.compute_reward, wave_attenuation.py:113-139
-              if (kVar & 2) sv = sv * T(22);   // timing experiment: no reduction (wrong reward)
-              else if (kVar & 1) { for (int o = EPW; o < 32; o <<= 1) sv += __shfl_xor_sync(FULL, sv, o); }
-              else sv = env_sum_full<T, G>(sv, es);
+              sv = env_sum_full<T, G>(sv, es);
               r = kF32 ? sv * P.rew_scale : N::div(mul(T(4), N::div(sv, P.n_veh_t)), T(20));
               if (act_abs > T(0)) r = add(r, mul(T(4), T(0) - act_abs));
               r = cr ? T(0) : r;
@@ -372,31 +374,9 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
 }
 
 // ---- host-side dispatch (one translation unit per dtype instantiates these)
-#ifdef FS_HOT_EXPERIMENTS
-template <typename T, int VPT, int G>
-static bool launch_hot_var(int var, int grid, int block, cudaStream_t st,
-                           const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
-  switch (var) {
-    case 1: ring1_hot_kernel<T, VPT, G, true, true, 1><<<grid, block, 0, st>>>(c, b, a); return true;
-    case 2: ring1_hot_kernel<T, VPT, G, true, true, 2><<<grid, block, 0, st>>>(c, b, a); return true;
-    case 4: ring1_hot_kernel<T, VPT, G, true, true, 4><<<grid, block, 0, st>>>(c, b, a); return true;
-    case 6: ring1_hot_kernel<T, VPT, G, true, true, 6><<<grid, block, 0, st>>>(c, b, a); return true;
-    case 8: ring1_hot_kernel<T, VPT, G, true, true, 8><<<grid, block, 0, st>>>(c, b, a); return true;
-    case 12: ring1_hot_kernel<T, VPT, G, true, true, 12><<<grid, block, 0, st>>>(c, b, a); return true;
-    default: return false;
-  }
-}
-#endif
-
 template <typename T, int VPT, int G>
 static cudaError_t launch_hot_shape(bool noise, bool act, int grid, int block, cudaStream_t st,
                                     const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
-#ifdef FS_HOT_EXPERIMENTS
-  if (sizeof(T) == 4 && noise && act && G >= 4) {
-    static const int var = getenv("FS_HOT_VAR") ? atoi(getenv("FS_HOT_VAR")) : 0;
-    if (var && launch_hot_var<T, VPT, G>(var, grid, block, st, c, b, a)) return cudaGetLastError();
-  }
-#endif
   auto go = [&](void (*kern)(const FastP<T>, const RingBufs<T>, const StepArgs<T>)) {
     if (a.pdl) {   // programmatic dependent launch: overlaps this launch's ramp with the previous tail
       cudaLaunchConfig_t lc = {};
@@ -410,13 +390,13 @@ static cudaError_t launch_hot_shape(bool noise, bool act, int grid, int block, c
       kern<<<grid, block, 0, st>>>(c, b, a);
     }
   };
-  if (noise) {
-    if (act) go(ring1_hot_kernel<T, VPT, G, true, true>);
-    else go(ring1_hot_kernel<T, VPT, G, true, false>);
-  } else {
-    if (act) go(ring1_hot_kernel<T, VPT, G, false, true>);
-    else go(ring1_hot_kernel<T, VPT, G, false, false>);
-  }
+  const bool safe = c.any_speed_mode != 0;
+#define FS_HOT(NZ, AC) \
+  do { if (safe) go(ring1_hot_kernel<T, VPT, G, NZ, AC, true>); \
+       else go(ring1_hot_kernel<T, VPT, G, NZ, AC, false>); } while (0)
+  if (noise) { if (act) FS_HOT(true, true); else FS_HOT(true, false); }
+  else { if (act) FS_HOT(false, true); else FS_HOT(false, false); }
+#undef FS_HOT
   return cudaGetLastError();
 }
 

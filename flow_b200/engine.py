@@ -63,8 +63,11 @@ class VType(dict):
 
 def make_vtype(controller, p=(), fail_safe=None, noise=0.0, delay=0.0,
                max_accel=2.6, max_decel=4.5, length=5.0, sim_tau=1.0,
-               sim_min_gap=2.5, sim_max_speed=30.0, lc_controller=LC_SIM):
+               sim_min_gap=2.5, sim_max_speed=30.0, lc_controller=LC_SIM, speed_mode=0):
+    """speed_mode: SumoCarFollowingParams.speed_mode as an int (flow/core/params.py:12-18);
+    0 = 'aggressive' (Flow's commanded speed is taken as is), the reference's default is 25."""
     t = _lib.FsVType()
+    t.speed_mode = int(speed_mode)
     t.controller = controller
     t.fail_safe = FAILSAFE[fail_safe] if not isinstance(fail_safe, int) else fail_safe
     t.lc_controller = lc_controller

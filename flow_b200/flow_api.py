@@ -540,7 +540,10 @@ def _vtype_row(ini, lc_env):
                          noise=ctrl.noise, delay=ctrl.delay, max_accel=cf['accel'],
                          max_decel=cf['decel'], length=length, sim_tau=cf['tau'],
                          sim_min_gap=cf['minGap'], sim_max_speed=cf['maxSpeed'],
-                         lc_controller=lc)
+                         lc_controller=lc,
+                         # setSpeedMode at departure (vehicle/traci.py:343-347): the restated
+                         # clamp on the speeds Flow commands (include/flowstep.h fs_vtype)
+                         speed_mode=int(ini['car_following_params'].speed_mode))
 
 
 def compile_spec(env_cls, env_params, sim_params, network, seed=None):

@@ -3,54 +3,59 @@ SURVEY.md §8d). Each returns (types, type_of_vehicle, engine_kwargs)."""
 from . import engine as EN
 
 IDM_DEFAULT = [30, 1, 1, 1.5, 4, 2]  # flow/controllers/car_following_models.py:437-447
+# SumoCarFollowingParams.speed_mode: every shipped config leaves the default 'right_of_way'
+# (flow/core/params.py:12-18, 841) in place, so the workloads carry it (0 = 'aggressive')
+SPEED_MODE = 25
 
 
-def ring_c1():
+def ring_c1(speed_mode=SPEED_MODE):
     """examples/exp_configs/non_rl/ring.py: 22 IDM, 230 m, bunching 20 (noise 0)."""
-    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT)]
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, speed_mode=speed_mode)]
     kw = dict(env_kind=EN.ENV_ACCEL, length_lo=230.0, length_hi=230.0, bunching=20.0,
               target_velocity=10.0, horizon=3000, warmup_steps=0, act_lo=-3.0, act_hi=3.0)
     return types, [0] * 22, kw
 
 
-def ring_c2(noise=0.0):
+def ring_c2(noise=0.0, speed_mode=SPEED_MODE):
     """examples/exp_configs/rl/singleagent/singleagent_ring.py:
     WaveAttenuationPOEnv, 21 IDM (min_gap 0) + 1 RL, length ~ U{220..270},
     bunching 50, warm-up 750, horizon 3000, actions in [-1, 1]."""
-    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, sim_min_gap=0.0),
-             EN.make_vtype(EN.CTRL_RL)]
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, sim_min_gap=0.0,
+                           speed_mode=speed_mode),
+             EN.make_vtype(EN.CTRL_RL, speed_mode=speed_mode)]
     kw = dict(env_kind=EN.ENV_WAVE_ATTENUATION_PO, length_lo=220.0, length_hi=270.0,
               bunching=50.0, init_min_gap=0.0, warmup_steps=750, horizon=3000,
               act_lo=-1.0, act_hi=1.0, obs_max_length=270.0, clip_actions=0)
     return types, [0] * 21 + [1], kw
 
 
-def ring_ma(noise=0.0):
+def ring_ma(noise=0.0, speed_mode=SPEED_MODE):
     """examples/exp_configs/rl/multiagent/multiagent_ring.py:
     MultiAgentWaveAttenuationPOEnv, (1 RL + 10 IDM) x 2 on one ring."""
-    human = EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, sim_min_gap=0.0)
-    types = [EN.make_vtype(EN.CTRL_RL), human]
+    human = EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, sim_min_gap=0.0,
+                          speed_mode=speed_mode)
+    types = [EN.make_vtype(EN.CTRL_RL, speed_mode=speed_mode), human]
     kw = dict(env_kind=EN.ENV_MA_WAVE_ATTENUATION_PO, length_lo=220.0, length_hi=270.0,
               bunching=50.0, init_min_gap=0.0, warmup_steps=750, horizon=3000,
               act_lo=-1.0, act_hi=1.0, obs_max_length=270.0, clip_actions=0)
     return types, [0] + [1] * 10 + [0] + [1] * 10, kw
 
 
-def ring_c3(noise=0.0):
+def ring_c3(noise=0.0, speed_mode=SPEED_MODE):
     """LaneChangeAccelEnv on a 3-lane 230 m ring, 66 vehicles 3-abreast
     (63 IDM that keep their lane + 3 RL that change lane), actions [accel, direction] per RL."""
-    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise),
-             EN.make_vtype(EN.CTRL_RL, lc_controller=EN.LC_RL)]
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, speed_mode=speed_mode),
+             EN.make_vtype(EN.CTRL_RL, lc_controller=EN.LC_RL, speed_mode=speed_mode)]
     kw = dict(env_kind=EN.ENV_LANE_CHANGE_ACCEL, n_lanes=3, length_lo=230.0, length_hi=230.0,
               target_velocity=10.0, horizon=3000, warmup_steps=0, act_lo=-3.0, act_hi=3.0,
               lane_change_duration=5)
     return types, [0] * 63 + [1] * 3, kw
 
 
-def highway_c4(noise=0.0):
+def highway_c4(noise=0.0, speed_mode=SPEED_MODE):
     """single-lane 1 km HighwayNetwork, IDM vehicles, inflow 2000 veh/h at
     20 m/s, 160 vehicle slots per env, departures / arrivals compacted every step."""
-    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise)]
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, speed_mode=speed_mode)]
     kw = dict(topology=EN.TOPO_HIGHWAY, env_kind=EN.ENV_HIGHWAY, length_lo=1000.0, length_hi=1000.0,
               junction_len=0.0, target_velocity=10.0, horizon=3000, warmup_steps=0,
               inflow_vehs_per_hour=2000.0, inflow_depart_speed=20.0, inflow_type=0,
@@ -58,12 +63,13 @@ def highway_c4(noise=0.0):
     return types, [0] * 20, kw
 
 
-def highway_ma(noise=0.0):
+def highway_ma(noise=0.0, speed_mode=SPEED_MODE):
     """MultiAgentHighwayPOEnv (flow/envs/multiagent/highway.py) on the single-lane 1 km
     HighwayNetwork with the inflow split of examples/exp_configs/rl/multiagent/
     multiagent_highway.py (20 % RL penetration): an RL inflow of 400 veh/h served before an IDM
     inflow of 1600 veh/h, 160 slots, up to 32 agent rows per env."""
-    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise), EN.make_vtype(EN.CTRL_RL)]
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, speed_mode=speed_mode),
+             EN.make_vtype(EN.CTRL_RL, speed_mode=speed_mode)]
     kw = dict(topology=EN.TOPO_HIGHWAY, env_kind=EN.ENV_MA_HIGHWAY_PO, length_lo=1000.0,
               length_hi=1000.0, junction_len=0.0, target_velocity=25.0, horizon=3000,
               warmup_steps=0, capacity=160, max_agents=32,

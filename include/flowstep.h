@@ -143,7 +143,13 @@ typedef struct fs_vtype {
   int32_t controller;    /* FS_CTRL_*                                           */
   int32_t fail_safe;     /* FS_FAILSAFE_*                                       */
   int32_t lc_controller; /* FS_LC_*                                             */
-  int32_t reserved;
+  int32_t speed_mode;    /* SumoCarFollowingParams.speed_mode (flow/core/params.py:12-18, default
+                          * 25 there; 0 = 'aggressive' = Flow's command is taken as is). Applies to
+                          * speeds Flow commands (controller or RL action), RESTATED SUMO: bit 0 caps
+                          * the commanded speed by the simulator model's own next speed (IDM with
+                          * the sim_* / max_accel / max_decel fields below), bit 1 caps the
+                          * acceleration at max_accel, bit 2 floors it at -max_decel; bits 3-4
+                          * (right of way, red lights) have nothing to act on here                 */
   double p[FS_NPARAM];   /* controller parameters, order as listed above        */
   double noise;          /* std of the Gaussian added to accel (0 = none)       */
   double delay;          /* used by the safe_velocity fail-safe                 */

@@ -26,7 +26,7 @@ class VType:
     def __init__(self, controller=IDM, p=(), fail_safe=FS_NONE, noise=0.0,
                  delay=0.0, max_accel=2.6, max_decel=4.5, length=5.0,
                  sim_tau=1.0, sim_min_gap=2.5, sim_max_speed=30.0,
-                 lc_controller=0):
+                 lc_controller=0, speed_mode=0):
         self.controller = controller
         self.p = list(p) + [0.0] * (8 - len(p))
         self.fail_safe = fail_safe
@@ -39,6 +39,7 @@ class VType:
         self.sim_min_gap = sim_min_gap
         self.sim_max_speed = sim_max_speed
         self.lc_controller = lc_controller
+        self.speed_mode = int(speed_mode)   # SUMO speed-mode bits (flow/core/params.py:12-18)
 
 
 def idm_params(v0=30, T=1, a=1, b=1.5, delta=4, s0=2):
@@ -212,6 +213,34 @@ def safe_velocity_action(k, i, action, dt, delay):
             return (v_safe - this_vel) / dt
         return -this_vel / dt
     return action
+
+
+def sim_model_accel(k, i, vt, speed_limit):
+    """Acceleration of the restated simulator model for vehicle i: IDM fed with the type's
+    SumoCarFollowingParams (carFollowModel "IDM" is the default of
+    flow/core/params.py:833)."""
+    lead = k.leader[i]
+    v0 = min(vt.sim_max_speed, speed_limit)
+    return idm_accel(k.vel[i], _speed(k, lead), k.headway[i], lead >= 0, v0, vt.sim_tau,
+                     vt.max_accel, vt.max_decel, 4, vt.sim_min_gap)
+
+
+def speed_mode_accel(k, i, vt, accel, speed_limit):
+    """What SUMO makes of a speed commanded through slowDown (apply_acceleration,
+    flow/core/kernel/vehicle/traci.py:952-963) under the vehicle's speed mode
+    (setSpeedMode at departure, :343-347; modes flow/core/params.py:12-18). RESTATED SUMO,
+    "parity unpinned": bit 0 (regard safe speed) caps the commanded speed by the car-following
+    model's own next speed - here the restated simulator model; bit 1 caps the acceleration at
+    the type's `accel`, bit 2 floors it at -`decel`. Expressed on accelerations:
+    v' = max(v + a dt, 0) with a = this function's result equals min / max of the speeds."""
+    m = vt.speed_mode
+    if m & 1:
+        accel = min(accel, sim_model_accel(k, i, vt, speed_limit))
+    if m & 2:
+        accel = min(accel, vt.max_accel)
+    if m & 4:
+        accel = max(accel, -vt.max_decel)
+    return accel
 
 
 def get_action(k, i, vt, st, dt, speed_limit, noise_sample=0.0):

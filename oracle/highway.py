@@ -174,11 +174,15 @@ class HighwaySim:
             vt = self.types[self.type_of[s]]
             z = self.noise_fn(self.time_counter - 1, s) if (self.noise_fn and vt.noise > 0) else 0.0
             a = C.get_action(self, s, vt, {}, dt, self.speed_limit, z)
+            commanded = vt.controller not in (C.SIM, C.RL)
             if vt.controller == C.RL and actions and self.ids[s] in actions:
                 raw = float(actions[self.ids[s]])
                 if raw == raw:          # NaN = no command for this agent
                     a = raw             # multiagent/highway.py:86-95, not clipped
+                    commanded = True
             self.accel[s] = a
+            if commanded and vt.speed_mode:     # SUMO's speed mode on a commanded speed (restated)
+                a = C.speed_mode_accel(self, s, vt, a, self.speed_limit)
             nv[s] = max(self.vel[s] + a * dt, 0.0)
         for s in range(n):
             if self.use_ballistic:

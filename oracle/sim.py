@@ -357,6 +357,11 @@ class RingSim:
                 a = C.get_action(self, i, vt, self.ctrl_state[i], dt,
                                  self.speed_limit, z)
             self.accel[i] = a
+            # a speed commanded through slowDown passes SUMO's speed mode (restated); vehicles
+            # the simulator drives itself (SimCarFollowingController, un-commanded RL) do not
+            commanded = vt.controller != C.SIM and not (vt.controller == C.RL and clipped is None)
+            if commanded and vt.speed_mode:
+                a = C.speed_mode_accel(self, i, vt, a, self.speed_limit)
             # apply_acceleration, vehicle/traci.py:961-962
             next_vel[i] = max(self.vel[i] + a * dt, 0.0)
         # apply_lane_change (vehicle/traci.py:965-997) + restated execution: the

@@ -150,6 +150,32 @@ def ring_c1():
         sum_reward=t['reward'].sum())
 
 
+def ring_c2_speed_mode():
+    """c2 with the speed modes singleagent_ring.py leaves at the reference's default
+    ('right_of_way' = 25 on humans and on the RL vehicle) and, second case, 'no_collide' (7):
+    actions well beyond what the gap allows, so the restated clamp binds on the RL vehicle; the
+    simulator model behind the clamp is evaluated by the reference's own IDMController."""
+    out = {}
+    for tag, length, mode, seed in (('a', 260, 'right_of_way', 11), ('b', 223, 'no_collide', 12)):
+        ring = RefRing([('human', IDM, {}, {'min_gap': 0, 'speed_mode': mode}, 21),
+                        ('rl', 'rl', {}, {'speed_mode': mode}, 1)], length, 'wave_po',
+                       init_kw=dict(bunching=50, min_gap=0),
+                       env_additional={'max_accel': 1, 'max_decel': 1, 'ring_length': [220, 270]},
+                       use_speed_mode=True)
+        rng = np.random.default_rng(seed)
+        n_w, n_a = 100, 700
+        acts = np.full((n_w + n_a, 1), np.nan)
+        acts[n_w:, 0] = rng.uniform(-0.6, 1.5, n_a)     # accelerating on average: rams without the clamp
+        t = trajectory(ring, n_w + n_a, acts)
+        assert not t['crash'].any() and len(t['reward']) == n_w + n_a
+        out.update({'length_' + tag: length, 'mode_' + tag: ring.speed_mode[0],
+                    'actions_' + tag: acts[n_w:, 0],
+                    'pos_' + tag: t['pos'][n_w:], 'vel_' + tag: t['vel'][n_w:],
+                    'obs_' + tag: t['obs'][n_w - 1:], 'reward_' + tag: t['reward'][n_w:],
+                    'pos0_' + tag: t['pos'][0]})
+    np.savez_compressed(os.path.join(HERE, 'ring_c2_speed_mode.npz'), **out)
+
+
 def ring_c2():
     out = {}
     for tag, length, seed in (('a', 260, 1), ('b', 223, 2)):
@@ -463,7 +489,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos()
+    ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos()
     highway_ma()
     sumo_fixture()
     print('golden vectors written to', HERE)

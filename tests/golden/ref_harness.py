@@ -182,7 +182,8 @@ class RefRing:
 
     def __init__(self, groups, length, env_kind='accel', dt=0.1, lanes=1,
                  speed_limit=30, init_kw=None, env_additional=None,
-                 warmup_steps=0, horizon=3000, clip_actions=False, index_shortcut=False):
+                 warmup_steps=0, horizon=3000, clip_actions=False, index_shortcut=False,
+                 use_speed_mode=False):
         """groups: list of (name, controller_class_or_'rl', ctrl_kwargs,
         SumoCarFollowingParams kwargs, count)."""
         self.dt = self.sim_step = dt
@@ -192,21 +193,28 @@ class RefRing:
         self.index_shortcut = index_shortcut
         self.ids, self.ctrl, self.rl_idx = [], [], []
         self.sim_ctrl = {}
+        self.speed_mode, self.cf_limits = [], []
         for name, cls, kw, cf_kw, n in groups:
             for q in range(n):
                 vid = '%s_%d' % (name, q)
                 cf = SumoCarFollowingParams(**cf_kw)
+                # restated simulator default model: the reference's IDM
+                # law fed with the type's SUMO params. It drives un-commanded RL vehicles and
+                # is the "safe speed" of the restated speed mode (bit 0) of every vehicle.
+                cp = cf.controller_params
+                self.sim_ctrl[len(self.ids)] = ref_ctrl.IDMController(
+                    vid, v0=min(float(cp['maxSpeed']), speed_limit),
+                    T=float(cp['tau']), a=float(cp['accel']),
+                    b=float(cp['decel']), delta=4, s0=float(cp['minGap']),
+                    car_following_params=cf)
+                # the reference's params object carries the mode (params.py:841, default 25);
+                # the harness applies it only on request (goldens made before the restated
+                # clamp existed stay what they were)
+                self.speed_mode.append(int(cf.speed_mode) if use_speed_mode else 0)
+                self.cf_limits.append((float(cp['accel']), float(cp['decel'])))
                 if cls == 'rl':
                     self.rl_idx.append(len(self.ids))
                     self.ctrl.append(None)
-                    # restated simulator default model:
-                    # the reference's IDM law fed with the type's SUMO params
-                    cp = cf.controller_params
-                    self.sim_ctrl[len(self.ids)] = ref_ctrl.IDMController(
-                        vid, v0=min(float(cp['maxSpeed']), speed_limit),
-                        T=float(cp['tau']), a=float(cp['accel']),
-                        b=float(cp['decel']), delta=4, s0=float(cp['minGap']),
-                        car_following_params=cf)
                 else:
                     self.ctrl.append(cls(vid, car_following_params=cf, **kw))
                 self.ids.append(vid)
@@ -266,6 +274,8 @@ class RefRing:
             for i in self.rl_idx:
                 acc[i] = self.sim_ctrl[i].get_accel(self)
         self._before_move()
+        self.accel_cmd = list(acc)
+        acc = self._speed_mode(acc, rl_actions is not None)
         # reference apply_acceleration (vehicle/traci.py:952-963), unbound
         stub = type('V', (), {})()
         stub.sim_step = self.dt
@@ -276,7 +286,7 @@ class RefRing:
         self.sink.cmd = {}
         TraCIVehicle.apply_acceleration(stub, self.ids, acc)
         for i, vid in enumerate(self.ids):
-            self.accel[i] = acc[i]
+            self.accel[i] = self.accel_cmd[i]      # what the controller commanded
             self.vel[i] = self.sink.cmd[vid]
             self.pos[i] = (self.pos[i] + self.vel[i] * self.dt) % self.net.circ
         self._update()
@@ -289,6 +299,26 @@ class RefRing:
     def _assign_rl(self, acc, clipped):
         for q, i in enumerate(self.rl_idx):
             acc[i] = float(clipped[q])
+
+    def _speed_mode(self, acc, rl_commanded):
+        """RESTATED SUMO (what the simulator makes of a commanded speed, see
+        oracle/controllers.speed_mode_accel): bit 0 caps it by the simulator model's own
+        acceleration - evaluated with the reference's IDMController on the SUMO params -
+        bit 1 / bit 2 bound it by the type's accel / decel. Vehicles the simulator drives
+        itself (un-commanded RL) are left alone."""
+        out = list(acc)
+        for i, m in enumerate(self.speed_mode):
+            if not m or (i in self.rl_idx and not rl_commanded):
+                continue
+            a = out[i]
+            if m & 1:
+                a = min(a, self.sim_ctrl[i].get_accel(self))
+            if m & 2:
+                a = min(a, self.cf_limits[i][0])
+            if m & 4:
+                a = max(a, -self.cf_limits[i][1])
+            out[i] = a
+        return out
 
     def _before_move(self):      # Env.additional_command, base.py:365
         pass

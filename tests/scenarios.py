@@ -18,7 +18,7 @@ DEFAULT_P = dict(
 
 def vt(controller, count, p=None, fail_safe=None, noise=0.0, delay=0.0,
        max_accel=2.6, max_decel=4.5, sim_min_gap=2.5, sim_tau=1.0,
-       sim_max_speed=30.0):
+       sim_max_speed=30.0, speed_mode=0):
     if controller in ('FOLLOWER_STOPPER', 'NONLOCAL_FOLLOWER_STOPPER'):
         # velocity_controllers.py:31-33: forced delay=1.0 + safe_velocity
         fail_safe, delay = 'safe_velocity', 1.0
@@ -28,7 +28,7 @@ def vt(controller, count, p=None, fail_safe=None, noise=0.0, delay=0.0,
                 p=list(DEFAULT_P[controller] if p is None else p),
                 fail_safe=fail_safe, noise=noise, delay=delay, max_accel=max_accel,
                 max_decel=max_decel, sim_min_gap=sim_min_gap, sim_tau=sim_tau,
-                sim_max_speed=sim_max_speed)
+                sim_max_speed=sim_max_speed, speed_mode=speed_mode)
 
 
 def type_table(groups):
@@ -41,14 +41,16 @@ def type_table(groups):
 def oracle_types(groups):
     return [OC.VType(CTRL[g['controller']], g['p'], FAILSAFE[g['fail_safe']], g['noise'],
                      g['delay'], g['max_accel'], g['max_decel'], 5.0, g['sim_tau'],
-                     g['sim_min_gap'], g['sim_max_speed']) for g in groups]
+                     g['sim_min_gap'], g['sim_max_speed'], speed_mode=g.get('speed_mode', 0))
+            for g in groups]
 
 
 def engine_types(groups):
     from flow_b200 import engine as EN
     return [EN.make_vtype(CTRL[g['controller']], g['p'], g['fail_safe'], g['noise'],
                           g['delay'], g['max_accel'], g['max_decel'], 5.0, g['sim_tau'],
-                          g['sim_min_gap'], g['sim_max_speed']) for g in groups]
+                          g['sim_min_gap'], g['sim_max_speed'], speed_mode=g.get('speed_mode', 0))
+            for g in groups]
 
 
 def make_oracle(groups, length, env_kind=OS.ENV_ACCEL, **kw):
@@ -75,9 +77,11 @@ def c1_groups():
 C1 = dict(length=230, bunching=20.0, target_velocity=10.0, horizon=3000)
 
 
-def c2_groups(noise=0.0):
-    """examples/exp_configs/rl/singleagent/singleagent_ring.py: 21 IDM + 1 RL."""
-    return [vt('IDM', 21, noise=noise, sim_min_gap=0.0), vt('RL', 1)]
+def c2_groups(noise=0.0, speed_mode=0):
+    """examples/exp_configs/rl/singleagent/singleagent_ring.py: 21 IDM + 1 RL. The config leaves
+    speed_mode at the reference's default (25); 0 = the goldens' setting (no SUMO clamp)."""
+    return [vt('IDM', 21, noise=noise, sim_min_gap=0.0, speed_mode=speed_mode),
+            vt('RL', 1, speed_mode=speed_mode)]
 
 
 C2 = dict(bunching=50.0, init_min_gap=0.0, warmup_steps=750, horizon=3000,

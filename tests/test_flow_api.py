@@ -18,15 +18,19 @@ REF = '/root/reference'
 
 
 def ring_flow_params(api=F, ctrl=None, env=None, noise=0.0, length=260, ring=(220, 270),
-                     lanes=1, env_extra=None, n_human=21, n_rl=1, warmup=750):
-    """examples/exp_configs/rl/singleagent/singleagent_ring.py, spelled with `api`'s classes."""
+                     lanes=1, env_extra=None, n_human=21, n_rl=1, warmup=750, speed_mode=None):
+    """examples/exp_configs/rl/singleagent/singleagent_ring.py, spelled with `api`'s classes.
+    speed_mode None = the config's (the reference's default 'right_of_way'); the goldens were
+    produced without SUMO's clamp, i.e. 'aggressive'."""
     ctrl = ctrl or api.IDMController
+    sm = {} if speed_mode is None else {'speed_mode': speed_mode}
     v = api.VehicleParams()
     v.add(veh_id='human', acceleration_controller=(ctrl, {'noise': noise} if noise else {}),
-          car_following_params=api.SumoCarFollowingParams(min_gap=0),
+          car_following_params=api.SumoCarFollowingParams(min_gap=0, **sm),
           routing_controller=(api.ContinuousRouter, {}), num_vehicles=n_human)
     if n_rl:
         v.add(veh_id='rl', acceleration_controller=(api.RLController, {}),
+              car_following_params=api.SumoCarFollowingParams(**sm),
               routing_controller=(api.ContinuousRouter, {}), num_vehicles=n_rl)
     add = {'max_accel': 1, 'max_decel': 1, 'ring_length': list(ring)}
     add.update(env_extra or {})
@@ -41,10 +45,12 @@ def ring_flow_params(api=F, ctrl=None, env=None, noise=0.0, length=260, ring=(22
         veh=v, initial=api.InitialConfig(bunching=50, min_gap=0), detector_params=None)
 
 
-def c1_flow_params(api=F):
+def c1_flow_params(api=F, speed_mode=None):
     """examples/exp_configs/non_rl/ring.py: 22 IDM, 230 m, AccelEnv."""
     v = api.VehicleParams()
+    sm = {} if speed_mode is None else {'speed_mode': speed_mode}
     v.add(veh_id='idm', acceleration_controller=(api.IDMController, {}),
+          car_following_params=api.SumoCarFollowingParams(**sm),
           routing_controller=(api.ContinuousRouter, {}), num_vehicles=22)
     return dict(
         exp_tag='ring', env_name=api.AccelEnv, network=api.RingNetwork, simulator='traci',
@@ -172,9 +178,12 @@ def test_lane_change_direction_check_is_the_references():
 def lane_change_po_flow_params(api=F):
     """3-lane 230 m ring, 21 IDM + 1 RL, LaneChangeAccelPOEnv (tests/golden/ring_c3_po.npz, case a)."""
     v = api.VehicleParams()
+    # the golden was produced without SUMO's speed-mode clamp: 'aggressive'
     v.add(veh_id='human', acceleration_controller=(api.IDMController, {}),
+          car_following_params=api.SumoCarFollowingParams(speed_mode='aggressive'),
           routing_controller=(api.ContinuousRouter, {}), num_vehicles=21)
     v.add(veh_id='rl', acceleration_controller=(api.RLController, {}),
+          car_following_params=api.SumoCarFollowingParams(speed_mode='aggressive'),
           routing_controller=(api.ContinuousRouter, {}), num_vehicles=1)
     return dict(
         exp_tag='lc_po', env_name=api.LaneChangeAccelPOEnv, network=api.RingNetwork,
@@ -227,7 +236,7 @@ def test_gpu_experiment_c1_matches_reference_golden():
     """Experiment(flow_params).run through the mirrored API == the trajectory the
     REAL reference controllers produced (tests/golden/ring_c1.npz)."""
     z = np.load(os.path.join(G, 'ring_c1.npz'))
-    fp = c1_flow_params()
+    fp = c1_flow_params(speed_mode='aggressive')
     create_env, name = F.make_create_env(fp)
     assert name.startswith('AccelEnv-v')
     env = create_env()
@@ -261,7 +270,7 @@ def test_gpu_experiment_c1_matches_reference_golden():
     assert not env.k.simulation.check_collision()
     env.terminate()
 
-    exp = F.Experiment(c1_flow_params())
+    exp = F.Experiment(c1_flow_params(speed_mode='aggressive'))
     exp.env.env_params.horizon = 300
     info = exp.run(1)
     assert info['returns'][0] == pytest.approx(float(z['reward'][:300].sum()), rel=1e-9)
@@ -274,7 +283,7 @@ def test_gpu_wave_attenuation_po_env_matches_golden():
     because the golden run starts from a stated position vector)."""
     z = np.load(os.path.join(G, 'ring_c2.npz'))
     for tag in ('a', 'b'):
-        fp = ring_flow_params(warmup=0)
+        fp = ring_flow_params(warmup=0, speed_mode='aggressive')
         env = F.make_create_env(fp)[0]()
         env.reset()
         env.engine.reset(lengths=[float(z['length_' + tag])])   # the golden run's ring length

