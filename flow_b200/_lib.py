@@ -59,6 +59,7 @@ class FsConfig(C.Structure):
 
 FS_ABI_VERSION = 3
 FS_MAX_INFLOWS = 4
+FS_NOALLOC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 
 class FsInflow(C.Structure):
@@ -107,6 +108,7 @@ SYMBOLS = [
     ('fs_step_unfused', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_host_staging', C.c_int, [C.c_void_p, C.c_int, C.POINTER(FsHostViews)]),
+    ('fs_step_host_noalloc', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host_async', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_buffers', C.c_int, [C.c_void_p, C.POINTER(FsViews)]),
     ('fs_dlpack_wrap', C.c_void_p, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -1118,6 +1118,89 @@ extern "C" int fs_step_host(fs_engine* e, const void* actions, int k, void* obs_
   return FS_OK;
 }
 
+// ---- fs_step_host_noalloc -----------------------------------------------------------------
+// No counterpart in the reference: added for callers
+// that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it). Same contract as fs_step_host, but the device staging the step kernels read
+// the actions from and write every step's obs / reward / done into does NOT come from
+// cudaMalloc (fs_step_host grows its staging with cudaMalloc / cudaFree whenever a call is
+// larger than the last): it is this file-scope device array of FS_NOALLOC_SCRATCH_BYTES.
+// Every GPU that loads the library holds these bytes until the process exits.
+//
+// In HOST code the name `fs_noalloc_scratch` is only a stand-in for the symbol, not a device
+// address: the address is looked up with cudaGetSymbolAddress once per device, with that
+// device current (scratch_base below), and that pointer is what the kernels get.
+//
+// All calls on one GPU share the array (also calls on different engines): it keeps the last
+// call's contents, so the output regions a call uses are cleared first, and calls that overlap
+// on the GPU (two host threads, two engines on different streams) race - serialise them.
+static __device__ __align__(256) unsigned char fs_noalloc_scratch[FS_NOALLOC_SCRATCH_BYTES];
+
+// never launched: names the array in device code so that it is kept in the device image even
+// though only host code (cudaGetSymbolAddress) refers to it
+__global__ void fs_noalloc_keepalive(unsigned char** out) { *out = fs_noalloc_scratch; }
+
+static const int FS_NOALLOC_MAX_DEVICES = 64;
+static unsigned char* g_noalloc_base[FS_NOALLOC_MAX_DEVICES] = {};
+
+// device address of the array on the engine's device (which the caller made current)
+static int scratch_base(fs_engine* e, unsigned char** out) {
+  const int dev = e->cfg.device;
+  if (dev < 0 || dev >= FS_NOALLOC_MAX_DEVICES)
+    return fail(e, FS_EINVAL, "fs_step_host_noalloc: device ordinal beyond 63");
+  if (!g_noalloc_base[dev]) {
+    void* ptr = nullptr;
+    cudaError_t st = cudaGetSymbolAddress(&ptr, fs_noalloc_scratch);
+    if (st != cudaSuccess || !ptr) {
+      e->err = std::string("fs_step_host_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(st);
+      return FS_ECUDA;
+    }
+    g_noalloc_base[dev] = (unsigned char*)ptr;
+  }
+  *out = g_noalloc_base[dev];
+  return FS_OK;
+}
+
+extern "C" int fs_step_host_noalloc(fs_engine* e, const void* actions, int k, void* obs_seq,
+                                    void* reward_seq, uint8_t* done_seq) {
+  if (!e) return FS_EINVAL;
+  if (!e->types_set) return fail(e, FS_ESTATE, "fs_step_host_noalloc: call fs_set_types first");
+  if (k < 0) return fail(e, FS_EINVAL, "fs_step_host_noalloc: k must be >= 0");
+  cudaSetDevice(e->cfg.device);
+  unsigned char* base = nullptr;
+  int rc = scratch_base(e, &base);
+  if (rc != FS_OK || k == 0) return rc;     // k == 0: set-up only (resolve the address, e.g. before a capture)
+  const size_t E = e->cfg.n_envs, ts = tsize(e);
+  const bool with_act = actions && e->act_dim > 0;
+  const size_t nb_act = with_act ? (size_t)k * e->act_dim * E * ts : 0,
+               nb_obs = obs_seq ? (size_t)k * E * e->obs_dim * ts : 0,
+               nb_rew = reward_seq ? (size_t)k * E * ts : 0, nb_done = done_seq ? (size_t)k * E : 0;
+  const size_t o_obs = align256(nb_act), o_rew = o_obs + align256(nb_obs),
+               o_done = o_rew + align256(nb_rew), total = o_done + align256(nb_done);
+  if (total > (size_t)FS_NOALLOC_SCRATCH_BYTES) {
+    char msg[256];
+    snprintf(msg, sizeof(msg), "fs_step_host_noalloc: this call needs %zu bytes of device staging "
+             "(k = %d steps x %zu envs), the static scratch holds FS_NOALLOC_SCRATCH_BYTES = %d; "
+             "use fewer steps per call or fs_step_host", total, k, E, FS_NOALLOC_SCRATCH_BYTES);
+    return fail(e, FS_EINVAL, msg);
+  }
+  if (with_act)
+    FS_CUDA(e, cudaMemcpyAsync(base, actions, nb_act, cudaMemcpyHostToDevice, e->stream));
+  // the array keeps the previous call's results: clear the regions this call hands back
+  if (total > o_obs) FS_CUDA(e, cudaMemsetAsync(base + o_obs, 0, total - o_obs, e->stream));
+  rc = fs_step(e, with_act ? base : nullptr, k, obs_seq ? base + o_obs : nullptr,
+               reward_seq ? base + o_rew : nullptr, done_seq ? base + o_done : nullptr);
+  if (rc != FS_OK) return rc;
+  if (obs_seq)
+    FS_CUDA(e, cudaMemcpyAsync(obs_seq, base + o_obs, nb_obs, cudaMemcpyDeviceToHost, e->stream));
+  if (reward_seq)
+    FS_CUDA(e, cudaMemcpyAsync(reward_seq, base + o_rew, nb_rew, cudaMemcpyDeviceToHost, e->stream));
+  if (done_seq)
+    FS_CUDA(e, cudaMemcpyAsync(done_seq, base + o_done, nb_done, cudaMemcpyDeviceToHost, e->stream));
+  FS_CUDA(e, cudaStreamSynchronize(e->stream));
+  return FS_OK;
+}
+
 extern "C" int fs_step_host_async(fs_engine* e, const void* actions, int k, void* obs_seq,
                                   void* reward_seq, uint8_t* done_seq) {
   if (!e) return FS_EINVAL;

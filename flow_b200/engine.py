@@ -255,6 +255,24 @@ class Engine:
             None if obs is None else obs.ctypes.data, rew.ctypes.data, done.ctypes.data))
         return obs, rew, done
 
+    def step_host_noalloc(self, actions, k=1, want_obs=True):
+        """step_host() through fs_step_host_noalloc: same results, device staging in the
+        library's static scratch array (no cudaMalloc in the call; see include/flowstep.h for
+        the size limit and the sharing rule)."""
+        E = self.n_envs
+        a = None
+        if actions is not None:
+            a = np.ascontiguousarray(actions, dtype=self.np_dtype)
+            if a.size != k * self.act_dim * E:
+                raise ValueError('actions must have k*act_dim*n_envs elements')
+        obs = np.empty((k, E, self.obs_dim), self.np_dtype) if want_obs else None
+        rew = np.empty((k, E), self.np_dtype)
+        done = np.empty((k, E), np.uint8)
+        self._check(self.lib.fs_step_host_noalloc(
+            self.h, None if a is None else a.ctypes.data, k,
+            None if obs is None else obs.ctypes.data, rew.ctypes.data, done.ctypes.data))
+        return obs, rew, done
+
     def host_staging(self, k=1):
         """The engine's pinned host block for closed-loop calls of k <= 8 steps
         (fs_host_staging): numpy views (actions [k, act_dim, E], obs [k, E, obs_dim],

@@ -314,6 +314,26 @@ typedef struct fs_host_views {
 } fs_host_views;
 int fs_host_staging(fs_engine* e, int k, fs_host_views* out);
 
+/* fs_step_host for callers that may not allocate device memory. NO COUNTERPART IN THE
+ * REFERENCE: added (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc). Same arguments and results as fs_step_host
+ * (HOST buffers in and out, blocks until the results are on the host), but the device staging
+ * between the copies and the step kernels is a file-scope static __device__ array of
+ * FS_NOALLOC_SCRATCH_BYTES instead of cudaMalloc'ed blocks: the call makes no cudaMalloc /
+ * cudaFree and no allocating library call. Limits and rules:
+ *   - a call whose actions + obs + reward + done of all k steps (each rounded up to 256 B)
+ *     exceed FS_NOALLOC_SCRATCH_BYTES is rejected with FS_EINVAL and a message naming both sizes
+ *     (c2, 4096 envs fp32: 86 KB per step -> k <= 48; 65 536 envs: k <= 2);
+ *   - every GPU that loads the library holds the array until the process exits;
+ *   - ALL calls on one GPU share it, whatever the engine: calls that overlap on the GPU race,
+ *     the caller serialises them; the regions a call hands back are cleared first, nothing of an
+ *     earlier call is visible;
+ *   - k = 0 does the one-time set-up only (looks the array's device address up for the
+ *     engine's device), e.g. ahead of a stream capture. */
+#define FS_NOALLOC_SCRATCH_BYTES (4 * 1024 * 1024)
+int fs_step_host_noalloc(fs_engine* e, const void* actions, int k, void* obs_seq,
+                         void* reward_seq, uint8_t* done_seq);
+
 /* Pipelined form of fs_step_host for open-loop rollouts (the action sequence
  * is known up front): enqueues H2D actions -> k fused steps -> D2H results on
  * three internal streams and returns without waiting, so the upload of call
