@@ -57,6 +57,9 @@ PEAK_TFLOPS = {'f32': SM_COUNT * 128 * 2 * SM_GHZ / 1e3, 'f64': SM_COUNT * 64 * 
 # counted flop per vehicle-step (IDM + move + headway + reward = 30; Philox +
 # Box-Muller amortised over 4 normals = 25 more when the humans carry noise)
 FLOP_IDM, FLOP_NOISE = 30, 25
+# speed-mode bit 0 (the reference's default mode 25 has it): a second IDM evaluation (the restated
+# simulator model) + min: |h| clamp 2 + dv 1 + s* 6 + (v/v0)^4 3 + (s*/h)^2 2 + a(1-.-.) 3 + min 1
+FLOP_SAFE = 18
 DEFAULT_FUSE = {'c2': 500, 'ma': 500}          # else 100 (what BASELINE.json states for c5)
 
 
@@ -74,6 +77,10 @@ def parse(argv=None):
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     ap.add_argument('--noise', type=float, default=0.2,
                     help='IDM accel noise std (0.2 in singleagent_ring.py; 0 = parity setting)')
+    ap.add_argument('--speed-mode', type=int, default=25,
+                    help="SumoCarFollowingParams.speed_mode of every type (25 = 'right_of_way', the "
+                         "reference's default, which every shipped config leaves in place; 0 = "
+                         "'aggressive': no restated SUMO clamp on commanded speeds)")
     ap.add_argument('--target-ms', type=float, default=100.0,
                     help='GPU work inside every timed bracket (the K-step pass is repeated)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -148,7 +155,7 @@ def _ref_root():
 _CPU = {}
 
 
-def _cpu_init(kind, seed_base, noise):
+def _cpu_init(kind, seed_base, noise, speed_mode):
     """Pool initializer: one persistent c2 env per worker process.
     kind 'reference': the reference's OWN IDMController.get_action (noise + fail-safe),
     TraCIVehicle.apply_acceleration, WaveAttenuationPOEnv.get_state / compute_reward
@@ -161,11 +168,12 @@ def _cpu_init(kind, seed_base, noise):
     if kind == 'reference':
         os.environ['FLOW_REFERENCE'] = _ref_root()
         from tests.golden.ref_harness import RefRing, ref_ctrl
-        env = RefRing([('human', ref_ctrl.IDMController, {'noise': noise}, {'min_gap': 0}, 21),
-                       ('rl', 'rl', {}, {}, 1)], length, 'wave_po',
+        env = RefRing([('human', ref_ctrl.IDMController, {'noise': noise},
+                        {'min_gap': 0, 'speed_mode': speed_mode}, 21),
+                       ('rl', 'rl', {}, {'speed_mode': speed_mode}, 1)], length, 'wave_po',
                       init_kw=dict(bunching=50, min_gap=0),
                       env_additional={'max_accel': 1, 'max_decel': 1, 'ring_length': [220, 270]},
-                      index_shortcut=True)
+                      index_shortcut=True, use_speed_mode=True)
 
         def advance(acts):
             for a in acts:
@@ -175,7 +183,8 @@ def _cpu_init(kind, seed_base, noise):
     else:
         from oracle import sim as OS
         from oracle import controllers as OC
-        types = [OC.VType(OC.IDM, OC.idm_params(), noise=noise, sim_min_gap=0.0), OC.VType(OC.RL)]
+        types = [OC.VType(OC.IDM, OC.idm_params(), noise=noise, sim_min_gap=0.0, speed_mode=speed_mode),
+                 OC.VType(OC.RL, speed_mode=speed_mode)]
         env = OS.RingSim(types, [0] * 21 + [1], length, bunching=50.0,
                          env_kind=OS.ENV_WAVE_ATTENUATION_PO, warmup_steps=0, horizon=10 ** 9,
                          act_lo=-1, act_hi=1, obs_max_length=270.0,
@@ -204,11 +213,11 @@ def _cpu_kind():
 class CpuArm:
     """All host cores, one env per worker process (how RLlib runs the reference)."""
 
-    def __init__(self, kind, noise, cores=None):
+    def __init__(self, kind, noise, speed_mode, cores=None):
         import multiprocessing as mp
         self.kind, self.cores = kind, cores or os.cpu_count() or 1
         self.pool = mp.get_context('spawn').Pool(self.cores, initializer=_cpu_init,
-                                                 initargs=(kind, 977, noise))
+                                                 initargs=(kind, 977, noise, speed_mode))
         cal = self.pool.map(_cpu_advance, [60] * self.cores, chunksize=1)   # untimed: imports, first steps
         self.per_core = 60.0 / statistics.mean(cal)                          # Env.steps/s per worker
 
@@ -234,12 +243,12 @@ class CpuArm:
                 '%d passes, workload c2 on %s' % (self.cores, chunk, n_passes, what))
 
 
-def cpu_baseline(seconds, noise):
+def cpu_baseline(seconds, noise, speed_mode):
     """Bounded sample of workload c2 on the host cores: the reference-code harness
     (kind 'reference') when the reference package is importable, and the oracle port beside it."""
     out = None
     for kind in ([_cpu_kind()] if _cpu_kind() == 'port' else ['reference', 'port']):
-        arm = CpuArm(kind, noise)
+        arm = CpuArm(kind, noise, speed_mode)
         budget = seconds * (0.7 if kind == 'reference' else 0.3) if _cpu_kind() == 'reference' else seconds
         chunk = int(max(20, min(3000, arm.per_core * budget)))
         steps, wall = arm.run(chunk, 1)
@@ -266,7 +275,7 @@ def run_reference(a):
     if rank != 0:
         return
     kind = _cpu_kind()
-    arm = CpuArm(kind, a.noise)
+    arm = CpuArm(kind, a.noise, a.speed_mode)
     chunk = int(max(1, min(3000, arm.per_core * 60.0 / max(a.warmup + a.steps, 1))))
     arm.run(chunk, a.warmup)
     env_steps, wall = arm.run(chunk, a.steps)
@@ -279,6 +288,7 @@ def run_reference(a):
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
         'data': 'synthetic', 'env_steps_per_s': env_steps / wall,
         'config': {'workload': workload_name('c2'), 'vehicles_per_env': N_VEH, 'idm_noise': a.noise,
+                   'speed_mode': a.speed_mode,
                    'envs_per_gpu': arm.cores, 'env_steps_per_bench_step': chunk * arm.cores,
                    'note': 'CPU arm: one env per host core; a bench step = every core advances its env '
                            'by %d Env.steps (bounded sample of the same workload)' % chunk},
@@ -381,7 +391,7 @@ class Leg:
         self.K = k_steps
         self.F = a.fuse or DEFAULT_FUSE.get(workload, 100)
         E = (a.envs if (a.envs and workload == a.workload) else 0) or wl['n_envs']
-        types, tov, kw = wl['builder'](noise=a.noise)
+        types, tov, kw = wl['builder'](noise=a.noise, speed_mode=a.speed_mode)
         self.H = int(kw['horizon'])
         if scaling == 'strong':
             env_id_base, E = SH.shard_envs(E, rank, world)   # the workload's envs split over the GPUs
@@ -559,7 +569,8 @@ class Leg:
 
     # ---- rooflines
     def flop_per_vehicle_step(self):
-        return FLOP_IDM + (FLOP_NOISE if self.a.noise > 0 else 0)
+        return FLOP_IDM + (FLOP_NOISE if self.a.noise > 0 else 0) + \
+            (FLOP_SAFE if self.a.speed_mode & 1 else 0)
 
     def bytes_per_env_step(self, active_per_env):
         """SURVEY 8d single-step algorithmic bytes: state round trip 4 x T per (active) vehicle
@@ -596,7 +607,7 @@ class Leg:
                     'launch, DRAM carries only actions in and obs/reward/done out (`traffic`), so the '
                     'bound is instruction issue (SURVEY 8d second bullet): achieved = vehicle-steps/s '
                     'per GPU x counted flop per vehicle-step (IDM + move + headway + reward 30, '
-                    'Philox + Box-Muller noise 25). The HBM reading belongs to the one-step-per-launch '
+                    'Philox + Box-Muller noise 25, speed-mode safe speed = second IDM 18). The HBM reading belongs to the one-step-per-launch '
                     'variant: `roofline_single_step`.'}
 
     def roofline_single(self, r, active_per_env):
@@ -697,7 +708,8 @@ def run_b200(a):
         'data': 'synthetic',
         'env_steps_per_s': fused['env_steps'] / (fused['ms'] * 1e-3),
         'config': {'workload': info['workload'], 'envs_per_gpu': E,
-                   'vehicles_per_env': info['n_slots'], 'idm_noise': a.noise, 'fuse': info['fuse'],
+                   'vehicles_per_env': info['n_slots'], 'idm_noise': a.noise,
+                   'speed_mode': a.speed_mode, 'fuse': info['fuse'],
                    'reps': fused['reps'], 'timed_region_ms': fused['ms'],
                    'env_steps_timed_per_env': fused['steps'],
                    'timing': 'the K-step pass repeated `reps` times back to back (calibrated so the '
@@ -746,7 +758,7 @@ def run_b200(a):
     if legs:
         line['legs'] = legs
     if world == 1 and not a.no_cpu_baseline and not a.only_fused:
-        line['cpu_baseline'] = cpu_baseline(a.cpu_seconds, a.noise)
+        line['cpu_baseline'] = cpu_baseline(a.cpu_seconds, a.noise, a.speed_mode)
     _emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

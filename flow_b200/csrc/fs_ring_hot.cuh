@@ -143,6 +143,9 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
   IdmRegs<T> pm = P.pa;
   T nz = P.noise;
   if (VPT == 1 && is_rl) { pm = P.pb; nz = T(0); }
+  // simulator model behind the speed mode for slot RL_SLOT: the RL type's on the RL thread
+  IdmRegs<T> psim_rl = P.ps;
+  if (kSafe && is_rl) psim_rl = P.pb;
   const T len = P.len, dt = P.dt;
   const T C = B.circ[e];
   const T crash_thr = P.collision_min_gap ? P.min_gap : T(0);
@@ -270,19 +273,36 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
               T vl;
               if (i + 1 < VPT) vl = (kExact || i + 1 < n_mine) ? v[i + 1 < VPT ? i + 1 : 0] : v_lead_last;
               else vl = v_lead_last;
-              T a = idm_fast<T, true>(vi, vl, hi, pm);
+              // controller law and, with a speed mode (kSafe), the simulator model whose next
+              // speed caps what Flow commands (restated SUMO, speed_mode_fast): for the RL
+              // vehicle's slot the model of the RL type on the RL thread (psim_rl)
+              T a, a_sim = T(0);
+              if (kSafe && kF32) {
+                float af, asf;
+                idm_pair_f32((float)vi, (float)vl, (float)hi, reinterpret_cast<const IdmRegs<float>&>(pm),
+                             reinterpret_cast<const IdmRegs<float>&>(i == RL_SLOT ? psim_rl : P.ps), af, asf);
+                a = (T)af; a_sim = (T)asf;
+              } else {
+                a = idm_fast<T, true>(vi, vl, hi, pm);
+                if (kSafe) a_sim = idm_fast<T, true>(vi, vl, hi, i == RL_SLOT ? psim_rl : P.ps);
+              }
               if (kNoise) {
                 const T z = kTimeNoise ? zn[kNoise ? i : 0][j] : zn[kNoise ? (i >> 2) : 0][i & 3];
                 a = add(a, mul(VPT == 1 ? nz : P.noise, z));
               }
-              if (kSafe)   // SUMO's speed mode on the human's commanded speed (restated)
-                a = speed_mode_fast<T>(a, vi, vl, hi, true, P.ps, P.safe_a, P.cap_a, P.floor_a);
+              if (kSafe) {   // SUMO's speed mode on the human's commanded speed
+                if (P.safe_a) a = N::min(a, a_sim);
+                a = N::max(N::min(a, P.cap_a), P.floor_a);
+              }
               if (i == RL_SLOT) {
                 if (kAct) {  // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
                   const T raw = ac[j];
                   T a_c = N::min(N::max(raw, P.act_lo), P.act_hi);
                   act_abs = N::abs(P.clip_actions ? a_c : raw);
-                  if (kSafe) a_c = speed_mode_fast<T>(a_c, vi, vl, hi, true, P.pb, P.safe_b, P.cap_b, P.floor_b);
+                  if (kSafe) {
+                    if (P.safe_b) a_c = N::min(a_c, a_sim);
+                    a_c = N::max(N::min(a_c, P.cap_b), P.floor_b);
+                  }
                   a = is_rl ? a_c : a;
                 } else {  // un-commanded RL vehicle: restated simulator default model, no speed mode
                   if (is_rl) a = idm_fast<T, true>(vi, vl, hi, P.pb);
