@@ -27,6 +27,7 @@
 #pragma once
 #include "fs_common.cuh"
 #include "fs_ring.cuh"
+#include "fs_ring_fast.cuh"
 
 namespace fs {
 
@@ -253,11 +254,23 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         const T vi = v[r], hi = h[r];
         const T vl = has_lead ? vs[s - 1] : T(-1001);
         T st0 = T(0);
-        T a;
+        T a, a_sim = T(0);
+        bool have_sim = false;
         if (kGeneric)
           a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, has_f, has_f ? vs[s + 1] : T(-1001),
                             has_f ? hs[s + 1] : T(-1001), mean_v, dt, cfg.inv_dt, st0);
-        else   // the same arithmetic as ctrl_accel's IDM / SIM cases (fs_ring.cuh does the same)
+        else if (sizeof(T) == 4 && (tp.speed_mode & 1) && tp.e_delta == T(4)) {
+          // IDM-law vehicle under a speed mode: its law and the simulator model behind the
+          // mode's safe speed evaluated together (idm_pair_f32, fs_ring_fast.cuh)
+          IdmRegs<float> pp, pq;
+          pp.s0 = (float)tp.e_s0; pp.Tt = (float)tp.e_T; pp.inv_tsab = (float)tp.e_inv_tsab;
+          pp.inv_v0 = (float)tp.e_inv_v0; pp.a = (float)tp.e_a;
+          pq.s0 = (float)tp.sim_min_gap; pq.Tt = (float)tp.sim_tau; pq.inv_tsab = (float)tp.sim_inv_two_sqrt_ab;
+          pq.inv_v0 = (float)tp.sim_inv_v0; pq.a = (float)tp.max_accel;
+          float af, asf;
+          idm_pair_f32((float)vi, (float)vl, (float)hi, pp, pq, af, asf, has_lead);
+          a = (T)af; a_sim = (T)asf; have_sim = true;
+        } else   // the same arithmetic as ctrl_accel's IDM / SIM cases (fs_ring.cuh does the same)
           a = idm_accel<T>(vi, vl, hi, has_lead, tp.e_v0, tp.e_inv_v0, tp.e_T, tp.e_a, tp.e_tsab,
                            tp.e_inv_tsab, tp.e_delta, tp.e_s0);
         bool commanded = ctrl != FS_CTRL_SIM && ctrl != FS_CTRL_RL;
@@ -277,7 +290,17 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         }
         acc[r] = a;      // commanded (the `accel` view)
         // a speed Flow commands passes SUMO's speed mode (restated, fs_common.cuh)
-        aeff[r] = (commanded && tp.speed_mode != 0) ? speed_mode_accel<T>(tp, a, vi, vl, hi, has_lead) : a;
+        T ae = a;
+        if (commanded && tp.speed_mode != 0) {
+          if (have_sim) {
+            ae = N::min(a, a_sim);
+            if (tp.speed_mode & 2) ae = N::min(ae, tp.max_accel);
+            if (tp.speed_mode & 4) ae = N::max(ae, T(0) - tp.max_decel);
+          } else {
+            ae = speed_mode_accel<T>(tp, a, vi, vl, hi, has_lead);
+          }
+        }
+        aeff[r] = ae;
       }
       __syncwarp();
       tc += 1;

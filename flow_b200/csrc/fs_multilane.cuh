@@ -460,8 +460,18 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
               ae = a;
             }
           } else {
-            a = idm_accel<T>(vi, vlead, hi, has_lead, P.pa.v0, P.pa.inv_v0, P.pa.Tt, P.pa.a,
-                             P.pa.tsab, P.pa.inv_tsab, P.pa.delta, P.pa.s0);
+            T a_sim = T(0);
+            const bool pair = kF32 && P.safe_a && !P.human_is_sim && P.pa.delta == T(4);   // uniform
+            if (pair) {   // controller law + the simulator model behind the speed mode, fused
+              float af, asf;
+              idm_pair_f32((float)vi, (float)vlead, (float)hi,
+                           reinterpret_cast<const IdmRegs<float>&>(P.pa),
+                           reinterpret_cast<const IdmRegs<float>&>(P.ps), af, asf, has_lead);
+              a = (T)af; a_sim = (T)asf;
+            } else {
+              a = idm_accel<T>(vi, vlead, hi, has_lead, P.pa.v0, P.pa.inv_v0, P.pa.Tt, P.pa.a,
+                               P.pa.tsab, P.pa.inv_tsab, P.pa.delta, P.pa.s0);
+            }
             ae = a;
             if (!P.human_is_sim) {   // base_controller.py:109-116: noise, then fail-safe
               if (noisy) a = add(a, mul(P.noise, zn[s]));
@@ -469,7 +479,8 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
                 a = failsafe_instantaneous<T>(a, vi, hi, has_lead, V, dt);
               else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
                 a = failsafe_safe_velocity<T>(a, vi, vlead, hi, V, dt, P.delay);
-              ae = speed_mode_fast<T>(a, vi, vlead, hi, has_lead, P.ps, P.safe_a, P.cap_a, P.floor_a);
+              if (pair) ae = N::max(N::min(N::min(a, a_sim), P.cap_a), P.floor_a);
+              else ae = speed_mode_fast<T>(a, vi, vlead, hi, has_lead, P.ps, P.safe_a, P.cap_a, P.floor_a);
             }
           }
         } else {

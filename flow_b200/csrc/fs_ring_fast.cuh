@@ -180,12 +180,14 @@ __device__ __forceinline__ T speed_mode_fast(T a, T v, T v_l, T h, bool has_lead
 // both with delta = 4. Same values as two idm_fast<float, true> calls (x / h there is
 // x * rcp(h) too), about 10 instructions instead of 16 for the second law and no second MUFU.
 __device__ __forceinline__ void idm_pair_f32(float v, float v_lead, float h, const IdmRegs<float>& p,
-                                             const IdmRegs<float>& q, float& a_p, float& a_q) {
+                                             const IdmRegs<float>& q, float& a_p, float& a_q,
+                                             bool has_lead = true) {
   if (fabsf(h) < 1e-3f) h = 1e-3f;
   const float ih = __fdividef(1.0f, h);
   const float vv = v * (v - v_lead);
-  const float sp = p.s0 + fmaxf(0.0f, v * p.Tt + vv * p.inv_tsab);
-  const float sq = q.s0 + fmaxf(0.0f, v * q.Tt + vv * q.inv_tsab);
+  // no leader: s* = 0 (car_following_models.py:474-480)
+  const float sp = has_lead ? p.s0 + fmaxf(0.0f, v * p.Tt + vv * p.inv_tsab) : 0.0f;
+  const float sq = has_lead ? q.s0 + fmaxf(0.0f, v * q.Tt + vv * q.inv_tsab) : 0.0f;
   const float rp = v * p.inv_v0, rq = v * q.inv_v0;
   const float rp2 = rp * rp, rq2 = rq * rq;
   const float hp = sp * ih, hq = sq * ih;
