@@ -600,8 +600,9 @@ class Leg:
             'kernel': '%s<%s> (flow_b200/csrc/), %d fused steps per launch'
                       % (KERNEL_OF.get(self.workload, 'ring1_hot_kernel'), self.dtype, self.F),
             'launch_ms': r['ms'] / max(r['launches'], 1),
-            'ncu': {k: prof.get(k) for k in ('issue_active_pct', 'warp_inst_per_vehicle_step',
-                                             'thread_inst_per_vehicle_step', 'warps_active_pct',
+            'ncu': {k: prof.get(k) for k in ('issue_active_pct', 'warps_active_pct',
+                                             'warp_inst_per_env_step', 'thread_inst_per_vehicle_step',
+                                             'fma_pipe_pct', 'alu_pipe_pct', 'xu_pipe_pct',
                                              'capture') if k in prof} or None,
             'note': 'fused K-step launch: vehicle state lives in registers / shared memory for the whole '
                     'launch, DRAM carries only actions in and obs/reward/done out (`traffic`), so the '

@@ -117,10 +117,16 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     pending[f] = (kProb && f < B.n_flows && B.prob[f] > 0.0) ? B.pending[(size_t)f * E + e] : 0;
   double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
 
+  // Slot rows (32 slots each) that hold a vehicle: at 2000 veh/h about 14 of c4's 160 slots are
+  // occupied, so every per-row loop below stops at the populated rows (warp-uniform bound);
+  // rows beyond keep x = v = 0, type 0 and are neither published nor read.
+  auto rows_of = [&](int m) { const int q = (m + 31) >> 5; return q < SLOTS ? q : SLOTS; };
   auto publish = [&]() {
     __syncwarp();
+    const int rows = rows_of(n);
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
+      if (r >= rows) break;
       const int s = lane_id + 32 * r;
       if (s < CAP) { xs[s] = x[r]; vs[s] = v[r]; ts[s] = ty[r]; }
     }
@@ -128,14 +134,17 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   };
   auto update = [&]() {  // headway to slot s-1; the head sees 1000 (no leader)
     publish();
+    const int rows = rows_of(n);
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
+      if (r >= rows) { h[r] = T(1000); continue; }
       const int s = lane_id + 32 * r;
       h[r] = (s > 0 && s < n) ? (xs[s - 1] - x[r]) - cfg.types[ts[s - 1]].length : T(1000);
     }
     __syncwarp();
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
+      if (r >= rows) break;
       const int s = lane_id + 32 * r;
       if (s < CAP) hs[s] = h[r];
     }
@@ -150,8 +159,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   auto rank_agents = [&]() {
     if (!kMA) return;
     n_rl = 0;
+    const int rows = rows_of(n);
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
+      if (r >= rows) { rank[kMA ? r : 0] = -1; continue; }
       const int s = lane_id + 32 * r;
       const bool rl = s < n && ((rl_types >> ty[r]) & 1u);
       const unsigned m = __ballot_sync(0xffffffffu, rl);
@@ -165,8 +176,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
   auto write_agents = [&](T* o, T* ol, bool with_reward, T cost1, bool fail) {
     if (!kMA) return;
     T rsum = T(0);
+    const int rows = rows_of(n);
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
+      if (r >= rows) break;
       const int s = lane_id + 32 * r;
       const int a = rank[kMA ? r : 0];
       if (a < 0 || a >= AG) continue;
@@ -224,8 +237,9 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     for (int r = 0; r < SLOTS; ++r) {
       const int s = lane_id + 32 * r;
       if (s >= CAP) continue;
-      const T a0 = s < n ? N::div(v[r], cfg.speed_limit) : T(0);
-      const T a1 = s < n ? N::div(x[r], Lr) : T(0);
+      const bool live_row = 32 * r < n;     // warp-uniform
+      const T a0 = (live_row && s < n) ? N::div(v[r], cfg.speed_limit) : T(0);
+      const T a1 = (live_row && s < n) ? N::div(x[r], Lr) : T(0);
       if (o) { o[s] = a0; o[CAP + s] = a1; }
       if (ol) { ol[s] = a0; ol[CAP + s] = a1; }
     }
@@ -244,8 +258,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         mean_v = N::div(sm, T(n > 0 ? n : 1));
       }
       // controllers -> apply_acceleration -> Euler move (all read the published state)
+      const int rows0 = rows_of(n);
 #pragma unroll
       for (int r = 0; r < SLOTS; ++r) {
+        if (r >= rows0) break;
         const int s = lane_id + 32 * r;
         if (s >= n) continue;
         const TypeP<T>& tp = cfg.types[ty[r]];
@@ -309,6 +325,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       int dst[SLOTS];
 #pragma unroll
       for (int r = 0; r < SLOTS; ++r) {
+        if (r >= rows0) { dst[r] = -1; continue; }
         const int s = lane_id + 32 * r;
         bool keep = false;
         if (s < n) {
@@ -334,6 +351,7 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
         __syncwarp();
 #pragma unroll
         for (int r = 0; r < SLOTS; ++r) {
+          if (r >= rows0) break;
           const int s = lane_id + 32 * r;
           if (s < n_keep) { x[r] = xs[s]; v[r] = vs[s]; ty[r] = ts[s]; acc[r] = hs[s]; }
           else { x[r] = T(0); v[r] = T(0); ty[r] = 0; acc[r] = T(0); }
@@ -387,8 +405,10 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
       update();
       bool cr = false;
       T sv = T(0), sq = T(0), s2 = T(0);
+      const int rows1 = rows_of(n);
 #pragma unroll
       for (int r = 0; r < SLOTS; ++r) {
+        if (r >= rows1) break;
         const int s = lane_id + 32 * r;
         if (s >= n) continue;
         cr |= h[r] < T(0);

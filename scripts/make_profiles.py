@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""Condense gpurun_out/ ncu exports into the tracked profiles/ summaries of a round.
-usage: make_profiles.py r01"""
+"""Condense gpurun_out/ ncu exports (scripts/gpu_r2_profile.sh) into the tracked profiles/
+summaries of a round.   usage: make_profiles.py r02"""
 import collections
 import csv
 import json
@@ -10,7 +10,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G, P = os.path.join(ROOT, 'gpurun_out'), os.path.join(ROOT, 'profiles')
-tag = sys.argv[1] if len(sys.argv) > 1 else 'r01'
+tag = sys.argv[1] if len(sys.argv) > 1 else 'r02'
+CMD = 'python bench.py --no-cpu-baseline --only-fused --target-ms 5 --steps 20 --warmup 5'
 
 
 def short(name):
@@ -23,76 +24,69 @@ def short(name):
 
 
 # 1. launch list -> per-kernel totals and shares
-ll = os.path.join(G, 'launches_c2.csv')
+ll = os.path.join(G, 'p2_launches_c2.csv')
 if os.path.exists(ll):
     rows = [r for r in csv.reader(open(ll)) if len(r) > 10 and r[0].isdigit()]
     agg = collections.OrderedDict()
     for r in rows:
-        k = short(r[4])
-        a = agg.setdefault(k, [0, 0.0, r[7], r[8]])
+        a = agg.setdefault(short(r[4]), [0, 0.0, r[7], r[8]])
         a[0] += 1
         a[1] += float(r[-1])
     tot = sum(a[1] for a in agg.values())
     with open(os.path.join(P, '%s_launches_c2_summary.csv' % tag), 'w') as f:
-        f.write('# ncu --metrics gpu__time_duration.sum --clock-control none, python bench.py '
-                '--steps 300 --warmup 100 --no-cpu-baseline (c2); per-launch times are '
-                'serialised and cold-cache: compare SHARES, not absolutes\n')
+        f.write('# ncu --metrics gpu__time_duration.sum --clock-control none -c 400, python bench.py '
+                '--no-cpu-baseline --no-extra-legs --only-fused --target-ms 20 --steps 20 --warmup 5 (c2); '
+                'per-launch times are serialised and cold-cache: compare SHARES, not absolutes. '
+                'ring1_hot_kernel<float, 3, 8, 1, 1, 1> = the timed fused launches (500 steps each), '
+                '<..., 1, 0, 1> = the 750 warm-up steps inside fs_reset (outside the timed brackets)\n')
         f.write('kernel,launches,total_us,share,block,grid\n')
         for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
             f.write('"%s",%d,%.1f,%.4f,"%s","%s"\n' % (k, a[0], a[1] / 1e3, a[1] / tot, a[2], a[3]))
-    # the raw list, ring kernels only, one line per launch
     with open(os.path.join(P, '%s_launches_c2.csv' % tag), 'w') as f:
         f.write('id,kernel,block,grid,gpu_time_ns\n')
         for r in rows:
             f.write('%s,"%s","%s","%s",%s\n' % (r[0], short(r[4]), r[7], r[8], r[-1]))
 
-# 2. full captures -> summary csv + traffic json
-traffic = {}
+# 2. full captures -> summary csv + per-env-step traffic / issue figures for bench.py
 KERNEL = {'c2': 'ring1_hot', 'c5': 'ring1_hot', 'c3': 'ring_ml', 'c4': 'highway_kernel'}
+traffic = {}
 for wl in ('c2', 'c5', 'c3', 'c4'):
-    raw = os.path.join(G, 'prof_%s_final_raw.csv' % wl)
-    if not os.path.exists(raw) and os.path.exists(os.path.join(G, 'prof_%s_raw.csv' % wl)):
-        raw = os.path.join(G, 'prof_%s_raw.csv' % wl)     # exported on the GPU box (gpu_final.sh)
-    rep = os.path.join(G, ('prof_%s_final.ncu-rep' if wl in ('c2', 'c5') else 'prof_%s.ncu-rep') % wl)
-    if os.path.exists(rep) and (not os.path.exists(raw) or os.path.getmtime(raw) < os.path.getmtime(rep)):
-        with open(raw, 'w') as f:
-            subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], stdout=f, stderr=subprocess.DEVNULL)
-    if not os.path.exists(raw):
+    raw = os.path.join(G, 'p2_%s_raw.csv' % wl)
+    plain = os.path.join(G, 'p2_plain_%s.json' % wl)
+    if not (os.path.exists(raw) and os.path.exists(plain)):
         continue
     out = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'ncu_summary.py'), raw],
                          capture_output=True, text=True).stdout
-    open(os.path.join(P, '%s_ncu_full_%s_%s_f32.csv' % (tag, wl, KERNEL[wl] if wl in ('c3', 'c4') else 'ring1_hot')), 'w').write(
-        '# ncu --set full --clock-control none --import-source on -k regex:%s, one timed '
-        'fused launch (%d steps) of python bench.py --workload %s --only-fused\n'
-        % (KERNEL[wl], 500 if wl == 'c2' else 100, wl) + out)
+    name = '%s_ncu_full_%s_%s_f32.csv' % (tag, wl, KERNEL[wl])
+    b = json.load(open(plain))
+    fuse, E = b['config']['fuse'], b['config']['envs_per_gpu']
+    open(os.path.join(P, name), 'w').write(
+        '# ncu --set full --clock-control none --import-source on -k regex:%s -s 2 -c 1: one timed '
+        'fused launch (%d steps x %d envs) of %s --workload %s (speed mode 25, idm noise 0.2)\n'
+        % (KERNEL[wl], fuse, E, CMD, wl) + out)
     rows = list(csv.reader(open(raw)))
     h, u, r = rows[0], rows[1], rows[2]
+
     def val(k):
-        i = h.index(k)
-        x = float(r[i])
-        return x * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u[i]]
-    traffic['%s_f32_fuse%d' % (wl, 500 if wl == 'c2' else 100)] = \
-        val('dram__bytes_read.sum') + val('dram__bytes_write.sum')
-rep = os.path.join(G, 'prof_c5_single.ncu-rep')
-raw = os.path.join(G, 'prof_c5_single_raw.csv')
-if os.path.exists(rep):
-    with open(raw, 'w') as f:
-        subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], stdout=f, stderr=subprocess.DEVNULL)
-if os.path.exists(raw):
-    out = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'ncu_summary.py'), raw],
-                         capture_output=True, text=True).stdout
-    open(os.path.join(P, '%s_ncu_full_c5_single_step.csv' % tag), 'w').write(
-        '# ncu --set full --clock-control none --import-source on -k regex:ring1_hot -s 12 -c 1, ONE '
-        'single-step launch (k = 1, 65 536 envs) of FS_NO_GRAPH=1 FS_NO_PDL=1 python bench.py '
-        '--workload c5 --steps 40 --warmup 10 --fuse 40\n' + out)
+        x = float(r[h.index(k)].replace(',', ''))
+        return x * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}.get(u[h.index(k)], 1)
+    env_steps = float(fuse) * E
+    veh = b['active_vehicles_per_env']
+    winst = val('smsp__inst_executed.sum')
+    tinst = val('smsp__thread_inst_executed.sum') if 'smsp__thread_inst_executed.sum' in h else \
+        winst * val('smsp__thread_inst_executed_per_inst_executed.ratio')
+    traffic['%s_f32' % wl] = {
+        'dram_bytes_per_env_step': (val('dram__bytes_read.sum') + val('dram__bytes_write.sum')) / env_steps,
+        'issue_active_pct': val('smsp__issue_active.avg.pct_of_peak_sustained_active'),
+        'warps_active_pct': val('sm__warps_active.avg.pct_of_peak_sustained_active'),
+        'warp_inst_per_env_step': winst / env_steps,
+        'thread_inst_per_vehicle_step': tinst / env_steps / veh,
+        'fma_pipe_pct': val('sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active'),
+        'alu_pipe_pct': val('sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active'),
+        'xu_pipe_pct': val('sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active'),
+        'launch_us_under_ncu': val('gpu__time_duration.sum') if u[h.index('gpu__time_duration.sum')] == 'us'
+        else val('gpu__time_duration.sum') / 1e3,
+        'capture': 'profiles/' + name}
 if traffic:
     json.dump(traffic, open(os.path.join(P, 'ncu_traffic.json'), 'w'), indent=1)
-
-# 3. bench lines
-for wl, src in (('c2', 'final_default.json'), ('c5', 'final_c5.json'), ('c3', 'bench_c3.json'),
-                ('c4', 'bench_c4.json'), ('mah', 'bench_mah.json'),
-                ('reference_arm', 'final_reference.json')):
-    b = os.path.join(G, src)
-    if os.path.exists(b):
-        open(os.path.join(P, '%s_bench_%s.json' % (tag, wl)), 'w').write(open(b).read())
-print(sorted(os.listdir(P)))
+print(json.dumps(traffic, indent=1))
