@@ -395,6 +395,10 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
       if (s.controller == FS_CTRL_IDM && s.p[4] != 4.0) ok = false;
     }
     if (ta < 0) ok = false;
+    // the IDM fast paths keep ONE collision threshold (the human type's minGap): with
+    // collision_min_gap set, types whose minGap differ need the generic kernel's per-leader test
+    if (ok && e->cfg.collision_min_gap && tb >= 0 && types[ta].sim_min_gap != types[tb].sim_min_gap)
+      ok = false;
     e->fast_ok = ok;
     {
       // hot-kernel pattern: exactly one RL vehicle and it is the last one
@@ -714,7 +718,8 @@ static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void
       const bool last = q == S - 1;
       int rc = do_step1<T>(e, act, 1, last && obs_seq ? (T*)obs_seq + s * obs_row : nullptr,
                            last && reward_seq ? (T*)reward_seq + s * E : nullptr,
-                           last && done_seq ? done_seq + s * E : nullptr, mask, stats, ignore_done);
+                           last && done_seq ? done_seq + s * E : nullptr, mask,
+                           stats ? (last ? 1 : 2) : 0, ignore_done);   // 2: see substep_stats
       if (rc != FS_OK) return rc;
     }
   }

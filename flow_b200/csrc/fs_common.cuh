@@ -60,6 +60,15 @@ __device__ __forceinline__ double* stat_stripe(double* stats) {
   return stats + (w & (FS_STAT_STRIPES - 1)) * 8;
 }
 
+// StepArgs.accumulate_stats == 2: an INTERMEDIATE simulation sub-step of an Env.step
+// (EnvParams.sims_per_step > 1). The reference computes the reward and counts the Env.step once,
+// after the last sub-step or after the one that collided (flow/envs/base.py:325-410): speeds,
+// vehicle-steps and crashes are kept, the reward is not summed and the env-step is counted only
+// where the env collided in this sub-step (vals: reward, v, v^2, vehicle-steps, env-steps, crashes).
+__device__ __forceinline__ void substep_stats(int mode, double* vals) {
+  if (mode == 2) { vals[0] = 0.0; vals[4] = vals[5]; }
+}
+
 template <typename T> struct Num;
 template <> struct Num<float> {
   static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }

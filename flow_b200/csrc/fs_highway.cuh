@@ -488,7 +488,8 @@ highway_kernel(const __grid_constant__ Cfg<T> cfg, const HwBufs<T> B, const Step
     B.crash[e] = crash ? 1 : 0;
     B.reward[e] = reward;
     if (A.accumulate_stats) {
-      const double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
+      double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
+      substep_stats(A.accumulate_stats, vals);
       for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&stat_stripe(B.stats)[q], vals[q]);
     }
   }

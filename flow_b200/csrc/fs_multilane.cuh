@@ -629,7 +629,8 @@ ring_ml_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MlBuf
     }
     if (lane_id == 0) {
       const double adv = (double)(tc - tc0);
-      const double vals[6] = {st_rew, st_v, st_v2, adv * V, adv, st_cr};
+      double vals[6] = {st_rew, st_v, st_v2, adv * V, adv, st_cr};
+      substep_stats(A.accumulate_stats, vals);
       for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&stat_stripe(B.stats)[q], vals[q]);
     }
   }

@@ -426,6 +426,7 @@ ring1_kernel(const __grid_constant__ Cfg<T> cfg, const RingBufs<T> B, const Step
   }
   if (A.accumulate_stats) {
     double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
+    substep_stats(A.accumulate_stats, vals);
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       double s = vals[q];

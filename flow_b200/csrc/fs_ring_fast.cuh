@@ -521,6 +521,7 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
     // stats[]: sum reward, sum v, sum v^2, vehicle-steps, env-steps, crashes
     double vals[6] = {(double)st_rew, (double)st_v, (double)st_v2, (double)(st_adv * n_mine),
                       is_writer ? (double)st_adv : 0.0, (double)st_cr};
+    substep_stats(A.accumulate_stats, vals);
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       double s = vals[q];

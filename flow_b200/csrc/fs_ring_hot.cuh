@@ -383,6 +383,7 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
     double vals[6] = {(st_on && is_rl) ? (double)st_rew : 0.0, st_on ? (double)st_v : 0.0,
                       st_on ? (double)st_v2 : 0.0, (double)(adv * n_mine),
                       is_rl ? (double)adv : 0.0, (st_on && is_rl) ? (double)st_cr : 0.0};
+    substep_stats(A.accumulate_stats, vals);
     double* sp = stat_stripe(B.stats);
 #pragma unroll
     for (int q = 0; q < 6; ++q) {

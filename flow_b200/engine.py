@@ -126,11 +126,9 @@ class Engine:
         if rc != 0:
             raise FlowStepError(rc, self.lib.fs_last_error(None).decode())
         self.h = h
-        if use_torch_stream:
-            import torch
-            with torch.cuda.device(device):
-                s = torch.cuda.current_stream().cuda_stream
-            self._check(self.lib.fs_set_stream(self.h, C.c_void_p(s)))
+        self._use_torch_stream = use_torch_stream
+        self._stream = None
+        self._bind_stream()
         arr = (_lib.FsVType * len(types))(*types)
         tov = np.ascontiguousarray(type_of_vehicle, dtype=np.uint8)
         self._check(self.lib.fs_set_types(self.h, arr, len(types), tov.ctypes.data))
@@ -180,12 +178,49 @@ class Engine:
             self.veh_type = T(av.veh_type, (E, V), 'u8')
         self._fs_step = self.lib.fs_step
 
+    def _bind_stream(self):
+        """Run on torch's CURRENT stream of the engine's device: re-read on every call, the
+        engine is re-bound (fs_set_stream waits for the old stream) when the caller moved to
+        another one, e.g. inside `with torch.cuda.stream(s)`."""
+        if not self._use_torch_stream:
+            return
+        import torch
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        if s != self._stream:
+            self._check(self.lib.fs_set_stream(self.h, C.c_void_p(s)))
+            self._stream = s
+
+    def _dev_ptr(self, t, name, numel=None, dtype=None):
+        """data_ptr of a tensor that must live on this engine's GPU (None passes through)."""
+        if t is None:
+            return None
+        if not t.is_cuda or t.device.index != self.device:
+            raise ValueError('%s must be a tensor on cuda:%d, got %s' % (name, self.device, t.device))
+        if not t.is_contiguous():
+            raise ValueError('%s must be contiguous' % name)
+        if dtype is not None and t.dtype != dtype:
+            raise ValueError('%s must have dtype %s, got %s' % (name, dtype, t.dtype))
+        if numel is not None and t.numel() != numel:
+            raise ValueError('%s must have %d elements, got %d' % (name, numel, t.numel()))
+        return t.data_ptr()
+
     def _check(self, rc):
         if rc != 0:
             raise FlowStepError(rc, self.lib.fs_last_error(self.h).decode())
 
+    _VIEWS = ('pos', 'vel', 'lane', 'active', 'headway', 'accel', 'leader', 'follower', 'length',
+              'obs', 'reward', 'done', 'crash', 'time_counter', 'counters', 'agent_obs',
+              'agent_reward', 'agent_id', 'veh_id', 'veh_type')
+
     def close(self):
+        """Free the engine. The tensors it handed out alias memory the library owns: the
+        attributes are dropped here so that nothing of this object can reach freed memory;
+        tensors a caller kept elsewhere (e.g. the return value of reset()) dangle after close."""
         if getattr(self, 'h', None):
+            for name in self._VIEWS:
+                if hasattr(self, name):
+                    setattr(self, name, None)
+            self._staging = None
             self.lib.fs_destroy(self.h)
             self.h = None
 
@@ -197,6 +232,7 @@ class Engine:
 
     # -- reset / step -------------------------------------------------------
     def reset(self, mask=None, lengths=None):
+        self._bind_stream()
         m = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
         ln = None if lengths is None else np.ascontiguousarray(lengths, dtype=np.float64)
         self._check(self.lib.fs_reset(self.h, None if m is None else m.ctypes.data,
@@ -207,19 +243,26 @@ class Engine:
         """k fused steps with DEVICE tensors (any DLPack producer).
         actions: [k, act_dim, E] (or [act_dim, E] / [E] when k == 1)."""
         import torch
+        self._bind_stream()
+        want = torch.float64 if self.dtype == 'f64' else torch.float32
         a_ptr = None
         if actions is not None:
             if not isinstance(actions, torch.Tensor):
                 actions = torch.from_dlpack(actions)
-            want = torch.float64 if self.dtype == 'f64' else torch.float32
+            if not actions.is_cuda or actions.device.index != self.device:
+                raise ValueError('actions must be on cuda:%d (host arrays: step_host), got %s'
+                                 % (self.device, actions.device))
             if actions.dtype != want or not actions.is_contiguous():
-                actions = actions.to(want).contiguous()
+                actions = actions.to(want).contiguous()     # on the current stream, like the launch
             if actions.numel() != k * self.act_dim * self.n_envs:
                 raise ValueError('actions must have k*act_dim*n_envs = %d elements, got %d'
                                  % (k * self.act_dim * self.n_envs, actions.numel()))
             a_ptr = actions.data_ptr()
-        p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
-        self._check(self.lib.fs_step(self.h, a_ptr, k, p(obs_seq), p(reward_seq), p(done_seq)))
+        E = self.n_envs
+        po = self._dev_ptr(obs_seq, 'obs_seq', k * E * self.obs_dim, want)
+        pr = self._dev_ptr(reward_seq, 'reward_seq', k * E, want)
+        pd = self._dev_ptr(done_seq, 'done_seq', k * E, torch.uint8)
+        self._check(self.lib.fs_step(self.h, a_ptr, k, po, pr, pd))
         return self.obs, self.reward, self.done
 
     def step_ptr(self, actions_ptr, k, obs_ptr=0, reward_ptr=0, done_ptr=0):

@@ -364,7 +364,10 @@ void* fs_dlpack_wrap(void* dev_ptr, int device, int type_code, int bits, int ndi
                      const int64_t* shape, const int64_t* strides);
 
 /* Overwrite state from host arrays (T [V][E], any may be NULL), then refresh
- * leader/headway exactly as k.update does. lane: u8 [V][E]. */
+ * leader/headway exactly as k.update does. lane: u8 [V][E]. Only positions, speeds, lanes and
+ * lengths are replaced: done / crash flags, time counters, the sort_vehicles keys and the
+ * controller state of PISaturation / LAC vehicles keep their values (call fs_reset first for a
+ * clean episode). */
 int fs_set_state(fs_engine* e, const void* pos, const void* vel,
                  const uint8_t* lane, const double* lengths);
 

@@ -133,8 +133,11 @@ def get_accel(k, i, vt, st, dt, speed_limit):
         v0, acc, b, b_l, s0, tau = p[:6]
         v_l = _speed(k, lead)
         v_acc = v + (2.5 * acc * tau * (1 - (v / v0)) * math.sqrt(0.025 + (v / v0)))
-        v_safe = (tau * b) + math.sqrt(((tau ** 2) * (b ** 2)) - (
-            b * ((2 * (h - s0)) - (tau * v) - ((v_l ** 2) / b_l))))
+        inner = ((tau ** 2) * (b ** 2)) - (b * ((2 * (h - s0)) - (tau * v) - ((v_l ** 2) / b_l)))
+        # the reference takes np.sqrt: a negative argument gives NaN (a RuntimeWarning, no
+        # exception), and Python's min() then never selects it because every comparison with
+        # NaN is false and v_acc comes first
+        v_safe = (tau * b) + (math.sqrt(inner) if inner >= 0 else float('nan'))
         v_next = min(v_acc, v_safe, v0)
         return (v_next - v) / dt
     if c in (FOLLOWER_STOPPER, NONLOCAL_FOLLOWER_STOPPER):

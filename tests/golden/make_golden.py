@@ -267,6 +267,10 @@ ZOO = [
     ('fs', FS, {'v_des': 5.0}, 'FOLLOWER_STOPPER', 'safe_velocity'),
     ('nlfs', NLFS, {}, 'NONLOCAL_FOLLOWER_STOPPER', 'safe_velocity'),
     ('pi', PI, {}, 'PI_SATURATION', None),
+    # Gipps with a SHORT reaction time and hard braking: the square root's argument goes negative
+    # on the bunched start (np.sqrt -> NaN, skipped by min) and positive later
+    ('gipps', GIPPS, {'tau': 0.5, 'b': -3.0, 'b_l': -3.5, 's0': 5, 'fail_safe': 'instantaneous'},
+     'GIPPS', 'instantaneous'),
 ]
 
 

@@ -163,3 +163,57 @@ def test_fp32_resync_per_step_and_aggregates():
     assert abs(m_e - m_o) <= 0.01 * abs(m_o)
     assert abs(amp_e - amp_o) <= 0.01 * max(abs(amp_o), 0.05)
     assert abs(r_e - r_o) <= 0.01 * abs(r_o)
+
+
+def test_sims_per_step_statistics_count_env_steps_not_sub_steps():
+    """with sims_per_step = 3 the rollout statistics follow Experiment.run's
+    bookkeeping - one reward and one env-step per Env.step (sub-steps still count their
+    vehicle-steps), also for the Env.step that ends in a collision on an early sub-step."""
+    import torch
+    g = [S.vt('IDM', 21, sim_min_gap=0.0), S.vt('RL', 1)]       # mode 0: the RL car can ram
+    E, K, SPS = 64, 40, 3
+    eng = S.make_engine(g, E, 'f64', env_kind=OS.ENV_WAVE_ATTENUATION_PO, length_lo=220.,
+                        length_hi=270., seed=3, sims_per_step=SPS, **dict(S.C2, warmup_steps=10))
+    eng.reset()
+    eng.stats(reset=True)
+    act = torch.full((K, 1, E), 1.0, device='cuda', dtype=torch.float64)    # full throttle
+    rew = torch.empty(K, E, device='cuda', dtype=torch.float64)
+    done = torch.empty(K, E, device='cuda', dtype=torch.uint8)
+    eng.step(act, k=K, reward_seq=rew, done_seq=done)
+    st = eng.stats()
+    d = done.cpu().numpy().astype(bool)
+    steps_alive = (~d).sum() + d.any(0).sum()       # Env.steps taken, the terminal one included
+    assert d.any(), 'the scenario is meant to collide'
+    assert st['env_steps'] == steps_alive
+    assert st['crashes'] == eng.crash.sum().item() > 0
+    assert abs(st['sum_reward'] - rew.sum().item()) <= 1e-9 * max(1.0, abs(rew.sum().item()))
+    tc = eng.time_counter.cpu().numpy() - SPS * 10          # simulation sub-steps since the reset
+    assert st['vehicle_steps'] == 22.0 * tc.sum()
+
+
+def test_engine_follows_the_callers_stream_and_rejects_host_tensors():
+    """Engine.step runs on torch's CURRENT stream (re-read per call) and refuses
+    tensors that do not live on its GPU or have the wrong size / dtype."""
+    import torch
+    g = S.c2_groups()
+    kw = dict(env_kind=OS.ENV_WAVE_ATTENUATION_PO, length_lo=220., length_hi=270., seed=3, **S.C2)
+    a, b = S.make_engine(g, 128, 'f32', **kw), S.make_engine(g, 128, 'f32', **kw)
+    a.reset(); b.reset()
+    act = torch.rand(30, 1, 128, device='cuda') * 2 - 1
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        scaled = act * 1.0                      # produced on the side stream ...
+        a.step(scaled, k=30)                    # ... consumed there too, no race
+        pa = a.pos.clone()
+    side.synchronize()
+    b.step(act, k=30)
+    assert torch.equal(pa, b.pos)
+    with pytest.raises(ValueError):
+        a.step(act.cpu(), k=30)
+    with pytest.raises(ValueError):
+        a.step(act, k=30, obs_seq=torch.empty(30, 128, 2, device='cuda'))
+    with pytest.raises(ValueError):
+        a.step(act, k=30, reward_seq=torch.empty(30, 128, device='cuda', dtype=torch.float64))
+    a.close()
+    assert a.pos is None and a.obs is None

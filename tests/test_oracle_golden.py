@@ -133,11 +133,13 @@ ZOO = [('ovm', 'OVM', None), ('ovm_inst', 'OVM', 'instantaneous'),
        ('bcm', 'BCM', None), ('cfm_safe', 'CFM', 'safe_velocity'), ('lac', 'LAC', None),
        ('idm_inst', 'IDM', 'instantaneous'), ('idm_safe', 'IDM', 'safe_velocity'),
        ('fs', 'FOLLOWER_STOPPER', None), ('nlfs', 'NONLOCAL_FOLLOWER_STOPPER', None),
-       ('pi', 'PI_SATURATION', None)]
+       ('pi', 'PI_SATURATION', None), ('gipps', 'GIPPS', 'instantaneous')]
 
 
 def zoo_groups(ctrl, fail_safe):
     p = [5.0] if ctrl == 'FOLLOWER_STOPPER' else None
+    if ctrl == 'GIPPS':     # v0, acc, b, b_l, s0, tau (make_golden.ZOO 'gipps')
+        p = [30, 1.5, -3.0, -3.5, 5, 0.5]
     x = S.vt(ctrl, 1, p=p, fail_safe=fail_safe)
     return [S.vt('IDM', 10), x, S.vt('IDM', 10), dict(x)]
 
