@@ -104,6 +104,7 @@ SYMBOLS = [
     ('fs_last_error', C.c_char_p, [C.c_void_p]),
     ('fs_set_types', C.c_int, [C.c_void_p, C.POINTER(FsVType), C.c_int, C.c_void_p]),
     ('fs_reset', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    ('fs_reset_stage', C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     ('fs_step', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_unfused', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     ('fs_step_host', C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -823,7 +823,7 @@ extern "C" int fs_step_unfused(fs_engine* e, const void* actions, int k, void* o
 }
 
 template <typename T>
-static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths_dev) {
+static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths_dev, int stages) {
   fs::ResetBufs<T> b;
   b.pos = (T*)e->pos; b.vel = (T*)e->vel; b.circ = (T*)e->circ; b.st0 = (T*)e->st0;
   b.hist_sum = e->hist_sum; b.hist_cnt = e->hist_cnt; b.n_pi = e->n_pi;
@@ -833,13 +833,16 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
   b.last_lc = e->last_lc;
   b.vs = e->env_major ? 1 : e->cfg.n_envs; b.es = e->env_major ? e->cfg.n_veh : 1;
   const int E = e->cfg.n_envs, block = 128;
-  if (e->cfg.topology == FS_TOPO_HIGHWAY)
-    fs::highway_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(
-        cfg_of<T>(e), hw_bufs<T>(e), mask_dev, e->cfg.n_initial);
-  else
-    fs::ring_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(cfg_of<T>(e), b);
-  e->launches++;
-  FS_CUDA(e, cudaGetLastError());
+  if (stages & FS_RESET_PLACE) {
+    if (e->cfg.topology == FS_TOPO_HIGHWAY)
+      fs::highway_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(
+          cfg_of<T>(e), hw_bufs<T>(e), mask_dev, e->cfg.n_initial);
+    else
+      fs::ring_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(cfg_of<T>(e), b);
+    e->launches++;
+    FS_CUDA(e, cudaGetLastError());
+  }
+  if (!(stages & FS_RESET_WARMUP)) return FS_OK;
   // warm-up: Env.reset steps with rl_actions=None (flow/envs/base.py:554-555)
   int rc = do_step<T>(e, nullptr, e->cfg.warmup_steps, nullptr, nullptr, nullptr, mask_dev, 0, 1);
   if (rc == FS_OK && e->sort_on()) {  // AccelEnv.reset tail (accel.py:178-181), after the observation
@@ -904,8 +907,15 @@ extern "C" int fs_agents(fs_engine* e, fs_agent_views* out) {
 }
 
 extern "C" int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* lengths) {
+  return fs_reset_stage(e, env_mask, lengths, FS_RESET_PLACE | FS_RESET_WARMUP);
+}
+
+extern "C" int fs_reset_stage(fs_engine* e, const uint8_t* env_mask, const double* lengths,
+                              int stages) {
   if (!e) return FS_EINVAL;
   if (!e->types_set) return fail(e, FS_ESTATE, "fs_reset: call fs_set_types first");
+  if (stages < 1 || stages > (FS_RESET_PLACE | FS_RESET_WARMUP))
+    return fail(e, FS_EINVAL, "fs_reset_stage: stages must be FS_RESET_PLACE, FS_RESET_WARMUP or both");
   cudaSetDevice(e->cfg.device);
   const size_t E = e->cfg.n_envs;
   int rc = check_room(e, e->cfg.length_lo);
@@ -924,7 +934,8 @@ extern "C" int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* len
                                cudaMemcpyHostToDevice, e->stream));
     len_dev = e->lengths_dev;
   }
-  rc = e->f64 ? do_reset<double>(e, mask_dev, len_dev) : do_reset<float>(e, mask_dev, len_dev);
+  rc = e->f64 ? do_reset<double>(e, mask_dev, len_dev, stages)
+              : do_reset<float>(e, mask_dev, len_dev, stages);
   if (rc != FS_OK) return rc;
   // host buffers may be reused by the caller right away
   if (env_mask || lengths) FS_CUDA(e, cudaStreamSynchronize(e->stream));

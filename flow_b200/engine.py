@@ -239,6 +239,19 @@ class Engine:
                                       None if ln is None else ln.ctypes.data))
         return self.obs
 
+    RESET_PLACE, RESET_WARMUP = 1, 2
+
+    def reset_stage(self, stages, mask=None, lengths=None):
+        """fs_reset_stage: RESET_PLACE (ring length, even placement, counters) and / or
+        RESET_WARMUP (the warm-up steps on the current state); between the two the caller may
+        replace positions / lanes with set_state (host-drawn placements, flow_api)."""
+        self._bind_stream()
+        m = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+        ln = None if lengths is None else np.ascontiguousarray(lengths, dtype=np.float64)
+        self._check(self.lib.fs_reset_stage(self.h, None if m is None else m.ctypes.data,
+                                            None if ln is None else ln.ctypes.data, int(stages)))
+        return self.obs
+
     def step(self, actions=None, k=1, obs_seq=None, reward_seq=None, done_seq=None):
         """k fused steps with DEVICE tensors (any DLPack producer).
         actions: [k, act_dim, E] (or [act_dim, E] / [E] when k == 1)."""

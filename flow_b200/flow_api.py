@@ -554,9 +554,15 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         if p not in ap:
             raise KeyError('Environment parameter "{}" not supplied'.format(p))
     veh, net, ini = network.vehicles, network.net_params.additional_params, network.initial_config
-    if ini.spacing != 'uniform' or ini.shuffle or ini.perturbation:
-        raise NotImplementedError('only InitialConfig(spacing="uniform", shuffle=False, '
-                                  'perturbation=0) placements are compiled')
+    if ini.spacing not in ('uniform', 'random'):
+        raise NotImplementedError('InitialConfig(spacing=%r): only "uniform" and "random" placements '
+                                  'exist here ("custom" belongs to networks that are not built)'
+                                  % (ini.spacing,))
+    if ini.shuffle and len([r for r in veh.initial if r['num_vehicles'] > 0]) > 1:
+        # random.shuffle(initial_ids) moves every vehicle TYPE to another start position in every
+        # env; the engine's type table is per vehicle index, shared by the batch. With one type
+        # (what the reference's own shuffle test and non_rl/highway.py use) only the names move.
+        raise NotImplementedError('InitialConfig(shuffle=True) with several vehicle types')
     if ini.edges_distribution != 'all':
         raise NotImplementedError('edges_distribution other than "all"')
     sort_on = bool(ap.get('sort_vehicles')) and env_cls.KIND in (
@@ -913,6 +919,25 @@ class Env:
         self.step_counter = 0
         self.state = None
         self.obs_var_labels = []
+        # placements the reference draws from host random streams (flow_b200/placement.py)
+        ic = self.initial_config
+        self._host_placement = ic.spacing == 'random' or ic.perturbation > 0 or bool(ic.shuffle)
+        self._placed = None
+        if self._host_placement and self.spec.kw.get('length_lo') != self.spec.kw.get('length_hi'):
+            # WaveAttenuationEnv.reset builds a NEW InitialConfig(bunching=50, min_gap=0) for every
+            # ring length it draws (wave_attenuation.py:171-174): the options never take effect
+            import warnings
+            warnings.warn('InitialConfig(perturbation / spacing="random" / shuffle) has no effect on '
+                          'an env that redraws its ring length at reset, as in the reference')
+            self._host_placement = False
+        if self._host_placement:
+            if self.spec.capacity is not None and (ic.spacing == 'random' or ic.perturbation > 0) \
+                    and len(set(self.spec.type_of[:len(self._initial_ids)])) > 1:
+                raise NotImplementedError('perturbed / random start positions on the highway with '
+                                          'several vehicle types (slots are kept head first)')
+            # Env.__init__ -> setup_initial_state (base.py:183-199): one shuffle + one draw here,
+            # so that the host streams stand where the reference's stand after construction
+            self._draw_host_placement()
 
     # spaces -----------------------------------------------------------------
     @property
@@ -933,6 +958,60 @@ class Env:
         if self.engine.headway is None:
             raise RuntimeError('get_headway / get_leader / get_follower need '
                                'record_views=True on a batched env')
+
+    def _draw_host_placement(self):
+        """setup_initial_state (flow/envs/base.py:268-292): shuffle the ids, then generate the
+        start positions - with the reference's own host streams (placement.py). Leaves the
+        engine placed (stage FS_RESET_PLACE done) and the drawn state in self._placed."""
+        from . import placement as PL
+        ic, eng, ring = self.initial_config, self.engine, self.network.TOPOLOGY == EN.TOPO_RING
+        if ic.shuffle:
+            if self.spec.capacity is not None:
+                self._initial_ids = PL.shuffled(self._initial_ids)
+            else:
+                self.spec.veh_ids = PL.shuffled(self.spec.veh_ids)
+                self._index = {v: i for i, v in enumerate(self.spec.veh_ids)}
+                self.rl_ids = [v for i, v in enumerate(self.spec.veh_ids) if self._is_rl[i]]
+        eng.reset_stage(eng.RESET_PLACE)
+        self._placed = None
+        if ic.spacing != 'random' and not ic.perturbation > 0:
+            return                                    # shuffle only: the even placement stands
+        pos = eng.pos.double().cpu().numpy().copy()   # [V or slots, E]
+        lane = eng.lane.cpu().numpy().copy()
+        circ = eng.length.double().cpu().numpy()
+        lanes = int(self.net_params.additional_params['lanes'])
+        n = len(self._initial_ids) if self.spec.capacity is not None else eng.n_veh
+        for e in range(self.n_envs):
+            edges = PL.ring_edges(circ[e] - 4 * RING_JUNCTION_LENGTH) if ring else \
+                PL.highway_edges(circ[e])
+            if ic.spacing == 'random':
+                try:
+                    xs, ls = PL.random_positions(edges, lanes, ic.lanes_distribution, ic.min_gap,
+                                                 ic.bunching, n)
+                except ValueError as exc:
+                    raise FatalFlowError(str(exc))
+            else:
+                order = list(range(n)) if ring else sorted(range(n), key=lambda i: pos[i, e])
+                xs = PL.perturb([pos[i, e] for i in order], edges, ic.perturbation)
+                ls = [int(lane[i, e]) for i in order]
+            if not ring:      # highway slots are kept head first (largest x in slot 0)
+                by_x = sorted(range(n), key=lambda i: -xs[i])
+                xs, ls = [xs[i] for i in by_x], [ls[i] for i in by_x]
+            pos[:n, e], lane[:n, e] = xs, ls
+        self._placed = (pos, lane)
+
+    def _reset_host_placed(self):
+        """Env.reset with host-drawn placements: with shuffle the reference redraws everything at
+        every reset (base.py:466-467), otherwise it re-adds the vehicles at the positions drawn
+        once at construction (base.py:497-530)."""
+        eng = self.engine
+        if self.initial_config.shuffle:
+            self._draw_host_placement()
+        else:
+            eng.reset_stage(eng.RESET_PLACE)
+        if self._placed is not None:
+            eng.set_state(pos=self._placed[0], lane=self._placed[1])
+        return eng.reset_stage(eng.RESET_WARMUP)
 
     def _edge_of(self, x):
         """(edge name, edge start) of loop coordinate x."""
@@ -980,7 +1059,7 @@ class Env:
         """flow/envs/base.py:414-560: new episode (ring length draw, even
         placement, warm-up steps with rl_actions=None) for every env."""
         self.time_counter = 0
-        obs = self.engine.reset()
+        obs = self._reset_host_placed() if self._host_placement else self.engine.reset()
         self._count_hist = []
         self._log_counts()
         self.k.vehicle._invalidate()

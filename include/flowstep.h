@@ -273,6 +273,18 @@ int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
  * RL action. Observation of the reset envs is left in views.obs. */
 int fs_reset(fs_engine* e, const uint8_t* env_mask, const double* lengths);
 
+/* The two halves of fs_reset, for placements the engine does not generate itself
+ * (InitialConfig(perturbation > 0 / spacing = 'random' / shuffle = True),
+ * flow/core/kernel/network/base.py:384-389, 393-487, flow/envs/base.py:275-277: the reference
+ * draws them from Python's `random` and numpy's global generator ON THE HOST, and so does the
+ * host side here, with the same streams): FS_RESET_PLACE = everything fs_reset does before the
+ * warm-up (ring length, even placement, counters, flags, episode + 1); the caller then replaces
+ * positions / lanes with fs_set_state; FS_RESET_WARMUP = the warm-up steps (and the
+ * sort_vehicles key snapshot) on the state as it is now. Both bits = fs_reset. */
+#define FS_RESET_PLACE  1
+#define FS_RESET_WARMUP 2
+int fs_reset_stage(fs_engine* e, const uint8_t* env_mask, const double* lengths, int stages);
+
 /* k fused steps. actions: DEVICE pointer, T [k][act_dim][E], or NULL (no RL
  * action: RL vehicles are driven by the simulator model). If obs_seq /
  * reward_seq / done_seq are non-NULL (device, T [k][E][obs_dim], T [k][E],

@@ -481,6 +481,31 @@ def start_pos():
     json.dump(out, open(os.path.join(HERE, 'start_pos.json'), 'w'), indent=1)
 
 
+def start_pos_stochastic():
+    """InitialConfig(perturbation / spacing='random' / shuffle): the reference's generators read
+    Python's `random` and numpy's global stream; seeded here, so the host restatement
+    (flow_b200/placement.py) can be checked number for number."""
+    import random
+    cases = [dict(length=230, n=22, lanes=1, seed=7, kw=dict(bunching=20, perturbation=1.0)),
+             dict(length=260, n=22, lanes=1, seed=8, kw=dict(perturbation=4.0)),      # clips at edge ends
+             dict(length=230, n=21, lanes=3, seed=9, kw=dict(lanes_distribution=float('inf'),
+                                                             perturbation=2.0)),
+             dict(length=230, n=22, lanes=1, seed=10, kw=dict(spacing='random')),
+             dict(length=300, n=10, lanes=1, seed=11, kw=dict(spacing='random', min_gap=1.5)),
+             dict(length=230, n=5, lanes=4, seed=12, kw=dict(spacing='random', lanes_distribution=2)),
+             dict(length=230, n=40, lanes=3, seed=13, kw=dict(spacing='random', bunching=10))]
+    out = []
+    for c in cases:
+        random.seed(c['seed']); np.random.seed(c['seed'])
+        x, lane = ref_start_positions(c['length'], c['n'], c['lanes'], **c['kw'])
+        ids = ['test_%d' % i for i in range(c['n'])]
+        random.shuffle(ids)                 # flow/envs/base.py:275-277, same stream, drawn after
+        kw = {k: (v if v != float('inf') else 'inf') for k, v in c['kw'].items()}
+        out.append(dict(length=c['length'], n=c['n'], lanes=c['lanes'], seed=c['seed'], kw=kw,
+                        x=[float(v) for v in x], lane=[int(v) for v in lane], shuffled_ids=ids))
+    json.dump(out, open(os.path.join(HERE, 'start_pos_stochastic.json'), 'w'), indent=1)
+
+
 def sumo_fixture():
     src = os.path.join(ref_shim.REF, 'tests/fast_tests/test_files/ring_230_emission.csv')
     rows = list(csv.DictReader(open(src)))
@@ -493,7 +518,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos()
+    ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos(); start_pos_stochastic()
     highway_ma()
     sumo_fixture()
     print('golden vectors written to', HERE)

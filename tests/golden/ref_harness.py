@@ -87,14 +87,20 @@ class _Net:
         return [(self._ORDER[(self._ORDER.index(edge) - 1) % 8], lane)]
 
     gen_even_start_pos = BaseKernelNetwork.gen_even_start_pos
+    gen_random_start_pos = BaseKernelNetwork.gen_random_start_pos
     _get_start_pos_util = BaseKernelNetwork._get_start_pos_util
 
 
 def ref_start_positions(length, num_vehicles, lanes=1, **init_kw):
-    """Loop coordinates + lanes from the reference's own gen_even_start_pos."""
+    """Loop coordinates + lanes from the reference's own gen_even_start_pos (or
+    gen_random_start_pos for spacing='random'); these read the host RNG streams
+    (`random`, `np.random`) the caller has seeded."""
     net = _Net(length, lanes, 30)
     ic = InitialConfig(**init_kw)
-    pos, lane = net.gen_even_start_pos(ic, num_vehicles)
+    if ic.spacing == 'random':
+        pos, lane = net.gen_random_start_pos(ic, num_vehicles)
+    else:
+        pos, lane = net.gen_even_start_pos(ic, num_vehicles)
     return [net.get_x(e, p) for e, p in pos], list(lane)
 
 
