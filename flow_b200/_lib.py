@@ -13,7 +13,7 @@ ROOT = os.path.dirname(_HERE)
 SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
 SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu', 'fs_ring_f32.cu', 'fs_ring_f64.cu',
-           'fs_ml_f32.cu', 'fs_ml_f64.cu', 'fs_hw_f32.cu', 'fs_hw_f64.cu']
+           'fs_ml_f32.cu', 'fs_ml_f64.cu', 'fs_hw_f32.cu', 'fs_hw_f64.cu', 'fs_mg_f32.cu', 'fs_mg_f64.cu']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -54,16 +54,18 @@ class FsConfig(C.Structure):
                 ('record_views', C.c_int32), ('lc_corrected', C.c_int32),
                 ('n_initial', C.c_int32), ('env_flags', C.c_int32),
                 ('inflow_begin', C.c_double),
-                ('max_agents', C.c_int32), ('reserved0', C.c_int32)]
+                ('max_agents', C.c_int32), ('reserved0', C.c_int32),
+                ('merge_pre', C.c_double), ('merge_ramp', C.c_double),
+                ('merge_post', C.c_double), ('merge_zone', C.c_double)]
 
 
-FS_ABI_VERSION = 3
+FS_ABI_VERSION = 4
 FS_MAX_INFLOWS = 4
 FS_NOALLOC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 
 class FsInflow(C.Structure):
-    _fields_ = [('vtype', C.c_int32), ('reserved', C.c_int32),
+    _fields_ = [('vtype', C.c_int32), ('arm', C.c_int32),
                 ('vehs_per_hour', C.c_double), ('depart_speed', C.c_double),
                 ('begin', C.c_double), ('end', C.c_double), ('probability', C.c_double)]
 

@@ -57,6 +57,8 @@ struct fs_engine {
   int* agent_id = nullptr;     // [E][A]
   void* agent_reward = nullptr;  // T [E][A]
   bool ma_highway() const { return cfg.env_kind == FS_ENV_MA_HIGHWAY_PO; }
+  bool merge() const { return cfg.topology == FS_TOPO_MERGE; }
+  int* seq = nullptr;          // merge: [E][CAP] departure order of the vehicle in each slot
   // fs_step_unfused: the k single-step launches of the last call, kept as an instantiated graph
   cudaGraphExec_t uf_exec = nullptr;
   const void* uf_key[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -168,6 +170,9 @@ static int obs_dim_for(const fs_config& c) {
     case FS_ENV_MA_HIGHWAY_PO:
       return c.topology == FS_TOPO_HIGHWAY && c.max_agents >= 1 && c.max_agents <= c.n_veh
                  ? 5 * c.max_agents : -1;
+    case FS_ENV_MERGE_PO:
+      return c.topology == FS_TOPO_MERGE && c.max_agents >= 1 && c.max_agents <= 32 &&
+                     c.max_agents <= c.n_veh ? 5 * c.max_agents : -1;
     case FS_ENV_MA_WAVE_ATTENUATION_PO: return 3 * c.n_veh;  // capacity; 3 * n_rl after fs_set_types
     case FS_ENV_MA_ACCEL_PO:                                  // capacity; 6 * n_rl after fs_set_types
       return c.topology == FS_TOPO_RING && c.n_lanes == 1 ? 6 * c.n_veh : -1;
@@ -188,6 +193,13 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
     return fail(nullptr, FS_EINVAL, "fs_create: n_lanes must be in 1..8");
   if (obs_dim_for(*cfg) < 0)
     return fail(nullptr, FS_EINVAL, "fs_create: unsupported env_kind");
+  if ((cfg->topology == FS_TOPO_MERGE) != (cfg->env_kind == FS_ENV_MERGE_PO))
+    return fail(nullptr, FS_EINVAL, "fs_create: FS_TOPO_MERGE goes with FS_ENV_MERGE_PO and vice versa");
+  if (cfg->topology == FS_TOPO_MERGE &&
+      (!(cfg->merge_pre > 0) || !(cfg->merge_ramp > 0) || !(cfg->merge_post > 0) || cfg->n_lanes != 1 ||
+       cfg->merge_zone < 0 || (cfg->env_flags & ~FS_ENVF_EVALUATE)))
+    return fail(nullptr, FS_EINVAL, "fs_create: merge network needs merge_pre / merge_ramp / merge_post "
+                                    "> 0, one lane per road, merge_zone >= 0, no env flag but evaluate");
   if ((cfg->env_flags & FS_ENVF_SORT_VEHICLES) &&
       (cfg->topology != FS_TOPO_RING ||
        (cfg->env_kind != FS_ENV_ACCEL && cfg->env_kind != FS_ENV_LANE_CHANGE_ACCEL &&
@@ -230,9 +242,14 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->time_counter, E * 4); A(&e->episode, E * 4);
   A(&e->obs, E * e->obs_dim * ts); A(&e->reward, E * ts);
   A(&e->stats, FS_STAT_STRIPES * 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
-  e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY;
+  e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY || e->merge();
   if (e->env_major) A(&e->last_lc, V * E * 4);
   if (e->sort_on()) { A(&e->abs_pos, V * E * ts); A(&e->prev_pos, V * E * ts); A(&e->keys_valid, E); }
+  if (e->merge()) {
+    A(&e->counters, (3 + 2 * FS_MAX_INFLOWS) * E * 4); A(&e->vtype, V * E);
+    A(&e->veh_id, V * E * 4); A(&e->seq, V * E * 4);
+    A(&e->agent_id, E * (size_t)cfg->max_agents * 4);
+  }
   if (cfg->topology == FS_TOPO_HIGHWAY) {
     A(&e->counters, (3 + 2 * FS_MAX_INFLOWS) * E * 4); A(&e->vtype, V * E);
     if (cfg->inflow_vehs_per_hour > 0) {
@@ -297,6 +314,12 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
   c.obs_max_length = (T)g.obs_max_length;
   c.length_lo = (T)g.length_lo; c.length_hi = (T)g.length_hi;
   c.lanes_distribution = g.lanes_distribution;
+  {  // merge geometry, summed in the order oracle/merge.py MergeGeometry sums it
+    const double LH = ((100.0 + 0.1) + g.merge_pre) + 22.5, LM = ((100.0 + 0.1) + g.merge_ramp) + 22.5;
+    c.mg_LH = (T)LH; c.mg_LM = (T)LM; c.mg_post = (T)g.merge_post;
+    c.mg_zone = (T)(g.merge_zone > 0 ? g.merge_zone : g.merge_ramp + 22.5);
+    c.mg_pre = (T)g.merge_pre; c.mg_ramp = (T)g.merge_ramp;
+  }
   c.evaluate = (g.env_flags & FS_ENVF_EVALUATE) ? 1 : 0;
   c.ballistic = (g.env_flags & FS_ENVF_BALLISTIC) ? 1 : 0;
   for (int t = 0; t < n_types; ++t) {
@@ -348,7 +371,8 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
   if (g.env_kind == FS_ENV_LANE_CHANGE_ACCEL_PO) {
     e->obs_dim = 4 * n_rl * g.n_lanes + (g.lc_corrected ? n_rl : 1); c.obs_dim = e->obs_dim;
   }
-  if (g.env_kind == FS_ENV_MA_HIGHWAY_PO) c.act_dim = g.max_agents;  // one action row per agent row
+  if (g.env_kind == FS_ENV_MA_HIGHWAY_PO || g.env_kind == FS_ENV_MERGE_PO)
+    c.act_dim = g.max_agents;  // one action row per agent / controlled-vehicle row
   e->n_rl = n_rl;
   e->act_dim = c.act_dim;
 }
@@ -442,6 +466,16 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
     if (ok && ta >= 0 && tb >= 0 && e->cfg.collision_min_gap &&
         types[ta].sim_min_gap != types[tb].sim_min_gap) ok = false;
     e->ml_uniform = ok;
+  }
+  if (e->merge()) {
+    if (e->cfg.n_initial < 0 || e->cfg.n_initial > e->cfg.n_veh)
+      return fail(e, FS_EINVAL, "fs_set_types: n_initial must be within the slot capacity");
+    for (int t = 0; t < n_types; ++t) {
+      const int c = types[t].controller;
+      if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC || c == FS_CTRL_BCM)
+        return fail(e, FS_EINVAL, "fs_set_types: PISaturation / LAC / BCM vehicles are not supported on "
+                                  "the merge network (per-slot controller state / follower input)");
+    }
   }
   if (e->cfg.topology == FS_TOPO_HIGHWAY) {
     // inflow vehicles may be of a type no initial vehicle has: look at every type
@@ -567,6 +601,45 @@ static fs::HwBufs<T> hw_bufs(fs_engine* e) {
 }
 
 template <typename T>
+static fs::MgBufs<T> mg_bufs(fs_engine* e) {
+  fs::MgBufs<T> b;
+  const size_t E = e->cfg.n_envs;
+  b.pos = (T*)e->pos; b.vel = (T*)e->vel; b.arm = e->lane; b.vtype = e->vtype; b.active = e->active;
+  b.vid = e->veh_id; b.seq = e->seq;
+  b.n_active = e->counters; b.departed = e->counters + E; b.arrived = e->counters + 2 * E;
+  b.spawned = e->counters + 3 * E;
+  int* extra = e->counters + (3 + FS_MAX_INFLOWS) * E;     // the highway's `pending` rows
+  b.n_ctrl = extra; b.hi_seq = extra + E; b.next_seq = extra + 2 * E;
+  b.ctrl_id = e->agent_id;
+  b.time_counter = e->time_counter; b.episode = e->episode; b.done = e->done; b.crash = e->crash;
+  b.obs = (T*)e->obs; b.reward = (T*)e->reward;
+  b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
+  b.v_leader = e->leader; b.v_follower = e->follower; b.stats = e->stats;
+  b.n_flows = e->n_flows; b.max_agents = e->cfg.max_agents;
+  for (int f = 0; f < FS_MAX_INFLOWS; ++f) {
+    const fs_inflow& q = e->flows[f];
+    const bool on = f < e->n_flows && q.vehs_per_hour > 0;
+    b.period[f] = on ? 3600.0 / q.vehs_per_hour : 0.0;
+    b.begin[f] = on ? q.begin : 0.0;
+    b.depart_speed[f] = on ? (T)q.depart_speed : T(0);
+    b.inflow_type[f] = on ? q.vtype : 0;
+    b.inflow_arm[f] = on ? q.arm : 0;
+  }
+  return b;
+}
+
+template <typename T>
+static int launch_mg(fs_engine* e, const fs::StepArgs<T>& a) {
+  const int E = e->cfg.n_envs, CAP = e->cfg.n_veh;
+  const int wpb = E <= 148 * 8 ? 1 : 4;
+  const int grid = (E + wpb - 1) / wpb;
+  const size_t smem = (size_t)wpb * fs::mg_smem_per_warp<T>(CAP);
+  FS_CUDA(e, fs_launch_mg<T>(CAP, grid, wpb * 32, smem, e->stream, cfg_of<T>(e), mg_bufs<T>(e), a));
+  e->launches++;
+  return FS_OK;
+}
+
+template <typename T>
 static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
   const int E = e->cfg.n_envs, CAP = e->cfg.n_veh;
   const int wpb = E <= 148 * 8 ? 1 : 4;
@@ -607,6 +680,7 @@ static cudaError_t launch_hot(int shape, bool noise, int E, cudaStream_t st,
 template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->cfg.topology == FS_TOPO_HIGHWAY) return launch_hw<T>(e, a);
+  if (e->merge()) return launch_mg<T>(e, a);
   const int V = e->cfg.n_veh, E = e->cfg.n_envs;
   if (e->multilane()) return launch_ml<T>(e, a);
   if (e->fast_ok) {
@@ -709,7 +783,7 @@ template <typename T>
 static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
                    uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done) {
   const int S = e->cfg.sims_per_step;
-  if (S <= 1 || k == 0)
+  if (S <= 1 || k == 0 || e->merge())      // the merge kernel loops over the sub-steps itself
     return do_step1<T>(e, actions, k, obs_seq, reward_seq, done_seq, mask, stats, ignore_done);
   const size_t E = e->cfg.n_envs, act_row = (size_t)e->act_dim * E, obs_row = E * e->obs_dim;
   for (int s = 0; s < k; ++s) {
@@ -834,7 +908,10 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
   b.vs = e->env_major ? 1 : e->cfg.n_envs; b.es = e->env_major ? e->cfg.n_veh : 1;
   const int E = e->cfg.n_envs, block = 128;
   if (stages & FS_RESET_PLACE) {
-    if (e->cfg.topology == FS_TOPO_HIGHWAY)
+    if (e->merge())
+      FS_CUDA(e, fs_launch_mg_reset<T>(E, e->stream, cfg_of<T>(e), mg_bufs<T>(e), mask_dev,
+                                       e->cfg.n_initial, (T*)e->circ));
+    else if (e->cfg.topology == FS_TOPO_HIGHWAY)
       fs::highway_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(
           cfg_of<T>(e), hw_bufs<T>(e), mask_dev, e->cfg.n_initial);
     else
@@ -857,6 +934,7 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
 static int check_room(fs_engine* e, double L) {
   // _get_start_pos_util raises FatalFlowError when vehicles do not fit
   const fs_config& g = e->cfg;
+  if (g.topology == FS_TOPO_MERGE) return FS_OK;   // initial vehicles are placed by the caller
   const double min_gap = fmax(0.0, g.init_min_gap), bunching = fmax(0.0, g.bunching);
   int ld = g.lanes_distribution;
   if (ld > g.n_lanes) ld = g.n_lanes;
@@ -871,8 +949,8 @@ static int check_room(fs_engine* e, double L) {
 
 extern "C" int fs_set_inflows(fs_engine* e, const fs_inflow* flows, int n_flows) {
   if (!e) return FS_EINVAL;
-  if (e->cfg.topology != FS_TOPO_HIGHWAY)
-    return fail(e, FS_EINVAL, "fs_set_inflows: inflows exist on the highway topology only");
+  if (e->cfg.topology != FS_TOPO_HIGHWAY && !e->merge())
+    return fail(e, FS_EINVAL, "fs_set_inflows: inflows exist on the highway and merge topologies only");
   if (!e->types_set) return fail(e, FS_ESTATE, "fs_set_inflows: call fs_set_types first");
   if (n_flows < 0 || n_flows > FS_MAX_INFLOWS || (n_flows > 0 && !flows))
     return fail(e, FS_EINVAL, "fs_set_inflows: 0..4 flows");
@@ -888,8 +966,11 @@ extern "C" int fs_set_inflows(fs_engine* e, const fs_inflow* flows, int n_flows)
                                 "(0, 1]; depart_speed >= 0, begin >= 0");
     const fs::TypeP<double>* td = e->f64 ? &e->cd.types[flows[f].vtype] : nullptr;
     const int ctrl = td ? td->ctrl : e->cf.types[flows[f].vtype].ctrl;
-    if (ctrl == FS_CTRL_RL && !e->ma_highway())
-      return fail(e, FS_EINVAL, "fs_set_inflows: an RL inflow needs FS_ENV_MA_HIGHWAY_PO");
+    if (ctrl == FS_CTRL_RL && !e->ma_highway() && !e->merge())
+      return fail(e, FS_EINVAL, "fs_set_inflows: an RL inflow needs FS_ENV_MA_HIGHWAY_PO / FS_ENV_MERGE_PO");
+    if (e->merge() ? (flows[f].arm != 0 && flows[f].arm != 1 || !periodic) : flows[f].arm != 0)
+      return fail(e, FS_EINVAL, "fs_set_inflows: arm is 0 (1 = the ramp, merge network only); merge "
+                                "flows are periodic (vehs_per_hour)");
   }
   drop_graphs(e);
   e->n_flows = n_flows;
@@ -899,7 +980,8 @@ extern "C" int fs_set_inflows(fs_engine* e, const fs_inflow* flows, int n_flows)
 
 extern "C" int fs_agents(fs_engine* e, fs_agent_views* out) {
   if (!e || !out) return FS_EINVAL;
-  if (!e->ma_highway()) return fail(e, FS_EINVAL, "fs_agents: FS_ENV_MA_HIGHWAY_PO only");
+  if (!e->ma_highway() && !e->merge())
+    return fail(e, FS_EINVAL, "fs_agents: FS_ENV_MA_HIGHWAY_PO / FS_ENV_MERGE_PO only");
   out->agent_obs = e->obs; out->agent_reward = e->agent_reward; out->agent_id = e->agent_id;
   out->veh_id = e->veh_id; out->veh_type = e->vtype;
   out->max_agents = e->cfg.max_agents; out->obs_per_agent = 5;

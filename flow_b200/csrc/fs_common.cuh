@@ -46,6 +46,9 @@ struct Cfg {
   T target_velocity, act_lo, act_hi, obs_max_length;
   T length_lo, length_hi;
   int lanes_distribution;
+  // FS_TOPO_MERGE: arm lengths up to the merge point (highway / ramp), the common edge, the
+  // cross-arm look-ahead zone, the edge lengths they were built from (flowstep.cu fill_cfg)
+  T mg_LH, mg_LM, mg_post, mg_zone, mg_pre, mg_ramp;
   int16_t evaluate;   // EnvParams.evaluate (AccelEnv reward = mean speed)
   int16_t ballistic;  // SumoParams.use_ballistic: x += (v_old + v_new)/2 dt instead of v_new dt
   TypeP<T> types[FS_MAX_TYPES];
@@ -78,6 +81,7 @@ template <> struct Num<float> {
   static __device__ __forceinline__ float abs(float a) { return fabsf(a); }
   static __device__ __forceinline__ float max(float a, float b) { return fmaxf(a, b); }
   static __device__ __forceinline__ float min(float a, float b) { return fminf(a, b); }
+  static __device__ __forceinline__ float nan() { return __int_as_float(0x7fc00000); }
 };
 template <> struct Num<double> {
   static __device__ __forceinline__ double div(double a, double b) { return a / b; }
@@ -87,6 +91,7 @@ template <> struct Num<double> {
   static __device__ __forceinline__ double abs(double a) { return fabs(a); }
   static __device__ __forceinline__ double max(double a, double b) { return fmax(a, b); }
   static __device__ __forceinline__ double min(double a, double b) { return fmin(a, b); }
+  static __device__ __forceinline__ double nan() { return __longlong_as_double(0x7ff8000000000000LL); }
 };
 
 // No fused multiply-add in double: Python evaluates a*b+c with two roundings,

@@ -8,6 +8,7 @@
 #include "fs_ring_fast.cuh"
 #include "fs_multilane.cuh"
 #include "fs_highway.cuh"
+#include "fs_merge.cuh"
 
 cudaError_t fs_launch_fast22_f32(int shape, int variant, int n_envs, cudaStream_t st,
                                  const fs::FastP<float>& c, const fs::RingBufs<float>& b,
@@ -33,3 +34,10 @@ template <typename T>
 cudaError_t fs_launch_hw(int cap, bool multi_agent, bool single_periodic, bool generic, int grid,
                          int block, size_t smem, cudaStream_t st, const fs::Cfg<T>& c,
                          const fs::HwBufs<T>& b, const fs::StepArgs<T>& a);
+// merge network (fs_merge.cuh)
+template <typename T>
+cudaError_t fs_launch_mg(int cap, int grid, int block, size_t smem, cudaStream_t st,
+                         const fs::Cfg<T>& c, const fs::MgBufs<T>& b, const fs::StepArgs<T>& a);
+template <typename T>
+cudaError_t fs_launch_mg_reset(int E, cudaStream_t st, const fs::Cfg<T>& c, const fs::MgBufs<T>& b,
+                               const uint8_t* mask, int n_initial, T* length);

@@ -12,10 +12,10 @@ from . import _lib
 
 # ---- constants mirrored from include/flowstep.h ----------------------------
 F32, F64 = 0, 1
-TOPO_RING, TOPO_HIGHWAY = 0, 1
+TOPO_RING, TOPO_HIGHWAY, TOPO_MERGE = 0, 1, 2
 ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
     ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY, \
-    ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO, ENV_MA_HIGHWAY_PO = range(9)
+    ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO, ENV_MA_HIGHWAY_PO, ENV_MERGE_PO = range(10)
 CTRL_SIM, CTRL_IDM, CTRL_OVM, CTRL_LINEAR_OVM, CTRL_BCM, CTRL_CFM, CTRL_LAC, \
     CTRL_GIPPS, CTRL_FOLLOWER_STOPPER, CTRL_NONLOCAL_FOLLOWER_STOPPER, \
     CTRL_PI_SATURATION, CTRL_RL = range(12)
@@ -103,8 +103,9 @@ class Engine:
                         act_hi=2.6, obs_max_length=0.0, inflow_vehs_per_hour=0.0,
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
                         record_views=0, lc_corrected=0, n_initial=0, inflow_begin=1.0,
-                        evaluate=0, sort_vehicles=0, use_ballistic=0, max_agents=0)
-        # [(vtype, vehs_per_hour, depart_speed, begin[, end[, probability]]), ...]
+                        evaluate=0, sort_vehicles=0, use_ballistic=0, max_agents=0,
+                        merge_pre=0.0, merge_ramp=0.0, merge_post=0.0, merge_zone=0.0)
+        # [(vtype, vehs_per_hour, depart_speed, begin[, end[, probability[, arm]]]), ...]
         inflows = cfg.pop('inflows', None)
         unknown = set(cfg) - set(defaults)
         if unknown:
@@ -140,6 +141,7 @@ class Engine:
                     int(vt), float(rate), float(speed), float(begin)
                 r.end = float(row[4]) if len(row) > 4 else 0.0
                 r.probability = float(row[5]) if len(row) > 5 else 0.0
+                r.arm = int(row[6]) if len(row) > 6 else 0
             self._check(self.lib.fs_set_inflows(self.h, rows, len(inflows)))
         v = _lib.FsViews()
         self._check(self.lib.fs_buffers(self.h, C.byref(v)))
@@ -166,13 +168,13 @@ class Engine:
         self.time_counter = T(v.time_counter, (E,), 'i32')
         self.counters = T(v.counters, (3, E), 'i32')   # highway: in network, departed, arrived
         self.agent_obs = self.agent_reward = self.agent_id = self.veh_id = self.veh_type = None
-        if c.env_kind == ENV_MA_HIGHWAY_PO:
+        if c.env_kind in (ENV_MA_HIGHWAY_PO, ENV_MERGE_PO):
             av = _lib.FsAgentViews()
             self._check(self.lib.fs_agents(self.h, C.byref(av)))
             A = av.max_agents
             self.max_agents = A
             self.agent_obs = T(av.agent_obs, (E, A, av.obs_per_agent))
-            self.agent_reward = T(av.agent_reward, (E, A))
+            self.agent_reward = T(av.agent_reward, (E, A)) if av.agent_reward else None
             self.agent_id = T(av.agent_id, (E, A), 'i32')
             self.veh_id = T(av.veh_id, (E, V), 'i32')       # per highway slot, head first
             self.veh_type = T(av.veh_type, (E, V), 'u8')

@@ -50,7 +50,7 @@
 extern "C" {
 #endif
 
-#define FS_ABI_VERSION 3
+#define FS_ABI_VERSION 4
 
 /* error codes */
 #define FS_OK 0
@@ -66,6 +66,16 @@ extern "C" {
 /* topology */
 #define FS_TOPO_RING 0
 #define FS_TOPO_HIGHWAY 1
+#define FS_TOPO_MERGE 2   /* MergeNetwork (flow/networks/merge.py), single-lane highway + single-lane
+                           * on-ramp: edges inflow_highway (100 m) - left (pre_merge_length) -
+                           * center (post_merge_length), ramp inflow_merge (100 m) - bottom
+                           * (merge_length) joining at 'center'; junction lengths 0.1 / 22.5 m as
+                           * specify_edge_starts implies. n_veh = slot capacity, vehicles enter
+                           * through fs_set_inflows (fs_inflow.arm) and leave at the end of 'center';
+                           * `lane` holds the ARM of a slot's vehicle (0 highway, 1 ramp), `pos` the
+                           * distance travelled on that arm. SUMO's junction is RESTATED:
+                           * both arms on one axis aligned at the merge point, cross-arm car following
+                           * inside merge_zone, collision only on a shared road. */
 
 /* environment front: selects observation + reward */
 #define FS_ENV_ACCEL 0             /* AccelEnv: obs 2V, desired_velocity            */
@@ -114,6 +124,11 @@ extern "C" {
                                 (x_lead - x - len)/L  -- NOT wrapped, like the reference --,
                                 (v-v_follow)/vmax, headway(follower)/L); shared desired_velocity reward */
 
+#define FS_ENV_MERGE_PO 9 /* MergePOEnv (flow/envs/merge.py:28-231) on FS_TOPO_MERGE: max_agents = num_rl
+                           * controlled vehicles (the reference's `rl_veh` list: FIFO from the queue of
+                           * RL vehicles in the network, a row closes up when its vehicle left), obs
+                           * 5 * num_rl, one action row per controlled vehicle, reward desired_velocity +
+                           * 0.1 * time-headway penalty; fs_agents gives the ids behind the rows */
 #define FS_ENV_MA_HIGHWAY_PO 8 /* MultiAgentHighwayPOEnv (flow/envs/multiagent/highway.py:97-196) on the
                                 single-lane open highway: every RL vehicle IN the network is an agent.
                                 obs [max_agents][5] per env, row a = a-th RL vehicle counted from the
@@ -200,8 +215,12 @@ typedef struct fs_config {
   int32_t n_initial;
   int32_t env_flags;     /* FS_ENVF_* bits (0 = reference defaults)              */
   double inflow_begin;   /* s; InFlows.add(begin=1) */
-  int32_t max_agents;    /* FS_ENV_MA_HIGHWAY_PO: observation / action rows per env (<= n_veh) */
+  int32_t max_agents;    /* FS_ENV_MA_HIGHWAY_PO: observation / action rows per env (<= n_veh);
+                          * FS_ENV_MERGE_PO: num_rl (<= 32) */
   int32_t reserved0;
+  /* FS_TOPO_MERGE (net_params.additional_params of MergeNetwork); merge_zone = metres before the
+   * merge point in which vehicles of the two arms follow one another (0: merge_length + 22.5) */
+  double merge_pre, merge_ramp, merge_post, merge_zone;
 } fs_config;
 
 /* one <flow> of the open highway (InFlows.add: veh_type, vehs_per_hour | period | probability,
@@ -215,7 +234,7 @@ typedef struct fs_config {
 #define FS_MAX_INFLOWS 4
 typedef struct fs_inflow {
   int32_t vtype;         /* vehicle type index                                  */
-  int32_t reserved;
+  int32_t arm;           /* FS_TOPO_MERGE: 0 = edge 'inflow_highway', 1 = 'inflow_merge' (else 0) */
   double vehs_per_hour, depart_speed, begin;
   double end;            /* s; <= 0: never ends (InFlows.add default 86400)      */
   double probability;    /* per second, in (0, 1]; 0 = periodic flow             */

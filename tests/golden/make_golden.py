@@ -506,6 +506,30 @@ def start_pos_stochastic():
     json.dump(out, open(os.path.join(HERE, 'start_pos_stochastic.json'), 'w'), indent=1)
 
 
+def merge():
+    """MergePOEnv: the reference's own _apply_rl_actions / additional_command / get_state /
+    compute_reward (RefMerge) on the restated merge network, 300 Env.steps of 5 simulation steps;
+    controlled vehicles come and go, rows close up, a vehicle that left is observed once."""
+    from .ref_harness import RefMerge
+    from tests.scenarios import merge_sim, MERGE
+    sim = merge_sim()
+    ref = RefMerge(sim, 1.5, 1.5)
+    rng = np.random.default_rng(1)
+    A, O, R, D, CT, N = [], [], [], [], [], []
+    for k in range(MERGE['horizon']):
+        act = np.clip(rng.uniform(-1.0, 1.5, MERGE['num_rl']), -1.5, 1.5)
+        obs, rew, done = ref.step(act)
+        A.append(act); O.append(obs); R.append(rew); D.append(done)
+        CT.append([int(v) for v in ref.rl_veh] + [-1] * (MERGE['num_rl'] - len(ref.rl_veh)))
+        N.append([sim.num_vehicles, sim.departed, sim.arrived])
+        if done:
+            break
+    np.savez_compressed(os.path.join(HERE, 'merge.npz'), actions=np.array(A), obs=np.array(O),
+                        reward=np.array(R), done=np.array(D), ctrl=np.array(CT), counts=np.array(N),
+                        pos_final=np.array(sim.pos), arm_final=np.array(sim.arm),
+                        ids_final=np.array(sim.ids))
+
+
 def sumo_fixture():
     src = os.path.join(ref_shim.REF, 'tests/fast_tests/test_files/ring_230_emission.csv')
     rows = list(csv.DictReader(open(src)))
@@ -520,6 +544,7 @@ def main():
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
     ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos(); start_pos_stochastic()
     highway_ma()
+    merge()
     sumo_fixture()
     print('golden vectors written to', HERE)
 

@@ -613,3 +613,104 @@ class RefHighwayMA:
     def compute_reward(self, rl_actions, fail=False):
         r = self._cls.compute_reward(self, rl_actions, fail=fail)
         return {int(k): float(v) for k, v in r.items()}
+
+
+class RefMerge:
+    """MergePOEnv of the REFERENCE (flow/envs/merge.py:106-220: _apply_rl_actions,
+    additional_command, get_state, compute_reward with rewards.desired_velocity) run on the state
+    of the restated merge network (oracle/merge.py: SUMO's move, junction, insertion and arrival
+    are the restatement). Vehicle ids are zero-padded decimal strings of the engine ids."""
+
+    def __init__(self, sim, max_accel=3, max_decel=3, evaluate=False):
+        import collections
+        from flow.envs.merge import MergePOEnv
+        self._cls = MergePOEnv
+        self.sim = sim
+        self.num_rl = sim.num_rl
+        self.rl_queue, self.rl_veh = collections.deque(), []
+        self.leader, self.follower = [], []
+        self.env_params = EnvParams(evaluate=evaluate, additional_params={
+            'max_accel': max_accel, 'max_decel': max_decel, 'target_velocity': sim.target_velocity,
+            'num_rl': sim.num_rl})
+        h = self
+        name = lambda i: '%012d' % i          # noqa: E731
+
+        class V:
+            def _s(self, vid):
+                try:
+                    return h.sim.ids.index(int(vid))
+                except ValueError:
+                    return -1
+
+            def get_ids(self):
+                return [name(i) for i in h.sim.ids]
+
+            def get_rl_ids(self):     # kept sorted by the reference (vehicle/traci.py:259,366)
+                return sorted(name(h.sim.ids[s]) for s in range(len(h.sim.ids)) if h.sim.is_rl(s))
+
+            @property
+            def num_vehicles(self):
+                return len(h.sim.ids)
+
+            def get_speed(self, vid, error=-1001):
+                if isinstance(vid, (list, np.ndarray)):
+                    return [self.get_speed(v, error) for v in vid]
+                s = self._s(vid)
+                return error if s < 0 else h.sim.vel[s]
+
+            def get_headway(self, vid, error=-1001):
+                s = self._s(vid)
+                return error if s < 0 else h.sim.headway[s]
+
+            def get_leader(self, vid, error=''):
+                s = self._s(vid)
+                if s < 0:
+                    return error
+                return None if h.sim.leader[s] < 0 else name(h.sim.ids[h.sim.leader[s]])
+
+            def get_follower(self, vid, error=''):
+                s = self._s(vid)
+                if s < 0:
+                    return error
+                return None if h.sim.follower[s] < 0 else name(h.sim.ids[h.sim.follower[s]])
+
+            def get_x_by_id(self, vid):
+                s = self._s(vid)
+                return h.sim.g.x_abs(h.sim.arm[s], h.sim.pos[s])
+
+            def get_length(self, vid, error=-1001):
+                return h.sim.types[h.sim.type_of[self._s(vid)]].length
+
+            def set_observed(self, vid):
+                pass
+
+            def apply_acceleration(self, vid, acc):
+                h.commands[int(vid)] = float(acc)
+
+        class Nw:
+            def max_speed(self):
+                return h.sim.speed_limit
+
+            def length(self):
+                return h.sim.g.net_length
+
+        self.k = type('K', (), {})()
+        self.k.vehicle, self.k.network = V(), Nw()
+        self.commands = {}
+
+    def step(self, rl_actions):
+        """Env.step (flow/envs/base.py:294-412) around the restated simulator."""
+        sim = self.sim
+        for _ in range(sim.sims_per_step):
+            self.commands = {}
+            if rl_actions is not None:
+                self._cls._apply_rl_actions(self, rl_actions)
+            sim._sim_step(None, commanded_ids=self.commands,
+                          additional_command=lambda: self._cls.additional_command(self))
+            if sim.crash:
+                break
+        sim.done = sim.crash or sim.time_counter >= sim.sims_per_step * (sim.warmup_steps + sim.horizon)
+        obs = np.asarray(self._cls.get_state(self), dtype=float)
+        rew = float(self._cls.compute_reward(self, rl_actions, fail=sim.crash))
+        return obs, rew, sim.done
+

@@ -137,3 +137,57 @@ def highway_ma_action(sim, slot, z):
         return float(np.clip(0.5 * (20.0 - v), -3.0, 1.2)) + z
     return float(np.clip(0.1 * (sim.headway[slot] - 5.0 - 1.5 * v) + 0.6 * (sim.vel[slot - 1] - v),
                          -6.0, 1.2)) + z
+
+
+# merge network under MergePOEnv (tests/golden/merge.npz) -----------------------------------
+MERGE = dict(pre=500.0, ramp=100.0, post=100.0, capacity=128, num_rl=3, dt=0.2, sims_per_step=5,
+             target_velocity=20.0, horizon=300, speed_limit=30.0,
+             initial=[(0, 0, 50.0), (0, 0, 300.0), (0, 1, 30.0)],          # (type, arm, position)
+             # (type, arm, vehs_per_hour, depart_speed, begin): singleagent_merge.py's three flows
+             inflows=[(0, 0, 1800.0, 10.0, 1.0), (1, 0, 200.0, 10.0, 1.0), (0, 1, 100.0, 7.5, 1.0)])
+
+
+def merge_groups(noise=0.0, speed_mode=1):
+    """singleagent_merge.py: IDM humans and RL vehicles, both speed_mode 'obey_safe_speed'."""
+    return [vt('IDM', 0, noise=noise, speed_mode=speed_mode), vt('RL', 0, speed_mode=speed_mode)]
+
+
+def merge_sim(groups=None, **over):
+    from oracle import merge as OM
+    c = dict(MERGE, **over)
+    return OM.MergeSim(oracle_types(groups or merge_groups()), OM.MergeGeometry(c['pre'], c['ramp'], c['post']),
+                       initial=c['initial'],
+                       inflows=[dict(type=t, arm=a, vehs_per_hour=q, depart_speed=v, begin=b)
+                                for t, a, q, v, b in c['inflows']],
+                       dt=c['dt'], speed_limit=c['speed_limit'], capacity=c['capacity'],
+                       num_rl=c['num_rl'], target_velocity=c['target_velocity'], horizon=c['horizon'],
+                       sims_per_step=c['sims_per_step'], zone=c.get('zone'),
+                       evaluate=c.get('evaluate', False), warmup_steps=c.get('warmup_steps', 0))
+
+
+def merge_engine(n_envs, dtype='f64', groups=None, **over):
+    """Engine on the merge network, reset with the scenario's initial vehicles in place."""
+    from flow_b200 import engine as EN
+    c = dict(MERGE, **over)
+    eng = EN.Engine(engine_types(groups or merge_groups()), [t for t, _, _ in c['initial']], n_envs,
+                    dtype=dtype, capacity=c['capacity'], topology=EN.TOPO_MERGE,
+                    env_kind=EN.ENV_MERGE_PO, merge_pre=c['pre'], merge_ramp=c['ramp'],
+                    merge_post=c['post'], merge_zone=c.get('zone') or 0.0, max_agents=c['num_rl'],
+                    sim_step=c['dt'], speed_limit=c['speed_limit'], horizon=c['horizon'],
+                    sims_per_step=c['sims_per_step'], target_velocity=c['target_velocity'],
+                    warmup_steps=c.get('warmup_steps', 0), evaluate=int(c.get('evaluate', False)),
+                    record_views=1, seed=over.get('seed', 0),
+                    inflows=[(t, q, v, b, 0.0, 0.0, a) for t, a, q, v, b in c['inflows']])
+    merge_reset(eng, c['initial'])
+    return eng
+
+
+def merge_reset(eng, initial):
+    """fs_reset in its two halves with the initial vehicles' (arm, position) set in between."""
+    eng.reset_stage(eng.RESET_PLACE)
+    pos = np.zeros((eng.n_veh, eng.n_envs), eng.np_dtype)
+    arm = np.zeros((eng.n_veh, eng.n_envs), np.uint8)
+    for i, (_, a, p) in enumerate(initial):
+        pos[i], arm[i] = p, a
+    eng.set_state(pos=pos, lane=arm)
+    return eng.reset_stage(eng.RESET_WARMUP)
