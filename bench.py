@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — env-steps/s and vehicle-steps/s of the batched step path (BASELINE.json metric).
 
-  python bench.py --gpus N --steps K --warmup W [--workload c2|c5|c3|c4|ma|mah] [--dtype f32|f64]
+  python bench.py --gpus N --steps K --warmup W [--workload c2|c5|c3|c4|ma|mah|mg] [--dtype f32|f64]
   python bench.py --impl reference ...     # CPU arm: the reference's own code on the host cores
 
 A "step" is one Env.step of EVERY environment of the batch (E per GPU). Workload c2 (default,
@@ -69,7 +69,7 @@ def parse(argv=None):
     ap.add_argument('--steps', type=int, default=3000)
     ap.add_argument('--warmup', type=int, default=300)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4', 'mah'])
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4', 'mah', 'mg'])
     ap.add_argument('--fuse', type=int, default=0,
                     help='steps per fused launch; 0 = per workload: 100 (what BASELINE.json states '
                          'for c5), 500 for the 4096-env rings c2 / ma (their 100-step launch lasts '
@@ -372,7 +372,7 @@ def ncu_profile(workload, dtype):
 
 
 KERNEL_OF = {'ma': 'ring1_fast_kernel', 'c3': 'ring_ml_kernel', 'c4': 'highway_kernel',
-             'mah': 'highway_kernel'}
+             'mah': 'highway_kernel', 'mg': 'merge_kernel'}
 
 
 class Leg:
@@ -577,7 +577,7 @@ class Leg:
         (+ lane / slot-type byte r/w, + the 4-byte vehicle id on the multi-agent highway), ring
         length + actions in, obs + reward + done out."""
         ts, env = self.ts, self.env
-        extra = {'c3': 2, 'c4': 2, 'mah': 10}.get(self.workload, 0)
+        extra = {'c3': 2, 'c4': 2, 'mah': 10, 'mg': 20}.get(self.workload, 0)   # mg: arm, type, id, seq r/w
         return active_per_env * (4 * ts + extra) + ts + ts * self.A + ts * env.obs_dim + ts + 1
 
     def roofline_fused(self, r):
@@ -640,10 +640,13 @@ def run_leg(a, ctx, workload, dtype, scaling, k_steps, modes):
         out['host_blocking'] = leg.timed(leg.call_host_blocking, F, target_ms=a.target_ms / 2)
         out['host_closed'] = leg.timed(leg.call_host_closed_loop, F, target_ms=a.target_ms / 2)
     fused = out['fused']
-    active = fused['vehicle_steps'] / max(fused['env_steps'], 1.0)   # vehicles advanced per env-step
+    sps = int(getattr(leg.eng.config, 'sims_per_step', 1) or 1)
+    # vehicles in an env: vehicle-steps per Env.step / simulation steps per Env.step
+    active = fused['vehicle_steps'] / max(fused['env_steps'], 1.0) / sps
     info = dict(workload=workload_name(workload), envs_per_gpu=leg.E, dtype=dtype, fuse=F,
                 scaling=scaling, obs_dim=leg.env.obs_dim, act_dim=leg.A, ring_steps=leg.NB,
-                active_vehicles_per_env=active, n_slots=leg.eng.n_veh,
+                active_vehicles_per_env=active, n_slots=leg.eng.n_veh, horizon=leg.H,
+                sims_per_step=sps,
                 h2d_bytes_per_step=leg.act_b, d2h_bytes_per_step=leg.out_b,
                 streamed_mb_per_ring_cycle=leg.NB * (leg.act_b + leg.out_b) / 1e6)
     roof = dict(fused=leg.roofline_fused(fused))
@@ -685,7 +688,7 @@ def run_b200(a):
             d = brief(r['fused'])
             d.update(config=i, roofline=rf['fused'],
                      crashed_env_frac=r['fused']['crashes'] / max(
-                         i['envs_per_gpu'] * world * math.ceil(r['fused']['steps'] / 3000.0), 1))
+                         i['envs_per_gpu'] * world * math.ceil(r['fused']['steps'] / float(i['horizon'])), 1))
             if 'single' in r:
                 d['single_step'] = brief(r['single'])
                 d['roofline_single_step'] = rf['single']
@@ -716,8 +719,8 @@ def run_b200(a):
                    'timing': 'the K-step pass repeated `reps` times back to back (calibrated so the '
                              'bracket holds >= %.0f ms of GPU work, same R on every rank); issued as a '
                              'long rollout: fused launches of `fuse` steps, envs reset (+ warm-up) every '
-                             '3000 steps BETWEEN the CUDA-event pairs on the same stream; '
-                             'ms_per_step = sum of brackets / (reps x steps)' % a.target_ms,
+                             '%d steps (the horizon) BETWEEN the CUDA-event pairs on the same stream; '
+                             'ms_per_step = sum of brackets / (reps x steps)' % (a.target_ms, info['horizon']),
                    'parallelism': 'envs sharded, %d GPU(s), no data-path collective' % world,
                    'l2': 'actions / obs / reward / done stream through device ring buffers of %d steps = '
                          '%.0f MB per cycle (> 126 MB L2; actions alone %.0f MB); vehicle state is '
@@ -727,7 +730,7 @@ def run_b200(a):
                    'host_cores_bound_to_gpu_numa_node': numa_cores,
                    'counted': 'vehicle-steps actually advanced (engine counter); frozen (crashed) '
                               'envs are not counted'},
-        'crashed_env_frac': fused['crashes'] / max(E * world * math.ceil(fused['steps'] / 3000.0), 1),
+        'crashed_env_frac': fused['crashes'] / max(E * world * math.ceil(fused['steps'] / float(info['horizon'])), 1),   # per episode
         'mean_reward': fused['mean_reward'], 'mean_speed': fused['mean_speed'],
         'active_vehicles_per_env': info['active_vehicles_per_env'],
         'gpu_launches': fused['launches'],

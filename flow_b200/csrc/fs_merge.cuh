@@ -244,8 +244,13 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
         const TypeP<T>& tp = cfg.types[ty[r]];
         const int ctrl = tp.ctrl;
         const bool has_lead = lead[r] >= 0;
-        const T vi = v[r], hi = h[r];
+        const T vi = v[r];
         const T vl = has_lead ? vs[lead[r]] : T(-1001);
+        // an overlapping leader on the OTHER approach road reads as bumper to bumper: with a
+        // negative gap an IDM accelerates again once |gap| > s* (include/flowstep.h FS_TOPO_MERGE)
+        T hi = h[r];
+        if (has_lead && hi < T(0) && (at[lead[r]] & 0xff) != arm[r] && !(us[s] >= zc && us[lead[r]] >= zc))
+          hi = T(1e-3);
         T st0 = T(0);
         T a = ctrl_accel<T>(tp, ctrl, vi, has_lead, vl, hi, false, T(-1001), T(-1001), mean_v, dt,
                             cfg.inv_dt, st0);
@@ -424,9 +429,9 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
         }
         reward = N::max(add(cost1, mul(T(0.1), c2)), T(0));
       }
-      if (A.accumulate_stats && lane_id == 0 && (done || q == cfg.sims_per_step - 1)) {
-        st_rew += (double)reward; st_v += (double)sv; st_v2 += (double)s2;
-        st_vs += n; st_es += 1; st_cr += crash ? 1 : 0;
+      if (A.accumulate_stats && lane_id == 0) {   // speeds and vehicle-steps of every sub-step,
+        st_v += (double)sv; st_v2 += (double)s2; st_vs += n;   // reward / env-step once (substep_stats)
+        if (done || q == cfg.sims_per_step - 1) { st_rew += (double)reward; st_es += 1; st_cr += crash ? 1 : 0; }
       }
     }
     }
@@ -453,7 +458,10 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     if (A.write_views) {
       B.v_headway[eo + s] = s < n ? h[r] : T(0);
       B.v_leader[eo + s] = s < n ? lead[r] : -1;
-      B.v_follower[eo + s] = -1;
+      int fj = -1; T fh = T(0);      // the closest vehicle that calls this one its leader
+      if (s < n)
+        for (int j = 0; j < n; ++j) if (ld[j] == s && (fj < 0 || hs[j] < fh)) { fj = j; fh = hs[j]; }
+      B.v_follower[eo + s] = fj;
       if (A.k_steps > 0) B.v_accel[eo + s] = s < n ? acc[r] : T(0);
     }
   }

@@ -469,9 +469,21 @@ class HighwayNetwork(Network):
     TOPOLOGY = EN.TOPO_HIGHWAY
 
 
+MERGE_NET_PARAMS = {'merge_length': 100, 'pre_merge_length': 200, 'post_merge_length': 100,
+                    'merge_lanes': 1, 'highway_lanes': 1, 'speed_limit': 30}
+
+
+class MergeNetwork(Network):
+    """flow/networks/merge.py:27-221: a highway (inflow_highway -> left -> center) joined by an
+    on-ramp (inflow_merge -> bottom -> center), single lane each."""
+    ADDITIONAL = MERGE_NET_PARAMS
+    TOPOLOGY = EN.TOPO_MERGE
+
+
 _NET_BY_NAME = {'RingNetwork': RingNetwork, 'HighwayNetwork': HighwayNetwork,
-                'LoopScenario': RingNetwork, 'RingScenario': RingNetwork,
-                'HighwayScenario': HighwayNetwork}
+                'MergeNetwork': MergeNetwork, 'LoopScenario': RingNetwork,
+                'RingScenario': RingNetwork, 'HighwayScenario': HighwayNetwork,
+                'MergeScenario': MergeNetwork}
 
 
 # =============================================================================
@@ -546,6 +558,46 @@ def _vtype_row(ini, lc_env):
                          speed_mode=int(ini['car_following_params'].speed_mode))
 
 
+def _inflow_rows(network, names, types, rl_ok, arms=None):
+    """InFlows.get() -> [(type, vehs_per_hour, depart_speed, begin, end, probability, arm)]
+    (flow/core/params.py:1135-1236 holds SUMO's <flow> attributes)."""
+    flows = network.net_params.inflows.get()
+    if len(flows) > 4:
+        raise NotImplementedError('more than four inflows')
+    rows = []
+    for f in flows:
+        rate, prob = f.get('vehsPerHour'), float(f.get('probability') or 0.0)
+        begin, end = float(f['begin']), float(f.get('end') or 0.0)
+        if rate is None and f.get('period') is not None:
+            rate = 3600.0 / float(f['period'])
+        if f.get('number') is not None and end > begin:
+            # SUMO: `number` vehicles, evenly spaced over [begin, end) when no rate is given,
+            # else the flow ends after `number` vehicles
+            if rate is None and not prob:
+                rate = 3600.0 * float(f['number']) / (end - begin)
+            elif rate is not None:
+                end = min(end, begin + float(f['number']) * 3600.0 / float(rate))
+        if rate is None and not prob:
+            raise ValueError('inflow %r: one of vehs_per_hour, probability, period, number is '
+                             'needed' % (f.get('name'),))
+        if isinstance(f['departSpeed'], str):
+            raise NotImplementedError('depart_speed=%r: SUMO picks the speed; only numeric '
+                                      'departure speeds are compiled' % (f['departSpeed'],))
+        if f['vtype'] not in names:
+            raise KeyError('inflow of unknown vehicle type %r' % (f['vtype'],))
+        t = names.index(f['vtype'])
+        if types[t].controller == EN.CTRL_RL and not rl_ok:
+            raise NotImplementedError('an RL inflow needs MultiAgentHighwayPOEnv')
+        arm = 0
+        if arms is not None:
+            if f['edge'] not in arms:
+                raise NotImplementedError('inflow on edge %r: vehicles enter at %s'
+                                          % (f['edge'], ' / '.join(arms)))
+            arm = arms[f['edge']]
+        rows.append((t, float(rate or 0.0), float(f['departSpeed']), begin, end, prob, arm))
+    return rows
+
+
 def compile_spec(env_cls, env_params, sim_params, network, seed=None):
     """Build the engine configuration an env of class `env_cls` needs.
     Raises the reference's exceptions for the reference's error cases."""
@@ -570,11 +622,19 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
     if sort_on and network.TOPOLOGY != EN.TOPO_RING:
         raise NotImplementedError('sort_vehicles=True on the open highway (slots are re-packed)')
     lc_env = env_cls.KIND in (EN.ENV_LANE_CHANGE_ACCEL, EN.ENV_LANE_CHANGE_ACCEL_PO)
+    merge = network.TOPOLOGY == EN.TOPO_MERGE
+    if merge != (env_cls.KIND == EN.ENV_MERGE_PO):
+        raise NotImplementedError('MergePOEnv runs on MergeNetwork, and only it does')
+    n_lanes = 1 if merge else int(net['lanes'])
+    if merge and (int(net['merge_lanes']) != 1 or int(net['highway_lanes']) != 1):
+        raise NotImplementedError('merge: one lane on the highway and on the ramp only')
+    if merge and (ini.spacing != 'uniform' or ini.perturbation > 0 or ini.shuffle):
+        raise NotImplementedError('merge: the even initial placement only')
     types, names, type_of, ids = [], [], [], []
     for t, row in enumerate(veh.initial):
         lcp = row.get('lane_change_params')
         mode = getattr(lcp, 'lane_change_mode', 512)
-        if int(net['lanes']) > 1 and isinstance(mode, (int, float)) and int(mode) & 0xFF:
+        if n_lanes > 1 and isinstance(mode, (int, float)) and int(mode) & 0xFF:
             # bits 0-7 = SUMO's autonomous strategic / cooperative / speed-gain / keep-right
             # changes (LC2013 / SL2015): not restated, and never silently dropped
             raise NotImplementedError(
@@ -589,7 +649,7 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         raise NotImplementedError('more than 16 vehicle types')
     horizon = env_params.horizon
     kw = dict(
-        topology=network.TOPOLOGY, env_kind=env_cls.KIND, n_lanes=int(net['lanes']),
+        topology=network.TOPOLOGY, env_kind=env_cls.KIND, n_lanes=n_lanes,
         sim_step=float(sim_params.sim_step), speed_limit=float(net['speed_limit']),
         x0=float(ini.x0), bunching=float(ini.bunching), init_min_gap=float(ini.min_gap),
         lanes_distribution=int(min(ini.lanes_distribution, 1 << 30)),
@@ -616,46 +676,40 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         if env_cls.KIND in (EN.ENV_WAVE_ATTENUATION_PO, EN.ENV_MA_WAVE_ATTENUATION_PO) and ring:
             kw['obs_max_length'] = hi        # wave_attenuation.py:253-256
         # network/base.py:599-605: no room -> the reference aborts the run
-        lanes_d = int(min(max(ini.lanes_distribution, 1), int(net['lanes'])))
+        lanes_d = int(min(max(ini.lanes_distribution, 1), n_lanes))
         room = lo * lanes_d - lanes_d * max(ini.bunching, 0) - \
             len(ids) * (max(ini.min_gap, 0) + VEHICLE_LENGTH)
         if room < 0:
             raise FatalFlowError('There is not enough space to place all vehicles in the '
                                  'network.')
+    elif merge:
+        pre, ramp, post = (float(net[k]) for k in ('pre_merge_length', 'merge_length',
+                                                   'post_merge_length'))
+        rows = _inflow_rows(network, names, types, rl_ok=True,
+                            arms={'inflow_highway': 0, 'inflow_merge': 1})
+        if any(r[4] < 86400 or r[5] for r in rows):
+            raise NotImplementedError('merge: periodic inflows (vehs_per_hour / period) without an '
+                                      'end only')
+        kw.update(merge_pre=pre, merge_ramp=ramp, merge_post=post,
+                  max_agents=int(ap['num_rl']), inflows=[r[:4] + (0.0, 0.0, r[6]) for r in rows])
+        from . import placement as PL
+        real, internal = PL.merge_edges(pre, ramp, post)
+        try:      # network/base.py:599-605: no room -> the reference aborts the run
+            PL.even_positions(real, internal, ini.x0, ini.min_gap, ini.bunching, len(ids))
+        except ValueError as exc:
+            raise FatalFlowError(str(exc))
+        # slots: both arms and the merged road bumper to bumper is the physical maximum
+        road = 2 * PL.MERGE_INFLOW_EDGE_LEN + pre + ramp + post + 45.2
+        capacity = min(256, max(64, int(math.ceil(road / (VEHICLE_LENGTH + 2.5) / 32) * 32)))
+        if len(ids) > capacity:
+            raise NotImplementedError('merge: more than %d vehicles' % capacity)
     else:
         if int(net['lanes']) != 1 or int(net.get('num_edges', 1)) != 1:
             raise NotImplementedError('highway: single lane, single edge only')
         ma = env_cls.KIND == EN.ENV_MA_HIGHWAY_PO
         kw.update(length_lo=float(net['length']), length_hi=float(net['length']),
                   junction_len=0.0, env_kind=EN.ENV_MA_HIGHWAY_PO if ma else EN.ENV_HIGHWAY)
-        flows = network.net_params.inflows.get()
-        if len(flows) > 4:
-            raise NotImplementedError('more than four inflows')
-        rows = []
-        for f in flows:
-            rate, prob = f.get('vehsPerHour'), float(f.get('probability') or 0.0)
-            begin, end = float(f['begin']), float(f.get('end') or 0.0)
-            if rate is None and f.get('period') is not None:
-                rate = 3600.0 / float(f['period'])
-            if f.get('number') is not None and end > begin:
-                # SUMO: `number` vehicles, evenly spaced over [begin, end) when no rate is given,
-                # else the flow ends after `number` vehicles
-                if rate is None and not prob:
-                    rate = 3600.0 * float(f['number']) / (end - begin)
-                elif rate is not None:
-                    end = min(end, begin + float(f['number']) * 3600.0 / float(rate))
-            if rate is None and not prob:
-                raise ValueError('inflow %r: one of vehs_per_hour, probability, period, number is '
-                                 'needed' % (f.get('name'),))
-            if isinstance(f['departSpeed'], str):
-                raise NotImplementedError('depart_speed=%r: SUMO picks the speed; only numeric '
-                                          'departure speeds are compiled' % (f['departSpeed'],))
-            if f['vtype'] not in names:
-                raise KeyError('inflow of unknown vehicle type %r' % (f['vtype'],))
-            t = names.index(f['vtype'])
-            if types[t].controller == EN.CTRL_RL and not ma:
-                raise NotImplementedError('an RL inflow needs MultiAgentHighwayPOEnv')
-            rows.append((t, float(rate or 0.0), float(f['departSpeed']), begin, end, prob))
+        rows = [r[:6] for r in _inflow_rows(network, names, types, rl_ok=ma)]
         if len(rows) == 1 and not rows[0][5] and rows[0][4] >= 86400:   # the single <flow> of fs_config
             kw.update(inflow_type=rows[0][0], inflow_vehs_per_hour=rows[0][1],
                       inflow_depart_speed=rows[0][2], inflow_begin=rows[0][3])
@@ -686,16 +740,28 @@ class _VehicleKernel:
         if self._cache is None:
             e, i = self._env.engine, self._env.view_env
             g = lambda t: None if t is None else t[:, i].cpu().numpy()  # noqa: E731
-            self._cache = dict(pos=g(e.pos), vel=g(e.vel), lane=g(e.lane), head=g(e.headway),
-                               lead=g(e.leader), foll=g(e.follower), act=g(e.active),
-                               C=float(e.length[i]))
+            self._cache = c = dict(pos=g(e.pos), vel=g(e.vel), lane=g(e.lane), head=g(e.headway),
+                                   lead=g(e.leader), foll=g(e.follower), act=g(e.active),
+                                   C=float(e.length[i]), names=None)
+            if e.veh_id is not None and hasattr(self._env, 'vehicle_name'):
+                # vehicles come and go: every occupied slot answers to the name SUMO would use
+                vid, c['vtype'] = e.veh_id[i].cpu().numpy(), e.veh_type[i].cpu().numpy()
+                c['slot_names'] = [self._env.vehicle_name(v) if c['act'][k] and v >= 0 else None
+                                   for k, v in enumerate(vid)]
+                c['names'] = {n: k for k, n in enumerate(c['slot_names']) if n is not None}
         return self._cache
 
     def _invalidate(self):
         self._cache = None
 
     def _idx(self, veh_id):
-        return self._env._index.get(veh_id, -1)
+        names = self._snap()['names']
+        return (self._env._index if names is None else names).get(veh_id, -1)
+
+    def _vtype(self, i):
+        s = self._snap()
+        t = s['vtype'][i] if s['names'] is not None else self._env.spec.type_of[i]
+        return self._env.spec.types[int(t)], self._env.spec.type_names[int(t)]
 
     def _get(self, key, veh_id, error):
         if isinstance(veh_id, (list, tuple, np.ndarray)):
@@ -709,21 +775,28 @@ class _VehicleKernel:
     # ids ------------------------------------------------------------------
     def get_ids(self):
         s, ids = self._snap(), self._env.spec.veh_ids
+        if s['names'] is not None:
+            return list(s['names'])
         if self._env.spec.capacity is None:
             return list(ids)
         return [v for i, v in enumerate(ids) if s['act'][i]]
 
     def get_rl_ids(self):
+        s = self._snap()
+        if s['names'] is not None:     # kept sorted by the reference (vehicle/traci.py:259,366)
+            return sorted(n for n, k in s['names'].items()
+                          if self._vtype(k)[0].controller == EN.CTRL_RL)
         return [v for v in self._env.spec.veh_ids if self._env._is_rl[self._env._index[v]]]
 
     def get_human_ids(self):
+        s = self._snap()
+        if s['names'] is not None:
+            return [n for n, k in s['names'].items() if self._vtype(k)[0].controller != EN.CTRL_RL]
         return [v for v in self._env.spec.veh_ids if not self._env._is_rl[self._env._index[v]]]
 
     def get_controlled_ids(self):
         sim = (EN.CTRL_SIM, EN.CTRL_RL)
-        return [v for v in self._env.spec.veh_ids
-                if self._env.spec.types[self._env.spec.type_of[self._env._index[v]]].controller
-                not in sim]
+        return [v for v in self.get_ids() if self._vtype(self._idx(v))[0].controller not in sim]
 
     @property
     def num_vehicles(self):
@@ -734,24 +807,43 @@ class _VehicleKernel:
         return len(self.get_rl_ids())
 
     def get_type(self, veh_id):
-        i = self._idx(veh_id)
-        return self._env.spec.type_names[self._env.spec.type_of[i]]
+        return self._vtype(self._idx(veh_id))[1]
 
     # state ----------------------------------------------------------------
     def get_speed(self, veh_id, error=-1001):
         return self._get('vel', veh_id, error)
 
+    def _merge_lengths(self):
+        net = self._env.net_params.additional_params
+        return (float(net['pre_merge_length']), float(net['merge_length']),
+                float(net['post_merge_length']))
+
+    def _arm_pos(self, veh_id):
+        """merge: (arm, metres along it) of a vehicle, None when it is not in the network"""
+        p = self._get('pos', veh_id, None)
+        return None if p is None else (int(self._get('lane', veh_id, 0)), p)
+
     def get_x_by_id(self, veh_id):
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            if isinstance(veh_id, (list, tuple, np.ndarray)):
+                return [self.get_x_by_id(v) for v in veh_id]
+            from . import placement as PL
+            ap = self._arm_pos(veh_id)
+            return -1001 if ap is None else PL.merge_x(ap[0], ap[1], *self._merge_lengths())
         return self._get('pos', veh_id, -1001)
 
     def get_lane(self, veh_id, error=-1001):
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:    # the lane buffer holds the arm
+            if isinstance(veh_id, (list, tuple, np.ndarray)):
+                return [self.get_lane(v, error) for v in veh_id]
+            return error if self._get('pos', veh_id, None) is None else 0
         return self._get('lane', veh_id, error)
 
     def get_length(self, veh_id, error=-1001):
         if isinstance(veh_id, (list, tuple, np.ndarray)):
             return [self.get_length(v, error) for v in veh_id]
         i = self._idx(veh_id)
-        return error if i < 0 else float(self._env.spec.types[self._env.spec.type_of[i]].length)
+        return error if i < 0 else float(self._vtype(i)[0].length)
 
     def get_edge(self, veh_id, error=''):
         """Edge name from the loop coordinate (ring.py:194-216 edge starts;
@@ -761,6 +853,9 @@ class _VehicleKernel:
         x = self._get('pos', veh_id, None)
         if x is None:
             return error
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            from . import placement as PL
+            return PL.merge_edge_of(self._arm_pos(veh_id)[0], x, *self._merge_lengths())[0]
         return self._env._edge_of(x)[0]
 
     def get_position(self, veh_id, error=-1001):
@@ -770,6 +865,9 @@ class _VehicleKernel:
         x = self._get('pos', veh_id, None)
         if x is None:
             return error
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            from . import placement as PL
+            return PL.merge_edge_of(self._arm_pos(veh_id)[0], x, *self._merge_lengths())[1]
         return x - self._env._edge_of(x)[1]
 
     def get_headway(self, veh_id, error=-1001):
@@ -783,7 +881,10 @@ class _VehicleKernel:
         j = self._get(key, veh_id, None)
         if j is None:
             return error          # unknown vehicle
-        return None if j < 0 else self._env.spec.veh_ids[j]   # None: nobody ahead / behind
+        if j < 0:
+            return None                                       # nobody ahead / behind
+        s = self._snap()
+        return self._env.spec.veh_ids[j] if s['names'] is None else s['slot_names'][j]
 
     def get_leader(self, veh_id, error=''):
         return self._neighbour('lead', veh_id, error)
@@ -822,6 +923,8 @@ class _NetworkKernel:
     def non_internal_length(self):
         if self._env.network.TOPOLOGY == EN.TOPO_RING:
             return self.length() - 4 * RING_JUNCTION_LENGTH
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            return self.length() - (2 * 0.1 + 22.5)
         return self.length()
 
     def max_speed(self):
@@ -831,19 +934,29 @@ class _NetworkKernel:
         return self.max_speed()
 
     def num_lanes(self, edge=None):
-        return int(self._env.network.net_params.additional_params['lanes'])
+        return int(self._env.network.net_params.additional_params.get('lanes', 1))
 
     def get_edge_list(self):
         if self._env.network.TOPOLOGY == EN.TOPO_RING:
             return ['bottom', 'right', 'top', 'left']
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            return ['inflow_highway', 'left', 'inflow_merge', 'bottom', 'center']
         return ['highway_0']
 
     def get_junction_list(self):
         if self._env.network.TOPOLOGY == EN.TOPO_RING:
             return [':right_0', ':top_0', ':left_0', ':bottom_0']
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            return [':left', ':bottom', ':center']
         return []
 
     def edge_length(self, edge):
+        if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
+            net = self._env.network.net_params.additional_params
+            return {'inflow_highway': 100.0, 'inflow_merge': 100.0, ':left': 0.1, ':bottom': 0.1,
+                    ':center': 22.5, 'left': float(net['pre_merge_length']),
+                    'bottom': float(net['merge_length']),
+                    'center': float(net['post_merge_length'])}[edge]
         if edge.startswith(':'):
             return RING_JUNCTION_LENGTH
         n = len(self.get_edge_list())
@@ -921,7 +1034,8 @@ class Env:
         self.obs_var_labels = []
         # placements the reference draws from host random streams (flow_b200/placement.py)
         ic = self.initial_config
-        self._host_placement = ic.spacing == 'random' or ic.perturbation > 0 or bool(ic.shuffle)
+        self._host_placement = ic.spacing == 'random' or ic.perturbation > 0 or bool(ic.shuffle) \
+            or network.TOPOLOGY == EN.TOPO_MERGE     # five unequal edges: placed on the host
         self._placed = None
         if self._host_placement and self.spec.kw.get('length_lo') != self.spec.kw.get('length_hi'):
             # WaveAttenuationEnv.reset builds a NEW InitialConfig(bunching=50, min_gap=0) for every
@@ -1353,10 +1467,77 @@ class MultiAgentHighwayPOEnv(Env):
         return obs, rew, d, {name: {} for _, name in rows}
 
 
+class MergePOEnv(Env):
+    """flow/envs/merge.py:24-220 on MergeNetwork (one lane each way). At most `num_rl` RL vehicles
+    are controlled at a time: action k drives the k-th vehicle of `rl_veh`; vehicles that leave
+    free their row, RL vehicles that entered later wait for one in order of arrival. Per row the
+    observation holds own speed, the speed difference and bumper-to-bumper distance to the leader
+    and to the follower, scaled by the speed limit and the network length; the reward is
+    rewards.desired_velocity minus a penalty for time headways under one second.
+
+    Vehicle names are the ones SUMO gives: "<type>_<i>" for the initial vehicles,
+    "<inflow name>.<k>" for inflow vehicles.
+
+    Restated simulator behaviour, documented in DESIGN.md: both arms share one axis measured from
+    the merge point; a ramp vehicle and a highway vehicle see each other from `merge_zone` before
+    it on (default: the ramp edge + the 22.5 m junction); a scheduled vehicle enters when the gap
+    to the last vehicle of its arm is the model's desired gap at the departure speed, flows are
+    served earliest due first. The reference removes from `rl_veh` while iterating over it, which
+    skips one element for a step when a controlled vehicle leaves; not reproduced."""
+    KIND = EN.ENV_MERGE_PO
+    ADDITIONAL = {'max_accel': 3, 'max_decel': 3, 'target_velocity': 25, 'num_rl': 5}
+
+    def __init__(self, env_params, sim_params, network, simulator='b200', **kw):
+        super().__init__(env_params, sim_params, network, simulator, **kw)
+        self.num_rl = int(env_params.additional_params['num_rl'])
+        self._flow_names = [f['name'] for f in network.net_params.inflows.get()]
+        self.leader, self.follower = [], []
+
+    @property
+    def action_space(self):
+        ap = self.env_params.additional_params
+        return _box(low=-abs(ap['max_decel']), high=ap['max_accel'], shape=(self.num_rl,),
+                    dtype=np.float32)
+
+    @property
+    def observation_space(self):
+        return _box(low=0, high=1, shape=(5 * self.num_rl,), dtype=np.float32)
+
+    def vehicle_name(self, vid):
+        """engine vehicle id -> the id SUMO would give the vehicle"""
+        vid = int(vid)
+        if vid < (1 << 24):
+            return self._initial_ids[vid]
+        return '%s.%d' % (self._flow_names[(vid >> 24) - 1], vid & 0xFFFFFF)
+
+    @property
+    def rl_veh(self):
+        """names of the controlled vehicles, row order (merge.py:60-63)"""
+        ids = self.engine.agent_id[self.view_env].cpu().numpy()
+        return [self.vehicle_name(v) for v in ids if v >= 0]
+
+    def _draw_host_placement(self):
+        """gen_even_start_pos over the five edges (placement.even_positions), identical in every
+        env of the batch; initial vehicles take the positions in the order they were added."""
+        from . import placement as PL
+        eng, ic, net = self.engine, self.initial_config, self.net_params.additional_params
+        pre, ramp, post = (float(net[k]) for k in ('pre_merge_length', 'merge_length',
+                                                   'post_merge_length'))
+        eng.reset_stage(eng.RESET_PLACE)
+        real, internal = PL.merge_edges(pre, ramp, post)
+        where, _ = PL.even_positions(real, internal, ic.x0, ic.min_gap, ic.bunching,
+                                     len(self._initial_ids))
+        pos = np.zeros((eng.n_veh, self.n_envs), eng.np_dtype)
+        arm = np.zeros((eng.n_veh, self.n_envs), np.uint8)
+        for i, (edge, p) in enumerate(where):
+            arm[i], pos[i] = PL.merge_arm_position(edge, p, pre)
+        self._placed = (pos, arm)
+
+
 _ENV_BY_NAME = {c.__name__: c for c in (AccelEnv, WaveAttenuationEnv, WaveAttenuationPOEnv,
                                         LaneChangeAccelEnv, LaneChangeAccelPOEnv,
                                         MultiAgentWaveAttenuationPOEnv, MultiAgentAccelPOEnv,
-                                        MultiAgentHighwayPOEnv)}
+                                        MultiAgentHighwayPOEnv, MergePOEnv)}
 
 
 # =============================================================================

@@ -104,3 +104,113 @@ def shuffled(ids, shuffle=None):
     out = list(ids)
     (random.shuffle if shuffle is None else shuffle)(out)
     return out
+
+
+# ---- networks with several edges of different length (the merge) -----------------------------
+MERGE_INFLOW_EDGE_LEN = 100.0     # flow/networks/merge.py:9
+
+
+def merge_edges(pre, merge, post):
+    """([(name, start, length)] real edges, [(name, start)] internal edges) of a MergeNetwork
+    (specify_edge_starts / specify_internal_edge_starts, flow/networks/merge.py:196-221), with
+    the nominal edge lengths of specify_edges (merge.py:120-160)."""
+    I = MERGE_INFLOW_EDGE_LEN
+    real = [('inflow_highway', 0.0, I), ('left', I + 0.1, float(pre)),
+            ('center', I + pre + 22.6, float(post)), ('inflow_merge', I + pre + post + 22.6, I),
+            ('bottom', 2 * I + pre + post + 22.7, float(merge))]
+    internal = [(':left', I), (':center', I + pre + 0.1), (':bottom', 2 * I + pre + post + 22.6)]
+    return real, internal
+
+
+def merge_arm_position(edge, p, pre):
+    """(arm, metres along the arm) of position p on `edge`: the engine's merge coordinates
+    (include/flowstep.h FS_TOPO_MERGE). Arm 0 = inflow_highway -> left -> center,
+    arm 1 = inflow_merge -> bottom -> center."""
+    I = MERGE_INFLOW_EDGE_LEN
+    return {'inflow_highway': (0, p), 'left': (0, I + 0.1 + p), 'center': (0, I + 0.1 + pre + 22.5 + p),
+            'inflow_merge': (1, p), 'bottom': (1, I + 0.1 + p)}[edge]
+
+
+def even_positions(real, internal, x0, min_gap, bunching, num_vehicles, num_lanes=1,
+                   lanes_distribution=1 << 30):
+    """gen_even_start_pos (network/base.py:256-392) with edges_distribution = 'all' on a network
+    whose edges all have `num_lanes` lanes: [(edge, position)] and lanes, in placement order.
+    Raises ValueError where the reference raises FatalFlowError."""
+    min_gap = max(0, min_gap)
+    lanes_distr = min(max(int(min(lanes_distribution, 1 << 30)), 1), num_lanes)
+    length = {n: ln for n, _, ln in real}
+    usable = [n for n, _, ln in real if ln > min_gap + VEHICLE_LENGTH]
+    available = sum(length[n] * min(num_lanes, lanes_distr) for n in usable) - \
+        lanes_distr * bunching - num_vehicles * (min_gap + VEHICLE_LENGTH)
+    if available < 0:
+        raise ValueError('There is not enough space to place all vehicles in the network.')
+    if num_vehicles == 0:
+        return [], []
+    non_internal = sum(length.values())
+    total = sorted([(n, s) for n, s, _ in real] + list(internal), key=lambda t: t[1])
+    names = [n for n, _ in total]
+    internal_names = {n for n, _ in internal}
+
+    def get_edge(x):
+        for n, s in reversed(total):
+            if x >= s:
+                return n, x - s
+
+    increment = available / num_vehicles
+    x, count, out, lanes = x0, 0, [], []
+    while count < num_vehicles:
+        pos = get_edge(x)
+        while pos[0] in internal_names:           # never inside a junction: start of the next edge
+            i = names.index(pos[0])
+            nxt = total[0] if i == len(total) - 1 else total[i + 1]
+            x, pos = nxt[1], (nxt[0], 0)
+        while pos[0] not in usable:
+            x = (x + length[pos[0]]) % non_internal
+            pos = get_edge(x)
+        for lane in range(min(num_lanes, lanes_distr)):
+            count += 1
+            out.append(pos)
+            lanes.append(lane)
+            if count == num_vehicles:
+                break
+        x = (x + increment + VEHICLE_LENGTH + min_gap) % non_internal
+    return out, lanes
+
+
+def merge_x(arm, p, pre, merge, post):
+    """get_x_by_id of a vehicle p metres into its arm: edge start + position on a real edge, the
+    bare start of an internal one (network/traci.py:273-289 with the merge tables above)."""
+    I, jc = MERGE_INFLOW_EDGE_LEN, MERGE_INFLOW_EDGE_LEN + pre + 0.1
+    ramp0 = I + pre + post + 22.6
+    LH, LM = I + 0.1 + pre + 22.5, I + 0.1 + merge + 22.5
+    if arm == 0:
+        if p < I:
+            return p
+        if p < I + 0.1:
+            return I
+        if p < I + 0.1 + pre:
+            return p
+        return jc if p < LH else p
+    if p < I:
+        return ramp0 + p
+    if p < I + 0.1:
+        return ramp0 + I
+    if p < I + 0.1 + merge:
+        return ramp0 + p
+    return jc if p < LM else LH + (p - LM)
+
+
+def merge_edge_of(arm, p, pre, merge, post):
+    """(edge name, position on it) of a vehicle p metres into its arm."""
+    I = MERGE_INFLOW_EDGE_LEN
+    first, second, mid = (('inflow_highway', 'left', pre), ('inflow_merge', 'bottom', merge))[arm][0:3]
+    junction = ':left' if arm == 0 else ':bottom'
+    if p < I:
+        return first, p
+    if p < I + 0.1:
+        return junction, p - I
+    if p < I + 0.1 + mid:
+        return second, p - (I + 0.1)
+    if p < I + 0.1 + mid + 22.5:
+        return ':center', p - (I + 0.1 + mid)
+    return 'center', p - (I + 0.1 + mid + 22.5)

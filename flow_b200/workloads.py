@@ -77,7 +77,27 @@ def highway_ma(noise=0.0, speed_mode=SPEED_MODE):
     return types, [0] * 20, kw
 
 
+def merge_mg(noise=0.0, speed_mode=SPEED_MODE):
+    """MergePOEnv on MergeNetwork with the numbers of examples/exp_configs/rl/
+    singleagent/singleagent_merge.py (pre-merge 500 m, ramp and post-merge 100 m, 2000 veh/h on
+    the highway of which 10 % RL, 100 veh/h on the ramp, 5 controlled rows, sim_step 0.2 with
+    sims_per_step 5, horizon 600). The network starts empty and fills during 100 warm-up
+    Env.steps; 128 slots."""
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, speed_mode=speed_mode),
+             EN.make_vtype(EN.CTRL_RL, speed_mode=speed_mode)]
+    kw = dict(topology=EN.TOPO_MERGE, env_kind=EN.ENV_MERGE_PO, merge_pre=500.0, merge_ramp=100.0,
+              merge_post=100.0, max_agents=5, sim_step=0.2, sims_per_step=5, target_velocity=20.0,
+              horizon=600, warmup_steps=100, capacity=128,
+              inflows=[(0, 1800.0, 10.0, 1.0, 0.0, 0.0, 0), (1, 200.0, 10.0, 1.0, 0.0, 0.0, 0),
+                       (0, 100.0, 7.5, 1.0, 0.0, 0.0, 1)])
+    return types, [], kw
+
+
 WORKLOADS = {
+    'mg': dict(builder=merge_mg, n_envs=1024, n_veh=128,
+               name='MergePOEnv on MergeNetwork (500 / 100 / 100 m), inflows 1800 + 200 RL + 100 veh/h, '
+                    '5 controlled rows, 5 simulation steps per Env.step, 128 slots, 1024 envs/GPU, '
+                    'random accelerations'),
     'mah': dict(builder=highway_ma, n_envs=1024, n_veh=160,
                 name='MultiAgentHighwayPOEnv open 1 km highway, IDM inflow 1600 + RL inflow 400 veh/h, '
                      '160 slots, 32 agent rows, 1024 envs/GPU, agents without command (simulator model)'),

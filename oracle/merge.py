@@ -20,8 +20,11 @@ among: vehicles of its own arm, vehicles past the merge point, and - once both a
 `zone` metres of the merge point - vehicles of the other arm (a zipper by position stands in
 for SUMO's junction right-of-way). Ties in u: the lower slot is ahead. Collision <=> headway < 0
 towards a leader that shares the road: same arm, or both inside the junction / on 'center'
-(u >= LH - 22.5); two vehicles side by side on the two approach roads are no collision, the one
-behind on the axis just brakes for the other.
+(u >= LH - 22.5); two vehicles side by side on the two approach roads are no collision: the
+one behind on the axis brakes for the other as if bumper to bumper - its controller and the
+simulator model read a gap of MIN_CTRL_GAP instead of the negative projected one (with a negative
+gap an IDM accelerates again once |gap| > s*, and the pair would drive into the junction abreast).
+Observations and rewards keep the geometric headway.
 Vehicles leave at the end of 'center'; a <flow> emits at the start of its arm, at most one
 vehicle per flow and step, the flow with the earliest scheduled departure first, once the gap to the arm's last vehicle reaches
 the simulator model's desired gap s* for the depart speed (SUMO delays an insertion it deems
@@ -37,6 +40,23 @@ INFLOW_EDGE_LEN = 100.0        # flow/networks/merge.py:8
 J_SMALL, J_CENTER = 0.1, 22.5  # junction lengths implied by specify_edge_starts (0.1 / 22.6 - 0.1)
 F32_EPS = float(np.finfo(np.float32).eps)
 ARM_HIGHWAY, ARM_RAMP = 0, 1
+MIN_CTRL_GAP = 1e-3            # what a controller reads for an overlapping cross-arm leader
+
+
+class _ControlView:
+    """The simulator as the controllers see it: everything of MergeSim, headways floored for
+    overlapping leaders on the other approach road (module docstring)."""
+
+    def __init__(self, sim):
+        self._sim = sim
+        zc = sim.g.LH - J_CENTER
+        self.headway = [
+            MIN_CTRL_GAP if (h < 0 and j >= 0 and sim.arm[i] != sim.arm[j] and
+                             not (sim.u(i) >= zc and sim.u(j) >= zc)) else h
+            for i, (h, j) in enumerate(zip(sim.headway, sim.leader))]
+
+    def __getattr__(self, name):
+        return getattr(self._sim, name)
 
 
 class MergeGeometry:
@@ -202,16 +222,17 @@ class MergeSim:
                 if vid in slot_of:
                     commanded[slot_of[vid]] = float(actions[k])
         nv = [0.0] * n
+        view = _ControlView(self)
         for s in range(n):
             vt = self.types[self.type_of[s]]
             z = self.noise_fn(self.time_counter - 1, s) if (self.noise_fn and vt.noise > 0) else 0.0
-            a = C.get_action(self, s, vt, {}, dt, self.speed_limit, z)
+            a = C.get_action(view, s, vt, {}, dt, self.speed_limit, z)
             cmd = vt.controller not in (C.SIM, C.RL)
             if s in commanded:
                 a, cmd = commanded[s], True           # clipped by the caller's Box (base.py:614)
             self.accel[s] = a
             if cmd and vt.speed_mode:
-                a = C.speed_mode_accel(self, s, vt, a, self.speed_limit)
+                a = C.speed_mode_accel(view, s, vt, a, self.speed_limit)
             nv[s] = max(self.vel[s] + a * dt, 0.0)
         (additional_command or self.additional_command)()   # base.py:365, before simulation_step
         for s in range(n):

@@ -506,6 +506,23 @@ def start_pos_stochastic():
     json.dump(out, open(os.path.join(HERE, 'start_pos_stochastic.json'), 'w'), indent=1)
 
 
+def start_pos_merge():
+    """gen_even_start_pos of the reference on its own MergeNetwork tables (five edges of unequal
+    length, three junction slots): the initial vehicles of singleagent_merge.py and denser cases."""
+    from .ref_harness import ref_merge_start_positions
+    cases = [dict(pre=500, merge=100, post=100, n=5, kw={}),            # singleagent_merge.py
+             dict(pre=200, merge=100, post=100, n=5, kw={}),            # the network's defaults
+             dict(pre=500, merge=100, post=100, n=40, kw=dict(min_gap=1.0, bunching=30)),
+             dict(pre=300, merge=60, post=80, n=17, kw=dict(x0=77.0)),
+             dict(pre=500, merge=100, post=100, n=1, kw={}),
+             dict(pre=50, merge=4, post=100, n=9, kw={})]               # an edge too short to use
+    out = []
+    for c in cases:
+        pos, lane = ref_merge_start_positions(c['pre'], c['merge'], c['post'], c['n'], **c['kw'])
+        out.append(dict(c, pos=[[e, p] for e, p in pos], lane=lane))
+    json.dump(out, open(os.path.join(HERE, 'start_pos_merge.json'), 'w'), indent=1)
+
+
 def merge():
     """MergePOEnv: the reference's own _apply_rl_actions / additional_command / get_state /
     compute_reward (RefMerge) on the restated merge network, 300 Env.steps of 5 simulation steps;
@@ -542,7 +559,7 @@ def sumo_fixture():
 def main():
     json.dump(dict(controllers=kat(), rewards=reward_kat()),
               open(os.path.join(HERE, 'kat.json'), 'w'), indent=1)
-    ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos(); start_pos_stochastic()
+    ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos(); start_pos_stochastic(); start_pos_merge()
     highway_ma()
     merge()
     sumo_fixture()

@@ -104,6 +104,50 @@ def ref_start_positions(length, num_vehicles, lanes=1, **init_kw):
     return [net.get_x(e, p) for e, p in pos], list(lane)
 
 
+class _EdgeNet:
+    """Stand-in for TraCIKernelNetwork on a network of the REFERENCE (its own specify_edges /
+    specify_edge_starts / specify_internal_edge_starts tables, nominal edge lengths): what the
+    reference's gen_even_start_pos reads."""
+
+    def __init__(self, network):
+        self.edgestarts = list(network.edge_starts)
+        self.internal_edgestarts = list(network.internal_edge_starts)
+        self.total_edgestarts = sorted(self.edgestarts + self.internal_edgestarts,
+                                       key=lambda t: t[1])
+        self.total_edgestarts_dict = dict(self.total_edgestarts)
+        self._len = {e['id']: float(e['length']) for e in network.edges}
+        lanes = {t['id']: int(t['numLanes']) for t in network.types}
+        self._lanes = {e['id']: lanes[e['type']] for e in network.edges}
+
+    def get_edge_list(self):
+        return list(self._len)
+
+    def num_lanes(self, edge):
+        return self._lanes[edge]
+
+    def edge_length(self, edge):
+        return self._len[edge]
+
+    def non_internal_length(self):
+        return sum(self._len.values())
+
+    get_edge = _Net.get_edge
+    get_x = _Net.get_x
+    gen_even_start_pos = BaseKernelNetwork.gen_even_start_pos
+    _get_start_pos_util = BaseKernelNetwork._get_start_pos_util
+
+
+def ref_merge_start_positions(pre, merge, post, num_vehicles, **init_kw):
+    """[(edge, position)] from the reference's gen_even_start_pos on its own MergeNetwork."""
+    from flow.networks.merge import MergeNetwork
+    from flow.core.params import NetParams, VehicleParams
+    net = MergeNetwork('merge', VehicleParams(), NetParams(additional_params={
+        'merge_length': merge, 'pre_merge_length': pre, 'post_merge_length': post,
+        'merge_lanes': 1, 'highway_lanes': 1, 'speed_limit': 30}))
+    pos, lane = _EdgeNet(net).gen_even_start_pos(InitialConfig(**init_kw), num_vehicles)
+    return [(e, float(p)) for e, p in pos], list(lane)
+
+
 class _Veh:
     """The getter surface of TraCIVehicle the controllers/rewards call,
     string ids in, backed by arrays."""

@@ -34,6 +34,10 @@ def check_state(eng, e, sim, tol, tag):
     assert list(st['ctrl']) == list(sim.rl_veh) + [-1] * (sim.num_rl - len(sim.rl_veh)), tag
     assert close(st['pos'], sim.pos) <= tol, tag
     assert close(st['vel'], sim.vel) <= tol, tag
+    n = st['n']
+    assert eng.leader[:n, e].cpu().numpy().tolist() == sim.leader, tag
+    assert eng.follower[:n, e].cpu().numpy().tolist() == sim.follower, tag
+    assert close(eng.headway[:n, e].cpu().numpy(), sim.headway) <= tol * 1e3, tag
 
 
 @pytest.mark.parametrize('K', [1, 7])
@@ -175,3 +179,118 @@ def test_merge_noise_and_stats():
     eng2 = S.merge_engine(4, 'f32', groups=groups, seed=3)
     eng2.step(a, k=50)
     np.testing.assert_array_equal(eng2.pos.cpu().numpy(), p1)
+
+
+def merge_flow_params(F, n_initial=5, flow_rate=2000.0, rl_pen=0.1, num_rl=5, horizon=120):
+    """examples/exp_configs/rl/singleagent/singleagent_merge.py, written against module F
+    (flow_b200.flow_api here; the reference's own modules take the same calls)."""
+    vehicles = F.VehicleParams()
+    vehicles.add(veh_id='human', acceleration_controller=(F.IDMController, {}),
+                 car_following_params=F.SumoCarFollowingParams(speed_mode='obey_safe_speed'),
+                 num_vehicles=n_initial)
+    vehicles.add(veh_id='rl', acceleration_controller=(F.RLController, {}),
+                 car_following_params=F.SumoCarFollowingParams(speed_mode='obey_safe_speed'),
+                 num_vehicles=0)
+    inflow = F.InFlows()
+    inflow.add(veh_type='human', edge='inflow_highway', vehs_per_hour=(1 - rl_pen) * flow_rate,
+               depart_lane='free', depart_speed=10)
+    inflow.add(veh_type='rl', edge='inflow_highway', vehs_per_hour=rl_pen * flow_rate,
+               depart_lane='free', depart_speed=10)
+    inflow.add(veh_type='human', edge='inflow_merge', vehs_per_hour=100, depart_lane='free',
+               depart_speed=7.5)
+    net = dict(F.MERGE_NET_PARAMS)
+    net.update(merge_lanes=1, highway_lanes=1, pre_merge_length=500)
+    return dict(
+        exp_tag='stabilizing_open_network_merges', env_name=F.MergePOEnv, network=F.MergeNetwork,
+        simulator='traci', sim=F.SumoParams(sim_step=0.2, render=False, restart_instance=True),
+        env=F.EnvParams(horizon=horizon, sims_per_step=5, warmup_steps=0, additional_params={
+            'max_accel': 1.5, 'max_decel': 1.5, 'target_velocity': 20, 'num_rl': num_rl}),
+        net=F.NetParams(inflows=inflow, additional_params=net), veh=vehicles,
+        initial=F.InitialConfig())
+
+
+def test_merge_env_through_the_flow_api():
+    """make_create_env on singleagent_merge.py-style flow_params: spaces, the initial placement
+    (the reference-written start_pos_merge.json case), the gym step against the oracle, names."""
+    import json
+    from flow_b200 import flow_api as F
+    from flow_b200 import placement as PL
+    from oracle import merge as OM
+    params = merge_flow_params(F)
+    create_env, name = F.make_create_env(params)
+    assert name.startswith('MergePOEnv-v')
+    env = create_env()
+    assert env.action_space.shape == (5,) and env.observation_space.shape == (25,)
+    assert float(env.action_space.low[0]) == -1.5 and float(env.action_space.high[0]) == 1.5
+    obs = env.reset()
+    assert obs.shape == (25,) and not obs.any()
+    case = json.load(open(os.path.join(os.path.dirname(GOLD), 'start_pos_merge.json')))[0]
+    assert (case['pre'], case['n']) == (500, 5)
+    assert [[env.k.vehicle.get_edge(v), env.k.vehicle.get_position(v)]
+            for v in env.k.vehicle.get_ids()] == [[e, pytest.approx(p, abs=1e-9)] for e, p in case['pos']]
+    assert env.k.vehicle.get_ids() == ['human_%d' % i for i in range(5)]
+    assert env.k.network.length() == pytest.approx(200 + 500 + 100 + 100 + 0.2 + 22.5)
+    # the same scenario on the oracle
+    groups = S.merge_groups()
+    initial = [(0,) + PL.merge_arm_position(e, p, 500) for e, p in case['pos']]
+    sim = S.merge_sim(groups=groups, initial=initial, num_rl=5, horizon=120,
+                      inflows=[(0, 0, 1800.0, 10.0, 1.0), (1, 0, 200.0, 10.0, 1.0),
+                               (0, 1, 100.0, 7.5, 1.0)])
+    rng = np.random.default_rng(3)
+    for s in range(120):
+        a = rng.uniform(-1.5, 1.5, 5)
+        o, r, d, _ = env.step(a)
+        o_obs, o_rew, o_done = sim.step(a)
+        assert close(o, o_obs) <= 1e-9, s
+        assert abs(r - o_rew) <= 1e-9 and d == o_done, s
+        names = ['flow_%d.%d' % ((v >> 24) - 1, v & 0xFFFFFF) if v >= (1 << 24) else 'human_%d' % v
+                 for v in sim.rl_veh]
+        assert env.rl_veh == names, s
+    assert d and len(env.rl_veh) >= 3
+    kv = env.k.vehicle
+    ids = kv.get_ids()
+    assert len(ids) == sim.num_vehicles and kv.get_rl_ids() == sorted(
+        n for n in ids if n.startswith('flow_1.'))
+    v0 = env.rl_veh[0]
+    s0 = sim.ids.index(sim.rl_veh[0])
+    assert kv.get_type(v0) == 'rl'
+    assert kv.get_x_by_id(v0) == pytest.approx(sim.g.x_abs(sim.arm[s0], sim.pos[s0]), abs=1e-9)
+    lead = kv.get_leader(v0)
+    assert (lead is None) == (sim.leader[s0] < 0)
+    if lead is not None:
+        assert kv.get_speed(lead) == pytest.approx(sim.vel[sim.leader[s0]], abs=1e-9)
+    assert kv.get_headway(v0) == pytest.approx(sim.headway[s0], abs=1e-9)
+    assert kv.get_inflow_rate(20) > 0 and kv.get_outflow_rate(20) >= 0
+    env.terminate()
+
+
+def test_merge_env_batched_and_error_cases():
+    import torch
+    from flow_b200 import flow_api as F
+    params = merge_flow_params(F, horizon=50)
+    create_env, _ = F.make_create_env(params, n_envs=64, dtype='f32')
+    env = create_env()
+    obs = env.reset()
+    assert tuple(obs.shape) == (64, 25)
+    for s in range(50):
+        obs, rew, done, _ = env.step(torch.zeros(64, 5, device='cuda'))
+    assert bool(done.all()) and float(rew.min()) >= 0.0
+    assert int(env.engine.counters[2].min()) > 0           # vehicles reached the end in every env
+    env.terminate()
+    bad = merge_flow_params(F)
+    bad['net'].additional_params['highway_lanes'] = 2
+    with pytest.raises(NotImplementedError):
+        F.make_create_env(bad)[0]()
+    bad = merge_flow_params(F)
+    bad['net'].inflows.add(veh_type='human', edge='center', vehs_per_hour=10, depart_speed=5)
+    with pytest.raises(NotImplementedError):
+        F.make_create_env(bad)[0]()
+    bad = merge_flow_params(F)
+    del bad['env'].additional_params['num_rl']
+    with pytest.raises(KeyError):
+        F.make_create_env(bad)[0]()
+    bad = merge_flow_params(F)
+    bad['network'] = F.RingNetwork
+    bad['net'] = F.NetParams(additional_params=dict(F.RING_NET_PARAMS))
+    with pytest.raises(NotImplementedError):
+        F.make_create_env(bad)[0]()

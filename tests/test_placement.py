@@ -149,3 +149,28 @@ def test_gpu_random_spacing_batched_and_stepping():
         env.step(None)
     assert int(env.engine.crash.sum()) == 0 and int(env.engine.time_counter[0]) == 70
     env.terminate()
+
+
+MERGE_CASES = json.load(open(os.path.join(G, 'start_pos_merge.json')))
+
+
+@pytest.mark.parametrize('c', MERGE_CASES, ids=['%d-%d-%d-n%d' % (c['pre'], c['merge'], c['post'], c['n'])
+                                                for c in MERGE_CASES])
+def test_even_placement_on_the_merge_network(c):
+    """tests/golden/start_pos_merge.json: the reference's gen_even_start_pos on its own
+    MergeNetwork edge tables."""
+    real, internal = PL.merge_edges(c['pre'], c['merge'], c['post'])
+    kw = c['kw']
+    pos, lane = PL.even_positions(real, internal, kw.get('x0', 0), kw.get('min_gap', 0),
+                                  kw.get('bunching', 0), c['n'])
+    assert [[e, p] for e, p in pos] == c['pos']              # bit for bit
+    assert lane == c['lane']
+    for e, p in pos:
+        arm, d = PL.merge_arm_position(e, p, c['pre'])
+        assert arm == (1 if e in ('inflow_merge', 'bottom') else 0) and d >= p
+
+
+def test_even_placement_refuses_an_overfull_network():
+    real, internal = PL.merge_edges(50, 10, 20)
+    with pytest.raises(ValueError):
+        PL.even_positions(real, internal, 0, 0, 0, 80)
