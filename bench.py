@@ -713,7 +713,8 @@ def run_b200(a):
         'env_steps_per_s': fused['env_steps'] / (fused['ms'] * 1e-3),
         'config': {'workload': info['workload'], 'envs_per_gpu': E,
                    'vehicles_per_env': info['n_slots'], 'idm_noise': a.noise,
-                   'speed_mode': a.speed_mode, 'fuse': info['fuse'],
+                   'speed_mode': a.speed_mode, 'fuse': info['fuse'], 'horizon': info['horizon'],
+                   'sims_per_step': info['sims_per_step'],
                    'reps': fused['reps'], 'timed_region_ms': fused['ms'],
                    'env_steps_timed_per_env': fused['steps'],
                    'timing': 'the K-step pass repeated `reps` times back to back (calibrated so the '

@@ -21,8 +21,9 @@
 // reaches the simulator model's desired gap s* for the depart speed.
 //
 // Mapping: one warp per env, slot s = lane + 32 r in insertion order (= departure order, which
-// is what the reference's rl_queue follows), state env-major. Leader search: every vehicle
-// scans the n published (u, arm) pairs in shared memory (n ~ 50 of the 2000 veh/h config).
+// is what the reference's rl_queue follows), state env-major. Leader search: previous slot of
+// the own arm + a bisection of the other arm's in-zone list (see update()); the all-pairs scan
+// only where the slot order is not the road order.
 #pragma once
 #include "fs_common.cuh"
 #include "fs_ring.cuh"
@@ -146,24 +147,93 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       }
     }
     __syncwarp();
+    // Slots are in departure order and nobody overtakes on its own arm, so an arm's vehicles
+    // normally sit in the slot array by descending u: the own-arm leader is the previous slot of
+    // the arm (ballot + clz), and the other arm only matters through its vehicles inside the
+    // zone, kept as two short sorted lists (ballot compaction into `ld`, arm 0 from the front,
+    // arm 1 from the back) that a vehicle inside the zone bisects. Anything else (initial
+    // vehicles placed in another order, states after a collision) takes the full scan below.
+    int pred[SLOTS];
+    int last0 = -1, last1 = -1, zn0 = 0, zn1 = 0, np0 = 0, np1 = 0;
+    bool sorted = true;
 #pragma unroll
     for (int r = 0; r < SLOTS; ++r) {
       const int s = lane_id + 32 * r;
-      int bj = -1; T bd = T(0);
-      if (s < n) {
-        const T ui = us[s];
-        const bool in_zone = ui >= z0;
-        for (int j = 0; j < n; ++j) {
-          const T uj = us[j];
-          if (j == s || !(uj > ui || (uj == ui && j < s))) continue;
-          const bool ok = (at[j] & 0xff) == arm[r] || uj >= LH || (in_zone && uj >= z0);
-          if (!ok) continue;
-          const T d = uj - ui;
-          if (bj < 0 || d < bd) { bj = j; bd = d; }
-        }
+      const bool on = s < n;
+      const T ui = on ? us[s] : T(0);
+      const unsigned mv = __ballot_sync(FULL, on);
+      const unsigned m1 = __ballot_sync(FULL, on && arm[r] != 0), m0 = mv & ~m1;
+      const unsigned mine_m = arm[r] ? m1 : m0, below = mine_m & ((1u << lane_id) - 1u);
+      pred[r] = below ? 32 * r + 31 - __clz(below) : (arm[r] ? last1 : last0);
+      if (on && pred[r] >= 0) sorted &= us[pred[r]] > ui;
+      if (m0) last0 = 32 * r + 31 - __clz(m0);
+      if (m1) last1 = 32 * r + 31 - __clz(m1);
+      const bool zin = on && ui >= z0;
+      const unsigned z1 = __ballot_sync(FULL, zin && arm[r] != 0);
+      const unsigned z0m = __ballot_sync(FULL, zin && arm[r] == 0);
+      const unsigned p1 = __ballot_sync(FULL, on && arm[r] != 0 && ui >= LH);
+      const unsigned p0 = __ballot_sync(FULL, on && arm[r] == 0 && ui >= LH);
+      if (zin) {
+        const unsigned lower = (1u << lane_id) - 1u;
+        if (arm[r]) ld[CAP - 1 - (zn1 + __popc(z1 & lower))] = s;
+        else ld[zn0 + __popc(z0m & lower)] = s;
       }
-      lead[r] = bj;
-      h[r] = bj >= 0 ? bd - cfg.types[at[bj] >> 8].length : T(1000);
+      zn0 += __popc(z0m); zn1 += __popc(z1); np0 += __popc(p0); np1 += __popc(p1);
+    }
+    sorted = __all_sync(FULL, sorted);
+    __syncwarp();
+    if (sorted) {
+#pragma unroll
+      for (int r = 0; r < SLOTS; ++r) {
+        const int s = lane_id + 32 * r;
+        int bj = -1; T bd = T(0);
+        if (s < n) {
+          const T ui = us[s];
+          bj = pred[r];
+          if (bj >= 0) bd = us[bj] - ui;
+          // other arm: nearest vehicle ahead inside the zone when this one is inside it too,
+          // else the last vehicle past the merge point
+          const int zn = arm[r] ? zn0 : zn1, np = arm[r] ? np0 : np1;
+          int c = np;
+          if (ui >= z0) {
+            int lo = 0, hi = zn;              // entries [0, lo) are ahead of this vehicle
+            while (lo < hi) {
+              const int mid = (lo + hi) >> 1;
+              const int j = arm[r] ? ld[mid] : ld[CAP - 1 - mid];
+              const T uj = us[j];
+              if (uj > ui || (uj == ui && j < s)) lo = mid + 1; else hi = mid;
+            }
+            c = lo;
+          }
+          if (c > 0) {
+            const int j = arm[r] ? ld[c - 1] : ld[CAP - 1 - (c - 1)];
+            const T d = us[j] - ui;
+            if (bj < 0 || d < bd || (d == bd && j < bj)) { bj = j; bd = d; }
+          }
+        }
+        lead[r] = bj;
+        h[r] = bj >= 0 ? bd - cfg.types[at[bj] >> 8].length : T(1000);
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < SLOTS; ++r) {
+        const int s = lane_id + 32 * r;
+        int bj = -1; T bd = T(0);
+        if (s < n) {
+          const T ui = us[s];
+          const bool in_zone = ui >= z0;
+          for (int j = 0; j < n; ++j) {
+            const T uj = us[j];
+            if (j == s || !(uj > ui || (uj == ui && j < s))) continue;
+            const bool ok = (at[j] & 0xff) == arm[r] || uj >= LH || (in_zone && uj >= z0);
+            if (!ok) continue;
+            const T d = uj - ui;
+            if (bj < 0 || d < bd) { bj = j; bd = d; }
+          }
+        }
+        lead[r] = bj;
+        h[r] = bj >= 0 ? bd - cfg.types[at[bj] >> 8].length : T(1000);
+      }
     }
     __syncwarp();
 #pragma unroll
@@ -172,9 +242,15 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       if (s < n) { ld[s] = lead[r]; hs[s] = h[r]; }
     }
     __syncwarp();
-    my_slot = -1;
-    if (my_ctrl >= 0)
-      for (int j = 0; j < n; ++j) if (is[j] == my_ctrl) { my_slot = j; break; }
+    my_slot = -1;          // row a of rl_veh: which slot carries its vehicle now
+    for (int a = 0; a < n_ctrl; ++a) {
+      const int cid = __shfl_sync(FULL, my_ctrl, a);
+#pragma unroll
+      for (int r = 0; r < SLOTS; ++r) {
+        const unsigned hit = __ballot_sync(FULL, lane_id + 32 * r < n && id[r] == cid);
+        if (hit && lane_id == a) my_slot = 32 * r + __ffs(hit) - 1;
+      }
+    }
   };
   update();
 
@@ -273,35 +349,42 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       {
         const bool keep = lane_id < n_ctrl && my_slot >= 0;
         const unsigned km = __ballot_sync(FULL, keep);
-        const int dst = __popc(km & ((1u << lane_id) - 1u));
-        int moved = -1;
+        if (km != (n_ctrl >= 32 ? FULL : (1u << n_ctrl) - 1u)) {   // a controlled vehicle left
+          const int dst = __popc(km & ((1u << lane_id) - 1u));
+          int moved = -1;
 #pragma unroll 1
-        for (int src = 0; src < 32; ++src) {      // lane dst takes the id of the dst-th kept row
-          const int idv = __shfl_sync(FULL, my_ctrl, src);
-          const int d = __shfl_sync(FULL, keep ? dst : -1, src);
-          if (d == lane_id) moved = idv;
-        }
-        n_ctrl = __popc(km);
-        my_ctrl = lane_id < n_ctrl ? moved : -1;
-        int base = n_ctrl;
-#pragma unroll
-        for (int r = 0; r < SLOTS; ++r) {
-          const int s = lane_id + 32 * r;
-          const bool w = s < n && ((rl_types >> ty[r]) & 1u) && sq[r] > hi_seq;
-          const unsigned wm = __ballot_sync(FULL, w);
-          const int row = w ? base + __popc(wm & ((1u << lane_id) - 1u)) : -1;
-          // hand (id, seq) of waiting vehicle -> row `row` if it fits
-#pragma unroll 1
-          for (unsigned m = wm; m; m &= m - 1) {
+          for (unsigned m = km; m; m &= m - 1) {    // lane dst takes the id of the dst-th kept row
             const int src = __ffs(m) - 1;
-            const int rw = __shfl_sync(FULL, row, src);
-            const int idv = __shfl_sync(FULL, id[r], src);
-            const int sv = __shfl_sync(FULL, sq[r], src);
-            if (rw < AG) { if (lane_id == rw) my_ctrl = idv; hi_seq = sv; }
+            const int idv = __shfl_sync(FULL, my_ctrl, src);
+            const int d = __shfl_sync(FULL, dst, src);
+            if (d == lane_id) moved = idv;
           }
-          base += __popc(wm);
+          n_ctrl = __popc(km);
+          my_ctrl = lane_id < n_ctrl ? moved : -1;
         }
-        n_ctrl = base < AG ? base : AG;
+        if (n_ctrl < AG) {                          // a row is free: the longest-waiting RL vehicles
+          int base = n_ctrl;
+#pragma unroll
+          for (int r = 0; r < SLOTS; ++r) {
+            const int s = lane_id + 32 * r;
+            const bool w = s < n && ((rl_types >> ty[r]) & 1u) && sq[r] > hi_seq;
+            const unsigned wm = __ballot_sync(FULL, w);
+            const int row = w ? base + __popc(wm & ((1u << lane_id) - 1u)) : -1;
+            // hand (id, seq) of waiting vehicle -> row `row` while rows are left
+#pragma unroll 1
+            for (unsigned m = wm; m; m &= m - 1) {
+              const int src = __ffs(m) - 1;
+              const int rw = __shfl_sync(FULL, row, src);
+              if (rw >= AG) break;
+              const int idv = __shfl_sync(FULL, id[r], src);
+              const int sv = __shfl_sync(FULL, sq[r], src);
+              if (lane_id == rw) my_ctrl = idv;
+              hi_seq = sv;
+            }
+            base += __popc(wm);
+          }
+          n_ctrl = base < AG ? base : AG;
+        }
       }
       tc += 1;
       // ---- move, exits (u >= end of 'center'), order-preserving ballot compaction

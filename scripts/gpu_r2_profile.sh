@@ -24,4 +24,5 @@ cap c2 ring1_hot
 cap c5 ring1_hot
 cap c3 ring_ml
 cap c4 highway_kernel
+cap mg merge_kernel
 ls -la gpurun_out | grep p2_ | head -30

@@ -16,7 +16,7 @@ CMD = 'python bench.py --no-cpu-baseline --only-fused --target-ms 5 --steps 20 -
 
 def short(name):
     for k in ('ring1_hot_kernel', 'ring1_fast_kernel', 'ring1_kernel', 'ring_reset_kernel',
-              'ring_ml_kernel', 'highway_kernel'):
+              'ring_ml_kernel', 'highway_kernel', 'merge_kernel'):
         if k in name:
             i = name.index(k)
             return name[i:name.index('(', i)] if '(' in name[i:] else name[i:]
@@ -48,9 +48,10 @@ if os.path.exists(ll):
             f.write('%s,"%s","%s","%s",%s\n' % (r[0], short(r[4]), r[7], r[8], r[-1]))
 
 # 2. full captures -> summary csv + per-env-step traffic / issue figures for bench.py
-KERNEL = {'c2': 'ring1_hot', 'c5': 'ring1_hot', 'c3': 'ring_ml', 'c4': 'highway_kernel'}
+KERNEL = {'c2': 'ring1_hot', 'c5': 'ring1_hot', 'c3': 'ring_ml', 'c4': 'highway_kernel',
+          'mg': 'merge_kernel'}
 traffic = {}
-for wl in ('c2', 'c5', 'c3', 'c4'):
+for wl in ('c2', 'c5', 'c3', 'c4', 'mg'):
     raw = os.path.join(G, 'p2_%s_raw.csv' % wl)
     plain = os.path.join(G, 'p2_plain_%s.json' % wl)
     if not (os.path.exists(raw) and os.path.exists(plain)):
@@ -71,6 +72,8 @@ for wl in ('c2', 'c5', 'c3', 'c4'):
         x = float(r[h.index(k)].replace(',', ''))
         return x * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}.get(u[h.index(k)], 1)
     env_steps = float(fuse) * E
+    # instruction counts are per SIMULATION step of an env (5 per Env.step on the merge, else 1)
+    sim_steps = env_steps * int(b['config'].get('sims_per_step', 1))
     veh = b['active_vehicles_per_env']
     winst = val('smsp__inst_executed.sum')
     tinst = val('smsp__thread_inst_executed.sum') if 'smsp__thread_inst_executed.sum' in h else \
@@ -79,8 +82,8 @@ for wl in ('c2', 'c5', 'c3', 'c4'):
         'dram_bytes_per_env_step': (val('dram__bytes_read.sum') + val('dram__bytes_write.sum')) / env_steps,
         'issue_active_pct': val('smsp__issue_active.avg.pct_of_peak_sustained_active'),
         'warps_active_pct': val('sm__warps_active.avg.pct_of_peak_sustained_active'),
-        'warp_inst_per_env_step': winst / env_steps,
-        'thread_inst_per_vehicle_step': tinst / env_steps / veh,
+        'warp_inst_per_env_step': winst / sim_steps,
+        'thread_inst_per_vehicle_step': tinst / sim_steps / veh,
         'fma_pipe_pct': val('sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active'),
         'alu_pipe_pct': val('sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active'),
         'xu_pipe_pct': val('sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active'),
