@@ -13,7 +13,8 @@ ROOT = os.path.dirname(_HERE)
 SO_PATH = os.path.join(_HERE, 'libflowstep.so')
 CSRC = os.path.join(_HERE, 'csrc')
 SOURCES = ['flowstep.cu', 'fs_fast_f32.cu', 'fs_fast_f64.cu', 'fs_ring_f32.cu', 'fs_ring_f64.cu',
-           'fs_ml_f32.cu', 'fs_ml_f64.cu', 'fs_hw_f32.cu', 'fs_hw_f64.cu', 'fs_mg_f32.cu', 'fs_mg_f64.cu']
+           'fs_ml_f32.cu', 'fs_ml_f64.cu', 'fs_hw_f32.cu', 'fs_hw_f64.cu', 'fs_mg_f32.cu', 'fs_mg_f64.cu',
+           'fs_f8_f32.cu', 'fs_f8_f64.cu']
 
 FS_NPARAM = 8
 FS_MAX_TYPES = 16
@@ -56,10 +57,11 @@ class FsConfig(C.Structure):
                 ('inflow_begin', C.c_double),
                 ('max_agents', C.c_int32), ('reserved0', C.c_int32),
                 ('merge_pre', C.c_double), ('merge_ramp', C.c_double),
-                ('merge_post', C.c_double), ('merge_zone', C.c_double)]
+                ('merge_post', C.c_double), ('merge_zone', C.c_double),
+                ('fig8_radius', C.c_double), ('fig8_zone', C.c_double)]
 
 
-FS_ABI_VERSION = 4
+FS_ABI_VERSION = 5
 FS_MAX_INFLOWS = 4
 FS_NOALLOC_SCRATCH_BYTES = 4 * 1024 * 1024
 

@@ -58,6 +58,7 @@ struct fs_engine {
   void* agent_reward = nullptr;  // T [E][A]
   bool ma_highway() const { return cfg.env_kind == FS_ENV_MA_HIGHWAY_PO; }
   bool merge() const { return cfg.topology == FS_TOPO_MERGE; }
+  bool fig8() const { return cfg.topology == FS_TOPO_FIGURE8; }
   int* seq = nullptr;          // merge: [E][CAP] departure order of the vehicle in each slot
   // fs_step_unfused: the k single-step launches of the last call, kept as an instantiated graph
   cudaGraphExec_t uf_exec = nullptr;
@@ -200,6 +201,14 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
        cfg->merge_zone < 0 || (cfg->env_flags & ~FS_ENVF_EVALUATE)))
     return fail(nullptr, FS_EINVAL, "fs_create: merge network needs merge_pre / merge_ramp / merge_post "
                                     "> 0, one lane per road, merge_zone >= 0, no env flag but evaluate");
+  if (cfg->topology == FS_TOPO_FIGURE8 &&
+      (cfg->env_kind != FS_ENV_ACCEL || cfg->n_lanes != 1 || !(cfg->fig8_radius > 0) ||
+       cfg->fig8_zone < 0 || cfg->fig8_zone > cfg->fig8_radius ||
+       !(cfg->fig8_radius > fmax(0.0, cfg->init_min_gap) + 5.0) || !(cfg->fig8_radius > 7.04) ||
+       (cfg->env_flags & ~FS_ENVF_EVALUATE)))
+    return fail(nullptr, FS_EINVAL, "fs_create: the figure-eight network runs AccelEnv on one lane, needs "
+                                    "fig8_radius > max(min_gap + 5, 7.04), 0 <= fig8_zone <= fig8_radius and no env "
+                                    "flag but evaluate");
   if ((cfg->env_flags & FS_ENVF_SORT_VEHICLES) &&
       (cfg->topology != FS_TOPO_RING ||
        (cfg->env_kind != FS_ENV_ACCEL && cfg->env_kind != FS_ENV_LANE_CHANGE_ACCEL &&
@@ -242,7 +251,7 @@ extern "C" int fs_create(const fs_config* cfg, fs_engine** out) {
   A(&e->time_counter, E * 4); A(&e->episode, E * 4);
   A(&e->obs, E * e->obs_dim * ts); A(&e->reward, E * ts);
   A(&e->stats, FS_STAT_STRIPES * 8 * sizeof(double)); A(&e->lengths_dev, E * sizeof(double));
-  e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY || e->merge();
+  e->env_major = e->multilane() || cfg->topology == FS_TOPO_HIGHWAY || e->merge() || e->fig8();
   if (e->env_major) A(&e->last_lc, V * E * 4);
   if (e->sort_on()) { A(&e->abs_pos, V * E * ts); A(&e->prev_pos, V * E * ts); A(&e->keys_valid, E); }
   if (e->merge()) {
@@ -319,6 +328,12 @@ static void fill_cfg(fs_engine* e, fs::Cfg<T>& c, const fs_vtype* types, int n_t
     c.mg_LH = (T)LH; c.mg_LM = (T)LM; c.mg_post = (T)g.merge_post;
     c.mg_zone = (T)(g.merge_zone > 0 ? g.merge_zone : g.merge_ramp + 22.5);
     c.mg_pre = (T)g.merge_pre; c.mg_ramp = (T)g.merge_ramp;
+  }
+  if (g.topology == FS_TOPO_FIGURE8) {
+    const fs::F8Geo q = fs::f8_geometry(g.fig8_radius);
+    c.f8_L = (T)q.L; c.f8_cA = (T)q.cA; c.f8_cB = (T)q.cB; c.f8_J = (T)q.J;
+    c.f8_zone = (T)(g.fig8_zone > 0 ? g.fig8_zone : g.fig8_radius);
+    for (int k = 0; k < 12; ++k) c.f8_start[k] = (T)q.start[k];
   }
   c.evaluate = (g.env_flags & FS_ENVF_EVALUATE) ? 1 : 0;
   c.ballistic = (g.env_flags & FS_ENVF_BALLISTIC) ? 1 : 0;
@@ -467,6 +482,13 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
         types[ta].sim_min_gap != types[tb].sim_min_gap) ok = false;
     e->ml_uniform = ok;
   }
+  if (e->fig8())
+    for (int t = 0; t < n_types; ++t) {
+      const int c = types[t].controller;
+      if (c == FS_CTRL_PI_SATURATION || c == FS_CTRL_LAC || c == FS_CTRL_BCM)
+        return fail(e, FS_EINVAL, "fs_set_types: PISaturation / LAC / BCM vehicles are not supported on "
+                                  "the figure-eight network (controller state / follower input)");
+    }
   if (e->merge()) {
     if (e->cfg.n_initial < 0 || e->cfg.n_initial > e->cfg.n_veh)
       return fail(e, FS_EINVAL, "fs_set_types: n_initial must be within the slot capacity");
@@ -640,6 +662,28 @@ static int launch_mg(fs_engine* e, const fs::StepArgs<T>& a) {
 }
 
 template <typename T>
+static fs::F8Bufs<T> f8_bufs(fs_engine* e) {
+  fs::F8Bufs<T> b;
+  b.pos = (T*)e->pos; b.vel = (T*)e->vel;
+  b.time_counter = e->time_counter; b.episode = e->episode; b.done = e->done; b.crash = e->crash;
+  b.obs = (T*)e->obs; b.reward = (T*)e->reward;
+  b.v_accel = (T*)e->accel; b.v_headway = (T*)e->headway;
+  b.v_leader = e->leader; b.v_follower = e->follower; b.stats = e->stats;
+  return b;
+}
+
+template <typename T>
+static int launch_f8(fs_engine* e, const fs::StepArgs<T>& a) {
+  const int E = e->cfg.n_envs, V = e->cfg.n_veh;
+  const int wpb = E <= 148 * 8 ? 1 : 4;
+  const int grid = (E + wpb - 1) / wpb;
+  const size_t smem = (size_t)wpb * fs::f8_smem_per_warp<T>(V);
+  FS_CUDA(e, fs_launch_f8<T>(V, grid, wpb * 32, smem, e->stream, cfg_of<T>(e), f8_bufs<T>(e), a));
+  e->launches++;
+  return FS_OK;
+}
+
+template <typename T>
 static int launch_hw(fs_engine* e, const fs::StepArgs<T>& a) {
   const int E = e->cfg.n_envs, CAP = e->cfg.n_veh;
   const int wpb = E <= 148 * 8 ? 1 : 4;
@@ -681,6 +725,7 @@ template <typename T>
 static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
   if (e->cfg.topology == FS_TOPO_HIGHWAY) return launch_hw<T>(e, a);
   if (e->merge()) return launch_mg<T>(e, a);
+  if (e->fig8()) return launch_f8<T>(e, a);
   const int V = e->cfg.n_veh, E = e->cfg.n_envs;
   if (e->multilane()) return launch_ml<T>(e, a);
   if (e->fast_ok) {
@@ -783,7 +828,7 @@ template <typename T>
 static int do_step(fs_engine* e, const void* actions, int k, void* obs_seq, void* reward_seq,
                    uint8_t* done_seq, const uint8_t* mask, int stats, int ignore_done) {
   const int S = e->cfg.sims_per_step;
-  if (S <= 1 || k == 0 || e->merge())      // the merge kernel loops over the sub-steps itself
+  if (S <= 1 || k == 0 || e->merge() || e->fig8())   // these kernels loop over the sub-steps themselves
     return do_step1<T>(e, actions, k, obs_seq, reward_seq, done_seq, mask, stats, ignore_done);
   const size_t E = e->cfg.n_envs, act_row = (size_t)e->act_dim * E, obs_row = E * e->obs_dim;
   for (int s = 0; s < k; ++s) {
@@ -911,6 +956,9 @@ static int do_reset(fs_engine* e, const uint8_t* mask_dev, const double* lengths
     if (e->merge())
       FS_CUDA(e, fs_launch_mg_reset<T>(E, e->stream, cfg_of<T>(e), mg_bufs<T>(e), mask_dev,
                                        e->cfg.n_initial, (T*)e->circ));
+    else if (e->fig8())
+      FS_CUDA(e, fs_launch_f8_reset<T>(E, e->stream, cfg_of<T>(e), f8_bufs<T>(e),
+                                       fs::f8_geometry(e->cfg.fig8_radius), mask_dev, (T*)e->circ));
     else if (e->cfg.topology == FS_TOPO_HIGHWAY)
       fs::highway_reset_kernel<T><<<(E + block - 1) / block, block, 0, e->stream>>>(
           cfg_of<T>(e), hw_bufs<T>(e), mask_dev, e->cfg.n_initial);
@@ -935,6 +983,12 @@ static int check_room(fs_engine* e, double L) {
   // _get_start_pos_util raises FatalFlowError when vehicles do not fit
   const fs_config& g = e->cfg;
   if (g.topology == FS_TOPO_MERGE) return FS_OK;   // initial vehicles are placed by the caller
+  if (g.topology == FS_TOPO_FIGURE8) {
+    const fs::F8Geo q = fs::f8_geometry(g.fig8_radius);
+    if (q.non_internal - fmax(0.0, g.bunching) - g.n_veh * (fmax(0.0, g.init_min_gap) + 5.0) < 0)
+      return fail(e, FS_EINVAL, "There is not enough space to place all vehicles in the network.");
+    return FS_OK;
+  }
   const double min_gap = fmax(0.0, g.init_min_gap), bunching = fmax(0.0, g.bunching);
   int ld = g.lanes_distribution;
   if (ld > g.n_lanes) ld = g.n_lanes;

@@ -49,6 +49,10 @@ struct Cfg {
   // FS_TOPO_MERGE: arm lengths up to the merge point (highway / ramp), the common edge, the
   // cross-arm look-ahead zone, the edge lengths they were built from (flowstep.cu fill_cfg)
   T mg_LH, mg_LM, mg_post, mg_zone, mg_pre, mg_ramp;
+  // FS_TOPO_FIGURE8: loop length, the two junction boxes, junction length, look-ahead zone and
+  // the starts of the 12 segments in driving order (even index = internal), fs::f8_geometry
+  T f8_L, f8_cA, f8_cB, f8_J, f8_zone;
+  T f8_start[12];
   int16_t evaluate;   // EnvParams.evaluate (AccelEnv reward = mean speed)
   int16_t ballistic;  // SumoParams.use_ballistic: x += (v_old + v_new)/2 dt instead of v_new dt
   TypeP<T> types[FS_MAX_TYPES];
@@ -56,6 +60,54 @@ struct Cfg {
   int16_t rl_index[FS_MAX_VEH];  // vehicle -> action slot, -1 if not RL
   int16_t pi_index[FS_MAX_VEH];  // vehicle -> PISaturation history slot, -1 if none
 };
+
+// FigureEightNetwork laid out as ONE loop (flow/networks/figure_eight.py:66-73, 217-263), in
+// double and in the operation order of oracle/figure8.py Figure8Geometry. Segments in driving
+// order: ':bottom' bottom ':center_1' top ':top' upper_ring ':right' right ':center_0' left
+// ':left' lower_ring (even index = internal edge).
+// Python's built-in sum() over floats (CPython >= 3.12: Neumaier-compensated; the reference's
+// _get_start_pos_util and non_internal_length call it): running sum t, compensation c, t + c.
+struct PySum {
+  double t = 0.0, c = 0.0;
+  __host__ __device__ void push(double x) {
+    const double n = t + x;
+    c += fabs(t) >= fabs(x) ? (t - n) + x : (x - n) + t;
+    t = n;
+  }
+  __host__ __device__ double value() const { return c != 0.0 ? t + c : t; }
+};
+
+struct F8Geo {
+  double start[12], len[12];
+  double L, cA, cB, J, non_internal;
+  double aimsun;   // start of the network's 'right_to_left' entry (see fig8_reset_kernel)
+};
+inline F8Geo f8_geometry(double r) {
+  F8Geo g;
+  const double rel = r * 3.141592653589793 / 2.0, il = 2 * r, jl = 2.9 + 3.3 * 1, sp = 0.28,
+               re3 = 3 * rel;
+  const double st[12] = {0.0, sp, il / 2 + sp, il / 2 + jl + sp, il + jl + sp, il + jl + 2 * sp,
+                         il + re3 + jl + 2 * sp, il + re3 + jl + 3 * sp,
+                         3.0 / 2 * il + re3 + jl + 3 * sp, 3.0 / 2 * il + re3 + 2 * jl + 3 * sp,
+                         2 * il + re3 + 2 * jl + 3 * sp, 2 * il + re3 + 2 * jl + 4 * sp};
+  // edge LENGTHS of the two ring edges are 3 r pi / 2 (specify_edges), their starts use
+  // 3 * (r pi / 2) (specify_edge_starts): an ulp apart, both kept as the reference has them
+  const double rl = 3 * r * 3.141592653589793 / 2.0;
+  const double ln[12] = {sp, r, jl, r, sp, rl, sp, r, jl, r, sp, rl};
+  for (int k = 0; k < 12; ++k) { g.start[k] = st[k]; g.len[k] = ln[k]; }
+  g.L = 2 * il + 2 * re3 + 2 * jl + 4 * sp;
+  g.cA = il / 2 + sp;
+  g.cB = 3.0 / 2 * il + re3 + jl + 3 * sp;
+  g.J = jl;
+  g.aimsun = +jl + 3 * sp;
+  // get_edge_list order of the harness = specify_edges order: bottom, top, right, left,
+  // upper_ring, lower_ring, summed like Python's sum()
+  PySum ni;
+  const int order[6] = {1, 3, 7, 9, 5, 11};
+  for (int q = 0; q < 6; ++q) ni.push(ln[order[q]]);
+  g.non_internal = ni.value();
+  return g;
+}
 
 // ---------------------------------------------------------------- helpers
 __device__ __forceinline__ double* stat_stripe(double* stats) {

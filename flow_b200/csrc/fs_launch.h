@@ -1,5 +1,5 @@
 // fs_launch.h — launch entry points of the per-kernel-family, per-dtype translation units
-// (fs_fast_*.cu, fs_ring_*.cu, fs_ml_*.cu, fs_hw_*.cu): the kernel templates are instantiated
+// (fs_fast_*.cu, fs_ring_*.cu, fs_ml_*.cu, fs_hw_*.cu, fs_mg_*.cu, fs_f8_*.cu): the kernel templates are instantiated
 // there so that the families compile in parallel; flowstep.cu only sees these declarations.
 #pragma once
 #include <cuda_runtime.h>
@@ -9,6 +9,7 @@
 #include "fs_multilane.cuh"
 #include "fs_highway.cuh"
 #include "fs_merge.cuh"
+#include "fs_fig8.cuh"
 
 cudaError_t fs_launch_fast22_f32(int shape, int variant, int n_envs, cudaStream_t st,
                                  const fs::FastP<float>& c, const fs::RingBufs<float>& b,
@@ -41,3 +42,10 @@ cudaError_t fs_launch_mg(int cap, int grid, int block, size_t smem, cudaStream_t
 template <typename T>
 cudaError_t fs_launch_mg_reset(int E, cudaStream_t st, const fs::Cfg<T>& c, const fs::MgBufs<T>& b,
                                const uint8_t* mask, int n_initial, T* length);
+// figure-eight network (fs_fig8.cuh)
+template <typename T>
+cudaError_t fs_launch_f8(int V, int grid, int block, size_t smem, cudaStream_t st,
+                         const fs::Cfg<T>& c, const fs::F8Bufs<T>& b, const fs::StepArgs<T>& a);
+template <typename T>
+cudaError_t fs_launch_f8_reset(int E, cudaStream_t st, const fs::Cfg<T>& c, const fs::F8Bufs<T>& b,
+                               const fs::F8Geo& g, const uint8_t* mask, T* length);

@@ -12,7 +12,7 @@ from . import _lib
 
 # ---- constants mirrored from include/flowstep.h ----------------------------
 F32, F64 = 0, 1
-TOPO_RING, TOPO_HIGHWAY, TOPO_MERGE = 0, 1, 2
+TOPO_RING, TOPO_HIGHWAY, TOPO_MERGE, TOPO_FIGURE8 = 0, 1, 2, 3
 ENV_ACCEL, ENV_WAVE_ATTENUATION, ENV_WAVE_ATTENUATION_PO, \
     ENV_LANE_CHANGE_ACCEL, ENV_LANE_CHANGE_ACCEL_PO, ENV_HIGHWAY, \
     ENV_MA_WAVE_ATTENUATION_PO, ENV_MA_ACCEL_PO, ENV_MA_HIGHWAY_PO, ENV_MERGE_PO = range(10)
@@ -104,7 +104,8 @@ class Engine:
                         inflow_depart_speed=0.0, inflow_type=0, collision_min_gap=0,
                         record_views=0, lc_corrected=0, n_initial=0, inflow_begin=1.0,
                         evaluate=0, sort_vehicles=0, use_ballistic=0, max_agents=0,
-                        merge_pre=0.0, merge_ramp=0.0, merge_post=0.0, merge_zone=0.0)
+                        merge_pre=0.0, merge_ramp=0.0, merge_post=0.0, merge_zone=0.0,
+                        fig8_radius=0.0, fig8_zone=0.0)
         # [(vtype, vehs_per_hour, depart_speed, begin[, end[, probability[, arm]]]), ...]
         inflows = cfg.pop('inflows', None)
         unknown = set(cfg) - set(defaults)

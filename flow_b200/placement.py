@@ -214,3 +214,41 @@ def merge_edge_of(arm, p, pre, merge, post):
     if p < I + 0.1 + mid + 22.5:
         return ':center', p - (I + 0.1 + mid)
     return 'center', p - (I + 0.1 + mid + 22.5)
+
+
+# ---- the figure-eight loop -------------------------------------------------------------------
+def figure8_edges(radius, placement_table=True):
+    """([(name, start, length)] real edges in specify_edges order, [(name, start)] internal edges)
+    of a one-lane FigureEightNetwork (flow/networks/figure_eight.py:66-73, 120-176, 217-263).
+    placement_table: keep the two entries the network lists "for aimsun" ('bottom_to_top' at the
+    start of ':center_1', 'right_to_left' at 6.2 + 3 * 0.28 = 7.04 m). gen_even_start_pos reads
+    them through get_edge like any internal edge, so on the reference every x from 7.04 m to the
+    end of the first junction pass is moved to the start of 'top'."""
+    import math
+    r = float(radius)
+    rel, il, jl, sp = r * math.pi / 2., 2 * r, 2.9 + 3.3 * 1, 0.28
+    real = [('bottom', sp, il / 2), ('top', il / 2 + jl + sp, il / 2),
+            ('right', il + 3 * rel + jl + 3 * sp, il / 2),
+            ('left', 3 / 2 * il + 3 * rel + 2 * jl + 3 * sp, il / 2),
+            ('upper_ring', il + jl + 2 * sp, 3 * r * math.pi / 2.),
+            ('lower_ring', 2 * il + 3 * rel + 2 * jl + 4 * sp, 3 * r * math.pi / 2.)]
+    internal = [(':bottom', 0), (':center_1', il / 2 + sp), (':top', il + jl + sp),
+                (':right', il + 3 * rel + jl + 2 * sp),
+                (':center_0', 3 / 2 * il + 3 * rel + jl + 3 * sp),
+                (':left', 2 * il + 3 * rel + 2 * jl + 3 * sp)]
+    if placement_table:
+        internal += [('bottom_to_top', il / 2 + sp), ('right_to_left', + jl + 3 * sp)]
+    return real, internal
+
+
+def figure8_edge_of(s, radius):
+    """(edge name as SUMO reports it, position on it) of loop coordinate s."""
+    real, internal = figure8_edges(radius, placement_table=False)
+    total = sorted([(n, st) for n, st, _ in real] + list(internal), key=lambda t: t[1])
+    name, start = total[0]
+    for n, st in total:
+        if s >= st:
+            name, start = n, st
+    if name in (':bottom', ':top', ':right', ':left'):
+        name += '_0'
+    return name, s - start

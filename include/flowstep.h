@@ -50,7 +50,7 @@
 extern "C" {
 #endif
 
-#define FS_ABI_VERSION 4
+#define FS_ABI_VERSION 5
 
 /* error codes */
 #define FS_OK 0
@@ -76,6 +76,18 @@ extern "C" {
                            * distance travelled on that arm. SUMO's junction is RESTATED:
                            * both arms on one axis aligned at the merge point, cross-arm car following
                            * inside merge_zone, collision only on a shared road. */
+
+#define FS_TOPO_FIGURE8 3 /* FigureEightNetwork (flow/networks/figure_eight.py), one lane: ONE closed loop
+                           * of length 4 r + 3 pi r + 2 * 6.2 + 4 * 0.28 that passes the centre
+                           * junction twice (northbound bottom -> top, westbound right -> left);
+                           * `pos` is the loop coordinate (0 = start of ':bottom'). Runs FS_ENV_ACCEL
+                           * (singleagent_figure_eight.py); fs_reset places with gen_even_start_pos
+                           * over the loop's edges. Controllers give no command on internal edges
+                           * (base_controller.py:96-99), the simulator model drives there. SUMO's
+                           * junction is RESTATED: the crossing is a merge followed by a
+                           * diverge - inside fig8_zone before the junction box a vehicle also follows
+                           * the vehicles of the other pass that are closer to / inside the box;
+                           * collision at the crossing = overlapping while both bodies are in the box. */
 
 /* environment front: selects observation + reward */
 #define FS_ENV_ACCEL 0             /* AccelEnv: obs 2V, desired_velocity            */
@@ -221,6 +233,9 @@ typedef struct fs_config {
   /* FS_TOPO_MERGE (net_params.additional_params of MergeNetwork); merge_zone = metres before the
    * merge point in which vehicles of the two arms follow one another (0: merge_length + 22.5) */
   double merge_pre, merge_ramp, merge_post, merge_zone;
+  /* FS_TOPO_FIGURE8: radius_ring of the network; fig8_zone = metres before the junction box in
+   * which a vehicle regards the other pass (0: the approach edge = fig8_radius; <= fig8_radius) */
+  double fig8_radius, fig8_zone;
 } fs_config;
 
 /* one <flow> of the open highway (InFlows.add: veh_type, vehs_per_hour | period | probability,

@@ -523,6 +523,37 @@ def start_pos_merge():
     json.dump(out, open(os.path.join(HERE, 'start_pos_merge.json'), 'w'), indent=1)
 
 
+def figure8():
+    """AccelEnv on FigureEightNetwork (singleagent_figure_eight.py: 13 IDM + 1 RL, radius 30):
+    the reference's gen_even_start_pos on its own network tables, then 600 steps of the
+    reference's IDMController.get_action (junction guard included), AccelEnv._apply_rl_actions /
+    get_state / compute_reward and get_x on the restated loop (RefFigure8)."""
+    import flow.controllers as RC
+    from .ref_harness import RefFigure8, ref_figure8_start_positions
+    from tests.scenarios import figure8_sim, FIGURE8
+    cases = [dict(radius=30, n=14, kw={}), dict(radius=50, n=22, kw=dict(x0=3.0, min_gap=1.0)),
+             dict(radius=30, n=40, kw=dict(bunching=20)), dict(radius=20, n=1, kw={})]
+    out = []
+    for c in cases:
+        pos, xs = ref_figure8_start_positions(c['radius'], c['n'], **c['kw'])
+        out.append(dict(c, pos=[[e, p] for e, p in pos], x=xs))
+    json.dump(out, open(os.path.join(HERE, 'start_pos_figure8.json'), 'w'), indent=1)
+    sim = figure8_sim(positions=out[0]['x'])
+    cf = dict(speed_mode='obey_safe_speed', decel=1.5)
+    ref = RefFigure8(sim, [('human', RC.IDMController, {}, cf, 13), ('rl', 'rl', {}, cf, 1)])
+    rng = np.random.default_rng(2)
+    A, O, R, D, P = [], [], [], [], [np.array(sim.pos)]
+    for k in range(FIGURE8['horizon']):
+        act = rng.uniform(-0.6, 1.2, 1)
+        obs, rew, done = ref.step(act)
+        A.append(act); O.append(obs); R.append(rew); D.append(done); P.append(np.array(sim.pos))
+        if done:
+            break
+    np.savez_compressed(os.path.join(HERE, 'figure8.npz'), actions=np.array(A), obs=np.array(O),
+                        reward=np.array(R), done=np.array(D), pos=np.array(P),
+                        vel_final=np.array(sim.vel))
+
+
 def merge():
     """MergePOEnv: the reference's own _apply_rl_actions / additional_command / get_state /
     compute_reward (RefMerge) on the restated merge network, 300 Env.steps of 5 simulation steps;
@@ -562,6 +593,7 @@ def main():
     ring_c1(); ring_c2(); ring_c2_speed_mode(); ring_c3(); ring_c3_po(); ring_sorted(); ring_zoo(); ring_ma(); ring_ma_accel(); start_pos(); start_pos_stochastic(); start_pos_merge()
     highway_ma()
     merge()
+    figure8()
     sumo_fixture()
     print('golden vectors written to', HERE)
 

@@ -148,6 +148,17 @@ def ref_merge_start_positions(pre, merge, post, num_vehicles, **init_kw):
     return [(e, float(p)) for e, p in pos], list(lane)
 
 
+def ref_figure8_start_positions(radius, num_vehicles, **init_kw):
+    """[(edge, position)] from the reference's gen_even_start_pos on its own FigureEightNetwork."""
+    from flow.networks.figure_eight import FigureEightNetwork
+    from flow.core.params import NetParams, VehicleParams
+    net = FigureEightNetwork('figure8', VehicleParams(), NetParams(additional_params={
+        'radius_ring': radius, 'lanes': 1, 'speed_limit': 30, 'resolution': 40}))
+    en = _EdgeNet(net)
+    pos, lane = en.gen_even_start_pos(InitialConfig(**init_kw), num_vehicles)
+    return [(e, float(p)) for e, p in pos], [float(en.get_x(e, p)) for e, p in pos]
+
+
 class _Veh:
     """The getter surface of TraCIVehicle the controllers/rewards call,
     string ids in, backed by arrays."""
@@ -758,3 +769,116 @@ class RefMerge:
         rew = float(self._cls.compute_reward(self, rl_actions, fail=sim.crash))
         return obs, rew, sim.done
 
+
+
+class RefFigure8:
+    """AccelEnv on FigureEightNetwork with the REFERENCE's code wherever the reference has code:
+    the controllers' get_action (incl. the internal-edge guard, base_controller.py:96-99, fed with
+    SUMO-style edge ids), AccelEnv._apply_rl_actions / get_state / compute_reward, get_x through
+    TraCIKernelNetwork.get_x on the network's own edge-start tables. SUMO's part (move, loop and
+    crossing leaders, collision, the model that drives un-commanded vehicles) is the restatement
+    oracle/figure8.py, which this harness steps through its `commanded` hook."""
+
+    def __init__(self, sim, groups, max_accel=3, max_decel=3, clip_actions=True, evaluate=False):
+        """groups: [(name, controller class or 'rl', ctrl kwargs, SumoCarFollowingParams kwargs,
+        count)] in the order of sim.type_of."""
+        from flow.networks.figure_eight import FigureEightNetwork
+        from flow.core.params import NetParams, VehicleParams
+        from flow.core.kernel.network.traci import TraCIKernelNetwork
+        self.sim = sim
+        net = FigureEightNetwork('figure8', VehicleParams(), NetParams(additional_params={
+            'radius_ring': sim.g.r, 'lanes': 1, 'speed_limit': sim.speed_limit, 'resolution': 40}))
+        self.ids, self.ctrl, self.rl_idx = [], [], []
+        for name, cls, kw, cf_kw, n in groups:
+            for q in range(n):
+                vid = '%s_%d' % (name, q)
+                if cls == 'rl':
+                    self.rl_idx.append(len(self.ids))
+                    self.ctrl.append(None)
+                else:
+                    self.ctrl.append(cls(vid, car_following_params=SumoCarFollowingParams(**cf_kw), **kw))
+                self.ids.append(vid)
+        self.index = {v: i for i, v in enumerate(self.ids)}
+        self.sim_step = sim.dt
+        self.env_params = EnvParams(
+            horizon=sim.horizon, clip_actions=clip_actions, evaluate=evaluate, additional_params={
+                'max_accel': max_accel, 'max_decel': max_decel, 'target_velocity': sim.target_velocity,
+                'sort_vehicles': False})
+        h = self
+
+        class Nw:
+            edgestarts = list(net.edge_starts)
+            internal_edgestarts = list(net.internal_edge_starts)
+            total_edgestarts = sorted(edgestarts + internal_edgestarts, key=lambda t: t[1])
+            total_edgestarts_dict = dict(total_edgestarts)
+            internal_edgestarts_dict = dict(internal_edgestarts)
+            get_x = TraCIKernelNetwork.get_x
+
+            def max_speed(self):
+                return h.sim.speed_limit
+
+            def length(self):
+                return h.sim.g.L
+
+        class V(_Veh):
+            def get_edge(self, vid, error=""):
+                # SUMO's ids: a junction's internal edges are ':<node>_<k>'. The centre junction's
+                # two passes are ':center_1' / ':center_0' (the keys the network lists); the four
+                # plain nodes carry one internal edge each, ':<node>_0'
+                name = h.sim.g.segment(h.sim.pos[self._i(vid)])[0]
+                return name + '_0' if name in h.sim.g.start_only else name
+
+            def get_position(self, vid, error=-1001):
+                s = h.sim.pos[self._i(vid)]
+                return s - h.sim.g.segment(s)[1]
+
+            def get_x_by_id(self, vid):
+                return h.k.network.get_x(self.get_edge(vid), self.get_position(vid))
+
+            def get_length(self, vid, error=-1001):
+                return h.sim.length_of(self._i(vid))
+
+            def apply_acceleration(self, veh_ids, acc):
+                for vid, a in zip(veh_ids, acc):
+                    if a is not None:
+                        h.commanded[self._i(vid)] = float(a)
+
+        self.k = type('K', (), {})()
+        self.k.vehicle, self.k.network = V(self), Nw()
+        self.commanded = {}
+        self._view()
+
+    # arrays the _Veh getters read: what the controllers are meant to see
+    def _view(self):
+        from oracle.figure8 import _ControlView
+        sim = self.sim
+        self.vel, self.pos, self.lane = sim.vel, sim.pos, [0] * len(self.ids)
+        self.leader, self.follower = sim.leader, sim.follower
+        self.headway = _ControlView(sim).headway
+
+    sorted_ids = property(lambda self: list(self.ids))
+
+    def step(self, rl_actions):
+        """Env.step (flow/envs/base.py:294-412) around the restated simulator."""
+        sim = self.sim
+        if rl_actions is not None and self.env_params.clip_actions:
+            rl_actions = np.clip(rl_actions, -abs(self.env_params.additional_params['max_decel']),
+                                 self.env_params.additional_params['max_accel'])
+        for _ in range(sim.sims_per_step):
+            self.commanded = {}
+            self._view()
+            for i, c in enumerate(self.ctrl):        # base.py:329-339
+                if c is not None:
+                    a = c.get_action(self)
+                    if a is not None:
+                        self.commanded[i] = float(a)
+            if rl_actions is not None:
+                AccelEnv._apply_rl_actions(self, rl_actions)
+            sim._sim_step(None, commanded=self.commanded)
+            if sim.crash:
+                break
+        sim.done = sim.crash or sim.time_counter >= sim.sims_per_step * (sim.warmup_steps + sim.horizon)
+        self._view()
+        obs = np.asarray(AccelEnv.get_state(self), dtype=float)
+        rew = float(AccelEnv.compute_reward(self, rl_actions, fail=sim.crash))
+        return obs, rew, sim.done

@@ -191,3 +191,42 @@ def merge_reset(eng, initial):
         pos[i], arm[i] = p, a
     eng.set_state(pos=pos, lane=arm)
     return eng.reset_stage(eng.RESET_WARMUP)
+
+
+# figure-eight network under AccelEnv (tests/golden/figure8.npz) -------------------------------
+FIGURE8 = dict(radius=30.0, dt=0.1, horizon=600, target_velocity=20.0, speed_limit=30.0,
+               act_lo=-3.0, act_hi=3.0)
+
+
+def figure8_groups(n_human=13, n_rl=1, noise=0.0, speed_mode=1):
+    """singleagent_figure_eight.py: IDM humans and one RL vehicle, 'obey_safe_speed', decel 1.5"""
+    return [vt('IDM', n_human, noise=noise, speed_mode=speed_mode, max_decel=1.5),
+            vt('RL', n_rl, speed_mode=speed_mode, max_decel=1.5)]
+
+
+def figure8_sim(groups=None, positions=None, **over):
+    from oracle import figure8 as F8
+    c = dict(FIGURE8, **over)
+    groups = groups or figure8_groups()
+    type_of = [t for t, g in enumerate(groups) for _ in range(g['count'])]
+    return F8.Figure8Sim(oracle_types(groups), type_of, c['radius'], positions, dt=c['dt'],
+                         speed_limit=c['speed_limit'], target_velocity=c['target_velocity'],
+                         horizon=c['horizon'], warmup_steps=c.get('warmup_steps', 0),
+                         sims_per_step=c.get('sims_per_step', 1), zone=c.get('zone'),
+                         act_lo=c['act_lo'], act_hi=c['act_hi'],
+                         clip_actions=c.get('clip_actions', True), evaluate=c.get('evaluate', False))
+
+
+def figure8_engine(n_envs, dtype='f64', groups=None, **over):
+    from flow_b200 import engine as EN
+    c = dict(FIGURE8, **over)
+    groups = groups or figure8_groups()
+    type_of = [t for t, g in enumerate(groups) for _ in range(g['count'])]
+    return EN.Engine(engine_types(groups), type_of, n_envs, dtype=dtype, topology=EN.TOPO_FIGURE8,
+                     env_kind=EN.ENV_ACCEL, fig8_radius=c['radius'], fig8_zone=c.get('zone') or 0.0,
+                     sim_step=c['dt'], speed_limit=c['speed_limit'], horizon=c['horizon'],
+                     warmup_steps=c.get('warmup_steps', 0), sims_per_step=c.get('sims_per_step', 1),
+                     target_velocity=c['target_velocity'], act_lo=c['act_lo'], act_hi=c['act_hi'],
+                     clip_actions=int(c.get('clip_actions', True)), evaluate=int(c.get('evaluate', False)),
+                     x0=c.get('x0', 0.0), init_min_gap=c.get('min_gap', 0.0), bunching=c.get('bunching', 0.0),
+                     record_views=1, seed=over.get('seed', 0))

@@ -25,7 +25,7 @@ def test_library_builds_and_exports_header_symbols():
     assert declared == bound, declared ^ bound
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.fs_abi_version() == _lib.FS_ABI_VERSION == 4
+    assert lib.fs_abi_version() == _lib.FS_ABI_VERSION == 5
 
 
 def test_struct_layouts_match_header():
