@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — env-steps/s and vehicle-steps/s of the batched step path (BASELINE.json metric).
 
-  python bench.py --gpus N --steps K --warmup W [--workload c2|c5|c3|c4|ma|mah|mg] [--dtype f32|f64]
+  python bench.py --gpus N --steps K --warmup W [--workload c2|c5|c3|c4|ma|mah|mg|f8] [--dtype f32|f64]
   python bench.py --impl reference ...     # CPU arm: the reference's own code on the host cores
 
 A "step" is one Env.step of EVERY environment of the batch (E per GPU). Workload c2 (default,
@@ -69,7 +69,7 @@ def parse(argv=None):
     ap.add_argument('--steps', type=int, default=3000)
     ap.add_argument('--warmup', type=int, default=300)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4', 'mah', 'mg'])
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5', 'ma', 'c3', 'c4', 'mah', 'mg', 'f8'])
     ap.add_argument('--fuse', type=int, default=0,
                     help='steps per fused launch; 0 = per workload: 100 (what BASELINE.json states '
                          'for c5), 500 for the 4096-env rings c2 / ma (their 100-step launch lasts '
@@ -372,7 +372,7 @@ def ncu_profile(workload, dtype):
 
 
 KERNEL_OF = {'ma': 'ring1_fast_kernel', 'c3': 'ring_ml_kernel', 'c4': 'highway_kernel',
-             'mah': 'highway_kernel', 'mg': 'merge_kernel'}
+             'mah': 'highway_kernel', 'mg': 'merge_kernel', 'f8': 'fig8_kernel'}
 
 
 class Leg:

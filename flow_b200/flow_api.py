@@ -480,10 +480,21 @@ class MergeNetwork(Network):
     TOPOLOGY = EN.TOPO_MERGE
 
 
+FIGURE_EIGHT_NET_PARAMS = {'radius_ring': 30, 'lanes': 1, 'speed_limit': 30, 'resolution': 40}
+
+
+class FigureEightNetwork(Network):
+    """flow/networks/figure_eight.py:22-263: two rings joined by an intersection - one closed loop
+    that passes the centre junction twice. One lane."""
+    ADDITIONAL = FIGURE_EIGHT_NET_PARAMS
+    TOPOLOGY = EN.TOPO_FIGURE8
+
+
 _NET_BY_NAME = {'RingNetwork': RingNetwork, 'HighwayNetwork': HighwayNetwork,
-                'MergeNetwork': MergeNetwork, 'LoopScenario': RingNetwork,
-                'RingScenario': RingNetwork, 'HighwayScenario': HighwayNetwork,
-                'MergeScenario': MergeNetwork}
+                'MergeNetwork': MergeNetwork, 'FigureEightNetwork': FigureEightNetwork,
+                'LoopScenario': RingNetwork, 'RingScenario': RingNetwork,
+                'HighwayScenario': HighwayNetwork, 'MergeScenario': MergeNetwork,
+                'Figure8Scenario': FigureEightNetwork, 'FigureEightScenario': FigureEightNetwork}
 
 
 # =============================================================================
@@ -682,6 +693,18 @@ def compile_spec(env_cls, env_params, sim_params, network, seed=None):
         if room < 0:
             raise FatalFlowError('There is not enough space to place all vehicles in the '
                                  'network.')
+    elif network.TOPOLOGY == EN.TOPO_FIGURE8:
+        if env_cls.KIND != EN.ENV_ACCEL or n_lanes != 1 or sort_on:
+            raise NotImplementedError('figure eight: AccelEnv on one lane, sort_vehicles False')
+        if ini.spacing != 'uniform' or ini.perturbation > 0:
+            raise NotImplementedError('figure eight: the even initial placement only')
+        from . import placement as PL
+        try:      # network/base.py:599-605: no room -> the reference aborts the run
+            PL.even_positions(*PL.figure8_edges(float(net['radius_ring'])), ini.x0, ini.min_gap,
+                              ini.bunching, len(ids))
+        except ValueError as exc:
+            raise FatalFlowError(str(exc))
+        kw.update(fig8_radius=float(net['radius_ring']))
     elif merge:
         pre, ramp, post = (float(net[k]) for k in ('pre_merge_length', 'merge_length',
                                                    'post_merge_length'))
@@ -823,7 +846,20 @@ class _VehicleKernel:
         p = self._get('pos', veh_id, None)
         return None if p is None else (int(self._get('lane', veh_id, 0)), p)
 
+    def _fig8_radius(self):
+        return float(self._env.net_params.additional_params['radius_ring'])
+
     def get_x_by_id(self, veh_id):
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            # node slots report their start, everything else start + position (network/traci.py:273-289)
+            if isinstance(veh_id, (list, tuple, np.ndarray)):
+                return [self.get_x_by_id(v) for v in veh_id]
+            from . import placement as PL
+            s = self._get('pos', veh_id, None)
+            if s is None:
+                return -1001
+            name, p = PL.figure8_edge_of(s, self._fig8_radius())
+            return s - p if name.endswith('_0') and not name.startswith(':center') else (s - p) + p
         if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
             if isinstance(veh_id, (list, tuple, np.ndarray)):
                 return [self.get_x_by_id(v) for v in veh_id]
@@ -853,6 +889,9 @@ class _VehicleKernel:
         x = self._get('pos', veh_id, None)
         if x is None:
             return error
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            from . import placement as PL
+            return PL.figure8_edge_of(x, self._fig8_radius())[0]
         if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
             from . import placement as PL
             return PL.merge_edge_of(self._arm_pos(veh_id)[0], x, *self._merge_lengths())[0]
@@ -865,6 +904,9 @@ class _VehicleKernel:
         x = self._get('pos', veh_id, None)
         if x is None:
             return error
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            from . import placement as PL
+            return PL.figure8_edge_of(x, self._fig8_radius())[1]
         if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
             from . import placement as PL
             return PL.merge_edge_of(self._arm_pos(veh_id)[0], x, *self._merge_lengths())[1]
@@ -925,6 +967,8 @@ class _NetworkKernel:
             return self.length() - 4 * RING_JUNCTION_LENGTH
         if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
             return self.length() - (2 * 0.1 + 22.5)
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            return self.length() - (2 * 6.2 + 4 * 0.28)
         return self.length()
 
     def max_speed(self):
@@ -941,6 +985,8 @@ class _NetworkKernel:
             return ['bottom', 'right', 'top', 'left']
         if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
             return ['inflow_highway', 'left', 'inflow_merge', 'bottom', 'center']
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            return ['bottom', 'top', 'right', 'left', 'upper_ring', 'lower_ring']
         return ['highway_0']
 
     def get_junction_list(self):
@@ -948,6 +994,8 @@ class _NetworkKernel:
             return [':right_0', ':top_0', ':left_0', ':bottom_0']
         if self._env.network.TOPOLOGY == EN.TOPO_MERGE:
             return [':left', ':bottom', ':center']
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            return [':bottom_0', ':center_1', ':top_0', ':right_0', ':center_0', ':left_0']
         return []
 
     def edge_length(self, edge):
@@ -957,6 +1005,12 @@ class _NetworkKernel:
                     ':center': 22.5, 'left': float(net['pre_merge_length']),
                     'bottom': float(net['merge_length']),
                     'center': float(net['post_merge_length'])}[edge]
+        if self._env.network.TOPOLOGY == EN.TOPO_FIGURE8:
+            from . import placement as PL
+            r = float(self._env.network.net_params.additional_params['radius_ring'])
+            if edge.startswith(':'):
+                return 6.2 if edge.startswith(':center') else 0.28
+            return {n: ln for n, _, ln in PL.figure8_edges(r)[0]}[edge]
         if edge.startswith(':'):
             return RING_JUNCTION_LENGTH
         n = len(self.get_edge_list())

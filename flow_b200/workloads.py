@@ -93,7 +93,22 @@ def merge_mg(noise=0.0, speed_mode=SPEED_MODE):
     return types, [], kw
 
 
+def figure8_f8(noise=0.0, speed_mode=SPEED_MODE):
+    """AccelEnv on FigureEightNetwork with the numbers of examples/exp_configs/
+    rl/singleagent/singleagent_figure_eight.py (radius 30, 13 IDM humans + 1 RL vehicle, decel 1.5,
+    target velocity 20, horizon 1500)."""
+    types = [EN.make_vtype(EN.CTRL_IDM, IDM_DEFAULT, noise=noise, speed_mode=speed_mode, max_decel=1.5),
+             EN.make_vtype(EN.CTRL_RL, speed_mode=speed_mode, max_decel=1.5)]
+    kw = dict(topology=EN.TOPO_FIGURE8, env_kind=EN.ENV_ACCEL, fig8_radius=30.0, sim_step=0.1,
+              target_velocity=20.0, horizon=1500, warmup_steps=0, act_lo=-3.0, act_hi=3.0,
+              clip_actions=1)
+    return types, [0] * 13 + [1], kw
+
+
 WORKLOADS = {
+    'f8': dict(builder=figure8_f8, n_envs=4096, n_veh=14,
+               name='AccelEnv on FigureEightNetwork (radius 30), 13 IDM + 1 RL, 4096 envs/GPU, random '
+                    'RL accelerations'),
     'mg': dict(builder=merge_mg, n_envs=1024, n_veh=128,
                name='MergePOEnv on MergeNetwork (500 / 100 / 100 m), inflows 1800 + 200 RL + 100 veh/h, '
                     '5 controlled rows, 5 simulation steps per Env.step, 128 slots, 1024 envs/GPU, '

@@ -167,3 +167,62 @@ def test_figure8_noise_stats_and_validation():
         S.figure8_engine(1, radius=30.0, zone=31.0)
     with pytest.raises(EN.FlowStepError):          # 90 vehicles do not fit on a radius-10 loop
         S.figure8_engine(1, groups=[S.vt('IDM', 90)], radius=10.0).reset()
+
+
+def figure8_flow_params(F, horizon=600, noise=0.0):
+    """examples/exp_configs/rl/singleagent/singleagent_figure_eight.py against module F."""
+    vehicles = F.VehicleParams()
+    vehicles.add(veh_id='human', acceleration_controller=(F.IDMController, {'noise': noise}),
+                 routing_controller=(F.ContinuousRouter, {}),
+                 car_following_params=F.SumoCarFollowingParams(speed_mode='obey_safe_speed', decel=1.5),
+                 num_vehicles=13)
+    vehicles.add(veh_id='rl', acceleration_controller=(F.RLController, {}),
+                 routing_controller=(F.ContinuousRouter, {}),
+                 car_following_params=F.SumoCarFollowingParams(speed_mode='obey_safe_speed', decel=1.5),
+                 num_vehicles=1)
+    return dict(
+        exp_tag='singleagent_figure_eight', env_name=F.AccelEnv, network=F.FigureEightNetwork,
+        simulator='traci', sim=F.SumoParams(sim_step=0.1, render=False),
+        env=F.EnvParams(horizon=horizon, additional_params={
+            'target_velocity': 20, 'max_accel': 3, 'max_decel': 3, 'sort_vehicles': False}),
+        net=F.NetParams(additional_params=dict(F.FIGURE_EIGHT_NET_PARAMS)), veh=vehicles,
+        initial=F.InitialConfig())
+
+
+def test_figure8_env_through_the_flow_api():
+    """make_create_env on singleagent_figure_eight.py-style flow_params against the golden the
+    reference's own classes produced for the same scenario."""
+    import torch
+    from flow_b200 import flow_api as F
+    z = np.load(os.path.join(G, 'figure8.npz'))
+    env = F.make_create_env(figure8_flow_params(F))[0]()
+    assert env.action_space.shape == (1,) and env.observation_space.shape == (28,)
+    obs = env.reset()
+    kv = env.k.vehicle
+    assert [[kv.get_edge(v), kv.get_position(v)] for v in kv.get_ids()] == \
+        [[e, pytest.approx(p, abs=1e-9)] for e, p in CASES[0]['pos']]
+    assert env.k.network.length() == pytest.approx(416.2633388230813, abs=1e-9)
+    for k in range(len(z['actions'])):
+        obs, rew, done, _ = env.step(z['actions'][k])
+        assert close(obs, z['obs'][k]) <= 1e-9 and abs(rew - z['reward'][k]) <= 1e-9, k
+        assert done == bool(z['done'][k]), k
+    assert kv.get_x_by_id('rl_0') == pytest.approx(z['obs'][-1][27] * env.k.network.length(), abs=1e-9)
+    assert kv.get_edge('human_3') in env.k.network.get_edge_list() + env.k.network.get_junction_list()
+    env.terminate()
+    # a batch, noisy humans as in the shipped config; RL vehicle left to the simulator model
+    env = F.make_create_env(figure8_flow_params(F, horizon=300, noise=0.2), n_envs=256, dtype='f32')[0]()
+    env.reset()
+    for s in range(300):
+        obs, rew, done, _ = env.step(None)
+    assert tuple(obs.shape) == (256, 28) and bool(done.all())
+    assert float(env.engine.crash.float().mean()) < 0.05 and float(rew.mean()) > 0.05
+    env.terminate()
+    bad = figure8_flow_params(F)
+    bad['net'].additional_params['lanes'] = 2
+    with pytest.raises(NotImplementedError):
+        F.make_create_env(bad)[0]()
+    bad = figure8_flow_params(F)
+    bad['env_name'] = F.WaveAttenuationPOEnv
+    bad['env'].additional_params['ring_length'] = [220, 270]
+    with pytest.raises(NotImplementedError):
+        F.make_create_env(bad)[0]()
