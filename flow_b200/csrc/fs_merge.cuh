@@ -133,14 +133,18 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
   int my_slot = -1;
   unsigned rl_types = 0;
   for (int t = 0; t < cfg.n_types; ++t) rl_types |= (cfg.types[t].ctrl == FS_CTRL_RL ? 1u : 0u) << t;
-  double st_rew = 0, st_v = 0, st_v2 = 0, st_vs = 0, st_es = 0, st_cr = 0;
+  double st_rew = 0, st_vs = 0, st_es = 0, st_cr = 0;
+  double pl_v = 0, pl_v2 = 0;      // per-lane sums of v and v^2, reduced once at the end
 
   auto u_of = [&](int r) -> T { return arm[r] ? add(x[r], off1) : x[r]; };
   // k.update on the merged axis + slot of every controlled vehicle
+  // (every per-row loop below stops at the last populated slot row: n is warp-uniform, so the
+  //  bound is a uniform branch and the ballots inside stay full-warp)
   auto update = [&]() {
+    const int nrows = (n + 31) >> 5;
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < SLOTS; ++r) {
+    for (int r = 0; r < SLOTS && r < nrows; ++r) {
       const int s = lane_id + 32 * r;
       if (s < n) {
         us[s] = u_of(r); xp[s] = x[r]; vs[s] = v[r]; at[s] = arm[r] | (ty[r] << 8); is[s] = id[r];
@@ -157,7 +161,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     int last0 = -1, last1 = -1, zn0 = 0, zn1 = 0, np0 = 0, np1 = 0;
     bool sorted = true;
 #pragma unroll
-    for (int r = 0; r < SLOTS; ++r) {
+    for (int r = 0; r < SLOTS && r < nrows; ++r) {
       const int s = lane_id + 32 * r;
       const bool on = s < n;
       const T ui = on ? us[s] : T(0);
@@ -184,7 +188,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     __syncwarp();
     if (sorted) {
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) {
+      for (int r = 0; r < SLOTS && r < nrows; ++r) {
         const int s = lane_id + 32 * r;
         int bj = -1; T bd = T(0);
         if (s < n) {
@@ -216,7 +220,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       }
     } else {
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) {
+      for (int r = 0; r < SLOTS && r < nrows; ++r) {
         const int s = lane_id + 32 * r;
         int bj = -1; T bd = T(0);
         if (s < n) {
@@ -237,7 +241,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     }
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < SLOTS; ++r) {
+    for (int r = 0; r < SLOTS && r < nrows; ++r) {
       const int s = lane_id + 32 * r;
       if (s < n) { ld[s] = lead[r]; hs[s] = h[r]; }
     }
@@ -246,7 +250,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     for (int a = 0; a < n_ctrl; ++a) {
       const int cid = __shfl_sync(FULL, my_ctrl, a);
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) {
+      for (int r = 0; r < SLOTS && r < nrows; ++r) {
         const unsigned hit = __ballot_sync(FULL, lane_id + 32 * r < n && id[r] == cid);
         if (hit && lane_id == a) my_slot = 32 * r + __ffs(hit) - 1;
       }
@@ -296,11 +300,12 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     for (int q = 0; q < cfg.sims_per_step; ++q) {
     if (!done) {
       stepped = true;
+      const int nrows = (n + 31) >> 5, mrows = nrows;
       // ---- _apply_rl_actions (merge.py:106-112): action row k -> controlled vehicle k, if it is
       //      still in the network; NaN = no command (the simulator model drives)
       __syncwarp();
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) { const int s = lane_id + 32 * r; if (s < n) cmd[s] = N::nan(); }
+      for (int r = 0; r < SLOTS && r < nrows; ++r) { const int s = lane_id + 32 * r; if (s < n) cmd[s] = N::nan(); }
       __syncwarp();
       if (A.actions != nullptr && lane_id < n_ctrl && my_slot >= 0)
         cmd[my_slot] = A.actions[((size_t)k * cfg.act_dim + lane_id) * E + e];
@@ -309,12 +314,12 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       if (cfg.any_follower & 2) {
         T sm = T(0);
 #pragma unroll
-        for (int r = 0; r < SLOTS; ++r) if (lane_id + 32 * r < n) sm = add(sm, v[r]);
+        for (int r = 0; r < SLOTS && r < nrows; ++r) if (lane_id + 32 * r < n) sm = add(sm, v[r]);
         for (int o = 16; o > 0; o >>= 1) sm += __shfl_xor_sync(FULL, sm, o);
         mean_v = N::div(sm, T(n > 0 ? n : 1));
       }
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) {
+      for (int r = 0; r < SLOTS && r < nrows; ++r) {
         const int s = lane_id + 32 * r;
         if (s >= n) continue;
         const TypeP<T>& tp = cfg.types[ty[r]];
@@ -365,7 +370,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
         if (n_ctrl < AG) {                          // a row is free: the longest-waiting RL vehicles
           int base = n_ctrl;
 #pragma unroll
-          for (int r = 0; r < SLOTS; ++r) {
+          for (int r = 0; r < SLOTS && r < nrows; ++r) {
             const int s = lane_id + 32 * r;
             const bool w = s < n && ((rl_types >> ty[r]) & 1u) && sq[r] > hi_seq;
             const unsigned wm = __ballot_sync(FULL, w);
@@ -391,7 +396,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       int base = 0;
       int dst[SLOTS];
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) {
+      for (int r = 0; r < SLOTS && r < mrows; ++r) {
         const int s = lane_id + 32 * r;
         bool keep = false;
         if (s < n) {
@@ -409,14 +414,14 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       if (n_keep != n) {
         __syncwarp();
 #pragma unroll
-        for (int r = 0; r < SLOTS; ++r)
+        for (int r = 0; r < SLOTS && r < mrows; ++r)
           if (dst[r] >= 0) {
             xp[dst[r]] = x[r]; vs[dst[r]] = v[r]; hs[dst[r]] = acc[r];
             at[dst[r]] = arm[r] | (ty[r] << 8); is[dst[r]] = id[r]; ld[dst[r]] = sq[r];
           }
         __syncwarp();
 #pragma unroll
-        for (int r = 0; r < SLOTS; ++r) {
+        for (int r = 0; r < SLOTS && r < mrows; ++r) {
           const int s = lane_id + 32 * r;
           if (s < n_keep) {
             x[r] = xp[s]; v[r] = vs[s]; acc[r] = hs[s]; arm[r] = at[s] & 0xff; ty[r] = at[s] >> 8;
@@ -425,35 +430,50 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
         }
         n = n_keep;
       }
-      // ---- inflows: earliest scheduled departure first (ties: definition order)
+      // ---- inflows: earliest scheduled departure first (ties: definition order). Everything is
+      //      indexed with compile-time constants (selects over the four flows): no local memory
       {
         const double t = (double)tc * (double)cfg.dt;
         double due[FS_MAX_INFLOWS];
-        bool served[FS_MAX_INFLOWS];
+        unsigned open = 0;
 #pragma unroll
         for (int f = 0; f < FS_MAX_INFLOWS; ++f) {
-          served[f] = !(f < B.n_flows && B.period[f] > 0.0);
-          due[f] = served[f] ? 0.0 : B.begin[f] + (double)spawned[f] * B.period[f];
+          const bool on = f < B.n_flows && B.period[f] > 0.0;
+          due[f] = on ? B.begin[f] + (double)spawned[f] * B.period[f] : 0.0;
+          // a flow that is not due yet (or finds the slots full) can be dropped right away:
+          // serving order only matters among the flows that do emit
+          if (on && t >= due[f]) open |= 1u << f;
         }
 #pragma unroll 1
-        for (int it = 0; it < FS_MAX_INFLOWS; ++it) {
-          int f = -1;
+        while (open != 0 && n < CAP) {
+          int f = -1; double bd = 0.0;
 #pragma unroll
-          for (int q = 0; q < FS_MAX_INFLOWS; ++q) if (!served[q] && (f < 0 || due[q] < due[f])) f = q;
-          if (f < 0) break;
-          served[f] = true;
-          if (!(t >= due[f] && n < CAP)) continue;
+          for (int q = 0; q < FS_MAX_INFLOWS; ++q)
+            if (((open >> q) & 1u) && (f < 0 || due[q] < bd)) { f = q; bd = due[q]; }
+          open &= ~(1u << f);
           const int fa = B.inflow_arm[f];
           const TypeP<T>& nt = cfg.types[B.inflow_type[f]];
           // last vehicle of the arm: smallest distance travelled
           T bx = T(0), bv = T(0); int bt = -1;
 #pragma unroll
-          for (int r = 0; r < SLOTS; ++r)
+          for (int r = 0; r < SLOTS && r < ((n + 31) >> 5); ++r)
             if (lane_id + 32 * r < n && arm[r] == fa && (bt < 0 || x[r] < bx)) { bx = x[r]; bv = v[r]; bt = ty[r]; }
-          for (int o = 16; o > 0; o >>= 1) {
-            const T ox = __shfl_xor_sync(FULL, bx, o), ov = __shfl_xor_sync(FULL, bv, o);
-            const int ot = __shfl_xor_sync(FULL, bt, o);
-            if (ot >= 0 && (bt < 0 || ox < bx)) { bx = ox; bv = ov; bt = ot; }
+          if (sizeof(T) == 4) {
+            // x >= 0: the float's bits order like the float; one REDUX instead of a shuffle tree
+            const unsigned key = bt >= 0 ? __float_as_uint((float)bx) : 0xffffffffu;
+            const unsigned kmin = __reduce_min_sync(FULL, key);
+            const unsigned owners = __ballot_sync(FULL, key == kmin && bt >= 0);
+            if (owners) {
+              const int src = __ffs(owners) - 1;
+              bx = __shfl_sync(FULL, bx, src); bv = __shfl_sync(FULL, bv, src);
+              bt = __shfl_sync(FULL, bt, src);
+            } else bt = -1;
+          } else {
+            for (int o = 16; o > 0; o >>= 1) {
+              const T ox = __shfl_xor_sync(FULL, bx, o), ov = __shfl_xor_sync(FULL, bv, o);
+              const int ot = __shfl_xor_sync(FULL, bt, o);
+              if (ot >= 0 && (bt < 0 || ox < bx)) { bx = ox; bv = ov; bt = ot; }
+            }
           }
           bool spawn = true;
           if (bt >= 0) {   // restated SUMO insertion: gap >= the simulator model's s* at depart speed
@@ -463,22 +483,25 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
             spawn = (bx - cfg.types[bt].length) >= s_star;
           }
           if (spawn) {
+            int sp = 0;
 #pragma unroll
-            for (int r = 0; r < SLOTS; ++r)
+            for (int q = 0; q < FS_MAX_INFLOWS; ++q) if (q == f) { sp = spawned[q]; spawned[q] += 1; }
+#pragma unroll
+            for (int r = 0; r < SLOTS && r < ((n + 32) >> 5); ++r)
               if (lane_id + 32 * r == n) {
                 x[r] = T(0); v[r] = B.depart_speed[f]; ty[r] = B.inflow_type[f]; arm[r] = fa;
-                acc[r] = T(0); id[r] = ((f + 1) << 24) | spawned[f]; sq[r] = next_seq;
+                acc[r] = T(0); id[r] = ((f + 1) << 24) | sp; sq[r] = next_seq;
               }
-            n += 1; spawned[f] += 1; departed += 1; next_seq += 1;
+            n += 1; departed += 1; next_seq += 1;
           }
         }
       }
       update();
       // ---- collision (shared road only), desired_velocity, time-headway penalty
       bool cr = false;
-      T sv = T(0), sqd = T(0), s2 = T(0);
+      T sv = T(0), sqd = T(0);
 #pragma unroll
-      for (int r = 0; r < SLOTS; ++r) {
+      for (int r = 0; r < SLOTS && r < ((n + 31) >> 5); ++r) {
         const int s = lane_id + 32 * r;
         if (s >= n) continue;
         if (lead[r] >= 0 && h[r] < T(0)) {
@@ -488,33 +511,33 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
         sv = add(sv, v[r]);
         const T d = v[r] - cfg.target_velocity;
         sqd = add(sqd, mul(d, d));
-        s2 += v[r] * v[r];
+        if (A.accumulate_stats) pl_v2 += (double)v[r] * (double)v[r];
       }
-      T c2 = T(0);     // merge.py:176-184, t_min = 1
-      if (lane_id < n_ctrl && my_slot >= 0 && ld[my_slot] >= 0 && vs[my_slot] > T(0))
-        c2 = N::min(N::max(N::div(hs[my_slot], vs[my_slot]), T(0)) - T(1), T(0));
-      for (int o = 16; o > 0; o >>= 1) {
-        sv += __shfl_xor_sync(FULL, sv, o);
-        sqd += __shfl_xor_sync(FULL, sqd, o);
-        s2 += __shfl_xor_sync(FULL, s2, o);
-        c2 += __shfl_xor_sync(FULL, c2, o);
-      }
+      if (A.accumulate_stats) { pl_v += (double)sv; if (lane_id == 0) st_vs += n; }
       crash = __any_sync(FULL, cr);
       done = crash || tc >= t_end;
-      if (cfg.evaluate) reward = N::div(sv, T(n));
-      else if (crash) reward = T(0);
-      else {
-        T cost1 = T(0);
-        if (n > 0) {
-          const T mc2 = mul(mul(cfg.target_velocity, cfg.target_velocity), T(n));
-          const T max_cost = N::sqrt(mc2), cost = N::sqrt(sqd);
-          cost1 = N::div(N::max(max_cost - cost, T(0)), add(max_cost, T(1.1920928955078125e-07)));
+      // the reward is read once per Env.step: after the last sub-step or the one that collided
+      if (done || q == cfg.sims_per_step - 1) {
+        T c2 = T(0);     // merge.py:176-184, t_min = 1
+        if (lane_id < n_ctrl && my_slot >= 0 && ld[my_slot] >= 0 && vs[my_slot] > T(0))
+          c2 = N::min(N::max(N::div(hs[my_slot], vs[my_slot]), T(0)) - T(1), T(0));
+        for (int o = 16; o > 0; o >>= 1) {
+          sv += __shfl_xor_sync(FULL, sv, o);
+          sqd += __shfl_xor_sync(FULL, sqd, o);
+          c2 += __shfl_xor_sync(FULL, c2, o);
         }
-        reward = N::max(add(cost1, mul(T(0.1), c2)), T(0));
-      }
-      if (A.accumulate_stats && lane_id == 0) {   // speeds and vehicle-steps of every sub-step,
-        st_v += (double)sv; st_v2 += (double)s2; st_vs += n;   // reward / env-step once (substep_stats)
-        if (done || q == cfg.sims_per_step - 1) { st_rew += (double)reward; st_es += 1; st_cr += crash ? 1 : 0; }
+        if (cfg.evaluate) reward = N::div(sv, T(n));
+        else if (crash) reward = T(0);
+        else {
+          T cost1 = T(0);
+          if (n > 0) {
+            const T mc2 = mul(mul(cfg.target_velocity, cfg.target_velocity), T(n));
+            const T max_cost = N::sqrt(mc2), cost = N::sqrt(sqd);
+            cost1 = N::div(N::max(max_cost - cost, T(0)), add(max_cost, T(1.1920928955078125e-07)));
+          }
+          reward = N::max(add(cost1, mul(T(0.1), c2)), T(0));
+        }
+        if (A.accumulate_stats && lane_id == 0) { st_rew += (double)reward; st_es += 1; st_cr += crash ? 1 : 0; }
       }
     }
     }
@@ -548,6 +571,11 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
       if (A.k_steps > 0) B.v_accel[eo + s] = s < n ? acc[r] : T(0);
     }
   }
+  if (A.accumulate_stats)
+    for (int o = 16; o > 0; o >>= 1) {
+      pl_v += __shfl_xor_sync(FULL, pl_v, o);
+      pl_v2 += __shfl_xor_sync(FULL, pl_v2, o);
+    }
   if (lane_id < AG) B.ctrl_id[(size_t)e * AG + lane_id] = lane_id < n_ctrl ? my_ctrl : -1;
   if (lane_id == 0) {
     B.n_active[e] = n; B.departed[e] = departed; B.arrived[e] = arrived;
@@ -559,8 +587,7 @@ merge_kernel(const __grid_constant__ Cfg<T> cfg, const __grid_constant__ MgBufs<
     B.crash[e] = crash ? 1 : 0;
     B.reward[e] = reward;
     if (A.accumulate_stats) {
-      double vals[6] = {st_rew, st_v, st_v2, st_vs, st_es, st_cr};
-      substep_stats(A.accumulate_stats, vals);
+      double vals[6] = {st_rew, pl_v, pl_v2, st_vs, st_es, st_cr};
       for (int q = 0; q < 6; ++q) if (vals[q] != 0.0) atomicAdd(&stat_stripe(B.stats)[q], vals[q]);
     }
   }

@@ -109,9 +109,9 @@ WORKLOADS = {
     'f8': dict(builder=figure8_f8, n_envs=4096, n_veh=14,
                name='AccelEnv on FigureEightNetwork (radius 30), 13 IDM + 1 RL, 4096 envs/GPU, random '
                     'RL accelerations'),
-    'mg': dict(builder=merge_mg, n_envs=1024, n_veh=128,
+    'mg': dict(builder=merge_mg, n_envs=4096, n_veh=128,
                name='MergePOEnv on MergeNetwork (500 / 100 / 100 m), inflows 1800 + 200 RL + 100 veh/h, '
-                    '5 controlled rows, 5 simulation steps per Env.step, 128 slots, 1024 envs/GPU, '
+                    '5 controlled rows, 5 simulation steps per Env.step, 128 slots, 4096 envs/GPU, '
                     'random accelerations'),
     'mah': dict(builder=highway_ma, n_envs=1024, n_veh=160,
                 name='MultiAgentHighwayPOEnv open 1 km highway, IDM inflow 1600 + RL inflow 400 veh/h, '

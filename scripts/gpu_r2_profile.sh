@@ -25,4 +25,5 @@ cap c5 ring1_hot
 cap c3 ring_ml
 cap c4 highway_kernel
 cap mg merge_kernel
+cap f8 fig8_kernel
 ls -la gpurun_out | grep p2_ | head -30

@@ -16,7 +16,7 @@ CMD = 'python bench.py --no-cpu-baseline --only-fused --target-ms 5 --steps 20 -
 
 def short(name):
     for k in ('ring1_hot_kernel', 'ring1_fast_kernel', 'ring1_kernel', 'ring_reset_kernel',
-              'ring_ml_kernel', 'highway_kernel', 'merge_kernel'):
+              'ring_ml_kernel', 'highway_kernel', 'merge_kernel', 'fig8_kernel'):
         if k in name:
             i = name.index(k)
             return name[i:name.index('(', i)] if '(' in name[i:] else name[i:]
@@ -49,9 +49,9 @@ if os.path.exists(ll):
 
 # 2. full captures -> summary csv + per-env-step traffic / issue figures for bench.py
 KERNEL = {'c2': 'ring1_hot', 'c5': 'ring1_hot', 'c3': 'ring_ml', 'c4': 'highway_kernel',
-          'mg': 'merge_kernel'}
+          'mg': 'merge_kernel', 'f8': 'fig8_kernel'}
 traffic = {}
-for wl in ('c2', 'c5', 'c3', 'c4', 'mg'):
+for wl in ('c2', 'c5', 'c3', 'c4', 'mg', 'f8'):
     raw = os.path.join(G, 'p2_%s_raw.csv' % wl)
     plain = os.path.join(G, 'p2_plain_%s.json' % wl)
     if not (os.path.exists(raw) and os.path.exists(plain)):
@@ -87,8 +87,8 @@ for wl in ('c2', 'c5', 'c3', 'c4', 'mg'):
         'fma_pipe_pct': val('sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active'),
         'alu_pipe_pct': val('sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active'),
         'xu_pipe_pct': val('sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active'),
-        'launch_us_under_ncu': val('gpu__time_duration.sum') if u[h.index('gpu__time_duration.sum')] == 'us'
-        else val('gpu__time_duration.sum') / 1e3,
+        'launch_us_under_ncu': val('gpu__time_duration.sum') * {'ns': 1e-3, 'us': 1.0, 'ms': 1e3, 's': 1e6}.get(
+            u[h.index('gpu__time_duration.sum')], 1e-3),
         'capture': 'profiles/' + name}
 if traffic:
     json.dump(traffic, open(os.path.join(P, 'ncu_traffic.json'), 'w'), indent=1)
