@@ -625,9 +625,20 @@ __global__ void merge_reset_kernel(const __grid_constant__ Cfg<T> cfg, const MgB
 template <typename T>
 static cudaError_t launch_mg_impl(int cap, int grid, int block, size_t smem, cudaStream_t st,
                                   const Cfg<T>& c, const MgBufs<T>& b, const StepArgs<T>& a) {
-  if (cap <= 64) merge_kernel<T, 2><<<grid, block, smem, st>>>(c, b, a);
-  else if (cap <= 128) merge_kernel<T, 4><<<grid, block, smem, st>>>(c, b, a);
-  else merge_kernel<T, 8><<<grid, block, smem, st>>>(c, b, a);
+  // 4 warps x 256 slots in fp64 need more than the 48 KB a kernel gets without opting in
+#define FS_MG(S)                                                                          \
+  do {                                                                                    \
+    if (smem > 48 * 1024) {                                                               \
+      cudaError_t rc = cudaFuncSetAttribute(merge_kernel<T, S>,                           \
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+      if (rc != cudaSuccess) return rc;                                                   \
+    }                                                                                     \
+    merge_kernel<T, S><<<grid, block, smem, st>>>(c, b, a);                               \
+  } while (0)
+  if (cap <= 64) FS_MG(2);
+  else if (cap <= 128) FS_MG(4);
+  else FS_MG(8);
+#undef FS_MG
   return cudaGetLastError();
 }
 template <typename T>

@@ -115,6 +115,12 @@ def test_merge_capacity_classes_and_empty_network():
         obs_seq = torch.empty(60, 2, 15, device='cuda', dtype=torch.float64)
         eng.step(a, k=60, obs_seq=obs_seq)
         assert close(obs_seq.cpu().numpy()[:, 1], z['obs'][:60]) <= 1e-9, cap
+    # 4-warp blocks x 256 slots in fp64: more than 48 KB of dynamic shared memory per block
+    big = S.merge_engine(1500, 'f64', capacity=256)
+    a = torch.tensor(np.repeat(z['actions'][:20, :, None], 1500, 2), device='cuda')
+    obs_seq = torch.empty(20, 1500, 15, device='cuda', dtype=torch.float64)
+    big.step(a, k=20, obs_seq=obs_seq)
+    assert close(obs_seq.cpu().numpy()[:, 1499], z['obs'][:20]) <= 1e-9
     eng = S.merge_engine(2, 'f64', initial=[])
     sim = S.merge_sim(initial=[])
     for s in range(40):
