@@ -231,6 +231,11 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
     T ac[UNR], an[UNR];
     int j0 = ph;        // first (possibly partial) block starts at slot j0
     int kb = -j0;       // launch-relative step of the block's slot 0
+    // running output pointers of the block's slot 0 (a 64-bit add per block instead of a
+    // 64-bit multiply per step and stream; slots before step 0 are never dereferenced)
+    T* obs_p = obs_b + (ptrdiff_t)kb * (ptrdiff_t)obs_st;
+    T* rew_p = rew_b + (ptrdiff_t)kb * (ptrdiff_t)rew_st;
+    uint8_t* done_p = done_b + (ptrdiff_t)kb * (ptrdiff_t)done_st;
 #pragma unroll
     for (int j = 0; j < UNR; ++j) { ac[j] = T(0); an[j] = (kAct && is_rl) ? ld_act(kb + j) : T(0); }
 
@@ -346,19 +351,19 @@ ring1_hot_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const 
           }
           // ---- per-step outputs
           if (seq_on) {
-            const unsigned s = (unsigned)(kb + j);
             if (wr && sel) {
               T o0, o1, o2; po_obs(o0, o1, o2);
-              T* o = obs_b + (size_t)s * obs_st;
+              T* o = obs_p + (unsigned)j * obs_st;
               o[0] = o0; o[1] = o1; o[2] = o2;
-              rew_b[(size_t)s * rew_st] = reward;
-              done_b[(size_t)s * done_st] = done ? 1 : 0;
+              rew_p[(unsigned)j * rew_st] = reward;
+              done_p[(unsigned)j * done_st] = done ? 1 : 0;
             }
           }
         }
       }
       kb += UNR;
       j0 = 0;
+      obs_p += (unsigned)UNR * obs_st; rew_p += (unsigned)UNR * rew_st; done_p += (unsigned)UNR * done_st;
     }
   }
 
