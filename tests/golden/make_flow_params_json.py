@@ -28,15 +28,23 @@ def ref_api():
         RLController=rc.RLController, ContinuousRouter=rc.ContinuousRouter,
         WaveAttenuationPOEnv=re_.WaveAttenuationPOEnv, RingNetwork=rn.RingNetwork,
         AccelEnv=re_.AccelEnv, HighwayNetwork=rn.HighwayNetwork,
-        MultiAgentWaveAttenuationPOEnv=rm.MultiAgentWaveAttenuationPOEnv)
+        MultiAgentWaveAttenuationPOEnv=rm.MultiAgentWaveAttenuationPOEnv,
+        MergePOEnv=re_.MergePOEnv, MergeNetwork=rn.MergeNetwork,
+        FigureEightNetwork=rn.FigureEightNetwork,
+        MERGE_NET_PARAMS=__import__('flow.networks.merge', fromlist=['x']).ADDITIONAL_NET_PARAMS,
+        FIGURE_EIGHT_NET_PARAMS=__import__('flow.networks.figure_eight',
+                                           fromlist=['x']).ADDITIONAL_NET_PARAMS)
 
 
 def main():
     from tests.test_flow_api import ring_flow_params, c1_flow_params
     from tests.test_rllib_compat import highway_flow_params
+    from tests.test_gpu_merge import merge_flow_params
+    from tests.test_gpu_figure8 import figure8_flow_params
     api = ref_api()
     for name, fp in (('c2', ring_flow_params(api, noise=0.2)), ('c1', c1_flow_params(api)),
-                     ('highway', highway_flow_params(api))):
+                     ('highway', highway_flow_params(api)), ('merge', merge_flow_params(api)),
+                     ('figure8', figure8_flow_params(api, noise=0.2))):
         txt = json.dumps(fp, cls=FlowParamsEncoder, sort_keys=True, indent=4)
         open(os.path.join(HERE, 'flow_params_%s.json' % name), 'w').write(txt)
         print(name, len(txt))

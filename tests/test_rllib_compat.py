@@ -9,6 +9,8 @@ import pytest
 from flow_b200 import flow_api as F
 from flow_b200 import rllib_compat as RC
 from tests.test_flow_api import c1_flow_params, ring_flow_params, spec_of, struct_bytes
+from tests.test_gpu_figure8 import figure8_flow_params
+from tests.test_gpu_merge import merge_flow_params
 
 G = os.path.join(os.path.dirname(__file__), 'golden')
 
@@ -35,7 +37,9 @@ def same_spec(a, b):
 
 
 @pytest.mark.parametrize('mk', [lambda: ring_flow_params(noise=0.2), c1_flow_params,
-                                highway_flow_params], ids=['c2', 'c1', 'highway'])
+                                highway_flow_params, lambda: merge_flow_params(F),
+                                lambda: figure8_flow_params(F, noise=0.2)],
+                         ids=['c2', 'c1', 'highway', 'merge', 'figure8'])
 def test_round_trip_through_json(mk, tmp_path):
     fp = mk()
     txt = RC.dump_flow_params(fp, str(tmp_path / 'flow_params.json'))
@@ -51,7 +55,9 @@ def test_round_trip_through_json(mk, tmp_path):
 
 
 @pytest.mark.parametrize('name,mk', [('c2', lambda: ring_flow_params(noise=0.2)),
-                                     ('c1', c1_flow_params), ('highway', highway_flow_params)])
+                                     ('c1', c1_flow_params), ('highway', highway_flow_params),
+                                     ('merge', lambda: merge_flow_params(F)),
+                                     ('figure8', lambda: figure8_flow_params(F, noise=0.2))])
 def test_reads_files_written_by_the_reference_encoder(name, mk):
     """tests/golden/flow_params_*.json were produced by the reference's own
     FlowParamsEncoder from its own classes (make_flow_params_json.py)."""
