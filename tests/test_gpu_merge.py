@@ -300,3 +300,16 @@ def test_merge_env_batched_and_error_cases():
     bad['net'] = F.NetParams(additional_params=dict(F.RING_NET_PARAMS))
     with pytest.raises(NotImplementedError):
         F.make_create_env(bad)[0]()
+
+
+def test_experiment_runs_on_the_junction_networks(capsys):
+    """flow/core/experiment.py's loop (returns, mean speeds, outflow) over MergePOEnv and over
+    AccelEnv on the figure eight, RL vehicles left to the simulator model."""
+    from flow_b200 import flow_api as F
+    from tests.test_gpu_figure8 import figure8_flow_params
+    info = F.Experiment(merge_flow_params(F, horizon=80)).run(1)
+    assert len(info['returns']) == 1 and info['returns'][0] > 0 and info['velocities'][0] > 1.0
+    assert info['outflows'][0] >= 0
+    info = F.Experiment(figure8_flow_params(F, horizon=80)).run(2)
+    assert len(info['returns']) == 2 and info['returns'][0] == info['returns'][1] > 0
+    assert 'Average, std returns' in capsys.readouterr().out
