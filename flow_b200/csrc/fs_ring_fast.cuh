@@ -177,8 +177,9 @@ __device__ __forceinline__ T speed_mode_fast(T a, T v, T v_l, T h, bool has_lead
 
 // fp32 only: the controller's IDM and the simulator model's IDM (the safe speed of the speed
 // mode) on the same (v, v_lead, h), sharing the |h| clamp, ONE reciprocal of h and v (v - v_lead);
-// both with delta = 4. Same values as two idm_fast<float, true> calls (x / h there is
-// x * rcp(h) too), about 10 instructions instead of 16 for the second law and no second MUFU.
+// both with delta = 4. The values of two idm_fast<float, true> calls up to fp32 rounding (x / h there
+// is x * rcp(h) too; (v / v0)^4 is v^4 * (1 / v0^4) here), about 9 instructions instead of 16 for
+// the second law and no second MUFU.
 __device__ __forceinline__ void idm_pair_f32(float v, float v_lead, float h, const IdmRegs<float>& p,
                                              const IdmRegs<float>& q, float& a_p, float& a_q,
                                              bool has_lead = true) {
@@ -188,11 +189,13 @@ __device__ __forceinline__ void idm_pair_f32(float v, float v_lead, float h, con
   // no leader: s* = 0 (car_following_models.py:474-480)
   const float sp = has_lead ? p.s0 + fmaxf(0.0f, v * p.Tt + vv * p.inv_tsab) : 0.0f;
   const float sq = has_lead ? q.s0 + fmaxf(0.0f, v * q.Tt + vv * q.inv_tsab) : 0.0f;
-  const float rp = v * p.inv_v0, rq = v * q.inv_v0;
-  const float rp2 = rp * rp, rq2 = rq * rq;
+  // (v / v0)^4 of both laws from ONE v^4: the 1 / v0^4 are loop-invariant constants
+  const float v2 = v * v, v4 = v2 * v2;
+  const float cp = (p.inv_v0 * p.inv_v0) * (p.inv_v0 * p.inv_v0);
+  const float cq = (q.inv_v0 * q.inv_v0) * (q.inv_v0 * q.inv_v0);
   const float hp = sp * ih, hq = sq * ih;
-  a_p = p.a * ((1.0f - rp2 * rp2) - hp * hp);
-  a_q = q.a * ((1.0f - rq2 * rq2) - hq * hq);
+  a_p = p.a * (fmaf(-v4, cp, 1.0f) - hp * hp);
+  a_q = q.a * (fmaf(-v4, cq, 1.0f) - hq * hq);
 }
 
 // sum over the threads of one env group. fp32: integer REDUX in 2^-20 fixed
