@@ -739,9 +739,11 @@ static int run_steps(fs_engine* e, const fs::StepArgs<T>& a) {
       shape = 1;
       while (shape < 32 && (long long)E * shape < 32768) shape <<= 1;
     }
-    // one thread per env is never picked automatically: 22 fp64 slots spill, and in fp32 two
-    // threads x 11 vehicles measured 4.09 against 3.95 x 10^11 on c5 (twice the warps to hide latency)
-    if (shape == 1 && e->ring_shape == 0) shape = 2;
+    // fp32 keeps one thread per env for the largest batches although two threads x 11 vehicles
+    // fuse 3.6 % faster on c5 (4.09 against 3.95 x 10^11): the one-step-per-launch variant of the
+    // same engine is HBM-bound and loses 11 % with it (0.43 -> 0.38 of the measured HBM peak),
+    // and the noise stream's counter layout is per shape, so both variants must share one
+    if (sizeof(T) == 8 && shape == 1 && e->ring_shape == 0) shape = 2;  // f64 x 22 slots spills
     if (e->hot_ok && !e->no_hot) {   // c2 / c5 configuration: fully specialised kernel
       FS_CUDA(e, launch_hot(shape, e->hot_noise, E, e->stream,
                             fs::make_fastp(cfg_of<T>(e)), ring_bufs<T>(e), a));

@@ -38,7 +38,7 @@ def auto_shape(n_envs, f64=False):
     g = 1
     while g < 32 and n_envs * g < 32768:
         g <<= 1
-    if g == 1:          # never one thread per env on its own (f64 spills; fp32 measured slower)
+    if f64 and g == 1:
         g = 2
     return g
 

@@ -26,5 +26,5 @@ def test_stream_is_standard_normal_and_keyed_by_env_episode_vehicle():
 
 def test_shape_tables_follow_the_engine():
     assert [vpt_of_shape(g) for g in (1, 2, 4, 8, 16, 32)] == [22, 11, 6, 3, 2, 1]
-    assert auto_shape(4096) == 8 and auto_shape(65536) == 2 and auto_shape(65536, f64=True) == 2
+    assert auto_shape(4096) == 8 and auto_shape(65536) == 1 and auto_shape(65536, f64=True) == 2
     assert auto_shape(5) == 32
