@@ -134,3 +134,32 @@ def test_fuzz_figure8_vs_oracle_fp64(seed):
         check_state(eng, 1, sim, 1e-9, tag)
         assert close(obs[0].cpu().numpy(), o_obs) <= 1e-9 and close(rew[1].item(), o_rew) <= 1e-9, tag
         assert bool(done[0].item()) == o_done and bool(eng.crash[1].item()) == sim.crash, tag
+
+
+@pytest.mark.parametrize('net', ['merge', 'figure8'])
+def test_fp32_aggregates_within_one_percent_of_fp64(net):
+    """Free-running fp32 against fp64 over a whole episode (no re-synchronisation): mean speed
+    and mean reward of 64 envs agree within 1 % (BASELINE.json's aggregate bar)."""
+    import torch
+    E = 64
+    rng = np.random.default_rng(3)
+    out = {}
+    for dtype in ('f64', 'f32'):
+        td = torch.float64 if dtype == 'f64' else torch.float32
+        if net == 'merge':
+            eng = S.merge_engine(E, dtype, initial=[], warmup_steps=40, horizon=260)
+            K, A = 260, 3
+        else:
+            eng = S.figure8_engine(E, dtype, horizon=1500)
+            eng.reset()
+            K, A = 1500, 1
+        acts = torch.tensor(np.random.default_rng(17).uniform(-0.5, 1.0, (K, A, E)), device='cuda', dtype=td)
+        eng.stats(reset=True)
+        eng.step(acts, k=K)
+        st = eng.stats()
+        out[dtype] = (st['sum_speed'] / st['vehicle_steps'], st['sum_reward'] / st['env_steps'],
+                      st['crashes'], st['vehicle_steps'])
+    (v64, r64, c64, n64), (v32, r32, c32, n32) = out['f64'], out['f32']
+    assert c64 == c32 == 0
+    assert abs(v32 - v64) <= 0.01 * v64 and abs(r32 - r64) <= 0.01 * r64, out
+    assert abs(n32 - n64) <= 0.01 * n64
