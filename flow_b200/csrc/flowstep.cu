@@ -26,7 +26,7 @@ struct fs_engine {
   bool types_set = false;
   bool generic = false;   // some controller is not IDM/SIM/RL
   bool fast_ok = false;   // fs_ring_fast.cuh applies (see fs_set_types)
-  int fast_variant = 0;   // 0 plain, 1 noise, 2 noise+fail-safe, 3 = 2 + views
+  int fast_variant = 0;   // 0 plain, 1 noise, 2 noise+fail-safe+speed mode, 3 = 2 + views, 4 = noise+speed mode
   bool ml_uniform = false;  // multi-lane kernel: one IDM-law human type + at most one RL type
   int cl_mode = 0;                // FS_CL_MODE at fs_create: zero-copy bits of the closed-loop host step
   bool ml_force_generic = false;  // FS_ML_GENERIC=1 at fs_create: table-driven instantiation (A/B tests)
@@ -456,12 +456,12 @@ extern "C" int fs_set_types(fs_engine* e, const fs_vtype* types, int n_types,
       e->fast_variant = e->cfg.record_views ? 3
                         : (!sim && s.fail_safe != FS_FAILSAFE_NONE) ? 2
                         : (!sim && s.noise > 0) ? 1 : 0;
-      if (e->fast_variant > 1) e->hot_ok = false;
+      if (e->fast_variant > 1) e->hot_ok = false;   // (before the speed mode picks variant 4)
       // a SUMO speed mode on some type: the fast kernel applies it in its fail-safe variants,
       // the hot kernel in its kSafe instantiations
       const bool any_mode = (!sim && (s.speed_mode & 7) != 0) ||
                             (tb >= 0 && (types[tb].speed_mode & 7) != 0);
-      if (any_mode && e->fast_variant < 2) e->fast_variant = 2;
+      if (any_mode && e->fast_variant < 2) e->fast_variant = 4;   // speed mode, no fail-safe code
       e->hot_noise = !sim && s.noise > 0;
     }
   }

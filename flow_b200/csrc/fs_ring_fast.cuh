@@ -211,7 +211,8 @@ __device__ __forceinline__ T env_sum(T part, unsigned gmask) {
 }
 
 
-template <typename T, int VPT, int G, bool kExact, bool kNoise, bool kFS, bool kViews>
+// kFS: fail-safe and / or speed mode compiled in; kFail: the fail-safe itself (false: speed mode only)
+template <typename T, int VPT, int G, bool kExact, bool kNoise, bool kFS, bool kViews, bool kFail = true>
 __global__ void __launch_bounds__(128)
 ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const StepArgs<T> A) {
   typedef Num<T> N;
@@ -352,6 +353,8 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
   uint8_t* done_k = A.done_seq + (w_done ? e : 0);
   const size_t obs_stride = (size_t)E * P.obs_dim;
   const bool st_on = A.accumulate_stats && valid;
+  // a second law is evaluated next to the controller's (see the step body)
+  const bool two_laws = (kFS && P.any_speed_mode) || P.n_rl > 0;
 
   for (int k = 0; k < K; ++k) {
     // ---- RL action of this step (block of 4 promoted every 4th step; next block requested)
@@ -409,19 +412,43 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
         T vl;
         if (j + 1 < VPT) vl = (kExact || j + 1 < n_mine) ? v[j + 1 < VPT ? j + 1 : 0] : v_lead_last;
         else vl = v_lead_last;
-        T a = idm_fast<T, true>(vi, vl, hi, pm);
-        T a_rl = a;
-        if (VPT > 1 && rlj && !have_act) a_rl = idm_fast<T, true>(vi, vl, hi, P.pb);
+        // fp32: ONE evaluation of two laws per vehicle - the controller's and law q, which is
+        // the simulator model behind a human's speed mode (P.ps) or, in an RL vehicle's slot,
+        // the RL type's own model (P.pb: it drives the vehicle while it has no command and is
+        // the safe speed of a commanded one). fp64 keeps the separate evaluations, whose
+        // operation order is the reference's.
+        T a, a_q = T(0), a_rl;
+        if (kF32 && two_laws) {
+          IdmRegs<float> q;
+          const IdmRegs<float>& qa = reinterpret_cast<const IdmRegs<float>&>(P.ps);
+          const IdmRegs<float>& qb = reinterpret_cast<const IdmRegs<float>&>(P.pb);
+          q.s0 = rlj ? qb.s0 : qa.s0; q.Tt = rlj ? qb.Tt : qa.Tt; q.inv_tsab = rlj ? qb.inv_tsab : qa.inv_tsab;
+          q.inv_v0 = rlj ? qb.inv_v0 : qa.inv_v0; q.a = rlj ? qb.a : qa.a;
+          float af, aqf;
+          idm_pair_f32((float)vi, (float)vl, (float)hi, reinterpret_cast<const IdmRegs<float>&>(pm), q, af, aqf);
+          a = (T)af; a_q = (T)aqf;
+          a_rl = a_q;
+        } else {
+          a = idm_fast<T, true>(vi, vl, hi, pm);
+          a_rl = a;
+          if (VPT > 1 && rlj && !have_act) a_rl = idm_fast<T, true>(vi, vl, hi, P.pb);
+        }
         if (kNoise) a = add(a, mul(VPT == 1 ? noise_m : P.noise, zs[kNoise ? j : 0]));
-        if (kFS) {  // base_controller.py:113-116
+        if (kFS && kFail) {  // base_controller.py:113-116
           if (P.fail_safe == FS_FAILSAFE_INSTANTANEOUS)
             a = failsafe_instantaneous<T>(a, vi, hi, true, V, dt);
           else if (P.fail_safe == FS_FAILSAFE_SAFE_VELOCITY)
             a = failsafe_safe_velocity<T>(a, vi, vl, hi, V, dt, P.delay);
         }
         T a_h = a;          // what moves a human (after SUMO's speed mode, restated)
-        if (kFS && P.any_speed_mode)
-          a_h = speed_mode_fast<T>(a, vi, vl, hi, true, P.ps, P.safe_a, P.cap_a, P.floor_a);
+        if (kFS && P.any_speed_mode) {
+          if (kF32) {
+            if (P.safe_a) a_h = N::min(a_h, a_q);
+            a_h = N::max(N::min(a_h, P.cap_a), P.floor_a);
+          } else {
+            a_h = speed_mode_fast<T>(a, vi, vl, hi, true, P.ps, P.safe_a, P.cap_a, P.floor_a);
+          }
+        }
         T a_rl_eff = a_rl;
         if (have_act) {
           // Env.apply_rl_actions: Box clip, then apply_acceleration (base.py:599-615)
@@ -433,8 +460,14 @@ ring1_fast_kernel(const __grid_constant__ FastP<T> P, const RingBufs<T> B, const
           const T aa = N::abs(P.clip_actions ? a_rl : raw);
           act_abs_sum = rlj ? add(act_abs_sum, aa) : act_abs_sum;
           a_rl_eff = a_rl;
-          if (kFS && P.any_speed_mode)
-            a_rl_eff = speed_mode_fast<T>(a_rl, vi, vl, hi, true, P.pb, P.safe_b, P.cap_b, P.floor_b);
+          if (kFS && P.any_speed_mode) {
+            if (kF32) {
+              if (P.safe_b) a_rl_eff = N::min(a_rl_eff, a_q);
+              a_rl_eff = N::max(N::min(a_rl_eff, P.cap_b), P.floor_b);
+            } else {
+              a_rl_eff = speed_mode_fast<T>(a_rl, vi, vl, hi, true, P.pb, P.safe_b, P.cap_b, P.floor_b);
+            }
+          }
         }
         a = rlj ? a_rl : a;                       // commanded (the `accel` view)
         const T a_mv = rlj ? a_rl_eff : a_h;
@@ -542,13 +575,15 @@ static cudaError_t launch_fast_shape(int variant, int grid, int block, cudaStrea
     case 0: ring1_fast_kernel<T, VPT, G, kExact, false, false, false><<<grid, block, 0, st>>>(c, b, a); break;
     case 1: ring1_fast_kernel<T, VPT, G, kExact, true, false, false><<<grid, block, 0, st>>>(c, b, a); break;
     case 2: ring1_fast_kernel<T, VPT, G, kExact, true, true, false><<<grid, block, 0, st>>>(c, b, a); break;
+    case 4: ring1_fast_kernel<T, VPT, G, kExact, true, true, false, false><<<grid, block, 0, st>>>(c, b, a); break;
     default: ring1_fast_kernel<T, VPT, G, kExact, true, true, true><<<grid, block, 0, st>>>(c, b, a); break;
   }
   return cudaGetLastError();
 }
 
 // shape = threads per env (1, 2, 4, 8, 16, 32) for V = 22; variant: 0 plain,
-// 1 noise, 2 noise + fail-safe, 3 = 2 + views (accel / headway / leader / follower)
+// 1 noise, 2 noise + fail-safe + speed mode, 3 = 2 + views (accel / headway / leader / follower),
+// 4 = noise + speed mode without the fail-safe code (what the reference's default mode 25 needs)
 template <typename T>
 static cudaError_t launch_fast22(int shape, int variant, int n_envs, cudaStream_t st,
                                  const FastP<T>& c, const RingBufs<T>& b, const StepArgs<T>& a) {
